@@ -1,0 +1,97 @@
+"""ctypes binding of libaqua_b200.so (include/aqua_b200.h).
+
+The product path has no fallback: if the library is missing or no sm_100 GPU is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+LIB_NAME = "libaqua_b200.so"
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+
+AQ_OK = 0
+AQ_ACT_NONE, AQ_ACT_SILU = 0, 1
+
+
+class AquaError(RuntimeError):
+    pass
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [("src", C.c_int), ("src_c_off", C.c_int), ("c_in", C.c_int),
+                ("dst", C.c_int), ("dst_c_off", C.c_int), ("c_out", C.c_int),
+                ("k", C.c_int), ("stride", C.c_int), ("act", C.c_int),
+                ("res", C.c_int), ("res_c_off", C.c_int),
+                ("weight", C.c_void_p), ("bias", C.c_void_p),
+                ("tile_n", C.c_int), ("chunks_per_stage", C.c_int)]
+
+
+class DetectDesc(C.Structure):
+    _fields_ = [("src", C.c_int), ("src_c_off", C.c_int), ("c_in", C.c_int),
+                ("nc", C.c_int), ("level_row_off", C.c_int), ("stride", C.c_float),
+                ("anchors_px", C.c_float * 6),
+                ("weight", C.c_void_p), ("bias", C.c_void_p)]
+
+
+# name -> (restype, argtypes); every symbol include/aqua_b200.h declares
+SIGNATURES = {
+    "aq_abi_version": (C.c_int, []),
+    "aq_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "aq_destroy": (None, [C.c_void_p]),
+    "aq_last_error": (C.c_char_p, [C.c_void_p]),
+    "aq_plan_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "aq_plan_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "aq_plan_conv": (C.c_int, [C.c_void_p, C.POINTER(ConvDesc)]),
+    "aq_plan_sppf_pool": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "aq_plan_upsample2x": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "aq_plan_detect": (C.c_int, [C.c_void_p, C.POINTER(DetectDesc)]),
+    "aq_plan_end": (C.c_int, [C.c_void_p]),
+    "aq_buffer_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                 C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "aq_pred_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
+    "aq_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "aq_preprocess_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "aq_forward": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "aq_nms": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double, C.c_int, C.c_int,
+                         C.POINTER(C.c_int), C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                         C.c_void_p]),
+    "aq_detect": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
+                            C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "aq_detect_submit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                   C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p,
+                                   C.c_void_p]),
+    "aq_format_labels": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                   C.POINTER(C.c_char_p), C.c_int, C.c_int]),
+    "aq_format_label_text": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
+                                       C.c_size_t]),
+    "aq_memcpy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]),
+    "aq_sync": (C.c_int, [C.c_void_p, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the shared library and bind every declared symbol; raise if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise AquaError(f"{LIB_PATH} is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        f"(or `make -C aquaculture_b200/csrc`). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing: loud by design
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(lib, ctx, rc: int, what: str) -> int:
+    if rc < 0:
+        msg = lib.aq_last_error(ctx)
+        raise AquaError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+    return rc

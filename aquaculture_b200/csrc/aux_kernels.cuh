@@ -1,0 +1,33 @@
+// Bandwidth-bound helper kernels of the tile path: letterbox/normalise, SPPF pooling, nearest upsample.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace aq {
+
+struct PreParams {
+  const uint8_t* src;  // (n, in_h, in_w, 3) uint8
+  int n, in_h, in_w, bgr;
+  int net_h, net_w;    // letterboxed size (multiples of 32)
+  int new_h, new_w;    // resized (unpadded) size
+  int top, left;       // padding offsets
+  int resize;          // 0: copy, 1: bilinear (cv2 INTER_LINEAR fixed point)
+  // per destination column / row (resize == 1): source indices and 11-bit weights
+  const int* x0; const int* x1; const short* ax0; const short* ax1;
+  const int* y0; const int* y1; const short* ay0; const short* ay1;
+  __half* out_s2d;     // (n, net_h/2, net_w/2, 16) fp16, channel (py*2+px)*3 + rgb, 12..15 = 0
+  uint8_t* out_u8;     // (n, net_h, net_w, 3) RGB, optional debug/parity output
+};
+
+cudaError_t launch_preprocess(const PreParams& p, cudaStream_t stream);
+cudaError_t launch_preprocess_u8(const PreParams& p, cudaStream_t stream);
+
+// SPPF: three chained 5x5/s1/p2 max pools of channels [c_off, c_off+c) written to the next three slices.
+cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream);
+cudaError_t sppf_init();
+// nearest 2x upsample of a channel slice into a channel slice of the destination
+cudaError_t launch_upsample2x(const __half* src, int n, int h, int w, int src_ct, int src_c_off, int c, __half* dst,
+                              int dst_ct, int dst_c_off, cudaStream_t stream);
+
+}  // namespace aq

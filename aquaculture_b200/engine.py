@@ -1,0 +1,320 @@
+"""Host-side mirror of the reference's model wiring for the tile path.
+
+`TileDetector` plays the role of upstream `DetectMultiBackend` + `DetectionModel._forward_once` +
+`non_max_suppression` as `yolov5/detect.py` drives them [REF README.md:77; UPSTREAM-RECALLED SURVEY.md
+§3.1-3.2], but it only *plans* the graph: every arithmetic step runs in libaqua_b200.so (hand-written
+sm_100a CUDA behind the C ABI in include/aqua_b200.h).  torch is used for weight tensors and pinned
+host memory only.  There is no CPU or torch execution path; a missing library or GPU raises.
+
+Graph rewrites done here (all exact):
+  * BN folded into conv weights/bias in fp32, then cast to fp16 (`weights.fold_bn`);
+  * 6x6/s2 stem == 3x3/s1 conv over the 2x2 space-to-depth input (12 -> 16 channels), which the
+    preprocess kernel writes directly;
+  * C3.cv1 and C3.cv2 read the same tensor -> one GEMM with N = 2c_;
+  * torch.cat / Concat never copy: producers write into channel slices of the consumer's buffer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib, arch, weights
+from ._lib import AQ_ACT_NONE, AQ_ACT_SILU, AquaError, ConvDesc, DetectDesc
+
+MAX_WH = 7680.0   # upstream non_max_suppression: class offset (pixels)
+MAX_NMS = 30000   # upstream non_max_suppression: boxes into torchvision.ops.nms
+
+
+def pack_krsc(w_oihw: torch.Tensor) -> np.ndarray:
+    """OIHW fp32 -> [O][kh][kw][I] fp16 bits (uint16), contiguous."""
+    return np.ascontiguousarray(w_oihw.permute(0, 2, 3, 1).contiguous().half().numpy().view(np.uint16))
+
+
+def pack_stem_s2d(w_oihw: torch.Tensor) -> torch.Tensor:
+    """6x6/s2/p2 stem weights (O,3,6,6) -> equivalent 3x3/s1/p1 weights (O,16,3,3) over the space-to-depth
+    input whose channel is (py*2+px)*3 + rgb: W2[o, (py*2+px)*3+c, a, b] = W[o, c, 2a+py, 2b+px]."""
+    o = w_oihw.shape[0]
+    w2 = torch.zeros(o, 16, 3, 3, dtype=w_oihw.dtype)
+    for py in range(2):
+        for px in range(2):
+            for c in range(3):
+                w2[:, (py * 2 + px) * 3 + c] = w_oihw[:, c, py::2, px::2]
+    return w2
+
+
+class Context:
+    """Owns one aq_ctx."""
+
+    def __init__(self, device: int = 0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.aq_create(device, C.byref(h))
+        if rc < 0:
+            raise AquaError(f"aq_create(device={device}) failed ({rc}): {self.lib.aq_last_error(None).decode()}")
+        self.h = h
+        self.device = device
+        self._keep = []  # host arrays referenced by descriptors until plan_end
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.aq_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def call(self, name: str, *args) -> int:
+        return _lib.check(self.lib, self.h, getattr(self.lib, name)(self.h, *args), name)
+
+    # ---- plan helpers
+    def plan_begin(self, batch, net_h, net_w, nc):
+        self.call("aq_plan_begin", batch, net_h, net_w, nc)
+
+    def buffer(self, h, w, c) -> int:
+        return self.call("aq_plan_buffer", h, w, c)
+
+    def conv(self, src, dst, w_oihw: torch.Tensor, bias: torch.Tensor, k, stride, act=True, res=None,
+             tile_n=0, chunks_per_stage=0):
+        """src/dst/res are (buffer id, channel offset); w_oihw fp32 (O,I,k,k)."""
+        wk = pack_krsc(w_oihw)
+        b = np.ascontiguousarray(bias.float().numpy())
+        self._keep += [wk, b]
+        d = ConvDesc(src[0], src[1], w_oihw.shape[1], dst[0], dst[1], w_oihw.shape[0], k, stride,
+                     AQ_ACT_SILU if act else AQ_ACT_NONE, res[0] if res else -1, res[1] if res else 0,
+                     wk.ctypes.data, b.ctypes.data, tile_n, chunks_per_stage)
+        self.call("aq_plan_conv", C.byref(d))
+
+    def detect_level(self, src, w_oi: torch.Tensor, bias: torch.Tensor, nc, level_row_off, stride, anchors_px):
+        wk = np.ascontiguousarray(w_oi.reshape(w_oi.shape[0], -1).half().numpy().view(np.uint16))
+        b = np.ascontiguousarray(bias.float().numpy())
+        self._keep += [wk, b]
+        d = DetectDesc(src[0], src[1], wk.shape[1], nc, level_row_off, float(stride),
+                       (C.c_float * 6)(*[float(a) for a in anchors_px]), wk.ctypes.data, b.ctypes.data)
+        self.call("aq_plan_detect", C.byref(d))
+
+    def plan_end(self):
+        self.call("aq_plan_end")
+        self._keep = []
+
+    def buffer_info(self, buf) -> Tuple[int, Tuple[int, int, int, int]]:
+        p = C.c_void_p()
+        n, h, w, c = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        self.call("aq_buffer_info", buf, C.byref(p), C.byref(n), C.byref(h), C.byref(w), C.byref(c))
+        return p.value, (n.value, h.value, w.value, c.value)
+
+    def upload(self, buf: int, arr: np.ndarray):
+        """NHWC fp16 numpy -> planned buffer."""
+        ptr, shape = self.buffer_info(buf)
+        assert tuple(arr.shape) == shape and arr.dtype == np.float16, (arr.shape, shape, arr.dtype)
+        arr = np.ascontiguousarray(arr)
+        self.call("aq_memcpy", C.c_void_p(ptr), arr.ctypes.data, arr.nbytes, 0, None)
+        self.call("aq_sync", None)
+
+    def download(self, buf: int) -> np.ndarray:
+        ptr, shape = self.buffer_info(buf)
+        out = np.empty(shape, np.float16)
+        self.call("aq_memcpy", out.ctypes.data, C.c_void_p(ptr), out.nbytes, 1, None)
+        self.call("aq_sync", None)
+        return out
+
+    def forward(self):
+        self.call("aq_forward", None)
+
+    def sync(self):
+        self.call("aq_sync", None)
+
+    def pred(self) -> np.ndarray:
+        p = C.c_void_p()
+        rows, no = C.c_int(), C.c_int()
+        self.call("aq_pred_info", C.byref(p), C.byref(rows), C.byref(no))
+        _, (n, _, _, _) = self.buffer_info(0)
+        out = np.empty((n, rows.value, no.value), np.float32)
+        self.call("aq_memcpy", out.ctypes.data, p, out.nbytes, 1, None)
+        self.call("aq_sync", None)
+        return out
+
+
+def nms_device(ctx: Context, pred: torch.Tensor, conf_thres=0.25, iou_thres=0.45, max_det=1000, agnostic=False,
+               classes: Optional[Sequence[int]] = None, max_wh=MAX_WH, max_nms=MAX_NMS):
+    """Standalone batched NMS on a CUDA fp32 tensor (B, rows, no) -> (dets (B,max_det,6), counts (B), keep_rows)."""
+    assert pred.is_cuda and pred.dtype == torch.float32 and pred.is_contiguous()
+    b, rows, no = pred.shape
+    dets = torch.zeros(b, max_det, 6, device=pred.device)
+    counts = torch.zeros(b, dtype=torch.int32, device=pred.device)
+    keep = torch.full((b, max_det), -1, dtype=torch.int32, device=pred.device)
+    cls_arr = (C.c_int * len(classes))(*classes) if classes else None
+    torch.cuda.synchronize()
+    ctx.call("aq_nms", C.c_void_p(pred.data_ptr()), b, rows, no, float(conf_thres), float(iou_thres), max_det,
+             int(agnostic), cls_arr, len(classes) if classes else 0, float(max_wh), max_nms,
+             C.c_void_p(dets.data_ptr()), C.c_void_p(counts.data_ptr()), C.c_void_p(keep.data_ptr()), None)
+    ctx.sync()
+    return dets, counts, keep
+
+
+@dataclass
+class Detections:
+    dets: np.ndarray    # (n, max_det, 6) fp32: x1,y1,x2,y2,conf,cls in letterboxed pixels, descending conf
+    counts: np.ndarray  # (n,) int32
+
+
+class TileDetector:
+    """YOLOv5m over batches of equally-sized tiles on one B200."""
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], nc: int, batch: int = 64, imgsz=(640, 640),
+                 device: int = 0, conf_thres=0.25, iou_thres=0.45, max_det=1000, agnostic=False,
+                 classes: Optional[Sequence[int]] = None, ctx=None):
+        self.nc, self.batch = nc, batch
+        self.net_h, self.net_w = int(imgsz[0]), int(imgsz[1])
+        self.conf_thres, self.iou_thres, self.max_det = float(conf_thres), float(iou_thres), int(max_det)
+        self.agnostic, self.classes = bool(agnostic), list(classes) if classes else None
+        self.ctx = ctx if ctx is not None else Context(device)   # `ctx` lets tests inject the plan emulator
+        self._build(state_dict)
+        self._dets = self._counts = None  # pinned host staging, double-buffered, allocated on first use
+        self._slot = 0
+
+    # ------------------------------------------------------------------ plan
+    def _build(self, sd):
+        ctx, nc = self.ctx, self.nc
+        H, W, B = self.net_h, self.net_w, self.batch
+        fw = weights.fold_bn(sd, nc)
+        ctx.plan_begin(B, H, W, nc)
+        buf = ctx.buffer
+        b_in = buf(H // 2, W // 2, 16)
+        x0 = buf(H // 2, W // 2, 48)
+        x1 = buf(H // 4, W // 4, 96)
+        x2 = buf(H // 4, W // 4, 96)
+        x3 = buf(H // 8, W // 8, 192)
+        cat16 = buf(H // 8, W // 8, 384)    # [up(L14) | L4]
+        x5 = buf(H // 16, W // 16, 384)
+        cat12 = buf(H // 16, W // 16, 768)  # [up(L10) | L6]
+        x7 = buf(H // 32, W // 32, 768)
+        x8 = buf(H // 32, W // 32, 768)
+        sppf = buf(H // 32, W // 32, 1536)
+        x9 = buf(H // 32, W // 32, 768)
+        cat22 = buf(H // 32, W // 32, 768)  # [L21 | L10]
+        x13 = buf(H // 16, W // 16, 384)
+        cat19 = buf(H // 16, W // 16, 384)  # [L18 | L14]
+        x17 = buf(H // 8, W // 8, 192)
+        x20 = buf(H // 16, W // 16, 384)
+        x23 = buf(H // 32, W // 32, 768)
+        assert b_in == 0
+
+        def conv(name, src, dst, k, s, res=None):
+            w, b = fw[name]
+            ctx.conv(src, dst, w, b, k, s, True, res)
+
+        def c3(idx, src, c1, dst, c2, n, shortcut, hw):
+            c_ = c2 // 2
+            cat = buf(hw[0], hw[1], 2 * c_)
+            tmp = buf(hw[0], hw[1], c_)
+            pre = f"model.{idx}"
+            w1, b1 = fw[pre + ".cv1"]
+            w2, b2 = fw[pre + ".cv2"]
+            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, True)
+            for j in range(n):
+                conv(f"{pre}.m.{j}.cv1", (cat, 0), (tmp, 0), 1, 1)
+                conv(f"{pre}.m.{j}.cv2", (tmp, 0), (cat, 0), 3, 1, res=(cat, 0) if shortcut else None)
+            conv(pre + ".cv3", (cat, 0), dst, 1, 1)
+
+        L = {l.idx: l for l in arch.yolov5m_layers(nc)}
+        # backbone
+        w0, b0 = fw["model.0"]
+        ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, True)
+        conv("model.1", (x0, 0), (x1, 0), 3, 2)
+        c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4))
+        conv("model.3", (x2, 0), (x3, 0), 3, 2)
+        c3(4, (x3, 0), 192, (cat16, 192), 192, L[4].n, True, (H // 8, W // 8))
+        conv("model.5", (cat16, 192), (x5, 0), 3, 2)
+        c3(6, (x5, 0), 384, (cat12, 384), 384, L[6].n, True, (H // 16, W // 16))
+        conv("model.7", (cat12, 384), (x7, 0), 3, 2)
+        c3(8, (x7, 0), 768, (x8, 0), 768, L[8].n, True, (H // 32, W // 32))
+        conv("model.9.cv1", (x8, 0), (sppf, 0), 1, 1)
+        ctx.call("aq_plan_sppf_pool", sppf, 0, 384)
+        conv("model.9.cv2", (sppf, 0), (x9, 0), 1, 1)
+        # head
+        conv("model.10", (x9, 0), (cat22, 384), 1, 1)
+        ctx.call("aq_plan_upsample2x", cat22, 384, 384, cat12, 0)
+        c3(13, (cat12, 0), 768, (x13, 0), 384, L[13].n, False, (H // 16, W // 16))
+        conv("model.14", (x13, 0), (cat19, 192), 1, 1)
+        ctx.call("aq_plan_upsample2x", cat19, 192, 192, cat16, 0)
+        c3(17, (cat16, 0), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8))
+        conv("model.18", (x17, 0), (cat19, 0), 3, 2)
+        c3(20, (cat19, 0), 384, (x20, 0), 384, L[20].n, False, (H // 16, W // 16))
+        conv("model.21", (x20, 0), (cat22, 0), 3, 2)
+        c3(23, (cat22, 0), 768, (x23, 0), 768, L[23].n, False, (H // 32, W // 32))
+        # detect
+        anc = weights.anchors_px(sd)
+        row_off = 0
+        for lvl, (src, s) in enumerate(((x17, 8), (x20, 16), (x23, 32))):
+            w, b = fw[f"model.24.m.{lvl}"]
+            ctx.detect_level((src, 0), w, b, nc, row_off, s, anc[lvl].reshape(-1))
+            row_off += 3 * (H // s) * (W // s)
+        self.rows = row_off
+        ctx.plan_end()
+        self.n_launches = ctx.call("aq_plan_num_launches")
+        self.buffers = dict(x0=x0, x1=x1, x2=x2, x3=x3, x17=x17, x20=x20, x23=x23, x9=x9, x8=x8)
+
+    # ------------------------------------------------------------------ run
+    def detect_submit(self, tiles, bgr=True, src_is_device=False, stream=None):
+        """Enqueue one batch.  tiles: uint8 (n, h, w, 3) torch tensor (pinned host, or cuda).  Returns the slot
+        holding the pinned results; call `detect_wait` before reading them."""
+        n, h, w, _ = tiles.shape
+        assert n <= self.batch and tiles.dtype == torch.uint8 and tiles.is_contiguous()
+        if self._dets is None:
+            self._dets = [torch.empty(self.batch, self.max_det, 6, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._counts = [torch.empty(self.batch, dtype=torch.int32).pin_memory() for _ in range(2)]
+        slot = self._slot
+        self._slot ^= 1
+        cls_arr = (C.c_int * len(self.classes))(*self.classes) if self.classes else None
+        self.ctx.call("aq_detect_submit", C.c_void_p(tiles.data_ptr()), n, h, w, int(bgr), int(src_is_device),
+                      self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
+                      len(self.classes) if self.classes else 0, C.c_void_p(self._dets[slot].data_ptr()),
+                      C.c_void_p(self._counts[slot].data_ptr()), stream)
+        return slot, n
+
+    def detect_wait(self, slot_n, stream=None) -> Detections:
+        slot, n = slot_n
+        self.ctx.call("aq_sync", stream)
+        return Detections(self._dets[slot][:n].numpy(), self._counts[slot][:n].numpy())
+
+    def detect(self, tiles, bgr=True, src_is_device=False) -> Detections:
+        return self.detect_wait(self.detect_submit(tiles, bgr, src_is_device))
+
+    def close(self):
+        self.ctx.close()
+
+
+def format_label_text(det: np.ndarray, net_hw, hw0, save_conf=True) -> str:
+    """Label text of one image via the C formatter (det: (n,6) fp32, descending conf)."""
+    lib = _lib.load()
+    det = np.ascontiguousarray(det, np.float32)
+    cap = 128 * max(len(det), 1) + 16
+    out = C.create_string_buffer(cap)
+    rc = lib.aq_format_label_text(det.ctypes.data, len(det), int(net_hw[0]), int(net_hw[1]), int(hw0[0]), int(hw0[1]),
+                                  int(save_conf), out, cap)
+    if rc < 0:
+        raise AquaError(f"aq_format_label_text failed ({rc})")
+    return out.value.decode()
+
+
+def write_labels(dets: Detections, net_hw, hw0_list, paths: List[str], save_conf=True, threads=8) -> int:
+    """Write one label file per image with >= 1 detection; returns the number of files written."""
+    lib = _lib.load()
+    n = len(paths)
+    d = np.ascontiguousarray(dets.dets, np.float32)
+    cnt = np.ascontiguousarray(dets.counts, np.int32)
+    h0 = np.asarray([h for h, _ in hw0_list], np.int32)
+    w0 = np.asarray([w for _, w in hw0_list], np.int32)
+    arr = (C.c_char_p * n)(*[p.encode() for p in paths])
+    rc = lib.aq_format_labels(d.ctypes.data, cnt.ctypes.data, n, d.shape[1], int(net_hw[0]), int(net_hw[1]),
+                              h0.ctypes.data, w0.ctypes.data, arr, int(save_conf), threads)
+    if rc < 0:
+        raise AquaError(f"aq_format_labels failed ({rc})")
+    return rc

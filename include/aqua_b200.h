@@ -1,0 +1,177 @@
+/*
+ * aqua_b200.h — C ABI of the B200-native YOLOv5m tile-detection path.
+ *
+ * This library replaces the compute behind the reference's one GPU-shaped stage,
+ *     python3 yolov5/detect.py --weights ...exp2.pt --source data/jpegs --nosave --save-txt --save-conf
+ *                                                                    [REF README.md:77]
+ * The reference exposes NO plugin / FFI interface for this path (it is a CLI on one side and a directory
+ * of label files on the other, consumed by [REF src/process_yolo/geocode_results.py:140-172]); the entry
+ * points below are therefore the boundary a maintainer binds with ctypes from a detect.py replacement
+ * (INTEGRATION.md).  Each entry cites the upstream function whose arithmetic it replaces
+ * ([UPSTREAM-RECALLED] = ultralytics/yolov5, the absent submodule of [REF .SUBMODULES.json:8-16]).
+ *
+ * Conventions: plain pointers and sizes only; every function returns AQ_OK (0) or a negative aq_status
+ * and never throws; aq_last_error() gives the text.  The caller owns every buffer it passes; the context
+ * owns its workspace, weights and activation buffers.  One context per (process, device); not thread
+ * safe.  `stream` is a cudaStream_t passed as void* (NULL = the context's own stream).  There is no CPU
+ * fallback: without a CUDA device aq_create fails.
+ */
+#ifndef AQUA_B200_H
+#define AQUA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AQ_ABI_VERSION 1
+
+typedef enum aq_status {
+  AQ_OK = 0,
+  AQ_ERR_ARG = -1,          /* bad argument */
+  AQ_ERR_CUDA = -2,         /* CUDA runtime / driver error (text in aq_last_error) */
+  AQ_ERR_STATE = -3,        /* call out of order (e.g. forward before plan_end) */
+  AQ_ERR_NOMEM = -4,
+  AQ_ERR_UNSUPPORTED = -5,  /* shape or mode this build has no kernel for; never a silent fallback */
+  AQ_ERR_IO = -6
+} aq_status;
+
+typedef struct aq_ctx aq_ctx;
+
+/* Activation flags of a conv op. */
+#define AQ_ACT_NONE 0
+#define AQ_ACT_SILU 1
+
+/*
+ * One fused convolution = upstream models/common.py::Conv.forward_fuse (conv + folded BN bias + SiLU)
+ * optionally followed by models/common.py::Bottleneck's residual add, executed as an implicit GEMM on
+ * tcgen05 tensor cores.  Activations are NHWC fp16; an op reads channels [src_c_off, src_c_off+c_in) of
+ * buffer `src` and writes channels [dst_c_off, dst_c_off+c_out) of buffer `dst`, which is how
+ * torch.cat / models/common.py::Concat disappear (producers write into slices of the concat buffer).
+ */
+typedef struct aq_conv_desc {
+  int src, src_c_off, c_in;     /* input buffer id, first channel, channels (multiple of 16) */
+  int dst, dst_c_off, c_out;    /* output buffer id, first channel, channels */
+  int k;                        /* 1 or 3 (the 6x6/s2 stem is given as 3x3/s1 over the space-to-depth input) */
+  int stride;                   /* 1 or 2 */
+  int act;                      /* AQ_ACT_* */
+  int res, res_c_off;           /* residual buffer id (or -1) and first channel; added AFTER the activation */
+  const uint16_t* weight;       /* host, fp16 bits, [c_out][k][k][c_in] (KRSC), BN already folded */
+  const float* bias;            /* host, fp32 [c_out] */
+  /* tuning knobs; 0 = let the library choose */
+  int tile_n;                   /* UMMA N per tile */
+  int chunks_per_stage;
+} aq_conv_desc;
+
+/*
+ * Detect head level = upstream models/yolo.py::Detect.forward (eval branch): 1x1 conv with bias, then
+ * sigmoid, xy = (s*2 + grid - 0.5) * stride, wh = (s*2)^2 * anchor_px, conf = s, written as fp32 rows
+ * [level_row_off + a*ny*nx + y*nx + x][5+nc] of the prediction tensor (B, rows, 5+nc).
+ */
+typedef struct aq_detect_desc {
+  int src, src_c_off, c_in;
+  int nc;                       /* classes; no = nc + 5; conv N = 3*no */
+  int level_row_off;            /* first row of this level inside one image's prediction */
+  float stride;                 /* 8, 16, 32 */
+  float anchors_px[6];          /* 3 anchors (w,h) in pixels */
+  const uint16_t* weight;       /* host fp16 [3*no][c_in] */
+  const float* bias;            /* host fp32 [3*no] */
+} aq_detect_desc;
+
+/* ------------------------------------------------------------------ lifetime */
+int aq_abi_version(void);
+/* Fails with AQ_ERR_CUDA when no sm_100 device is usable: there is no CPU path. */
+int aq_create(int device, aq_ctx** out);
+void aq_destroy(aq_ctx* ctx);
+const char* aq_last_error(const aq_ctx* ctx); /* ctx may be NULL: error of the last failed aq_create */
+
+/* ------------------------------------------------------------------ plan (replaces DetectionModel.__init__/fuse/_forward_once wiring) */
+/* Begin a plan for `batch` tiles whose letterboxed network input is net_h x net_w (multiples of 32). */
+int aq_plan_begin(aq_ctx* ctx, int batch, int net_h, int net_w, int nc);
+/* Declare an NHWC fp16 activation buffer (h, w, c); returns its id >= 0.  Buffer 0 must be the network
+ * input in space-to-depth form: (net_h/2, net_w/2, 16) with channel (py*2+px)*3 + rgb, 12..15 zero. */
+int aq_plan_buffer(aq_ctx* ctx, int h, int w, int c);
+int aq_plan_conv(aq_ctx* ctx, const aq_conv_desc* d);
+/* models/common.py::SPPF's three chained MaxPool2d(5,1,2): reads channels [c_off, c_off+c) of `buf` and
+ * writes the pooled maps to [c_off+c, c_off+2c), [c_off+2c, ..), [c_off+3c, ..) of the same buffer. */
+int aq_plan_sppf_pool(aq_ctx* ctx, int buf, int c_off, int c);
+/* nn.Upsample(scale_factor=2, mode='nearest') into a channel slice of the consumer's concat buffer. */
+int aq_plan_upsample2x(aq_ctx* ctx, int src, int src_c_off, int c, int dst, int dst_c_off);
+int aq_plan_detect(aq_ctx* ctx, const aq_detect_desc* d);
+/* Allocate, upload weights, encode TMA tensor maps, capture the forward as a CUDA graph. */
+int aq_plan_end(aq_ctx* ctx);
+/* Introspection for tests: device pointer and geometry of a planned buffer. */
+int aq_buffer_info(aq_ctx* ctx, int buf, void** dev_ptr, int* n, int* h, int* w, int* c);
+/* Device pointer of the decoded predictions (batch, rows, 5+nc) fp32 written by aq_forward. */
+int aq_pred_info(aq_ctx* ctx, float** dev_ptr, int* rows, int* no);
+int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
+
+/* ------------------------------------------------------------------ execution */
+/*
+ * Letterbox + to-tensor: upstream utils/augmentations.py::letterbox (cv2.resize INTER_LINEAR in cv2's
+ * 11-bit fixed point + copyMakeBorder 114) fused with LoadImages' HWC->CHW/BGR->RGB and detect.py's
+ * float()/255 [UPSTREAM-RECALLED].  `tiles` = n uint8 HWC images of in_h x in_w x 3 (device pointer, or
+ * pinned/pageable host pointer when src_is_device == 0, in which case the H2D copy is issued here).
+ * Result: buffer 0 of the plan.  `bgr` != 0 means the source is BGR (cv2.imread order).
+ */
+int aq_preprocess(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_w, int bgr,
+                  int src_is_device, void* stream);
+/* Letterboxed uint8 image (n, net_h, net_w, 3) in RGB order, for bit-exact checks of the resize/pad. */
+int aq_preprocess_u8(aq_ctx* ctx, const uint8_t* tiles_dev, int n, int in_h, int in_w, int bgr,
+                     uint8_t* out_dev, void* stream);
+/* Conv stack + Detect decode (one CUDA graph launch). */
+int aq_forward(aq_ctx* ctx, void* stream);
+/*
+ * Batched NMS = upstream utils/general.py::non_max_suppression (+ xywh2xyxy, torchvision.ops.nms)
+ * [UPSTREAM-RECALLED].  pred: device fp32 (batch, rows, no) or NULL to use the plan's own predictions.
+ * dets_out: device fp32 (batch, max_det, 6) rows [x1,y1,x2,y2,conf,cls] in descending confidence;
+ * counts_out: device int32 (batch); keep_rows_out: device int32 (batch, max_det) source row of each kept
+ * detection (may be NULL).  classes: host int array or NULL.  Keep indices are bit-exact w.r.t. the
+ * reference semantics: stable descending sort, fp32 IoU inter/(a_i+a_j-inter), suppress iff
+ * (double)iou > iou_thres.
+ */
+int aq_nms(aq_ctx* ctx, const float* pred, int batch, int rows, int no, float conf_thres, double iou_thres,
+           int max_det, int agnostic, const int* classes, int n_classes, float max_wh, int max_nms,
+           float* dets_out, int* counts_out, int* keep_rows_out, void* stream);
+/*
+ * Whole path for one batch: preprocess -> forward -> NMS -> copy detections to host.
+ * dets_host (batch, max_det, 6) fp32 and counts_host (batch) int32 should be pinned for overlap.
+ * Synchronises `stream` before returning.
+ */
+int aq_detect(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device,
+              float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+              int n_classes, float* dets_host, int* counts_host, void* stream);
+/* Asynchronous halves of aq_detect for double-buffered pipelines: submit enqueues everything on `stream`
+ * including the D2H copies and returns; the caller synchronises the stream (or an event) itself. */
+int aq_detect_submit(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_w, int bgr,
+                     int src_is_device, float conf_thres, double iou_thres, int max_det, int agnostic,
+                     const int* classes, int n_classes, float* dets_host, int* counts_host, void* stream);
+
+/* ------------------------------------------------------------------ host-side label epilogue (no GPU) */
+/*
+ * upstream utils/general.py::{scale_boxes, clip_boxes, xyxy2xywh} + detect.py::run's --save-txt block
+ * [UPSTREAM-RECALLED]; grammar pinned by the consumer [REF src/process_yolo/geocode_results.py:140-172].
+ * For image i: dets + i*det_stride*6 holds counts[i] rows; boxes are rescaled from the letterboxed
+ * (net_h, net_w) to the original (h0[i], w0[i]), clipped, rounded, normalised; lines are emitted in
+ * ASCENDING confidence as "cls cx cy w h[ conf]\n" with "%g"; zero detections produce NO file; files
+ * are opened in append mode as upstream does.  paths[i] = full path of the label file.
+ * Returns the number of files written (>= 0) or a negative aq_status.
+ */
+int aq_format_labels(const float* dets, const int* counts, int n_images, int det_stride, int net_h, int net_w,
+                     const int* h0, const int* w0, const char* const* paths, int save_conf, int n_threads);
+/* Same text into a caller buffer (for tests): returns bytes written or negative status. */
+int aq_format_label_text(const float* dets, int count, int net_h, int net_w, int h0, int w0, int save_conf,
+                         char* out, size_t out_cap);
+
+/* ------------------------------------------------------------------ misc */
+/* cudaMemcpyAsync wrapper so hosts without a CUDA binding can move test data: kind 0=H2D 1=D2H 2=D2D. */
+int aq_memcpy(aq_ctx* ctx, void* dst, const void* src, size_t bytes, int kind, void* stream);
+int aq_sync(aq_ctx* ctx, void* stream);
+/* Elapsed GPU milliseconds of the last aq_forward's conv graph per op class is not exposed; use events. */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AQUA_B200_H */

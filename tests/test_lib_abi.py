@@ -1,0 +1,81 @@
+"""CPU: the C-ABI library loads, exports every symbol include/aqua_b200.h declares, refuses to run without a
+GPU (no CPU fallback), and its host-side label formatter is bit-identical to the oracle's text."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from aquaculture_b200 import _lib, engine
+from oracle import labels as OL
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "aqua_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(aq_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported():
+    lib = _lib.load()
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/aqua_b200.h but not exported"
+    assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
+    assert lib.aq_abi_version() == 1
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    with pytest.raises(_lib.AquaError, match="no CUDA device|CPU path"):
+        engine.Context(0)
+
+
+def test_missing_library_is_loud(monkeypatch):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libaqua_b200.so")
+    with pytest.raises(_lib.AquaError, match="not built"):
+        _lib.load()
+
+
+@pytest.mark.parametrize("hw0", [(640, 640), (1024, 1024), (600, 1000), (333, 517)])
+def test_label_text_matches_oracle(hw0):
+    g = torch.Generator().manual_seed(hw0[0])
+    n = 200
+    net = (640, 640)
+    xy = torch.rand(n, 2, generator=g) * 700 - 30
+    wh = torch.rand(n, 2, generator=g) * 150
+    det = torch.cat((xy - wh / 2, xy + wh / 2, torch.rand(n, 1, generator=g), torch.randint(0, 5, (n, 1), generator=g).float()), 1)
+    det = det[det[:, 4].argsort(descending=True)]
+    for save_conf in (True, False):
+        exp = "".join(l + "\n" for l in OL.label_lines(det, net, hw0, save_conf))
+        got = engine.format_label_text(det.numpy(), net, hw0, save_conf)
+        assert got == exp
+
+
+def test_label_text_half_pixel_rounding():
+    # boxes exactly on .5 after rescale exercise round-half-even
+    det = torch.tensor([[0.3125, 0.9375, 1.5625, 2.1875, 0.5, 1.0], [10.0, 10.0, 20.0, 20.0, 0.25, 0.0]])
+    exp = "".join(l + "\n" for l in OL.label_lines(det, (640, 640), (1024, 1024)))
+    assert engine.format_label_text(det.numpy(), (640, 640), (1024, 1024)) == exp
+
+
+def test_write_labels_files(tmp_path):
+    dets = np.zeros((3, 5, 6), np.float32)
+    dets[0, 0] = [10, 10, 50, 50, 0.9, 1]
+    dets[0, 1] = [100, 100, 150, 160, 0.6, 0]
+    dets[2, 0] = [5, 5, 9, 9, 0.3, 2]
+    counts = np.array([2, 0, 1], np.int32)
+    paths = [str(tmp_path / f"L2020_{i}_0_0.txt") for i in range(3)]
+    n = engine.write_labels(engine.Detections(dets, counts), (640, 640), [(640, 640)] * 3, paths)
+    assert n == 2 and not os.path.exists(paths[1])
+    a = np.loadtxt(paths[0])
+    assert a.shape == (2, 6) and a[0, 5] < a[1, 5]          # ascending confidence
+    assert np.loadtxt(paths[2]).shape == (6,)
+    engine.write_labels(engine.Detections(dets, counts), (640, 640), [(640, 640)] * 3, paths)
+    assert np.loadtxt(paths[0]).shape == (4, 6)              # append mode, as upstream

@@ -1,0 +1,139 @@
+"""CPU: the oracle pinned against golden vectors from the genuine third-party kernels (tests/golden, made
+by tools/make_golden.py) and against those kernels live (torchvision.ops.nms, cv2)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from aquaculture_b200 import arch
+from oracle import labels as OL
+from oracle import letterbox as LB
+from oracle import nms as ONMS
+from oracle import yolov5m
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_architecture_selfcheck():
+    # upstream README: YOLOv5m 21.2 M params, 49.0 GFLOPs @640 (nc=80)
+    m = yolov5m.YOLOv5m(80)
+    n = sum(p.numel() for p in m.parameters())
+    assert abs(n / 1e6 - 21.19) < 0.02
+    assert len(arch.iter_convs(3)) == 82
+    assert abs(arch.conv_flops_per_tile(640, 640, 3) / 1e9 - 47.879) < 0.01
+    assert abs(arch.conv_flops_per_tile(1280, 1280, 3) / 1e9 - 191.516) < 0.01
+    assert abs(arch.conv_flops_per_tile(640, 640, 80) / 1e9 - 48.872) < 0.01
+    assert arch.detect_rows(640, 640) == 25200 and arch.detect_rows(1280, 1280) == 100800
+
+
+def test_nms_core_against_golden_torchvision():
+    z = np.load(os.path.join(GOLD, "nms_torchvision.npz"))
+    names = sorted({k.rsplit("_", 1)[0] for k in z.files})
+    assert len(names) == 7
+    for n in names:
+        thr = float(n.split("_")[-1])
+        keep = ONMS.greedy_nms_numpy(z[n + "_boxes"], z[n + "_scores"], thr)
+        assert np.array_equal(keep, z[n + "_keep"]), n
+
+
+def test_nms_core_live_torchvision():
+    import torchvision
+    g = torch.Generator().manual_seed(0)
+    for n, q in [(1, None), (2, None), (700, None), (400, 8)]:
+        xy = torch.rand(n, 2, generator=g) * 300
+        wh = torch.rand(n, 2, generator=g) * 90 + 1
+        boxes = torch.cat((xy - wh / 2, xy + wh / 2), 1)
+        scores = torch.rand(n, generator=g)
+        if q:
+            scores = (scores * q).round() / q
+        for thr in (0.45, 0.1, 0.7):
+            assert np.array_equal(ONMS.greedy_nms_numpy(boxes.numpy(), scores.numpy(), thr),
+                                  torchvision.ops.nms(boxes, scores, thr).numpy())
+
+
+def test_nms_driver_semantics():
+    # obj filter, conf = obj*cls, first-max class, per-class offsets, max_det, empty image
+    pred = torch.zeros(2, 6, 7)
+    pred[0, 0] = torch.tensor([50, 50, 20, 20, 0.9, 0.8, 0.1])
+    pred[0, 1] = torch.tensor([51, 50, 20, 20, 0.9, 0.7, 0.1])   # same class, overlaps -> suppressed
+    pred[0, 2] = torch.tensor([51, 50, 20, 20, 0.9, 0.1, 0.6])   # other class -> kept
+    pred[0, 3] = torch.tensor([200, 200, 20, 20, 0.2, 0.9, 0.9])  # obj below threshold
+    pred[0, 4] = torch.tensor([300, 300, 20, 20, 0.6, 0.4, 0.4])  # conf 0.24 below threshold
+    pred[0, 5] = torch.tensor([400, 400, 20, 20, 0.9, 0.5, 0.5])  # class tie -> class 0
+    out, rows = ONMS.non_max_suppression(pred, return_rows=True)
+    assert rows[0].tolist() == [0, 2, 5] and out[0][:, 5].tolist() == [0.0, 1.0, 0.0]
+    assert out[1].shape == (0, 6)
+    assert torch.allclose(out[0][0, :4], torch.tensor([40.0, 40, 60, 60]))
+    assert len(ONMS.non_max_suppression(pred, max_det=2)[0]) == 2
+    assert ONMS.non_max_suppression(pred, agnostic=True, return_rows=True)[1][0].tolist() == [0, 5]
+    assert ONMS.non_max_suppression(pred, classes=[1], return_rows=True)[1][0].tolist() == [2]
+
+
+def test_resize_against_golden_cv2():
+    z = np.load(os.path.join(GOLD, "resize_cv2.npz"))
+    for n in sorted({k.rsplit("_", 1)[0] for k in z.files}):
+        dst = z[n + "_dst"]
+        got = LB.resize_bilinear_u8(z[n + "_src"], dst.shape[1], dst.shape[0])
+        assert np.array_equal(got, dst), f"{n}: {np.count_nonzero(got != dst)} samples differ"
+
+
+@pytest.mark.parametrize("hw,new", [((1024, 1024), 640), ((600, 1000), 640), ((300, 500), 640), ((640, 640), 640),
+                                    ((50, 37), 640)])
+def test_letterbox_live_cv2(hw, new):
+    rng = np.random.default_rng(3)
+    im = rng.integers(0, 256, (*hw, 3), dtype=np.uint8)
+    for auto in (True, False):
+        a = LB.letterbox(im, (new, new), auto=auto, use_cv2=True)
+        b = LB.letterbox(im, (new, new), auto=auto, use_cv2=False)
+        assert np.array_equal(a, b)
+        assert a.shape[0] % 32 == 0 and a.shape[1] % 32 == 0
+        if not auto:
+            assert a.shape[:2] == (new, new)
+
+
+def test_letterbox_reference_tile_geometry():
+    # 1024^2 tiles [REF src/utils.py:18-19] -> r = 0.625, 640^2, no padding
+    assert LB.letterbox_geometry(1024, 1024, (640, 640)) == (640, 640, 0, 0, 0, 0)
+    assert LB.letterbox_geometry(640, 640, (640, 640)) == (640, 640, 0, 0, 0, 0)
+    nw, nh, t, b, l, r = LB.letterbox_geometry(600, 1000, (640, 640), auto=True)
+    assert (nw, nh) == (640, 384) and (t, b, l, r) == (0, 0, 0, 0)
+    assert LB.letterbox_geometry(600, 1000, (640, 640), auto=False)[2:] == (128, 128, 0, 0)
+
+
+def test_label_grammar_and_consumer(tmp_path):
+    det = torch.tensor([[10.2, 20.7, 30.4, 41.0, 0.873421, 0.0], [100.0, 100.0, 140.6, 120.5, 0.5, 1.0]])
+    lines = OL.label_lines(det, (640, 640), (1024, 1024))
+    # ascending confidence, %g, six columns
+    assert lines[0].split()[0] == "1" and lines[1].split()[0] == "0"
+    assert lines[1] == "0 0.0317383 0.0483398 0.0322266 0.0322266 0.873421"
+    assert OL.write_labels(str(tmp_path), "ORTHO2020_12_0_5120", lines)
+    assert not OL.write_labels(str(tmp_path), "ORTHO2020_12_0_6144", [])
+    assert not (tmp_path / "ORTHO2020_12_0_6144.txt").exists()   # zero detections -> NO file
+    # the consumer's own parsing [REF src/process_yolo/geocode_results.py:140-172]
+    path = str(tmp_path / "ORTHO2020_12_0_5120.txt")
+    inf_bboxs = np.loadtxt(path)
+    assert inf_bboxs.shape == (2, 6)
+    _, bbox_ind, x_offset, y_offset = os.path.basename(path).replace(".txt", "").split("_")
+    year = int(os.path.basename(path).replace(".txt", ".jpeg").split("_")[0][-4:])
+    assert (int(bbox_ind), int(x_offset), int(y_offset), year) == (12, 0, 5120, 2020)
+    REVERSE_CLASS_MAPPING = {0: "circle_farm", 1: "square_farm", 2: "triangle_farm", 3: "other_farm", 4: "rectangle_farm"}
+    for bbox in inf_bboxs:
+        xmin = int(1024 * (bbox[1] - bbox[3] / 2))
+        assert 0 <= xmin <= 1024 and 0 < bbox[5] <= 1
+        assert REVERSE_CLASS_MAPPING[bbox[0]]
+    one = np.loadtxt(_one_line(tmp_path))
+    assert one.ndim == 1 and one.shape == (6,)
+
+
+def _one_line(tmp_path):
+    p = tmp_path / "single.txt"
+    p.write_text("0 0.5 0.25 0.0195312 0.0205078 0.873421\n")
+    return str(p)
+
+
+def test_scale_boxes_clip_round():
+    det = torch.tensor([[-5.0, 3.3, 700.0, 650.0, 0.9, 2.0]])
+    lines = OL.label_lines(det, (640, 640), (1024, 1024))
+    c, x, y, w, h, conf = (float(v) for v in lines[0].split())
+    assert (c, conf) == (2.0, 0.9) and x == 0.5 and w == 1.0 and abs(y - (5 + 1024) / 2 / 1024) < 1e-6

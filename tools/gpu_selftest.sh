@@ -1,0 +1,16 @@
+#!/bin/bash
+# Runs the GPU parity suite in separate processes (a trapped kernel poisons its CUDA context) and keeps logs.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+run() { # name, pytest -k expr
+  timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -x --tb=short -k "$2" > gpurun_out/selftest_$1.log 2>&1
+  echo "$1 exit=$? $(tail -1 gpurun_out/selftest_$1.log)"
+}
+run conv1x1 "conv1x1"
+run conv3x3s1 "conv3x3_s1 or residual"
+run conv3x3s2 "conv3x3_s2"
+run persistent "many_tiles"
+run detect "detect_decode"
+run prepost "preprocess or sppf"
+run nms "nms"
+run e2e "e2e or label_files"

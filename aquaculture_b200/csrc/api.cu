@@ -107,8 +107,8 @@ CUtensorMapSwizzle swizzle_for(int inner_bytes) {
 
 int encode_map(aq_ctx* c, CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                const uint32_t* box, CUtensorMapSwizzle swz) {
-  cuuint64_t gd[5], gs[4];
-  cuuint32_t bx[5], es[5];
+  cuuint64_t gd[5] = {1, 1, 1, 1, 1}, gs[4] = {0, 0, 0, 0};
+  cuuint32_t bx[5] = {1, 1, 1, 1, 1}, es[5] = {1, 1, 1, 1, 1};
   for (int i = 0; i < rank; ++i) {
     gd[i] = dims[i];
     bx[i] = box[i];
@@ -223,7 +223,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   k.kstages = (k.total_chunks + k.cps - 1) / k.cps;
   k.stage_bytes = k.cps * (k.a_sub_bytes + k.b_sub_bytes);
   k.c_bytes = det ? 0 : kTileM * k.tile_n * 2;
-  const int budget = 225 * 1024 - (int)k.c_bytes - 1024;
+  const int budget = kConvMaxDynSmem - (int)k.c_bytes - 1024;
   int st = budget / (int)k.stage_bytes;
   if (st > kMaxStages) st = kMaxStages;
   if (st < 2) return fail(c, AQ_ERR_UNSUPPORTED, "conv stage of %u bytes does not fit twice in shared memory", k.stage_bytes);
@@ -475,10 +475,13 @@ int aq_create(int device, aq_ctx** out) {
     return fail(nullptr, AQ_ERR_CUDA, "cuTensorMapEncodeTiled unavailable: %s", cudaGetErrorString(e));
   }
   c->encode = (EncodeTiledFn)fn;
+  const char* what = "stream";
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
-      (e = conv_kernels_init()) != cudaSuccess || (e = nms_init()) != cudaSuccess || (e = sppf_init()) != cudaSuccess) {
+      (what = "conv smem attr", e = conv_kernels_init()) != cudaSuccess ||
+      (what = "nms smem attr", e = nms_init()) != cudaSuccess ||
+      (what = "sppf smem attr", e = sppf_init()) != cudaSuccess) {
     delete c;
-    return fail(nullptr, AQ_ERR_CUDA, "init: %s", cudaGetErrorString(e));
+    return fail(nullptr, AQ_ERR_CUDA, "init (%s): %s", what, cudaGetErrorString(e));
   }
   *out = c;
   return AQ_OK;

@@ -336,10 +336,12 @@ size_t conv_smem_bytes(const ConvKParams& p) {
 }
 
 cudaError_t conv_kernels_init() {
+  // 227 KB per CTA includes the kernel's static shared memory (barriers): leave 1 KB for it
   cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       232448);
+                                       kConvMaxDynSmem);
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(conv_igemm_kernel<EPI_DETECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  return cudaFuncSetAttribute(conv_igemm_kernel<EPI_DETECT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              kConvMaxDynSmem);
 }
 
 cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, cudaStream_t stream) {

@@ -29,6 +29,7 @@ enum { EPI_STORE = 0, EPI_DETECT = 1 };
 constexpr int kConvThreads = 192;
 constexpr int kMaxStages = 8;
 constexpr int kTileM = 128;
+constexpr int kConvMaxDynSmem = 232448 - 1024;  // 227 KB opt-in limit minus static smem
 
 struct alignas(64) ConvKParams {
   CUtensorMap tmA;    // activation loads

@@ -1,0 +1,297 @@
+"""Drop-in command line for the reference's inference step
+
+    python3 yolov5/detect.py --weights ...exp2.pt --source data/jpegs --nosave --save-txt --save-conf
+                                                                            [REF README.md:77]
+
+Mirrors upstream `detect.py::{parse_opt, main, run}` [UPSTREAM-RECALLED, SURVEY.md §8 a-1 / §8b]: same flag
+names and defaults, same output layout `<project>/<name>{,2,3..}/labels/<stem>.txt`, same label grammar
+(consumer: [REF src/process_yolo/geocode_results.py:140-172]).  What differs is underneath: tiles are batched,
+every arithmetic step runs in libaqua_b200.so on a B200, and `--device 0,1,...` shards the sorted tile list
+over GPUs (one process per GPU, no collective on the data path; NCCL gathers three counters at the end).
+Modes the B200 path does not implement raise instead of falling back to another executor.
+"""
+from __future__ import annotations
+
+import argparse
+import glob
+import os
+import re
+import subprocess
+import sys
+import time
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+from typing import List, Optional, Tuple
+
+IMG_FORMATS = ("bmp", "dng", "jpeg", "jpg", "mpo", "png", "tif", "tiff", "webp", "pfm")
+STRIDE = 32
+
+
+def parse_opt(argv=None):
+    p = argparse.ArgumentParser(prog="detect.py")
+    p.add_argument("--weights", nargs="+", type=str, default=["yolov5s.pt"], help="model path; 'synthetic' = seeded stand-in weights")
+    p.add_argument("--source", type=str, default="data/images", help="file/dir/glob of images")
+    p.add_argument("--data", type=str, default="data/coco128.yaml", help="(accepted, unused: class names come from the checkpoint)")
+    p.add_argument("--imgsz", "--img", "--img-size", nargs="+", type=int, default=[640], help="inference size h,w")
+    p.add_argument("--conf-thres", type=float, default=0.25)
+    p.add_argument("--iou-thres", type=float, default=0.45)
+    p.add_argument("--max-det", type=int, default=1000)
+    p.add_argument("--device", default="", help="cuda device(s), i.e. 0 or 0,1,2,3 (tiles are sharded across them)")
+    p.add_argument("--view-img", action="store_true")
+    p.add_argument("--save-txt", action="store_true")
+    p.add_argument("--save-conf", action="store_true")
+    p.add_argument("--save-crop", action="store_true")
+    p.add_argument("--nosave", action="store_true")
+    p.add_argument("--classes", nargs="+", type=int)
+    p.add_argument("--agnostic-nms", action="store_true")
+    p.add_argument("--augment", action="store_true")
+    p.add_argument("--visualize", action="store_true")
+    p.add_argument("--update", action="store_true")
+    p.add_argument("--project", default="runs/detect")
+    p.add_argument("--name", default="exp")
+    p.add_argument("--exist-ok", action="store_true")
+    p.add_argument("--line-thickness", default=3, type=int)
+    p.add_argument("--hide-labels", default=False, action="store_true")
+    p.add_argument("--hide-conf", default=False, action="store_true")
+    p.add_argument("--half", action="store_true", help="(accepted: the B200 path always computes fp16 in, fp32 accumulate)")
+    p.add_argument("--dnn", action="store_true")
+    p.add_argument("--vid-stride", type=int, default=1)
+    # additive
+    p.add_argument("--batch-size", type=int, default=64, help="tiles per GPU batch")
+    p.add_argument("--synthetic", type=int, default=0, help="run on N seeded synthetic tiles instead of --source")
+    p.add_argument("--synthetic-size", type=int, default=640)
+    p.add_argument("--seed", type=int, default=0)
+    p.add_argument("--nc", type=int, default=3, help="classes of the synthetic stand-in weights")
+    p.add_argument("--verbose", action="store_true", help="per-image log lines as upstream prints them")
+    p.add_argument("--io-threads", type=int, default=8)
+    opt = p.parse_args(argv)
+    opt.imgsz *= 2 if len(opt.imgsz) == 1 else 1
+    return opt
+
+
+def check_unsupported(opt):
+    bad = [f for f in ("augment", "visualize", "save_crop", "dnn", "update") if getattr(opt, f)]
+    if bad:
+        raise SystemExit("detect.py (B200 path): unsupported mode(s) " + ", ".join("--" + b.replace("_", "-") for b in bad) +
+                         "; there is no fallback executor")
+    if opt.view_img:
+        print("WARNING: --view-img ignored (no window system)", file=sys.stderr)
+    if not opt.nosave and not opt.save_txt:
+        raise SystemExit("detect.py (B200 path): annotated-image output is not implemented; pass --nosave --save-txt "
+                         "[--save-conf] as the reference does [README.md:77]")
+    if len(opt.weights) != 1:
+        raise SystemExit("detect.py (B200 path): model ensembles (several --weights) are not supported")
+    src = opt.source
+    if opt.synthetic <= 0 and (src.isnumeric() or src.lower().startswith(("rtsp://", "rtmp://", "http://", "https://", "screen")) or
+                               src.endswith(".streams") or src.rsplit(".", 1)[-1].lower() in ("mp4", "avi", "mov", "mkv", "gif")):
+        raise SystemExit("detect.py (B200 path): only image files/directories are supported as --source")
+
+
+def check_img_size(imgsz, s=STRIDE):
+    """upstream utils/general.py::check_img_size: round each side UP to a multiple of the max stride."""
+    import math
+    new = [max(int(math.ceil(x / s) * s), 0) for x in imgsz]
+    if new != list(imgsz):
+        print(f"WARNING: --img-size {imgsz} must be multiple of max stride {s}, updating to {new}", file=sys.stderr)
+    return new
+
+
+def increment_path(path, exist_ok=False) -> Path:
+    """upstream utils/general.py::increment_path: runs/exp -> runs/exp2, runs/exp3, ..."""
+    path = Path(path)
+    if path.exists() and not exist_ok:
+        for n in range(2, 9999):
+            p = f"{path}{n}"
+            if not os.path.exists(p):
+                path = Path(p)
+                break
+    return path
+
+
+def list_images(source: str) -> List[str]:
+    """upstream utils/dataloaders.py::LoadImages: sorted glob / dir listing / single file, image suffixes only."""
+    p = str(Path(source).resolve()) if not any(ch in source for ch in "*?[") else source
+    if "*" in p or "?" in p or "[" in p:
+        files = sorted(glob.glob(p, recursive=True))
+    elif os.path.isdir(p):
+        files = sorted(glob.glob(os.path.join(p, "*.*")))
+    elif os.path.isfile(p):
+        files = [p]
+    else:
+        raise FileNotFoundError(f"{p} does not exist")
+    images = [x for x in files if x.rsplit(".", 1)[-1].lower() in IMG_FORMATS]
+    if not images:
+        raise FileNotFoundError(f"No images found in {p}. Supported formats are: {IMG_FORMATS}")
+    return images
+
+
+def net_shape_for(h0: int, w0: int, imgsz: Tuple[int, int]) -> Tuple[int, int]:
+    """Letterboxed (h, w) upstream produces with auto=True (minimum rectangle, multiples of 32)."""
+    r = min(imgsz[0] / h0, imgsz[1] / w0)
+    nw, nh = int(round(w0 * r)), int(round(h0 * r))
+    dw, dh = (imgsz[1] - nw) % STRIDE, (imgsz[0] - nh) % STRIDE
+    top, bottom = int(round(dh / 2 - 0.1)), int(round(dh / 2 + 0.1))
+    left, right = int(round(dw / 2 - 0.1)), int(round(dw / 2 + 0.1))
+    return nh + top + bottom, nw + left + right
+
+
+def dist_env():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def spawn_ranks(devices: List[int], argv: List[str]) -> int:
+    """`--device 0,1,..`: one process per GPU; rank r takes tiles r, r+W, ... of the sorted list."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = []
+    for r, d in enumerate(devices):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(len(devices)), LOCAL_RANK=str(d), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), AQ_SPAWNED="1")
+        procs.append(subprocess.Popen([sys.executable, "-m", "aquaculture_b200.detect_cli"] + argv, env=env))
+    return max(p.wait() for p in procs)
+
+
+def run(opt, argv) -> int:
+    check_unsupported(opt)
+    rank, world, local = dist_env()
+    devs = [int(d) for d in str(opt.device).replace("cuda:", "").split(",") if d.strip() != ""] if opt.device not in ("", "cpu") else [0]
+    if opt.device == "cpu":
+        raise SystemExit("detect.py (B200 path): --device cpu is not available; there is no CPU fallback")
+    if len(devs) > 1 and "AQ_SPAWNED" not in os.environ and world == 1:
+        # resolve the run directory once so all ranks write into the same labels/
+        save_dir = increment_path(Path(opt.project) / opt.name, exist_ok=opt.exist_ok)
+        (save_dir / "labels").mkdir(parents=True, exist_ok=True)
+        argv = list(argv) + ["--project", str(save_dir.parent), "--name", save_dir.name, "--exist-ok"]
+        return spawn_ranks(devs, argv)
+    device = local if "AQ_SPAWNED" in os.environ or world > 1 else devs[0]
+
+    import numpy as np
+    import torch
+    from . import engine, tiles, weights
+
+    imgsz = tuple(check_img_size(opt.imgsz))
+    save_dir = increment_path(Path(opt.project) / opt.name, exist_ok=opt.exist_ok or world > 1)
+    label_dir = save_dir / "labels"
+    if opt.save_txt:
+        label_dir.mkdir(parents=True, exist_ok=True)
+    else:
+        save_dir.mkdir(parents=True, exist_ok=True)
+
+    # ---- model
+    w = opt.weights[0]
+    if w == "synthetic":
+        sd, nc, names = weights.synthetic_state(opt.nc, opt.seed), opt.nc, [f"class{i}" for i in range(opt.nc)]
+    else:
+        if not os.path.isfile(w):
+            raise SystemExit(f"detect.py: weights file {w} not found")
+        sd, nc, names = weights.load_checkpoint(w)
+
+    # ---- tile list and this rank's shard (strided over the sorted list)
+    if opt.synthetic > 0:
+        idx = tiles.shard_indices(opt.synthetic, rank, world)
+        items = [("synthetic", i) for i in idx]
+        stems = [tiles.tile_stem(i) for i in idx]
+    else:
+        files = list_images(opt.source)
+        files = [files[i] for i in tiles.shard_indices(len(files), rank, world)]
+        items = [("file", f) for f in files]
+        stems = [Path(f).stem for f in files]
+
+    import cv2
+    cv2.setNumThreads(1)
+
+    def load(item):
+        kind, v = item
+        if kind == "synthetic":
+            return tiles.synthetic_tile(v, opt.synthetic_size, opt.synthetic_size, opt.seed)
+        im = cv2.imread(v)  # BGR, as upstream LoadImages
+        if im is None:
+            raise SystemExit(f"Image Not Found {v}")
+        return im
+
+    detectors = {}
+
+    def detector_for(net_hw):
+        if net_hw not in detectors:
+            detectors[net_hw] = engine.TileDetector(sd, nc, batch=opt.batch_size, imgsz=net_hw, device=device,
+                                                    conf_thres=opt.conf_thres, iou_thres=opt.iou_thres, max_det=opt.max_det,
+                                                    agnostic=opt.agnostic_nms, classes=opt.classes)
+        return detectors[net_hw]
+
+    t_start = time.perf_counter()
+    dt = [0.0, 0.0]  # load+stage, gpu (pre+inference+NMS) + label write
+    seen = n_files = n_dets = 0
+    pool = ThreadPoolExecutor(opt.io_threads)
+    B = opt.batch_size
+    pos = 0
+    pending = {}  # (h0, w0) -> list of (image, stem)
+
+    def flush(shape0, group):
+        nonlocal seen, n_files, n_dets
+        h0, w0 = shape0
+        net_hw = net_shape_for(h0, w0, imgsz)
+        det = detector_for(net_hw)
+        t0 = time.perf_counter()
+        batch = torch.from_numpy(np.stack([g[0] for g in group]))
+        t1 = time.perf_counter()
+        res = det.detect(batch, bgr=True)
+        if opt.save_txt:
+            paths = [str(label_dir / (g[1] + ".txt")) for g in group]
+            n_files += engine.write_labels(res, net_hw, [shape0] * len(group), paths, save_conf=opt.save_conf,
+                                           threads=opt.io_threads)
+        t2 = time.perf_counter()
+        dt[0] += t1 - t0
+        dt[1] += t2 - t1
+        seen += len(group)
+        n_dets += int(res.counts.sum())
+        if opt.verbose:
+            for g, c in zip(group, res.counts):
+                print(f"image {g[1]}: {net_hw[0]}x{net_hw[1]} {int(c)} detections")
+
+    while pos < len(items):
+        chunk = items[pos:pos + B]
+        t0 = time.perf_counter()
+        imgs = list(pool.map(load, chunk))
+        dt[0] += time.perf_counter() - t0
+        for im, stem in zip(imgs, stems[pos:pos + B]):
+            key = im.shape[:2]
+            pending.setdefault(key, []).append((im, stem))
+            if len(pending[key]) == B:
+                flush(key, pending.pop(key))
+        pos += B
+    for key in list(pending):
+        flush(key, pending.pop(key))
+    for d in detectors.values():
+        d.close()
+    wall = time.perf_counter() - t_start
+
+    # ---- the one collective: gather per-rank counters (NCCL), rank 0 prints the summary
+    totals = [seen, n_files, n_dets]
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(device)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
+        t = torch.tensor(totals, dtype=torch.int64, device="cuda")
+        allc = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allc, t)
+        totals = torch.stack(allc).sum(0).tolist()
+        dist.destroy_process_group()
+    if rank == 0:
+        per = 1e3 / max(seen, 1)
+        print(f"Speed: {dt[0] * per:.2f}ms load, {dt[1] * per:.2f}ms pre-process+inference+NMS+labels per image at shape "
+              f"({opt.batch_size}, 3, {imgsz[0]}, {imgsz[1]}); {totals[0] / wall:.1f} tiles/s over {world} GPU(s)")
+        if opt.save_txt:
+            print(f"{totals[1]} labels saved to {label_dir} ({totals[2]} detections in {totals[0]} images)")
+        print(f"Results saved to {save_dir}")
+    return 0
+
+
+def main(argv=None):
+    argv = list(sys.argv[1:] if argv is None else argv)
+    return run(parse_opt(argv), argv)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

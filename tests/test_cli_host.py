@@ -1,0 +1,112 @@
+"""CPU: host-side logic of the drop-in CLI (flag surface, output dir rules, letterbox shape, sharding)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from aquaculture_b200 import detect_cli as cli
+from aquaculture_b200 import tiles
+from oracle import letterbox as LB
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_reference_command_line_parses():
+    # the exact flags the reference README uses [REF README.md:77]
+    opt = cli.parse_opt(["--weights", "output/model_weights/multilabel_farms_exp2.pt", "--source", "data/jpegs",
+                         "--nosave", "--save-txt", "--save-conf"])
+    assert opt.imgsz == [640, 640] and opt.conf_thres == 0.25 and opt.iou_thres == 0.45 and opt.max_det == 1000
+    assert opt.nosave and opt.save_txt and opt.save_conf and opt.project == "runs/detect" and opt.name == "exp"
+    cli.check_unsupported(opt)
+
+
+def test_all_upstream_flags_accepted():
+    opt = cli.parse_opt(["--weights", "a.pt", "--source", "x", "--data", "d.yaml", "--img", "1280", "--conf-thres", "0.3",
+                         "--iou-thres", "0.5", "--max-det", "300", "--device", "0", "--save-txt", "--save-conf", "--nosave",
+                         "--classes", "0", "2", "--agnostic-nms", "--project", "p", "--name", "n", "--exist-ok",
+                         "--line-thickness", "2", "--hide-labels", "--hide-conf", "--half", "--vid-stride", "2"])
+    assert opt.imgsz == [1280, 1280] and opt.classes == [0, 2] and opt.agnostic_nms
+    assert cli.parse_opt(["--img-size", "640", "480"]).imgsz == [640, 480]
+
+
+@pytest.mark.parametrize("flag", ["--augment", "--visualize", "--save-crop", "--dnn", "--update"])
+def test_unsupported_modes_error_explicitly(flag):
+    opt = cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", flag])
+    with pytest.raises(SystemExit, match="unsupported"):
+        cli.check_unsupported(opt)
+
+
+def test_stream_sources_and_cpu_device_rejected():
+    with pytest.raises(SystemExit, match="only image"):
+        cli.check_unsupported(cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--source", "rtsp://x"]))
+    opt = cli.parse_opt(["--weights", "synthetic", "--nosave", "--save-txt", "--device", "cpu", "--synthetic", "2"])
+    with pytest.raises(SystemExit, match="no CPU fallback"):
+        cli.run(opt, [])
+
+
+def test_check_img_size_rounds_up():
+    assert cli.check_img_size([640, 640]) == [640, 640]
+    assert cli.check_img_size([1000, 650]) == [1024, 672]
+
+
+def test_increment_path(tmp_path):
+    p = tmp_path / "exp"
+    assert cli.increment_path(p) == p
+    p.mkdir()
+    assert cli.increment_path(p).name == "exp2"
+    (tmp_path / "exp2").mkdir()
+    assert cli.increment_path(p).name == "exp3"
+    assert cli.increment_path(p, exist_ok=True) == p
+
+
+def test_list_images_sorted_and_filtered(tmp_path):
+    for n in ["b_1_0_0.jpeg", "a_1_0_0.jpeg", "notes.txt", "c_1_0_0.PNG"]:
+        (tmp_path / n).write_bytes(b"x")
+    got = [os.path.basename(f) for f in cli.list_images(str(tmp_path))]
+    assert got == ["a_1_0_0.jpeg", "b_1_0_0.jpeg", "c_1_0_0.PNG"]
+    with pytest.raises(FileNotFoundError):
+        cli.list_images(str(tmp_path / "missing"))
+
+
+@pytest.mark.parametrize("hw", [(1024, 1024), (640, 640), (600, 1000), (333, 517), (2000, 900)])
+def test_net_shape_matches_oracle_letterbox(hw):
+    im = np.zeros((*hw, 3), np.uint8)
+    assert cli.net_shape_for(hw[0], hw[1], (640, 640)) == LB.letterbox(im, (640, 640), auto=True).shape[:2]
+
+
+def test_sharding_covers_each_tile_once():
+    for n, w in [(10, 1), (10, 4), (200000, 8), (7, 8)]:
+        seen = sorted(i for r in range(w) for i in tiles.shard_indices(n, r, w))
+        assert seen == list(range(n))
+    stem = tiles.tile_stem(12345)
+    f = stem.split("_")
+    assert len(f) == 4 and f[0][-4:] == "2020"      # what geocode_results.py:89,143 parses
+
+
+def test_synthetic_tiles_are_reproducible():
+    a = tiles.synthetic_tile(5, 64, 64, 0)
+    assert np.array_equal(a, tiles.synthetic_tiles([5], 64, 64, 0)[0]) and not np.array_equal(a, tiles.synthetic_tile(6, 64, 64, 0))
+
+
+def test_counter_gather_gloo_world2(tmp_path):
+    """The path's only collective (per-rank counters) on 2 ranks over gloo."""
+    script = tmp_path / "g.py"
+    script.write_text(
+        "import os, torch, torch.distributed as dist\n"
+        "import sys; sys.path.insert(0, %r)\n"
+        "from aquaculture_b200 import tiles\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "mine = tiles.shard_indices(101, r, w)\n"
+        "t = torch.tensor([len(mine), sum(mine), r], dtype=torch.int64)\n"
+        "allc = [torch.zeros_like(t) for _ in range(w)]\n"
+        "dist.all_gather(allc, t)\n"
+        "tot = torch.stack(allc).sum(0).tolist()\n"
+        "assert tot[0] == 101 and tot[1] == sum(range(101)), tot\n"
+        "dist.destroy_process_group()\n" % ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
+                       capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stderr[-2000:]

@@ -51,6 +51,8 @@ SIGNATURES = {
                                  C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "aq_pred_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
+    "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
+    "aq_op_describe": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
     "aq_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "aq_preprocess_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "aq_forward": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -672,6 +672,64 @@ int aq_pred_info(aq_ctx* c, float** dev_ptr, int* rows, int* no) {
 
 int aq_plan_num_launches(aq_ctx* c) { return c ? c->n_launches : AQ_ERR_ARG; }
 
+int aq_profile_ops(aq_ctx* c, int iters, float* ms_per_op, int cap) {
+  if (!c || !ms_per_op || iters <= 0) return AQ_ERR_ARG;
+  if (!c->planned) return fail(c, AQ_ERR_STATE, "profile before plan_end");
+  cudaSetDevice(c->device);
+  const int n = (int)c->ops.size();
+  if (cap < n) return fail(c, AQ_ERR_ARG, "profile: need room for %d ops", n);
+  cudaEvent_t e0, e1;
+  CU_CHECK(c, cudaEventCreate(&e0));
+  CU_CHECK(c, cudaEventCreate(&e1));
+  std::vector<Op> all;
+  all.swap(c->ops);
+  int rc = AQ_OK;
+  for (int i = 0; i < n && rc == AQ_OK; ++i) {
+    c->ops.clear();
+    c->ops.push_back(all[i]);
+    rc = run_ops(c, c->stream);  // warm-up
+    if (rc) break;
+    cudaEventRecord(e0, c->stream);
+    for (int k = 0; k < iters && rc == AQ_OK; ++k) rc = run_ops(c, c->stream);
+    cudaEventRecord(e1, c->stream);
+    if (cudaEventSynchronize(e1) != cudaSuccess) rc = fail(c, AQ_ERR_CUDA, "profile: op %d failed: %s", i, cudaGetErrorString(cudaGetLastError()));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    ms_per_op[i] = ms / iters;
+  }
+  c->ops.swap(all);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return rc ? rc : n;
+}
+
+int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
+  if (!c || !buf || i < 0 || i >= (int)c->ops.size()) return AQ_ERR_ARG;
+  const Op& op = c->ops[i];
+  if (op.kind == OP_CONV || op.kind == OP_DETECT) {
+    const bool det = op.kind == OP_DETECT;
+    const ConvKParams& k = op.kp;
+    const Buffer& sb = c->bufs[det ? op.det.src : op.conv.src];
+    const int stride = det ? 1 : op.conv.stride;
+    const int c_in = det ? op.det.c_in : op.conv.c_in;
+    const int c_out = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
+    const double M = (double)c->batch * (sb.h / stride) * (sb.w / stride);
+    const double flops = 2.0 * M * c_out * c_in * k.ksize * k.ksize;
+    const double bytes = 2.0 * ((double)c->batch * sb.h * sb.w * c_in + M * c_out * (k.has_res ? 2 : 1)) +
+                         2.0 * c_out * c_in * k.ksize * k.ksize;
+    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f tileN=%d cb=%d cps=%d stages=%d tile=%dx%d mt=%d nt=%d | flop=%.4g bytes=%.4g",
+             det ? "detect" : "conv", k.ksize, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, k.tile_n, k.cb, k.cps,
+             k.num_stages, k.tw, k.th, k.m_tiles, k.n_tiles_n, flops, bytes);
+  } else if (op.kind == OP_POOL) {
+    const Buffer& b = c->bufs[op.buf];
+    snprintf(buf, cap, "sppf_pool %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 4.0);
+  } else {
+    const Buffer& b = c->bufs[op.buf];
+    snprintf(buf, cap, "upsample2x %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 5.0);
+  }
+  return AQ_OK;
+}
+
 int aq_preprocess(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device, void* stream) {
   if (!c || !tiles) return AQ_ERR_ARG;
   if (!c->planned) return fail(c, AQ_ERR_STATE, "preprocess before plan_end");

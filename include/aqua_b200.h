@@ -107,6 +107,11 @@ int aq_buffer_info(aq_ctx* ctx, int buf, void** dev_ptr, int* n, int* h, int* w,
 /* Device pointer of the decoded predictions (batch, rows, 5+nc) fp32 written by aq_forward. */
 int aq_pred_info(aq_ctx* ctx, float** dev_ptr, int* rows, int* no);
 int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
+/* Measurement aids: time every planned op alone (CUDA events on the context stream, `iters` launches each,
+ * after one warm-up) into ms_per_op[0..n_ops); returns n_ops.  aq_op_describe writes a one-line description
+ * (kind, GEMM shape, tile configuration, algorithmic FLOPs and bytes) of op `i`. */
+int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
+int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
 
 /* ------------------------------------------------------------------ execution */
 /*

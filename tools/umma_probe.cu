@@ -1,0 +1,383 @@
+// Hardware probes that decide kernel design choices on sm_100a (run on the GPU box; results are recorded
+// in DESIGN.md):
+//   T1  UMMA shared-memory descriptors on shifted / strided views of one swizzled patch
+//       (start address offset by whole 128-byte rows, SBO that is not a multiple of 1024, base_offset field)
+//   T3  TMA tensor maps whose pixel stride is smaller than the box inner extent (overlapping rows)
+//   T4  TMA load throughput per SM as a function of the box inner row size (32 / 64 / 128 bytes)
+//   T5  accuracy of SiLU variants (ex2+rcp vs tanh.approx)
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/umma_probe tools/umma_probe.cu
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../aquaculture_b200/csrc/ptx.cuh"
+
+using namespace aq::ptx;
+
+#define CK(x)                                                                                   \
+  do {                                                                                          \
+    cudaError_t e_ = (x);                                                                       \
+    if (e_ != cudaSuccess) {                                                                    \
+      printf("CUDA error %s at %s:%d: %s\n", #x, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      exit(2);                                                                                  \
+    }                                                                                           \
+  } while (0)
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode;
+
+__device__ __forceinline__ uint64_t make_desc_ex(uint32_t addr, uint32_t sbo_bytes, uint32_t base_off) {
+  return (uint64_t)((addr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) |
+         ((uint64_t)(base_off & 7) << 49) | (2ull << 61);
+}
+
+// ------------------------------------------------------------------------------------------------ T1
+constexpr int kPN = 32;  // UMMA N of the probe
+__global__ void __launch_bounds__(128) umma_view_kernel(const __half* Apatch, const __half* B, float* D, int off_rows,
+                                                        int sbo_bytes, int bo, int R) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t tslot;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  uint8_t* sm = raw + (base - smem_u32(raw));
+  for (int i = threadIdx.x; i < R * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    *reinterpret_cast<uint4*>(sm + r * 128 + ((j ^ (r & 7)) << 4)) = reinterpret_cast<const uint4*>(Apatch)[i];
+  }
+  const uint32_t boff = ((R * 128 + 1023) / 1024) * 1024;
+  for (int i = threadIdx.x; i < kPN * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    *reinterpret_cast<uint4*>(sm + boff + r * 128 + ((j ^ (r & 7)) << 4)) = reinterpret_cast<const uint4*>(B)[i];
+  }
+  fence_proxy_async_smem();
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&tslot), 32);
+    tmem_relinquish();
+  }
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tslot;
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc_f16(128, kPN);
+    const uint32_t a_addr = base + off_rows * 128;
+    for (int k = 0; k < 4; ++k)
+      umma_f16(tmem, make_desc_ex(a_addr + k * 32, sbo_bytes, bo), make_desc_ex(base + boff + k * 32, 1024, 0), idesc,
+               k > 0);
+    umma_commit(smem_u32(&bar));
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  tc_fence_after();
+  for (int c0 = 0; c0 < kPN; c0 += 16) {
+    uint32_t v[16];
+    tmem_ld16(tmem + ((warp * 32u) << 16) + c0, v);
+    tmem_ld_wait();
+    for (int i = 0; i < 16; ++i) D[(warp * 32 + lane) * kPN + c0 + i] = __uint_as_float(v[i]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 32);
+}
+
+static void run_t1() {
+  const int R = 320;
+  std::vector<__half> A(R * 64), B(kPN * 64);
+  srand(1);
+  for (auto& v : A) v = __float2half((float)(rand() % 9 - 4));
+  for (auto& v : B) v = __float2half((float)(rand() % 7 - 3));
+  __half *dA, *dB;
+  float* dD;
+  CK(cudaMalloc(&dA, A.size() * 2));
+  CK(cudaMalloc(&dB, B.size() * 2));
+  CK(cudaMalloc(&dD, 128 * kPN * 4));
+  CK(cudaMemcpy(dA, A.data(), A.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dB, B.data(), B.size() * 2, cudaMemcpyHostToDevice));
+  const size_t smem = R * 128 + kPN * 128 + 2048;
+  CK(cudaFuncSetAttribute(umma_view_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // expected rows: full[r][n] = sum_k A[r][k] B[n][k]
+  std::vector<float> full(R * kPN);
+  for (int r = 0; r < R; ++r)
+    for (int n = 0; n < kPN; ++n) {
+      float s = 0;
+      for (int k = 0; k < 64; ++k) s += __half2float(A[r * 64 + k]) * __half2float(B[n * 64 + k]);
+      full[r * kPN + n] = s;
+    }
+  struct V { int off, sbo, bo; };
+  const V vars[] = {{0, 1024, 0},  {8, 1024, 0},  {16, 1024, 0}, {1, 1024, 0},  {1, 1024, 1},  {3, 1024, 0},
+                    {3, 1024, 3},  {4, 1024, 0},  {4, 1024, 4},  {0, 1280, 0},  {11, 1280, 0}, {11, 1280, 3},
+                    {0, 2304, 0},  {19, 2304, 0}, {19, 2304, 3}, {0, 512, 0},   {2, 512, 0},   {0, 2048, 0},
+                    {9, 2048, 0},  {9, 2048, 1}};
+  for (const V& v : vars) {
+    CK(cudaMemset(dD, 0, 128 * kPN * 4));
+    umma_view_kernel<<<1, 128, smem>>>(dA, dB, dD, v.off, v.sbo, v.bo, R);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+      printf("T1 off=%d sbo=%d bo=%d: CUDA error %s\n", v.off, v.sbo, v.bo, cudaGetErrorString(e));
+      exit(3);
+    }
+    std::vector<float> D(128 * kPN);
+    CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
+    int ok_rows = 0, matched_other = 0, unmatched = 0;
+    char map[256] = {0};
+    int mp = 0;
+    for (int m = 0; m < 128; ++m) {
+      const int want = v.off + (m / 8) * (v.sbo / 128) + (m % 8);
+      int found = -1;
+      for (int r = 0; r < R && found < 0; ++r)
+        if (!memcmp(&D[m * kPN], &full[r * kPN], kPN * 4)) found = r;
+      if (found == want) ++ok_rows;
+      else if (found >= 0) ++matched_other;
+      else ++unmatched;
+      if (m < 20 && mp < 200) mp += snprintf(map + mp, sizeof(map) - mp, "%d>%d ", want, found);
+    }
+    printf("T1 off=%2d sbo=%4d bo=%d : rows ok %3d / other-row %3d / garbage %3d | want>got: %s\n", v.off, v.sbo, v.bo,
+           ok_rows, matched_other, unmatched, map);
+  }
+  cudaFree(dA); cudaFree(dB); cudaFree(dD);
+}
+
+// ------------------------------------------------------------------------------------------------ T3
+__global__ void __launch_bounds__(128) tma_overlap_kernel(const __grid_constant__ CUtensorMap tm, __half* out, int rank,
+                                                          int c0, int c1, int c2, int c3, int rows) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  uint8_t* sm = raw + (base - smem_u32(raw));
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(smem_u32(&bar), rows * 128);
+    if (rank == 2) tma_load_2d(base, &tm, smem_u32(&bar), c0, c1);
+    else tma_load_4d(base, &tm, smem_u32(&bar), c0, c1, c2, c3);
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  for (int i = threadIdx.x; i < rows * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    reinterpret_cast<uint4*>(out)[i] = *reinterpret_cast<const uint4*>(sm + r * 128 + ((j ^ (r & 7)) << 4));
+  }
+}
+
+static void run_t3() {
+  const int W = 40, H = 10, N = 2, C = 16;  // 16 channels per pixel (32 B), rows of 64 elements (4 pixels)
+  const size_t n_el = (size_t)N * H * W * C + 256;
+  std::vector<__half> src(n_el);
+  for (size_t i = 0; i < n_el; ++i) src[i] = __float2half((float)(i % 2039));
+  __half *d, *dout;
+  CK(cudaMalloc(&d, n_el * 2));
+  CK(cudaMalloc(&dout, 64 * 64 * 2));
+  CK(cudaMemcpy(d, src.data(), n_el * 2, cudaMemcpyHostToDevice));
+  CK(cudaFuncSetAttribute(tma_overlap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+  {
+    CUtensorMap tm;
+    cuuint64_t gd[2] = {64, (cuuint64_t)N * H * W};
+    cuuint64_t gs[1] = {(cuuint64_t)C * 2};
+    cuuint32_t bx[2] = {64, 8}, es[2] = {1, 1};
+    CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    printf("T3 2-D overlapped map (dim0 64 el, pixel stride 16 el): encode result %d\n", (int)r);
+    if (r == CUDA_SUCCESS) {
+      tma_overlap_kernel<<<1, 128, 16384>>>(tm, dout, 2, 0, 5, 0, 0, 8);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("T3 2-D: CUDA error %s\n", cudaGetErrorString(e)); exit(3); }
+      std::vector<__half> o(8 * 64);
+      CK(cudaMemcpy(o.data(), dout, o.size() * 2, cudaMemcpyDeviceToHost));
+      int bad = 0;
+      for (int p = 0; p < 8; ++p)
+        for (int k = 0; k < 64; ++k)
+          if (__half2float(o[p * 64 + k]) != __half2float(src[(5 + p) * C + k])) ++bad;
+      printf("T3 2-D overlapped load: %d / 512 elements wrong\n", bad);
+    }
+  }
+  {
+    CUtensorMap tm;
+    cuuint64_t gd[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t bx[4] = {64, 8, 4, 1}, es[4] = {1, 1, 1, 1};
+    CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    printf("T3 4-D overlapped map: encode result %d\n", (int)r);
+    if (r == CUDA_SUCCESS) {
+      tma_overlap_kernel<<<1, 128, 16384>>>(tm, dout, 4, 0, -1, -1, 1, 32);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("T3 4-D: CUDA error %s\n", cudaGetErrorString(e)); exit(3); }
+      std::vector<__half> o(32 * 64);
+      CK(cudaMemcpy(o.data(), dout, o.size() * 2, cudaMemcpyDeviceToHost));
+      int bad = 0;
+      for (int yy = 0; yy < 4; ++yy)
+        for (int xx = 0; xx < 8; ++xx)
+          for (int k = 0; k < 64; ++k) {
+            const int y = yy - 1, x = xx - 1;
+            float want = 0.f;
+            if (y >= 0 && x >= 0) want = __half2float(src[(((size_t)1 * H + y) * W + x) * C + k]);
+            if (__half2float(o[(yy * 8 + xx) * 64 + k]) != want) ++bad;
+          }
+      printf("T3 4-D overlapped load with negative start (OOB rows -> 0): %d / 2048 elements wrong\n", bad);
+    }
+  }
+  cudaFree(d); cudaFree(dout);
+}
+
+// ------------------------------------------------------------------------------------------------ T4
+constexpr int kS = 6;
+__global__ void __launch_bounds__(96) tma_rate_kernel(const __grid_constant__ CUtensorMap tm, int iters, int loads,
+                                                      int box_rows, int row_bytes, long rows_total, int nprod,
+                                                      unsigned long long* sink) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bars[2 * kS];
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t stage_bytes = loads * box_rows * row_bytes;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kS; ++s) {
+      mbar_init(smem_u32(&bars[s]), nprod);
+      mbar_init(smem_u32(&bars[kS + s]), 1);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (warp < (uint32_t)nprod && lane == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < iters; ++it) {
+      mbar_wait(smem_u32(&bars[kS + stage]), phase ^ 1);
+      const int my_loads = loads / nprod;
+      mbar_arrive_expect_tx(smem_u32(&bars[stage]), my_loads * box_rows * row_bytes);
+      for (int l = 0; l < my_loads; ++l) {
+        const int li = warp * my_loads + l;
+        const long row = (((long)blockIdx.x * iters + it) * loads + li) * box_rows % rows_total;
+        tma_load_2d(base + stage * stage_bytes + li * box_rows * row_bytes, &tm, smem_u32(&bars[stage]), 0, (int)row);
+      }
+      if (++stage == kS) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 2 && lane == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    unsigned long long acc = 0;
+    for (int it = 0; it < iters; ++it) {
+      mbar_wait(smem_u32(&bars[stage]), phase);
+      acc += *reinterpret_cast<volatile uint32_t*>(raw + 1024 + stage * stage_bytes);
+      mbar_arrive(smem_u32(&bars[kS + stage]));
+      if (++stage == kS) { stage = 0; phase ^= 1; }
+    }
+    if (acc == 0x1234567) *sink = acc;
+  }
+}
+
+static void run_t4() {
+  const size_t big = (size_t)6 << 30;  // 6 GiB source for the HBM runs
+  uint8_t* d;
+  unsigned long long* sink;
+  CK(cudaMalloc(&d, big));
+  CK(cudaMemset(d, 1, big));
+  CK(cudaMalloc(&sink, 8));
+  CK(cudaFuncSetAttribute(tma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  struct V { int cb, box_rows, loads, nprod; bool l2; };
+  const V vars[] = {{16, 128, 4, 1, true}, {32, 128, 4, 1, true}, {64, 128, 1, 1, true},  {64, 128, 1, 1, false},
+                    {32, 128, 2, 1, false}, {16, 128, 4, 1, false}, {64, 128, 2, 2, true}, {16, 128, 4, 2, true},
+                    {64, 256, 1, 1, true}, {64, 32, 4, 1, true},   {64, 8, 16, 1, true},  {16, 256, 2, 1, true}};
+  for (const V& v : vars) {
+    const int row_bytes = v.cb * 2;
+    const long rows_total = v.l2 ? (long)(32 << 20) / row_bytes : (long)(big / row_bytes);
+    CUtensorMap tm;
+    cuuint64_t gd[2] = {(cuuint64_t)v.cb, (cuuint64_t)rows_total};
+    cuuint64_t gs[1] = {(cuuint64_t)row_bytes};
+    cuuint32_t bx[2] = {(cuuint32_t)v.cb, (cuuint32_t)v.box_rows}, es[2] = {1, 1};
+    CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          row_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                           : (row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B),
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { printf("T4 encode failed %d\n", (int)r); continue; }
+    const int iters = v.l2 ? 4000 : 1500;
+    const size_t smem = (size_t)kS * v.loads * v.box_rows * row_bytes + 2048;
+    for (int rep = 0; rep < 2; ++rep) {
+      cudaEventRecord(e0);
+      tma_rate_kernel<<<148, 96, smem>>>(tm, iters, v.loads, v.box_rows, row_bytes, rows_total - 4096, v.nprod, sink);
+      cudaEventRecord(e1);
+      cudaError_t e = cudaEventSynchronize(e1);
+      if (e != cudaSuccess) { printf("T4: CUDA error %s\n", cudaGetErrorString(e)); exit(3); }
+      float ms;
+      cudaEventElapsedTime(&ms, e0, e1);
+      if (rep == 1) {
+        const double rows = 148.0 * iters * v.loads * v.box_rows;
+        const double bytes = rows * row_bytes;
+        printf("T4 row %3d B, box %3d rows x %2d loads/stage, %d producer(s), %s: %.3f ms  %.2f TB/s  %.1f ns/row/SM  (%.2f Grows/s chip)\n",
+               row_bytes, v.box_rows, v.loads, v.nprod, v.l2 ? "L2-resident" : "HBM", ms, bytes / ms / 1e9,
+               ms * 1e6 / (rows / 148.0), rows / ms / 1e6);
+      }
+    }
+  }
+  cudaFree(d); cudaFree(sink);
+}
+
+// ------------------------------------------------------------------------------------------------ T5
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__global__ void silu_kernel(const float* x, float* a, float* b, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = x[i];
+  a[i] = __fdividef(v, 1.0f + __expf(-v));
+  const float h = 0.5f * v;
+  b[i] = fmaf(h, tanh_approx(h), h);
+}
+static void run_t5() {
+  const int n = 1 << 20;
+  std::vector<float> x(n), a(n), b(n);
+  for (int i = 0; i < n; ++i) x[i] = -16.f + 32.f * (float)i / n;
+  float *dx, *da, *db;
+  CK(cudaMalloc(&dx, n * 4)); CK(cudaMalloc(&da, n * 4)); CK(cudaMalloc(&db, n * 4));
+  CK(cudaMemcpy(dx, x.data(), n * 4, cudaMemcpyHostToDevice));
+  silu_kernel<<<n / 256, 256>>>(dx, da, db, n);
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(a.data(), da, n * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(b.data(), db, n * 4, cudaMemcpyDeviceToHost));
+  double ea = 0, eb = 0, ra = 0, rb = 0, ha = 0, hb = 0;
+  for (int i = 0; i < n; ++i) {
+    const double v = x[i], ref = v / (1.0 + exp(-v));
+    const double da_ = fabs(a[i] - ref), db_ = fabs(b[i] - ref);
+    ea = fmax(ea, da_); eb = fmax(eb, db_);
+    if (fabs(ref) > 1e-3) { ra = fmax(ra, da_ / fabs(ref)); rb = fmax(rb, db_ / fabs(ref)); }
+    // error measured in fp16 ulps of the result (what matters after the fp16 store)
+    const double ulp = fmax(ldexp(1.0, (int)floor(log2(fmax(fabs(ref), 6.1e-5))) - 10), 5.96e-8);
+    ha = fmax(ha, da_ / ulp); hb = fmax(hb, db_ / ulp);
+  }
+  printf("T5 SiLU ex2+rcp : max abs %.3e  max rel %.3e  max err in fp16 ulps %.3f\n", ea, ra, ha);
+  printf("T5 SiLU tanh    : max abs %.3e  max rel %.3e  max err in fp16 ulps %.3f\n", eb, rb, hb);
+  cudaFree(dx); cudaFree(da); cudaFree(db);
+}
+
+int main(int argc, char** argv) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+  g_encode = (EncodeTiledFn)fn;
+  const char* which = argc > 1 ? argv[1] : "1345";
+  if (strchr(which, '1')) run_t1();
+  if (strchr(which, '3')) run_t3();
+  if (strchr(which, '5')) run_t5();
+  if (strchr(which, '4')) run_t4();
+  return 0;
+}

@@ -11,7 +11,7 @@ LIB_NAME = "libaqua_b200.so"
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
 
 AQ_OK = 0
-AQ_ACT_NONE, AQ_ACT_SILU = 0, 1
+AQ_ACT_NONE, AQ_ACT_SILU, AQ_ACT_SILU_FAST = 0, 1, 2
 
 
 class AquaError(RuntimeError):
@@ -24,7 +24,7 @@ class ConvDesc(C.Structure):
                 ("k", C.c_int), ("stride", C.c_int), ("act", C.c_int),
                 ("res", C.c_int), ("res_c_off", C.c_int),
                 ("weight", C.c_void_p), ("bias", C.c_void_p),
-                ("tile_n", C.c_int), ("chunks_per_stage", C.c_int)]
+                ("tile_n", C.c_int), ("mblk", C.c_int), ("mode", C.c_int)]
 
 
 class DetectDesc(C.Structure):
@@ -53,6 +53,7 @@ SIGNATURES = {
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
     "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_op_describe": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "aq_debug_plan_conv": (C.c_int, [C.c_int] * 10 + [C.c_char_p, C.c_size_t]),
     "aq_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "aq_preprocess_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "aq_forward": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -64,6 +65,7 @@ struct aq_ctx {
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
+  int pdl = 1;  // programmatic dependent launch between conv kernels (AQUA_PDL=0 disables)
   // preprocess state
   uint8_t* stage_u8 = nullptr;
   size_t stage_bytes = 0;
@@ -100,11 +102,6 @@ int fail(aq_ctx* c, int code, const char* fmt, ...) {
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-CUtensorMapSwizzle swizzle_for(int inner_bytes) {
-  return inner_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
-                            : inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
-}
-
 int encode_map(aq_ctx* c, CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                const uint32_t* box, CUtensorMapSwizzle swz) {
   cuuint64_t gd[5] = {1, 1, 1, 1, 1}, gs[4] = {0, 0, 0, 0};
@@ -127,11 +124,11 @@ int encode_map(aq_ctx* c, CUtensorMap* m, void* base, int rank, const uint64_t* 
   return AQ_OK;
 }
 
-// Pick the spatial M tile (tw x th <= 128 pixels) that wastes the fewest MMA rows on an (h, w) map.
+// Pick the spatial M block (tw x th <= 128 pixels) that wastes the fewest MMA rows on an (h, w) map.
 void pick_spatial_tile(int h, int w, int* tw_out, int* th_out) {
   double best = -1;
   int btw = 16, bth = 8;
-  for (int tw = 1; tw <= 128 && tw <= 256; ++tw) {
+  for (int tw = 1; tw <= 128; ++tw) {
     if (tw > w && tw != 1) break;
     int th = 128 / tw;
     if (th > h) th = h;
@@ -163,6 +160,87 @@ int pow2_at_least(int v) {
   return p;
 }
 
+// One candidate tiling of a conv; fill_candidate() completes the shared-memory / TMEM plan and the cost.
+struct Cand {
+  int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
+  // derived
+  int tiles_x = 1, tiles_y = 1, m_tiles = 0, pw = 0, ph = 0;
+  int na = 0, nb = 0, b_res = 0, n_stg = 0, acc_stages = 0;
+  uint32_t a_slot = 0, a_tx = 0;
+  double cycles = 1e30;
+  bool ok = false;
+};
+
+// Rough per-SM cycle model used only to rank candidates: each tile costs the slowest of its MMA time
+// (128 x N x 16 per N/2 cycles), its L2 -> SM operand traffic (~40 B/clk/SM measured), the TMA issue rate of
+// one producer thread (~600 clk per box, profiles/r1_hw_probe_v1.txt T4) and the epilogue.
+void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles_n, int n_steps, int cpt, int num_sms) {
+  const int groups = (tile_n + 63) / 64;
+  const uint32_t b_slot = (uint32_t)round_up(tile_n * 128, 1024);
+  const uint32_t stg = (uint32_t)groups * kTileM * 128;
+  int a_instr_per_group = 1, n_groups = n_steps;
+  if (cd.mode == CONV_MODE_FLAT) {
+    const int m_blocks = (batch * ho * wo + kTileM - 1) / kTileM;
+    cd.m_tiles = (m_blocks + cd.mblk - 1) / cd.mblk;
+    cd.a_slot = cd.a_tx = (uint32_t)cd.mblk * kTileM * 128;
+  } else if (cd.mode == CONV_MODE_HALO) {
+    cd.mblk = cd.mx * cd.my;
+    cd.pw = 8 * cd.mx + 2;
+    cd.ph = 16 * cd.my + 2;
+    cd.tiles_x = (wo + 8 * cd.mx - 1) / (8 * cd.mx);
+    cd.tiles_y = (ho + 16 * cd.my - 1) / (16 * cd.my);
+    cd.m_tiles = batch * cd.tiles_x * cd.tiles_y;
+    cd.a_tx = (uint32_t)cd.pw * cd.ph * 128;
+    cd.a_slot = (uint32_t)round_up((int)cd.a_tx, 1024);
+    n_groups = cpt;
+  } else {
+    cd.tiles_x = (wo + cd.tw - 1) / cd.tw;
+    cd.tiles_y = (ho + cd.th - 1) / cd.th;
+    const int m_blocks = batch * cd.tiles_x * cd.tiles_y;
+    cd.m_tiles = (m_blocks + cd.mblk - 1) / cd.mblk;
+    cd.a_tx = (uint32_t)cd.mblk * cd.tw * cd.th * 128;
+    cd.a_slot = (uint32_t)cd.mblk * kTileM * 128;
+    a_instr_per_group = cd.mblk;
+  }
+  const int acc_pitch = round_up(tile_n, 32);  // each accumulator starts on a 32-column boundary
+  if (cd.mblk * acc_pitch > 512) return;
+  cd.acc_stages = 2 * cd.mblk * acc_pitch <= 512 ? 2 : 1;
+  // ---- shared memory: minimal plan first, then grow the rings
+  const long budget = kConvMaxDynSmem - 1024;
+  cd.b_res = (n_tiles_n == 1 && n_steps <= kMaxB && (long)n_steps * b_slot <= 112 * 1024) ? 1 : 0;
+  cd.na = 2;
+  cd.n_stg = 1;
+  cd.nb = cd.b_res ? n_steps : 3;
+  auto used = [&]() { return (long)cd.na * cd.a_slot + (long)cd.nb * b_slot + (long)cd.n_stg * stg; };
+  if (used() > budget) {
+    if (!cd.b_res) return;
+    cd.b_res = 0;
+    cd.nb = 3;
+    if (used() > budget) return;
+  }
+  auto grow = [&](int& v, int cap, long unit) {
+    while (v < cap && used() + unit <= budget) ++v;
+  };
+  if (!cd.b_res) grow(cd.nb, 5, b_slot);
+  grow(cd.n_stg, 2, stg);
+  grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
+  if (!cd.b_res) grow(cd.nb, 12, b_slot);
+  // ---- cost
+  const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
+  const double a_bytes = (double)n_groups * cd.a_tx;
+  const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0;
+  const double o_bytes = (double)cd.mblk * kTileM * tile_n * 2.0;
+  const double l2 = (a_bytes + b_bytes + o_bytes) / 40.0;
+  const double issue = 600.0 * fmax((double)n_groups * a_instr_per_group, cd.b_res ? 0.0 : (double)n_steps);
+  const double epi = (double)cd.mblk * tile_n * 8.0 + 400.0;
+  double tile_cyc = fmax(fmax(mma, l2), fmax(issue, epi)) + 300.0;
+  if (cd.acc_stages == 1) tile_cyc += epi;
+  const long total_tiles = (long)cd.m_tiles * n_tiles_n;
+  const long per_sm = (total_tiles + num_sms - 1) / num_sms;
+  cd.cycles = per_sm * tile_cyc + 4000.0;
+  cd.ok = true;
+}
+
 // Fill everything of ConvKParams except device pointers / tensor maps.
 int plan_conv_geometry(aq_ctx* c, Op& op) {
   const bool det = op.kind == OP_DETECT;
@@ -170,67 +248,102 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   memset(&k, 0, sizeof k);
   const int src = det ? op.det.src : op.conv.src;
   const int c_in = det ? op.det.c_in : op.conv.c_in;
+  const int c_out = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
   const int ksize = det ? 1 : op.conv.k;
   const int stride = det ? 1 : op.conv.stride;
   const Buffer& sb = c->bufs[src];
   const int ho = sb.h / stride, wo = sb.w / stride;
-  k.ksize = ksize;
-  k.pad = ksize / 2;
-  k.cb = c_in % 64 == 0 ? 64 : (c_in % 32 == 0 ? 32 : 16);
-  if (c_in % 16) return fail(c, AQ_ERR_UNSUPPORTED, "conv c_in %d is not a multiple of 16", c_in);
-  k.cpt = c_in / k.cb;
-  k.total_chunks = ksize * ksize * k.cpt;
+  if (c_in % 8) return fail(c, AQ_ERR_UNSUPPORTED, "conv c_in %d is not a multiple of 8", c_in);
+  if (!((ksize == 1 && stride == 1) || (ksize == 3 && (stride == 1 || stride == 2))))
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv k=%d s=%d unsupported", ksize, stride);
+  if (stride == 2 && ((sb.h | sb.w) & 1)) return fail(c, AQ_ERR_UNSUPPORTED, "stride-2 conv on odd map");
+  k.stride = stride;
+  k.taps = ksize * ksize;
+  k.cpt = (c_in + 63) / 64;
+  k.n_steps = k.taps * k.cpt;
   if (det) {
-    k.tile_n = round_up(3 * (op.det.nc + 5), 16);
-    if (k.tile_n > 256) return fail(c, AQ_ERR_UNSUPPORTED, "detect head with nc=%d needs N=%d > 256", op.det.nc, k.tile_n);
+    k.tile_n = round_up(c_out, 16);
+    k.n_tiles_n = 1;
+  } else if (op.conv.tile_n > 0) {
+    k.tile_n = op.conv.tile_n;
+    k.n_tiles_n = (c_out + k.tile_n - 1) / k.tile_n;
+  } else if (c_out <= 256) {
+    k.tile_n = round_up(c_out, 16);
     k.n_tiles_n = 1;
   } else {
-    k.tile_n = op.conv.tile_n > 0 ? op.conv.tile_n : largest_divisor_tile_n(op.conv.c_out);
-    if (k.tile_n <= 0 || k.tile_n > 256 || k.tile_n % 16 || op.conv.c_out % k.tile_n)
-      return fail(c, AQ_ERR_UNSUPPORTED, "conv c_out %d has no valid UMMA N tile (got %d)", op.conv.c_out, k.tile_n);
-    k.n_tiles_n = op.conv.c_out / k.tile_n;
+    k.tile_n = largest_divisor_tile_n(c_out);
+    k.n_tiles_n = k.tile_n > 0 ? c_out / k.tile_n : 0;
   }
-  k.ob = k.tile_n % 64 == 0 ? 64 : (k.tile_n % 32 == 0 ? 32 : 16);
-  int rows_per_tile;
-  if (ksize == 1 && stride == 1) {
-    k.mode = CONV_MODE_FLAT;
-    k.m_tiles = (c->batch * ho * wo + kTileM - 1) / kTileM;
-    k.tw = kTileM;
-    k.th = 1;
-    k.tiles_x = k.tiles_y = 1;
-    rows_per_tile = kTileM;
+  if (k.tile_n <= 0 || k.tile_n > 256 || k.tile_n % 16 || k.n_tiles_n * k.tile_n > kMaxCout)
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv c_out %d has no valid UMMA N tile (got %d)", c_out, k.tile_n);
+  k.groups = (k.tile_n + 63) / 64;
+  // ---- candidates
+  std::vector<Cand> cands;
+  const int want_mblk = det ? 0 : op.conv.mblk;
+  const int want_mode = det ? 0 : op.conv.mode;  // 0 auto, 1 halo, 2 tap (3x3/s1 only)
+  if (ksize == 1) {
+    for (int mb = 1; mb <= 2; ++mb) {
+      Cand cd;
+      cd.mode = CONV_MODE_FLAT;
+      cd.mblk = mb;
+      cands.push_back(cd);
+    }
   } else {
-    if (ksize != 3 || (stride != 1 && stride != 2))
-      return fail(c, AQ_ERR_UNSUPPORTED, "conv k=%d s=%d unsupported", ksize, stride);
-    if (stride == 2 && ((sb.h | sb.w) & 1)) return fail(c, AQ_ERR_UNSUPPORTED, "stride-2 conv on odd map");
-    k.mode = stride == 1 ? CONV_MODE_S1 : CONV_MODE_S2;
-    pick_spatial_tile(ho, wo, &k.tw, &k.th);
-    k.tiles_x = (wo + k.tw - 1) / k.tw;
-    k.tiles_y = (ho + k.th - 1) / k.th;
-    k.m_tiles = c->batch * k.tiles_x * k.tiles_y;
-    rows_per_tile = k.tw * k.th;
+    if (stride == 1 && want_mode != 2) {
+      const int arr[3][2] = {{1, 1}, {2, 1}, {1, 2}};
+      for (auto& a : arr) {
+        Cand cd;
+        cd.mode = CONV_MODE_HALO;
+        cd.mx = a[0];
+        cd.my = a[1];
+        cd.mblk = a[0] * a[1];
+        cands.push_back(cd);
+      }
+    }
+    if (stride == 2 || want_mode != 1) {
+      for (int mb = 1; mb <= 2; ++mb) {
+        Cand cd;
+        cd.mode = CONV_MODE_TAP;
+        cd.mblk = mb;
+        pick_spatial_tile(ho, wo, &cd.tw, &cd.th);
+        cands.push_back(cd);
+      }
+    }
   }
-  k.src_ct = sb.c;
-  k.src_c_off = det ? op.det.src_c_off : op.conv.src_c_off;
-  k.act = det ? 0 : op.conv.act;
+  Cand best;
+  for (auto& cd : cands) {
+    if (want_mblk > 0 && cd.mblk != want_mblk) continue;
+    fill_candidate(cd, c->batch, ho, wo, k.tile_n, k.n_tiles_n, k.n_steps, k.cpt, c->num_sms);
+    if (cd.ok && cd.cycles < best.cycles) best = cd;
+  }
+  if (!best.ok) return fail(c, AQ_ERR_UNSUPPORTED, "conv %dx%d c_in %d c_out %d: no tiling fits shared memory / TMEM", ksize, ksize, c_in, c_out);
+  k.mode = best.mode;
+  k.mblk = best.mblk;
+  k.mx = best.mx;
+  k.my = best.my;
+  k.pw = best.pw;
+  k.tw = best.mode == CONV_MODE_HALO ? 8 : (best.mode == CONV_MODE_FLAT ? kTileM : best.tw);
+  k.th = best.mode == CONV_MODE_HALO ? 16 : (best.mode == CONV_MODE_FLAT ? 1 : best.th);
+  k.tiles_x = best.tiles_x;
+  k.tiles_y = best.tiles_y;
+  k.m_tiles = best.m_tiles;
+  k.a_group = best.mode == CONV_MODE_HALO ? 9 : 1;
+  k.na = best.na;
+  k.nb = best.nb;
+  k.b_res = best.b_res;
+  k.n_stg = best.n_stg;
+  k.acc_stages = best.acc_stages;
+  k.a_slot_bytes = best.a_slot;
+  k.a_tx_bytes = best.a_tx;
+  k.b_slot_bytes = (uint32_t)round_up(k.tile_n * 128, 1024);
+  k.b_tx_bytes = (uint32_t)k.tile_n * 128;
+  k.stg_bytes = det ? 0 : (uint32_t)k.groups * kTileM * 128;
+  if (det) k.n_stg = 1;
+  k.act = det ? ACT_NONE : op.conv.act;
   k.has_res = (!det && op.conv.res >= 0) ? 1 : 0;
-  k.a_sub_bytes = kTileM * k.cb * 2;
-  k.b_sub_bytes = round_up(k.tile_n * k.cb * 2, 1024);
-  k.a_box_bytes = rows_per_tile * k.cb * 2;
-  k.b_box_bytes = k.tile_n * k.cb * 2;
-  k.cps = (!det && op.conv.chunks_per_stage > 0) ? op.conv.chunks_per_stage : (64 / k.cb);
-  if (k.cps > k.total_chunks) k.cps = k.total_chunks;
-  k.kstages = (k.total_chunks + k.cps - 1) / k.cps;
-  k.stage_bytes = k.cps * (k.a_sub_bytes + k.b_sub_bytes);
-  k.c_bytes = det ? 0 : kTileM * k.tile_n * 2;
-  const int budget = kConvMaxDynSmem - (int)k.c_bytes - 1024;
-  int st = budget / (int)k.stage_bytes;
-  if (st > kMaxStages) st = kMaxStages;
-  if (st < 2) return fail(c, AQ_ERR_UNSUPPORTED, "conv stage of %u bytes does not fit twice in shared memory", k.stage_bytes);
-  k.num_stages = st;
-  k.tmem_cols = pow2_at_least(2 * k.tile_n);
-  k.acc_stride = k.tmem_cols / 2;
-  if (k.tmem_cols > 512) return fail(c, AQ_ERR_UNSUPPORTED, "tile_n %d needs more than 512 TMEM columns", k.tile_n);
+  k.acc_pitch = round_up(k.tile_n, 32);
+  k.acc_stride = k.mblk * k.acc_pitch;
+  k.tmem_cols = pow2_at_least(k.acc_stages * k.acc_stride);
   return AQ_OK;
 }
 
@@ -240,37 +353,42 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
   ConvKParams& k = op.kp;
   const int src = det ? op.det.src : op.conv.src;
   const int c_in = det ? op.det.c_in : op.conv.c_in;
+  const int src_c_off = det ? op.det.src_c_off : op.conv.src_c_off;
   const Buffer& sb = c->bufs[src];
   const uint64_t N = c->batch;
+  const CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_128B;
   int rc;
-  // ---- A
+  // ---- A: dim 0 is exactly the conv's input channels, so a 64-wide box past them is zero-filled
   if (k.mode == CONV_MODE_FLAT) {
     uint64_t dims[2] = {(uint64_t)c_in, N * sb.h * sb.w};
     uint64_t str[1] = {(uint64_t)sb.c * 2};
-    uint32_t box[2] = {(uint32_t)k.cb, (uint32_t)kTileM};
-    rc = encode_map(c, &k.tmA, sb.ptr + k.src_c_off, 2, dims, str, box, swizzle_for(k.cb * 2));
-  } else if (k.mode == CONV_MODE_S1) {
+    uint32_t box[2] = {64, (uint32_t)(kTileM * k.mblk)};
+    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 2, dims, str, box, sw);
+  } else if (k.mode == CONV_MODE_HALO || k.stride == 1) {
     uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
-    uint32_t box[4] = {(uint32_t)k.cb, (uint32_t)k.tw, (uint32_t)k.th, 1};
-    rc = encode_map(c, &k.tmA, sb.ptr + k.src_c_off, 4, dims, str, box, swizzle_for(k.cb * 2));
+    uint32_t box[4] = {64, (uint32_t)(k.mode == CONV_MODE_HALO ? k.pw : k.tw),
+                       (uint32_t)(k.mode == CONV_MODE_HALO ? 16 * k.my + 2 : k.th), 1};
+    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 4, dims, str, box, sw);
   } else {
-    // (x-parity*Ct + channel, W/2, y-parity, H/2, N): a stride-2 gather becomes a dense box
-    uint64_t dims[5] = {(uint64_t)2 * sb.c, (uint64_t)sb.w / 2, 2, (uint64_t)sb.h / 2, N};
+    // per x-parity: (channel, W/2, y-parity, H/2, N) -- a stride-2 gather becomes a dense box
+    uint64_t dims[5] = {(uint64_t)c_in, (uint64_t)sb.w / 2, 2, (uint64_t)sb.h / 2, N};
     uint64_t str[4] = {(uint64_t)2 * sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)2 * sb.w * sb.c * 2,
                        (uint64_t)sb.h * sb.w * sb.c * 2};
-    uint32_t box[5] = {(uint32_t)k.cb, (uint32_t)k.tw, 1, (uint32_t)k.th, 1};
-    rc = encode_map(c, &k.tmA, sb.ptr, 5, dims, str, box, swizzle_for(k.cb * 2));
+    uint32_t box[5] = {64, (uint32_t)k.tw, 1, (uint32_t)k.th, 1};
+    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 5, dims, str, box, sw);
+    if (rc) return rc;
+    rc = encode_map(c, &k.tmA2, sb.ptr + src_c_off + sb.c, 5, dims, str, box, sw);
   }
   if (rc) return rc;
-  // ---- B: weights [rows = c_out][K = k*k*c_in]
+  // ---- B: weights [rows = c_out][K = taps * cpt * 64] (zero padded per tap); rows past c_out are zero-filled
   {
     const int rows = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
-    const uint64_t K = (uint64_t)k.ksize * k.ksize * c_in;
+    const uint64_t K = (uint64_t)k.taps * k.cpt * 64;
     uint64_t dims[2] = {K, (uint64_t)rows};
     uint64_t str[1] = {K * 2};
-    uint32_t box[2] = {(uint32_t)k.cb, (uint32_t)k.tile_n};
-    rc = encode_map(c, &k.tmB, op.w_dev, 2, dims, str, box, swizzle_for(k.cb * 2));
+    uint32_t box[2] = {64, (uint32_t)k.tile_n};
+    rc = encode_map(c, &k.tmB, op.w_dev, 2, dims, str, box, sw);
     if (rc) return rc;
   }
   k.bias = op.b_dev;
@@ -286,24 +404,27 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     for (int i = 0; i < 6; ++i) k.det_anchor[i] = op.det.anchors_px[i];
     return AQ_OK;
   }
-  // ---- output (and residual) maps over the destination channel slice
-  auto out_map = [&](CUtensorMap* m, int buf, int c_off) -> int {
-    const Buffer& db = c->bufs[buf];
-    if (k.mode == CONV_MODE_FLAT) {
-      uint64_t dims[2] = {(uint64_t)op.conv.c_out, N * db.h * db.w};
-      uint64_t str[1] = {(uint64_t)db.c * 2};
-      uint32_t box[2] = {(uint32_t)k.ob, (uint32_t)kTileM};
-      return encode_map(c, m, db.ptr + c_off, 2, dims, str, box, swizzle_for(k.ob * 2));
-    }
-    uint64_t dims[4] = {(uint64_t)op.conv.c_out, (uint64_t)db.w, (uint64_t)db.h, N};
-    uint64_t str[3] = {(uint64_t)db.c * 2, (uint64_t)db.w * db.c * 2, (uint64_t)db.h * db.w * db.c * 2};
-    uint32_t box[4] = {(uint32_t)k.ob, (uint32_t)k.tw, (uint32_t)k.th, 1};
-    return encode_map(c, m, db.ptr + c_off, 4, dims, str, box, swizzle_for(k.ob * 2));
-  };
-  rc = out_map(&k.tmOut, op.conv.dst, op.conv.dst_c_off);
-  if (rc) return rc;
-  if (k.has_res) rc = out_map(&k.tmRes, op.conv.res, op.conv.res_c_off);
-  return rc;
+  // ---- output map over the destination channel slice (dim 0 = c_out: the 64-wide store box is clipped)
+  const Buffer& db = c->bufs[op.conv.dst];
+  if (k.mode == CONV_MODE_FLAT) {
+    uint64_t dims[2] = {(uint64_t)op.conv.c_out, N * db.h * db.w};
+    uint64_t str[1] = {(uint64_t)db.c * 2};
+    uint32_t box[2] = {64, (uint32_t)kTileM};
+    return encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 2, dims, str, box, sw);
+  }
+  uint64_t dims[4] = {(uint64_t)op.conv.c_out, (uint64_t)db.w, (uint64_t)db.h, N};
+  uint64_t str[3] = {(uint64_t)db.c * 2, (uint64_t)db.w * db.c * 2, (uint64_t)db.h * db.w * db.c * 2};
+  uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
+  return encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
+}
+
+// [c_out][taps][c_in] fp16 -> [c_out][taps][cpt * 64] with zero padding (so a 64-wide K chunk never straddles taps)
+void repack_weights(const uint16_t* w, int c_out, int taps, int c_in, std::vector<uint16_t>& out) {
+  const int cp = (c_in + 63) / 64 * 64;
+  out.assign((size_t)c_out * taps * cp, 0);
+  for (int o = 0; o < c_out; ++o)
+    for (int t = 0; t < taps; ++t)
+      memcpy(&out[((size_t)o * taps + t) * cp], &w[((size_t)o * taps + t) * c_in], (size_t)c_in * 2);
 }
 
 int check_buf(aq_ctx* c, int id, int c_off, int ch, const char* what) {
@@ -336,8 +457,8 @@ int run_ops(aq_ctx* c, cudaStream_t s) {
   for (auto& op : c->ops) {
     cudaError_t e = cudaSuccess;
     switch (op.kind) {
-      case OP_CONV: e = launch_conv(op.kp, EPI_STORE, c->num_sms, s); break;
-      case OP_DETECT: e = launch_conv(op.kp, EPI_DETECT, c->num_sms, s); break;
+      case OP_CONV: e = launch_conv(op.kp, EPI_STORE, c->num_sms, c->pdl, s); break;
+      case OP_DETECT: e = launch_conv(op.kp, EPI_DETECT, c->num_sms, c->pdl, s); break;
       case OP_POOL: {
         const Buffer& b = c->bufs[op.buf];
         e = launch_sppf_pool(b.ptr, c->batch, b.h, b.w, b.c, op.c_off, op.c, s);
@@ -475,6 +596,7 @@ int aq_create(int device, aq_ctx** out) {
     return fail(nullptr, AQ_ERR_CUDA, "cuTensorMapEncodeTiled unavailable: %s", cudaGetErrorString(e));
   }
   c->encode = (EncodeTiledFn)fn;
+  if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
   const char* what = "stream";
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (what = "conv smem attr", e = conv_kernels_init()) != cudaSuccess ||
@@ -536,12 +658,16 @@ int aq_plan_conv(aq_ctx* c, const aq_conv_desc* d) {
   if (d->stride != 1 && d->stride != 2) return fail(c, AQ_ERR_UNSUPPORTED, "conv stride %d", d->stride);
   if (sb.h / d->stride != db.h || sb.w / d->stride != db.w)
     return fail(c, AQ_ERR_ARG, "conv: src %dx%d / stride %d != dst %dx%d", sb.h, sb.w, d->stride, db.h, db.w);
-  if (d->res >= 0 && (c->bufs[d->res].h != db.h || c->bufs[d->res].w != db.w)) return fail(c, AQ_ERR_ARG, "conv: residual geometry mismatch");
+  if (d->res >= 0 && (d->res != d->dst || d->res_c_off != d->dst_c_off))
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv: the residual operand must be the destination slice itself (dst += f(conv)); "
+                                       "got res (%d,%d) vs dst (%d,%d)", d->res, d->res_c_off, d->dst, d->dst_c_off);
+  if (d->act != AQ_ACT_NONE && d->act != AQ_ACT_SILU && d->act != AQ_ACT_SILU_FAST) return fail(c, AQ_ERR_ARG, "conv: unknown activation %d", d->act);
   Op op;
   op.kind = OP_CONV;
   op.conv = *d;
   const size_t nw = (size_t)d->c_out * d->k * d->k * d->c_in;
-  op.w_host.assign(d->weight, d->weight + nw);
+  (void)nw;
+  repack_weights(d->weight, d->c_out, d->k * d->k, d->c_in, op.w_host);
   op.b_host.assign(d->bias, d->bias + d->c_out);
   op.conv.weight = nullptr;
   op.conv.bias = nullptr;
@@ -562,7 +688,7 @@ int aq_plan_detect(aq_ctx* c, const aq_detect_desc* d) {
   op.kind = OP_DETECT;
   op.det = *d;
   const int n_out = 3 * (d->nc + 5);
-  op.w_host.assign(d->weight, d->weight + (size_t)n_out * d->c_in);
+  repack_weights(d->weight, n_out, 1, d->c_in, op.w_host);
   op.b_host.assign(d->bias, d->bias + n_out);
   op.det.weight = nullptr;
   op.det.bias = nullptr;
@@ -621,6 +747,8 @@ int aq_plan_end(aq_ctx* c) {
     CU_CHECK(c, cudaMemcpyAsync(op.w_dev, op.w_host.data(), op.w_host.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
     std::vector<float> bias((size_t)k.n_tiles_n * k.tile_n, 0.f);
     memcpy(bias.data(), op.b_host.data(), op.b_host.size() * sizeof(float));
+    if (k.act == ACT_SILU_FAST)  // the kernel evaluates silu(x) = h + h * tanh(h) with h = acc / 2 + bias / 2
+      for (auto& b : bias) b *= 0.5f;
     CU_CHECK(c, cudaMalloc(&op.b_dev, bias.size() * sizeof(float)));
     CU_CHECK(c, cudaMemcpy(op.b_dev, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
     CU_CHECK(c, cudaStreamSynchronize(c->stream));
@@ -703,6 +831,30 @@ int aq_profile_ops(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   return rc ? rc : n;
 }
 
+int aq_debug_plan_conv(int batch, int h, int w, int c_in, int c_out, int k, int stride, int num_sms, int mblk, int mode,
+                       char* buf, size_t cap) {
+  if (!buf || batch <= 0 || h <= 0 || w <= 0) return AQ_ERR_ARG;
+  aq_ctx tmp;  // host-only: no CUDA call is made on this path
+  tmp.batch = batch;
+  tmp.num_sms = num_sms > 0 ? num_sms : 148;
+  Buffer s{}, d{};
+  s.h = h; s.w = w; s.c = c_in;
+  d.h = h / stride; d.w = w / stride; d.c = c_out;
+  tmp.bufs.push_back(s);
+  tmp.bufs.push_back(d);
+  Op op;
+  op.kind = OP_CONV;
+  op.conv.src = 0; op.conv.c_in = c_in; op.conv.dst = 1; op.conv.c_out = c_out; op.conv.k = k; op.conv.stride = stride;
+  op.conv.act = AQ_ACT_SILU; op.conv.res = -1; op.conv.mblk = mblk; op.conv.mode = mode;
+  int rc = plan_conv_geometry(&tmp, op);
+  if (rc) {
+    snprintf(buf, cap, "%s", tmp.err.c_str());
+    return rc;
+  }
+  tmp.ops.push_back(op);
+  return aq_op_describe(&tmp, 0, buf, cap);
+}
+
 int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
   if (!c || !buf || i < 0 || i >= (int)c->ops.size()) return AQ_ERR_ARG;
   const Op& op = c->ops[i];
@@ -714,12 +866,15 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
     const int c_in = det ? op.det.c_in : op.conv.c_in;
     const int c_out = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
     const double M = (double)c->batch * (sb.h / stride) * (sb.w / stride);
-    const double flops = 2.0 * M * c_out * c_in * k.ksize * k.ksize;
+    const double flops = 2.0 * M * c_out * c_in * k.taps;
     const double bytes = 2.0 * ((double)c->batch * sb.h * sb.w * c_in + M * c_out * (k.has_res ? 2 : 1)) +
-                         2.0 * c_out * c_in * k.ksize * k.ksize;
-    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f tileN=%d cb=%d cps=%d stages=%d tile=%dx%d mt=%d nt=%d | flop=%.4g bytes=%.4g",
-             det ? "detect" : "conv", k.ksize, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, k.tile_n, k.cb, k.cps,
-             k.num_stages, k.tw, k.th, k.m_tiles, k.n_tiles_n, flops, bytes);
+                         2.0 * c_out * c_in * k.taps;
+    const int ksz = k.taps == 9 ? 3 : 1;
+    static const char* mode_name[] = {"flat", "halo", "tap"};
+    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d tile=%dx%d mt=%d nt=%d | flop=%.4g bytes=%.4g",
+             det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
+             k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.tw, k.th,
+             k.m_tiles, k.n_tiles_n, flops, bytes);
   } else if (op.kind == OP_POOL) {
     const Buffer& b = c->bufs[op.buf];
     snprintf(buf, cap, "sppf_pool %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 4.0);

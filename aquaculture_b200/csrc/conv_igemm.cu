@@ -8,322 +8,407 @@ using namespace ptx;
 
 namespace {
 
-struct TileCoord {
-  int m_tile, n_tile;
-  int n, y0, x0;  // spatial modes
-  int m0;         // flat mode
+struct MBlock {
+  int n, y0, x0;  // spatial modes: image, first output row / column
+  int m0;         // flat mode: first flat pixel
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const ConvKParams& p, int tile) {
-  TileCoord t;
-  t.m_tile = tile / p.n_tiles_n;
-  t.n_tile = tile - t.m_tile * p.n_tiles_n;
-  t.m0 = t.m_tile * kTileM;
-  if (p.mode != CONV_MODE_FLAT) {
+// Output coordinates of M block `mb` of M tile `m_tile`.
+__device__ __forceinline__ MBlock mblock_coords(const ConvKParams& p, int m_tile, int mb) {
+  MBlock r;
+  r.n = r.y0 = r.x0 = r.m0 = 0;
+  if (p.mode == CONV_MODE_FLAT) {
+    r.m0 = (m_tile * p.mblk + mb) * kTileM;
+  } else if (p.mode == CONV_MODE_HALO) {
     const int per_img = p.tiles_x * p.tiles_y;
-    t.n = t.m_tile / per_img;
-    const int r = t.m_tile - t.n * per_img;
-    const int ty = r / p.tiles_x;
-    t.y0 = ty * p.th;
-    t.x0 = (r - ty * p.tiles_x) * p.tw;
+    r.n = m_tile / per_img;
+    const int rem = m_tile - r.n * per_img;
+    const int ty = rem / p.tiles_x;
+    const int tx = rem - ty * p.tiles_x;
+    r.x0 = tx * 8 * p.mx + (p.mx == 2 ? mb * 8 : 0);
+    r.y0 = ty * 16 * p.my + (p.my == 2 ? mb * 16 : 0);
   } else {
-    t.n = t.y0 = t.x0 = 0;
+    const int idx = m_tile * p.mblk + mb;
+    const int per_img = p.tiles_x * p.tiles_y;
+    r.n = idx / per_img;  // >= batch for the padding block of an odd count: TMA zero-fills / clips it
+    const int rem = idx - r.n * per_img;
+    const int ty = rem / p.tiles_x;
+    r.y0 = ty * p.th;
+    r.x0 = (rem - ty * p.tiles_x) * p.tw;
   }
-  return t;
+  return r;
 }
 
-// Byte offset of 16-byte chunk (row r, chunk j) inside a swizzled [128 x ob] fp16 staging group
-// (TMA swizzle modes 32B/64B/128B = XOR of address bits [4,4+B) with bits [7,7+B)).
-__device__ __forceinline__ uint32_t swz_off(uint32_t r, uint32_t j, uint32_t pitch, uint32_t mask) {
-  uint32_t a = r * pitch + (j << 4);
-  return a ^ (((a >> 7) & mask) << 4);
+// Weight chunk index (64 K elements each) of K step s: weights are [c_out][tap][chunk][64].
+__device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
+  if (p.mode != CONV_MODE_HALO) return s;  // FLAT: s = chunk; TAP: s = tap * cpt + chunk
+  const int c = s / 9;                     // HALO: s = chunk * 9 + tap
+  return (s - c * 9) * p.cpt + c;
 }
 
-__device__ __forceinline__ float silu(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
+__device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
 template <int EPI>
 __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 6];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8];
+  __shared__ __align__(16) float s_bias[kMaxCout];
   __shared__ uint32_t tmem_slot;
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t c_base = smem_base + p.num_stages * p.stage_bytes;
+  const uint32_t a_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t b_base = a_base + p.na * p.a_slot_bytes;
+  const uint32_t stg_base = b_base + p.nb * p.b_slot_bytes;
 
   const uint32_t bar0 = smem_u32(bars);
-  auto full_bar = [&](int s) { return bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return bar0 + 8u * (kMaxStages + s); };
-  auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + a); };
-  auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * kMaxStages + 2 + a); };
-  const uint32_t res_full = bar0 + 8u * (2 * kMaxStages + 4);
-  const uint32_t res_empty = bar0 + 8u * (2 * kMaxStages + 5);
+  auto a_full = [&](int s) { return bar0 + 8u * s; };
+  auto a_empty = [&](int s) { return bar0 + 8u * (kMaxA + s); };
+  auto b_full = [&](int s) { return bar0 + 8u * (2 * kMaxA + s); };
+  auto b_empty = [&](int s) { return bar0 + 8u * (2 * kMaxA + kMaxB + s); };
+  auto tfull = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
+  auto tempty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
+  auto stg_full = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 4 + a); };
+  auto stg_empty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 6 + a); };
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmA);
-    prefetch_tmap(&p.tmB);
-    if (EPI == EPI_STORE) {
-      prefetch_tmap(&p.tmOut);
-      if (p.has_res) prefetch_tmap(&p.tmRes);
-    }
+    if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
-  if (warp == 1) {
-    if (lane == 0) {
-      for (int s = 0; s < p.num_stages; ++s) {
-        mbar_init(full_bar(s), 1);
-        mbar_init(empty_bar(s), 1);
-      }
-      for (int a = 0; a < 2; ++a) {
-        mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), 4);
-      }
-      mbar_init(res_full, 1);
-      mbar_init(res_empty, 1);
-      fence_barrier_init();
+  if (warp == 3 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == 1 && lane == 0) {
+    prefetch_tmap(&p.tmB);
+    for (int s = 0; s < p.na; ++s) {
+      mbar_init(a_full(s), 1);
+      mbar_init(a_empty(s), 1);
     }
-    __syncwarp();
+    for (int s = 0; s < p.nb; ++s) {
+      mbar_init(b_full(s), 1);
+      mbar_init(b_empty(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull(a), 1);
+      mbar_init(tempty(a), kEpiWarps);
+      mbar_init(stg_full(a), kEpiWarps);
+      mbar_init(stg_empty(a), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
     tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
     tmem_relinquish();
   }
+  for (int i = threadIdx.x; i < p.n_tiles_n * p.tile_n; i += kConvThreads) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  griddep_launch_dependents();
 
   const int total_tiles = p.m_tiles * p.n_tiles_n;
 
   if (warp == 0) {
-    // =========================== TMA producer ===========================
+    // =========================== A producer ===========================
     if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const TileCoord t = decode_tile(p, tile);
-        const int n0 = t.n_tile * p.tile_n;
-        if (EPI == EPI_STORE && p.has_res) {
-          // residual tile -> output staging buffer, once the previous tile's store has drained it
-          mbar_wait(res_empty, (it & 1) ^ 1);
-          mbar_arrive_expect_tx(res_full, (p.a_box_bytes / (p.cb * 2)) * p.tile_n * 2);
-          const uint32_t grp_bytes = kTileM * p.ob * 2;
-          for (int g = 0; g < p.tile_n / p.ob; ++g) {
-            if (p.mode == CONV_MODE_FLAT)
-              tma_load_2d(c_base + g * grp_bytes, &p.tmRes, res_full, n0 + g * p.ob, t.m0);
-            else
-              tma_load_4d(c_base + g * grp_bytes, &p.tmRes, res_full, n0 + g * p.ob, t.x0, t.y0, t.n);
-          }
-        }
-        int chunk = 0;
-        for (int ks = 0; ks < p.kstages; ++ks) {
-          mbar_wait(empty_bar(stage), phase ^ 1);
-          const int nch = min(p.cps, p.total_chunks - chunk);
-          mbar_arrive_expect_tx(full_bar(stage), nch * (p.a_box_bytes + p.b_box_bytes));
-          const uint32_t sa = smem_base + stage * p.stage_bytes;
-          const uint32_t sb = sa + p.cps * p.a_sub_bytes;
-          for (int j = 0; j < nch; ++j, ++chunk) {
-            const int tap = chunk / p.cpt;
-            const int c0 = (chunk - tap * p.cpt) * p.cb;
-            const int kh = tap / p.ksize;
-            const int kw = tap - kh * p.ksize;
-            const uint32_t dst = sa + j * p.a_sub_bytes;
-            if (p.mode == CONV_MODE_FLAT) {
-              tma_load_2d(dst, &p.tmA, full_bar(stage), c0, t.m0);
-            } else if (p.mode == CONV_MODE_S1) {
-              tma_load_4d(dst, &p.tmA, full_bar(stage), c0, t.x0 + kw - p.pad, t.y0 + kh - p.pad, t.n);
-            } else {
-              // input row 2*Y + kh - 1: kh=0 -> (parity 1, Y-1), kh=1 -> (0, Y), kh=2 -> (1, Y)
-              const int yp = (kh + 1) & 1, dy = (kh == 0) ? -1 : 0;
-              const int xp = (kw + 1) & 1, dx = (kw == 0) ? -1 : 0;
-              tma_load_5d(dst, &p.tmA, full_bar(stage), xp * p.src_ct + p.src_c_off + c0, t.x0 + dx, yp,
-                          t.y0 + dy, t.n);
+      griddep_wait();  // activations are written by the previous kernel
+      const int n_groups = p.n_steps / p.a_group;
+      uint32_t ga = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_tile = tile / p.n_tiles_n;
+        for (int grp = 0; grp < n_groups; ++grp, ++ga) {
+          const uint32_t slot = ga % p.na;
+          mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+          const uint32_t dst = a_base + slot * p.a_slot_bytes;
+          if (p.mode == CONV_MODE_FLAT) {
+            tma_load_2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
+          } else if (p.mode == CONV_MODE_HALO) {
+            const MBlock t = mblock_coords(p, m_tile, 0);
+            tma_load_4d(dst, &p.tmA, a_full(slot), grp * 64, t.x0 - 1, t.y0 - 1, t.n);
+          } else {
+            const int tap = grp / p.cpt;
+            const int c0 = (grp - tap * p.cpt) * 64;
+            const int kh = tap / 3, kw = tap - kh * 3;
+            for (int mb = 0; mb < p.mblk; ++mb) {
+              const MBlock t = mblock_coords(p, m_tile, mb);
+              const uint32_t d = dst + mb * (kTileM * 128);
+              if (p.stride == 1) {
+                tma_load_4d(d, &p.tmA, a_full(slot), c0, t.x0 + kw - 1, t.y0 + kh - 1, t.n);
+              } else {
+                // input row 2*Y + kh - 1: kh=0 -> (parity 1, Y-1), kh=1 -> (0, Y), kh=2 -> (1, Y); same in x
+                const int yp = (kh + 1) & 1, dy = (kh == 0) ? -1 : 0;
+                const int xp = (kw + 1) & 1, dx = (kw == 0) ? -1 : 0;
+                tma_load_5d(d, xp ? &p.tmA2 : &p.tmA, a_full(slot), c0, t.x0 + dx, yp, t.y0 + dy, t.n);
+              }
             }
-            tma_load_2d(sb + j * p.b_sub_bytes, &p.tmB, full_bar(stage), tap * p.cpt * p.cb + c0, n0);
-          }
-          if (++stage == p.num_stages) {
-            stage = 0;
-            phase ^= 1;
           }
         }
       }
     }
   } else if (warp == 1) {
+    // =========================== weight producer ===========================
+    if (lane == 0) {
+      if (p.b_res) {
+        // all K steps of the (single) N tile stay resident: load once, never released
+        for (int s = 0; s < p.n_steps; ++s) {
+          mbar_arrive_expect_tx(b_full(s), p.b_tx_bytes);
+          tma_load_2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), weight_chunk(p, s) * 64, 0);
+        }
+      } else {
+        uint32_t g = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+          const int n0 = (tile % p.n_tiles_n) * p.tile_n;
+          for (int s = 0; s < p.n_steps; ++s, ++g) {
+            const uint32_t slot = g % p.nb;
+            mbar_wait(b_empty(slot), ((g / p.nb) & 1u) ^ 1u);
+            mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
+            tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 2) {
     // =========================== MMA issuer (one thread) ===========================
     if (lane == 0) {
       const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
-      const uint32_t swz = p.cb * 2;
-      int stage = 0;
-      uint32_t phase = 0;
+      const uint32_t a_sbo = p.mode == CONV_MODE_HALO ? p.pw * 128u : 1024u;
+      uint32_t g = 0, ga = 0;
       int it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(tempty_bar(as), aphase ^ 1);
+        const int as = it % p.acc_stages;
+        mbar_wait(tempty(as), (((uint32_t)(it / p.acc_stages)) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.acc_stride;
-        int chunk = 0;
-        uint32_t accumulate = 0;
-        for (int ks = 0; ks < p.kstages; ++ks) {
-          mbar_wait(full_bar(stage), phase);
-          tc_fence_after();
-          const int nch = min(p.cps, p.total_chunks - chunk);
-          const uint32_t sa = smem_base + stage * p.stage_bytes;
-          const uint32_t sb = sa + p.cps * p.a_sub_bytes;
-          for (int j = 0; j < nch; ++j) {
-            for (uint32_t kk = 0; kk < swz; kk += 32) {  // UMMA K = 16 fp16 = 32 bytes
-              umma_f16(d_tmem, make_kmajor_desc(sa + j * p.a_sub_bytes + kk, swz),
-                       make_kmajor_desc(sb + j * p.b_sub_bytes + kk, swz), idesc, accumulate);
-              accumulate = 1;
-            }
+        uint32_t a_slot_addr = 0;
+        for (int s = 0; s < p.n_steps; ++s) {
+          const int sg = s % p.a_group;
+          if (sg == 0) {
+            const uint32_t slot = ga % p.na;
+            mbar_wait(a_full(slot), (ga / p.na) & 1u);
+            a_slot_addr = a_base + slot * p.a_slot_bytes;
           }
-          chunk += nch;
-          umma_commit(empty_bar(stage));  // smem slot reusable once these MMAs retire
-          if (++stage == p.num_stages) {
-            stage = 0;
-            phase ^= 1;
+          uint32_t bslot;
+          if (p.b_res) {
+            bslot = s;
+            if (it == 0) mbar_wait(b_full(bslot), 0);
+          } else {
+            bslot = g % p.nb;
+            mbar_wait(b_full(bslot), (g / p.nb) & 1u);
+          }
+          tc_fence_after();
+          const uint32_t sb = b_base + bslot * p.b_slot_bytes;
+          for (int mb = 0; mb < p.mblk; ++mb) {
+            uint32_t sa;
+            if (p.mode == CONV_MODE_HALO) {
+              const int kh = sg / 3, kw = sg - kh * 3;
+              const int jx = p.mx == 2 ? mb : 0, jy = p.my == 2 ? mb : 0;
+              sa = a_slot_addr + (uint32_t)(((jy * 16 + kh) * p.pw) + jx * 8 + kw) * 128u;
+            } else {
+              sa = a_slot_addr + mb * (kTileM * 128);
+            }
+            const uint32_t d = d_tmem + mb * p.acc_pitch;
+#pragma unroll
+            for (uint32_t kk = 0; kk < 128; kk += 32)  // UMMA K = 16 fp16 = 32 bytes
+              umma_f16(d, make_sw128_desc(sa + kk, a_sbo), make_sw128_desc(sb + kk, 1024), idesc,
+                       (s > 0 || kk > 0) ? 1u : 0u);
+          }
+          if (!p.b_res) {
+            umma_commit(b_empty(bslot));  // weight slot reusable once these MMAs retire
+            ++g;
+          }
+          if (sg == p.a_group - 1) {
+            umma_commit(a_empty(ga % p.na));
+            ++ga;
           }
         }
-        umma_commit(tfull_bar(as));  // accumulator ready for the epilogue
+        umma_commit(tfull(as));  // accumulators ready for the epilogue
       }
     }
-  } else {
-    // =========================== epilogue warps 2..5 ===========================
-    const uint32_t q = warp & 3;        // TMEM lane quarter this warp may access
-    const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane
-    const bool store_thread = (warp == 2 && lane == 0);
-    const uint32_t pitch = p.ob * 2;
-    const uint32_t mask = (pitch >> 4) - 1;
-    const uint32_t grp_bytes = kTileM * pitch;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const TileCoord t = decode_tile(p, tile);
-      const int n0 = t.n_tile * p.tile_n;
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
-      mbar_wait(tfull_bar(as), aphase);
-      tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((q * 32u) << 16) + as * p.acc_stride;
-
-      if (EPI == EPI_STORE) {
-        if (p.has_res) {
-          mbar_wait(res_full, it & 1);
-        } else if (it > 0) {
-          if (store_thread) tma_store_wait_read0();  // previous tile's store has finished reading smem
-          named_bar_sync(1, 128);
-        }
-        for (int c0 = 0; c0 < p.tile_n; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld16(t_addr + c0, v);
-          tmem_ld_wait();
-          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + c0);
-          float f[16];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 b = __ldg(bp + i);
-            f[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + b.x;
-            f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b.y;
-            f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b.z;
-            f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b.w;
-          }
-          if (p.act) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] = silu(f[i]);
-          }
-          const int g = c0 / p.ob;
-          const uint32_t j = (uint32_t)(c0 - g * p.ob) >> 3;
-          const uint32_t a0 = c_base + g * grp_bytes + swz_off(row, j, pitch, mask);
-          const uint32_t a1 = c_base + g * grp_bytes + swz_off(row, j + 1, pitch, mask);
-          if (p.has_res) {
-            uint32_t r[8];
-            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a0));
-            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
-                         : "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(a1));
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float2 rr = __half22float2(*reinterpret_cast<const __half2*>(&r[i]));
-              f[2 * i] += rr.x;
-              f[2 * i + 1] += rr.y;
+  } else if (warp == 3) {
+    // =========================== TMA store issuer ===========================
+    if (EPI == EPI_STORE && lane == 0) {
+      uint32_t k = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_tile = tile / p.n_tiles_n;
+        const int n0 = (tile % p.n_tiles_n) * p.tile_n;
+        for (int mb = 0; mb < p.mblk; ++mb, ++k) {
+          const uint32_t sbuf = k % p.n_stg;
+          mbar_wait(stg_full(sbuf), (k / p.n_stg) & 1u);
+          const MBlock t = mblock_coords(p, m_tile, mb);
+          for (int gq = 0; gq < p.groups; ++gq) {
+            const uint32_t src = stg_base + sbuf * p.stg_bytes + gq * (kTileM * 128);
+            if (p.mode == CONV_MODE_FLAT) {
+              if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
+              else tma_store_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
+            } else {
+              if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
+              else tma_store_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
             }
           }
-          uint32_t h[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const __half2 hh = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
-            h[i] = *reinterpret_cast<const uint32_t*>(&hh);
-          }
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a0), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3])
-                       : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
-                       : "memory");
-        }
-        // accumulator stage drained -> MMA warp may overwrite it
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(as));
-        // make the staging writes visible to the async proxy, then one thread stores the tile
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (store_thread) {
-          for (int g = 0; g < p.tile_n / p.ob; ++g) {
-            if (p.mode == CONV_MODE_FLAT)
-              tma_store_2d(&p.tmOut, c_base + g * grp_bytes, n0 + g * p.ob, t.m0);
-            else
-              tma_store_4d(&p.tmOut, c_base + g * grp_bytes, n0 + g * p.ob, t.x0, t.y0, t.n);
-          }
           tma_store_commit();
-          if (p.has_res) {
+          if (p.n_stg == 2) {
+            tma_store_wait_read1();  // the previous block's staging buffer has been read
+            if (k > 0) mbar_arrive(stg_empty((k - 1) & 1u));
+          } else {
             tma_store_wait_read0();
-            mbar_arrive(res_empty);
+            mbar_arrive(stg_empty(0));
           }
         }
-      } else {
-        // ---- Detect decode: row = one grid cell, columns = 3 anchors x (5 + nc)
-        const int m = t.m0 + (int)row;
-        const int cells = p.det_ny * p.det_nx;
-        const int b = m / cells;
-        const int pos = m - b * cells;
-        const int gy = pos / p.det_nx;
-        const int gx = pos - gy * p.det_nx;
-        const bool valid = m < p.det_m_total;
-        const int ncols = 3 * p.det_no;
-        for (int c0 = 0; c0 < p.tile_n; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld16(t_addr + c0, v);
-          tmem_ld_wait();
-          if (valid) {
+      }
+      tma_store_wait0();
+    }
+  } else {
+    // =========================== epilogue warps 4..11 ===========================
+    const uint32_t e = warp - 4;
+    const uint32_t q = e & 3;            // TMEM lane quarter this warp may access (warp % 4)
+    const uint32_t half = e >> 2;        // which of the two interleaved sets of 16-column chunks
+    const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
+    const int n_chunks = p.tile_n >> 4;
+    uint32_t k = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int m_tile = tile / p.n_tiles_n;
+      const int n0 = (tile % p.n_tiles_n) * p.tile_n;
+      const int as = it % p.acc_stages;
+      mbar_wait(tfull(as), ((uint32_t)(it / p.acc_stages)) & 1u);
+      tc_fence_after();
+      for (int mb = 0; mb < p.mblk; ++mb, ++k) {
+        const uint32_t t_addr = tmem_base + ((q * 32u) << 16) + as * p.acc_stride + mb * p.acc_pitch;
+        if (EPI == EPI_STORE) {
+          const uint32_t sbuf = k % p.n_stg;
+          mbar_wait(stg_empty(sbuf), ((k / p.n_stg) & 1u) ^ 1u);
+          const uint32_t stg = stg_base + sbuf * p.stg_bytes;
+          for (int ch = half; ch < n_chunks; ch += 2) {
+            const int c0 = ch << 4;
+            uint32_t v[16];
+            tmem_ld16(t_addr + c0, v);
+            tmem_ld_wait();
+            const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c0);
+            float f[16];
+            if (p.act == ACT_SILU_FAST) {
+              // silu(x) = h + h * tanh(h), h = x / 2; s_bias holds bias / 2
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 b = bp[i];
+                const float h0 = fmaf(__uint_as_float(v[4 * i + 0]), 0.5f, b.x);
+                const float h1 = fmaf(__uint_as_float(v[4 * i + 1]), 0.5f, b.y);
+                const float h2 = fmaf(__uint_as_float(v[4 * i + 2]), 0.5f, b.z);
+                const float h3 = fmaf(__uint_as_float(v[4 * i + 3]), 0.5f, b.w);
+                f[4 * i + 0] = fmaf(h0, tanh_approx(h0), h0);
+                f[4 * i + 1] = fmaf(h1, tanh_approx(h1), h1);
+                f[4 * i + 2] = fmaf(h2, tanh_approx(h2), h2);
+                f[4 * i + 3] = fmaf(h3, tanh_approx(h3), h3);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 b = bp[i];
+                f[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + b.x;
+                f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b.y;
+                f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b.z;
+                f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b.w;
+              }
+              if (p.act == ACT_SILU) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = silu_exact(f[i]);
+              }
+            }
+            uint32_t h[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) h[i] = pack_half2(f[2 * i], f[2 * i + 1]);
+            // staging: 64-channel groups of [128 rows][128 B], 16-byte chunk j of row r at j ^ (r & 7)
+            const uint32_t grp = stg + (uint32_t)(c0 >> 6) * (kTileM * 128) + row * 128u;
+            const uint32_t j = (uint32_t)(c0 & 63) >> 3;
+            const uint32_t a0 = grp + (((j) ^ (row & 7u)) << 4);
+            const uint32_t a1 = grp + (((j + 1) ^ (row & 7u)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a0), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3])
+                         : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
+                         : "memory");
+          }
+          if (mb == p.mblk - 1) {
+            // every TMEM read of this tile is done -> the MMA warp may overwrite the accumulators
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(as));
+          }
+          // make the staging writes visible to the async proxy, then hand the block to the store warp
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(stg_full(sbuf));
+        } else {
+          // ---- Detect decode: row = one grid cell, columns = 3 anchors x (5 + nc)
+          const MBlock t = mblock_coords(p, m_tile, mb);
+          const int m = t.m0 + (int)row;
+          const int cells = p.det_ny * p.det_nx;
+          const int b = m / cells;
+          const int pos = m - b * cells;
+          const int gy = pos / p.det_nx;
+          const int gx = pos - gy * p.det_nx;
+          const bool valid = m < p.det_m_total;
+          const int ncols = 3 * p.det_no;
+          for (int ch = half; ch < n_chunks; ch += 2) {
+            const int c0 = ch << 4;
+            uint32_t v[16];
+            tmem_ld16(t_addr + c0, v);
+            tmem_ld_wait();
+            float o[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const int col = c0 + i;
-              if (col < ncols) {
-                const int a = col / p.det_no;
-                const int o = col - a * p.det_no;
-                const float z = __uint_as_float(v[i]) + __ldg(p.bias + col);
-                const float s = __fdividef(1.0f, 1.0f + __expf(-z));
-                float out;
-                if (o == 0) out = (s * 2.0f + ((float)gx - 0.5f)) * p.det_stride;
-                else if (o == 1) out = (s * 2.0f + ((float)gy - 0.5f)) * p.det_stride;
-                else if (o == 2) out = (s * 2.0f) * (s * 2.0f) * p.det_anchor[2 * a];
-                else if (o == 3) out = (s * 2.0f) * (s * 2.0f) * p.det_anchor[2 * a + 1];
-                else out = s;
-                const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
-                p.pred[r * p.det_no + o] = out;
+              const int a = col / p.det_no;
+              const int oi = col - a * p.det_no;
+              const float z = __uint_as_float(v[i]) + s_bias[col < kMaxCout ? col : 0];
+              const float s = __fdividef(1.0f, 1.0f + __expf(-z));
+              float out;
+              if (oi == 0) out = (s * 2.0f + ((float)gx - 0.5f)) * p.det_stride;
+              else if (oi == 1) out = (s * 2.0f + ((float)gy - 0.5f)) * p.det_stride;
+              else if (oi == 2) out = (s * 2.0f) * (s * 2.0f) * p.det_anchor[a < 3 ? 2 * a : 0];
+              else if (oi == 3) out = (s * 2.0f) * (s * 2.0f) * p.det_anchor[a < 3 ? 2 * a + 1 : 0];
+              else out = s;
+              o[i] = out;
+            }
+            if (valid) {
+              if (p.det_no == 8) {
+                // two anchors per 16-column chunk, 8 floats = 32 contiguous bytes per (anchor, cell)
+#pragma unroll
+                for (int aa = 0; aa < 2; ++aa) {
+                  const int a = (c0 >> 3) + aa;
+                  if (a < 3) {
+                    const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
+                    float4* dst = reinterpret_cast<float4*>(p.pred + r * 8);
+                    dst[0] = make_float4(o[8 * aa + 0], o[8 * aa + 1], o[8 * aa + 2], o[8 * aa + 3]);
+                    dst[1] = make_float4(o[8 * aa + 4], o[8 * aa + 5], o[8 * aa + 6], o[8 * aa + 7]);
+                  }
+                }
+              } else {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  const int col = c0 + i;
+                  if (col < ncols) {
+                    const int a = col / p.det_no;
+                    const int oi = col - a * p.det_no;
+                    const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
+                    p.pred[r * p.det_no + oi] = o[i];
+                  }
+                }
               }
             }
           }
+          if (mb == p.mblk - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(as));
+          }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(as));
       }
     }
-    if (EPI == EPI_STORE && store_thread) tma_store_wait0();
   }
 
   // teardown: everyone done with TMEM before the allocating warp frees it
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
@@ -332,11 +417,10 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 }  // namespace
 
 size_t conv_smem_bytes(const ConvKParams& p) {
-  return (size_t)p.num_stages * p.stage_bytes + p.c_bytes + 1024;
+  return (size_t)p.na * p.a_slot_bytes + (size_t)p.nb * p.b_slot_bytes + (size_t)p.n_stg * p.stg_bytes + 1024;
 }
 
 cudaError_t conv_kernels_init() {
-  // 227 KB per CTA includes the kernel's static shared memory (barriers): leave 1 KB for it
   cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        kConvMaxDynSmem);
   if (e != cudaSuccess) return e;
@@ -344,15 +428,20 @@ cudaError_t conv_kernels_init() {
                               kConvMaxDynSmem);
 }
 
-cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, cudaStream_t stream) {
+cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
   const int total = p.m_tiles * p.n_tiles_n;
-  const int grid = total < num_sms ? total : num_sms;
-  const size_t smem = conv_smem_bytes(p);
-  if (epi == EPI_STORE)
-    conv_igemm_kernel<EPI_STORE><<<grid, kConvThreads, smem, stream>>>(p);
-  else
-    conv_igemm_kernel<EPI_DETECT><<<grid, kConvThreads, smem, stream>>>(p);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(total < num_sms ? total : num_sms);
+  cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = conv_smem_bytes(p);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE>, p);
+  return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT>, p);
 }
 
 }  // namespace aq

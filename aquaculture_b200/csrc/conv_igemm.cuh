@@ -4,51 +4,68 @@
 // models/yolo.py::Detect.forward [UPSTREAM-RECALLED; the reference reaches them through
 // `yolov5/detect.py`, REF README.md:77].
 //
-//   D[M = pixels, N = c_out] = sum over taps (kh,kw) and channel chunks of  A_tap[M, cb] * W_tap[N, cb]^T
+//   D[M = pixels, N = c_out] = sum over taps (kh,kw) and 64-channel chunks of  A_tap[M, 64] * W_tap[N, 64]^T
 //
-// * activations NHWC fp16; one M tile = 128 output pixels: 128 consecutive flat pixels for 1x1 convs, or a
-//   tw x th spatial patch of one image for 3x3 convs.  Each (tap, channel-chunk) A operand is ONE TMA box
-//   load of the shifted patch; conv zero padding is TMA out-of-bounds fill.  Stride-2 convs use a 5-D
-//   view (x-parity*C, W/2, y-parity, H/2, N) of the same buffer so the strided gather is still a dense box.
-// * weights [c_out][k*k*c_in] fp16, K-major; accumulators fp32 in TMEM (double-buffered so the epilogue of
-//   tile i overlaps the MMAs of tile i+1).
-// * warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
-//   warps 2..5 = epilogue (TMEM -> regs -> bias + SiLU (+ residual) -> fp16 -> swizzled smem -> TMA store
-//   into a channel slice of the destination buffer, which is how concat disappears).
-// * persistent CTAs (grid = min(tiles, SMs)), static round-robin tile order with N tiles adjacent so
-//   CTAs sharing an A patch run concurrently and hit L2.
+// * activations NHWC fp16.  Every TMA row is one pixel x 64 channels = 128 bytes (SWIZZLE_128B); channel
+//   counts that are not multiples of 64 are completed by TMA out-of-bounds zero fill (loads) / clipping
+//   (stores), so no buffer is padded in HBM.  Weights are stored [c_out][tap][chunk][64] with zero padding.
+// * an "M block" is 128 output pixels = one UMMA M=128 accumulator; a CTA tile is 1 or 2 M blocks that share
+//   every weight tile (halves the weight traffic L2 -> SM per output).  Three ways to feed A:
+//     FLAT  1x1 convs: 128 consecutive pixels per M block, one box load per 64-channel chunk.
+//     HALO  3x3/s1 convs: the CTA loads the (8*mx+2) x (16*my+2) pixel halo patch ONCE per chunk; the nine
+//           taps are nine UMMA descriptors into that patch (start address shifted by whole 128-byte rows,
+//           stride-byte-offset = patch row pitch; the swizzle is a function of the absolute smem address, so
+//           any 128-byte-multiple offset is legal -- measured, profiles/r1_hw_probe_v1.txt T1).
+//     TAP   3x3/s2 convs and small maps: one shifted box per (tap, chunk); stride 2 uses a parity view
+//           (c, W/2, y-parity, H/2, N) per x-parity so the strided gather is still a dense box.
+// * warp roles (384 threads): warp 0 = A producer, warp 1 = weight producer, warp 2 = TMEM allocator +
+//   single-thread MMA issuer, warp 3 = TMA store issuer, warps 4..11 = epilogue (TMEM -> regs -> bias + SiLU
+//   -> fp16 -> swizzled smem staging).  Separate warps because one thread sustains only one
+//   cp.async.bulk.tensor per ~0.2-0.4 us (measured, T4): loads, weight loads and stores must not queue
+//   behind each other.
+// * the Bottleneck residual (dst += f(conv)) is a TMA reduce-add of the staged tile into the destination
+//   (the residual operand is the destination slice itself), so it costs no load.
+// * weights of small layers stay resident in shared memory for the whole (persistent) kernel.
+// * accumulators fp32 in TMEM, double-buffered when 2 * mblk * N <= 512 columns.
+// * persistent CTAs (grid = min(tiles, SMs)), static round-robin tile order with N tiles adjacent; launched
+//   with programmatic dependent launch so the prologue (barrier init, TMEM alloc, weight prefetch) overlaps
+//   the previous kernel's tail.
 #pragma once
 #include <cuda.h>
 #include <stdint.h>
 
 namespace aq {
 
-enum { CONV_MODE_FLAT = 0, CONV_MODE_S1 = 1, CONV_MODE_S2 = 2 };
+enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2 };
 enum { EPI_STORE = 0, EPI_DETECT = 1 };
+enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
-constexpr int kConvThreads = 192;
-constexpr int kMaxStages = 8;
+constexpr int kConvThreads = 384;
+constexpr int kEpiWarps = 8;
+constexpr int kMaxA = 4;    // A ring slots
+constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
 constexpr int kTileM = 128;
-constexpr int kConvMaxDynSmem = 232448 - 1024;  // 227 KB opt-in limit minus static smem
+constexpr int kMaxCout = 768;
+constexpr int kConvMaxDynSmem = 232448 - 6144;  // 227 KB opt-in limit minus static smem (barriers, bias)
 
 struct alignas(64) ConvKParams {
-  CUtensorMap tmA;    // activation loads
+  CUtensorMap tmA;    // activation loads (TAP stride 2: x-parity 0)
+  CUtensorMap tmA2;   // TAP stride 2: x-parity 1
   CUtensorMap tmB;    // weight loads
-  CUtensorMap tmOut;  // output stores        (EPI_STORE)
-  CUtensorMap tmRes;  // residual tile loads  (EPI_STORE, has_res)
-  const float* bias;  // [n_tiles_n * tile_n], zero padded
-  int mode, ksize, pad;
-  int cb, cpt;        // channels per chunk (16/32/64), chunks per tap (= c_in / cb)
-  int total_chunks, cps, kstages;  // chunks per tile, chunks per pipeline stage, ceil(total/cps)
-  int num_stages;
-  int tile_n, n_tiles_n, ob;       // UMMA N, number of N tiles, channels per output store group
-  int m_tiles, tw, th, tiles_x, tiles_y;
-  int src_ct, src_c_off;           // mode S2: channels of the source buffer / first channel
+  CUtensorMap tmOut;  // output stores / reduce-adds (EPI_STORE)
+  const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
+  int mode, stride;
+  int cpt, taps, n_steps;  // 64-channel chunks per tap, taps, K steps per tile (= taps * cpt)
+  int a_group;             // K steps that share one A slot (HALO: 9, else 1)
+  int mblk, mx, my, pw;    // M blocks per tile; HALO arrangement and patch width in pixels
+  int na, nb, b_res, n_stg, acc_stages;
+  int tile_n, n_tiles_n, groups;  // UMMA N, N tiles, 64-channel store groups per tile
+  int m_tiles;                    // tiles along M
+  int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;
-  uint32_t a_sub_bytes, b_sub_bytes, stage_bytes;  // smem strides (1024-aligned)
-  uint32_t a_box_bytes, b_box_bytes;               // bytes one TMA box actually delivers
-  uint32_t c_bytes;                                // output staging bytes
-  uint32_t tmem_cols, acc_stride;
+  uint32_t a_slot_bytes, b_slot_bytes, stg_bytes;
+  uint32_t a_tx_bytes, b_tx_bytes;  // bytes one slot fill delivers
+  uint32_t tmem_cols, acc_stride, acc_pitch;  // TMEM columns: allocation, per accumulator stage, per M block
   // EPI_DETECT
   float* pred;
   int det_no, det_rows, det_level_off, det_ny, det_nx, det_m_total;
@@ -57,7 +74,7 @@ struct alignas(64) ConvKParams {
 };
 
 size_t conv_smem_bytes(const ConvKParams& p);
-cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, cudaStream_t stream);
+cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
 cudaError_t conv_kernels_init();  // sets max dynamic smem attributes
 
 }  // namespace aq

@@ -16,6 +16,7 @@ Graph rewrites done here (all exact):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -23,7 +24,7 @@ import numpy as np
 import torch
 
 from . import _lib, arch, weights
-from ._lib import AQ_ACT_NONE, AQ_ACT_SILU, AquaError, ConvDesc, DetectDesc
+from ._lib import AQ_ACT_NONE, AQ_ACT_SILU, AQ_ACT_SILU_FAST, AquaError, ConvDesc, DetectDesc
 
 MAX_WH = 7680.0   # upstream non_max_suppression: class offset (pixels)
 MAX_NMS = 30000   # upstream non_max_suppression: boxes into torchvision.ops.nms
@@ -81,14 +82,15 @@ class Context:
         return self.call("aq_plan_buffer", h, w, c)
 
     def conv(self, src, dst, w_oihw: torch.Tensor, bias: torch.Tensor, k, stride, act=True, res=None,
-             tile_n=0, chunks_per_stage=0):
-        """src/dst/res are (buffer id, channel offset); w_oihw fp32 (O,I,k,k)."""
+             tile_n=0, mblk=0, mode=0):
+        """src/dst/res are (buffer id, channel offset); w_oihw fp32 (O,I,k,k).  act: False/0 none, True/1 SiLU
+        (ex2+rcp), 2 SiLU via tanh.approx; res must equal dst (in-place Bottleneck add)."""
         wk = pack_krsc(w_oihw)
         b = np.ascontiguousarray(bias.float().numpy())
         self._keep += [wk, b]
         d = ConvDesc(src[0], src[1], w_oihw.shape[1], dst[0], dst[1], w_oihw.shape[0], k, stride,
-                     AQ_ACT_SILU if act else AQ_ACT_NONE, res[0] if res else -1, res[1] if res else 0,
-                     wk.ctypes.data, b.ctypes.data, tile_n, chunks_per_stage)
+                     int(act), res[0] if res else -1, res[1] if res else 0,
+                     wk.ctypes.data, b.ctypes.data, tile_n, mblk, mode)
         self.call("aq_plan_conv", C.byref(d))
 
     def detect_level(self, src, w_oi: torch.Tensor, bias: torch.Tensor, nc, level_row_off, stride, anchors_px):
@@ -174,6 +176,9 @@ class TileDetector:
         self.net_h, self.net_w = int(imgsz[0]), int(imgsz[1])
         self.conf_thres, self.iou_thres, self.max_det = float(conf_thres), float(iou_thres), int(max_det)
         self.agnostic, self.classes = bool(agnostic), list(classes) if classes else None
+        # SiLU evaluation in the conv epilogues: "fast" = tanh.approx form (<= 1.1e-5 absolute error, measured),
+        # "exact" = ex2 + rcp.  Both are device code; this only selects the epilogue variant.
+        self.act = AQ_ACT_SILU if os.environ.get("AQUA_SILU", "fast") == "exact" else AQ_ACT_SILU_FAST
         self.ctx = ctx if ctx is not None else Context(device)   # `ctx` lets tests inject the plan emulator
         self._build(state_dict)
         self._dets = self._counts = None  # pinned host staging, double-buffered, allocated on first use
@@ -208,7 +213,7 @@ class TileDetector:
 
         def conv(name, src, dst, k, s, res=None):
             w, b = fw[name]
-            ctx.conv(src, dst, w, b, k, s, True, res)
+            ctx.conv(src, dst, w, b, k, s, self.act, res)
 
         def c3(idx, src, c1, dst, c2, n, shortcut, hw):
             c_ = c2 // 2
@@ -217,7 +222,7 @@ class TileDetector:
             pre = f"model.{idx}"
             w1, b1 = fw[pre + ".cv1"]
             w2, b2 = fw[pre + ".cv2"]
-            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, True)
+            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, self.act)
             for j in range(n):
                 conv(f"{pre}.m.{j}.cv1", (cat, 0), (tmp, 0), 1, 1)
                 conv(f"{pre}.m.{j}.cv2", (tmp, 0), (cat, 0), 3, 1, res=(cat, 0) if shortcut else None)
@@ -226,7 +231,7 @@ class TileDetector:
         L = {l.idx: l for l in arch.yolov5m_layers(nc)}
         # backbone
         w0, b0 = fw["model.0"]
-        ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, True)
+        ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, self.act)
         conv("model.1", (x0, 0), (x1, 0), 3, 2)
         c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4))
         conv("model.3", (x2, 0), (x3, 0), 3, 2)

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define AQ_ABI_VERSION 1
+#define AQ_ABI_VERSION 2
 
 typedef enum aq_status {
   AQ_OK = 0,
@@ -42,7 +42,9 @@ typedef struct aq_ctx aq_ctx;
 
 /* Activation flags of a conv op. */
 #define AQ_ACT_NONE 0
-#define AQ_ACT_SILU 1
+#define AQ_ACT_SILU 1       /* x * sigmoid(x) with ex2 + rcp (~1e-6 absolute) */
+#define AQ_ACT_SILU_FAST 2  /* h + h * tanh.approx(h), h = x / 2: one MUFU per element, <= 1.1e-5 absolute
+                               (profiles/r1_hw_probe_v1.txt T5), below the fp16 rounding of the stored value */
 
 /*
  * One fused convolution = upstream models/common.py::Conv.forward_fuse (conv + folded BN bias + SiLU)
@@ -57,12 +59,15 @@ typedef struct aq_conv_desc {
   int k;                        /* 1 or 3 (the 6x6/s2 stem is given as 3x3/s1 over the space-to-depth input) */
   int stride;                   /* 1 or 2 */
   int act;                      /* AQ_ACT_* */
-  int res, res_c_off;           /* residual buffer id (or -1) and first channel; added AFTER the activation */
+  int res, res_c_off;           /* residual buffer id (or -1) and first channel; added AFTER the activation.
+                                   Must name the destination slice itself (Bottleneck runs in place in the C3
+                                   concat buffer): the add is a TMA reduce-add into dst, it costs no load. */
   const uint16_t* weight;       /* host, fp16 bits, [c_out][k][k][c_in] (KRSC), BN already folded */
   const float* bias;            /* host, fp32 [c_out] */
   /* tuning knobs; 0 = let the library choose */
   int tile_n;                   /* UMMA N per tile */
-  int chunks_per_stage;
+  int mblk;                     /* 128-pixel M blocks per CTA tile (1 or 2) */
+  int mode;                     /* 3x3/s1 only: 1 = halo patch in shared memory, 2 = one box per tap */
 } aq_conv_desc;
 
 /*
@@ -112,6 +117,10 @@ int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
  * (kind, GEMM shape, tile configuration, algorithmic FLOPs and bytes) of op `i`. */
 int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
+/* Host-only planner probe (no device needed): the tiling the library would choose for one conv of the given
+ * shape, written as the same one-line description aq_op_describe gives.  mblk / mode = 0 lets it choose. */
+int aq_debug_plan_conv(int batch, int h, int w, int c_in, int c_out, int k, int stride, int num_sms, int mblk, int mode,
+                       char* buf, size_t cap);
 
 /* ------------------------------------------------------------------ execution */
 /*

@@ -24,7 +24,7 @@ class PlanEmulator:
         self.bufs.append(torch.zeros(self.batch, h, w, c))
         return len(self.bufs) - 1
 
-    def conv(self, src, dst, w_oihw, bias, k, stride, act=True, res=None, tile_n=0, chunks_per_stage=0):
+    def conv(self, src, dst, w_oihw, bias, k, stride, act=True, res=None, tile_n=0, mblk=0, mode=0):
         # weights go through the same fp16 rounding the device sees
         self.ops.append(("conv", src, dst, w_oihw.half().float(), bias.float(), k, stride, act, res))
 

@@ -23,7 +23,7 @@ def ctx():
 
 
 def run_conv_case(ctx, B, H, W, c_in, c_out, k, s, act=True, res=False, src_ct=None, src_off=0, dst_ct=None,
-                  dst_off=0, seed=0, tile_n=0, cps=0):
+                  dst_off=0, seed=0, tile_n=0, mblk=0, mode=0):
     g = torch.Generator().manual_seed(seed)
     src_ct = src_ct or c_in
     dst_ct = dst_ct or c_out
@@ -35,14 +35,14 @@ def run_conv_case(ctx, B, H, W, c_in, c_out, k, s, act=True, res=False, src_ct=N
     ctx.plan_begin(B, 64, 64, 3)
     bs = ctx.buffer(H, W, src_ct)
     bd = ctx.buffer(Ho, Wo, dst_ct)
-    br = ctx.buffer(Ho, Wo, c_out) if res else None
-    ctx.conv((bs, src_off), (bd, dst_off), w, b, k, s, act, (br, 0) if res else None, tile_n, cps)
+    # the residual operand is the destination slice itself (in-place Bottleneck add)
+    ctx.conv((bs, src_off), (bd, dst_off), w, b, k, s, act, (bd, dst_off) if res else None, tile_n, mblk, mode)
     ctx.plan_end()
     ctx.upload(bs, x.numpy())
-    sentinel = np.full((B, Ho, Wo, dst_ct), 7.0, np.float16)
-    ctx.upload(bd, sentinel)
+    init = np.full((B, Ho, Wo, dst_ct), 7.0, np.float16)
     if res:
-        ctx.upload(br, r.numpy())
+        init[..., dst_off:dst_off + c_out] = r.numpy()
+    ctx.upload(bd, init)
     ctx.forward()
     ctx.sync()
     out = torch.from_numpy(ctx.download(bd)).float()
@@ -112,6 +112,37 @@ def test_conv3x3_s2(ctx, B, H, W, ci, co):
 
 def test_conv3x3_s2_channel_slice(ctx):
     run_conv_case(ctx, 2, 40, 40, 192, 192, 3, 2, src_ct=384, src_off=192, dst_ct=384, dst_off=0)
+
+
+# every A-feeding variant of the 3x3/s1 conv: halo patch with 1 or 2 M blocks (side by side / stacked), one
+# box per tap with 1 or 2 M blocks; channel counts completed by TMA zero fill (16, 48, 96)
+@pytest.mark.parametrize("mode,mblk", [(1, 1), (1, 2), (2, 1), (2, 2)])
+@pytest.mark.parametrize("B,H,W,ci,co", [(2, 32, 32, 64, 64), (3, 40, 24, 48, 48), (2, 20, 20, 96, 96),
+                                          (1, 48, 40, 16, 48), (2, 40, 40, 192, 192)])
+def test_conv3x3_s1_variants(ctx, mode, mblk, B, H, W, ci, co):
+    run_conv_case(ctx, B, H, W, ci, co, 3, 1, mode=mode, mblk=mblk)
+    run_conv_case(ctx, B, H, W, ci, co, 3, 1, res=True, mode=mode, mblk=mblk, act=2)
+
+
+@pytest.mark.parametrize("mblk", [1, 2])
+def test_conv_mblk_variants(ctx, mblk):
+    run_conv_case(ctx, 3, 20, 20, 384, 384, 1, 1, mblk=mblk)     # 2 N tiles, streamed weights
+    run_conv_case(ctx, 5, 20, 12, 96, 96, 1, 1, mblk=mblk)       # resident weights, odd M-block count
+    run_conv_case(ctx, 2, 40, 40, 96, 192, 3, 2, mblk=mblk)
+    run_conv_case(ctx, 3, 24, 24, 48, 96, 3, 2, mblk=mblk)
+
+
+def test_conv_fast_silu(ctx):
+    run_conv_case(ctx, 2, 32, 32, 64, 64, 1, 1, act=2)
+    run_conv_case(ctx, 2, 32, 32, 96, 48, 3, 1, act=2)
+
+
+def test_conv_residual_must_be_destination(ctx):
+    ctx.plan_begin(1, 64, 64, 3)
+    a, b_, r_ = ctx.buffer(16, 16, 64), ctx.buffer(16, 16, 64), ctx.buffer(16, 16, 64)
+    with pytest.raises(engine.AquaError):
+        ctx.conv((a, 0), (b_, 0), torch.zeros(64, 64, 3, 3), torch.zeros(64), 3, 1, True, (r_, 0))
+    ctx.plan_end()
 
 
 def test_conv_many_tiles_persistent(ctx):

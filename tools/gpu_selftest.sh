@@ -7,7 +7,9 @@ run() { # name, pytest -k expr
   echo "$1 exit=$? $(tail -1 gpurun_out/selftest_$1.log)"
 }
 run conv1x1 "conv1x1"
-run conv3x3s1 "conv3x3_s1 or residual"
+run conv3x3s1 "conv3x3_s1 and not variants or residual"
+run variants "variants"
+run mblk "mblk_variants or fast_silu"
 run conv3x3s2 "conv3x3_s2"
 run persistent "many_tiles"
 run detect "detect_decode"

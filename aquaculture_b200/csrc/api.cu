@@ -188,8 +188,8 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     cd.pw = 8 * cd.mx + 2;
     cd.ph = 16 * cd.my + 2;
     cd.tiles_x = (wo + 8 * cd.mx - 1) / (8 * cd.mx);
-    cd.tiles_y = (ho + 16 * cd.my - 1) / (16 * cd.my);
-    cd.m_tiles = batch * cd.tiles_x * cd.tiles_y;
+    cd.tiles_y = (batch * (ho + 1) + 16 * cd.my - 1) / (16 * cd.my);  // tall rows: images + one zero row each
+    cd.m_tiles = cd.tiles_x * cd.tiles_y;
     cd.a_tx = (uint32_t)cd.pw * cd.ph * 128;
     cd.a_slot = (uint32_t)round_up((int)cd.a_tx, 1024);
     n_groups = cpt;
@@ -231,7 +231,12 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0;
   const double o_bytes = (double)cd.mblk * kTileM * tile_n * 2.0;
   const double l2 = (a_bytes + b_bytes + o_bytes) / 40.0;
-  const double issue = 600.0 * fmax((double)n_groups * a_instr_per_group, cd.b_res ? 0.0 : (double)n_steps);
+  // TMA: one producer thread per operand, ~600 clk per box and ~4500 clk latency per ring slot; the HALO
+  // patch is gathered by 128 cp.async threads (~1.5 clk per 128-byte row)
+  const double lat = 4500.0;
+  double issue = cd.b_res ? 0.0 : fmax(600.0 * n_steps, lat * n_steps / cd.nb);
+  if (cd.mode == CONV_MODE_HALO) issue = fmax(issue, 1.5 * cd.pw * cd.ph * n_groups);
+  else issue = fmax(issue, fmax(600.0 * n_groups * a_instr_per_group, lat * n_groups / cd.na));
   const double epi = (double)cd.mblk * tile_n * 8.0 + 400.0;
   double tile_cyc = fmax(fmax(mma, l2), fmax(issue, epi)) + 300.0;
   if (cd.acc_stages == 1) tile_cyc += epi;
@@ -290,7 +295,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
     }
   } else {
     if (stride == 1 && want_mode != 2) {
-      const int arr[3][2] = {{1, 1}, {2, 1}, {1, 2}};
+      const int arr[5][2] = {{1, 1}, {2, 1}, {1, 2}, {2, 2}, {4, 1}};
       for (auto& a : arr) {
         Cand cd;
         cd.mode = CONV_MODE_HALO;
@@ -322,6 +327,8 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   k.mx = best.mx;
   k.my = best.my;
   k.pw = best.pw;
+  k.ph = best.ph;
+  k.pw_inv = best.pw > 0 ? (65536 + best.pw - 1) / best.pw : 0;
   k.tw = best.mode == CONV_MODE_HALO ? 8 : (best.mode == CONV_MODE_FLAT ? kTileM : best.tw);
   k.th = best.mode == CONV_MODE_HALO ? 16 : (best.mode == CONV_MODE_FLAT ? 1 : best.th);
   k.tiles_x = best.tiles_x;
@@ -364,11 +371,15 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     uint64_t str[1] = {(uint64_t)sb.c * 2};
     uint32_t box[2] = {64, (uint32_t)(kTileM * k.mblk)};
     rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 2, dims, str, box, sw);
-  } else if (k.mode == CONV_MODE_HALO || k.stride == 1) {
+  } else if (k.mode == CONV_MODE_HALO) {
+    // gathered with cp.async: plain pointer + geometry
+    k.a_src = sb.ptr + src_c_off;
+    k.a_n = c->batch; k.a_h = sb.h; k.a_w = sb.w; k.a_ct = sb.c; k.a_cin = c_in;
+    rc = AQ_OK;
+  } else if (k.stride == 1) {
     uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
-    uint32_t box[4] = {64, (uint32_t)(k.mode == CONV_MODE_HALO ? k.pw : k.tw),
-                       (uint32_t)(k.mode == CONV_MODE_HALO ? 16 * k.my + 2 : k.th), 1};
+    uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
     rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 4, dims, str, box, sw);
   } else {
     // per x-parity: (channel, W/2, y-parity, H/2, N) -- a stride-2 gather becomes a dense box
@@ -415,7 +426,13 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
   uint64_t dims[4] = {(uint64_t)op.conv.c_out, (uint64_t)db.w, (uint64_t)db.h, N};
   uint64_t str[3] = {(uint64_t)db.c * 2, (uint64_t)db.w * db.c * 2, (uint64_t)db.h * db.w * db.c * 2};
   uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
-  return encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
+  rc = encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
+  if (rc || k.mode != CONV_MODE_HALO) return rc;
+  for (int hb = 0; hb < 4 && !rc; ++hb) {
+    uint32_t bx[4] = {64, 8, (uint32_t)(8 >> hb), 1};
+    rc = encode_map(c, &k.tmOutR[hb], db.ptr + op.conv.dst_c_off, 4, dims, str, bx, sw);
+  }
+  return rc;
 }
 
 // [c_out][taps][c_in] fp16 -> [c_out][taps][cpt * 64] with zero padding (so a 64-wide K chunk never straddles taps)

@@ -20,13 +20,13 @@ __device__ __forceinline__ MBlock mblock_coords(const ConvKParams& p, int m_tile
   if (p.mode == CONV_MODE_FLAT) {
     r.m0 = (m_tile * p.mblk + mb) * kTileM;
   } else if (p.mode == CONV_MODE_HALO) {
-    const int per_img = p.tiles_x * p.tiles_y;
-    r.n = m_tile / per_img;
-    const int rem = m_tile - r.n * per_img;
-    const int ty = rem / p.tiles_x;
-    const int tx = rem - ty * p.tiles_x;
-    r.x0 = tx * 8 * p.mx + (p.mx == 2 ? mb * 8 : 0);
-    r.y0 = ty * 16 * p.my + (p.my == 2 ? mb * 16 : 0);
+    // y0 is a row of the "tall" image: all images stacked with one shared zero row between them,
+    // tall row R = n * (H + 1) + y + 1 (rows n * (H + 1) are the zero rows)
+    const int ty = m_tile / p.tiles_x;
+    const int tx = m_tile - ty * p.tiles_x;
+    const int jx = mb % p.mx, jy = mb / p.mx;
+    r.x0 = (tx * p.mx + jx) * 8;
+    r.y0 = (ty * p.my + jy) * 16;
   } else {
     const int idx = m_tile * p.mblk + mb;
     const int per_img = p.tiles_x * p.tiles_y;
@@ -46,6 +46,9 @@ __device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
   return (s - c * 9) * p.cpt + c;
 }
 
+constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpEpi0 = 8;
+constexpr int kHaloThreads = 128;
+
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
 template <int EPI>
@@ -54,6 +57,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8];
   __shared__ __align__(16) float s_bias[kMaxCout];
   __shared__ uint32_t tmem_slot;
+  __shared__ int s_rowbase[2][40];
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
@@ -71,15 +75,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   auto stg_full = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 4 + a); };
   auto stg_empty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 6 + a); };
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && lane == 0 && p.mode != CONV_MODE_HALO) {
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
-  if (warp == 3 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
-  if (warp == 1 && lane == 0) {
+  if (warp == kWarpStore && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
-      mbar_init(a_full(s), 1);
+      mbar_init(a_full(s), p.mode == CONV_MODE_HALO ? kHaloThreads : 1);
       mbar_init(a_empty(s), 1);
     }
     for (int s = 0; s < p.nb; ++s) {
@@ -94,7 +98,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == kWarpMma) {
     tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
     tmem_relinquish();
   }
@@ -107,24 +111,70 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
   const int total_tiles = p.m_tiles * p.n_tiles_n;
 
-  if (warp == 0) {
+  if (warp < 4) {
     // =========================== A producer ===========================
-    if (lane == 0) {
+    if (p.mode == CONV_MODE_HALO) {
+      // 128 threads gather the halo patch with 16-byte cp.async (zero fill outside the image / past c_in):
+      // a multi-line TMA box costs ~0.2-0.4 us per line (measured), cp.async has no such per-line cost and
+      // lets the patch rows come from the tall (image-stacked) coordinate system.
+      griddep_wait();
+      const int t = threadIdx.x;
+      const uint32_t j = t & 7;  // 16-byte chunk inside the 128-byte pixel row
+      const int rows = p.pw * p.ph;
+      const int hp1 = p.a_h + 1;
+      uint32_t ga = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int m_tile = tile / p.n_tiles_n;
+        const MBlock t0 = mblock_coords(p, m_tile, 0);
+        // per patch row: element offset of pixel (n, y, 0) in the source buffer, or -1 for a zero row
+        int* rb = s_rowbase[it & 1];
+        if (t < p.ph) {
+          const int R = t0.y0 - 1 + t;
+          int off = -1;
+          if (R >= 0) {
+            const int n = R / hp1, y = R - n * hp1 - 1;
+            if (y >= 0 && n < p.a_n) off = (n * p.a_h + y) * p.a_w * p.a_ct;
+          }
+          rb[t] = off;
+        }
+        named_bar_sync(1, kHaloThreads);
+        for (int c = 0; c < p.cpt; ++c, ++ga) {
+          const uint32_t slot = ga % p.na;
+          mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
+          const uint32_t dst0 = a_base + slot * p.a_slot_bytes;
+          const int cc = c * 64 + (int)j * 8;
+          const bool cvalid = cc < p.a_cin;
+          const __half* cbase = p.a_src + cc;
+          for (int r = t >> 3; r < rows; r += kHaloThreads / 8) {
+            const int py = (r * p.pw_inv) >> 16;
+            const int px = r - py * p.pw;
+            const int gx = t0.x0 - 1 + px;
+            const int off = rb[py];
+            const bool ok = cvalid && off >= 0 && gx >= 0 && gx < p.a_w;
+            const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
+            const uint32_t dst = dst0 + (uint32_t)r * 128u + ((j ^ ((uint32_t)r & 7u)) << 4);
+            cp_async_16_zfill(dst, src, ok ? 16u : 0u);
+          }
+          cp_async_commit();
+          // this thread's part of the patch has landed -> make it visible to the tensor core (async proxy)
+          cp_async_wait_all();
+          fence_proxy_async_smem();
+          mbar_arrive(a_full(slot));
+        }
+      }
+    } else if (warp == 0 && lane == 0) {
       griddep_wait();  // activations are written by the previous kernel
-      const int n_groups = p.n_steps / p.a_group;
       uint32_t ga = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int m_tile = tile / p.n_tiles_n;
-        for (int grp = 0; grp < n_groups; ++grp, ++ga) {
+        for (int grp = 0; grp < p.n_steps; ++grp, ++ga) {
           const uint32_t slot = ga % p.na;
           mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
           mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
           const uint32_t dst = a_base + slot * p.a_slot_bytes;
           if (p.mode == CONV_MODE_FLAT) {
             tma_load_2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
-          } else if (p.mode == CONV_MODE_HALO) {
-            const MBlock t = mblock_coords(p, m_tile, 0);
-            tma_load_4d(dst, &p.tmA, a_full(slot), grp * 64, t.x0 - 1, t.y0 - 1, t.n);
           } else {
             const int tap = grp / p.cpt;
             const int c0 = (grp - tap * p.cpt) * 64;
@@ -145,7 +195,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kWarpB) {
     // =========================== weight producer ===========================
     if (lane == 0) {
       if (p.b_res) {
@@ -167,7 +217,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         }
       }
     }
-  } else if (warp == 2) {
+  } else if (warp == kWarpMma) {
     // =========================== MMA issuer (one thread) ===========================
     if (lane == 0) {
       const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
@@ -201,7 +251,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             uint32_t sa;
             if (p.mode == CONV_MODE_HALO) {
               const int kh = sg / 3, kw = sg - kh * 3;
-              const int jx = p.mx == 2 ? mb : 0, jy = p.my == 2 ? mb : 0;
+              const int jx = mb % p.mx, jy = mb / p.mx;
               sa = a_slot_addr + (uint32_t)(((jy * 16 + kh) * p.pw) + jx * 8 + kw) * 128u;
             } else {
               sa = a_slot_addr + mb * (kTileM * 128);
@@ -224,7 +274,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         umma_commit(tfull(as));  // accumulators ready for the epilogue
       }
     }
-  } else if (warp == 3) {
+  } else if (warp == kWarpStore) {
     // =========================== TMA store issuer ===========================
     if (EPI == EPI_STORE && lane == 0) {
       uint32_t k = 0;
@@ -240,6 +290,37 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             if (p.mode == CONV_MODE_FLAT) {
               if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
               else tma_store_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
+            } else if (p.mode == CONV_MODE_HALO) {
+              // the 16 tall rows of the block touch one or two images: one clipped box per image (rows
+              // outside [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
+              const int hp1 = p.a_h + 1;
+              const int n_first = t.y0 / hp1;
+              int n_last = (t.y0 + 15) / hp1;
+              if (n_last > p.a_n - 1) n_last = p.a_n - 1;
+              for (int n = n_first; n <= n_last; ++n) {
+                const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0
+                if (ys >= 0) {
+                  // rows past H (the zero row, the next image) are clipped by TMA
+                  if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, n0 + gq * 64, t.x0, ys, n);
+                  else tma_store_4d(&p.tmOut, src, n0 + gq * 64, t.x0, ys, n);
+                } else {
+                  // a TMA store may not start at a negative coordinate (illegal instruction, probe T6):
+                  // write staging rows [-ys, 16) to image rows [0, 16 + ys) as boxes of 8 / 4 / 2 / 1 rows
+                  int s0 = -ys, y = 0;
+                  int len = 16 - s0;
+                  if (len > p.a_h) len = p.a_h;
+                  for (int hb = 0; hb < 4; ++hb) {
+                    const int h = 8 >> hb;
+                    if (len & h) {
+                      const uint32_t ssrc = src + (uint32_t)s0 * 1024u;
+                      if (p.has_res) tma_reduce_add_4d(&p.tmOutR[hb], ssrc, n0 + gq * 64, t.x0, y, n);
+                      else tma_store_4d(&p.tmOutR[hb], ssrc, n0 + gq * 64, t.x0, y, n);
+                      s0 += h;
+                      y += h;
+                    }
+                  }
+                }
+              }
             } else {
               if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
               else tma_store_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
@@ -257,9 +338,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
       tma_store_wait0();
     }
-  } else {
-    // =========================== epilogue warps 4..11 ===========================
-    const uint32_t e = warp - 4;
+  } else if (warp >= kWarpEpi0) {
+    // =========================== epilogue warps 8..15 ===========================
+    const uint32_t e = warp - kWarpEpi0;
     const uint32_t q = e & 3;            // TMEM lane quarter this warp may access (warp % 4)
     const uint32_t half = e >> 2;        // which of the two interleaved sets of 16-column chunks
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
@@ -408,7 +489,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   // teardown: everyone done with TMEM before the allocating warp frees it
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == kWarpMma) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }

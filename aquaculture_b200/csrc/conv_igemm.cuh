@@ -18,11 +18,14 @@
 //           any 128-byte-multiple offset is legal -- measured, profiles/r1_hw_probe_v1.txt T1).
 //     TAP   3x3/s2 convs and small maps: one shifted box per (tap, chunk); stride 2 uses a parity view
 //           (c, W/2, y-parity, H/2, N) per x-parity so the strided gather is still a dense box.
-// * warp roles (384 threads): warp 0 = A producer, warp 1 = weight producer, warp 2 = TMEM allocator +
-//   single-thread MMA issuer, warp 3 = TMA store issuer, warps 4..11 = epilogue (TMEM -> regs -> bias + SiLU
-//   -> fp16 -> swizzled smem staging).  Separate warps because one thread sustains only one
-//   cp.async.bulk.tensor per ~0.2-0.4 us (measured, T4): loads, weight loads and stores must not queue
-//   behind each other.
+// * warp roles (512 threads): warps 0..3 = A producer (HALO: 128 threads of 16-byte cp.async with zero fill --
+//   a multi-line TMA box costs ~0.2-0.4 us per line; FLAT/TAP: one thread issuing TMA boxes), warp 4 = weight
+//   producer (TMA), warp 5 = TMEM allocator + single-thread MMA issuer, warp 6 = TMA store issuer,
+//   warps 8..15 = epilogue (TMEM -> regs -> bias + SiLU -> fp16 -> swizzled smem staging).  Separate warps
+//   because one thread sustains only one cp.async.bulk.tensor per ~0.2-0.4 us (measured, T4): loads, weight
+//   loads and stores must not queue behind each other.
+// * HALO tiles live in a "tall" coordinate system: all images stacked with one shared zero row between them,
+//   so small maps (20x20, 40x40) fill 16-row M blocks without per-image waste; stores are clipped per image.
 // * the Bottleneck residual (dst += f(conv)) is a TMA reduce-add of the staged tile into the destination
 //   (the residual operand is the destination slice itself), so it costs no load.
 // * weights of small layers stay resident in shared memory for the whole (persistent) kernel.
@@ -32,6 +35,7 @@
 //   the previous kernel's tail.
 #pragma once
 #include <cuda.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace aq {
@@ -40,7 +44,7 @@ enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2 };
 enum { EPI_STORE = 0, EPI_DETECT = 1 };
 enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
-constexpr int kConvThreads = 384;
+constexpr int kConvThreads = 512;
 constexpr int kEpiWarps = 8;
 constexpr int kMaxA = 4;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
@@ -53,11 +57,15 @@ struct alignas(64) ConvKParams {
   CUtensorMap tmA2;   // TAP stride 2: x-parity 1
   CUtensorMap tmB;    // weight loads
   CUtensorMap tmOut;  // output stores / reduce-adds (EPI_STORE)
+  CUtensorMap tmOutR[4];  // HALO: the same with boxes of 8 / 4 / 2 / 1 rows (blocks that start on a zero row)
   const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
   int mode, stride;
   int cpt, taps, n_steps;  // 64-channel chunks per tap, taps, K steps per tile (= taps * cpt)
   int a_group;             // K steps that share one A slot (HALO: 9, else 1)
-  int mblk, mx, my, pw;    // M blocks per tile; HALO arrangement and patch width in pixels
+  int mblk, mx, my;        // M blocks per tile; HALO arrangement (mx side by side, my stacked)
+  int pw, ph, pw_inv;      // HALO patch size in pixels, ceil(65536 / pw)
+  const __half* a_src;     // HALO: source slice (first channel), geometry of the source buffer
+  int a_n, a_h, a_w, a_ct, a_cin;
   int na, nb, b_res, n_stg, acc_stages;
   int tile_n, n_tiles_n, groups;  // UMMA N, N tiles, 64-channel store groups per tile
   int m_tiles;                    // tiles along M

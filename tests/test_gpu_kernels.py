@@ -124,6 +124,13 @@ def test_conv3x3_s1_variants(ctx, mode, mblk, B, H, W, ci, co):
     run_conv_case(ctx, B, H, W, ci, co, 3, 1, res=True, mode=mode, mblk=mblk, act=2)
 
 
+def test_conv3x3_halo_four_blocks(ctx):
+    # 4 M blocks per tile (2x2 or 4x1), images stacked in the tall coordinate system, ragged sizes
+    run_conv_case(ctx, 5, 20, 20, 48, 48, 3, 1, mode=1, mblk=4, res=True)
+    run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4)
+    run_conv_case(ctx, 7, 12, 9 * 8, 64, 32, 3, 1, mode=1, mblk=4)
+
+
 @pytest.mark.parametrize("mblk", [1, 2])
 def test_conv_mblk_variants(ctx, mblk):
     run_conv_case(ctx, 3, 20, 20, 384, 384, 1, 1, mblk=mblk)     # 2 N tiles, streamed weights

@@ -330,11 +330,6 @@ static void run_t4() {
 }
 
 // ------------------------------------------------------------------------------------------------ T5
-__device__ __forceinline__ float tanh_approx(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 __global__ void silu_kernel(const float* x, float* a, float* b, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -369,6 +364,60 @@ static void run_t5() {
   cudaFree(dx); cudaFree(da); cudaFree(db);
 }
 
+// ------------------------------------------------------------------------------------------------ T6
+// TMA *store* of a box whose start coordinate is negative (rows before 0 must simply be dropped)
+__global__ void __launch_bounds__(128) tma_store_neg_kernel(const __grid_constant__ CUtensorMap tm, int y0, int use_reduce) {
+  extern __shared__ uint8_t raw[];
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  uint8_t* sm = raw + (base - smem_u32(raw));
+  // smem box [16 rows y][8 px][64 ch] fp16, value = y * 8 + x + 1, swizzled
+  for (int i = threadIdx.x; i < 128 * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    __half v[8];
+    for (int k = 0; k < 8; ++k) v[k] = __float2half((float)(r + 1));
+    *reinterpret_cast<uint4*>(sm + r * 128 + ((j ^ (r & 7)) << 4)) = *reinterpret_cast<uint4*>(v);
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (use_reduce) tma_reduce_add_4d(&tm, base, 0, 0, y0, 0);
+    else tma_store_4d(&tm, base, 0, 0, y0, 0);
+    tma_store_commit();
+    tma_store_wait0();
+  }
+}
+static void run_t6() {
+  const int W = 8, H = 20, C = 64;
+  __half* d;
+  CK(cudaMalloc(&d, (size_t)H * W * C * 2));
+  CK(cudaFuncSetAttribute(tma_store_neg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768));
+  CUtensorMap tm;
+  cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, 1};
+  cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t bx[4] = {64, 8, 16, 1}, es[4] = {1, 1, 1, 1};
+  CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { printf("T6 encode failed %d\n", (int)r); return; }
+  const int tests[][2] = {{3, 0}, {10, 0}, {-3, 0}, {-3, 1}, {-15, 0}};
+  for (auto& t : tests) {
+    CK(cudaMemset(d, 0, (size_t)H * W * C * 2));
+    tma_store_neg_kernel<<<1, 128, 32768>>>(tm, t[0], t[1]);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("T6 y0=%d reduce=%d: CUDA error %s\n", t[0], t[1], cudaGetErrorString(e)); exit(3); }
+    std::vector<__half> o((size_t)H * W * C);
+    CK(cudaMemcpy(o.data(), d, o.size() * 2, cudaMemcpyDeviceToHost));
+    int bad = 0;
+    for (int y = 0; y < H; ++y)
+      for (int x = 0; x < W; ++x) {
+        const int by = y - t[0];
+        const float want = (by >= 0 && by < 16) ? (float)(by * 8 + x + 1) : 0.f;
+        for (int c = 0; c < C; ++c) bad += __half2float(o[((size_t)y * W + x) * C + c]) != want;
+      }
+    printf("T6 store box rows [%d, %d) into H=%d (%s): %d wrong elements\n", t[0], t[0] + 16, H, t[1] ? "reduce-add" : "store", bad);
+  }
+  cudaFree(d);
+}
+
 int main(int argc, char** argv) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -379,5 +428,6 @@ int main(int argc, char** argv) {
   if (strchr(which, '3')) run_t3();
   if (strchr(which, '5')) run_t5();
   if (strchr(which, '4')) run_t4();
+  if (strchr(which, '6')) run_t6();
   return 0;
 }

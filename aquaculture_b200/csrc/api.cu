@@ -340,6 +340,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   k.b_res = best.b_res;
   k.n_stg = best.n_stg;
   k.acc_stages = best.acc_stages;
+  k.n_mma = best.mblk > 1 ? 2 : 1;
   k.a_slot_bytes = best.a_slot;
   k.a_tx_bytes = best.a_tx;
   k.b_slot_bytes = (uint32_t)round_up(k.tile_n * 128, 1024);

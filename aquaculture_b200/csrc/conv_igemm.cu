@@ -46,7 +46,7 @@ __device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
   return (s - c * 9) * p.cpt + c;
 }
 
-constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpEpi0 = 8;
+constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpMma1 = 7, kWarpEpi0 = 8;
 constexpr int kHaloThreads = 128;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
@@ -84,14 +84,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
       mbar_init(a_full(s), p.mode == CONV_MODE_HALO ? kHaloThreads : 1);
-      mbar_init(a_empty(s), 1);
+      mbar_init(a_empty(s), p.n_mma);
     }
     for (int s = 0; s < p.nb; ++s) {
       mbar_init(b_full(s), 1);
-      mbar_init(b_empty(s), 1);
+      mbar_init(b_empty(s), p.n_mma);
     }
     for (int a = 0; a < 2; ++a) {
-      mbar_init(tfull(a), 1);
+      mbar_init(tfull(a), p.n_mma);
       mbar_init(tempty(a), kEpiWarps);
       mbar_init(stg_full(a), kEpiWarps);
       mbar_init(stg_empty(a), 1);
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           mbar_arrive(a_full(slot));
         }
       }
-    } else if (warp == 0 && lane == 0) {
+    } else if (warp == 0) {
       griddep_wait();  // activations are written by the previous kernel
       uint32_t ga = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -171,8 +171,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         for (int grp = 0; grp < p.n_steps; ++grp, ++ga) {
           const uint32_t slot = ga % p.na;
           mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
-          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
           const uint32_t dst = a_base + slot * p.a_slot_bytes;
+          if (!elect_one()) continue;
+          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
           if (p.mode == CONV_MODE_FLAT) {
             tma_load_2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
           } else {
@@ -197,31 +198,52 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp == kWarpB) {
     // =========================== weight producer ===========================
-    if (lane == 0) {
-      if (p.b_res) {
-        // all K steps of the (single) N tile stay resident: load once, never released
-        for (int s = 0; s < p.n_steps; ++s) {
+    if (p.b_res) {
+      // all K steps of the (single) N tile stay resident: load once, never released
+      for (int s = 0; s < p.n_steps; ++s) {
+        if (elect_one()) {
           mbar_arrive_expect_tx(b_full(s), p.b_tx_bytes);
           tma_load_2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), weight_chunk(p, s) * 64, 0);
         }
-      } else {
-        uint32_t g = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-          const int n0 = (tile % p.n_tiles_n) * p.tile_n;
-          for (int s = 0; s < p.n_steps; ++s, ++g) {
-            const uint32_t slot = g % p.nb;
-            mbar_wait(b_empty(slot), ((g / p.nb) & 1u) ^ 1u);
+      }
+    } else {
+      uint32_t g = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n0 = (tile % p.n_tiles_n) * p.tile_n;
+        for (int s = 0; s < p.n_steps; ++s, ++g) {
+          const uint32_t slot = g % p.nb;
+          mbar_wait(b_empty(slot), ((g / p.nb) & 1u) ^ 1u);
+          if (elect_one()) {
             mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
             tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
           }
         }
       }
     }
-  } else if (warp == kWarpMma) {
-    // =========================== MMA issuer (one thread) ===========================
-    if (lane == 0) {
+  } else if (warp == kWarpMma || warp == kWarpMma1) {
+    // =========================== MMA issuers (one thread each) ===========================
+    // Two issuing threads (one per M block of a 2-block tile): a single thread needs ~100 ns of address
+    // arithmetic + issue per tcgen05.mma in this loop, more than the MMA itself takes for small N.
+    // The whole warp runs the (warp-uniform) loop and one elected lane issues: operands then live in
+    // uniform registers; a loop entered by lane 0 only makes the compiler wrap every tcgen05.mma in an
+    // elect / R2UR broadcast loop.
+    const int mi = warp == kWarpMma ? 0 : 1;
+    if (mi < p.n_mma) {
       const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
-      const uint32_t a_sbo = p.mode == CONV_MODE_HALO ? p.pw * 128u : 1024u;
+      const bool halo = p.mode == CONV_MODE_HALO;
+      // descriptor halves: lo = start>>4 | LBO(1)<<16 ; hi = SBO>>4 | version(1)<<14 | SWIZZLE_128B(2)<<29
+      const uint32_t a_hi = ((halo ? p.pw * 128u : 1024u) >> 4) | (1u << 14) | (2u << 29);
+      const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      const uint32_t lo_flags = 1u << 16;
+      // per M block handled by this thread: A offset inside the slot (16-byte units) and TMEM column offset
+      uint32_t mb_a[2], mb_d[2];
+      int n_my = 0;
+      for (int mb = mi; mb < p.mblk; mb += p.n_mma, ++n_my) {
+        const int jx = mb % p.mx, jy = mb / p.mx;
+        mb_a[n_my] = halo ? (uint32_t)(jy * 16 * p.pw + jx * 8) * 8u : (uint32_t)mb * (kTileM * 128 / 16);
+        mb_d[n_my] = mb * p.acc_pitch;
+      }
+      const uint32_t pw8 = p.pw * 8u;
       uint32_t g = 0, ga = 0;
       int it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
@@ -229,13 +251,16 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         mbar_wait(tempty(as), (((uint32_t)(it / p.acc_stages)) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * p.acc_stride;
-        uint32_t a_slot_addr = 0;
+        uint32_t a_lo = 0;
+        int sg = 0;
+        uint32_t tap_off = 0, kw = 0;  // HALO: (kh * pw + kw) * 8 of the current tap
         for (int s = 0; s < p.n_steps; ++s) {
-          const int sg = s % p.a_group;
           if (sg == 0) {
             const uint32_t slot = ga % p.na;
             mbar_wait(a_full(slot), (ga / p.na) & 1u);
-            a_slot_addr = a_base + slot * p.a_slot_bytes;
+            a_lo = (((a_base + slot * p.a_slot_bytes) & 0x3FFFFu) >> 4) | lo_flags;
+            tap_off = 0;
+            kw = 0;
           }
           uint32_t bslot;
           if (p.b_res) {
@@ -246,37 +271,46 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             mbar_wait(b_full(bslot), (g / p.nb) & 1u);
           }
           tc_fence_after();
-          const uint32_t sb = b_base + bslot * p.b_slot_bytes;
-          for (int mb = 0; mb < p.mblk; ++mb) {
-            uint32_t sa;
-            if (p.mode == CONV_MODE_HALO) {
-              const int kh = sg / 3, kw = sg - kh * 3;
-              const int jx = mb % p.mx, jy = mb / p.mx;
-              sa = a_slot_addr + (uint32_t)(((jy * 16 + kh) * p.pw) + jx * 8 + kw) * 128u;
-            } else {
-              sa = a_slot_addr + mb * (kTileM * 128);
-            }
-            const uint32_t d = d_tmem + mb * p.acc_pitch;
+          const uint32_t b_lo = (((b_base + bslot * p.b_slot_bytes) & 0x3FFFFu) >> 4) | lo_flags;
+          const uint32_t acc = s > 0 ? 1u : 0u;
+          const bool last_of_group = sg + 1 == p.a_group;
+          if (elect_one()) {
 #pragma unroll
-            for (uint32_t kk = 0; kk < 128; kk += 32)  // UMMA K = 16 fp16 = 32 bytes
-              umma_f16(d, make_sw128_desc(sa + kk, a_sbo), make_sw128_desc(sb + kk, 1024), idesc,
-                       (s > 0 || kk > 0) ? 1u : 0u);
+            for (int q = 0; q < 2; ++q) {
+              if (q < n_my) {
+                const uint32_t al = a_lo + tap_off + mb_a[q];
+                const uint32_t d = d_tmem + mb_d[q];
+                umma_f16_split(d, al, a_hi, b_lo, b_hi, idesc, acc);  // UMMA K = 16 fp16 = 32 bytes = 2 units
+                umma_f16_split(d, al + 2, a_hi, b_lo + 2, b_hi, idesc, 1u);
+                umma_f16_split(d, al + 4, a_hi, b_lo + 4, b_hi, idesc, 1u);
+                umma_f16_split(d, al + 6, a_hi, b_lo + 6, b_hi, idesc, 1u);
+              }
+            }
+            if (!p.b_res) umma_commit(b_empty(bslot));  // weight slot reusable once these MMAs retire
+            if (last_of_group) umma_commit(a_empty(ga % p.na));
+            if (s + 1 == p.n_steps) umma_commit(tfull(as));  // accumulators ready for the epilogue
           }
-          if (!p.b_res) {
-            umma_commit(b_empty(bslot));  // weight slot reusable once these MMAs retire
-            ++g;
+          __syncwarp();
+          if (!p.b_res) ++g;
+          if (halo) {  // next tap of the 3x3 window
+            if (++kw == 3) {
+              kw = 0;
+              tap_off += pw8 - 16u;
+            } else {
+              tap_off += 8u;
+            }
           }
-          if (sg == p.a_group - 1) {
-            umma_commit(a_empty(ga % p.na));
+          if (++sg == p.a_group) {
+            sg = 0;
             ++ga;
           }
         }
-        umma_commit(tfull(as));  // accumulators ready for the epilogue
       }
     }
   } else if (warp == kWarpStore) {
     // =========================== TMA store issuer ===========================
-    if (EPI == EPI_STORE && lane == 0) {
+    if (EPI == EPI_STORE) {
+      // warp-uniform loop; lane 0 issues (bulk-group bookkeeping is per thread)
       uint32_t k = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int m_tile = tile / p.n_tiles_n;
@@ -285,6 +319,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const uint32_t sbuf = k % p.n_stg;
           mbar_wait(stg_full(sbuf), (k / p.n_stg) & 1u);
           const MBlock t = mblock_coords(p, m_tile, mb);
+          if (lane != 0) continue;
           for (int gq = 0; gq < p.groups; ++gq) {
             const uint32_t src = stg_base + sbuf * p.stg_bytes + gq * (kTileM * 128);
             if (p.mode == CONV_MODE_FLAT) {
@@ -336,7 +371,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
         }
       }
-      tma_store_wait0();
+      if (lane == 0) tma_store_wait0();
     }
   } else if (warp >= kWarpEpi0) {
     // =========================== epilogue warps 8..15 ===========================

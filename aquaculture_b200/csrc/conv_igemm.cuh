@@ -67,6 +67,7 @@ struct alignas(64) ConvKParams {
   const __half* a_src;     // HALO: source slice (first channel), geometry of the source buffer
   int a_n, a_h, a_w, a_ct, a_cin;
   int na, nb, b_res, n_stg, acc_stages;
+  int n_mma;               // MMA-issuing threads (2 when the tile has more than one M block)
   int tile_n, n_tiles_n, groups;  // UMMA N, N tiles, 64-channel store groups per tile
   int m_tiles;                    // tiles along M
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th

@@ -117,13 +117,30 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       // 128 threads gather the halo patch with 16-byte cp.async (zero fill outside the image / past c_in):
       // a multi-line TMA box costs ~0.2-0.4 us per line (measured), cp.async has no such per-line cost and
       // lets the patch rows come from the tall (image-stacked) coordinate system.
-      griddep_wait();
       const int t = threadIdx.x;
-      const uint32_t j = t & 7;  // 16-byte chunk inside the 128-byte pixel row
       const int rows = p.pw * p.ph;
       const int hp1 = p.a_h + 1;
+      // 16-byte chunks of a 128-byte row that ever carry data.  With a single K chunk (c_in <= 64) the rest
+      // of every row is zeroed once and stays zero; a power-of-two count also gets a compact thread mapping
+      // (the 16-channel stem would otherwise spend 3/4 of its copies on zero fill).
+      const int jn = p.cpt == 1 ? (p.a_cin + 7) >> 3 : 8;
+      const bool compact = jn < 8 && (jn & (jn - 1)) == 0;
+      const int jshift = jn == 1 ? 0 : (jn == 2 ? 1 : 2);
+      if (jn < 8) {
+        const int nz = 8 - jn;
+        for (int idx = t; idx < p.na * rows * nz; idx += kHaloThreads) {
+          const int rr = idx / nz;  // row over all slots
+          const uint32_t jz = jn + (idx - rr * nz);
+          const int slot = rr / rows, r = rr - slot * rows;
+          const uint32_t dst = a_base + slot * p.a_slot_bytes + (uint32_t)r * 128u + ((jz ^ ((uint32_t)r & 7u)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u) : "memory");
+        }
+      }
+      griddep_wait();  // activations are written by the previous kernel
+      const int la = p.na >= 3 ? 1 : 0;  // patches kept in flight behind the one being issued
       uint32_t ga = 0;
       int it = 0;
+      int pend_slot = -1;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const int m_tile = tile / p.n_tiles_n;
         const MBlock t0 = mblock_coords(p, m_tile, 0);
@@ -143,25 +160,56 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const uint32_t slot = ga % p.na;
           mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
           const uint32_t dst0 = a_base + slot * p.a_slot_bytes;
-          const int cc = c * 64 + (int)j * 8;
-          const bool cvalid = cc < p.a_cin;
-          const __half* cbase = p.a_src + cc;
-          for (int r = t >> 3; r < rows; r += kHaloThreads / 8) {
-            const int py = (r * p.pw_inv) >> 16;
-            const int px = r - py * p.pw;
-            const int gx = t0.x0 - 1 + px;
-            const int off = rb[py];
-            const bool ok = cvalid && off >= 0 && gx >= 0 && gx < p.a_w;
-            const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
-            const uint32_t dst = dst0 + (uint32_t)r * 128u + ((j ^ ((uint32_t)r & 7u)) << 4);
-            cp_async_16_zfill(dst, src, ok ? 16u : 0u);
+          const int xl = t0.x0 - 1;
+          if (compact) {
+            const uint32_t j = (uint32_t)t & (uint32_t)(jn - 1);
+            const __half* cbase = p.a_src + c * 64 + (int)j * 8;
+            for (int r = t >> jshift; r < rows; r += kHaloThreads >> jshift) {
+              const int py = (r * p.pw_inv) >> 16;
+              const int gx = xl + r - py * p.pw;
+              const int off = rb[py];
+              const bool ok = off >= 0 && gx >= 0 && gx < p.a_w;
+              const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
+              cp_async_16_zfill(dst0 + (uint32_t)r * 128u + ((j ^ ((uint32_t)r & 7u)) << 4), src, ok ? 16u : 0u);
+            }
+          } else {
+            const uint32_t j = (uint32_t)t & 7u;
+            const int cc = c * 64 + (int)j * 8;
+            if ((int)j < jn) {
+              const bool cvalid = cc < p.a_cin;
+              const __half* cbase = p.a_src + cc;
+              const uint32_t dsw = dst0 + ((j ^ ((uint32_t)(t >> 3) & 7u)) << 4);  // (r & 7) is fixed per thread
+              for (int r = t >> 3; r < rows; r += kHaloThreads / 8) {
+                const int py = (r * p.pw_inv) >> 16;
+                const int gx = xl + r - py * p.pw;
+                const int off = rb[py];
+                const bool ok = cvalid && off >= 0 && gx >= 0 && gx < p.a_w;
+                const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
+                cp_async_16_zfill(dsw + (uint32_t)r * 128u, src, ok ? 16u : 0u);
+              }
+            }
           }
           cp_async_commit();
-          // this thread's part of the patch has landed -> make it visible to the tensor core (async proxy)
-          cp_async_wait_all();
-          fence_proxy_async_smem();
-          mbar_arrive(a_full(slot));
+          // signal the patch issued `la` iterations ago: this thread's part has landed -> make it visible
+          // to the tensor core (async proxy) and arrive
+          if (la == 0) {
+            cp_async_wait_all();
+            fence_proxy_async_smem();
+            mbar_arrive(a_full(slot));
+          } else {
+            if (pend_slot >= 0) {
+              cp_async_wait_1();
+              fence_proxy_async_smem();
+              mbar_arrive(a_full(pend_slot));
+            }
+            pend_slot = (int)slot;
+          }
         }
+      }
+      if (pend_slot >= 0) {
+        cp_async_wait_all();
+        fence_proxy_async_smem();
+        mbar_arrive(a_full(pend_slot));
       }
     } else if (warp == 0) {
       griddep_wait();  // activations are written by the previous kernel

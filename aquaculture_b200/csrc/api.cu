@@ -266,6 +266,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   if (stride == 2 && ((sb.h | sb.w) & 1)) return fail(c, AQ_ERR_UNSUPPORTED, "stride-2 conv on odd map");
   k.stride = stride;
   k.taps = ksize * ksize;
+  k.c_in = c_in;
   k.cpt = (c_in + 63) / 64;
   k.n_steps = k.taps * k.cpt;
   if (det) {
@@ -849,6 +850,32 @@ int aq_profile_ops(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   return rc ? rc : n;
+}
+
+int aq_trace_op(aq_ctx* c, int i, long long* out, size_t cap_vals) {
+  if (!c || !out) return AQ_ERR_ARG;
+  if (!c->planned) return fail(c, AQ_ERR_STATE, "trace before plan_end");
+  if (i < 0 || i >= (int)c->ops.size()) return fail(c, AQ_ERR_ARG, "trace: op %d out of range", i);
+  Op& op = c->ops[i];
+  if (op.kind != OP_CONV && op.kind != OP_DETECT) return fail(c, AQ_ERR_ARG, "trace: op %d is not a conv", i);
+  cudaSetDevice(c->device);
+  const int total = op.kp.m_tiles * op.kp.n_tiles_n;
+  const int grid = total < c->num_sms ? total : c->num_sms;
+  const size_t vals = (size_t)grid * kTraceRoles * kTraceTiles * kTraceVals;
+  if (cap_vals < vals) return fail(c, AQ_ERR_ARG, "trace: need room for %zu values", vals);
+  const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
+  unsigned long long* dev = nullptr;
+  CU_CHECK(c, cudaMalloc(&dev, vals * 8));
+  CU_CHECK(c, cudaMemsetAsync(dev, 0, vals * 8, c->stream));
+  ConvKParams kp = op.kp;
+  cudaError_t e = launch_conv(kp, epi, c->num_sms, 0, c->stream);  // warm-up, untraced
+  kp.trace = dev;
+  if (e == cudaSuccess) e = launch_conv(kp, epi, c->num_sms, 0, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, dev, vals * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(dev);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "trace: %s", cudaGetErrorString(e));
+  return grid;
 }
 
 int aq_debug_plan_conv(int batch, int h, int w, int c_in, int c_out, int k, int stride, int num_sms, int mblk, int mode,

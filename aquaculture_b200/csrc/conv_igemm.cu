@@ -46,18 +46,195 @@ __device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
   return (s - c * 9) * p.cpt + c;
 }
 
+// Ring position advanced with compare/reset: `x % n` and `x / n` by a runtime n cost a ~100-clk dependent
+// instruction chain each, which made every role's inner loop scalar-latency bound (measured, trace_s7b).
+__device__ __forceinline__ void split_tile(const ConvKParams& p, int tile, int& m_tile, int& n_idx) {
+  if (p.n_tiles_n == 1) {
+    m_tile = tile;
+    n_idx = 0;
+  } else {
+    m_tile = tile / p.n_tiles_n;
+    n_idx = tile - m_tile * p.n_tiles_n;
+  }
+}
+
+struct Ring {
+  uint32_t slot = 0, phase = 0;
+  __device__ __forceinline__ void advance(uint32_t n) {
+    if (++slot == n) {
+      slot = 0;
+      phase ^= 1u;
+    }
+  }
+};
+
 constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpMma1 = 7, kWarpEpi0 = 8;
 constexpr int kHaloThreads = 128;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
-template <int EPI>
+// Per-role timeline (TRACE builds only): role r of CTA b writes kTraceVals clock64() values per tile at
+// trace[((b * kTraceRoles + r) * kTraceTiles + it) * kTraceVals]; see tools/trace_op.py.
+#define TR_NOW() (TRACE ? clock64() : 0ll)
+#define TR_WAIT(acc, ...)                  \
+  do {                                     \
+    if (TRACE) {                           \
+      const long long t_ = clock64();      \
+      __VA_ARGS__;                         \
+      acc += clock64() - t_;               \
+    } else {                               \
+      __VA_ARGS__;                         \
+    }                                      \
+  } while (0)
+
+template <bool TRACE>
+__device__ __forceinline__ void trace_put(const ConvKParams& p, int role, int it, long long v0, long long v1,
+                                          long long v2, long long v3) {
+  if (TRACE) {
+    if (it < kTraceTiles) {
+      long long* d = reinterpret_cast<long long*>(p.trace) +
+                     (((size_t)blockIdx.x * kTraceRoles + role) * kTraceTiles + it) * kTraceVals;
+      d[0] = v0; d[1] = v1; d[2] = v2; d[3] = v3;
+    }
+  }
+}
+
+
+// Barrier addresses inside the static `bars` array (see the kernel for the layout).
+struct MmaCtx {
+  uint32_t bar0, a_base, b_base, tmem_base;
+  int mi, total_tiles;
+};
+
+// MMA issuer role, specialised at compile time so that the per-K-step path is a handful of instructions:
+// the generic runtime-parameter loop needed ~130 dependent SASS instructions (~640 clk) per step, several
+// times the 4 x 46..128 clk the tensor core needs (profiles/r1_trace_*.txt, r1_hw_probe T7).
+//   HALO : the nine taps of a 3x3/s1 conv are shifted views of one patch slot (else: one A slot per step)
+//   BRES : every weight tile is resident in shared memory (loaded once), no ring
+//   NMY  : M blocks issued by this thread (block indices mi, mi + n_mma)
+template <bool HALO, bool BRES, int NMY, bool TRACE>
+__device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc) {
+  const uint32_t bar0 = mc.bar0;
+  auto a_full = [&](uint32_t s) { return bar0 + 8u * s; };
+  auto a_empty = [&](uint32_t s) { return bar0 + 8u * (kMaxA + s); };
+  auto b_full = [&](uint32_t s) { return bar0 + 8u * (2 * kMaxA + s); };
+  auto b_empty = [&](uint32_t s) { return bar0 + 8u * (2 * kMaxA + kMaxB + s); };
+  auto tfull = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
+  auto tempty = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
+  // loop invariants in registers
+  const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
+  const uint32_t pw8 = p.pw * 8u;
+  // descriptor halves: lo = start>>4 | LBO(1)<<16 ; hi = SBO>>4 | version(1)<<14 | SWIZZLE_128B(2)<<29
+  const uint32_t a_hi = ((HALO ? p.pw * 128u : 1024u) >> 4) | (1u << 14) | (2u << 29);
+  const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+  const uint32_t lo_flags = 1u << 16;
+  const uint32_t a_lo0 = ((mc.a_base & 0x3FFFFu) >> 4) | lo_flags, a_slot16 = p.a_slot_bytes >> 4;
+  const uint32_t b_lo0 = ((mc.b_base & 0x3FFFFu) >> 4) | lo_flags, b_slot16 = p.b_slot_bytes >> 4;
+  const uint32_t na = p.na, nb = p.nb, acc_stages = p.acc_stages, acc_stride = p.acc_stride;
+  const int cpt = p.cpt, n_steps = p.n_steps;
+  // K = 16 MMAs that carry data in the last 64-channel chunk (the rest of the chunk is zero padding)
+  const int c_in = HALO ? p.a_cin : p.c_in;
+  const int kk_last = (c_in - 64 * (cpt - 1) + 15) >> 4;
+  uint32_t mb_a[NMY], mb_d[NMY];
+#pragma unroll
+  for (int q = 0; q < NMY; ++q) {
+    const int mb = mc.mi + q * p.n_mma;
+    const int jx = mb % p.mx, jy = mb / p.mx;
+    mb_a[q] = HALO ? (uint32_t)(jy * 16 * p.pw + jx * 8) * 8u : (uint32_t)mb * (kTileM * 128 / 16);
+    mb_d[q] = mb * p.acc_pitch;
+  }
+  const bool leader = elect_one();
+  Ring ra, rb, rt;
+  int it = 0;
+  for (int tile = blockIdx.x; tile < mc.total_tiles; tile += gridDim.x, ++it, rt.advance(acc_stages)) {
+    const uint32_t as = rt.slot;
+    const long long tr0 = TR_NOW();
+    long long trwa = 0, trwb = 0;
+    mbar_wait(tempty(as), rt.phase ^ 1u);
+    const long long tr1 = TR_NOW();
+    tc_fence_after();
+    const uint32_t d_tmem = mc.tmem_base + as * acc_stride;
+    uint32_t acc = 0;
+    // one K step: `kk` MMAs of K = 16 per owned M block on A view `al`, weight slot `bs`
+    auto issue = [&](uint32_t al, uint32_t bl, int kk) {
+#pragma unroll
+      for (int q = 0; q < NMY; ++q) {
+        const uint32_t d = d_tmem + mb_d[q];
+        const uint32_t aq = al + mb_a[q];
+        umma_f16_split(d, aq, a_hi, bl, b_hi, idesc, acc);
+        if (kk > 1) umma_f16_split(d, aq + 2, a_hi, bl + 2, b_hi, idesc, 1u);
+        if (kk > 2) umma_f16_split(d, aq + 4, a_hi, bl + 4, b_hi, idesc, 1u);
+        if (kk > 3) umma_f16_split(d, aq + 6, a_hi, bl + 6, b_hi, idesc, 1u);
+      }
+    };
+    if (HALO) {
+      int s = 0;
+      for (int c = 0; c < cpt; ++c) {
+        TR_WAIT(trwa, mbar_wait(a_full(ra.slot), ra.phase));
+        const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
+        const int kk = c == cpt - 1 ? kk_last : 4;
+        uint32_t tap_off = 0;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap, ++s) {
+          const uint32_t bs = BRES ? (uint32_t)s : rb.slot;
+          if (BRES) {
+            if (it == 0) TR_WAIT(trwb, mbar_wait(b_full(bs), 0));
+          } else {
+            TR_WAIT(trwb, mbar_wait(b_full(bs), rb.phase));
+          }
+          tc_fence_after();
+          if (leader) {
+            issue(a_lo + tap_off, b_lo0 + bs * b_slot16, kk);
+            if (!BRES) umma_commit(b_empty(bs));  // weight slot reusable once these MMAs retire
+            if (tap == 8) {
+              umma_commit(a_empty(ra.slot));
+              if (c == cpt - 1) umma_commit(tfull(as));  // accumulators ready for the epilogue
+            }
+          }
+          __syncwarp();
+          acc = 1u;
+          if (!BRES) rb.advance(nb);
+          tap_off += (tap % 3 == 2) ? pw8 - 16u : 8u;
+        }
+        ra.advance(na);
+      }
+    } else {
+      int chunk = 0;
+      for (int s = 0; s < n_steps; ++s) {
+        TR_WAIT(trwa, mbar_wait(a_full(ra.slot), ra.phase));
+        const uint32_t bs = BRES ? (uint32_t)s : rb.slot;
+        if (BRES) {
+          if (it == 0) TR_WAIT(trwb, mbar_wait(b_full(bs), 0));
+        } else {
+          TR_WAIT(trwb, mbar_wait(b_full(bs), rb.phase));
+        }
+        tc_fence_after();
+        const int kk = chunk == cpt - 1 ? kk_last : 4;
+        if (leader) {
+          issue(a_lo0 + ra.slot * a_slot16, b_lo0 + bs * b_slot16, kk);
+          if (!BRES) umma_commit(b_empty(bs));
+          umma_commit(a_empty(ra.slot));
+          if (s == n_steps - 1) umma_commit(tfull(as));
+        }
+        __syncwarp();
+        acc = 1u;
+        if (!BRES) rb.advance(nb);
+        ra.advance(na);
+        if (++chunk == cpt) chunk = 0;
+      }
+    }
+    if (mc.mi == 0 && leader) trace_put<TRACE>(p, 2, it, tr0, tr1 - tr0, (trwa << 32) | trwb, TR_NOW());
+  }
+}
+
+template <int EPI, bool TRACE>
 __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8];
   __shared__ __align__(16) float s_bias[kMaxCout];
   __shared__ uint32_t tmem_slot;
   __shared__ int s_rowbase[2][40];
+  __shared__ uint8_t s_det_a[EPI == EPI_DETECT ? 256 : 1], s_det_o[EPI == EPI_DETECT ? 256 : 1];  // column -> anchor, output
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
@@ -103,6 +280,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     tmem_relinquish();
   }
   for (int i = threadIdx.x; i < p.n_tiles_n * p.tile_n; i += kConvThreads) s_bias[i] = __ldg(p.bias + i);
+  if (EPI == EPI_DETECT) {
+    for (int i = threadIdx.x; i < 256; i += kConvThreads) {
+      const int a = i / p.det_no;
+      s_det_a[i] = (uint8_t)a;
+      s_det_o[i] = (uint8_t)(i - a * p.det_no);
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -138,11 +322,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
       griddep_wait();  // activations are written by the previous kernel
       const int la = p.na >= 3 ? 1 : 0;  // patches kept in flight behind the one being issued
-      uint32_t ga = 0;
+      Ring ra;
       int it = 0;
       int pend_slot = -1;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int m_tile = tile / p.n_tiles_n;
+        int m_tile, n_idx;
+        split_tile(p, tile, m_tile, n_idx);
         const MBlock t0 = mblock_coords(p, m_tile, 0);
         // per patch row: element offset of pixel (n, y, 0) in the source buffer, or -1 for a zero row
         int* rb = s_rowbase[it & 1];
@@ -156,9 +341,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           rb[t] = off;
         }
         named_bar_sync(1, kHaloThreads);
-        for (int c = 0; c < p.cpt; ++c, ++ga) {
-          const uint32_t slot = ga % p.na;
-          mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
+        const long long tr0 = TR_NOW();
+        long long trw = 0, trd = 0;
+        for (int c = 0; c < p.cpt; ++c, ra.advance(p.na)) {
+          const uint32_t slot = ra.slot;
+          TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
           const uint32_t dst0 = a_base + slot * p.a_slot_bytes;
           const int xl = t0.x0 - 1;
           if (compact) {
@@ -198,13 +385,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             mbar_arrive(a_full(slot));
           } else {
             if (pend_slot >= 0) {
-              cp_async_wait_1();
+              TR_WAIT(trd, cp_async_wait_1());
               fence_proxy_async_smem();
               mbar_arrive(a_full(pend_slot));
             }
             pend_slot = (int)slot;
           }
         }
+        if (t == 0) trace_put<TRACE>(p, 0, it, tr0, trw, trd, TR_NOW());
       }
       if (pend_slot >= 0) {
         cp_async_wait_all();
@@ -213,23 +401,36 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
     } else if (warp == 0) {
       griddep_wait();  // activations are written by the previous kernel
-      uint32_t ga = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.n_tiles_n;
-        for (int grp = 0; grp < p.n_steps; ++grp, ++ga) {
-          const uint32_t slot = ga % p.na;
-          mbar_wait(a_empty(slot), ((ga / p.na) & 1u) ^ 1u);
+      Ring ra;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        int m_tile, n_idx;
+        split_tile(p, tile, m_tile, n_idx);
+        const long long tr0 = TR_NOW();
+        long long trw = 0;
+        MBlock tb0 = {}, tb1 = {};
+        if (p.mode == CONV_MODE_TAP) {
+          tb0 = mblock_coords(p, m_tile, 0);
+          tb1 = mblock_coords(p, m_tile, p.mblk > 1 ? 1 : 0);
+        }
+        int tap = 0, chunk = 0;  // TAP: grp = tap * cpt + chunk
+        for (int grp = 0; grp < p.n_steps; ++grp, ra.advance(p.na)) {
+          const uint32_t slot = ra.slot;
+          TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
           const uint32_t dst = a_base + slot * p.a_slot_bytes;
+          const int c0 = chunk * 64;
+          const int kh = tap / 3, kw = tap - kh * 3;
+          if (++chunk == p.cpt) {
+            chunk = 0;
+            ++tap;
+          }
           if (!elect_one()) continue;
           mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
           if (p.mode == CONV_MODE_FLAT) {
             tma_load_2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
           } else {
-            const int tap = grp / p.cpt;
-            const int c0 = (grp - tap * p.cpt) * 64;
-            const int kh = tap / 3, kw = tap - kh * 3;
             for (int mb = 0; mb < p.mblk; ++mb) {
-              const MBlock t = mblock_coords(p, m_tile, mb);
+              const MBlock t = mb ? tb1 : tb0;
               const uint32_t d = dst + mb * (kTileM * 128);
               if (p.stride == 1) {
                 tma_load_4d(d, &p.tmA, a_full(slot), c0, t.x0 + kw - 1, t.y0 + kh - 1, t.n);
@@ -242,6 +443,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             }
           }
         }
+        if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
       }
     }
   } else if (warp == kWarpB) {
@@ -255,104 +457,38 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         }
       }
     } else {
-      uint32_t g = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n0 = (tile % p.n_tiles_n) * p.tile_n;
-        for (int s = 0; s < p.n_steps; ++s, ++g) {
-          const uint32_t slot = g % p.nb;
-          mbar_wait(b_empty(slot), ((g / p.nb) & 1u) ^ 1u);
+      Ring rb;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        int m_tile, n_idx;
+        split_tile(p, tile, m_tile, n_idx);
+        const int n0 = n_idx * p.tile_n;
+        const long long tr0 = TR_NOW();
+        long long trw = 0;
+        for (int s = 0; s < p.n_steps; ++s, rb.advance(p.nb)) {
+          const uint32_t slot = rb.slot;
+          TR_WAIT(trw, mbar_wait(b_empty(slot), rb.phase ^ 1u));
           if (elect_one()) {
             mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
             tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
           }
         }
+        if (lane == 0) trace_put<TRACE>(p, 1, it, tr0, trw, 0, TR_NOW());
       }
     }
   } else if (warp == kWarpMma || warp == kWarpMma1) {
-    // =========================== MMA issuers (one thread each) ===========================
-    // Two issuing threads (one per M block of a 2-block tile): a single thread needs ~100 ns of address
-    // arithmetic + issue per tcgen05.mma in this loop, more than the MMA itself takes for small N.
-    // The whole warp runs the (warp-uniform) loop and one elected lane issues: operands then live in
-    // uniform registers; a loop entered by lane 0 only makes the compiler wrap every tcgen05.mma in an
-    // elect / R2UR broadcast loop.
+    // =========================== MMA issuers (one elected lane each) ===========================
     const int mi = warp == kWarpMma ? 0 : 1;
     if (mi < p.n_mma) {
-      const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
+      const MmaCtx mc{bar0, a_base, b_base, tmem_base, mi, total_tiles};
+      const int n_my = p.mblk > p.n_mma ? 2 : 1;  // M blocks this issuer owns: mi, mi + n_mma
       const bool halo = p.mode == CONV_MODE_HALO;
-      // descriptor halves: lo = start>>4 | LBO(1)<<16 ; hi = SBO>>4 | version(1)<<14 | SWIZZLE_128B(2)<<29
-      const uint32_t a_hi = ((halo ? p.pw * 128u : 1024u) >> 4) | (1u << 14) | (2u << 29);
-      const uint32_t b_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
-      const uint32_t lo_flags = 1u << 16;
-      // per M block handled by this thread: A offset inside the slot (16-byte units) and TMEM column offset
-      uint32_t mb_a[2], mb_d[2];
-      int n_my = 0;
-      for (int mb = mi; mb < p.mblk; mb += p.n_mma, ++n_my) {
-        const int jx = mb % p.mx, jy = mb / p.mx;
-        mb_a[n_my] = halo ? (uint32_t)(jy * 16 * p.pw + jx * 8) * 8u : (uint32_t)mb * (kTileM * 128 / 16);
-        mb_d[n_my] = mb * p.acc_pitch;
-      }
-      const uint32_t pw8 = p.pw * 8u;
-      uint32_t g = 0, ga = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int as = it % p.acc_stages;
-        mbar_wait(tempty(as), (((uint32_t)(it / p.acc_stages)) & 1u) ^ 1u);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * p.acc_stride;
-        uint32_t a_lo = 0;
-        int sg = 0;
-        uint32_t tap_off = 0, kw = 0;  // HALO: (kh * pw + kw) * 8 of the current tap
-        for (int s = 0; s < p.n_steps; ++s) {
-          if (sg == 0) {
-            const uint32_t slot = ga % p.na;
-            mbar_wait(a_full(slot), (ga / p.na) & 1u);
-            a_lo = (((a_base + slot * p.a_slot_bytes) & 0x3FFFFu) >> 4) | lo_flags;
-            tap_off = 0;
-            kw = 0;
-          }
-          uint32_t bslot;
-          if (p.b_res) {
-            bslot = s;
-            if (it == 0) mbar_wait(b_full(bslot), 0);
-          } else {
-            bslot = g % p.nb;
-            mbar_wait(b_full(bslot), (g / p.nb) & 1u);
-          }
-          tc_fence_after();
-          const uint32_t b_lo = (((b_base + bslot * p.b_slot_bytes) & 0x3FFFFu) >> 4) | lo_flags;
-          const uint32_t acc = s > 0 ? 1u : 0u;
-          const bool last_of_group = sg + 1 == p.a_group;
-          if (elect_one()) {
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-              if (q < n_my) {
-                const uint32_t al = a_lo + tap_off + mb_a[q];
-                const uint32_t d = d_tmem + mb_d[q];
-                umma_f16_split(d, al, a_hi, b_lo, b_hi, idesc, acc);  // UMMA K = 16 fp16 = 32 bytes = 2 units
-                umma_f16_split(d, al + 2, a_hi, b_lo + 2, b_hi, idesc, 1u);
-                umma_f16_split(d, al + 4, a_hi, b_lo + 4, b_hi, idesc, 1u);
-                umma_f16_split(d, al + 6, a_hi, b_lo + 6, b_hi, idesc, 1u);
-              }
-            }
-            if (!p.b_res) umma_commit(b_empty(bslot));  // weight slot reusable once these MMAs retire
-            if (last_of_group) umma_commit(a_empty(ga % p.na));
-            if (s + 1 == p.n_steps) umma_commit(tfull(as));  // accumulators ready for the epilogue
-          }
-          __syncwarp();
-          if (!p.b_res) ++g;
-          if (halo) {  // next tap of the 3x3 window
-            if (++kw == 3) {
-              kw = 0;
-              tap_off += pw8 - 16u;
-            } else {
-              tap_off += 8u;
-            }
-          }
-          if (++sg == p.a_group) {
-            sg = 0;
-            ++ga;
-          }
-        }
+      if (halo) {
+        if (p.b_res) { if (n_my == 2) mma_role<true, true, 2, TRACE>(p, mc); else mma_role<true, true, 1, TRACE>(p, mc); }
+        else         { if (n_my == 2) mma_role<true, false, 2, TRACE>(p, mc); else mma_role<true, false, 1, TRACE>(p, mc); }
+      } else {
+        if (p.b_res) mma_role<false, true, 1, TRACE>(p, mc);
+        else mma_role<false, false, 1, TRACE>(p, mc);
       }
     }
   } else if (warp == kWarpStore) {
@@ -360,12 +496,17 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     if (EPI == EPI_STORE) {
       // warp-uniform loop; lane 0 issues (bulk-group bookkeeping is per thread)
       uint32_t k = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.n_tiles_n;
-        const int n0 = (tile % p.n_tiles_n) * p.tile_n;
-        for (int mb = 0; mb < p.mblk; ++mb, ++k) {
-          const uint32_t sbuf = k % p.n_stg;
-          mbar_wait(stg_full(sbuf), (k / p.n_stg) & 1u);
+      Ring rs;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        int m_tile, n_idx;
+        split_tile(p, tile, m_tile, n_idx);
+        const int n0 = n_idx * p.tile_n;
+        const long long tr0 = TR_NOW();
+        long long trw = 0, trr = 0;
+        for (int mb = 0; mb < p.mblk; ++mb, ++k, rs.advance(p.n_stg)) {
+          const uint32_t sbuf = rs.slot;
+          TR_WAIT(trw, mbar_wait(stg_full(sbuf), rs.phase));
           const MBlock t = mblock_coords(p, m_tile, mb);
           if (lane != 0) continue;
           for (int gq = 0; gq < p.groups; ++gq) {
@@ -411,13 +552,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
           tma_store_commit();
           if (p.n_stg == 2) {
-            tma_store_wait_read1();  // the previous block's staging buffer has been read
+            TR_WAIT(trr, tma_store_wait_read1());  // the previous block's staging buffer has been read
             if (k > 0) mbar_arrive(stg_empty((k - 1) & 1u));
           } else {
-            tma_store_wait_read0();
+            TR_WAIT(trr, tma_store_wait_read0());
             mbar_arrive(stg_empty(0));
           }
         }
+        if (lane == 0) trace_put<TRACE>(p, 4, it, tr0, trw, trr, TR_NOW());
       }
       if (lane == 0) tma_store_wait0();
     }
@@ -428,25 +570,28 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     const uint32_t half = e >> 2;        // which of the two interleaved sets of 16-column chunks
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
     const int n_chunks = p.tile_n >> 4;
-    uint32_t k = 0;
+    Ring rs, rt;
     int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int m_tile = tile / p.n_tiles_n;
-      const int n0 = (tile % p.n_tiles_n) * p.tile_n;
-      const int as = it % p.acc_stages;
-      mbar_wait(tfull(as), ((uint32_t)(it / p.acc_stages)) & 1u);
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(p.acc_stages)) {
+      int m_tile, n_idx;
+      split_tile(p, tile, m_tile, n_idx);
+      const int n0 = n_idx * p.tile_n;
+      const int as = rt.slot;
+      const long long tr0 = TR_NOW();
+      long long trs = 0;
+      mbar_wait(tfull(as), rt.phase);
+      const long long tr1 = TR_NOW();
       tc_fence_after();
-      for (int mb = 0; mb < p.mblk; ++mb, ++k) {
+      for (int mb = 0; mb < p.mblk; ++mb) {
         const uint32_t t_addr = tmem_base + ((q * 32u) << 16) + as * p.acc_stride + mb * p.acc_pitch;
         if (EPI == EPI_STORE) {
-          const uint32_t sbuf = k % p.n_stg;
-          mbar_wait(stg_empty(sbuf), ((k / p.n_stg) & 1u) ^ 1u);
+          const uint32_t sbuf = rs.slot;
+          TR_WAIT(trs, mbar_wait(stg_empty(sbuf), rs.phase ^ 1u));
+          rs.advance(p.n_stg);
           const uint32_t stg = stg_base + sbuf * p.stg_bytes;
-          for (int ch = half; ch < n_chunks; ch += 2) {
+          // one 16-column chunk: bias + SiLU -> fp16 -> swizzled staging
+          auto process = [&](const uint32_t (&v)[16], int ch) {
             const int c0 = ch << 4;
-            uint32_t v[16];
-            tmem_ld16(t_addr + c0, v);
-            tmem_ld_wait();
             const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c0);
             float f[16];
             if (p.act == ACT_SILU_FAST) {
@@ -489,6 +634,27 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
                          : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
                          : "memory");
+                    };
+          // software pipeline: the TMEM load of the next chunk is in flight while this one is processed
+          {
+            uint32_t v0[16], v1[16];
+            int ch = half;
+            if (ch < n_chunks) {
+              tmem_ld16(t_addr + (ch << 4), v0);
+              while (true) {
+                tmem_ld_wait();
+                const bool more1 = ch + 2 < n_chunks;
+                if (more1) tmem_ld16(t_addr + ((ch + 2) << 4), v1);
+                process(v0, ch);
+                if (!more1) break;
+                tmem_ld_wait();
+                const bool more0 = ch + 4 < n_chunks;
+                if (more0) tmem_ld16(t_addr + ((ch + 4) << 4), v0);
+                process(v1, ch + 2);
+                if (!more0) break;
+                ch += 4;
+              }
+            }
           }
           if (mb == p.mblk - 1) {
             // every TMEM read of this tile is done -> the MMA warp may overwrite the accumulators
@@ -520,8 +686,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
               const int col = c0 + i;
-              const int a = col / p.det_no;
-              const int oi = col - a * p.det_no;
+              const int a = s_det_a[col];
+              const int oi = s_det_o[col];
               const float z = __uint_as_float(v[i]) + s_bias[col < kMaxCout ? col : 0];
               const float s = __fdividef(1.0f, 1.0f + __expf(-z));
               float out;
@@ -550,8 +716,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
                 for (int i = 0; i < 16; ++i) {
                   const int col = c0 + i;
                   if (col < ncols) {
-                    const int a = col / p.det_no;
-                    const int oi = col - a * p.det_no;
+                    const int a = s_det_a[col];
+                    const int oi = s_det_o[col];
                     const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
                     p.pred[r * p.det_no + oi] = o[i];
                   }
@@ -566,6 +732,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
         }
       }
+      if (e == 0 && lane == 0) trace_put<TRACE>(p, 3, it, tr0, tr1 - tr0, trs, TR_NOW());
     }
   }
 
@@ -585,11 +752,12 @@ size_t conv_smem_bytes(const ConvKParams& p) {
 }
 
 cudaError_t conv_kernels_init() {
-  cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kConvMaxDynSmem);
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(conv_igemm_kernel<EPI_DETECT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              kConvMaxDynSmem);
+  cudaError_t e = cudaSuccess;
+  const void* fns[4] = {(const void*)conv_igemm_kernel<EPI_STORE, false>, (const void*)conv_igemm_kernel<EPI_DETECT, false>,
+                        (const void*)conv_igemm_kernel<EPI_STORE, true>, (const void*)conv_igemm_kernel<EPI_DETECT, true>};
+  for (int i = 0; i < 4 && e == cudaSuccess; ++i)
+    e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, kConvMaxDynSmem);
+  return e;
 }
 
 cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
@@ -604,8 +772,12 @@ cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cud
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE>, p);
-  return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT>, p);
+  if (p.trace) {
+    if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE, true>, p);
+    return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT, true>, p);
+  }
+  if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE, false>, p);
+  return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT, false>, p);
 }
 
 }  // namespace aq

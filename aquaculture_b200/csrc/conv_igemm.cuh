@@ -50,6 +50,7 @@ constexpr int kMaxA = 4;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
 constexpr int kTileM = 128;
 constexpr int kMaxCout = 768;
+constexpr int kTraceRoles = 5, kTraceTiles = 48, kTraceVals = 4;  // roles: A producer, B producer, MMA0, epilogue warp 0, store
 constexpr int kConvMaxDynSmem = 232448 - 6144;  // 227 KB opt-in limit minus static smem (barriers, bias)
 
 struct alignas(64) ConvKParams {
@@ -60,6 +61,7 @@ struct alignas(64) ConvKParams {
   CUtensorMap tmOutR[4];  // HALO: the same with boxes of 8 / 4 / 2 / 1 rows (blocks that start on a zero row)
   const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
   int mode, stride;
+  int c_in;                // input channels of the conv (valid K columns per tap)
   int cpt, taps, n_steps;  // 64-channel chunks per tap, taps, K steps per tile (= taps * cpt)
   int a_group;             // K steps that share one A slot (HALO: 9, else 1)
   int mblk, mx, my;        // M blocks per tile; HALO arrangement (mx side by side, my stacked)
@@ -80,6 +82,7 @@ struct alignas(64) ConvKParams {
   int det_no, det_rows, det_level_off, det_ny, det_nx, det_m_total;
   float det_stride;
   float det_anchor[6];
+  unsigned long long* trace;  // device buffer [grid][kTraceRoles][kTraceTiles][kTraceVals] or NULL
 };
 
 size_t conv_smem_bytes(const ConvKParams& p);

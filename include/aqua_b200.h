@@ -117,6 +117,10 @@ int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
  * (kind, GEMM shape, tile configuration, algorithmic FLOPs and bytes) of op `i`. */
 int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
+/* Per-role timeline of planned conv op `i` (instrumented build of the same kernel, launched once after one
+ * warm-up): out[grid][5 roles][48 tiles][4] clock64 values (layout in conv_igemm.cuh); returns the grid size
+ * (CTAs) or a negative status; cap_vals = capacity of `out` in 64-bit values. */
+int aq_trace_op(aq_ctx* ctx, int i, long long* out, size_t cap_vals);
 /* Host-only planner probe (no device needed): the tiling the library would choose for one conv of the given
  * shape, written as the same one-line description aq_op_describe gives.  mblk / mode = 0 lets it choose. */
 int aq_debug_plan_conv(int batch, int h, int w, int c_in, int c_out, int k, int stride, int num_sms, int mblk, int mode,

@@ -418,6 +418,172 @@ static void run_t6() {
   cudaFree(d);
 }
 
+
+// ------------------------------------------------------------------------------------------------ T7
+// tcgen05.mma issue / execution rate of ONE thread: clk per K=16 MMA as a function of N, of the number of
+// accumulators the thread cycles through (dependent chains), of tcgen05.commit frequency and of a second
+// issuing thread.  Operands are zero-filled shared memory (no loads in flight).
+__global__ void __launch_bounds__(128) mma_rate_kernel(int N, int n_acc, int commit_every, int n_issuers, int iters,
+                                                       long long* out) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bars[8];
+  __shared__ uint32_t tslot;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  for (int i = threadIdx.x; i < (16384 + 32768) / 16; i += 128)
+    *reinterpret_cast<uint4*>(raw + (base - smem_u32(raw)) + i * 16) = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&tslot), 512);
+    tmem_relinquish();
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 8; ++i) mbar_init(smem_u32(&bars[i]), 1);
+    fence_barrier_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tslot;
+  if (warp < (uint32_t)n_issuers) {
+    const uint32_t idesc = make_idesc_f16(128, N);
+    const uint32_t a_hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    const uint32_t a_lo = ((base & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t b_lo = (((base + 16384) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t pitch = (N + 31) / 32 * 32;
+    int acc = 0;
+    const long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+      const uint32_t d = tmem + (warp * n_acc + acc) * pitch;
+      if (elect_one()) {
+        umma_f16_split(d, a_lo, a_hi, b_lo, a_hi, idesc, 1u);
+        umma_f16_split(d, a_lo + 2, a_hi, b_lo + 2, a_hi, idesc, 1u);
+        umma_f16_split(d, a_lo + 4, a_hi, b_lo + 4, a_hi, idesc, 1u);
+        umma_f16_split(d, a_lo + 6, a_hi, b_lo + 6, a_hi, idesc, 1u);
+        if (commit_every && (i % commit_every) == commit_every - 1) umma_commit(smem_u32(&bars[2 + warp]));
+      }
+      __syncwarp();
+      if (++acc == n_acc) acc = 0;
+    }
+    const long long t1 = clock64();
+    if (elect_one()) umma_commit(smem_u32(&bars[warp]));
+    __syncwarp();
+    mbar_wait(smem_u32(&bars[warp]), 0);
+    const long long t2 = clock64();
+    if (lane == 0 && blockIdx.x == 0) {
+      out[warp * 2] = t1 - t0;
+      out[warp * 2 + 1] = t2 - t0;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+static void run_t7() {
+  long long* d;
+  CK(cudaMalloc(&d, 64));
+  CK(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  struct V { int N, n_acc, commit_every, n_issuers; };
+  std::vector<V> vars;
+  for (int N : {48, 96, 192, 256}) {
+    vars.push_back({N, 1, 0, 1});
+    vars.push_back({N, 1, 1, 1});
+    vars.push_back({N, 1, 9, 1});
+    if (2 * ((N + 31) / 32 * 32) <= 512) {
+      vars.push_back({N, 2, 0, 1});
+      vars.push_back({N, 1, 0, 2});
+      vars.push_back({N, 1, 1, 2});
+    }
+    if (4 * ((N + 31) / 32 * 32) <= 512) vars.push_back({N, 2, 0, 2});
+  }
+  const int iters = 2000;
+  for (const V& v : vars) {
+    long long h[4] = {0, 0, 0, 0};
+    for (int rep = 0; rep < 2; ++rep) {
+      mma_rate_kernel<<<148, 128, 56 * 1024>>>(v.N, v.n_acc, v.commit_every, v.n_issuers, iters, d);
+      CK(cudaDeviceSynchronize());
+    }
+    CK(cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost));
+    printf("T7 N=%3d acc/thread=%d commit_every=%d issuers=%d : issue %.1f clk/MMA, complete %.1f clk/MMA per thread (ideal %d); "
+           "combined %.1f clk/MMA\n",
+           v.N, v.n_acc, v.commit_every, v.n_issuers, (double)h[0] / (iters * 4), (double)h[1] / (iters * 4), v.N / 2,
+           (double)h[1] / (iters * 4) / v.n_issuers);
+  }
+  cudaFree(d);
+}
+
+// ------------------------------------------------------------------------------------------------ T8
+// TMA load latency and throughput per SM vs boxes in flight: thread 0 issues `depth` boxes (128 rows x 128 B)
+// on one mbarrier, waits for all, repeats.  L2-resident source (32 MiB window).
+__global__ void __launch_bounds__(64) tma_lat_kernel(const __grid_constant__ CUtensorMap tm, int depth, int box_rows,
+                                                     int iters, long rows_total, long long* out) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long tot = 0, tissue = 0;
+    for (int it = 0; it < iters; ++it) {
+      const long long t0 = clock64();
+      mbar_arrive_expect_tx(smem_u32(&bar), depth * box_rows * 128);
+      for (int l = 0; l < depth; ++l) {
+        const long row = (((long)blockIdx.x * iters + it) * depth + l) * box_rows % rows_total;
+        tma_load_2d(base + l * box_rows * 128, &tm, smem_u32(&bar), 0, (int)row);
+      }
+      const long long t1 = clock64();
+      mbar_wait(smem_u32(&bar), it & 1);
+      tot += clock64() - t0;
+      tissue += t1 - t0;
+    }
+    if (blockIdx.x == 0) {
+      out[0] = tot / iters;
+      out[1] = tissue / iters;
+    }
+  }
+}
+
+static void run_t8() {
+  const size_t big = (size_t)1 << 30;
+  uint8_t* d;
+  long long* o;
+  CK(cudaMalloc(&d, big));
+  CK(cudaMemset(d, 1, big));
+  CK(cudaMalloc(&o, 64));
+  CK(cudaFuncSetAttribute(tma_lat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  for (int l2 = 1; l2 >= 0; --l2) {
+    for (int box_rows : {128, 256, 32}) {
+      const long rows_total = l2 ? (long)(32 << 20) / 128 : (long)(big / 128);
+      CUtensorMap tm;
+      cuuint64_t gd[2] = {64, (cuuint64_t)rows_total};
+      cuuint64_t gs[1] = {128};
+      cuuint32_t bx[2] = {64, (cuuint32_t)box_rows}, es[2] = {1, 1};
+      CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) { printf("T8 encode failed %d\n", (int)r); continue; }
+      for (int grid : {1, 148}) {
+        for (int depth : {1, 2, 4, 8}) {
+          if ((size_t)depth * box_rows * 128 > 190 * 1024) continue;
+          long long h[2];
+          for (int rep = 0; rep < 2; ++rep) {
+            tma_lat_kernel<<<grid, 64, depth * box_rows * 128 + 2048>>>(tm, depth, box_rows, l2 ? 400 : 100, rows_total - 4096, o);
+            CK(cudaDeviceSynchronize());
+          }
+          CK(cudaMemcpy(h, o, 16, cudaMemcpyDeviceToHost));
+          printf("T8 %s box %3d rows x128B, %d in flight, grid %3d: round trip %6lld clk (issue %5lld) -> %.1f B/clk/SM\n",
+                 l2 ? "L2 " : "HBM", box_rows, depth, grid, h[0], h[1], (double)depth * box_rows * 128 / h[0]);
+        }
+      }
+    }
+  }
+  cudaFree(d); cudaFree(o);
+}
+
 int main(int argc, char** argv) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -429,5 +595,7 @@ int main(int argc, char** argv) {
   if (strchr(which, '5')) run_t5();
   if (strchr(which, '4')) run_t4();
   if (strchr(which, '6')) run_t6();
+  if (strchr(which, '7')) run_t7();
+  if (strchr(which, '8')) run_t8();
   return 0;
 }

@@ -376,10 +376,16 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     uint32_t box[2] = {64, (uint32_t)(kTileM * k.mblk)};
     rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 2, dims, str, box, sw);
   } else if (k.mode == CONV_MODE_HALO) {
-    // gathered with cp.async: plain pointer + geometry
+    // patch rows are loaded as boxes of 32 / 16 / 8 / 4 / 2 / 1 image rows (per-image segments of the tall patch)
     k.a_src = sb.ptr + src_c_off;
     k.a_n = c->batch; k.a_h = sb.h; k.a_w = sb.w; k.a_ct = sb.c; k.a_cin = c_in;
+    uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
+    uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
     rc = AQ_OK;
+    for (int hb = 0; hb < 6 && !rc; ++hb) {
+      uint32_t box[4] = {64, (uint32_t)k.pw, (uint32_t)(32 >> hb), 1};
+      rc = encode_map(c, &k.tmH[hb], sb.ptr + src_c_off, 4, dims, str, box, sw);
+    }
   } else if (k.stride == 1) {
     uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};

@@ -69,7 +69,6 @@ struct Ring {
 };
 
 constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpMma1 = 7, kWarpEpi0 = 8;
-constexpr int kHaloThreads = 128;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -233,7 +232,6 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8];
   __shared__ __align__(16) float s_bias[kMaxCout];
   __shared__ uint32_t tmem_slot;
-  __shared__ int s_rowbase[2][40];
   __shared__ uint8_t s_det_a[EPI == EPI_DETECT ? 256 : 1], s_det_o[EPI == EPI_DETECT ? 256 : 1];  // column -> anchor, output
 
   const uint32_t warp = threadIdx.x >> 5;
@@ -252,6 +250,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   auto stg_full = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 4 + a); };
   auto stg_empty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 6 + a); };
 
+  if (warp == 0 && lane == 0 && p.mode == CONV_MODE_HALO) {
+    for (int hb = 0; hb < 6; ++hb) prefetch_tmap(&p.tmH[hb]);
+  }
   if (warp == 0 && lane == 0 && p.mode != CONV_MODE_HALO) {
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
-      mbar_init(a_full(s), p.mode == CONV_MODE_HALO ? kHaloThreads : 1);
+      mbar_init(a_full(s), 1);
       mbar_init(a_empty(s), p.n_mma);
     }
     for (int s = 0; s < p.nb; ++s) {
@@ -298,106 +299,52 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   if (warp < 4) {
     // =========================== A producer ===========================
     if (p.mode == CONV_MODE_HALO) {
-      // 128 threads gather the halo patch with 16-byte cp.async (zero fill outside the image / past c_in):
-      // a multi-line TMA box costs ~0.2-0.4 us per line (measured), cp.async has no such per-line cost and
-      // lets the patch rows come from the tall (image-stacked) coordinate system.
-      const int t = threadIdx.x;
-      const int rows = p.pw * p.ph;
-      const int hp1 = p.a_h + 1;
-      // 16-byte chunks of a 128-byte row that ever carry data.  With a single K chunk (c_in <= 64) the rest
-      // of every row is zeroed once and stays zero; a power-of-two count also gets a compact thread mapping
-      // (the 16-channel stem would otherwise spend 3/4 of its copies on zero fill).
-      const int jn = p.cpt == 1 ? (p.a_cin + 7) >> 3 : 8;
-      const bool compact = jn < 8 && (jn & (jn - 1)) == 0;
-      const int jshift = jn == 1 ? 0 : (jn == 2 ? 1 : 2);
-      if (jn < 8) {
-        const int nz = 8 - jn;
-        for (int idx = t; idx < p.na * rows * nz; idx += kHaloThreads) {
-          const int rr = idx / nz;  // row over all slots
-          const uint32_t jz = jn + (idx - rr * nz);
-          const int slot = rr / rows, r = rr - slot * rows;
-          const uint32_t dst = a_base + slot * p.a_slot_bytes + (uint32_t)r * 128u + ((jz ^ ((uint32_t)r & 7u)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u) : "memory");
-        }
-      }
-      griddep_wait();  // activations are written by the previous kernel
-      const int la = p.na >= 3 ? 1 : 0;  // patches kept in flight behind the one being issued
-      Ring ra;
-      int it = 0;
-      int pend_slot = -1;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        int m_tile, n_idx;
-        split_tile(p, tile, m_tile, n_idx);
-        const MBlock t0 = mblock_coords(p, m_tile, 0);
-        // per patch row: element offset of pixel (n, y, 0) in the source buffer, or -1 for a zero row
-        int* rb = s_rowbase[it & 1];
-        if (t < p.ph) {
-          const int R = t0.y0 - 1 + t;
-          int off = -1;
-          if (R >= 0) {
-            const int n = R / hp1, y = R - n * hp1 - 1;
-            if (y >= 0 && n < p.a_n) off = (n * p.a_h + y) * p.a_w * p.a_ct;
-          }
-          rb[t] = off;
-        }
-        named_bar_sync(1, kHaloThreads);
-        const long long tr0 = TR_NOW();
-        long long trw = 0, trd = 0;
-        for (int c = 0; c < p.cpt; ++c, ra.advance(p.na)) {
-          const uint32_t slot = ra.slot;
-          TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
-          const uint32_t dst0 = a_base + slot * p.a_slot_bytes;
+      // One thread loads the halo patch with TMA boxes (64 ch, pw pixels, h rows).  The patch lives in "tall"
+      // coordinates (images stacked with one shared zero row): it is cut into per-image segments, each a few
+      // boxes of 32/16/8/4/2/1 rows; rows outside an image (the shared zero rows, x = -1 / W, channels past
+      // c_in, images past the batch) come from TMA out-of-bounds zero fill.  Box destinations are only
+      // 128-byte aligned, which SWIZZLE_128B honours (absolute-address swizzle, probe T10); a patch costs
+      // 2-5 TMA instructions instead of ~2600 cp.async (probe T9: 18x18 patch round trip ~0.8k clk).
+      if (warp == 0) {
+        griddep_wait();  // activations are written by the previous kernel
+        const int hp1 = p.a_h + 1;
+        const uint32_t row_bytes = (uint32_t)p.pw * 128u;
+        Ring ra;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+          int m_tile, n_idx;
+          split_tile(p, tile, m_tile, n_idx);
+          const MBlock t0 = mblock_coords(p, m_tile, 0);
+          const long long tr0 = TR_NOW();
+          long long trw = 0;
           const int xl = t0.x0 - 1;
-          if (compact) {
-            const uint32_t j = (uint32_t)t & (uint32_t)(jn - 1);
-            const __half* cbase = p.a_src + c * 64 + (int)j * 8;
-            for (int r = t >> jshift; r < rows; r += kHaloThreads >> jshift) {
-              const int py = (r * p.pw_inv) >> 16;
-              const int gx = xl + r - py * p.pw;
-              const int off = rb[py];
-              const bool ok = off >= 0 && gx >= 0 && gx < p.a_w;
-              const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
-              cp_async_16_zfill(dst0 + (uint32_t)r * 128u + ((j ^ ((uint32_t)r & 7u)) << 4), src, ok ? 16u : 0u);
-            }
-          } else {
-            const uint32_t j = (uint32_t)t & 7u;
-            const int cc = c * 64 + (int)j * 8;
-            if ((int)j < jn) {
-              const bool cvalid = cc < p.a_cin;
-              const __half* cbase = p.a_src + cc;
-              const uint32_t dsw = dst0 + ((j ^ ((uint32_t)(t >> 3) & 7u)) << 4);  // (r & 7) is fixed per thread
-              for (int r = t >> 3; r < rows; r += kHaloThreads / 8) {
-                const int py = (r * p.pw_inv) >> 16;
-                const int gx = xl + r - py * p.pw;
-                const int off = rb[py];
-                const bool ok = cvalid && off >= 0 && gx >= 0 && gx < p.a_w;
-                const __half* src = ok ? cbase + off + gx * p.a_ct : p.a_src;
-                cp_async_16_zfill(dsw + (uint32_t)r * 128u, src, ok ? 16u : 0u);
+          for (int c = 0; c < p.cpt; ++c, ra.advance(p.na)) {
+            const uint32_t slot = ra.slot;
+            TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
+            if (!elect_one()) continue;
+            mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+            uint32_t dst = a_base + slot * p.a_slot_bytes;
+            int R = t0.y0 - 1, rem = p.ph;  // R = -1 (above the first zero row) resolves to n = 0, y = -2
+            while (rem > 0) {
+              const int n = R / hp1;
+              int y = R - n * hp1 - 1;  // -1 = the zero row above image n
+              int len = p.a_h - y;      // rows y .. H-1
+              if (len > rem) len = rem;
+              R += len;
+              rem -= len;
+#pragma unroll
+              for (int hb = 0; hb < 6; ++hb) {
+                const int h = 32 >> hb;
+                if (len & h) {
+                  tma_load_4d(dst, &p.tmH[hb], a_full(slot), c * 64, xl, y, n);
+                  dst += (uint32_t)h * row_bytes;
+                  y += h;
+                }
               }
             }
           }
-          cp_async_commit();
-          // signal the patch issued `la` iterations ago: this thread's part has landed -> make it visible
-          // to the tensor core (async proxy) and arrive
-          if (la == 0) {
-            cp_async_wait_all();
-            fence_proxy_async_smem();
-            mbar_arrive(a_full(slot));
-          } else {
-            if (pend_slot >= 0) {
-              TR_WAIT(trd, cp_async_wait_1());
-              fence_proxy_async_smem();
-              mbar_arrive(a_full(pend_slot));
-            }
-            pend_slot = (int)slot;
-          }
+          if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
         }
-        if (t == 0) trace_put<TRACE>(p, 0, it, tr0, trw, trd, TR_NOW());
-      }
-      if (pend_slot >= 0) {
-        cp_async_wait_all();
-        fence_proxy_async_smem();
-        mbar_arrive(a_full(pend_slot));
       }
     } else if (warp == 0) {
       griddep_wait();  // activations are written by the previous kernel
@@ -504,11 +451,21 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         const int n0 = n_idx * p.tile_n;
         const long long tr0 = TR_NOW();
         long long trw = 0, trr = 0;
+        const MBlock t0 = mblock_coords(p, m_tile, 0);
         for (int mb = 0; mb < p.mblk; ++mb, ++k, rs.advance(p.n_stg)) {
           const uint32_t sbuf = rs.slot;
           TR_WAIT(trw, mbar_wait(stg_full(sbuf), rs.phase));
-          const MBlock t = mblock_coords(p, m_tile, mb);
           if (lane != 0) continue;
+          MBlock t;
+          if (p.mode == CONV_MODE_TAP) {
+            t = mblock_coords(p, m_tile, mb);
+          } else {  // derive from the tile origin without divisions (mx is 1, 2 or 4)
+            const int jx = mb & (p.mx - 1), jy = mb >> (p.mx >> 1);
+            t = t0;
+            t.m0 += mb * kTileM;
+            t.x0 += jx * 8;
+            t.y0 += jy * 16;
+          }
           for (int gq = 0; gq < p.groups; ++gq) {
             const uint32_t src = stg_base + sbuf * p.stg_bytes + gq * (kTileM * 128);
             if (p.mode == CONV_MODE_FLAT) {
@@ -519,7 +476,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               // outside [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
               const int hp1 = p.a_h + 1;
               const int n_first = t.y0 / hp1;
-              int n_last = (t.y0 + 15) / hp1;
+              int n_last = n_first + (t.y0 + 15 - n_first * hp1 >= hp1 ? 1 : 0);
               if (n_last > p.a_n - 1) n_last = p.a_n - 1;
               for (int n = n_first; n <= n_last; ++n) {
                 const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0

@@ -58,6 +58,7 @@ struct alignas(64) ConvKParams {
   CUtensorMap tmA2;   // TAP stride 2: x-parity 1
   CUtensorMap tmB;    // weight loads
   CUtensorMap tmOut;  // output stores / reduce-adds (EPI_STORE)
+  CUtensorMap tmH[6];  // HALO patch loads: boxes (64 ch, pw, h rows) with h = 32 / 16 / 8 / 4 / 2 / 1
   CUtensorMap tmOutR[4];  // HALO: the same with boxes of 8 / 4 / 2 / 1 rows (blocks that start on a zero row)
   const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
   int mode, stride;

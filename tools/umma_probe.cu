@@ -584,6 +584,147 @@ static void run_t8() {
   cudaFree(d); cudaFree(o);
 }
 
+// ------------------------------------------------------------------------------------------------ T9
+// Halo-patch box loads: one 4-D TMA box (64 ch, pw, ph, 1 image) from an NHWC fp16 map, `depth` boxes in
+// flight per SM, coordinates precomputed (no div/mod in the issue loop).
+__global__ void __launch_bounds__(64) tma_patch_kernel(const __grid_constant__ CUtensorMap tm, int depth, int pw, int ph,
+                                                       int iters, int W, int H, int N, long long* out) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  const uint32_t slot = ((uint32_t)(pw * ph * 128) + 1023u) & ~1023u;
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long tot = 0, tissue = 0;
+    int x = (blockIdx.x * 8) % W, y = (blockIdx.x * 16) % H, n = blockIdx.x % N;
+    for (int it = 0; it < iters; ++it) {
+      const long long t0 = clock64();
+      mbar_arrive_expect_tx(smem_u32(&bar), depth * pw * ph * 128);
+      for (int l = 0; l < depth; ++l) {
+        tma_load_4d(base + l * slot, &tm, smem_u32(&bar), 0, x - 1, y - 1, n);
+        x += pw - 2;
+        if (x >= W) { x = 0; y += ph - 2; if (y >= H) { y = 0; if (++n == N) n = 0; } }
+      }
+      const long long t1 = clock64();
+      mbar_wait(smem_u32(&bar), it & 1);
+      tot += clock64() - t0;
+      tissue += t1 - t0;
+    }
+    if (blockIdx.x == 0) {
+      out[0] = tot / iters;
+      out[1] = tissue / iters;
+    }
+  }
+}
+
+static void run_t9() {
+  const int W = 160, H = 160, N = 64, C = 64;
+  const size_t bytes = (size_t)N * H * W * C * 2;
+  uint8_t* d;
+  long long* o;
+  CK(cudaMalloc(&d, bytes));
+  CK(cudaMemset(d, 1, bytes));
+  CK(cudaMalloc(&o, 64));
+  CK(cudaFuncSetAttribute(tma_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  const int shapes[4][2] = {{10, 18}, {18, 18}, {18, 34}, {34, 18}};
+  for (auto& sh : shapes) {
+    const int pw = sh[0], ph = sh[1];
+    CUtensorMap tm;
+    cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t bx[4] = {64, (cuuint32_t)pw, (cuuint32_t)ph, 1}, es[4] = {1, 1, 1, 1};
+    CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { printf("T9 encode failed %d\n", (int)r); continue; }
+    const size_t slot = ((size_t)pw * ph * 128 + 1023) & ~(size_t)1023;
+    for (int grid : {1, 148}) {
+      for (int depth : {1, 2, 3}) {
+        if (depth * slot > 200 * 1024) continue;
+        long long h[2];
+        for (int rep = 0; rep < 2; ++rep) {
+          tma_patch_kernel<<<grid, 64, depth * slot + 2048>>>(tm, depth, pw, ph, 300, W, H, N, o);
+          CK(cudaDeviceSynchronize());
+        }
+        CK(cudaMemcpy(h, o, 16, cudaMemcpyDeviceToHost));
+        printf("T9 patch box 64ch x %2d x %2d (%5.1f KB), %d in flight, grid %3d: round trip %6lld clk (issue %5lld) -> %.1f B/clk/SM\n",
+               pw, ph, pw * ph * 128 / 1024.0, depth, grid, h[0], h[1], (double)depth * pw * ph * 128 / h[0]);
+      }
+    }
+  }
+  cudaFree(d); cudaFree(o);
+}
+
+// ------------------------------------------------------------------------------------------------ T10
+// Does a SWIZZLE_128B TMA load honour the absolute-address swizzle when its shared-memory destination is only
+// 128-byte aligned (not 1024)?  Needed to land halo-patch segments at arbitrary patch rows.
+__global__ void __launch_bounds__(128) tma_unaligned_kernel(const __grid_constant__ CUtensorMap tm, int off_bytes, int pw,
+                                                            int ph, int x0, int y0, int* bad) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  uint8_t* sm = raw + (base - smem_u32(raw));
+  for (int i = threadIdx.x; i < 48 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0xFFFFFFFFu;
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(smem_u32(&bar), pw * ph * 128);
+    tma_load_4d(base + off_bytes, &tm, smem_u32(&bar), 0, x0, y0, 0);
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  int nbad = 0;
+  for (int i = threadIdx.x; i < pw * ph * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    const int py = r / pw, px = r - py * pw;
+    const uint32_t row_addr = base + off_bytes + r * 128;
+    const uint32_t a = row_addr + ((j ^ ((row_addr >> 7) & 7)) << 4);
+    const __half got = *reinterpret_cast<const __half*>(sm + (a - base));
+    const float want = (float)(((y0 + py) * 32 + (x0 + px)) * 8 + j);
+    if (__half2float(got) != want) ++nbad;
+  }
+  atomicAdd(bad, nbad);
+}
+
+static void run_t10() {
+  const int W = 32, H = 8, C = 64;
+  std::vector<__half> h((size_t)H * W * C);
+  for (int y = 0; y < H; ++y)
+    for (int x = 0; x < W; ++x)
+      for (int c = 0; c < C; ++c) h[((size_t)y * W + x) * C + c] = __float2half((float)((y * 32 + x) * 8 + (c >> 3)));
+  __half* d;
+  int* bad;
+  CK(cudaMalloc(&d, h.size() * 2));
+  CK(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&bad, 4));
+  CK(cudaFuncSetAttribute(tma_unaligned_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  const int pw = 18, ph = 2;
+  CUtensorMap tm;
+  cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, 1};
+  cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t bx[4] = {64, (cuuint32_t)pw, (cuuint32_t)ph, 1}, es[4] = {1, 1, 1, 1};
+  CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { printf("T10 encode failed %d\n", (int)r); return; }
+  for (int off : {0, 1024, 128, 256, 384, 896, 2304, 3 * 2304, 5 * 2304 + 128}) {
+    CK(cudaMemset(bad, 0, 4));
+    tma_unaligned_kernel<<<1, 128, 52 * 1024>>>(tm, off, pw, ph, 3, 1, bad);
+    cudaError_t e = cudaDeviceSynchronize();
+    int hb = -1;
+    if (e == cudaSuccess) CK(cudaMemcpy(&hb, bad, 4, cudaMemcpyDeviceToHost));
+    printf("T10 SW128 box 64x%dx%d to smem base+%5d: %s, %d / %d chunks wrong\n", pw, ph, off,
+           e == cudaSuccess ? "ok" : cudaGetErrorString(e), hb, pw * ph * 8);
+    if (e != cudaSuccess) break;
+  }
+}
+
 int main(int argc, char** argv) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -597,5 +738,7 @@ int main(int argc, char** argv) {
   if (strchr(which, '6')) run_t6();
   if (strchr(which, '7')) run_t7();
   if (strchr(which, '8')) run_t8();
+  if (strchr(which, '9')) run_t9();
+  if (strchr(which, 'a')) run_t10();
   return 0;
 }

@@ -177,7 +177,8 @@ struct Cand {
 void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles_n, int n_steps, int cpt, int num_sms) {
   const int groups = (tile_n + 63) / 64;
   const uint32_t b_slot = (uint32_t)round_up(tile_n * 128, 1024);
-  const uint32_t stg = (uint32_t)groups * kTileM * 128;
+  (void)groups;
+  const uint32_t stg = kTileM * 128;  // staging ring: 16 KB buffers, one 64-channel group of an M block each
   int a_instr_per_group = 1, n_groups = n_steps;
   if (cd.mode == CONV_MODE_FLAT) {
     const int m_blocks = (batch * ho * wo + kTileM - 1) / kTileM;
@@ -209,7 +210,7 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   const long budget = kConvMaxDynSmem - 1024;
   cd.b_res = (n_tiles_n == 1 && n_steps <= kMaxB && (long)n_steps * b_slot <= 112 * 1024) ? 1 : 0;
   cd.na = 2;
-  cd.n_stg = 1;
+  cd.n_stg = 2;
   cd.nb = cd.b_res ? n_steps : 3;
   auto used = [&]() { return (long)cd.na * cd.a_slot + (long)cd.nb * b_slot + (long)cd.n_stg * stg; };
   if (used() > budget) {
@@ -224,7 +225,7 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   // a third HALO patch slot lets the cp.async producer keep two patches in flight
   if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
   if (!cd.b_res) grow(cd.nb, 5, b_slot);
-  grow(cd.n_stg, 2, stg);
+  grow(cd.n_stg, 3, stg);
   grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
   if (!cd.b_res) grow(cd.nb, 12, b_slot);
   // ---- cost
@@ -348,7 +349,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   k.a_tx_bytes = best.a_tx;
   k.b_slot_bytes = (uint32_t)round_up(k.tile_n * 128, 1024);
   k.b_tx_bytes = (uint32_t)k.tile_n * 128;
-  k.stg_bytes = det ? 0 : (uint32_t)k.groups * kTileM * 128;
+  k.stg_bytes = det ? 0 : (uint32_t)kTileM * 128;
   if (det) k.n_stg = 1;
   k.act = det ? ACT_NONE : op.conv.act;
   k.has_res = (!det && op.conv.res >= 0) ? 1 : 0;

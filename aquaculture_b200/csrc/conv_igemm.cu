@@ -68,7 +68,7 @@ struct Ring {
   }
 };
 
-constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpStore = 6, kWarpMma1 = 7, kWarpEpi0 = 8;
+constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpMma1 = 7, kWarpEpi0 = 8;  // warp 6 is idle
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -98,6 +98,49 @@ __device__ __forceinline__ void trace_put(const ConvKParams& p, int role, int it
   }
 }
 
+
+// TMA store (or reduce-add, for the fused Bottleneck residual) of one staged 64-channel group
+// [128 rows][128 B, swizzled] of the M block at `t`; `ch0` = first output channel of the group.
+__device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& t, uint32_t src, int ch0) {
+  if (p.mode == CONV_MODE_FLAT) {
+    if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, ch0, t.m0);
+    else tma_store_2d(&p.tmOut, src, ch0, t.m0);
+  } else if (p.mode == CONV_MODE_HALO) {
+    // the 16 tall rows of the block touch one or two images: one clipped box per image (rows outside
+    // [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
+    const int hp1 = p.a_h + 1;
+    const int n_first = t.y0 / hp1;
+    int n_last = n_first + (t.y0 + 15 - n_first * hp1 >= hp1 ? 1 : 0);
+    if (n_last > p.a_n - 1) n_last = p.a_n - 1;
+    for (int n = n_first; n <= n_last; ++n) {
+      const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0
+      if (ys >= 0) {
+        if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, ch0, t.x0, ys, n);
+        else tma_store_4d(&p.tmOut, src, ch0, t.x0, ys, n);
+      } else {
+        // a TMA store may not start at a negative coordinate (illegal instruction, probe T6):
+        // write staging rows [-ys, 16) to image rows [0, 16 + ys) as boxes of 8 / 4 / 2 / 1 rows
+        int s0 = -ys, y = 0;
+        int len = 16 - s0;
+        if (len > p.a_h) len = p.a_h;
+#pragma unroll
+        for (int hb = 0; hb < 4; ++hb) {
+          const int h = 8 >> hb;
+          if (len & h) {
+            const uint32_t ssrc = src + (uint32_t)s0 * 1024u;
+            if (p.has_res) tma_reduce_add_4d(&p.tmOutR[hb], ssrc, ch0, t.x0, y, n);
+            else tma_store_4d(&p.tmOutR[hb], ssrc, ch0, t.x0, y, n);
+            s0 += h;
+            y += h;
+          }
+        }
+      }
+    }
+  } else {
+    if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, ch0, t.x0, t.y0, t.n);
+    else tma_store_4d(&p.tmOut, src, ch0, t.x0, t.y0, t.n);
+  }
+}
 
 // Barrier addresses inside the static `bars` array (see the kernel for the layout).
 struct MmaCtx {
@@ -247,8 +290,6 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   auto b_empty = [&](int s) { return bar0 + 8u * (2 * kMaxA + kMaxB + s); };
   auto tfull = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
   auto tempty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
-  auto stg_full = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 4 + a); };
-  auto stg_empty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 6 + a); };
 
   if (warp == 0 && lane == 0 && p.mode == CONV_MODE_HALO) {
     for (int hb = 0; hb < 6; ++hb) prefetch_tmap(&p.tmH[hb]);
@@ -257,7 +298,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
-  if (warp == kWarpStore && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpEpi0 + 4 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
   if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
@@ -271,8 +312,6 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull(a), p.n_mma);
       mbar_init(tempty(a), kEpiWarps);
-      mbar_init(stg_full(a), kEpiWarps);
-      mbar_init(stg_empty(a), 1);
     }
     fence_barrier_init();
   }
@@ -438,88 +477,6 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         else mma_role<false, false, 1, TRACE>(p, mc);
       }
     }
-  } else if (warp == kWarpStore) {
-    // =========================== TMA store issuer ===========================
-    if (EPI == EPI_STORE) {
-      // warp-uniform loop; lane 0 issues (bulk-group bookkeeping is per thread)
-      uint32_t k = 0;
-      Ring rs;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        int m_tile, n_idx;
-        split_tile(p, tile, m_tile, n_idx);
-        const int n0 = n_idx * p.tile_n;
-        const long long tr0 = TR_NOW();
-        long long trw = 0, trr = 0;
-        const MBlock t0 = mblock_coords(p, m_tile, 0);
-        for (int mb = 0; mb < p.mblk; ++mb, ++k, rs.advance(p.n_stg)) {
-          const uint32_t sbuf = rs.slot;
-          TR_WAIT(trw, mbar_wait(stg_full(sbuf), rs.phase));
-          if (lane != 0) continue;
-          MBlock t;
-          if (p.mode == CONV_MODE_TAP) {
-            t = mblock_coords(p, m_tile, mb);
-          } else {  // derive from the tile origin without divisions (mx is 1, 2 or 4)
-            const int jx = mb & (p.mx - 1), jy = mb >> (p.mx >> 1);
-            t = t0;
-            t.m0 += mb * kTileM;
-            t.x0 += jx * 8;
-            t.y0 += jy * 16;
-          }
-          for (int gq = 0; gq < p.groups; ++gq) {
-            const uint32_t src = stg_base + sbuf * p.stg_bytes + gq * (kTileM * 128);
-            if (p.mode == CONV_MODE_FLAT) {
-              if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
-              else tma_store_2d(&p.tmOut, src, n0 + gq * 64, t.m0);
-            } else if (p.mode == CONV_MODE_HALO) {
-              // the 16 tall rows of the block touch one or two images: one clipped box per image (rows
-              // outside [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
-              const int hp1 = p.a_h + 1;
-              const int n_first = t.y0 / hp1;
-              int n_last = n_first + (t.y0 + 15 - n_first * hp1 >= hp1 ? 1 : 0);
-              if (n_last > p.a_n - 1) n_last = p.a_n - 1;
-              for (int n = n_first; n <= n_last; ++n) {
-                const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0
-                if (ys >= 0) {
-                  // rows past H (the zero row, the next image) are clipped by TMA
-                  if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, n0 + gq * 64, t.x0, ys, n);
-                  else tma_store_4d(&p.tmOut, src, n0 + gq * 64, t.x0, ys, n);
-                } else {
-                  // a TMA store may not start at a negative coordinate (illegal instruction, probe T6):
-                  // write staging rows [-ys, 16) to image rows [0, 16 + ys) as boxes of 8 / 4 / 2 / 1 rows
-                  int s0 = -ys, y = 0;
-                  int len = 16 - s0;
-                  if (len > p.a_h) len = p.a_h;
-                  for (int hb = 0; hb < 4; ++hb) {
-                    const int h = 8 >> hb;
-                    if (len & h) {
-                      const uint32_t ssrc = src + (uint32_t)s0 * 1024u;
-                      if (p.has_res) tma_reduce_add_4d(&p.tmOutR[hb], ssrc, n0 + gq * 64, t.x0, y, n);
-                      else tma_store_4d(&p.tmOutR[hb], ssrc, n0 + gq * 64, t.x0, y, n);
-                      s0 += h;
-                      y += h;
-                    }
-                  }
-                }
-              }
-            } else {
-              if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
-              else tma_store_4d(&p.tmOut, src, n0 + gq * 64, t.x0, t.y0, t.n);
-            }
-          }
-          tma_store_commit();
-          if (p.n_stg == 2) {
-            TR_WAIT(trr, tma_store_wait_read1());  // the previous block's staging buffer has been read
-            if (k > 0) mbar_arrive(stg_empty((k - 1) & 1u));
-          } else {
-            TR_WAIT(trr, tma_store_wait_read0());
-            mbar_arrive(stg_empty(0));
-          }
-        }
-        if (lane == 0) trace_put<TRACE>(p, 4, it, tr0, trw, trr, TR_NOW());
-      }
-      if (lane == 0) tma_store_wait0();
-    }
   } else if (warp >= kWarpEpi0) {
     // =========================== epilogue warps 8..15 ===========================
     const uint32_t e = warp - kWarpEpi0;
@@ -527,6 +484,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     const uint32_t half = e >> 2;        // which of the two interleaved sets of 16-column chunks
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
     const int n_chunks = p.tile_n >> 4;
+    const int n_groups = p.groups;
+    const uint32_t n_stg = p.n_stg;
+    const bool issuer = e == 4 && lane == 0;  // the thread that issues every TMA store of this CTA
+    uint32_t v0[16], v1[16];
+    bool preloaded = false;
     Ring rs, rt;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(p.acc_stages)) {
@@ -539,15 +501,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       mbar_wait(tfull(as), rt.phase);
       const long long tr1 = TR_NOW();
       tc_fence_after();
+      MBlock t0 = {};
+      if (EPI == EPI_STORE) t0 = mblock_coords(p, m_tile, 0);
       for (int mb = 0; mb < p.mblk; ++mb) {
         const uint32_t t_addr = tmem_base + ((q * 32u) << 16) + as * p.acc_stride + mb * p.acc_pitch;
         if (EPI == EPI_STORE) {
-          const uint32_t sbuf = rs.slot;
-          TR_WAIT(trs, mbar_wait(stg_empty(sbuf), rs.phase ^ 1u));
-          rs.advance(p.n_stg);
-          const uint32_t stg = stg_base + sbuf * p.stg_bytes;
           // one 16-column chunk: bias + SiLU -> fp16 -> swizzled staging
-          auto process = [&](const uint32_t (&v)[16], int ch) {
+          auto process = [&](const uint32_t (&v)[16], int ch, uint32_t stg) {
             const int c0 = ch << 4;
             const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c0);
             float f[16];
@@ -582,8 +542,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             uint32_t h[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) h[i] = pack_half2(f[2 * i], f[2 * i + 1]);
-            // staging: 64-channel groups of [128 rows][128 B], 16-byte chunk j of row r at j ^ (r & 7)
-            const uint32_t grp = stg + (uint32_t)(c0 >> 6) * (kTileM * 128) + row * 128u;
+            // staging: one 64-channel group [128 rows][128 B], 16-byte chunk j of row r at j ^ (r & 7)
+            const uint32_t grp = stg + row * 128u;
             const uint32_t j = (uint32_t)(c0 & 63) >> 3;
             const uint32_t a0 = grp + (((j) ^ (row & 7u)) << 4);
             const uint32_t a1 = grp + (((j + 1) ^ (row & 7u)) << 4);
@@ -592,37 +552,59 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
                          : "memory");
                     };
-          // software pipeline: the TMEM load of the next chunk is in flight while this one is processed
-          {
-            uint32_t v0[16], v1[16];
-            int ch = half;
-            if (ch < n_chunks) {
-              tmem_ld16(t_addr + (ch << 4), v0);
-              while (true) {
-                tmem_ld_wait();
-                const bool more1 = ch + 2 < n_chunks;
-                if (more1) tmem_ld16(t_addr + ((ch + 2) << 4), v1);
-                process(v0, ch);
-                if (!more1) break;
-                tmem_ld_wait();
-                const bool more0 = ch + 4 < n_chunks;
-                if (more0) tmem_ld16(t_addr + ((ch + 4) << 4), v0);
-                process(v1, ch + 2);
-                if (!more0) break;
-                ch += 4;
-              }
+          // Output goes out in 64-channel groups through a ring of 16 KB staging buffers.  All eight warps fill
+          // a group (two 16-column chunks each), meet at a named barrier, and one thread issues its TMA store;
+          // before the barrier that thread makes sure the store that last used the NEXT buffer has finished
+          // reading shared memory, so one barrier per group is the only synchronisation.
+          MBlock t;
+          if (p.mode == CONV_MODE_TAP) {
+            t = mblock_coords(p, m_tile, mb);
+          } else {  // derive from the tile origin without divisions (mx is 1, 2 or 4)
+            const int jx = mb & (p.mx - 1), jy = mb >> (p.mx >> 1);
+            t = t0;
+            t.m0 += mb * kTileM;
+            t.x0 += jx * 8;
+            t.y0 += jy * 16;
+          }
+          for (int g = 0; g < n_groups; ++g) {
+            const uint32_t stg = stg_base + rs.slot * (kTileM * 128);
+            rs.advance(n_stg);
+            const int chA = 4 * g + (int)half, chB = chA + 2;
+            if (!preloaded) {
+              if (chA < n_chunks) tmem_ld16(t_addr + (chA << 4), v0);
+              if (chB < n_chunks) tmem_ld16(t_addr + (chB << 4), v1);
+            }
+            tmem_ld_wait();
+            const bool last_of_tile = mb == p.mblk - 1 && g == n_groups - 1;
+            if (last_of_tile) {
+              // every TMEM read of this tile is done -> the MMA warps may overwrite the accumulators
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(tempty(as));
+            }
+            if (chA < n_chunks) process(v0, chA, stg);
+            if (chB < n_chunks) process(v1, chB, stg);
+            // next group's accumulators travel TMEM -> registers while this group is stored
+            preloaded = !last_of_tile;
+            if (preloaded) {
+              const bool same = g + 1 < n_groups;
+              const uint32_t ta = same ? t_addr : t_addr + p.acc_pitch;
+              const int nA = same ? chA + 4 : (int)half;
+              if (nA < n_chunks) tmem_ld16(ta + (nA << 4), v0);
+              if (nA + 2 < n_chunks) tmem_ld16(ta + ((nA + 2) << 4), v1);
+            }
+            fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
+            if (issuer) {
+              if (n_stg == 2) tma_store_wait_read0();
+              else if (n_stg == 3) tma_store_wait_read1();
+              else tma_store_wait_read2();
+            }
+            TR_WAIT(trs, named_bar_sync(1, kEpiWarps * 32));
+            if (issuer) {
+              store_group(p, t, stg, n0 + g * 64);
+              tma_store_commit();
             }
           }
-          if (mb == p.mblk - 1) {
-            // every TMEM read of this tile is done -> the MMA warp may overwrite the accumulators
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty(as));
-          }
-          // make the staging writes visible to the async proxy, then hand the block to the store warp
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(stg_full(sbuf));
         } else {
           // ---- Detect decode: row = one grid cell, columns = 3 anchors x (5 + nc)
           const MBlock t = mblock_coords(p, m_tile, mb);
@@ -691,6 +673,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       }
       if (e == 0 && lane == 0) trace_put<TRACE>(p, 3, it, tr0, tr1 - tr0, trs, TR_NOW());
     }
+    if (EPI == EPI_STORE && issuer) tma_store_wait0();
   }
 
   // teardown: everyone done with TMEM before the allocating warp frees it

@@ -113,6 +113,9 @@ __device__ __forceinline__ void tma_store_wait_read0() {
 __device__ __forceinline__ void tma_store_wait_read1() {
   asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
 }
+__device__ __forceinline__ void tma_store_wait_read2() {
+  asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+}
 __device__ __forceinline__ void tma_store_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ------------------------------------------------------------------ cp.async (LDGSTS)

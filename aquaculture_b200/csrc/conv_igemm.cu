@@ -68,7 +68,7 @@ struct Ring {
   }
 };
 
-constexpr uint32_t kWarpB = 4, kWarpMma = 5, kWarpMma1 = 7, kWarpEpi0 = 8;  // warp 6 is idle
+constexpr uint32_t kWarpA = 0, kWarpB = 1, kWarpMma = 2, kWarpMma1 = 3, kWarpEpi0 = 4;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
-  if (warp == kWarpEpi0 + 4 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpEpi0 + 12 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
   if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
   const int total_tiles = p.m_tiles * p.n_tiles_n;
 
-  if (warp < 4) {
+  if (warp == kWarpA) {
     // =========================== A producer ===========================
     if (p.mode == CONV_MODE_HALO) {
       // One thread loads the halo patch with TMA boxes (64 ch, pw pixels, h rows).  The patch lives in "tall"
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       // c_in, images past the batch) come from TMA out-of-bounds zero fill.  Box destinations are only
       // 128-byte aligned, which SWIZZLE_128B honours (absolute-address swizzle, probe T10); a patch costs
       // 2-5 TMA instructions instead of ~2600 cp.async (probe T9: 18x18 patch round trip ~0.8k clk).
-      if (warp == 0) {
+      {
         griddep_wait();  // activations are written by the previous kernel
         const int hp1 = p.a_h + 1;
         const uint32_t row_bytes = (uint32_t)p.pw * 128u;
@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
         }
       }
-    } else if (warp == 0) {
+    } else {
       griddep_wait();  // activations are written by the previous kernel
       Ring ra;
       int it = 0;
@@ -481,13 +481,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     // =========================== epilogue warps 8..15 ===========================
     const uint32_t e = warp - kWarpEpi0;
     const uint32_t q = e & 3;            // TMEM lane quarter this warp may access (warp % 4)
-    const uint32_t half = e >> 2;        // which of the two interleaved sets of 16-column chunks
+    const uint32_t sub = e >> 2;         // which 16-column chunk of every 64-channel group (0..3)
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
     const int n_chunks = p.tile_n >> 4;
     const int n_groups = p.groups;
     const uint32_t n_stg = p.n_stg;
-    const bool issuer = e == 4 && lane == 0;  // the thread that issues every TMA store of this CTA
-    uint32_t v0[16], v1[16];
+    const bool issuer = e == 12 && lane == 0;  // the thread that issues every TMA store of this CTA
+    uint32_t v0[16];
     bool preloaded = false;
     Ring rs, rt;
     int it = 0;
@@ -552,8 +552,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
                          : "memory");
                     };
-          // Output goes out in 64-channel groups through a ring of 16 KB staging buffers.  All eight warps fill
-          // a group (two 16-column chunks each), meet at a named barrier, and one thread issues its TMA store;
+          // Output goes out in 64-channel groups through a ring of 16 KB staging buffers.  All sixteen warps fill
+          // a group (one 16-column chunk of 32 rows each), meet at a named barrier, and one thread issues its TMA store;
           // before the barrier that thread makes sure the store that last used the NEXT buffer has finished
           // reading shared memory, so one barrier per group is the only synchronisation.
           MBlock t;
@@ -569,10 +569,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           for (int g = 0; g < n_groups; ++g) {
             const uint32_t stg = stg_base + rs.slot * (kTileM * 128);
             rs.advance(n_stg);
-            const int chA = 4 * g + (int)half, chB = chA + 2;
+            const int chA = 4 * g + (int)sub;
             if (!preloaded) {
               if (chA < n_chunks) tmem_ld16(t_addr + (chA << 4), v0);
-              if (chB < n_chunks) tmem_ld16(t_addr + (chB << 4), v1);
             }
             tmem_ld_wait();
             const bool last_of_tile = mb == p.mblk - 1 && g == n_groups - 1;
@@ -583,15 +582,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               if (lane == 0) mbar_arrive(tempty(as));
             }
             if (chA < n_chunks) process(v0, chA, stg);
-            if (chB < n_chunks) process(v1, chB, stg);
             // next group's accumulators travel TMEM -> registers while this group is stored
             preloaded = !last_of_tile;
             if (preloaded) {
               const bool same = g + 1 < n_groups;
               const uint32_t ta = same ? t_addr : t_addr + p.acc_pitch;
-              const int nA = same ? chA + 4 : (int)half;
+              const int nA = same ? chA + 4 : (int)sub;
               if (nA < n_chunks) tmem_ld16(ta + (nA << 4), v0);
-              if (nA + 2 < n_chunks) tmem_ld16(ta + ((nA + 2) << 4), v1);
             }
             fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
             if (issuer) {
@@ -616,7 +613,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const int gx = pos - gy * p.det_nx;
           const bool valid = m < p.det_m_total;
           const int ncols = 3 * p.det_no;
-          for (int ch = half; ch < n_chunks; ch += 2) {
+          for (int ch = sub; ch < n_chunks; ch += 4) {
             const int c0 = ch << 4;
             uint32_t v[16];
             tmem_ld16(t_addr + c0, v);

@@ -44,8 +44,8 @@ enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2 };
 enum { EPI_STORE = 0, EPI_DETECT = 1 };
 enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
-constexpr int kConvThreads = 512;
-constexpr int kEpiWarps = 8;
+constexpr int kConvThreads = 640;  // 4 role warps + 16 epilogue warps
+constexpr int kEpiWarps = 16;
 constexpr int kMaxA = 4;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
 constexpr int kTileM = 128;

@@ -222,10 +222,12 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   auto grow = [&](int& v, int cap, long unit) {
     while (v < cap && used() + unit <= budget) ++v;
   };
-  // a third HALO patch slot lets the cp.async producer keep two patches in flight
+  // Growth order: a third staging buffer first (a TMA store needs ~1-2k clk before its shared-memory source may
+  // be overwritten, so two buffers serialise the epilogue on it), then deeper operand rings.
+  grow(cd.n_stg, 3, stg);
   if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
   if (!cd.b_res) grow(cd.nb, 5, b_slot);
-  grow(cd.n_stg, 3, stg);
+  grow(cd.n_stg, 4, stg);
   grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
   if (!cd.b_res) grow(cd.nb, 12, b_slot);
   // ---- cost

@@ -68,7 +68,10 @@ struct Ring {
   }
 };
 
-constexpr uint32_t kWarpA = 0, kWarpB = 1, kWarpMma = 2, kWarpMma1 = 3, kWarpEpi0 = 4;
+constexpr uint32_t kWarpA = 0, kWarpB = 1, kWarpMma = 2, kWarpMma1 = 3, kWarpEpi0 = 4, kWarpStore = 20;
+// named barriers: 1..4 = staging buffer b filled (16 epilogue warps arrive, the store warp waits),
+// 5..8 = staging buffer b read by its TMA store (the store warp arrives, the epilogue warps wait)
+constexpr uint32_t kBarStgFull = 1, kBarStgEmpty = 5, kBarStgThreads = kEpiWarps * 32 + 32;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -269,6 +272,185 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
   }
 }
 
+
+struct EpiCtx {
+  uint32_t bar0, stg_base, tmem_base, bias_smem;
+  int total_tiles;
+  uint32_t e, lane;  // epilogue warp index 0..15, lane
+};
+
+// Epilogue role of the storing kernel: TMEM -> registers -> bias + activation -> fp16 -> swizzled staging -> TMA
+// store / reduce-add.  Warp e reads TMEM lanes 32 * (e % 4) .. +31 (rows of the M block) and the 16-column chunk
+// e / 4 of every 64-channel group, so its staging offsets and TMEM column are loop invariants.  Output leaves in
+// 64-channel groups through a ring of 16 KB staging buffers: all sixteen warps fill a group and ARRIVE (without
+// waiting) on the buffer's "full" named barrier; the store warp waits there, issues the TMA store, and arrives on
+// the buffer's "empty" barrier once the store has read shared memory.  An epilogue warp only blocks when it comes
+// back to a buffer whose store is still in flight (issuing a store costs the issuing thread ~500 clk, measured).
+// Every warp runs at the latency of its own dependent instruction stream (~8 clk per instruction measured,
+// profiles/r1_trace_*.txt), so the per-group path is kept to the arithmetic: all parameters live in registers.
+template <int ACT, bool TRACE>
+__device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCtx& ec) {
+  const uint32_t bar0 = ec.bar0;
+  auto tfull = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
+  auto tempty = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
+  const uint32_t e = ec.e, lane = ec.lane;
+  const uint32_t q = e & 3, sub = e >> 2;
+  const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
+  // staging offsets of this thread's two 16-byte pieces inside a group buffer [128 rows][128 B]:
+  // 16-byte chunk j of row r sits at j ^ (r & 7)
+  const uint32_t st0 = row * 128u + (((2 * sub) ^ (row & 7u)) << 4);
+  const uint32_t st1 = row * 128u + (((2 * sub + 1) ^ (row & 7u)) << 4);
+  const int n_chunks = p.tile_n >> 4, n_groups = p.groups, mblk = p.mblk, tile_n = p.tile_n;
+  const uint32_t n_stg = p.n_stg, acc_stages = p.acc_stages, acc_stride = p.acc_stride, acc_pitch = p.acc_pitch;
+  const uint32_t t_lane = ec.tmem_base + ((q * 32u) << 16) + sub * 16u;
+  const uint32_t stg_base = ec.stg_base;
+  const int total_tiles = ec.total_tiles;
+  uint32_t v[16];
+  bool preloaded = false;
+  uint32_t gcount = 0;  // groups staged so far by this CTA
+  Ring rs, rt;
+  int it = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(acc_stages)) {
+    int m_tile, n_idx;
+    split_tile(p, tile, m_tile, n_idx);
+    const int n0 = n_idx * tile_n;
+    const uint32_t as = rt.slot;
+    const long long tr0 = TR_NOW();
+    long long trs = 0, d0 = 0, d1 = 0, d2 = 0, d3 = 0, d4 = 0, d5 = 0, d6 = 0, d7 = 0;
+    long long tp = TR_NOW();
+#define TR_PT(acc) do { if (TRACE) { const long long n_ = clock64(); acc += n_ - tp; tp = n_; } } while (0)
+    mbar_wait(tfull(as), rt.phase);
+    const long long tr1 = TR_NOW();
+    tc_fence_after();
+    uint32_t ta = t_lane + as * acc_stride;                      // TMEM address of (mb, g = 0, this chunk)
+    const uint32_t bias0 = ec.bias_smem + (uint32_t)(n0 + (int)sub * 16) * 4u;
+    for (int mb = 0; mb < mblk; ++mb, ta += acc_pitch) {
+      for (int g = 0; g < n_groups; ++g, ++gcount) {
+        const uint32_t buf = rs.slot;
+        const uint32_t stg = stg_base + buf * (kTileM * 128);
+        rs.advance(n_stg);
+        const bool valid = 4 * g + (int)sub < n_chunks;  // warp-uniform
+        TR_PT(d0);
+        if (!preloaded && valid) tmem_ld16(ta + g * 64, v);
+        tmem_ld_wait();
+        TR_PT(d1);
+        const bool last_of_tile = mb == mblk - 1 && g == n_groups - 1;
+        if (last_of_tile) {
+          // every TMEM read of this tile is done -> the MMA warps may overwrite the accumulators
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty(as));
+        }
+        TR_PT(d2);
+        // the TMA store that last used this staging buffer must have read it
+        if (gcount >= n_stg) TR_WAIT(trs, named_bar_sync(kBarStgEmpty + buf, kBarStgThreads));
+        if (valid) {
+          uint32_t b4[16];
+          const uint32_t ba = bias0 + (uint32_t)g * 256u;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(b4[4 * i]), "=r"(b4[4 * i + 1]), "=r"(b4[4 * i + 2]), "=r"(b4[4 * i + 3])
+                         : "r"(ba + 16u * i));
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            if (ACT == ACT_SILU_FAST) {
+              // silu(x) = h + h * tanh(h), h = x / 2; s_bias holds bias / 2
+              const float h = fmaf(__uint_as_float(v[i]), 0.5f, __uint_as_float(b4[i]));
+              f[i] = fmaf(h, tanh_approx(h), h);
+            } else {
+              const float x = __uint_as_float(v[i]) + __uint_as_float(b4[i]);
+              f[i] = ACT == ACT_SILU ? silu_exact(x) : x;
+            }
+          }
+          uint32_t h[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) h[i] = pack_half2(f[2 * i], f[2 * i + 1]);
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + st0), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3])
+                       : "memory");
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + st1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
+                       : "memory");
+        }
+        TR_PT(d3);
+        // the next group's accumulators travel TMEM -> registers while this group is stored
+        preloaded = !last_of_tile;
+        if (preloaded) {
+          const bool same = g + 1 < n_groups;
+          const int ng = same ? g + 1 : 0;
+          if (4 * ng + (int)sub < n_chunks) tmem_ld16((same ? ta : ta + acc_pitch) + ng * 64, v);
+        }
+        TR_PT(d4);
+        fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
+        TR_PT(d5);
+        named_bar_arrive(kBarStgFull + buf, kBarStgThreads);  // hand the group to the store warp
+        TR_PT(d6);
+      }
+    }
+    if (e == 0 && lane == 0) {
+      trace_put<TRACE>(p, 3, it, tr0, tr1 - tr0, trs, TR_NOW());
+      trace_put<TRACE>(p, 4, it, d0 | (d1 << 32), d2 | (d3 << 32), d4 | (d5 << 32), d6 | (d7 << 32));
+    }
+#undef TR_PT
+  }
+}
+
+
+// Store warp: waits for each staged group, issues its TMA store / reduce-add, frees staging buffers.
+template <bool TRACE>
+__device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_base, int total_tiles, uint32_t lane) {
+  const int n_groups = p.groups, mblk = p.mblk, tile_n = p.tile_n;
+  const uint32_t n_stg = p.n_stg;
+  const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const uint32_t total_groups = (uint32_t)(my_tiles * mblk * n_groups);
+  Ring rs;
+  uint32_t k = 0;  // groups stored so far
+  int it = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+    int m_tile, n_idx;
+    split_tile(p, tile, m_tile, n_idx);
+    const int n0 = n_idx * tile_n;
+    const MBlock t0 = mblock_coords(p, m_tile, 0);
+    const long long tr0 = TR_NOW();
+    long long trw = 0, trr = 0;
+    for (int mb = 0; mb < mblk; ++mb) {
+      MBlock t = t0;
+      if (p.mode == CONV_MODE_TAP) {
+        t = mblock_coords(p, m_tile, mb);
+      } else {  // derive from the tile origin without divisions (mx is 1, 2 or 4)
+        const int jx = mb & (p.mx - 1), jy = mb >> (p.mx >> 1);
+        t.m0 += mb * kTileM;
+        t.x0 += jx * 8;
+        t.y0 += jy * 16;
+      }
+      for (int g = 0; g < n_groups; ++g, ++k) {
+        const uint32_t buf = rs.slot;
+        rs.advance(n_stg);
+        TR_WAIT(trw, named_bar_sync(kBarStgFull + buf, kBarStgThreads));
+        if (lane == 0) {
+          store_group(p, t, stg_base + buf * (kTileM * 128), n0 + g * 64);
+          tma_store_commit();
+          // all but the latest n_stg - 2 stores have read their buffers -> the buffer of store k - (n_stg - 2),
+          // which group k + 2 will fill, is free
+          const long long tq = TR_NOW();
+          if (n_stg == 2) tma_store_wait_read0();
+          else if (n_stg == 3) tma_store_wait_read1();
+          else tma_store_wait_read2();  // n_stg == 4
+          trr += TR_NOW() - tq;
+        }
+        __syncwarp();
+        if (k + 2 >= n_stg && k + 2 < total_groups) {
+          uint32_t fb = buf + 2;  // (k + 2) % n_stg
+          if (fb >= n_stg) fb -= n_stg;
+          named_bar_arrive(kBarStgEmpty + fb, kBarStgThreads);
+        }
+      }
+    }
+    if (lane == 0) trace_put<TRACE>(p, 5, it, tr0, trw, trr, TR_NOW());
+  }
+  if (lane == 0) tma_store_wait0();
+}
+
 template <int EPI, bool TRACE>
 __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -298,7 +480,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
-  if (warp == kWarpEpi0 + 12 && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpStore && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
   if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
@@ -477,132 +659,34 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         else mma_role<false, false, 1, TRACE>(p, mc);
       }
     }
+  } else if (warp == kWarpStore) {
+    if (EPI == EPI_STORE) store_role<TRACE>(p, stg_base, total_tiles, lane);
+  } else if (warp >= kWarpEpi0 && EPI == EPI_STORE) {
+    // =========================== epilogue warps 4..19: bias + SiLU + TMA store ===========================
+    const EpiCtx ec{bar0, stg_base, tmem_base, smem_u32(s_bias), total_tiles, warp - kWarpEpi0, lane};
+    if (p.act == ACT_SILU_FAST) epi_store_role<ACT_SILU_FAST, TRACE>(p, ec);
+    else if (p.act == ACT_SILU) epi_store_role<ACT_SILU, TRACE>(p, ec);
+    else epi_store_role<ACT_NONE, TRACE>(p, ec);
   } else if (warp >= kWarpEpi0) {
-    // =========================== epilogue warps 8..15 ===========================
+    // =========================== epilogue warps 4..19: Detect decode ===========================
     const uint32_t e = warp - kWarpEpi0;
     const uint32_t q = e & 3;            // TMEM lane quarter this warp may access (warp % 4)
     const uint32_t sub = e >> 2;         // which 16-column chunk of every 64-channel group (0..3)
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
     const int n_chunks = p.tile_n >> 4;
-    const int n_groups = p.groups;
-    const uint32_t n_stg = p.n_stg;
-    const bool issuer = e == 12 && lane == 0;  // the thread that issues every TMA store of this CTA
-    uint32_t v0[16];
-    bool preloaded = false;
-    Ring rs, rt;
+    Ring rt;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(p.acc_stages)) {
       int m_tile, n_idx;
       split_tile(p, tile, m_tile, n_idx);
-      const int n0 = n_idx * p.tile_n;
       const int as = rt.slot;
       const long long tr0 = TR_NOW();
-      long long trs = 0;
       mbar_wait(tfull(as), rt.phase);
       const long long tr1 = TR_NOW();
       tc_fence_after();
-      MBlock t0 = {};
-      if (EPI == EPI_STORE) t0 = mblock_coords(p, m_tile, 0);
       for (int mb = 0; mb < p.mblk; ++mb) {
         const uint32_t t_addr = tmem_base + ((q * 32u) << 16) + as * p.acc_stride + mb * p.acc_pitch;
-        if (EPI == EPI_STORE) {
-          // one 16-column chunk: bias + SiLU -> fp16 -> swizzled staging
-          auto process = [&](const uint32_t (&v)[16], int ch, uint32_t stg) {
-            const int c0 = ch << 4;
-            const float4* bp = reinterpret_cast<const float4*>(s_bias + n0 + c0);
-            float f[16];
-            if (p.act == ACT_SILU_FAST) {
-              // silu(x) = h + h * tanh(h), h = x / 2; s_bias holds bias / 2
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float4 b = bp[i];
-                const float h0 = fmaf(__uint_as_float(v[4 * i + 0]), 0.5f, b.x);
-                const float h1 = fmaf(__uint_as_float(v[4 * i + 1]), 0.5f, b.y);
-                const float h2 = fmaf(__uint_as_float(v[4 * i + 2]), 0.5f, b.z);
-                const float h3 = fmaf(__uint_as_float(v[4 * i + 3]), 0.5f, b.w);
-                f[4 * i + 0] = fmaf(h0, tanh_approx(h0), h0);
-                f[4 * i + 1] = fmaf(h1, tanh_approx(h1), h1);
-                f[4 * i + 2] = fmaf(h2, tanh_approx(h2), h2);
-                f[4 * i + 3] = fmaf(h3, tanh_approx(h3), h3);
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float4 b = bp[i];
-                f[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + b.x;
-                f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b.y;
-                f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b.z;
-                f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b.w;
-              }
-              if (p.act == ACT_SILU) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) f[i] = silu_exact(f[i]);
-              }
-            }
-            uint32_t h[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) h[i] = pack_half2(f[2 * i], f[2 * i + 1]);
-            // staging: one 64-channel group [128 rows][128 B], 16-byte chunk j of row r at j ^ (r & 7)
-            const uint32_t grp = stg + row * 128u;
-            const uint32_t j = (uint32_t)(c0 & 63) >> 3;
-            const uint32_t a0 = grp + (((j) ^ (row & 7u)) << 4);
-            const uint32_t a1 = grp + (((j + 1) ^ (row & 7u)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a0), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3])
-                         : "memory");
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7])
-                         : "memory");
-                    };
-          // Output goes out in 64-channel groups through a ring of 16 KB staging buffers.  All sixteen warps fill
-          // a group (one 16-column chunk of 32 rows each), meet at a named barrier, and one thread issues its TMA store;
-          // before the barrier that thread makes sure the store that last used the NEXT buffer has finished
-          // reading shared memory, so one barrier per group is the only synchronisation.
-          MBlock t;
-          if (p.mode == CONV_MODE_TAP) {
-            t = mblock_coords(p, m_tile, mb);
-          } else {  // derive from the tile origin without divisions (mx is 1, 2 or 4)
-            const int jx = mb & (p.mx - 1), jy = mb >> (p.mx >> 1);
-            t = t0;
-            t.m0 += mb * kTileM;
-            t.x0 += jx * 8;
-            t.y0 += jy * 16;
-          }
-          for (int g = 0; g < n_groups; ++g) {
-            const uint32_t stg = stg_base + rs.slot * (kTileM * 128);
-            rs.advance(n_stg);
-            const int chA = 4 * g + (int)sub;
-            if (!preloaded) {
-              if (chA < n_chunks) tmem_ld16(t_addr + (chA << 4), v0);
-            }
-            tmem_ld_wait();
-            const bool last_of_tile = mb == p.mblk - 1 && g == n_groups - 1;
-            if (last_of_tile) {
-              // every TMEM read of this tile is done -> the MMA warps may overwrite the accumulators
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(tempty(as));
-            }
-            if (chA < n_chunks) process(v0, chA, stg);
-            // next group's accumulators travel TMEM -> registers while this group is stored
-            preloaded = !last_of_tile;
-            if (preloaded) {
-              const bool same = g + 1 < n_groups;
-              const uint32_t ta = same ? t_addr : t_addr + p.acc_pitch;
-              const int nA = same ? chA + 4 : (int)sub;
-              if (nA < n_chunks) tmem_ld16(ta + (nA << 4), v0);
-            }
-            fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
-            if (issuer) {
-              if (n_stg == 2) tma_store_wait_read0();
-              else if (n_stg == 3) tma_store_wait_read1();
-              else tma_store_wait_read2();
-            }
-            TR_WAIT(trs, named_bar_sync(1, kEpiWarps * 32));
-            if (issuer) {
-              store_group(p, t, stg, n0 + g * 64);
-              tma_store_commit();
-            }
-          }
-        } else {
+        {
           // ---- Detect decode: row = one grid cell, columns = 3 anchors x (5 + nc)
           const MBlock t = mblock_coords(p, m_tile, mb);
           const int m = t.m0 + (int)row;
@@ -668,9 +752,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
         }
       }
-      if (e == 0 && lane == 0) trace_put<TRACE>(p, 3, it, tr0, tr1 - tr0, trs, TR_NOW());
+      if (e == 0 && lane == 0) trace_put<TRACE>(p, 3, it, tr0, tr1 - tr0, 0, TR_NOW());
     }
-    if (EPI == EPI_STORE && issuer) tma_store_wait0();
   }
 
   // teardown: everyone done with TMEM before the allocating warp frees it

@@ -44,13 +44,13 @@ enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2 };
 enum { EPI_STORE = 0, EPI_DETECT = 1 };
 enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
-constexpr int kConvThreads = 640;  // 4 role warps + 16 epilogue warps
+constexpr int kConvThreads = 672;  // 4 role warps + 16 epilogue warps + 1 store warp
 constexpr int kEpiWarps = 16;
 constexpr int kMaxA = 4;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
 constexpr int kTileM = 128;
 constexpr int kMaxCout = 768;
-constexpr int kTraceRoles = 5, kTraceTiles = 48, kTraceVals = 4;  // roles: A producer, B producer, MMA0, epilogue warp 0, store
+constexpr int kTraceRoles = 6, kTraceTiles = 48, kTraceVals = 4;  // roles: A producer, B producer, MMA0, epilogue warp 0, its parts, store warp
 constexpr int kConvMaxDynSmem = 232448 - 6144;  // 227 KB opt-in limit minus static smem (barriers, bias)
 
 struct alignas(64) ConvKParams {

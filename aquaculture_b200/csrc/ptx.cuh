@@ -222,6 +222,10 @@ __device__ __forceinline__ uint32_t pack_half2(float a, float b) {
   return r;
 }
 
+// arrive without waiting (the producer side of a named barrier); counted per warp
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

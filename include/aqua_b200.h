@@ -118,7 +118,7 @@ int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
 int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
 /* Per-role timeline of planned conv op `i` (instrumented build of the same kernel, launched once after one
- * warm-up): out[grid][5 roles][48 tiles][4] clock64 values (layout in conv_igemm.cuh); returns the grid size
+ * warm-up): out[grid][6 roles][48 tiles][4] clock64 values (layout in conv_igemm.cuh); returns the grid size
  * (CTAs) or a negative status; cap_vals = capacity of `out` in 64-bit values. */
 int aq_trace_op(aq_ctx* ctx, int i, long long* out, size_t cap_vals);
 /* Host-only planner probe (no device needed): the tiling the library would choose for one conv of the given

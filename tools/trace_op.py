@@ -33,7 +33,7 @@ print(buf.value.decode())
 ms = (C.c_float * 1)()
 ctx.call("aq_profile_ops", 10, ms, 1)
 print(f"untraced: {ms[0]*1e3:.1f} us")
-R, T, V = 5, 48, 4
+R, T, V = 6, 48, 4
 out = np.zeros(148 * R * T * V, np.int64)
 grid = ctx.call("aq_trace_op", 0, out.ctypes.data, out.size)
 tr = out[:grid * R * T * V].reshape(grid, R, T, V)
@@ -50,13 +50,18 @@ for cta in [int(x) for x in a.cta.split(",") if int(x) < grid]:
     Bp = t[1, lo:hi]
     if Bp[:, 0].any(): print(f"  B-prod : busy {np.mean(Bp[:,3]-Bp[:,0]):7.0f}  wait b_empty {np.mean(Bp[:,1]):7.0f}")
     M = t[2, lo:hi]; print(f"  MMA0   : busy {np.mean(M[:,3]-M[:,0]):7.0f}  wait tempty {np.mean(M[:,1]):7.0f}  wait a_full {np.mean(M[:,2]>>32):7.0f}  wait b_full {np.mean(M[:,2]&0xffffffff):7.0f}")
-    E = t[3, lo:hi]; print(f"  EPI0   : busy {np.mean(E[:,3]-E[:,0]):7.0f}  wait tfull {np.mean(E[:,1]):7.0f}  wait stg_empty {np.mean(E[:,2]):7.0f}  work {np.mean(E[:,3]-E[:,0]-E[:,1]-E[:,2]):7.0f}")
+    E = t[3, lo:hi]; print(f"  EPI0   : busy {np.mean(E[:,3]-E[:,0]):7.0f}  wait tfull {np.mean(E[:,1]):7.0f}  wait barrier {np.mean(E[:,2]):7.0f}  work {np.mean(E[:,3]-E[:,0]-E[:,1]-E[:,2]):7.0f}")
     S = t[4, lo:hi]
-    if S[:, 0].any(): print(f"  STORE  : busy {np.mean(S[:,3]-S[:,0]):7.0f}  wait stg_full {np.mean(S[:,1]):7.0f}  wait smem read {np.mean(S[:,2]):7.0f}")
+    if S[:, 0].any():
+        lo32 = lambda x: np.mean(x & 0xffffffff); hi32 = lambda x: np.mean(x >> 32)
+        print(f"  EPI0 parts/tile: top->ld {lo32(S[:,0]):5.0f} | ld wait {hi32(S[:,0]):5.0f} | tempty arrive {lo32(S[:,1]):5.0f} | process {hi32(S[:,1]):5.0f} | "
+              f"prefetch {lo32(S[:,2]):5.0f} | fence+rdwait {hi32(S[:,2]):5.0f} | arrive {lo32(S[:,3]):5.0f}")
+    ST = t[5, lo:hi]
+    if ST[:, 0].any(): print(f"  STORE  : busy {np.mean(ST[:,3]-ST[:,0]):7.0f}  wait staged group {np.mean(ST[:,1]):7.0f}  wait smem read {np.mean(ST[:,2]):7.0f}")
     if a.tiles and cta == int(a.cta.split(",")[0]):
         t0 = t[2, 0, 0]
         for i in range(min(n, a.tiles)):
             print(f"   tile {i:2d}: A {t[0,i,0]-t0:7d}..{t[0,i,3]-t0:7d} (w {t[0,i,1]:6d} d {t[0,i,2]:6d}) | B {t[1,i,0]-t0:7d}..{t[1,i,3]-t0:7d} (w {t[1,i,1]:6d}) | "
                   f"MMA {t[2,i,0]-t0:7d}..{t[2,i,3]-t0:7d} (te {t[2,i,1]:6d} a {t[2,i,2]>>32:6d} b {t[2,i,2]&0xffffffff:6d}) | "
-                  f"EPI {t[3,i,0]-t0:7d}..{t[3,i,3]-t0:7d} (tf {t[3,i,1]:6d} se {t[3,i,2]:6d}) | ST {t[4,i,0]-t0:7d}..{t[4,i,3]-t0:7d} (sf {t[4,i,1]:6d} rd {t[4,i,2]:6d})")
+                  f"EPI {t[3,i,0]-t0:7d}..{t[3,i,3]-t0:7d} (tf {t[3,i,1]:6d} se {t[3,i,2]:6d})")
 ctx.close()

@@ -66,6 +66,7 @@ struct aq_ctx {
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
   int pdl = 1;  // programmatic dependent launch between conv kernels (AQUA_PDL=0 disables)
+  int autotune = 1;  // time every feasible tiling of each conv at plan time and keep the fastest (AQUA_AUTOTUNE=0: cost model)
   // preprocess state
   uint8_t* stage_u8 = nullptr;
   size_t stage_bytes = 0;
@@ -251,8 +252,10 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   cd.ok = true;
 }
 
-// Fill everything of ConvKParams except device pointers / tensor maps.
-int plan_conv_geometry(aq_ctx* c, Op& op) {
+// Fill everything of ConvKParams except device pointers / tensor maps.  The feasible tilings (UMMA N x A-feed
+// mode x M blocks per tile) are enumerated; `choice` < 0 takes the one the cost model ranks first, otherwise the
+// choice-th one (plan-time autotuning times them all on the device).  *n_choices receives their number.
+int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = nullptr) {
   const bool det = op.kind == OP_DETECT;
   ConvKParams& k = op.kp;
   memset(&k, 0, sizeof k);
@@ -272,24 +275,21 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
   k.c_in = c_in;
   k.cpt = (c_in + 63) / 64;
   k.n_steps = k.taps * k.cpt;
+  // ---- UMMA N options
+  std::vector<int> tile_ns;
   if (det) {
-    k.tile_n = round_up(c_out, 16);
-    k.n_tiles_n = 1;
+    tile_ns.push_back(round_up(c_out, 16));
   } else if (op.conv.tile_n > 0) {
-    k.tile_n = op.conv.tile_n;
-    k.n_tiles_n = (c_out + k.tile_n - 1) / k.tile_n;
+    tile_ns.push_back(op.conv.tile_n);
   } else if (c_out <= 256) {
-    k.tile_n = round_up(c_out, 16);
-    k.n_tiles_n = 1;
+    tile_ns.push_back(round_up(c_out, 16));
   } else {
-    k.tile_n = largest_divisor_tile_n(c_out);
-    k.n_tiles_n = k.tile_n > 0 ? c_out / k.tile_n : 0;
+    for (int n = 256; n >= 128; n -= 16)
+      if (c_out % n == 0) tile_ns.push_back(n);
+    if (tile_ns.empty()) tile_ns.push_back(largest_divisor_tile_n(c_out));
   }
-  if (k.tile_n <= 0 || k.tile_n > 256 || k.tile_n % 16 || k.n_tiles_n * k.tile_n > kMaxCout)
-    return fail(c, AQ_ERR_UNSUPPORTED, "conv c_out %d has no valid UMMA N tile (got %d)", c_out, k.tile_n);
-  k.groups = (k.tile_n + 63) / 64;
-  // ---- candidates
-  std::vector<Cand> cands;
+  // ---- A-feed candidates
+  std::vector<Cand> shapes;
   const int want_mblk = det ? 0 : op.conv.mblk;
   const int want_mode = det ? 0 : op.conv.mode;  // 0 auto, 1 halo, 2 tap (3x3/s1 only)
   if (ksize == 1) {
@@ -297,7 +297,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
       Cand cd;
       cd.mode = CONV_MODE_FLAT;
       cd.mblk = mb;
-      cands.push_back(cd);
+      shapes.push_back(cd);
     }
   } else {
     if (stride == 1 && want_mode != 2) {
@@ -308,7 +308,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
         cd.mx = a[0];
         cd.my = a[1];
         cd.mblk = a[0] * a[1];
-        cands.push_back(cd);
+        shapes.push_back(cd);
       }
     }
     if (stride == 2 || want_mode != 1) {
@@ -317,17 +317,36 @@ int plan_conv_geometry(aq_ctx* c, Op& op) {
         cd.mode = CONV_MODE_TAP;
         cd.mblk = mb;
         pick_spatial_tile(ho, wo, &cd.tw, &cd.th);
-        cands.push_back(cd);
+        shapes.push_back(cd);
       }
     }
   }
-  Cand best;
-  for (auto& cd : cands) {
-    if (want_mblk > 0 && cd.mblk != want_mblk) continue;
-    fill_candidate(cd, c->batch, ho, wo, k.tile_n, k.n_tiles_n, k.n_steps, k.cpt, c->num_sms);
-    if (cd.ok && cd.cycles < best.cycles) best = cd;
+  struct Choice { int tile_n, n_tiles_n; Cand cd; };
+  std::vector<Choice> choices;
+  for (int tn : tile_ns) {
+    if (tn <= 0 || tn > 256 || tn % 16) continue;
+    const int ntn = (c_out + tn - 1) / tn;
+    if (ntn * tn > kMaxCout) continue;
+    for (Cand cd : shapes) {
+      if (want_mblk > 0 && cd.mblk != want_mblk) continue;
+      fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+      if (cd.ok) choices.push_back({tn, ntn, cd});
+    }
   }
-  if (!best.ok) return fail(c, AQ_ERR_UNSUPPORTED, "conv %dx%d c_in %d c_out %d: no tiling fits shared memory / TMEM", ksize, ksize, c_in, c_out);
+  if (n_choices) *n_choices = (int)choices.size();
+  if (choices.empty())
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv %dx%d c_in %d c_out %d: no tiling fits shared memory / TMEM (UMMA N must be a multiple of 16 <= 256)", ksize, ksize, c_in, c_out);
+  int pick = choice;
+  if (pick < 0) {
+    pick = 0;
+    for (int i = 1; i < (int)choices.size(); ++i)
+      if (choices[i].cd.cycles < choices[pick].cd.cycles) pick = i;
+  }
+  if (pick >= (int)choices.size()) return fail(c, AQ_ERR_ARG, "conv tiling choice %d out of range", pick);
+  const Cand best = choices[pick].cd;
+  k.tile_n = choices[pick].tile_n;
+  k.n_tiles_n = choices[pick].n_tiles_n;
+  k.groups = (k.tile_n + 63) / 64;
   k.mode = best.mode;
   k.mblk = best.mblk;
   k.mx = best.mx;
@@ -446,6 +465,45 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     rc = encode_map(c, &k.tmOutR[hb], db.ptr + op.conv.dst_c_off, 4, dims, str, bx, sw);
   }
   return rc;
+}
+
+// Plan-time autotuning: launch every feasible tiling of this conv on its real buffers (1 warm-up + 3 timed
+// launches, CUDA events on the context stream) and keep the fastest.  The cost model only orders the search.
+int autotune_conv(aq_ctx* c, Op& op) {
+  int n = 0;
+  int rc = plan_conv_geometry(c, op, -1, &n);
+  if (rc) return rc;
+  if (n <= 1) return plan_conv_maps(c, op);
+  const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
+  cudaEvent_t e0, e1;
+  CU_CHECK(c, cudaEventCreate(&e0));
+  CU_CHECK(c, cudaEventCreate(&e1));
+  float best_ms = 1e30f;
+  int best = -1;
+  for (int i = 0; i < n; ++i) {
+    if (plan_conv_geometry(c, op, i) || plan_conv_maps(c, op)) continue;
+    cudaError_t e = launch_conv(op.kp, epi, c->num_sms, 0, c->stream);
+    cudaEventRecord(e0, c->stream);
+    for (int r = 0; r < 3 && e == cudaSuccess; ++r) e = launch_conv(op.kp, epi, c->num_sms, 0, c->stream);
+    cudaEventRecord(e1, c->stream);
+    if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+    if (e != cudaSuccess) {
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+      return fail(c, AQ_ERR_CUDA, "autotune: tiling %d of a conv failed: %s", i, cudaGetErrorString(e));
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (ms < best_ms) {
+      best_ms = ms;
+      best = i;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (best < 0) return fail(c, AQ_ERR_UNSUPPORTED, "autotune: no tiling could be planned");
+  if ((rc = plan_conv_geometry(c, op, best))) return rc;
+  return plan_conv_maps(c, op);
 }
 
 // [c_out][taps][c_in] fp16 -> [c_out][taps][cpt * 64] with zero padding (so a 64-wide K chunk never straddles taps)
@@ -627,6 +685,7 @@ int aq_create(int device, aq_ctx** out) {
   }
   c->encode = (EncodeTiledFn)fn;
   if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
   const char* what = "stream";
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (what = "conv smem attr", e = conv_kernels_init()) != cudaSuccess ||
@@ -775,16 +834,20 @@ int aq_plan_end(aq_ctx* c) {
     // weights: rows padded up to n_tiles_n * tile_n are handled by TMA OOB fill; bias is padded here
     CU_CHECK(c, cudaMalloc(&op.w_dev, op.w_host.size() * sizeof(uint16_t)));
     CU_CHECK(c, cudaMemcpyAsync(op.w_dev, op.w_host.data(), op.w_host.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
-    std::vector<float> bias((size_t)k.n_tiles_n * k.tile_n, 0.f);
+    std::vector<float> bias((size_t)kMaxCout, 0.f);  // padded to the largest N any tiling may read
     memcpy(bias.data(), op.b_host.data(), op.b_host.size() * sizeof(float));
     if (k.act == ACT_SILU_FAST)  // the kernel evaluates silu(x) = h + h * tanh(h) with h = acc / 2 + bias / 2
       for (auto& b : bias) b *= 0.5f;
     CU_CHECK(c, cudaMalloc(&op.b_dev, bias.size() * sizeof(float)));
     CU_CHECK(c, cudaMemcpy(op.b_dev, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
     CU_CHECK(c, cudaStreamSynchronize(c->stream));
-    int rc = plan_conv_maps(c, op);
+    int rc = c->autotune ? autotune_conv(c, op) : plan_conv_maps(c, op);
     if (rc) return rc;
     std::vector<uint16_t>().swap(op.w_host);
+  }
+  if (c->autotune) {  // the timing launches wrote into the activation buffers
+    for (auto& b : c->bufs) CU_CHECK(c, cudaMemsetAsync(b.ptr, 0, (size_t)c->batch * b.h * b.w * b.c * sizeof(__half), c->stream));
+    CU_CHECK(c, cudaMemsetAsync(c->pred, 0, (size_t)c->batch * c->rows * c->no * sizeof(float), c->stream));
   }
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
   c->n_launches = launches;

@@ -66,6 +66,7 @@ SIGNATURES = {
     "aq_detect_submit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                    C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p,
                                    C.c_void_p]),
+    "aq_detect_wait": (C.c_int, [C.c_void_p, C.c_int]),
     "aq_format_labels": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                    C.POINTER(C.c_char_p), C.c_int, C.c_int]),
     "aq_format_label_text": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,

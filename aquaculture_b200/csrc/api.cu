@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <map>
 #include <string>
 #include <vector>
 
@@ -67,9 +68,20 @@ struct aq_ctx {
   int n_launches = 0;
   int pdl = 1;  // programmatic dependent launch between conv kernels (AQUA_PDL=0 disables)
   int autotune = 1;  // time every feasible tiling of each conv at plan time and keep the fastest (AQUA_AUTOTUNE=0: cost model)
-  // preprocess state
-  uint8_t* stage_u8 = nullptr;
-  size_t stage_bytes = 0;
+  // AQUA_TUNE_CACHE=<file>: tilings chosen by an earlier run are replayed instead of re-timed (one "signature choice"
+  // line per conv); new measurements are appended.  Lets a profiler pass see the step, not the tuning launches.
+  std::string tune_path;
+  std::map<std::string, int> tune_cache;
+  // preprocess state: host tiles are staged through two device buffers filled on a dedicated copy stream, so the
+  // H2D copy of batch i+1 overlaps the kernels of batch i (aq_detect_submit / aq_detect_wait)
+  uint8_t* stage_u8[2] = {nullptr, nullptr};
+  size_t stage_bytes[2] = {0, 0};
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_h2d[2] = {nullptr, nullptr};    // staging buffer filled (copy stream)
+  cudaEvent_t ev_pre[2] = {nullptr, nullptr};    // staging buffer consumed by the preprocess kernel (compute stream)
+  cudaEvent_t ev_done[2] = {nullptr, nullptr};   // detections of the batch are in host memory (compute stream)
+  bool pre_recorded[2] = {false, false};
+  int pipe_slot = 0;
   int tab_in_h = -1, tab_in_w = -1;
   void* tab_dev = nullptr;
   PreParams pre{};
@@ -469,11 +481,32 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
 
 // Plan-time autotuning: launch every feasible tiling of this conv on its real buffers (1 warm-up + 3 timed
 // launches, CUDA events on the context stream) and keep the fastest.  The cost model only orders the search.
+std::string tune_signature(const aq_ctx* c, const Op& op, int n) {
+  char b[256];
+  if (op.kind == OP_DETECT) {
+    const Buffer& sb = c->bufs[op.det.src];
+    snprintf(b, sizeof b, "det:b%d:%dx%d:ct%d:ci%d:nc%d:n%d", c->batch, sb.h, sb.w, sb.c, op.det.c_in, op.det.nc, n);
+  } else {
+    const Buffer& sb = c->bufs[op.conv.src];
+    const Buffer& db = c->bufs[op.conv.dst];
+    snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", c->batch, sb.h, sb.w, sb.c,
+             op.conv.c_in, op.conv.c_out, db.c, op.conv.k, op.conv.stride, op.conv.act, op.conv.res >= 0 ? 1 : 0,
+             op.conv.tile_n, op.conv.mblk, op.conv.mode, n);
+  }
+  return b;
+}
+
 int autotune_conv(aq_ctx* c, Op& op) {
   int n = 0;
   int rc = plan_conv_geometry(c, op, -1, &n);
   if (rc) return rc;
   if (n <= 1) return plan_conv_maps(c, op);
+  const std::string sig = tune_signature(c, op, n);
+  {
+    auto it = c->tune_cache.find(sig);
+    if (it != c->tune_cache.end() && it->second >= 0 && it->second < n && !plan_conv_geometry(c, op, it->second))
+      return plan_conv_maps(c, op);
+  }
   const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
   cudaEvent_t e0, e1;
   CU_CHECK(c, cudaEventCreate(&e0));
@@ -502,6 +535,12 @@ int autotune_conv(aq_ctx* c, Op& op) {
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (best < 0) return fail(c, AQ_ERR_UNSUPPORTED, "autotune: no tiling could be planned");
+  c->tune_cache[sig] = best;
+  if (!c->tune_path.empty())
+    if (FILE* f = fopen(c->tune_path.c_str(), "a")) {
+      fprintf(f, "%s %d\n", sig.c_str(), best);
+      fclose(f);
+    }
   if ((rc = plan_conv_geometry(c, op, best))) return rc;
   return plan_conv_maps(c, op);
 }
@@ -633,23 +672,44 @@ int setup_preprocess(aq_ctx* c, int in_h, int in_w) {
   return AQ_OK;
 }
 
+// Host tiles -> staging buffer `slot` on the copy stream; stream `s` (the compute stream) is made to wait for the
+// copy.  The copy itself waits until the preprocess kernel that last read this staging buffer has finished.
+cudaError_t create_pipe_events(aq_ctx* c) {
+  cudaError_t e = cudaSuccess;
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+    e = cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_pre[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+  }
+  return e;
+}
+
 int stage_tiles(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int src_is_device, cudaStream_t s,
-                const uint8_t** dev_out) {
+                int slot, const uint8_t** dev_out) {
   if (src_is_device) {
     *dev_out = tiles;
     return AQ_OK;
   }
   const size_t bytes = (size_t)n * in_h * in_w * 3;
-  if (bytes > c->stage_bytes) {
-    if (c->stage_u8) cudaFree(c->stage_u8);
-    c->stage_u8 = nullptr;
-    CU_CHECK(c, cudaMalloc(&c->stage_u8, bytes));
-    c->stage_bytes = bytes;
+  if (bytes > c->stage_bytes[slot]) {
+    if (c->stage_u8[slot]) {
+      CU_CHECK(c, cudaDeviceSynchronize());
+      cudaFree(c->stage_u8[slot]);
+    }
+    c->stage_u8[slot] = nullptr;
+    CU_CHECK(c, cudaMalloc(&c->stage_u8[slot], bytes));
+    c->stage_bytes[slot] = bytes;
   }
-  CU_CHECK(c, cudaMemcpyAsync(c->stage_u8, tiles, bytes, cudaMemcpyHostToDevice, s));
-  *dev_out = c->stage_u8;
+  if (c->pre_recorded[slot]) CU_CHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_pre[slot], 0));
+  CU_CHECK(c, cudaMemcpyAsync(c->stage_u8[slot], tiles, bytes, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaEventRecord(c->ev_h2d[slot], c->copy_stream));
+  CU_CHECK(c, cudaStreamWaitEvent(s, c->ev_h2d[slot], 0));
+  *dev_out = c->stage_u8[slot];
   return AQ_OK;
 }
+
+int preprocess_slot(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device, int slot,
+                    cudaStream_t s);
 
 }  // namespace
 
@@ -686,8 +746,19 @@ int aq_create(int device, aq_ctx** out) {
   c->encode = (EncodeTiledFn)fn;
   if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
   if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_TUNE_CACHE")) {
+    c->tune_path = v;
+    if (FILE* f = fopen(v, "r")) {
+      char sig[256];
+      int choice;
+      while (fscanf(f, "%255s %d", sig, &choice) == 2) c->tune_cache[sig] = choice;
+      fclose(f);
+    }
+  }
   const char* what = "stream";
   if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (what = "copy stream", e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (what = "events", e = create_pipe_events(c)) != cudaSuccess ||
       (what = "conv smem attr", e = conv_kernels_init()) != cudaSuccess ||
       (what = "nms smem attr", e = nms_init()) != cudaSuccess ||
       (what = "sppf smem attr", e = sppf_init()) != cudaSuccess) {
@@ -703,7 +774,13 @@ void aq_destroy(aq_ctx* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   free_plan(c);
-  if (c->stage_u8) cudaFree(c->stage_u8);
+  for (int i = 0; i < 2; ++i) {
+    if (c->stage_u8[i]) cudaFree(c->stage_u8[i]);
+    if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
+    if (c->ev_pre[i]) cudaEventDestroy(c->ev_pre[i]);
+    if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+  }
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->tab_dev) cudaFree(c->tab_dev);
   if (c->nms_scratch) cudaFree(c->nms_scratch);
   if (c->nms_dets) cudaFree(c->nms_dets);
@@ -1006,9 +1083,16 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
 
 int aq_preprocess(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device, void* stream) {
   if (!c || !tiles) return AQ_ERR_ARG;
+  return preprocess_slot(c, tiles, n, in_h, in_w, bgr, src_is_device, 0, stream ? (cudaStream_t)stream : c->stream);
+}
+
+}  // extern "C"
+
+namespace {
+int preprocess_slot(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device, int slot,
+                    cudaStream_t s) {
   if (!c->planned) return fail(c, AQ_ERR_STATE, "preprocess before plan_end");
   if (n <= 0 || n > c->batch) return fail(c, AQ_ERR_ARG, "preprocess: n %d outside plan batch %d", n, c->batch);
-  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   cudaSetDevice(c->device);
   const Buffer& b0 = c->bufs[0];
   if (b0.h != c->net_h / 2 || b0.w != c->net_w / 2 || b0.c != 16)
@@ -1016,12 +1100,19 @@ int aq_preprocess(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, in
   int rc = setup_preprocess(c, in_h, in_w);
   if (rc) return rc;
   const uint8_t* dev = nullptr;
-  if ((rc = stage_tiles(c, tiles, n, in_h, in_w, src_is_device, s, &dev))) return rc;
+  if ((rc = stage_tiles(c, tiles, n, in_h, in_w, src_is_device, s, slot, &dev))) return rc;
   PreParams p = c->pre;
   p.src = dev; p.n = n; p.bgr = bgr; p.out_s2d = b0.ptr; p.out_u8 = nullptr;
   CU_CHECK(c, launch_preprocess(p, s));
+  if (!src_is_device) {
+    CU_CHECK(c, cudaEventRecord(c->ev_pre[slot], s));
+    c->pre_recorded[slot] = true;
+  }
   return AQ_OK;
 }
+}  // namespace
+
+extern "C" {
 
 int aq_preprocess_u8(aq_ctx* c, const uint8_t* tiles_dev, int n, int in_h, int in_w, int bgr, uint8_t* out_dev, void* stream) {
   if (!c || !tiles_dev || !out_dev) return AQ_ERR_ARG;
@@ -1095,9 +1186,11 @@ int aq_nms(aq_ctx* c, const float* pred, int batch, int rows, int no, float conf
 int aq_detect_submit(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device,
                      float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes, int n_classes,
                      float* dets_host, int* counts_host, void* stream) {
-  if (!c || !dets_host || !counts_host) return AQ_ERR_ARG;
+  if (!c || !tiles || !dets_host || !counts_host) return AQ_ERR_ARG;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
-  int rc = aq_preprocess(c, tiles, n, in_h, in_w, bgr, src_is_device, s);
+  const int slot = c->pipe_slot;
+  c->pipe_slot ^= 1;
+  int rc = preprocess_slot(c, tiles, n, in_h, in_w, bgr, src_is_device, slot, s);
   if (rc) return rc;
   if ((rc = aq_forward(c, s))) return rc;
   const size_t cap = (size_t)c->batch * max_det;
@@ -1114,6 +1207,14 @@ int aq_detect_submit(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w,
     return rc;
   CU_CHECK(c, cudaMemcpyAsync(counts_host, c->nms_counts, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaMemcpyAsync(dets_host, c->nms_dets, (size_t)n * max_det * 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CU_CHECK(c, cudaEventRecord(c->ev_done[slot], s));
+  return slot;  // ticket for aq_detect_wait
+}
+
+int aq_detect_wait(aq_ctx* c, int ticket) {
+  if (!c || ticket < 0 || ticket > 1) return AQ_ERR_ARG;
+  cudaSetDevice(c->device);
+  CU_CHECK(c, cudaEventSynchronize(c->ev_done[ticket]));
   return AQ_OK;
 }
 
@@ -1122,7 +1223,7 @@ int aq_detect(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bg
               int* counts_host, void* stream) {
   int rc = aq_detect_submit(c, tiles, n, in_h, in_w, bgr, src_is_device, conf_thres, iou_thres, max_det, agnostic,
                             classes, n_classes, dets_host, counts_host, stream);
-  if (rc) return rc;
+  if (rc < 0) return rc;
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   CU_CHECK(c, cudaStreamSynchronize(s));
   return AQ_OK;

@@ -228,27 +228,39 @@ def run(opt, argv) -> int:
     pos = 0
     pending = {}  # (h0, w0) -> list of (image, stem)
 
-    def flush(shape0, group):
+    deferred = []  # the batch in flight: (detector, ticket, group, shape0, net_hw)
+
+    def finish():
         nonlocal seen, n_files, n_dets
-        h0, w0 = shape0
-        net_hw = net_shape_for(h0, w0, imgsz)
-        det = detector_for(net_hw)
-        t0 = time.perf_counter()
-        batch = torch.from_numpy(np.stack([g[0] for g in group]))
+        if not deferred:
+            return
+        det, ticket, group, shape0, net_hw = deferred.pop()
         t1 = time.perf_counter()
-        res = det.detect(batch, bgr=True)
+        res = det.detect_wait(ticket)
         if opt.save_txt:
             paths = [str(label_dir / (g[1] + ".txt")) for g in group]
             n_files += engine.write_labels(res, net_hw, [shape0] * len(group), paths, save_conf=opt.save_conf,
                                            threads=opt.io_threads)
-        t2 = time.perf_counter()
-        dt[0] += t1 - t0
-        dt[1] += t2 - t1
+        dt[1] += time.perf_counter() - t1
         seen += len(group)
         n_dets += int(res.counts.sum())
         if opt.verbose:
             for g, c in zip(group, res.counts):
                 print(f"image {g[1]}: {net_hw[0]}x{net_hw[1]} {int(c)} detections")
+
+    def flush(shape0, group):
+        # two-deep pipeline: this batch is submitted (H2D on the copy stream + kernels) before the previous one is
+        # waited for, so image decoding / label writing on the host overlap the GPU
+        h0, w0 = shape0
+        net_hw = net_shape_for(h0, w0, imgsz)
+        det = detector_for(net_hw)
+        t0 = time.perf_counter()
+        batch = det.pinned_input(len(group), h0, w0)
+        np.stack([g[0] for g in group], out=batch.numpy())
+        dt[0] += time.perf_counter() - t0
+        ticket = det.detect_submit(batch, bgr=True)
+        finish()
+        deferred.append((det, ticket, [(None, g[1]) for g in group], shape0, net_hw))
 
     while pos < len(items):
         chunk = items[pos:pos + B]
@@ -263,6 +275,7 @@ def run(opt, argv) -> int:
         pos += B
     for key in list(pending):
         flush(key, pending.pop(key))
+    finish()
     for d in detectors.values():
         d.close()
     wall = time.perf_counter() - t_start

@@ -183,6 +183,8 @@ class TileDetector:
         self._build(state_dict)
         self._dets = self._counts = None  # pinned host staging, double-buffered, allocated on first use
         self._slot = 0
+        self._inflight = [None, None]
+        self._pin, self._pin_i = {}, {}
 
     # ------------------------------------------------------------------ plan
     def _build(self, sd):
@@ -268,8 +270,10 @@ class TileDetector:
 
     # ------------------------------------------------------------------ run
     def detect_submit(self, tiles, bgr=True, src_is_device=False, stream=None):
-        """Enqueue one batch.  tiles: uint8 (n, h, w, 3) torch tensor (pinned host, or cuda).  Returns the slot
-        holding the pinned results; call `detect_wait` before reading them."""
+        """Enqueue one batch.  tiles: uint8 (n, h, w, 3) torch tensor (pinned host, or cuda).  Returns a ticket;
+        `detect_wait(ticket)` blocks until that batch's detections are in pinned host memory.  Two batches may be
+        in flight: the H2D copy of the second overlaps the kernels of the first (the tiles tensor of a batch must
+        stay alive and unmodified until its ticket has been waited for)."""
         n, h, w, _ = tiles.shape
         assert n <= self.batch and tiles.dtype == torch.uint8 and tiles.is_contiguous()
         if self._dets is None:
@@ -278,15 +282,29 @@ class TileDetector:
         slot = self._slot
         self._slot ^= 1
         cls_arr = (C.c_int * len(self.classes))(*self.classes) if self.classes else None
-        self.ctx.call("aq_detect_submit", C.c_void_p(tiles.data_ptr()), n, h, w, int(bgr), int(src_is_device),
-                      self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
-                      len(self.classes) if self.classes else 0, C.c_void_p(self._dets[slot].data_ptr()),
-                      C.c_void_p(self._counts[slot].data_ptr()), stream)
-        return slot, n
+        ticket = self.ctx.call("aq_detect_submit", C.c_void_p(tiles.data_ptr()), n, h, w, int(bgr), int(src_is_device),
+                               self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
+                               len(self.classes) if self.classes else 0, C.c_void_p(self._dets[slot].data_ptr()),
+                               C.c_void_p(self._counts[slot].data_ptr()), stream)
+        self._inflight[slot] = tiles  # keeps the source alive while the copy stream may still read it
+        return slot, n, ticket
 
-    def detect_wait(self, slot_n, stream=None) -> Detections:
-        slot, n = slot_n
-        self.ctx.call("aq_sync", stream)
+    def pinned_input(self, n, h, w) -> torch.Tensor:
+        """One of two alternating pinned uint8 (n, h, w, 3) host buffers for `detect_submit` (a buffer is reused
+        every second call, i.e. after its batch has been waited for in a two-deep pipeline)."""
+        key = (h, w)
+        if self._pin.get(key) is None:
+            self._pin[key] = [torch.empty(self.batch, h, w, 3, dtype=torch.uint8).pin_memory() for _ in range(2)]
+            self._pin_i[key] = 0
+        i = self._pin_i[key]
+        self._pin_i[key] = i ^ 1
+        return self._pin[key][i][:n]
+
+    def detect_wait(self, ticket, stream=None) -> Detections:
+        """Results of one submitted batch (views of the pinned slot: copy them before the slot's next submit)."""
+        slot, n, t = ticket
+        self.ctx.call("aq_detect_wait", t)
+        self._inflight[slot] = None
         return Detections(self._dets[slot][:n].numpy(), self._counts[slot][:n].numpy())
 
     def detect(self, tiles, bgr=True, src_is_device=False) -> Detections:

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define AQ_ABI_VERSION 2
+#define AQ_ABI_VERSION 3
 
 typedef enum aq_status {
   AQ_OK = 0,
@@ -161,11 +161,16 @@ int aq_nms(aq_ctx* ctx, const float* pred, int batch, int rows, int no, float co
 int aq_detect(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device,
               float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
               int n_classes, float* dets_host, int* counts_host, void* stream);
-/* Asynchronous halves of aq_detect for double-buffered pipelines: submit enqueues everything on `stream`
- * including the D2H copies and returns; the caller synchronises the stream (or an event) itself. */
+/* Asynchronous halves of aq_detect for double-buffered pipelines.  aq_detect_submit enqueues the whole batch
+ * (kernels and the D2H copies on `stream`; for host tiles the H2D copy goes through one of two staging buffers on
+ * the library's own copy stream, so the copy of batch i+1 overlaps the kernels of batch i) and returns a ticket
+ * (0 or 1, alternating; negative = aq_status error).  aq_detect_wait blocks until the batch of that ticket has
+ * its detections in dets_host / counts_host.  At most two batches may be in flight; each needs its own
+ * dets_host / counts_host, and the host tiles of a batch must stay valid until its ticket has been waited for. */
 int aq_detect_submit(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_w, int bgr,
                      int src_is_device, float conf_thres, double iou_thres, int max_det, int agnostic,
                      const int* classes, int n_classes, float* dets_host, int* counts_host, void* stream);
+int aq_detect_wait(aq_ctx* ctx, int ticket);
 
 /* ------------------------------------------------------------------ host-side label epilogue (no GPU) */
 /*

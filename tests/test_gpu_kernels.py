@@ -379,6 +379,39 @@ def test_e2e_tiles_vs_oracle(synthetic_sd, in_hw):
     assert n_unmatched <= max(2, n_ref_total // 20), f"{n_unmatched} unmatched of {n_ref_total}"
 
 
+def test_e2e_two_batches_in_flight(synthetic_sd):
+    """aq_detect_submit / aq_detect_wait: batch i+1 submitted (H2D on the copy stream, staging buffer i+1 mod 2)
+    before batch i is waited for gives the same detections as one batch at a time."""
+    from aquaculture_b200 import tiles as T
+    B, NB = 3, 5
+    imgs = [T.synthetic_tiles(range(10 * k, 10 * k + B), 1024, 1024, seed=1) for k in range(NB)]
+    det = engine.TileDetector(synthetic_sd, 3, batch=B, imgsz=(640, 640))
+    try:
+        seq = []
+        for k in range(NB):
+            r = det.detect(torch.from_numpy(imgs[k]).pin_memory(), bgr=True)
+            seq.append((r.dets.copy(), r.counts.copy()))
+        pipe = []
+        bufs = []
+        for k in range(NB):
+            b = det.pinned_input(B, 1024, 1024)
+            b.numpy()[...] = imgs[k]
+            bufs.append(det.detect_submit(b, bgr=True))
+            if k >= 1:
+                r = det.detect_wait(bufs[k - 1])
+                pipe.append((r.dets.copy(), r.counts.copy()))
+        r = det.detect_wait(bufs[-1])
+        pipe.append((r.dets.copy(), r.counts.copy()))
+    finally:
+        det.close()
+    assert sum(int(c.sum()) for _, c in seq) > 0
+    for k in range(NB):
+        assert np.array_equal(seq[k][1], pipe[k][1]), f"batch {k}: counts differ"
+        for i in range(B):
+            n = int(seq[k][1][i])
+            assert np.array_equal(seq[k][0][i, :n], pipe[k][0][i, :n]), f"batch {k} tile {i}: detections differ"
+
+
 def test_label_files_match_oracle(synthetic_sd, tmp_path):
     from aquaculture_b200 import tiles as T
     from oracle import labels as OL

@@ -8,10 +8,12 @@ timeout 600 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_$TAG.json 2
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_$TAG.json 2>> gpurun_out/bench_$TAG.err; cat gpurun_out/bench_ref_$TAG.json
 timeout 300 python tools/profile_ops.py --out gpurun_out/ops_$TAG.txt > /dev/null 2> gpurun_out/ops_$TAG.err; tail -1 gpurun_out/ops_$TAG.txt
 if [ -z "$NO_NCU" ]; then
+export AQUA_TUNE_CACHE=gpurun_out/tune_$TAG.txt   # the ncu pass replays the plain run's tilings: no tuning launches in the list
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain_$TAG.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/launches_$TAG.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch_$TAG.log 2>&1
 echo "ncu launches exit=$?"
+unset AQUA_TUNE_CACHE
 for shp in "64 80 80 96 96 3 1" "64 160 160 48 48 3 1"; do
   n=$(echo $shp | tr ' ' '_')
   timeout 120 python tools/one_op.py $shp > gpurun_out/oneop_${n}_$TAG.log 2>&1 &&

@@ -176,6 +176,7 @@ int pow2_at_least(int v) {
 // One candidate tiling of a conv; fill_candidate() completes the shared-memory / TMEM plan and the cost.
 struct Cand {
   int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
+  int cluster = 1;  // CTAs per thread-block cluster sharing each weight tile by multicast (1, 2, 4)
   // derived
   int tiles_x = 1, tiles_y = 1, m_tiles = 0, pw = 0, ph = 0;
   int na = 0, nb = 0, b_res = 0, n_stg = 0, acc_stages = 0;
@@ -246,7 +247,8 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   // ---- cost
   const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
   const double a_bytes = (double)n_groups * cd.a_tx;
-  const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0;
+  if (cd.cluster > 1 && (cd.b_res || (tile_n / cd.cluster) % 8 || num_sms / cd.cluster < 1)) return;  // nothing to share / swizzle atom split
+  const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0 / cd.cluster;
   const double o_bytes = (double)cd.mblk * kTileM * tile_n * 2.0;
   const double l2 = (a_bytes + b_bytes + o_bytes) / 40.0;
   // TMA: one producer thread per operand, ~600 clk per box and ~4500 clk latency per ring slot; the HALO
@@ -258,9 +260,10 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   const double epi = (double)cd.mblk * tile_n * 8.0 + 400.0;
   double tile_cyc = fmax(fmax(mma, l2), fmax(issue, epi)) + 300.0;
   if (cd.acc_stages == 1) tile_cyc += epi;
-  const long total_tiles = (long)cd.m_tiles * n_tiles_n;
-  const long per_sm = (total_tiles + num_sms - 1) / num_sms;
-  cd.cycles = per_sm * tile_cyc + 4000.0;
+  const long total_tiles = (long)((cd.m_tiles + cd.cluster - 1) / cd.cluster) * n_tiles_n;  // cluster-tiles
+  const long n_clusters = num_sms / cd.cluster;
+  const long per_sm = (total_tiles + n_clusters - 1) / n_clusters;
+  cd.cycles = per_sm * tile_cyc + 4000.0 + (cd.cluster > 1 ? 500.0 : 0.0);
   cd.ok = true;
 }
 
@@ -304,6 +307,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   std::vector<Cand> shapes;
   const int want_mblk = det ? 0 : op.conv.mblk;
   const int want_mode = det ? 0 : op.conv.mode;  // 0 auto, 1 halo, 2 tap (3x3/s1 only)
+  const int want_cluster = det ? 1 : op.conv.cluster;  // 0 auto, else 1 / 2 / 4
   if (ksize == 1) {
     for (int mb = 1; mb <= 2; ++mb) {
       Cand cd;
@@ -339,10 +343,15 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
     if (tn <= 0 || tn > 256 || tn % 16) continue;
     const int ntn = (c_out + tn - 1) / tn;
     if (ntn * tn > kMaxCout) continue;
-    for (Cand cd : shapes) {
-      if (want_mblk > 0 && cd.mblk != want_mblk) continue;
-      fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
-      if (cd.ok) choices.push_back({tn, ntn, cd});
+    for (Cand cd0 : shapes) {
+      if (want_mblk > 0 && cd0.mblk != want_mblk) continue;
+      for (int cl = 1; cl <= 4; cl *= 2) {
+        if (want_cluster > 0 && cl != want_cluster) continue;
+        Cand cd = cd0;
+        cd.cluster = cl;
+        fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+        if (cd.ok) choices.push_back({tn, ntn, cd});
+      }
     }
   }
   if (n_choices) *n_choices = (int)choices.size();
@@ -371,6 +380,8 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.tiles_x = best.tiles_x;
   k.tiles_y = best.tiles_y;
   k.m_tiles = best.m_tiles;
+  k.cshift = best.cluster == 4 ? 2 : (best.cluster == 2 ? 1 : 0);
+  k.total_tiles = (best.m_tiles + best.cluster - 1) / best.cluster * k.n_tiles_n;
   k.a_group = best.mode == CONV_MODE_HALO ? 9 : 1;
   k.na = best.na;
   k.nb = best.nb;
@@ -442,7 +453,7 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     const uint64_t K = (uint64_t)k.taps * k.cpt * 64;
     uint64_t dims[2] = {K, (uint64_t)rows};
     uint64_t str[1] = {K * 2};
-    uint32_t box[2] = {64, (uint32_t)k.tile_n};
+    uint32_t box[2] = {64, (uint32_t)(k.tile_n >> k.cshift)};  // cluster: each CTA loads its share of the rows
     rc = encode_map(c, &k.tmB, op.w_dev, 2, dims, str, box, sw);
     if (rc) return rc;
   }
@@ -491,7 +502,7 @@ std::string tune_signature(const aq_ctx* c, const Op& op, int n) {
     const Buffer& db = c->bufs[op.conv.dst];
     snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", c->batch, sb.h, sb.w, sb.c,
              op.conv.c_in, op.conv.c_out, db.c, op.conv.k, op.conv.stride, op.conv.act, op.conv.res >= 0 ? 1 : 0,
-             op.conv.tile_n, op.conv.mblk, op.conv.mode, n);
+             op.conv.tile_n, op.conv.mblk, op.conv.mode * 8 + op.conv.cluster, n);
   }
   return b;
 }
@@ -1067,10 +1078,10 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
                          2.0 * c_out * c_in * k.taps;
     const int ksz = k.taps == 9 ? 3 : 1;
     static const char* mode_name[] = {"flat", "halo", "tap"};
-    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d tile=%dx%d mt=%d nt=%d | flop=%.4g bytes=%.4g",
+    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d tile=%dx%d mt=%d nt=%d cl=%d | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.tw, k.th,
-             k.m_tiles, k.n_tiles_n, flops, bytes);
+             k.m_tiles, k.n_tiles_n, 1 << k.cshift, flops, bytes);
   } else if (op.kind == OP_POOL) {
     const Buffer& b = c->bufs[op.buf];
     snprintf(buf, cap, "sppf_pool %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 4.0);

@@ -56,7 +56,12 @@ __device__ __forceinline__ void split_tile(const ConvKParams& p, int tile, int& 
     m_tile = tile / p.n_tiles_n;
     n_idx = tile - m_tile * p.n_tiles_n;
   }
+  if (p.cshift) m_tile = (m_tile << p.cshift) + (int)cluster_ctarank();  // CTA r of a cluster: M tile r of the group
 }
+
+// Persistent tile loop of a CTA: cluster-tiles tile_first(), + tile_step(), ... < p.total_tiles
+__device__ __forceinline__ int tile_first(const ConvKParams& p) { return (int)(blockIdx.x >> p.cshift); }
+__device__ __forceinline__ int tile_step(const ConvKParams& p) { return (int)(gridDim.x >> p.cshift); }
 
 struct Ring {
   uint32_t slot = 0, phase = 0;
@@ -189,9 +194,15 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
     mb_d[q] = mb * p.acc_pitch;
   }
   const bool leader = elect_one();
+  const uint16_t cmask = (uint16_t)((1u << (1u << p.cshift)) - 1u);  // all CTAs of the cluster
+  // a weight slot is refilled by multicast into every CTA of the cluster, so its release goes to all of them
+  auto release_b = [&](uint32_t bs) {
+    if (p.cshift) umma_commit_mc(b_empty(bs), cmask);
+    else umma_commit(b_empty(bs));
+  };
   Ring ra, rb, rt;
   int it = 0;
-  for (int tile = blockIdx.x; tile < mc.total_tiles; tile += gridDim.x, ++it, rt.advance(acc_stages)) {
+  for (int tile = tile_first(p); tile < mc.total_tiles; tile += tile_step(p), ++it, rt.advance(acc_stages)) {
     const uint32_t as = rt.slot;
     const long long tr0 = TR_NOW();
     long long trwa = 0, trwb = 0;
@@ -230,7 +241,7 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
           tc_fence_after();
           if (leader) {
             issue(a_lo + tap_off, b_lo0 + bs * b_slot16, kk);
-            if (!BRES) umma_commit(b_empty(bs));  // weight slot reusable once these MMAs retire
+            if (!BRES) release_b(bs);  // weight slot reusable once these MMAs retire
             if (tap == 8) {
               umma_commit(a_empty(ra.slot));
               if (c == cpt - 1) umma_commit(tfull(as));  // accumulators ready for the epilogue
@@ -257,7 +268,7 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
         const int kk = chunk == cpt - 1 ? kk_last : 4;
         if (leader) {
           issue(a_lo0 + ra.slot * a_slot16, b_lo0 + bs * b_slot16, kk);
-          if (!BRES) umma_commit(b_empty(bs));
+          if (!BRES) release_b(bs);
           umma_commit(a_empty(ra.slot));
           if (s == n_steps - 1) umma_commit(tfull(as));
         }
@@ -310,7 +321,7 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
   uint32_t gcount = 0;  // groups staged so far by this CTA
   Ring rs, rt;
   int it = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(acc_stages)) {
+  for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it, rt.advance(acc_stages)) {
     int m_tile, n_idx;
     split_tile(p, tile, m_tile, n_idx);
     const int n0 = n_idx * tile_n;
@@ -401,12 +412,12 @@ template <bool TRACE>
 __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_base, int total_tiles, uint32_t lane) {
   const int n_groups = p.groups, mblk = p.mblk, tile_n = p.tile_n;
   const uint32_t n_stg = p.n_stg;
-  const int my_tiles = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int my_tiles = (total_tiles - tile_first(p) + tile_step(p) - 1) / tile_step(p);
   const uint32_t total_groups = (uint32_t)(my_tiles * mblk * n_groups);
   Ring rs;
   uint32_t k = 0;  // groups stored so far
   int it = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+  for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
     int m_tile, n_idx;
     split_tile(p, tile, m_tile, n_idx);
     const int n0 = n_idx * tile_n;
@@ -489,7 +500,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     for (int s = 0; s < p.nb; ++s) {
       mbar_init(b_full(s), 1);
-      mbar_init(b_empty(s), p.n_mma);
+      mbar_init(b_empty(s), p.n_mma << p.cshift);  // the MMA issuers of every CTA of the cluster
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull(a), p.n_mma);
@@ -512,10 +523,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (p.cshift) cluster_sync_all();  // peers' barriers are initialised before anything is multicast to them
   const uint32_t tmem_base = tmem_slot;
   griddep_launch_dependents();
 
-  const int total_tiles = p.m_tiles * p.n_tiles_n;
+  const int total_tiles = p.total_tiles;
 
   if (warp == kWarpA) {
     // =========================== A producer ===========================
@@ -532,7 +544,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         const uint32_t row_bytes = (uint32_t)p.pw * 128u;
         Ring ra;
         int it = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
           int m_tile, n_idx;
           split_tile(p, tile, m_tile, n_idx);
           const MBlock t0 = mblock_coords(p, m_tile, 0);
@@ -571,7 +583,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       griddep_wait();  // activations are written by the previous kernel
       Ring ra;
       int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
         int m_tile, n_idx;
         split_tile(p, tile, m_tile, n_idx);
         const long long tr0 = TR_NOW();
@@ -627,7 +639,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     } else {
       Ring rb;
       int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
         int m_tile, n_idx;
         split_tile(p, tile, m_tile, n_idx);
         const int n0 = n_idx * p.tile_n;
@@ -638,7 +650,16 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           TR_WAIT(trw, mbar_wait(b_empty(slot), rb.phase ^ 1u));
           if (elect_one()) {
             mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
-            tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
+            if (p.cshift) {
+              // this CTA's share of the tile's rows, multicast to every CTA of the cluster (tmB's box is
+              // tile_n >> cshift rows); the other shares arrive from the peers on the same barrier
+              const uint32_t r = cluster_ctarank();
+              const uint32_t rows = (uint32_t)p.tile_n >> p.cshift;
+              tma_load_2d_mc(b_base + slot * p.b_slot_bytes + r * rows * 128u, &p.tmB, b_full(slot),
+                             weight_chunk(p, s) * 64, n0 + (int)(r * rows), (uint16_t)((1u << (1u << p.cshift)) - 1u));
+            } else {
+              tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
+            }
           }
         }
         if (lane == 0) trace_put<TRACE>(p, 1, it, tr0, trw, 0, TR_NOW());
@@ -676,7 +697,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     const int n_chunks = p.tile_n >> 4;
     Ring rt;
     int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it, rt.advance(p.acc_stages)) {
+    for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it, rt.advance(p.acc_stages)) {
       int m_tile, n_idx;
       split_tile(p, tile, m_tile, n_idx);
       const int as = rt.slot;
@@ -756,9 +777,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   }
 
-  // teardown: everyone done with TMEM before the allocating warp frees it
+  // teardown: everyone done with TMEM before the allocating warp frees it; in a cluster no CTA may exit while a
+  // peer can still multicast into its shared memory or arrive on its barriers
   tc_fence_before();
   __syncthreads();
+  if (p.cshift) cluster_sync_all();
   if (warp == kWarpMma) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -781,17 +804,30 @@ cudaError_t conv_kernels_init() {
 }
 
 cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
-  const int total = p.m_tiles * p.n_tiles_n;
+  const int cluster = 1 << p.cshift;
+  const int max_clusters = num_sms / cluster;
+  const int n_clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(total < num_sms ? total : num_sms);
+  cfg.gridDim = dim3(n_clusters * cluster);
   cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = conv_smem_bytes(p);
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cluster > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl ? 1 : 0;
+  cfg.numAttrs = na;
   if (p.trace) {
     if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE, true>, p);
     return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT, true>, p);

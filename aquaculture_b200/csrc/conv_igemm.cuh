@@ -73,6 +73,11 @@ struct alignas(64) ConvKParams {
   int n_mma;               // MMA-issuing threads (2 when the tile has more than one M block)
   int tile_n, n_tiles_n, groups;  // UMMA N, N tiles, 64-channel store groups per tile
   int m_tiles;                    // tiles along M
+  // Thread-block clusters of 1 << cshift CTAs (1, 2 or 4): the CTAs of a cluster work on consecutive M tiles of the
+  // same N tile in lockstep and share every weight tile -- each loads 1 / cluster of its rows and multicasts them to
+  // all, which divides the weight traffic L2 -> SM by the cluster size.  total_tiles = ceil(m_tiles / cluster) *
+  // n_tiles_n cluster-tiles; M tiles past m_tiles are computed on zero-filled operands and clipped by the stores.
+  int cshift, total_tiles;
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;
   uint32_t a_slot_bytes, b_slot_bytes, stg_bytes;

@@ -82,7 +82,7 @@ class Context:
         return self.call("aq_plan_buffer", h, w, c)
 
     def conv(self, src, dst, w_oihw: torch.Tensor, bias: torch.Tensor, k, stride, act=True, res=None,
-             tile_n=0, mblk=0, mode=0):
+             tile_n=0, mblk=0, mode=0, cluster=0):
         """src/dst/res are (buffer id, channel offset); w_oihw fp32 (O,I,k,k).  act: False/0 none, True/1 SiLU
         (ex2+rcp), 2 SiLU via tanh.approx; res must equal dst (in-place Bottleneck add)."""
         wk = pack_krsc(w_oihw)
@@ -90,7 +90,7 @@ class Context:
         self._keep += [wk, b]
         d = ConvDesc(src[0], src[1], w_oihw.shape[1], dst[0], dst[1], w_oihw.shape[0], k, stride,
                      int(act), res[0] if res else -1, res[1] if res else 0,
-                     wk.ctypes.data, b.ctypes.data, tile_n, mblk, mode)
+                     wk.ctypes.data, b.ctypes.data, tile_n, mblk, mode, cluster)
         self.call("aq_plan_conv", C.byref(d))
 
     def detect_level(self, src, w_oi: torch.Tensor, bias: torch.Tensor, nc, level_row_off, stride, anchors_px):

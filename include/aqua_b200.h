@@ -68,6 +68,7 @@ typedef struct aq_conv_desc {
   int tile_n;                   /* UMMA N per tile */
   int mblk;                     /* 128-pixel M blocks per CTA tile (1 or 2) */
   int mode;                     /* 3x3/s1 only: 1 = halo patch in shared memory, 2 = one box per tap */
+  int cluster;                  /* CTAs per thread-block cluster sharing each weight tile by TMA multicast (1, 2, 4) */
 } aq_conv_desc;
 
 /*

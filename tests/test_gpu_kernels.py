@@ -23,7 +23,7 @@ def ctx():
 
 
 def run_conv_case(ctx, B, H, W, c_in, c_out, k, s, act=True, res=False, src_ct=None, src_off=0, dst_ct=None,
-                  dst_off=0, seed=0, tile_n=0, mblk=0, mode=0):
+                  dst_off=0, seed=0, tile_n=0, mblk=0, mode=0, cluster=0):
     g = torch.Generator().manual_seed(seed)
     src_ct = src_ct or c_in
     dst_ct = dst_ct or c_out
@@ -36,7 +36,7 @@ def run_conv_case(ctx, B, H, W, c_in, c_out, k, s, act=True, res=False, src_ct=N
     bs = ctx.buffer(H, W, src_ct)
     bd = ctx.buffer(Ho, Wo, dst_ct)
     # the residual operand is the destination slice itself (in-place Bottleneck add)
-    ctx.conv((bs, src_off), (bd, dst_off), w, b, k, s, act, (bd, dst_off) if res else None, tile_n, mblk, mode)
+    ctx.conv((bs, src_off), (bd, dst_off), w, b, k, s, act, (bd, dst_off) if res else None, tile_n, mblk, mode, cluster)
     ctx.plan_end()
     ctx.upload(bs, x.numpy())
     init = np.full((B, Ho, Wo, dst_ct), 7.0, np.float16)
@@ -137,6 +137,19 @@ def test_conv_mblk_variants(ctx, mblk):
     run_conv_case(ctx, 5, 20, 12, 96, 96, 1, 1, mblk=mblk)       # resident weights, odd M-block count
     run_conv_case(ctx, 2, 40, 40, 96, 192, 3, 2, mblk=mblk)
     run_conv_case(ctx, 3, 24, 24, 48, 96, 3, 2, mblk=mblk)
+
+
+# thread-block clusters of 2 / 4 CTAs sharing every weight tile by TMA multicast (streamed weights only): odd M-tile
+# counts (a cluster's last CTAs run on zero-filled dummy tiles), several N tiles, every A-feed mode, residual
+@pytest.mark.parametrize("cluster", [2, 4])
+def test_conv_cluster_multicast(ctx, cluster):
+    run_conv_case(ctx, 3, 20, 20, 384, 384, 1, 1, cluster=cluster)                 # FLAT, 2-3 N tiles
+    run_conv_case(ctx, 5, 20, 12, 768, 384, 1, 1, cluster=cluster, mblk=1)         # odd number of M tiles
+    run_conv_case(ctx, 2, 40, 40, 192, 192, 3, 1, cluster=cluster, res=True)       # HALO, streamed weights
+    run_conv_case(ctx, 3, 20, 20, 384, 384, 3, 1, cluster=cluster, mode=1)         # HALO, tall coordinates
+    run_conv_case(ctx, 2, 40, 40, 96, 192, 3, 2, cluster=cluster)                  # TAP stride 2
+    run_conv_case(ctx, 3, 40, 40, 384, 768, 3, 2, cluster=cluster, mblk=1)         # TAP stride 2, 3 N tiles
+    run_conv_case(ctx, 16, 80, 80, 192, 384, 3, 2, cluster=cluster)                # many tiles per cluster (ring wrap)
 
 
 def test_conv_fast_silu(ctx):

@@ -11,6 +11,7 @@ run conv3x3s1 "conv3x3_s1 and not variants or residual"
 run variants "variants"
 run mblk "mblk_variants or fast_silu"
 run conv3x3s2 "conv3x3_s2"
+run cluster "cluster"
 run persistent "many_tiles"
 run detect "detect_decode"
 run prepost "preprocess or sppf"

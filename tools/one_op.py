@@ -13,6 +13,7 @@ ap.add_argument("--res", action="store_true")
 ap.add_argument("--mblk", type=int, default=0)
 ap.add_argument("--mode", type=int, default=0)
 ap.add_argument("--tile-n", type=int, default=0)
+ap.add_argument("--cluster", type=int, default=0)
 ap.add_argument("--act", type=int, default=2)
 ap.add_argument("--iters", type=int, default=10)
 a = ap.parse_args()
@@ -24,7 +25,7 @@ ctx = engine.Context(0)
 ctx.plan_begin(B, 64, 64, 3)
 bs = ctx.buffer(H, W, ci)
 bd = ctx.buffer(H // s, W // s, co)
-ctx.conv((bs, 0), (bd, 0), w, b, k, s, a.act, (bd, 0) if a.res else None, a.tile_n, a.mblk, a.mode)
+ctx.conv((bs, 0), (bd, 0), w, b, k, s, a.act, (bd, 0) if a.res else None, a.tile_n, a.mblk, a.mode, a.cluster)
 ctx.plan_end()
 x = torch.randn(1, H, W, ci, generator=g).half().numpy()
 ctx.upload(bs, np.ascontiguousarray(np.broadcast_to(x, (B, H, W, ci))))

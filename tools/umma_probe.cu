@@ -725,6 +725,79 @@ static void run_t10() {
   }
 }
 
+// ------------------------------------------------------------------------------------------------ T11
+// Nearest 2x upsample folded into a TMA load: 5-D map (c, dx, xs, dy, ys) over the LOW-resolution tensor whose
+// dx / dy dimensions (extent 2) have byte stride 0.  Does cuTensorMapEncodeTiled accept stride 0, and does the box
+// {64, 2, tw/2, 2, th/2} land as a row-major (2*ys+dy, 2*xs+dx) tile of replicated pixels?
+__global__ void __launch_bounds__(128) tma_upsample_kernel(const __grid_constant__ CUtensorMap tm, int xs0, int ys0,
+                                                           int tw, int th, int Ws, int* bad) {
+  extern __shared__ uint8_t raw[];
+  __shared__ __align__(8) uint64_t bar;
+  const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+  uint8_t* sm = raw + (base - smem_u32(raw));
+  for (int i = threadIdx.x; i < 32 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(sm)[i] = 0xFFFFFFFFu;
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async_smem();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(smem_u32(&bar), tw * th * 128);
+    tma_load_5d(base, &tm, smem_u32(&bar), 0, 0, xs0, 0, ys0);
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  int nbad = 0;
+  for (int i = threadIdx.x; i < tw * th * 8; i += 128) {
+    const int r = i >> 3, j = i & 7;
+    const int y = r / tw, x = r - y * tw;  // tile-local high-resolution pixel
+    const uint32_t row_addr = base + r * 128;
+    const uint32_t a = row_addr + ((j ^ ((row_addr >> 7) & 7)) << 4);
+    const __half got = *reinterpret_cast<const __half*>(sm + (a - base));
+    const int ys = ys0 + y / 2, xs = xs0 + x / 2;
+    const float want = (ys < 0 || xs < 0 || xs >= Ws || ys >= 8) ? 0.f : (float)((ys * Ws + xs) * 8 + j);
+    if (__half2float(got) != want) ++nbad;
+  }
+  atomicAdd(bad, nbad);
+}
+
+static void run_t11() {
+  const int Ws = 16, Hs = 8, C = 64;
+  std::vector<__half> h((size_t)Hs * Ws * C);
+  for (int y = 0; y < Hs; ++y)
+    for (int x = 0; x < Ws; ++x)
+      for (int c = 0; c < C; ++c) h[((size_t)y * Ws + x) * C + c] = __float2half((float)((y * Ws + x) * 8 + (c >> 3)));
+  __half* d;
+  int* bad;
+  CK(cudaMalloc(&d, h.size() * 2));
+  CK(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&bad, 4));
+  CK(cudaFuncSetAttribute(tma_upsample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  for (int variant = 0; variant < 2; ++variant) {
+    const int tw = variant ? 8 : 16, th = variant ? 16 : 8;
+    CUtensorMap tm;
+    cuuint64_t gd[5] = {(cuuint64_t)C, 2, (cuuint64_t)Ws, 2, (cuuint64_t)Hs};
+    cuuint64_t gs[4] = {0, (cuuint64_t)C * 2, 0, (cuuint64_t)Ws * C * 2};
+    cuuint32_t bx[5] = {64, 2, (cuuint32_t)tw / 2, 2, (cuuint32_t)th / 2}, es[5] = {1, 1, 1, 1, 1};
+    CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, d, gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    printf("T11 encode 5-D map with stride-0 dx/dy dims, box {64,2,%d,2,%d}: %s (%d)\n", tw / 2, th / 2,
+           r == CUDA_SUCCESS ? "accepted" : "REJECTED", (int)r);
+    if (r != CUDA_SUCCESS) continue;
+    const int coords[3][2] = {{0, 0}, {4, 2}, {12, 6}};  // the last one runs past Ws / Hs: OOB zero fill
+    for (auto& c : coords) {
+      CK(cudaMemset(bad, 0, 4));
+      tma_upsample_kernel<<<1, 128, 40 * 1024>>>(tm, c[0], c[1], tw, th, Ws, bad);
+      cudaError_t e = cudaDeviceSynchronize();
+      int hb = -1;
+      if (e == cudaSuccess) CK(cudaMemcpy(&hb, bad, 4, cudaMemcpyDeviceToHost));
+      printf("T11 upsampled tile %dx%d at low-res (%d,%d): %s, %d / %d chunks wrong\n", tw, th, c[0], c[1],
+             e == cudaSuccess ? "ok" : cudaGetErrorString(e), hb, tw * th * 8);
+      if (e != cudaSuccess) return;
+    }
+  }
+}
+
 int main(int argc, char** argv) {
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult q;
@@ -740,5 +813,6 @@ int main(int argc, char** argv) {
   if (strchr(which, '8')) run_t8();
   if (strchr(which, '9')) run_t9();
   if (strchr(which, 'a')) run_t10();
+  if (strchr(which, 'b')) run_t11();
   return 0;
 }

@@ -208,6 +208,18 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     cd.a_tx = (uint32_t)cd.pw * cd.ph * 128;
     cd.a_slot = (uint32_t)round_up((int)cd.a_tx, 1024);
     n_groups = cpt;
+  } else if (cd.mode == CONV_MODE_HALO2) {
+    // stride 2: four parity planes (input y-parity, x-parity) of (8mx+1) x (16my+1) half-resolution pixels each,
+    // one ring slot per plane; plane order (1,1) (1,0) (0,1) (0,0) carries 4 / 2 / 2 / 1 taps
+    cd.mblk = cd.mx * cd.my;
+    cd.pw = 8 * cd.mx + 1;
+    cd.ph = 16 * cd.my + 1;
+    cd.tiles_x = (wo + 8 * cd.mx - 1) / (8 * cd.mx);
+    cd.tiles_y = (batch * (ho + 1) + 16 * cd.my - 1) / (16 * cd.my);
+    cd.m_tiles = cd.tiles_x * cd.tiles_y;
+    cd.a_tx = (uint32_t)cd.pw * cd.ph * 128;
+    cd.a_slot = (uint32_t)round_up((int)cd.a_tx, 1024);
+    n_groups = cpt * 4;
   } else {
     cd.tiles_x = (wo + cd.tw - 1) / cd.tw;
     cd.tiles_y = (ho + cd.th - 1) / cd.th;
@@ -240,6 +252,7 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   // be overwritten, so two buffers serialise the epilogue on it), then deeper operand rings.
   grow(cd.n_stg, 3, stg);
   if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
+  if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
   if (!cd.b_res) grow(cd.nb, 5, b_slot);
   grow(cd.n_stg, 4, stg);
   grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
@@ -255,7 +268,7 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   // patch is gathered by 128 cp.async threads (~1.5 clk per 128-byte row)
   const double lat = 4500.0;
   double issue = cd.b_res ? 0.0 : fmax(600.0 * n_steps, lat * n_steps / cd.nb);
-  if (cd.mode == CONV_MODE_HALO) issue = fmax(issue, 1.5 * cd.pw * cd.ph * n_groups);
+  if (cd.mode == CONV_MODE_HALO || cd.mode == CONV_MODE_HALO2) issue = fmax(issue, 1.5 * cd.pw * cd.ph * n_groups);
   else issue = fmax(issue, fmax(600.0 * n_groups * a_instr_per_group, lat * n_groups / cd.na));
   const double epi = (double)cd.mblk * tile_n * 8.0 + 400.0;
   double tile_cyc = fmax(fmax(mma, l2), fmax(issue, epi)) + 300.0;
@@ -327,7 +340,18 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
         shapes.push_back(cd);
       }
     }
-    if (stride == 2 || want_mode != 1) {
+    if (stride == 2 && want_mode != 2) {
+      const int arr[5][2] = {{1, 1}, {2, 1}, {1, 2}, {2, 2}, {4, 1}};
+      for (auto& a : arr) {
+        Cand cd;
+        cd.mode = CONV_MODE_HALO2;
+        cd.mx = a[0];
+        cd.my = a[1];
+        cd.mblk = a[0] * a[1];
+        shapes.push_back(cd);
+      }
+    }
+    if ((stride == 2 && want_mode != 1) || (stride == 1 && want_mode != 1)) {
       for (int mb = 1; mb <= 2; ++mb) {
         Cand cd;
         cd.mode = CONV_MODE_TAP;
@@ -346,7 +370,9 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
     for (Cand cd0 : shapes) {
       if (want_mblk > 0 && cd0.mblk != want_mblk) continue;
       for (int cl = 1; cl <= 4; cl *= 2) {
-        if (want_cluster > 0 && cl != want_cluster) continue;
+        // measured (profiles/r1_cluster_multicast_sweep.txt): sharing weight tiles by multicast does not speed any
+        // layer up (cluster 2: +-1 %, cluster 4: slower), so clusters are only planned on request
+        if (cl != (want_cluster > 0 ? want_cluster : 1)) continue;
         Cand cd = cd0;
         cd.cluster = cl;
         fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
@@ -375,8 +401,9 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.pw = best.pw;
   k.ph = best.ph;
   k.pw_inv = best.pw > 0 ? (65536 + best.pw - 1) / best.pw : 0;
-  k.tw = best.mode == CONV_MODE_HALO ? 8 : (best.mode == CONV_MODE_FLAT ? kTileM : best.tw);
-  k.th = best.mode == CONV_MODE_HALO ? 16 : (best.mode == CONV_MODE_FLAT ? 1 : best.th);
+  const bool patch = best.mode == CONV_MODE_HALO || best.mode == CONV_MODE_HALO2;
+  k.tw = patch ? 8 : (best.mode == CONV_MODE_FLAT ? kTileM : best.tw);
+  k.th = patch ? 16 : (best.mode == CONV_MODE_FLAT ? 1 : best.th);
   k.tiles_x = best.tiles_x;
   k.tiles_y = best.tiles_y;
   k.m_tiles = best.m_tiles;
@@ -431,6 +458,19 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
       uint32_t box[4] = {64, (uint32_t)k.pw, (uint32_t)(32 >> hb), 1};
       rc = encode_map(c, &k.tmH[hb], sb.ptr + src_c_off, 4, dims, str, box, sw);
     }
+  } else if (k.mode == CONV_MODE_HALO2) {
+    // per x-parity: (channel, W/2, y-parity, H/2, N); a plane segment is a box (64 ch, pw, 1, h rows, 1)
+    k.a_src = sb.ptr + src_c_off;
+    k.a_n = c->batch; k.a_h = sb.h / 2; k.a_w = sb.w / 2; k.a_ct = sb.c; k.a_cin = c_in;
+    uint64_t dims[5] = {(uint64_t)c_in, (uint64_t)sb.w / 2, 2, (uint64_t)sb.h / 2, N};
+    uint64_t str[4] = {(uint64_t)2 * sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)2 * sb.w * sb.c * 2,
+                       (uint64_t)sb.h * sb.w * sb.c * 2};
+    rc = AQ_OK;
+    for (int hb = 0; hb < 6 && !rc; ++hb) {
+      uint32_t box[5] = {64, (uint32_t)k.pw, 1, (uint32_t)(32 >> hb), 1};
+      rc = encode_map(c, &k.tmH[hb], sb.ptr + src_c_off, 5, dims, str, box, sw);
+      if (!rc) rc = encode_map(c, &k.tmH2[hb], sb.ptr + src_c_off + sb.c, 5, dims, str, box, sw);
+    }
   } else if (k.stride == 1) {
     uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
@@ -482,7 +522,7 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
   uint64_t str[3] = {(uint64_t)db.c * 2, (uint64_t)db.w * db.c * 2, (uint64_t)db.h * db.w * db.c * 2};
   uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
   rc = encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
-  if (rc || k.mode != CONV_MODE_HALO) return rc;
+  if (rc || (k.mode != CONV_MODE_HALO && k.mode != CONV_MODE_HALO2)) return rc;
   for (int hb = 0; hb < 4 && !rc; ++hb) {
     uint32_t bx[4] = {64, 8, (uint32_t)(8 >> hb), 1};
     rc = encode_map(c, &k.tmOutR[hb], db.ptr + op.conv.dst_c_off, 4, dims, str, bx, sw);
@@ -1077,7 +1117,7 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
     const double bytes = 2.0 * ((double)c->batch * sb.h * sb.w * c_in + M * c_out * (k.has_res ? 2 : 1)) +
                          2.0 * c_out * c_in * k.taps;
     const int ksz = k.taps == 9 ? 3 : 1;
-    static const char* mode_name[] = {"flat", "halo", "tap"};
+    static const char* mode_name[] = {"flat", "halo", "tap", "halo2"};
     snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d tile=%dx%d mt=%d nt=%d cl=%d | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.tw, k.th,

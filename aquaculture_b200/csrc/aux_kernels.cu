@@ -74,7 +74,8 @@ __global__ void __launch_bounds__(256) preprocess_u8_kernel(const PreParams p) {
 // ---------------------------------------------------------------- SPPF pooling
 // grid (c / CG, n); the CTA keeps an (h*w) x CG-channel slab in shared memory and runs three separable
 // 5x5 max pools (horizontal then vertical), writing each result to its concat slice.
-constexpr int kPoolCG = 8;  // channels per CTA = one 16-byte vector per pixel
+constexpr int kPoolV = 4;            // 16-byte vectors per pixel per CTA: 64 contiguous bytes = two full 32-byte sectors
+constexpr int kPoolCG = 8 * kPoolV;  // channels per CTA
 
 __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
   uint4 r;
@@ -88,37 +89,40 @@ __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
 
 __global__ void __launch_bounds__(256) sppf_pool_kernel(__half* buf, int h, int w, int ct, int c_off, int c) {
   extern __shared__ uint4 s_pool[];
-  const int hw = h * w;
+  const int hw = h * w, nv = hw * kPoolV;  // element i = pixel (i / kPoolV), vector (i % kPoolV)
   uint4* s0 = s_pool;
-  uint4* s1 = s_pool + hw;
-  uint4* tmp = s_pool + 2 * hw;
+  uint4* s1 = s_pool + nv;
+  uint4* tmp = s_pool + 2 * nv;
   const int cg = blockIdx.x;
   const int n = blockIdx.y;
   __half* base = buf + (size_t)n * hw * ct + c_off + cg * kPoolCG;
-  for (int i = threadIdx.x; i < hw; i += blockDim.x) s0[i] = *reinterpret_cast<const uint4*>(base + (size_t)i * ct);
+  for (int i = threadIdx.x; i < nv; i += blockDim.x)
+    s0[i] = *reinterpret_cast<const uint4*>(base + (size_t)(i / kPoolV) * ct + (i % kPoolV) * 8);
   __syncthreads();
   uint4* src = s0;
   uint4* dst = s1;
   for (int pass = 1; pass <= 3; ++pass) {
-    for (int i = threadIdx.x; i < hw; i += blockDim.x) {
-      const int y = i / w, x = i - y * w;
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+      const int pix = i / kPoolV;
+      const int y = pix / w, x = pix - y * w;
       uint4 m = src[i];
       for (int d = 1; d <= 2; ++d) {
-        if (x - d >= 0) m = hmax8(m, src[i - d]);
-        if (x + d < w) m = hmax8(m, src[i + d]);
+        if (x - d >= 0) m = hmax8(m, src[i - d * kPoolV]);
+        if (x + d < w) m = hmax8(m, src[i + d * kPoolV]);
       }
       tmp[i] = m;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < hw; i += blockDim.x) {
-      const int y = i / w;
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+      const int pix = i / kPoolV;
+      const int y = pix / w;
       uint4 m = tmp[i];
       for (int d = 1; d <= 2; ++d) {
-        if (y - d >= 0) m = hmax8(m, tmp[i - d * w]);
-        if (y + d < h) m = hmax8(m, tmp[i + d * w]);
+        if (y - d >= 0) m = hmax8(m, tmp[i - d * w * kPoolV]);
+        if (y + d < h) m = hmax8(m, tmp[i + d * w * kPoolV]);
       }
       dst[i] = m;
-      *reinterpret_cast<uint4*>(base + (size_t)i * ct + (size_t)pass * c) = m;
+      *reinterpret_cast<uint4*>(base + (size_t)pix * ct + (i % kPoolV) * 8 + (size_t)pass * c) = m;
     }
     __syncthreads();
     uint4* t = src; src = dst; dst = t;
@@ -170,7 +174,7 @@ cudaError_t sppf_init() {
 }
 
 cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream) {
-  const size_t smem = (size_t)3 * h * w * sizeof(uint4);
+  const size_t smem = (size_t)3 * h * w * kPoolV * sizeof(uint4);
   if (smem > 200 * 1024 || (c % kPoolCG) != 0) return cudaErrorInvalidValue;
   dim3 grid(c / kPoolCG, n);
   sppf_pool_kernel<<<grid, 256, smem, stream>>>(buf, h, w, ct, c_off, c);

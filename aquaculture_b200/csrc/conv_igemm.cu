@@ -19,7 +19,7 @@ __device__ __forceinline__ MBlock mblock_coords(const ConvKParams& p, int m_tile
   r.n = r.y0 = r.x0 = r.m0 = 0;
   if (p.mode == CONV_MODE_FLAT) {
     r.m0 = (m_tile * p.mblk + mb) * kTileM;
-  } else if (p.mode == CONV_MODE_HALO) {
+  } else if (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) {
     // y0 is a row of the "tall" image: all images stacked with one shared zero row between them,
     // tall row R = n * (H + 1) + y + 1 (rows n * (H + 1) are the zero rows)
     const int ty = m_tile / p.tiles_x;
@@ -41,9 +41,12 @@ __device__ __forceinline__ MBlock mblock_coords(const ConvKParams& p, int m_tile
 
 // Weight chunk index (64 K elements each) of K step s: weights are [c_out][tap][chunk][64].
 __device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
-  if (p.mode != CONV_MODE_HALO) return s;  // FLAT: s = chunk; TAP: s = tap * cpt + chunk
+  if (p.mode != CONV_MODE_HALO && p.mode != CONV_MODE_HALO2) return s;  // FLAT: s = chunk; TAP: s = tap * cpt + chunk
   const int c = s / 9;                     // HALO: s = chunk * 9 + tap
-  return (s - c * 9) * p.cpt + c;
+  int tap = s - c * 9;
+  // HALO2: taps in plane order (1,1): 0 2 6 8 | (1,0): 1 7 | (0,1): 3 5 | (0,0): 4
+  if (p.mode == CONV_MODE_HALO2) tap = (int)((0x453718620ull >> (4 * tap)) & 15ull);
+  return tap * p.cpt + c;
 }
 
 // Ring position advanced with compare/reset: `x % n` and `x / n` by a runtime n cost a ~100-clk dependent
@@ -113,7 +116,7 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
   if (p.mode == CONV_MODE_FLAT) {
     if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, ch0, t.m0);
     else tma_store_2d(&p.tmOut, src, ch0, t.m0);
-  } else if (p.mode == CONV_MODE_HALO) {
+  } else if (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) {
     // the 16 tall rows of the block touch one or two images: one clipped box per image (rows outside
     // [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
     const int hp1 = p.a_h + 1;
@@ -162,8 +165,9 @@ struct MmaCtx {
 //   HALO : the nine taps of a 3x3/s1 conv are shifted views of one patch slot (else: one A slot per step)
 //   BRES : every weight tile is resident in shared memory (loaded once), no ring
 //   NMY  : M blocks issued by this thread (block indices mi, mi + n_mma)
-template <bool HALO, bool BRES, int NMY, bool TRACE>
+template <int FEED, bool BRES, int NMY, bool TRACE>
 __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc) {
+  constexpr bool HALO = FEED != 0;  // FEED: 0 = one A slot per K step, 1 = HALO (3x3/s1 patch), 2 = HALO2 (3x3/s2 planes)
   const uint32_t bar0 = mc.bar0;
   auto a_full = [&](uint32_t s) { return bar0 + 8u * s; };
   auto a_empty = [&](uint32_t s) { return bar0 + 8u * (kMaxA + s); };
@@ -223,7 +227,48 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
         if (kk > 3) umma_f16_split(d, aq + 6, a_hi, bl + 6, b_hi, idesc, 1u);
       }
     };
-    if (HALO) {
+    if (FEED == 2) {
+      // four parity planes per chunk, one A slot each; tap (kh, kw) of plane (yp, xp) is the plane shifted by
+      // (dy, dx) = (kh > 0, kw > 0) pixels: plane 0 = (1,1): 4 taps, 1 = (1,0): 2, 2 = (0,1): 2, 3 = (0,0): 1
+      int s = 0;
+      for (int c = 0; c < cpt; ++c) {
+        const int kk = c == cpt - 1 ? kk_last : 4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          TR_WAIT(trwa, mbar_wait(a_full(ra.slot), ra.phase));
+          const uint32_t a_lo = a_lo0 + ra.slot * a_slot16;
+          constexpr int kTaps[4] = {4, 2, 2, 1};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (j >= (q == 0 ? 4 : (q == 3 ? 1 : 2))) continue;
+            // (dy, dx) of tap j in plane q
+            const int dy = q == 0 ? (j >> 1) : (q == 1 ? j : 1);
+            const int dx = q == 0 ? (j & 1) : (q == 2 ? j : 1);
+            const uint32_t tap_off = dy ? pw8 + (dx ? 8u : 0u) : (dx ? 8u : 0u);
+            const uint32_t bs = BRES ? (uint32_t)s : rb.slot;
+            if (BRES) {
+              if (it == 0) TR_WAIT(trwb, mbar_wait(b_full(bs), 0));
+            } else {
+              TR_WAIT(trwb, mbar_wait(b_full(bs), rb.phase));
+            }
+            tc_fence_after();
+            if (leader) {
+              issue(a_lo + tap_off, b_lo0 + bs * b_slot16, kk);
+              if (!BRES) release_b(bs);
+              if (j == kTaps[q] - 1) {
+                umma_commit(a_empty(ra.slot));
+                if (q == 3 && c == cpt - 1) umma_commit(tfull(as));
+              }
+            }
+            __syncwarp();
+            acc = 1u;
+            if (!BRES) rb.advance(nb);
+            ++s;
+          }
+          ra.advance(na);
+        }
+      }
+    } else if (HALO) {
       int s = 0;
       for (int c = 0; c < cpt; ++c) {
         TR_WAIT(trwa, mbar_wait(a_full(ra.slot), ra.phase));
@@ -484,10 +529,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   auto tfull = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
   auto tempty = [&](int a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
 
-  if (warp == 0 && lane == 0 && p.mode == CONV_MODE_HALO) {
+  if (warp == 0 && lane == 0 && (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2)) {
     for (int hb = 0; hb < 6; ++hb) prefetch_tmap(&p.tmH[hb]);
+    if (p.mode == CONV_MODE_HALO2)
+      for (int hb = 0; hb < 6; ++hb) prefetch_tmap(&p.tmH2[hb]);
   }
-  if (warp == 0 && lane == 0 && p.mode != CONV_MODE_HALO) {
+  if (warp == 0 && lane == 0 && (p.mode == CONV_MODE_FLAT || p.mode == CONV_MODE_TAP)) {
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
   }
@@ -578,6 +625,51 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           }
           if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
         }
+      }
+    } else if (p.mode == CONV_MODE_HALO2) {
+      // 3x3/s2: per chunk the four parity planes (y-parity, x-parity) = (1,1) (1,0) (0,1) (0,0), one ring slot each.
+      // A plane holds half-resolution pixels xh = x0-1 .. x0+8mx-1, rows T = y0-1 .. y0+16my-1 of the tall plane
+      // (per image: one zero row = yh -1, then yh 0 .. H/2-1), cut into per-image segments exactly like HALO.
+      griddep_wait();
+      const int hp1 = p.a_h + 1;  // a_h = H/2 = output rows per image
+      const uint32_t row_bytes = (uint32_t)p.pw * 128u;
+      Ring ra;
+      int it = 0;
+      for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
+        int m_tile, n_idx;
+        split_tile(p, tile, m_tile, n_idx);
+        const MBlock t0 = mblock_coords(p, m_tile, 0);
+        const long long tr0 = TR_NOW();
+        long long trw = 0;
+        const int xl = t0.x0 - 1;
+        for (int cq = 0; cq < p.cpt * 4; ++cq, ra.advance(p.na)) {
+          const int c = cq >> 2, q = cq & 3;
+          const int yp = q < 2 ? 1 : 0, xp = (q & 1) ? 0 : 1;
+          const uint32_t slot = ra.slot;
+          TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
+          if (!elect_one()) continue;
+          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+          uint32_t dst = a_base + slot * p.a_slot_bytes;
+          int R = t0.y0 - 1, rem = p.ph;
+          while (rem > 0) {
+            const int n = R / hp1;
+            int y = R - n * hp1 - 1;  // -1 = the zero row above image n
+            int len = p.a_h - y;
+            if (len > rem) len = rem;
+            R += len;
+            rem -= len;
+#pragma unroll
+            for (int hb = 0; hb < 6; ++hb) {
+              const int h = 32 >> hb;
+              if (len & h) {
+                tma_load_5d(dst, xp ? &p.tmH2[hb] : &p.tmH[hb], a_full(slot), c * 64, xl, yp, y, n);
+                dst += (uint32_t)h * row_bytes;
+                y += h;
+              }
+            }
+          }
+        }
+        if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
       }
     } else {
       griddep_wait();  // activations are written by the previous kernel
@@ -671,13 +763,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     if (mi < p.n_mma) {
       const MmaCtx mc{bar0, a_base, b_base, tmem_base, mi, total_tiles};
       const int n_my = p.mblk > p.n_mma ? 2 : 1;  // M blocks this issuer owns: mi, mi + n_mma
-      const bool halo = p.mode == CONV_MODE_HALO;
-      if (halo) {
-        if (p.b_res) { if (n_my == 2) mma_role<true, true, 2, TRACE>(p, mc); else mma_role<true, true, 1, TRACE>(p, mc); }
-        else         { if (n_my == 2) mma_role<true, false, 2, TRACE>(p, mc); else mma_role<true, false, 1, TRACE>(p, mc); }
+      if (p.mode == CONV_MODE_HALO) {
+        if (p.b_res) { if (n_my == 2) mma_role<1, true, 2, TRACE>(p, mc); else mma_role<1, true, 1, TRACE>(p, mc); }
+        else         { if (n_my == 2) mma_role<1, false, 2, TRACE>(p, mc); else mma_role<1, false, 1, TRACE>(p, mc); }
+      } else if (p.mode == CONV_MODE_HALO2) {
+        if (p.b_res) { if (n_my == 2) mma_role<2, true, 2, TRACE>(p, mc); else mma_role<2, true, 1, TRACE>(p, mc); }
+        else         { if (n_my == 2) mma_role<2, false, 2, TRACE>(p, mc); else mma_role<2, false, 1, TRACE>(p, mc); }
       } else {
-        if (p.b_res) mma_role<false, true, 1, TRACE>(p, mc);
-        else mma_role<false, false, 1, TRACE>(p, mc);
+        if (p.b_res) mma_role<0, true, 1, TRACE>(p, mc);
+        else mma_role<0, false, 1, TRACE>(p, mc);
       }
     }
   } else if (warp == kWarpStore) {

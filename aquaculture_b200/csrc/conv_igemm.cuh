@@ -16,6 +16,10 @@
 //           taps are nine UMMA descriptors into that patch (start address shifted by whole 128-byte rows,
 //           stride-byte-offset = patch row pitch; the swizzle is a function of the absolute smem address, so
 //           any 128-byte-multiple offset is legal -- measured, profiles/r1_hw_probe_v1.txt T1).
+//     HALO2 3x3/s2 convs: the input is viewed as four parity planes (y-parity, x-parity) at half resolution; the
+//           CTA loads each plane's (8*mx+1) x (16*my+1) patch once per chunk (one ring slot per plane) and the
+//           nine taps are shifted UMMA views of the planes (4 / 2 / 2 / 1 taps per plane) -- 2.1 patches' worth
+//           of bytes per chunk instead of nine boxes.  Same tall output coordinates and stores as HALO.
 //     TAP   3x3/s2 convs and small maps: one shifted box per (tap, chunk); stride 2 uses a parity view
 //           (c, W/2, y-parity, H/2, N) per x-parity so the strided gather is still a dense box.
 // * warp roles (512 threads): warps 0..3 = A producer (HALO: 128 threads of 16-byte cp.async with zero fill --
@@ -40,13 +44,13 @@
 
 namespace aq {
 
-enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2 };
+enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2, CONV_MODE_HALO2 = 3 };
 enum { EPI_STORE = 0, EPI_DETECT = 1 };
 enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
 constexpr int kConvThreads = 672;  // 4 role warps + 16 epilogue warps + 1 store warp
 constexpr int kEpiWarps = 16;
-constexpr int kMaxA = 4;    // A ring slots
+constexpr int kMaxA = 6;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
 constexpr int kTileM = 128;
 constexpr int kMaxCout = 768;
@@ -59,6 +63,7 @@ struct alignas(64) ConvKParams {
   CUtensorMap tmB;    // weight loads
   CUtensorMap tmOut;  // output stores / reduce-adds (EPI_STORE)
   CUtensorMap tmH[6];  // HALO patch loads: boxes (64 ch, pw, h rows) with h = 32 / 16 / 8 / 4 / 2 / 1
+  CUtensorMap tmH2[6];  // HALO2 (3x3/s2 parity planes): tmH = x-parity 0, tmH2 = x-parity 1, 5-D (c, W/2, y-parity, H/2, N)
   CUtensorMap tmOutR[4];  // HALO: the same with boxes of 8 / 4 / 2 / 1 rows (blocks that start on a zero row)
   const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
   int mode, stride;

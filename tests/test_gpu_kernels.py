@@ -110,6 +110,17 @@ def test_conv3x3_s2(ctx, B, H, W, ci, co):
     run_conv_case(ctx, B, H, W, ci, co, 3, 2)
 
 
+# both A-feeding variants of the 3x3/s2 conv: parity-plane patches (mode 1: 1, 2 or 4 M blocks in tall coordinates)
+# and one box per tap (mode 2); ragged maps, channel counts completed by zero fill, several N tiles
+@pytest.mark.parametrize("mode,mblk", [(1, 1), (1, 2), (1, 4), (2, 1), (2, 2)])
+@pytest.mark.parametrize("B,H,W,ci,co", [(2, 32, 32, 64, 64), (3, 40, 24, 48, 96), (5, 40, 40, 96, 192),
+                                          (2, 80, 48, 192, 384), (3, 40, 40, 384, 768), (7, 12, 20, 16, 48)])
+def test_conv3x3_s2_variants(ctx, mode, mblk, B, H, W, ci, co):
+    if mblk == 4 and co > 96:
+        pytest.skip("4 M blocks x N > 512 TMEM columns / 227 KB shared memory: not a feasible tiling")
+    run_conv_case(ctx, B, H, W, ci, co, 3, 2, mode=mode, mblk=mblk, act=2)
+
+
 def test_conv3x3_s2_channel_slice(ctx):
     run_conv_case(ctx, 2, 40, 40, 192, 192, 3, 2, src_ct=384, src_off=192, dst_ct=384, dst_off=0)
 

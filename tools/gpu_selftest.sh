@@ -8,7 +8,8 @@ run() { # name, pytest -k expr
 }
 run conv1x1 "conv1x1"
 run conv3x3s1 "conv3x3_s1 and not variants or residual"
-run variants "variants"
+run variants "s1_variants"
+run s2variants "s2_variants"
 run mblk "mblk_variants or fast_silu"
 run conv3x3s2 "conv3x3_s2"
 run cluster "cluster"

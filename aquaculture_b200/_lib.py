@@ -24,7 +24,8 @@ class ConvDesc(C.Structure):
                 ("k", C.c_int), ("stride", C.c_int), ("act", C.c_int),
                 ("res", C.c_int), ("res_c_off", C.c_int),
                 ("weight", C.c_void_p), ("bias", C.c_void_p),
-                ("tile_n", C.c_int), ("mblk", C.c_int), ("mode", C.c_int), ("cluster", C.c_int)]
+                ("tile_n", C.c_int), ("mblk", C.c_int), ("mode", C.c_int), ("cluster", C.c_int),
+                ("up_src", C.c_int), ("up_c_off", C.c_int), ("up_c", C.c_int)]
 
 
 class DetectDesc(C.Structure):

@@ -138,13 +138,15 @@ int encode_map(aq_ctx* c, CUtensorMap* m, void* base, int rank, const uint64_t* 
 }
 
 // Pick the spatial M block (tw x th <= 128 pixels) that wastes the fewest MMA rows on an (h, w) map.
-void pick_spatial_tile(int h, int w, int* tw_out, int* th_out) {
+void pick_spatial_tile(int h, int w, int* tw_out, int* th_out, bool even = false) {
   double best = -1;
   int btw = 16, bth = 8;
   for (int tw = 1; tw <= 128; ++tw) {
     if (tw > w && tw != 1) break;
+    if (even && (tw & 1)) continue;
     int th = 128 / tw;
     if (th > h) th = h;
+    if (even) th &= ~1;
     if (th < 1) continue;
     const long tiles = (long)((w + tw - 1) / tw) * ((h + th - 1) / th);
     double eff = (double)h * w / (tiles * 128.0);
@@ -321,7 +323,17 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   const int want_mblk = det ? 0 : op.conv.mblk;
   const int want_mode = det ? 0 : op.conv.mode;  // 0 auto, 1 halo, 2 tap (3x3/s1 only)
   const int want_cluster = det ? 1 : op.conv.cluster;  // 0 auto, else 1 / 2 / 4
-  if (ksize == 1) {
+  const int up_c = det ? 0 : op.conv.up_c;
+  if (ksize == 1 && up_c > 0) {
+    // folded upsample: spatial (even x even) M blocks so the replicated 2x2 pixel groups stay inside a box
+    for (int mb = 1; mb <= 2; ++mb) {
+      Cand cd;
+      cd.mode = CONV_MODE_TAP;
+      cd.mblk = mb;
+      pick_spatial_tile(ho, wo, &cd.tw, &cd.th, true);
+      shapes.push_back(cd);
+    }
+  } else if (ksize == 1) {
     for (int mb = 1; mb <= 2; ++mb) {
       Cand cd;
       cd.mode = CONV_MODE_FLAT;
@@ -407,6 +419,8 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.tiles_x = best.tiles_x;
   k.tiles_y = best.tiles_y;
   k.m_tiles = best.m_tiles;
+  k.up_chunks = up_c / 64;
+  k.up_hs = sb.h / 2;
   k.cshift = best.cluster == 4 ? 2 : (best.cluster == 2 ? 1 : 0);
   k.total_tiles = (best.m_tiles + best.cluster - 1) / best.cluster * k.n_tiles_n;
   k.a_group = best.mode == CONV_MODE_HALO ? 9 : 1;
@@ -472,10 +486,20 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
       if (!rc) rc = encode_map(c, &k.tmH2[hb], sb.ptr + src_c_off + sb.c, 5, dims, str, box, sw);
     }
   } else if (k.stride == 1) {
-    uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
+    const int up_c = det ? 0 : op.conv.up_c;
+    uint64_t dims[4] = {(uint64_t)(c_in - up_c), (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
     uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
     rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 4, dims, str, box, sw);
+    if (!rc && up_c > 0) {
+      // (channel, dx, W/2, dy, H/2 * N) over the half-resolution tensor; dx / dy replicate with byte stride 0
+      // (accepted by cuTensorMapEncodeTiled and exact on sm_100a: probe T11, profiles/r1_hw_probe_t11.txt)
+      const Buffer& ub = c->bufs[op.conv.up_src];
+      uint64_t ud[5] = {(uint64_t)up_c, 2, (uint64_t)ub.w, 2, (uint64_t)ub.h * N};
+      uint64_t us[4] = {0, (uint64_t)ub.c * 2, 0, (uint64_t)ub.w * ub.c * 2};
+      uint32_t ubox[5] = {64, 2, (uint32_t)k.tw / 2, 2, (uint32_t)k.th / 2};
+      rc = encode_map(c, &k.tmUp, ub.ptr + op.conv.up_c_off, 5, ud, us, ubox, sw);
+    }
   } else {
     // per x-parity: (channel, W/2, y-parity, H/2, N) -- a stride-2 gather becomes a dense box
     uint64_t dims[5] = {(uint64_t)c_in, (uint64_t)sb.w / 2, 2, (uint64_t)sb.h / 2, N};
@@ -542,7 +566,7 @@ std::string tune_signature(const aq_ctx* c, const Op& op, int n) {
     const Buffer& db = c->bufs[op.conv.dst];
     snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", c->batch, sb.h, sb.w, sb.c,
              op.conv.c_in, op.conv.c_out, db.c, op.conv.k, op.conv.stride, op.conv.act, op.conv.res >= 0 ? 1 : 0,
-             op.conv.tile_n, op.conv.mblk, op.conv.mode * 8 + op.conv.cluster, n);
+             op.conv.tile_n, op.conv.mblk, op.conv.mode * 8 + op.conv.cluster + 64 * op.conv.up_c, n);
   }
   return b;
 }
@@ -866,8 +890,17 @@ int aq_plan_conv(aq_ctx* c, const aq_conv_desc* d) {
   if (!c || !d) return AQ_ERR_ARG;
   if (!c->planning) return fail(c, AQ_ERR_STATE, "plan_conv outside plan_begin/plan_end");
   int rc;
-  if ((rc = check_buf(c, d->src, d->src_c_off, d->c_in, "conv src"))) return rc;
+  if (d->up_c < 0 || d->up_c >= d->c_in) return fail(c, AQ_ERR_ARG, "conv: up_c %d outside [0, c_in %d)", d->up_c, d->c_in);
+  if ((rc = check_buf(c, d->src, d->src_c_off, d->c_in - d->up_c, "conv src"))) return rc;
   if ((rc = check_buf(c, d->dst, d->dst_c_off, d->c_out, "conv dst"))) return rc;
+  if (d->up_c > 0) {
+    if ((rc = check_buf(c, d->up_src, d->up_c_off, d->up_c, "conv upsample src"))) return rc;
+    const Buffer& ub = c->bufs[d->up_src];
+    const Buffer& s0 = c->bufs[d->src];
+    if (d->k != 1 || d->stride != 1 || d->up_c % 64 || 2 * ub.h != s0.h || 2 * ub.w != s0.w)
+      return fail(c, AQ_ERR_UNSUPPORTED, "conv: a folded upsample needs a 1x1/s1 conv, up_c %% 64 == 0 and a half-resolution source "
+                                         "(got k %d s %d up_c %d, %dx%d vs %dx%d)", d->k, d->stride, d->up_c, ub.h, ub.w, s0.h, s0.w);
+  }
   if (d->res >= 0 && (rc = check_buf(c, d->res, d->res_c_off, d->c_out, "conv residual"))) return rc;
   if (!d->weight || !d->bias) return fail(c, AQ_ERR_ARG, "conv: weight/bias NULL");
   const Buffer& sb = c->bufs[d->src];

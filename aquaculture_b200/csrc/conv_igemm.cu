@@ -117,11 +117,12 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
     if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, ch0, t.m0);
     else tma_store_2d(&p.tmOut, src, ch0, t.m0);
   } else if (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) {
-    // the 16 tall rows of the block touch one or two images: one clipped box per image (rows outside
+    // the 16 tall rows of the block touch one or more images: one clipped box per image (rows outside
     // [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
     const int hp1 = p.a_h + 1;
     const int n_first = t.y0 / hp1;
-    int n_last = n_first + (t.y0 + 15 - n_first * hp1 >= hp1 ? 1 : 0);
+    int n_last = n_first;  // usually one or two images; maps shorter than 15 rows put more into a block
+    while ((n_last + 1) * hp1 <= t.y0 + 15) ++n_last;
     if (n_last > p.a_n - 1) n_last = p.a_n - 1;
     for (int n = n_first; n <= n_last; ++n) {
       const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0
@@ -537,6 +538,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   if (warp == 0 && lane == 0 && (p.mode == CONV_MODE_FLAT || p.mode == CONV_MODE_TAP)) {
     prefetch_tmap(&p.tmA);
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
+    if (p.up_chunks) prefetch_tmap(&p.tmUp);
   }
   if (warp == kWarpStore && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
   if (warp == kWarpB && lane == 0) {
@@ -704,7 +706,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
             for (int mb = 0; mb < p.mblk; ++mb) {
               const MBlock t = mb ? tb1 : tb0;
               const uint32_t d = dst + mb * (kTileM * 128);
-              if (p.stride == 1) {
+              if (p.taps == 1) {
+                // 1x1 conv over [upsample2x(low-res tensor) | src]: the first up_chunks chunks are read from the
+                // half-resolution tensor through tmUp = (c, dx, W/2, dy, H/2 * N) whose dx / dy dimensions have
+                // stride 0, so the box {64, 2, tw/2, 2, th/2} lands as the tw x th tile of replicated pixels
+                if (grp < p.up_chunks) tma_load_5d(d, &p.tmUp, a_full(slot), c0, 0, t.x0 >> 1, 0, t.n * p.up_hs + (t.y0 >> 1));
+                else tma_load_4d(d, &p.tmA, a_full(slot), c0 - p.up_chunks * 64, t.x0, t.y0, t.n);
+              } else if (p.stride == 1) {
                 tma_load_4d(d, &p.tmA, a_full(slot), c0, t.x0 + kw - 1, t.y0 + kh - 1, t.n);
               } else {
                 // input row 2*Y + kh - 1: kh=0 -> (parity 1, Y-1), kh=1 -> (0, Y), kh=2 -> (1, Y); same in x

@@ -64,6 +64,7 @@ struct alignas(64) ConvKParams {
   CUtensorMap tmOut;  // output stores / reduce-adds (EPI_STORE)
   CUtensorMap tmH[6];  // HALO patch loads: boxes (64 ch, pw, h rows) with h = 32 / 16 / 8 / 4 / 2 / 1
   CUtensorMap tmH2[6];  // HALO2 (3x3/s2 parity planes): tmH = x-parity 0, tmH2 = x-parity 1, 5-D (c, W/2, y-parity, H/2, N)
+  CUtensorMap tmUp;     // TAP 1x1 with a folded nearest-2x upsample: (c, dx, W/2, dy, H/2 * N), dx / dy strides 0
   CUtensorMap tmOutR[4];  // HALO: the same with boxes of 8 / 4 / 2 / 1 rows (blocks that start on a zero row)
   const float* bias;  // [n_tiles_n * tile_n], zero padded (pre-multiplied by 0.5 for ACT_SILU_FAST)
   int mode, stride;
@@ -83,6 +84,7 @@ struct alignas(64) ConvKParams {
   // all, which divides the weight traffic L2 -> SM by the cluster size.  total_tiles = ceil(m_tiles / cluster) *
   // n_tiles_n cluster-tiles; M tiles past m_tiles are computed on zero-filled operands and clipped by the stores.
   int cshift, total_tiles;
+  int up_chunks, up_hs;  // leading 64-channel chunks that come from tmUp; rows of the half-resolution source
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;
   uint32_t a_slot_bytes, b_slot_bytes, stg_bytes;

@@ -82,15 +82,18 @@ class Context:
         return self.call("aq_plan_buffer", h, w, c)
 
     def conv(self, src, dst, w_oihw: torch.Tensor, bias: torch.Tensor, k, stride, act=True, res=None,
-             tile_n=0, mblk=0, mode=0, cluster=0):
+             tile_n=0, mblk=0, mode=0, cluster=0, up=None):
         """src/dst/res are (buffer id, channel offset); w_oihw fp32 (O,I,k,k).  act: False/0 none, True/1 SiLU
-        (ex2+rcp), 2 SiLU via tanh.approx; res must equal dst (in-place Bottleneck add)."""
+        (ex2+rcp), 2 SiLU via tanh.approx; res must equal dst (in-place Bottleneck add).  up = (buffer id, channel
+        offset, channels) of a half-resolution tensor whose nearest-2x upsampling forms the FIRST `channels` input
+        channels (upstream Upsample + Concat folded into the conv's TMA loads); src then supplies the rest."""
         wk = pack_krsc(w_oihw)
         b = np.ascontiguousarray(bias.float().numpy())
         self._keep += [wk, b]
         d = ConvDesc(src[0], src[1], w_oihw.shape[1], dst[0], dst[1], w_oihw.shape[0], k, stride,
                      int(act), res[0] if res else -1, res[1] if res else 0,
-                     wk.ctypes.data, b.ctypes.data, tile_n, mblk, mode, cluster)
+                     wk.ctypes.data, b.ctypes.data, tile_n, mblk, mode, cluster,
+                     up[0] if up else -1, up[1] if up else 0, up[2] if up else 0)
         self.call("aq_plan_conv", C.byref(d))
 
     def detect_level(self, src, w_oi: torch.Tensor, bias: torch.Tensor, nc, level_row_off, stride, anchors_px):
@@ -217,14 +220,14 @@ class TileDetector:
             w, b = fw[name]
             ctx.conv(src, dst, w, b, k, s, self.act, res)
 
-        def c3(idx, src, c1, dst, c2, n, shortcut, hw):
+        def c3(idx, src, c1, dst, c2, n, shortcut, hw, up=None):
             c_ = c2 // 2
             cat = buf(hw[0], hw[1], 2 * c_)
             tmp = buf(hw[0], hw[1], c_)
             pre = f"model.{idx}"
             w1, b1 = fw[pre + ".cv1"]
             w2, b2 = fw[pre + ".cv2"]
-            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, self.act)
+            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, self.act, up=up)
             for j in range(n):
                 conv(f"{pre}.m.{j}.cv1", (cat, 0), (tmp, 0), 1, 1)
                 conv(f"{pre}.m.{j}.cv2", (tmp, 0), (cat, 0), 3, 1, res=(cat, 0) if shortcut else None)
@@ -247,11 +250,20 @@ class TileDetector:
         conv("model.9.cv2", (sppf, 0), (x9, 0), 1, 1)
         # head
         conv("model.10", (x9, 0), (cat22, 384), 1, 1)
-        ctx.call("aq_plan_upsample2x", cat22, 384, 384, cat12, 0)
-        c3(13, (cat12, 0), 768, (x13, 0), 384, L[13].n, False, (H // 16, W // 16))
+        # Upsample + Concat (layers 11-12, 15-16): folded into the consuming C3's first conv, whose TMA loads read the
+        # half-resolution tensor through a stride-0 replicating tensor map (AQUA_FOLD_UPSAMPLE=0: separate kernel)
+        fold = os.environ.get("AQUA_FOLD_UPSAMPLE", "1") != "0"
+        if fold:
+            c3(13, (cat12, 384), 768, (x13, 0), 384, L[13].n, False, (H // 16, W // 16), up=(cat22, 384, 384))
+        else:
+            ctx.call("aq_plan_upsample2x", cat22, 384, 384, cat12, 0)
+            c3(13, (cat12, 0), 768, (x13, 0), 384, L[13].n, False, (H // 16, W // 16))
         conv("model.14", (x13, 0), (cat19, 192), 1, 1)
-        ctx.call("aq_plan_upsample2x", cat19, 192, 192, cat16, 0)
-        c3(17, (cat16, 0), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8))
+        if fold:
+            c3(17, (cat16, 192), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8), up=(cat19, 192, 192))
+        else:
+            ctx.call("aq_plan_upsample2x", cat19, 192, 192, cat16, 0)
+            c3(17, (cat16, 0), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8))
         conv("model.18", (x17, 0), (cat19, 0), 3, 2)
         c3(20, (cat19, 0), 384, (x20, 0), 384, L[20].n, False, (H // 16, W // 16))
         conv("model.21", (x20, 0), (cat22, 0), 3, 2)

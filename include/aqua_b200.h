@@ -69,6 +69,11 @@ typedef struct aq_conv_desc {
   int mblk;                     /* 128-pixel M blocks per CTA tile (1 or 2) */
   int mode;                     /* 3x3/s1 only: 1 = halo patch in shared memory, 2 = one box per tap */
   int cluster;                  /* CTAs per thread-block cluster sharing each weight tile by TMA multicast (1, 2, 4) */
+  /* nn.Upsample(2,'nearest') + Concat folded into this conv's loads (1x1 convs only; up_c = 0: off): input channels
+   * [0, up_c) are the nearest-2x upsampling of channels [up_c_off, up_c_off+up_c) of the half-resolution buffer
+   * up_src, read through a TMA tensor map whose replication dimensions have stride 0; channels [up_c, c_in) are
+   * src[src_c_off, src_c_off + c_in - up_c).  Neither the upsampled tensor nor the concat exists in memory. */
+  int up_src, up_c_off, up_c;
 } aq_conv_desc;
 
 /*

@@ -24,9 +24,9 @@ class PlanEmulator:
         self.bufs.append(torch.zeros(self.batch, h, w, c))
         return len(self.bufs) - 1
 
-    def conv(self, src, dst, w_oihw, bias, k, stride, act=True, res=None, tile_n=0, mblk=0, mode=0):
+    def conv(self, src, dst, w_oihw, bias, k, stride, act=True, res=None, tile_n=0, mblk=0, mode=0, cluster=0, up=None):
         # weights go through the same fp16 rounding the device sees
-        self.ops.append(("conv", src, dst, w_oihw.half().float(), bias.float(), k, stride, act, res))
+        self.ops.append(("conv", src, dst, w_oihw.half().float(), bias.float(), k, stride, act, res, up))
 
     def detect_level(self, src, w_oi, bias, nc, level_row_off, stride, anchors_px):
         self.ops.append(("detect", src, w_oi.reshape(w_oi.shape[0], -1).half().float(), bias.float(), nc, level_row_off, stride,
@@ -58,9 +58,13 @@ class PlanEmulator:
         pred = torch.zeros(self.batch, self.rows, self.nc + 5)
         for op in self.ops:
             if op[0] == "conv":
-                _, src, dst, w, b, k, s, act, res = op
+                _, src, dst, w, b, k, s, act, res, up = op
                 c_in, c_out = w.shape[1], w.shape[0]
-                x = self.bufs[src[0]][..., src[1]:src[1] + c_in].permute(0, 3, 1, 2)
+                if up is not None:  # input = [upsample2x(up buffer slice) | src slice]
+                    u = self.bufs[up[0]][..., up[1]:up[1] + up[2]].repeat_interleave(2, 1).repeat_interleave(2, 2)
+                    x = torch.cat((u, self.bufs[src[0]][..., src[1]:src[1] + c_in - up[2]]), -1).permute(0, 3, 1, 2)
+                else:
+                    x = self.bufs[src[0]][..., src[1]:src[1] + c_in].permute(0, 3, 1, 2)
                 y = F.conv2d(x, w, b, s, k // 2)
                 if act:
                     y = F.silu(y)

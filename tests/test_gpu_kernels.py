@@ -163,6 +163,36 @@ def test_conv_cluster_multicast(ctx, cluster):
     run_conv_case(ctx, 16, 80, 80, 192, 384, 3, 2, cluster=cluster)                # many tiles per cluster (ring wrap)
 
 
+# nn.Upsample(2,'nearest') + Concat folded into a 1x1 conv's loads: the first up_c input channels come from a
+# half-resolution buffer slice through a stride-0 replicating TMA map, the rest from the full-resolution source
+@pytest.mark.parametrize("B,H,W,up_c,c2,co,mblk", [(2, 40, 40, 384, 384, 384, 0), (3, 80, 80, 192, 192, 192, 1),
+                                                    (5, 20, 12, 64, 128, 96, 2), (2, 40, 24, 128, 64, 48, 0)])
+def test_conv1x1_folded_upsample(ctx, B, H, W, up_c, c2, co, mblk):
+    g = torch.Generator().manual_seed(5)
+    lo = torch.randn(B, H // 2, W // 2, up_c + 64, generator=g).half()     # slice [64, 64 + up_c) is upsampled
+    hi = torch.randn(B, H, W, c2 + 32, generator=g).half()                  # slice [32, 32 + c2)
+    c_in = up_c + c2
+    w = (torch.randn(co, c_in, 1, 1, generator=g) / math.sqrt(c_in)).half().float()
+    b = torch.randn(co, generator=g) * 0.5
+    ctx.plan_begin(B, 64, 64, 3)
+    bl = ctx.buffer(H // 2, W // 2, up_c + 64)
+    bh = ctx.buffer(H, W, c2 + 32)
+    bd = ctx.buffer(H, W, co)
+    ctx.conv((bh, 32), (bd, 0), w, b, 1, 1, 2, None, 0, mblk, 0, 0, up=(bl, 64, up_c))
+    ctx.plan_end()
+    ctx.upload(bl, lo.numpy())
+    ctx.upload(bh, hi.numpy())
+    ctx.forward()
+    ctx.sync()
+    got = torch.from_numpy(ctx.download(bd)).float()
+    u = lo[..., 64:64 + up_c].float().repeat_interleave(2, 1).repeat_interleave(2, 2)
+    x = torch.cat((u, hi[..., 32:32 + c2].float()), -1).permute(0, 3, 1, 2)
+    ref = F.silu(F.conv2d(x, w, b)).permute(0, 2, 3, 1)
+    err = (got - ref).abs()
+    bad = err > 2e-2 + 1e-2 * ref.abs()
+    assert not bad.any(), f"{int(bad.sum())} / {bad.numel()} off; max err {err.max():.4f}; first {bad.nonzero()[:4].tolist()}"
+
+
 def test_conv_fast_silu(ctx):
     run_conv_case(ctx, 2, 32, 32, 64, 64, 1, 1, act=2)
     run_conv_case(ctx, 2, 32, 32, 96, 48, 3, 1, act=2)

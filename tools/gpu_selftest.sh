@@ -6,7 +6,8 @@ run() { # name, pytest -k expr
   timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -x --tb=short -k "$2" > gpurun_out/selftest_$1.log 2>&1
   echo "$1 exit=$? $(tail -1 gpurun_out/selftest_$1.log)"
 }
-run conv1x1 "conv1x1"
+run conv1x1 "conv1x1 and not folded"
+run folded "folded_upsample"
 run conv3x3s1 "conv3x3_s1 and not variants or residual"
 run variants "s1_variants"
 run s2variants "s2_variants"

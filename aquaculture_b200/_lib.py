@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 LIB_NAME = "libaqua_b200.so"
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+LIB_PATH = os.environ.get("AQUA_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)  # override: A/B of two builds
 
 AQ_OK = 0
 AQ_ACT_NONE, AQ_ACT_SILU, AQ_ACT_SILU_FAST = 0, 1, 2

@@ -8,6 +8,19 @@ using namespace ptx;
 
 namespace {
 
+// This file is compiled twice (see the Makefile): AQ_CLUSTER=0 (default) builds the kernels every planned layer
+// uses; AQ_CLUSTER=1 builds the thread-block-cluster variants (weight tiles shared by TMA multicast) as a separate
+// set of kernels.  A runtime `if (p.cshift)` in the MMA issue loop cost the streamed-weight 3x3 layers 5-8 %
+// (A/B on one box, profiles/r1_ab_cluster_branch.txt), hence compile-time.
+#ifndef AQ_CLUSTER
+#define AQ_CLUSTER 0
+#endif
+#if AQ_CLUSTER
+#define CSHIFT(p) ((p).cshift)
+#else
+#define CSHIFT(p) 0
+#endif
+
 struct MBlock {
   int n, y0, x0;  // spatial modes: image, first output row / column
   int m0;         // flat mode: first flat pixel
@@ -59,12 +72,12 @@ __device__ __forceinline__ void split_tile(const ConvKParams& p, int tile, int& 
     m_tile = tile / p.n_tiles_n;
     n_idx = tile - m_tile * p.n_tiles_n;
   }
-  if (p.cshift) m_tile = (m_tile << p.cshift) + (int)cluster_ctarank();  // CTA r of a cluster: M tile r of the group
+  if (CSHIFT(p)) m_tile = (m_tile << CSHIFT(p)) + (int)cluster_ctarank();  // CTA r of a cluster: M tile r of the group
 }
 
 // Persistent tile loop of a CTA: cluster-tiles tile_first(), + tile_step(), ... < p.total_tiles
-__device__ __forceinline__ int tile_first(const ConvKParams& p) { return (int)(blockIdx.x >> p.cshift); }
-__device__ __forceinline__ int tile_step(const ConvKParams& p) { return (int)(gridDim.x >> p.cshift); }
+__device__ __forceinline__ int tile_first(const ConvKParams& p) { return (int)(blockIdx.x >> CSHIFT(p)); }
+__device__ __forceinline__ int tile_step(const ConvKParams& p) { return (int)(gridDim.x >> CSHIFT(p)); }
 
 struct Ring {
   uint32_t slot = 0, phase = 0;
@@ -199,10 +212,10 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
     mb_d[q] = mb * p.acc_pitch;
   }
   const bool leader = elect_one();
-  const uint16_t cmask = (uint16_t)((1u << (1u << p.cshift)) - 1u);  // all CTAs of the cluster
+  const uint16_t cmask = (uint16_t)((1u << (1u << CSHIFT(p))) - 1u);  // all CTAs of the cluster
   // a weight slot is refilled by multicast into every CTA of the cluster, so its release goes to all of them
   auto release_b = [&](uint32_t bs) {
-    if (p.cshift) umma_commit_mc(b_empty(bs), cmask);
+    if (CSHIFT(p)) umma_commit_mc(b_empty(bs), cmask);
     else umma_commit(b_empty(bs));
   };
   Ring ra, rb, rt;
@@ -549,7 +562,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
     for (int s = 0; s < p.nb; ++s) {
       mbar_init(b_full(s), 1);
-      mbar_init(b_empty(s), p.n_mma << p.cshift);  // the MMA issuers of every CTA of the cluster
+      mbar_init(b_empty(s), p.n_mma << CSHIFT(p));  // the MMA issuers of every CTA of the cluster
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull(a), p.n_mma);
@@ -572,7 +585,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (p.cshift) cluster_sync_all();  // peers' barriers are initialised before anything is multicast to them
+  if (CSHIFT(p)) cluster_sync_all();  // peers' barriers are initialised before anything is multicast to them
   const uint32_t tmem_base = tmem_slot;
   griddep_launch_dependents();
 
@@ -750,13 +763,13 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           TR_WAIT(trw, mbar_wait(b_empty(slot), rb.phase ^ 1u));
           if (elect_one()) {
             mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
-            if (p.cshift) {
+            if (CSHIFT(p)) {
               // this CTA's share of the tile's rows, multicast to every CTA of the cluster (tmB's box is
               // tile_n >> cshift rows); the other shares arrive from the peers on the same barrier
               const uint32_t r = cluster_ctarank();
-              const uint32_t rows = (uint32_t)p.tile_n >> p.cshift;
+              const uint32_t rows = (uint32_t)p.tile_n >> CSHIFT(p);
               tma_load_2d_mc(b_base + slot * p.b_slot_bytes + r * rows * 128u, &p.tmB, b_full(slot),
-                             weight_chunk(p, s) * 64, n0 + (int)(r * rows), (uint16_t)((1u << (1u << p.cshift)) - 1u));
+                             weight_chunk(p, s) * 64, n0 + (int)(r * rows), (uint16_t)((1u << (1u << CSHIFT(p))) - 1u));
             } else {
               tma_load_2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64, n0);
             }
@@ -883,7 +896,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   // peer can still multicast into its shared memory or arrive on its barriers
   tc_fence_before();
   __syncthreads();
-  if (p.cshift) cluster_sync_all();
+  if (CSHIFT(p)) cluster_sync_all();
   if (warp == kWarpMma) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -892,11 +905,30 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
 
 }  // namespace
 
+#if AQ_CLUSTER
+#define AQ_VARIANT(x) x##_cl
+#else
+#define AQ_VARIANT(x) x##_nocl
+#endif
+cudaError_t conv_kernels_init_cl();
+cudaError_t conv_kernels_init_nocl();
+cudaError_t launch_conv_cl(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
+cudaError_t launch_conv_nocl(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
+
+#if !AQ_CLUSTER
 size_t conv_smem_bytes(const ConvKParams& p) {
   return (size_t)p.na * p.a_slot_bytes + (size_t)p.nb * p.b_slot_bytes + (size_t)p.n_stg * p.stg_bytes + 1024;
 }
-
 cudaError_t conv_kernels_init() {
+  cudaError_t e = conv_kernels_init_nocl();
+  return e == cudaSuccess ? conv_kernels_init_cl() : e;
+}
+cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
+  return p.cshift ? launch_conv_cl(p, epi, num_sms, pdl, stream) : launch_conv_nocl(p, epi, num_sms, pdl, stream);
+}
+#endif
+
+cudaError_t AQ_VARIANT(conv_kernels_init)() {
   cudaError_t e = cudaSuccess;
   const void* fns[4] = {(const void*)conv_igemm_kernel<EPI_STORE, false>, (const void*)conv_igemm_kernel<EPI_DETECT, false>,
                         (const void*)conv_igemm_kernel<EPI_STORE, true>, (const void*)conv_igemm_kernel<EPI_DETECT, true>};
@@ -905,7 +937,7 @@ cudaError_t conv_kernels_init() {
   return e;
 }
 
-cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
+cudaError_t AQ_VARIANT(launch_conv)(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
   const int cluster = 1 << p.cshift;
   const int max_clusters = num_sms / cluster;
   const int n_clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;

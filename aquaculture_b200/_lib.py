@@ -53,6 +53,7 @@ SIGNATURES = {
     "aq_pred_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
     "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
+    "aq_profile_ops_insitu": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_op_describe": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
     "aq_trace_op": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "aq_debug_plan_conv": (C.c_int, [C.c_int] * 10 + [C.c_char_p, C.c_size_t]),

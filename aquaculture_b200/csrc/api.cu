@@ -1085,6 +1085,43 @@ int aq_profile_ops(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   return rc ? rc : n;
 }
 
+// In-situ variant: whole forward passes with an event after every op, so each op sees the cache state and the
+// neighbours it has in the real step (the isolated table above re-runs one op on warm buffers).
+int aq_profile_ops_insitu(aq_ctx* c, int iters, float* ms_per_op, int cap) {
+  if (!c || !ms_per_op || iters <= 0) return AQ_ERR_ARG;
+  if (!c->planned) return fail(c, AQ_ERR_STATE, "profile before plan_end");
+  cudaSetDevice(c->device);
+  const int n = (int)c->ops.size();
+  if (cap < n) return fail(c, AQ_ERR_ARG, "profile: need room for %d ops", n);
+  std::vector<cudaEvent_t> ev(n + 1);
+  for (auto& e : ev) CU_CHECK(c, cudaEventCreate(&e));
+  std::vector<Op> all;
+  all.swap(c->ops);
+  std::vector<double> acc(n, 0.0);
+  int rc = AQ_OK;
+  for (int k = 0; k <= iters && rc == AQ_OK; ++k) {  // pass 0 = warm-up
+    cudaEventRecord(ev[0], c->stream);
+    for (int i = 0; i < n && rc == AQ_OK; ++i) {
+      c->ops.clear();
+      c->ops.push_back(all[i]);
+      rc = run_ops(c, c->stream);
+      cudaEventRecord(ev[i + 1], c->stream);
+    }
+    if (rc == AQ_OK && cudaEventSynchronize(ev[n]) != cudaSuccess)
+      rc = fail(c, AQ_ERR_CUDA, "profile: %s", cudaGetErrorString(cudaGetLastError()));
+    for (int i = 0; i < n && rc == AQ_OK && k > 0; ++i) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+      acc[i] += ms;
+    }
+  }
+  c->ops.clear();
+  c->ops.swap(all);
+  for (int i = 0; i < n; ++i) ms_per_op[i] = (float)(acc[i] / iters);
+  for (auto& e : ev) cudaEventDestroy(e);
+  return rc ? rc : n;
+}
+
 int aq_trace_op(aq_ctx* c, int i, long long* out, size_t cap_vals) {
   if (!c || !out) return AQ_ERR_ARG;
   if (!c->planned) return fail(c, AQ_ERR_STATE, "trace before plan_end");

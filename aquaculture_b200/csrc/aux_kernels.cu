@@ -29,9 +29,17 @@ __device__ __forceinline__ int letterbox_sample(const PreParams& p, const uint8_
 }
 
 // One thread per space-to-depth output pixel: 2x2 source pixels x 3 channels -> 16 fp16 (two 16-byte stores).
+// u / 255 -> fp16 comes from a 256-entry shared-memory table built with the same IEEE division + rounding upstream's
+// `.half() / 255` path produces (bit-identical, 12 divisions per thread saved).  Tiles that need no resize and
+// no padding (the reference's 640x640 case) take a vectorised path: per source row the thread's two pixels are
+// six consecutive bytes, read as three aligned 16-bit loads (a warp reads 192 contiguous bytes per row).
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreParams p) {
+  __shared__ __half lut[256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = __float2half_rn(__fdiv_rn((float)i, 255.0f));
+  __syncthreads();
   const int W2 = p.net_w >> 1, H2 = p.net_h >> 1;
   const size_t total = (size_t)p.n * H2 * W2;
+  const bool direct = !p.resize && p.top == 0 && p.left == 0 && p.new_h == p.net_h && p.new_w == p.net_w && !(p.in_w & 1);
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (size_t)gridDim.x * blockDim.x) {
     const int X = (int)(idx % W2);
@@ -40,15 +48,28 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreParams p) {
     const int n = (int)(t / H2);
     const uint8_t* img = p.src + (size_t)n * p.in_h * p.in_w * 3;
     __align__(16) __half v[16];
+    if (direct) {
 #pragma unroll
-    for (int py = 0; py < 2; ++py)
+      for (int py = 0; py < 2; ++py) {
+        const uint16_t* row = reinterpret_cast<const uint16_t*>(img + ((size_t)(2 * Y + py) * p.in_w + 2 * X) * 3);
+        const uint32_t w0 = __ldg(row), w1 = __ldg(row + 1), w2 = __ldg(row + 2);
+        // pixel 0 = bytes 0..2, pixel 1 = bytes 3..5 of the row segment; bgr swaps the outer bytes of each pixel
+        const uint32_t a0 = w0 & 255u, a1 = w0 >> 8, a2 = w1 & 255u, a3 = w1 >> 8, a4 = w2 & 255u, a5 = w2 >> 8;
+        v[py * 6 + 0] = lut[p.bgr ? a2 : a0];
+        v[py * 6 + 1] = lut[a1];
+        v[py * 6 + 2] = lut[p.bgr ? a0 : a2];
+        v[py * 6 + 3] = lut[p.bgr ? a5 : a3];
+        v[py * 6 + 4] = lut[a4];
+        v[py * 6 + 5] = lut[p.bgr ? a3 : a5];
+      }
+    } else {
 #pragma unroll
-      for (int px = 0; px < 2; ++px)
+      for (int py = 0; py < 2; ++py)
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const int u = letterbox_sample(p, img, 2 * Y + py, 2 * X + px, c);
-          v[(py * 2 + px) * 3 + c] = __float2half_rn(__fdiv_rn((float)u, 255.0f));
-        }
+        for (int px = 0; px < 2; ++px)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = lut[letterbox_sample(p, img, 2 * Y + py, 2 * X + px, c)];
+    }
 #pragma unroll
     for (int c = 12; c < 16; ++c) v[c] = __float2half_rn(0.f);
     uint4* dst = reinterpret_cast<uint4*>(p.out_s2d + idx * 16);
@@ -74,8 +95,8 @@ __global__ void __launch_bounds__(256) preprocess_u8_kernel(const PreParams p) {
 // ---------------------------------------------------------------- SPPF pooling
 // grid (c / CG, n); the CTA keeps an (h*w) x CG-channel slab in shared memory and runs three separable
 // 5x5 max pools (horizontal then vertical), writing each result to its concat slice.
-constexpr int kPoolV = 4;            // 16-byte vectors per pixel per CTA: 64 contiguous bytes = two full 32-byte sectors
-constexpr int kPoolCG = 8 * kPoolV;  // channels per CTA
+// kPoolV = 16-byte vectors per pixel per CTA: 4 (64 contiguous bytes = two full 32-byte sectors) while the slab fits
+// shared memory (20x20 maps of the 640 configs), 1 for larger maps (40x40 at --img 1280, up to 4266 pixels).
 
 __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
   uint4 r;
@@ -87,7 +108,9 @@ __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
   return r;
 }
 
+template <int kPoolV>
 __global__ void __launch_bounds__(256) sppf_pool_kernel(__half* buf, int h, int w, int ct, int c_off, int c) {
+  constexpr int kPoolCG = 8 * kPoolV;  // channels per CTA
   extern __shared__ uint4 s_pool[];
   const int hw = h * w, nv = hw * kPoolV;  // element i = pixel (i / kPoolV), vector (i % kPoolV)
   uint4* s0 = s_pool;
@@ -170,14 +193,19 @@ cudaError_t launch_preprocess_u8(const PreParams& p, cudaStream_t stream) {
 }
 
 cudaError_t sppf_init() {
-  return cudaFuncSetAttribute(sppf_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  cudaError_t e = cudaFuncSetAttribute(sppf_pool_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(sppf_pool_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream) {
-  const size_t smem = (size_t)3 * h * w * kPoolV * sizeof(uint4);
-  if (smem > 200 * 1024 || (c % kPoolCG) != 0) return cudaErrorInvalidValue;
-  dim3 grid(c / kPoolCG, n);
-  sppf_pool_kernel<<<grid, 256, smem, stream>>>(buf, h, w, ct, c_off, c);
+  const size_t smem1 = (size_t)3 * h * w * sizeof(uint4);  // one 8-channel vector per pixel
+  if (4 * smem1 <= 200 * 1024 && (c % 32) == 0) {
+    sppf_pool_kernel<4><<<dim3(c / 32, n), 256, 4 * smem1, stream>>>(buf, h, w, ct, c_off, c);
+  } else {
+    if (smem1 > 200 * 1024 || (c % 8) != 0) return cudaErrorInvalidValue;  // maps beyond 4266 pixels: not supported
+    sppf_pool_kernel<1><<<dim3(c / 8, n), 256, smem1, stream>>>(buf, h, w, ct, c_off, c);
+  }
   return cudaGetLastError();
 }
 

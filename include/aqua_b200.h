@@ -122,6 +122,8 @@ int aq_plan_num_launches(aq_ctx* ctx); /* kernels launched by one aq_forward */
  * after one warm-up) into ms_per_op[0..n_ops); returns n_ops.  aq_op_describe writes a one-line description
  * (kind, GEMM shape, tile configuration, algorithmic FLOPs and bytes) of op `i`. */
 int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
+/* Same table measured in situ: `iters` whole forward passes with an event after every op (real cache state). */
+int aq_profile_ops_insitu(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
 /* Per-role timeline of planned conv op `i` (instrumented build of the same kernel, launched once after one
  * warm-up): out[grid][6 roles][48 tiles][4] clock64 values (layout in conv_igemm.cuh); returns the grid size

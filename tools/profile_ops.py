@@ -11,6 +11,7 @@ ap.add_argument("--batch", type=int, default=64)
 ap.add_argument("--img", type=int, default=640)
 ap.add_argument("--iters", type=int, default=10)
 ap.add_argument("--out", default="")
+ap.add_argument("--insitu", action="store_true", help="events between the ops of whole forward passes")
 a = ap.parse_args()
 sd = weights.synthetic_state(3, 0)
 det = engine.TileDetector(sd, 3, batch=a.batch, imgsz=(a.img, a.img))
@@ -18,7 +19,7 @@ t = torch.from_numpy(tiles.synthetic_tiles(range(a.batch), a.img, a.img)).pin_me
 det.detect(t)
 n = det.n_launches
 ms = (C.c_float * n)()
-det.ctx.call("aq_profile_ops", a.iters, ms, n)
+det.ctx.call("aq_profile_ops_insitu" if a.insitu else "aq_profile_ops", a.iters, ms, n)
 rows, tot_ms, tot_flop, tot_bytes = [], 0.0, 0.0, 0.0
 buf = C.create_string_buffer(512)
 for i in range(n):

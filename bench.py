@@ -95,6 +95,16 @@ class ClockSampler:
         return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
 
 
+def measured_traffic():
+    """DRAM bytes per conv-stack launch set (one batch of 64 tiles) from the committed ncu pass
+    (tools/gpu_dram_pass.sh -> tools/dram_summary.py -> profiles/r1_dram_traffic_v6.json); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_dram_traffic_v6.json")) as f:
+            return float(json.load(f)["conv_stack_dram_bytes"])
+    except Exception:
+        return None
+
+
 def cpu_baseline(sd, n_tiles, seed_base=10_000):
     """Oracle on the host cores: bounded sample of the same workload (batch 1, fp32, 640^2 tiles)."""
     from aquaculture_b200 import tiles
@@ -295,8 +305,11 @@ def main():
                                 "detections, '%g' label files written by the C formatter; two batches in flight"},
             "gpu_launches": (1 + det.n_launches + 1) * args.steps,
             "roofline": {"bound": "tensor", "achieved": round(achieved, 2), "peak": peaks["sustained"], "unit": "TFLOP/s",
-                         "frac": round(achieved / peaks["sustained"], 4), "traffic": None,
-                         "kernel": "conv_igemm_kernel (82 launches/step, the whole conv stack timed as one CUDA graph)",
+                         "frac": round(achieved / peaks["sustained"], 4), "traffic": measured_traffic(),
+                         "traffic_note": "DRAM read+write bytes of the conv-stack launch set (batch 64), ncu dram__bytes_* "
+                                         "(profiles/r1_dram_traffic_v6.*); algorithmic unfused bytes 13.6 GB",
+                         "kernel": f"conv_igemm_kernel ({det.n_launches} launches/step for the 82 convs + SPPF pool, "
+                                   "the whole conv stack timed as one CUDA graph)",
                          "algorithmic_flop_per_launch_set": flop_tile * BATCH,
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['src']}); burst {peaks['burst']}, "
                                         f"frac_of_burst {round(achieved / peaks['burst'], 4)}, frac_of_nominal_2250 {round(achieved / 2250.0, 4)}",

@@ -39,6 +39,7 @@ struct Op {
   std::vector<uint16_t> w_host;
   std::vector<float> b_host;
   __half* w_dev = nullptr;
+  __half* w_dev_dense = nullptr;  // 3x3 convs with c_in <= 16: [c_out][3 * 64], K = tap * 16 + channel (see Cand::b_dense)
   float* b_dev = nullptr;
   ConvKParams kp{};
   // pool / upsample
@@ -179,6 +180,7 @@ int pow2_at_least(int v) {
 struct Cand {
   int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
   int cluster = 1;  // CTAs per thread-block cluster sharing each weight tile by multicast (1, 2, 4)
+  int b_dense = 0;  // HALO with c_in <= 16: four taps share one 64-wide weight chunk (resident weights = 3 slots, not 9)
   // derived
   int tiles_x = 1, tiles_y = 1, m_tiles = 0, pw = 0, ph = 0;
   int na = 0, nb = 0, b_res = 0, n_stg = 0, acc_stages = 0;
@@ -236,14 +238,17 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   cd.acc_stages = 2 * cd.mblk * acc_pitch <= 512 ? 2 : 1;
   // ---- shared memory: minimal plan first, then grow the rings
   const long budget = kConvMaxDynSmem - 1024;
-  cd.b_res = (n_tiles_n == 1 && n_steps <= kMaxB && (long)n_steps * b_slot <= 112 * 1024) ? 1 : 0;
+  if (cd.b_dense && (cd.mode != CONV_MODE_HALO || cpt != 1 || n_tiles_n != 1)) cd.b_dense = 0;
+  const int res_slots = cd.b_dense ? (n_steps + 3) / 4 : n_steps;  // weight slots that hold the whole (single) N tile
+  cd.b_res = (n_tiles_n == 1 && res_slots <= kMaxB && (long)res_slots * b_slot <= 112 * 1024) ? 1 : 0;
   cd.na = 2;
   cd.n_stg = 2;
-  cd.nb = cd.b_res ? n_steps : 3;
+  cd.nb = cd.b_res ? res_slots : 3;
   auto used = [&]() { return (long)cd.na * cd.a_slot + (long)cd.nb * b_slot + (long)cd.n_stg * stg; };
   if (used() > budget) {
     if (!cd.b_res) return;
     cd.b_res = 0;
+    cd.b_dense = 0;
     cd.nb = 3;
     if (used() > budget) return;
   }
@@ -349,6 +354,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
         cd.mx = a[0];
         cd.my = a[1];
         cd.mblk = a[0] * a[1];
+        cd.b_dense = (c_in <= 16 && !getenv("AQUA_NO_DENSE")) ? 1 : 0;
         shapes.push_back(cd);
       }
     }
@@ -427,6 +433,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.na = best.na;
   k.nb = best.nb;
   k.b_res = best.b_res;
+  k.b_dense = best.b_res ? best.b_dense : 0;
   k.n_stg = best.n_stg;
   k.acc_stages = best.acc_stages;
   k.n_mma = best.mblk > 1 ? 2 : 1;
@@ -438,6 +445,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   if (det) k.n_stg = 1;
   k.act = det ? ACT_NONE : op.conv.act;
   k.has_res = (!det && op.conv.res >= 0) ? 1 : 0;
+  { const char* v = getenv("AQUA_DBG"); k.dbg = v ? atoi(v) : 0; }
   k.acc_pitch = round_up(k.tile_n, 32);
   k.acc_stride = k.mblk * k.acc_pitch;
   k.tmem_cols = pow2_at_least(k.acc_stages * k.acc_stride);
@@ -514,11 +522,12 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
   // ---- B: weights [rows = c_out][K = taps * cpt * 64] (zero padded per tap); rows past c_out are zero-filled
   {
     const int rows = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
-    const uint64_t K = (uint64_t)k.taps * k.cpt * 64;
+    // b_dense: the second copy [c_out][ceil(taps / 4) * 64] with K index = tap * 16 + channel
+    const uint64_t K = k.b_dense ? (uint64_t)(k.taps + 3) / 4 * 64 : (uint64_t)k.taps * k.cpt * 64;
     uint64_t dims[2] = {K, (uint64_t)rows};
     uint64_t str[1] = {K * 2};
     uint32_t box[2] = {64, (uint32_t)(k.tile_n >> k.cshift)};  // cluster: each CTA loads its share of the rows
-    rc = encode_map(c, &k.tmB, op.w_dev, 2, dims, str, box, sw);
+    rc = encode_map(c, &k.tmB, k.b_dense ? op.w_dev_dense : op.w_dev, 2, dims, str, box, sw);
     if (rc) return rc;
   }
   k.bias = op.b_dev;
@@ -646,6 +655,7 @@ void free_plan(aq_ctx* c) {
     if (b.ptr) cudaFree(b.ptr);
   for (auto& o : c->ops) {
     if (o.w_dev) cudaFree(o.w_dev);
+    if (o.w_dev_dense) cudaFree(o.w_dev_dense);
     if (o.b_dev) cudaFree(o.b_dev);
   }
   if (c->pred) cudaFree(c->pred);
@@ -995,6 +1005,16 @@ int aq_plan_end(aq_ctx* c) {
     // weights: rows padded up to n_tiles_n * tile_n are handled by TMA OOB fill; bias is padded here
     CU_CHECK(c, cudaMalloc(&op.w_dev, op.w_host.size() * sizeof(uint16_t)));
     CU_CHECK(c, cudaMemcpyAsync(op.w_dev, op.w_host.data(), op.w_host.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    if (op.kind == OP_CONV && op.conv.k == 3 && op.conv.c_in <= 16) {
+      // dense-tap copy for HALO tilings: K index = tap * 16 + channel, three 64-wide chunks instead of nine
+      const int taps = 9, co = op.conv.c_out;
+      std::vector<uint16_t> dense((size_t)co * 192, 0);
+      for (int o = 0; o < co; ++o)
+        for (int t = 0; t < taps; ++t)
+          memcpy(&dense[(size_t)o * 192 + t * 16], &op.w_host[((size_t)o * taps + t) * 64], 16 * sizeof(uint16_t));
+      CU_CHECK(c, cudaMalloc(&op.w_dev_dense, dense.size() * sizeof(uint16_t)));
+      CU_CHECK(c, cudaMemcpy(op.w_dev_dense, dense.data(), dense.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+    }
     std::vector<float> bias((size_t)kMaxCout, 0.f);  // padded to the largest N any tiling may read
     memcpy(bias.data(), op.b_host.data(), op.b_host.size() * sizeof(float));
     if (k.act == ACT_SILU_FAST)  // the kernel evaluates silu(x) = h + h * tanh(h) with h = acc / 2 + bias / 2

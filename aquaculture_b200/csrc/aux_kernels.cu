@@ -29,52 +29,90 @@ __device__ __forceinline__ int letterbox_sample(const PreParams& p, const uint8_
 }
 
 // One thread per space-to-depth output pixel: 2x2 source pixels x 3 channels -> 16 fp16 (two 16-byte stores).
-// u / 255 -> fp16 comes from a 256-entry shared-memory table built with the same IEEE division + rounding upstream's
-// `.half() / 255` path produces (bit-identical, 12 divisions per thread saved).  Tiles that need no resize and
-// no padding (the reference's 640x640 case) take a vectorised path: per source row the thread's two pixels are
-// six consecutive bytes, read as three aligned 16-bit loads (a warp reads 192 contiguous bytes per row).
+// u / 255 -> fp16 is evaluated as half_rn(float(u) * (1.0f / 255.0f)): for every u in 0..255 this equals both
+// half_rn(u / 255.0f) and upstream's `.half() / 255` (checked exhaustively, tests/test_oracle.py), so neither a
+// division nor a table lookup is needed.  Tiles that need no resize and no padding (the reference's 640x640 case)
+// take a vectorised path: per source row the thread's two pixels are six consecutive bytes, read as three aligned
+// 16-bit loads (a warp reads 192 contiguous bytes per row); two pixels per thread are in flight at once.
+__device__ __forceinline__ uint32_t norm2(uint32_t lo, uint32_t hi) {
+  const float k = 1.0f / 255.0f;
+  const __half2 h = __floats2half2_rn(__fmul_rn((float)lo, k), __fmul_rn((float)hi, k));
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+struct RowSeg { uint32_t w0, w1, w2; };
+
+__device__ __forceinline__ void emit_direct(__half* out, size_t idx, const RowSeg (&r)[2], int bgr) {
+  uint32_t b[2][6];
+#pragma unroll
+  for (int py = 0; py < 2; ++py) {
+    // pixel 0 = bytes 0..2, pixel 1 = bytes 3..5 of the row segment; bgr swaps the outer bytes of each pixel
+    const uint32_t a0 = r[py].w0 & 255u, a1 = r[py].w0 >> 8, a2 = r[py].w1 & 255u, a3 = r[py].w1 >> 8,
+                   a4 = r[py].w2 & 255u, a5 = r[py].w2 >> 8;
+    b[py][0] = bgr ? a2 : a0; b[py][1] = a1; b[py][2] = bgr ? a0 : a2;
+    b[py][3] = bgr ? a5 : a3; b[py][4] = a4; b[py][5] = bgr ? a3 : a5;
+  }
+  uint4 lo, hi;
+  lo.x = norm2(b[0][0], b[0][1]); lo.y = norm2(b[0][2], b[0][3]); lo.z = norm2(b[0][4], b[0][5]);
+  lo.w = norm2(b[1][0], b[1][1]); hi.x = norm2(b[1][2], b[1][3]); hi.y = norm2(b[1][4], b[1][5]);
+  hi.z = 0u; hi.w = 0u;
+  uint4* dst = reinterpret_cast<uint4*>(out + idx * 16);
+  __stcs(dst, lo);   // streamed: the stem conv reads it once
+  __stcs(dst + 1, hi);
+}
+
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreParams p) {
-  __shared__ __half lut[256];
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = __float2half_rn(__fdiv_rn((float)i, 255.0f));
-  __syncthreads();
   const int W2 = p.net_w >> 1, H2 = p.net_h >> 1;
   const size_t total = (size_t)p.n * H2 * W2;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
   const bool direct = !p.resize && p.top == 0 && p.left == 0 && p.new_h == p.net_h && p.new_w == p.net_w && !(p.in_w & 1);
-  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (size_t)gridDim.x * blockDim.x) {
+  if (direct) {
+    // in_h == net_h, in_w == net_w: s2d pixel idx = (n, Y, X) reads bytes [6 * idx' ..) of rows 2Y and 2Y+1
+    const size_t row_bytes = (size_t)p.in_w * 3;
+    auto load = [&](size_t idx, RowSeg (&r)[2]) {
+      const int X = (int)(idx % W2);
+      const size_t t = idx / W2;  // = n * H2 + Y; image n starts at row n * in_h = 2 * n * H2
+      const uint16_t* row = reinterpret_cast<const uint16_t*>(p.src + 2 * t * row_bytes + (size_t)X * 6);
+#pragma unroll
+      for (int py = 0; py < 2; ++py) {
+        const uint16_t* q = reinterpret_cast<const uint16_t*>(reinterpret_cast<const uint8_t*>(row) + py * row_bytes);
+        r[py].w0 = __ldg(q); r[py].w1 = __ldg(q + 1); r[py].w2 = __ldg(q + 2);
+      }
+    };
+    size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; idx + stride < total; idx += 2 * stride) {
+      RowSeg ra[2], rb[2];
+      load(idx, ra);
+      load(idx + stride, rb);
+      emit_direct(p.out_s2d, idx, ra, p.bgr);
+      emit_direct(p.out_s2d, idx + stride, rb, p.bgr);
+    }
+    if (idx < total) {
+      RowSeg ra[2];
+      load(idx, ra);
+      emit_direct(p.out_s2d, idx, ra, p.bgr);
+    }
+    return;
+  }
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
     const int X = (int)(idx % W2);
     const size_t t = idx / W2;
     const int Y = (int)(t % H2);
     const int n = (int)(t / H2);
     const uint8_t* img = p.src + (size_t)n * p.in_h * p.in_w * 3;
-    __align__(16) __half v[16];
-    if (direct) {
+    uint32_t b[12];
 #pragma unroll
-      for (int py = 0; py < 2; ++py) {
-        const uint16_t* row = reinterpret_cast<const uint16_t*>(img + ((size_t)(2 * Y + py) * p.in_w + 2 * X) * 3);
-        const uint32_t w0 = __ldg(row), w1 = __ldg(row + 1), w2 = __ldg(row + 2);
-        // pixel 0 = bytes 0..2, pixel 1 = bytes 3..5 of the row segment; bgr swaps the outer bytes of each pixel
-        const uint32_t a0 = w0 & 255u, a1 = w0 >> 8, a2 = w1 & 255u, a3 = w1 >> 8, a4 = w2 & 255u, a5 = w2 >> 8;
-        v[py * 6 + 0] = lut[p.bgr ? a2 : a0];
-        v[py * 6 + 1] = lut[a1];
-        v[py * 6 + 2] = lut[p.bgr ? a0 : a2];
-        v[py * 6 + 3] = lut[p.bgr ? a5 : a3];
-        v[py * 6 + 4] = lut[a4];
-        v[py * 6 + 5] = lut[p.bgr ? a3 : a5];
-      }
-    } else {
+    for (int py = 0; py < 2; ++py)
 #pragma unroll
-      for (int py = 0; py < 2; ++py)
+      for (int px = 0; px < 2; ++px)
 #pragma unroll
-        for (int px = 0; px < 2; ++px)
-#pragma unroll
-          for (int c = 0; c < 3; ++c) v[(py * 2 + px) * 3 + c] = lut[letterbox_sample(p, img, 2 * Y + py, 2 * X + px, c)];
-    }
-#pragma unroll
-    for (int c = 12; c < 16; ++c) v[c] = __float2half_rn(0.f);
+        for (int c = 0; c < 3; ++c) b[(py * 2 + px) * 3 + c] = (uint32_t)letterbox_sample(p, img, 2 * Y + py, 2 * X + px, c);
+    uint4 lo, hi;
+    lo.x = norm2(b[0], b[1]); lo.y = norm2(b[2], b[3]); lo.z = norm2(b[4], b[5]); lo.w = norm2(b[6], b[7]);
+    hi.x = norm2(b[8], b[9]); hi.y = norm2(b[10], b[11]); hi.z = 0u; hi.w = 0u;
     uint4* dst = reinterpret_cast<uint4*>(p.out_s2d + idx * 16);
-    dst[0] = reinterpret_cast<const uint4*>(v)[0];
-    dst[1] = reinterpret_cast<const uint4*>(v)[1];
+    dst[0] = lo;
+    dst[1] = hi;
   }
 }
 

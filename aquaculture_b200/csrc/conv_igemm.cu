@@ -200,6 +200,7 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
   const uint32_t b_lo0 = ((mc.b_base & 0x3FFFFu) >> 4) | lo_flags, b_slot16 = p.b_slot_bytes >> 4;
   const uint32_t na = p.na, nb = p.nb, acc_stages = p.acc_stages, acc_stride = p.acc_stride;
   const int cpt = p.cpt, n_steps = p.n_steps;
+  const bool b_dense = p.b_dense != 0;
   // K = 16 MMAs that carry data in the last 64-channel chunk (the rest of the chunk is zero padding)
   const int c_in = HALO ? p.a_cin : p.c_in;
   const int kk_last = (c_in - 64 * (cpt - 1) + 15) >> 4;
@@ -291,7 +292,9 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
         uint32_t tap_off = 0;
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap, ++s) {
-          const uint32_t bs = BRES ? (uint32_t)s : rb.slot;
+          // dense weights (c_in <= 16, resident): four taps per 64-wide chunk, K offset 16 elements = 32 bytes
+          const bool dense = BRES && b_dense;
+          const uint32_t bs = BRES ? (dense ? (uint32_t)(tap >> 2) : (uint32_t)s) : rb.slot;
           if (BRES) {
             if (it == 0) TR_WAIT(trwb, mbar_wait(b_full(bs), 0));
           } else {
@@ -299,7 +302,7 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
           }
           tc_fence_after();
           if (leader) {
-            issue(a_lo + tap_off, b_lo0 + bs * b_slot16, kk);
+            issue(a_lo + tap_off, b_lo0 + bs * b_slot16 + (dense ? 2u * (uint32_t)(tap & 3) : 0u), kk);
             if (!BRES) release_b(bs);  // weight slot reusable once these MMAs retire
             if (tap == 8) {
               umma_commit(a_empty(ra.slot));
@@ -401,7 +404,7 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
         rs.advance(n_stg);
         const bool valid = 4 * g + (int)sub < n_chunks;  // warp-uniform
         TR_PT(d0);
-        if (!preloaded && valid) tmem_ld16(ta + g * 64, v);
+        if (!preloaded && valid && !(p.dbg & 8)) tmem_ld16(ta + g * 64, v);
         tmem_ld_wait();
         TR_PT(d1);
         const bool last_of_tile = mb == mblk - 1 && g == n_groups - 1;
@@ -413,8 +416,8 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
         }
         TR_PT(d2);
         // the TMA store that last used this staging buffer must have read it
-        if (gcount >= n_stg) TR_WAIT(trs, named_bar_sync(kBarStgEmpty + buf, kBarStgThreads));
-        if (valid) {
+        if (gcount >= n_stg && !(p.dbg & 32)) TR_WAIT(trs, named_bar_sync(kBarStgEmpty + buf, kBarStgThreads));
+        if (valid && !(p.dbg & 2)) {
           uint32_t b4[16];
           const uint32_t ba = bias0 + (uint32_t)g * 256u;
 #pragma unroll
@@ -448,12 +451,12 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
         if (preloaded) {
           const bool same = g + 1 < n_groups;
           const int ng = same ? g + 1 : 0;
-          if (4 * ng + (int)sub < n_chunks) tmem_ld16((same ? ta : ta + acc_pitch) + ng * 64, v);
+          if (4 * ng + (int)sub < n_chunks && !(p.dbg & 8)) tmem_ld16((same ? ta : ta + acc_pitch) + ng * 64, v);
         }
         TR_PT(d4);
-        fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
+        if (!(p.dbg & 16)) fence_proxy_async_smem();  // staging writes -> visible to the async proxy (TMA)
         TR_PT(d5);
-        named_bar_arrive(kBarStgFull + buf, kBarStgThreads);  // hand the group to the store warp
+        if (!(p.dbg & 32)) named_bar_arrive(kBarStgFull + buf, kBarStgThreads);  // hand the group to the store warp
         TR_PT(d6);
       }
     }
@@ -476,6 +479,8 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
   Ring rs;
   uint32_t k = 0;  // groups stored so far
   int it = 0;
+  const bool halo = (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) && !(p.dbg & 64);
+  const int hp1 = p.a_h + 1;
   for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
     int m_tile, n_idx;
     split_tile(p, tile, m_tile, n_idx);
@@ -483,6 +488,16 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
     const MBlock t0 = mblock_coords(p, m_tile, 0);
     const long long tr0 = TR_NOW();
     long long trw = 0, trr = 0;
+    // HALO: lane L works out where M block L falls in the stack of images (one division) while the epilogue is
+    // still filling the first group, so the issuing lane's path after the barrier is the TMA instruction alone
+    // (one scalar warp runs ~8 clk per dependent instruction: the division + image loop cost ~1k clk per store)
+    int pre_n = 0, pre_ys = 0;
+    if (halo) {
+      const int mbl = (int)lane < mblk ? (int)lane : 0;
+      const int y0l = t0.y0 + (mbl >> (p.mx >> 1)) * 16;
+      pre_n = y0l / hp1;
+      pre_ys = y0l - (pre_n * hp1 + 1);
+    }
     for (int mb = 0; mb < mblk; ++mb) {
       MBlock t = t0;
       if (p.mode == CONV_MODE_TAP) {
@@ -493,12 +508,24 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
         t.x0 += jx * 8;
         t.y0 += jy * 16;
       }
+      const int img = __shfl_sync(0xffffffffu, pre_n, mb), ys = __shfl_sync(0xffffffffu, pre_ys, mb);
+      // the 16 rows lie inside one image (plus, at most, the zero row below it, which TMA clips)
+      const bool one_image = halo && ys >= 0 && ys + 15 <= p.a_h;
       for (int g = 0; g < n_groups; ++g, ++k) {
         const uint32_t buf = rs.slot;
         rs.advance(n_stg);
+        if (p.dbg & 32) continue;
         TR_WAIT(trw, named_bar_sync(kBarStgFull + buf, kBarStgThreads));
         if (lane == 0) {
-          store_group(p, t, stg_base + buf * (kTileM * 128), n0 + g * 64);
+          if (p.dbg & 1) {
+          } else if (one_image) {
+            if (img < p.a_n) {
+              if (p.has_res) tma_reduce_add_4d(&p.tmOut, stg_base + buf * (kTileM * 128), n0 + g * 64, t.x0, ys, img);
+              else tma_store_4d(&p.tmOut, stg_base + buf * (kTileM * 128), n0 + g * 64, t.x0, ys, img);
+            }
+          } else {
+            store_group(p, t, stg_base + buf * (kTileM * 128), n0 + g * 64);
+          }
           tma_store_commit();
           // all but the latest n_stg - 2 stores have read their buffers -> the buffer of store k - (n_stg - 2),
           // which group k + 2 will fill, is free
@@ -743,10 +770,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     // =========================== weight producer ===========================
     if (p.b_res) {
       // all K steps of the (single) N tile stay resident: load once, never released
-      for (int s = 0; s < p.n_steps; ++s) {
+      const int n_res = p.b_dense ? p.nb : p.n_steps;
+      for (int s = 0; s < n_res; ++s) {
         if (elect_one()) {
           mbar_arrive_expect_tx(b_full(s), p.b_tx_bytes);
-          tma_load_2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), weight_chunk(p, s) * 64, 0);
+          tma_load_2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), (p.b_dense ? s : weight_chunk(p, s)) * 64, 0);
         }
       }
     } else {

@@ -76,6 +76,7 @@ struct alignas(64) ConvKParams {
   const __half* a_src;     // HALO: source slice (first channel), geometry of the source buffer
   int a_n, a_h, a_w, a_ct, a_cin;
   int na, nb, b_res, n_stg, acc_stages;
+  int b_dense;             // HALO, c_in <= 16, resident: weight slot = tap / 4, K offset = (tap % 4) * 16 (see api.cu Cand)
   int n_mma;               // MMA-issuing threads (2 when the tile has more than one M block)
   int tile_n, n_tiles_n, groups;  // UMMA N, N tiles, 64-channel store groups per tile
   int m_tiles;                    // tiles along M
@@ -87,6 +88,7 @@ struct alignas(64) ConvKParams {
   int up_chunks, up_hs;  // leading 64-channel chunks that come from tmUp; rows of the half-resolution source
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;
+  int dbg;  // AQUA_DBG attribution experiments (results wrong): 1 = no TMA stores issued, 2 = epilogue skips math + staging, 4 = one store per tile only
   uint32_t a_slot_bytes, b_slot_bytes, stg_bytes;
   uint32_t a_tx_bytes, b_tx_bytes;  // bytes one slot fill delivers
   uint32_t tmem_cols, acc_stride, acc_pitch;  // TMEM columns: allocation, per accumulator stage, per M block

@@ -125,6 +125,15 @@ def test_conv3x3_s2_channel_slice(ctx):
     run_conv_case(ctx, 2, 40, 40, 192, 192, 3, 2, src_ct=384, src_off=192, dst_ct=384, dst_off=0)
 
 
+# c_in <= 16 (the space-to-depth stem): resident weights with four taps per 64-wide chunk (api.cu Cand::b_dense);
+# every halo arrangement incl. the 4x1 one the stem runs with, c_in 8 and 16, a source channel slice
+@pytest.mark.parametrize("mblk", [1, 2, 4])
+@pytest.mark.parametrize("B,H,W,ci,co,src_ct,src_off", [(2, 64, 64, 16, 48, None, 0), (1, 40, 72, 8, 32, None, 0),
+                                                          (2, 32, 48, 16, 64, 32, 16)])
+def test_conv3x3_s1_dense_taps(ctx, mblk, B, H, W, ci, co, src_ct, src_off):
+    run_conv_case(ctx, B, H, W, ci, co, 3, 1, mode=1, mblk=mblk, act=2, src_ct=src_ct, src_off=src_off)
+
+
 # every A-feeding variant of the 3x3/s1 conv: halo patch with 1 or 2 M blocks (side by side / stacked), one
 # box per tap with 1 or 2 M blocks; channel counts completed by TMA zero fill (16, 48, 96)
 @pytest.mark.parametrize("mode,mblk", [(1, 1), (1, 2), (2, 1), (2, 2)])

@@ -137,3 +137,13 @@ def test_scale_boxes_clip_round():
     lines = OL.label_lines(det, (640, 640), (1024, 1024))
     c, x, y, w, h, conf = (float(v) for v in lines[0].split())
     assert (c, conf) == (2.0, 0.9) and x == 0.5 and w == 1.0 and abs(y - (5 + 1024) / 2 / 1024) < 1e-6
+
+
+def test_u8_over_255_fp16_equals_reciprocal_multiply():
+    """preprocess_kernel evaluates u/255 -> fp16 as half(float(u) * (1/255f)); upstream computes `.half() / 255`
+    (detect.py::run).  Exhaustive over the 256 inputs: all three roundings agree."""
+    u = np.arange(256, dtype=np.float32)
+    by_mul = (u * np.float32(1.0 / 255.0)).astype(np.float16)
+    by_div = (u / np.float32(255.0)).astype(np.float16)
+    upstream = (torch.arange(256, dtype=torch.uint8).half() / 255).numpy()
+    assert (by_mul == by_div).all() and (by_mul == upstream).all()

@@ -8,7 +8,8 @@ run() { # name, pytest -k expr
 }
 run conv1x1 "conv1x1 and not folded"
 run folded "folded_upsample"
-run conv3x3s1 "conv3x3_s1 and not variants or residual"
+run conv3x3s1 "conv3x3_s1 and not variants and not dense or residual"
+run dense "dense_taps"
 run variants "s1_variants"
 run s2variants "s2_variants"
 run mblk "mblk_variants or fast_silu"

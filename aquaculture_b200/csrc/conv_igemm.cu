@@ -167,6 +167,77 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
   }
 }
 
+// Per-image segments of a halo patch in "tall" coordinates (images stacked with one zero row above each):
+// rows R0 .. R0 + ph - 1 cut where an image ends.  Worked out ONCE per tile (one runtime division per segment;
+// a scalar warp runs ~8 clk per dependent instruction) and reused by every chunk / parity plane of the tile.
+constexpr int kMaxSeg = 4;
+struct PatchSegs {
+  int n[kMaxSeg], y[kMaxSeg], len[kMaxSeg];
+  int count;  // > kMaxSeg: maps so short that the patch spans more images -- callers take the general loop
+};
+__device__ __forceinline__ PatchSegs patch_segments(int R0, int ph, int a_h) {
+  PatchSegs sg;
+  const int hp1 = a_h + 1;
+  int R = R0, rem = ph, k = 0;
+#pragma unroll
+  for (int i = 0; i < kMaxSeg; ++i) {
+    sg.n[i] = sg.y[i] = sg.len[i] = 0;
+    if (rem > 0) {
+      const int n = R / hp1;
+      const int y = R - n * hp1 - 1;  // -1 = the zero row above image n
+      int len = a_h - y;              // rows y .. H-1
+      if (len > rem) len = rem;
+      sg.n[i] = n; sg.y[i] = y; sg.len[i] = len;
+      R += len;
+      rem -= len;
+      ++k;
+    }
+  }
+  sg.count = rem > 0 ? kMaxSeg + 1 : k;
+  return sg;
+}
+// Issue the boxes of one patch: ld(hb, dst, y, n) loads 32 >> hb rows of image n starting at row y.
+template <class F>
+__device__ __forceinline__ void patch_issue(const PatchSegs& sg, int R0, int ph, int a_h, uint32_t dst, uint32_t row_bytes, F&& ld) {
+  if (sg.count <= kMaxSeg) {
+#pragma unroll
+    for (int i = 0; i < kMaxSeg; ++i) {
+      if (i < sg.count) {
+        int y = sg.y[i];
+#pragma unroll
+        for (int hb = 0; hb < 6; ++hb) {
+          const int h = 32 >> hb;
+          if (sg.len[i] & h) {
+            ld(hb, dst, y, sg.n[i]);
+            dst += (uint32_t)h * row_bytes;
+            y += h;
+          }
+        }
+      }
+    }
+    return;
+  }
+  const int hp1 = a_h + 1;
+  int R = R0, rem = ph;
+  while (rem > 0) {
+    const int n = R / hp1;
+    int y = R - n * hp1 - 1;
+    int len = a_h - y;
+    if (len > rem) len = rem;
+    R += len;
+    rem -= len;
+#pragma unroll
+    for (int hb = 0; hb < 6; ++hb) {
+      const int h = 32 >> hb;
+      if (len & h) {
+        ld(hb, dst, y, n);
+        dst += (uint32_t)h * row_bytes;
+        y += h;
+      }
+    }
+  }
+}
+
 // Barrier addresses inside the static `bars` array (see the kernel for the layout).
 struct MmaCtx {
   uint32_t bar0, a_base, b_base, tmem_base;
@@ -629,7 +700,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       // 2-5 TMA instructions instead of ~2600 cp.async (probe T9: 18x18 patch round trip ~0.8k clk).
       {
         griddep_wait();  // activations are written by the previous kernel
-        const int hp1 = p.a_h + 1;
+
         const uint32_t row_bytes = (uint32_t)p.pw * 128u;
         Ring ra;
         int it = 0;
@@ -640,30 +711,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const long long tr0 = TR_NOW();
           long long trw = 0;
           const int xl = t0.x0 - 1;
+          // R = -1 (above the first zero row) resolves to n = 0, y = -2
+          const PatchSegs sg = patch_segments(t0.y0 - 1, p.ph, p.a_h);
           for (int c = 0; c < p.cpt; ++c, ra.advance(p.na)) {
             const uint32_t slot = ra.slot;
             TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
             if (!elect_one()) continue;
             mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
-            uint32_t dst = a_base + slot * p.a_slot_bytes;
-            int R = t0.y0 - 1, rem = p.ph;  // R = -1 (above the first zero row) resolves to n = 0, y = -2
-            while (rem > 0) {
-              const int n = R / hp1;
-              int y = R - n * hp1 - 1;  // -1 = the zero row above image n
-              int len = p.a_h - y;      // rows y .. H-1
-              if (len > rem) len = rem;
-              R += len;
-              rem -= len;
-#pragma unroll
-              for (int hb = 0; hb < 6; ++hb) {
-                const int h = 32 >> hb;
-                if (len & h) {
-                  tma_load_4d(dst, &p.tmH[hb], a_full(slot), c * 64, xl, y, n);
-                  dst += (uint32_t)h * row_bytes;
-                  y += h;
-                }
-              }
-            }
+            patch_issue(sg, t0.y0 - 1, p.ph, p.a_h, a_base + slot * p.a_slot_bytes, row_bytes,
+                        [&](int hb, uint32_t dst, int y, int n) { tma_load_4d(dst, &p.tmH[hb], a_full(slot), c * 64, xl, y, n); });
           }
           if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
         }
@@ -673,7 +729,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       // A plane holds half-resolution pixels xh = x0-1 .. x0+8mx-1, rows T = y0-1 .. y0+16my-1 of the tall plane
       // (per image: one zero row = yh -1, then yh 0 .. H/2-1), cut into per-image segments exactly like HALO.
       griddep_wait();
-      const int hp1 = p.a_h + 1;  // a_h = H/2 = output rows per image
+
       const uint32_t row_bytes = (uint32_t)p.pw * 128u;
       Ring ra;
       int it = 0;
@@ -684,6 +740,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
         const long long tr0 = TR_NOW();
         long long trw = 0;
         const int xl = t0.x0 - 1;
+        const PatchSegs sg = patch_segments(t0.y0 - 1, p.ph, p.a_h);
         for (int cq = 0; cq < p.cpt * 4; ++cq, ra.advance(p.na)) {
           const int c = cq >> 2, q = cq & 3;
           const int yp = q < 2 ? 1 : 0, xp = (q & 1) ? 0 : 1;
@@ -691,25 +748,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
           if (!elect_one()) continue;
           mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
-          uint32_t dst = a_base + slot * p.a_slot_bytes;
-          int R = t0.y0 - 1, rem = p.ph;
-          while (rem > 0) {
-            const int n = R / hp1;
-            int y = R - n * hp1 - 1;  // -1 = the zero row above image n
-            int len = p.a_h - y;
-            if (len > rem) len = rem;
-            R += len;
-            rem -= len;
-#pragma unroll
-            for (int hb = 0; hb < 6; ++hb) {
-              const int h = 32 >> hb;
-              if (len & h) {
-                tma_load_5d(dst, xp ? &p.tmH2[hb] : &p.tmH[hb], a_full(slot), c * 64, xl, yp, y, n);
-                dst += (uint32_t)h * row_bytes;
-                y += h;
-              }
-            }
-          }
+          patch_issue(sg, t0.y0 - 1, p.ph, p.a_h, a_base + slot * p.a_slot_bytes, row_bytes, [&](int hb, uint32_t dst, int y, int n) {
+            tma_load_5d(dst, xp ? &p.tmH2[hb] : &p.tmH[hb], a_full(slot), c * 64, xl, yp, y, n);
+          });
         }
         if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
       }

@@ -180,6 +180,7 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version/info lines must not land on stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     sd = weights.synthetic_state(NC, 0)
@@ -249,6 +250,47 @@ def main():
     ms_fwd = f0.elapsed_time(f1) / args.steps
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- (2b) the HBM-bound helper kernels alone (north_star: achieved GB/s for pre/post-processing vs B200 peak)
+    aux = {}
+    if rank == 0:
+        reps = 20
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                ctx.call("aq_preprocess", C.c_void_p(dev_sets[0].data_ptr()), BATCH, IMG, IMG, 1, 1, sarg)
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            for i in range(reps):
+                ctx.call("aq_preprocess", C.c_void_p(dev_sets[i % NSETS].data_ptr()), BATCH, IMG, IMG, 1, 1, sarg)
+            p1.record()
+        stream.synchronize()
+        us_pre = 1e3 * p0.elapsed_time(p1) / reps
+        pre_bytes = BATCH * (IMG * IMG * 3 + (IMG // 2) * (IMG // 2) * 16 * 2)  # u8 HWC in, fp16 space-to-depth (16 ch) out
+        # NMS on the plan's own predictions (left by the last forward): reads (B, 25200, 5+nc) fp32, writes <= 1000 x 6 per tile
+        rows = 3 * ((IMG // 8) ** 2 + (IMG // 16) ** 2 + (IMG // 32) ** 2)
+        dets_d = torch.zeros(BATCH, det.max_det, 6, device="cuda")
+        cnt_d = torch.zeros(BATCH, dtype=torch.int32, device="cuda")
+        keep_d = torch.zeros(BATCH, det.max_det, dtype=torch.int32, device="cuda")
+        nms_args = (None, BATCH, rows, 5 + NC, C.c_float(0.25), C.c_double(0.45), det.max_det, 0, None, 0, C.c_float(7680.0), 30000,
+                    C.c_void_p(dets_d.data_ptr()), C.c_void_p(cnt_d.data_ptr()), C.c_void_p(keep_d.data_ptr()), sarg)
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                ctx.call("aq_nms", *nms_args)
+            n0_, n1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n0_.record()
+            for _ in range(reps):
+                ctx.call("aq_nms", *nms_args)
+            n1_.record()
+        stream.synchronize()
+        us_nms = 1e3 * n0_.elapsed_time(n1_) / reps
+        nms_bytes = BATCH * rows * (5 + NC) * 4
+        hbm = measured_peaks()["hbm"]
+        aux = {"preprocess_kernel": {"us": round(us_pre, 1), "algorithmic_bytes": pre_bytes,
+                                     "achieved_gbs": round(pre_bytes / us_pre / 1e3, 1), "frac_of_hbm_peak": round(pre_bytes / us_pre / 1e3 / hbm, 3)},
+               "nms_kernel": {"us": round(us_nms, 1), "algorithmic_bytes": nms_bytes,
+                              "achieved_gbs": round(nms_bytes / us_nms / 1e3, 1), "frac_of_hbm_peak": round(nms_bytes / us_nms / 1e3 / hbm, 3),
+                              "note": "compare/latency bound (sort + IoU bitmask + serial greedy scan), not bandwidth bound"},
+               "hbm_peak_gbs": hbm}
+
     # ---- (3) e2e: pinned host tiles -> label files, through the public API
     tmp = tempfile.mkdtemp(prefix=f"aq_bench_r{rank}_")
     stems = [[os.path.join(tmp, tiles.tile_stem(rank + world * (s * BATCH + i)) + ".txt") for i in range(BATCH)]
@@ -315,6 +357,7 @@ def main():
                                         f"frac_of_burst {round(achieved / peaks['burst'], 4)}, frac_of_nominal_2250 {round(achieved / 2250.0, 4)}",
                          "ms_per_conv_stack": round(ms_fwd, 4)},
             "clocks": clocks,
+            "aux_kernels": aux,
             "counters": {"tiles": int(counters[0]), "label_files_last_e2e_pass": int(counters[1]), "detections_last_batch": int(counters[2])},
         }
         if not args.no_cpu_baseline and world == 1:

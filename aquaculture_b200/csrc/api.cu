@@ -180,6 +180,7 @@ int pow2_at_least(int v) {
 struct Cand {
   int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
   int cluster = 1;  // CTAs per thread-block cluster sharing each weight tile by multicast (1, 2, 4)
+  int pref = 0;     // shared-memory split: 0 = staging / activation rings first, 1 = weight ring first (streamed weights)
   int b_dense = 0;  // HALO with c_in <= 16: four taps share one 64-wide weight chunk (resident weights = 3 slots, not 9)
   // derived
   int tiles_x = 1, tiles_y = 1, m_tiles = 0, pw = 0, ph = 0;
@@ -257,13 +258,28 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   };
   // Growth order: a third staging buffer first (a TMA store needs ~1-2k clk before its shared-memory source may
   // be overwritten, so two buffers serialise the epilogue on it), then deeper operand rings.
-  grow(cd.n_stg, 3, stg);
-  if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
-  if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
-  if (!cd.b_res) grow(cd.nb, 5, b_slot);
-  grow(cd.n_stg, 4, stg);
-  grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
-  if (!cd.b_res) grow(cd.nb, 12, b_slot);
+  if (cd.pref == 1) {
+    // Streamed weights are latency bound through a shallow ring: a slot is busy from its TMA issue (~1-1.5k clk to
+    // land) until the MMAs that read it retire, so nb slots carry nb - 1 tiles in flight; layers whose operand
+    // traffic L2 -> SM is the limit (3x3 convs with few M blocks per tile) want the bytes in the weight ring
+    // rather than in staging buffers.  The autotuner times both splits.
+    if (cd.b_res) return;
+    if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
+    grow(cd.nb, 6, b_slot);
+    grow(cd.n_stg, 3, stg);
+    if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
+    grow(cd.nb, 12, b_slot);
+    grow(cd.n_stg, 4, stg);
+    grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
+  } else {
+    grow(cd.n_stg, 3, stg);
+    if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
+    if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
+    if (!cd.b_res) grow(cd.nb, 5, b_slot);
+    grow(cd.n_stg, 4, stg);
+    grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
+    if (!cd.b_res) grow(cd.nb, 12, b_slot);
+  }
   // ---- cost
   const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
   const double a_bytes = (double)n_groups * cd.a_tx;
@@ -391,10 +407,18 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
         // measured (profiles/r1_cluster_multicast_sweep.txt): sharing weight tiles by multicast does not speed any
         // layer up (cluster 2: +-1 %, cluster 4: slower), so clusters are only planned on request
         if (cl != (want_cluster > 0 ? want_cluster : 1)) continue;
-        Cand cd = cd0;
-        cd.cluster = cl;
-        fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
-        if (cd.ok) choices.push_back({tn, ntn, cd});
+        for (int pref = 0; pref < 2; ++pref) {
+          Cand cd = cd0;
+          cd.cluster = cl;
+          cd.pref = pref;
+          fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+          if (!cd.ok) continue;
+          if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
+            const Cand& o = choices.back().cd;
+            if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg) continue;
+          }
+          choices.push_back({tn, ntn, cd});
+        }
       }
     }
   }

@@ -86,6 +86,8 @@ struct aq_ctx {
   int tab_in_h = -1, tab_in_w = -1;
   void* tab_dev = nullptr;
   PreParams pre{};
+  void* stats_scratch = nullptr;  // aq_tile_stats: column sums + TileStats
+  size_t stats_bytes = 0;
   // nms scratch
   void* nms_scratch = nullptr;
   size_t nms_scratch_bytes = 0;
@@ -750,6 +752,7 @@ int setup_preprocess(aq_ctx* c, int in_h, int in_w) {
   p.left = (int)nearbyint(dw - 0.1);
   p.resize = (p.new_w != in_w || p.new_h != in_h) ? 1 : 0;
   p.in_h = in_h; p.in_w = in_w; p.net_h = c->net_h; p.net_w = c->net_w;
+  p.row_pitch = (size_t)in_w * 3; p.windowed = 0; p.wins_y = 1; p.win0 = 0;
   if (c->tab_dev) { cudaFree(c->tab_dev); c->tab_dev = nullptr; }
   if (p.resize) {
     std::vector<int> x0, x1, y0, y1;
@@ -819,6 +822,8 @@ int stage_tiles(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int 
 
 int preprocess_slot(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, int bgr, int src_is_device, int slot,
                     cudaStream_t s);
+int forward_nms_d2h(aq_ctx* c, int n, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+                    int n_classes, float* dets_host, int* counts_host, cudaStream_t s, int slot);
 
 }  // namespace
 
@@ -892,6 +897,7 @@ void aq_destroy(aq_ctx* c) {
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->tab_dev) cudaFree(c->tab_dev);
   if (c->nms_scratch) cudaFree(c->nms_scratch);
+  if (c->stats_scratch) cudaFree(c->stats_scratch);
   if (c->nms_dets) cudaFree(c->nms_dets);
   if (c->nms_counts) cudaFree(c->nms_counts);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -1357,6 +1363,16 @@ int aq_detect_submit(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w,
   c->pipe_slot ^= 1;
   int rc = preprocess_slot(c, tiles, n, in_h, in_w, bgr, src_is_device, slot, s);
   if (rc) return rc;
+  return forward_nms_d2h(c, n, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, dets_host, counts_host, s, slot);
+}
+
+}  // extern "C"
+
+namespace {
+// conv stack + Detect decode + NMS + async copy of the detections to the host; records ev_done[slot]
+int forward_nms_d2h(aq_ctx* c, int n, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+                    int n_classes, float* dets_host, int* counts_host, cudaStream_t s, int slot) {
+  int rc;
   if ((rc = aq_forward(c, s))) return rc;
   const size_t cap = (size_t)c->batch * max_det;
   if (cap > c->nms_out_cap) {
@@ -1374,6 +1390,90 @@ int aq_detect_submit(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w,
   CU_CHECK(c, cudaMemcpyAsync(dets_host, c->nms_dets, (size_t)n * max_det * 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaEventRecord(c->ev_done[slot], s));
   return slot;  // ticket for aq_detect_wait
+}
+
+// PreParams for window `win0 ..` of a device-resident raster (checks the grid; see aux_kernels.cuh)
+int window_params(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0, int n,
+                  int bgr, PreParams* out) {
+  if (!c->planned) return fail(c, AQ_ERR_STATE, "windows before plan_end");
+  if (!raster_dev || win_h <= 0 || win_w <= 0 || raster_h < win_h || raster_w < win_w)
+    return fail(c, AQ_ERR_ARG, "windows: raster %dx%d, window %dx%d", raster_h, raster_w, win_h, win_w);
+  const int wins_x = raster_w / win_w, wins_y = raster_h / win_h;  // full windows only: the ragged right / bottom
+  if (n <= 0 || n > c->batch || win0 < 0 || win0 + n > wins_x * wins_y)  // strips go through the plain tile path
+    return fail(c, AQ_ERR_ARG, "windows: [%d, %d) outside the %d x %d grid of full windows (plan batch %d)", win0, win0 + n, wins_x, wins_y, c->batch);
+  int rc = setup_preprocess(c, win_h, win_w);
+  if (rc) return rc;
+  PreParams p = c->pre;
+  p.src = raster_dev; p.n = n; p.bgr = bgr;
+  p.row_pitch = (size_t)raster_w * 3; p.windowed = 1; p.wins_y = wins_y; p.win0 = win0;
+  p.out_s2d = nullptr; p.out_u8 = nullptr;
+  *out = p;
+  return AQ_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int aq_detect_windows(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0, int n,
+                      int bgr, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+                      int n_classes, float* dets_host, int* counts_host, void* stream) {
+  if (!c || !dets_host || !counts_host) return AQ_ERR_ARG;
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  PreParams p;
+  int rc = window_params(c, raster_dev, raster_h, raster_w, win_h, win_w, win0, n, bgr, &p);
+  if (rc) return rc;
+  p.out_s2d = c->bufs[0].ptr;
+  CU_CHECK(c, launch_preprocess(p, s));
+  const int slot = c->pipe_slot;
+  c->pipe_slot ^= 1;
+  rc = forward_nms_d2h(c, n, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, dets_host, counts_host, s, slot);
+  if (rc < 0) return rc;
+  CU_CHECK(c, cudaStreamSynchronize(s));
+  return AQ_OK;
+}
+
+int aq_preprocess_windows_u8(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,
+                             int n, int bgr, uint8_t* out_dev, void* stream) {
+  if (!c || !out_dev) return AQ_ERR_ARG;
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  PreParams p;
+  int rc = window_params(c, raster_dev, raster_h, raster_w, win_h, win_w, win0, n, bgr, &p);
+  if (rc) return rc;
+  p.out_u8 = out_dev;
+  CU_CHECK(c, launch_preprocess_u8(p, s));
+  return AQ_OK;
+}
+
+int aq_tile_stats(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w, int win0,
+                  int* stats_host, void* stream) {
+  if (!c || !src_dev || !stats_host || n <= 0 || in_h <= 0 || in_w <= 0) return AQ_ERR_ARG;
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  PreParams p{};
+  p.src = src_dev; p.n = n; p.bgr = bgr; p.in_h = in_h; p.in_w = in_w;
+  p.row_pitch = (size_t)in_w * 3; p.wins_y = 1;
+  if (raster_h > 0) {  // windows of a raster
+    const int wins_x = raster_w / in_w, wins_y = raster_h / in_h;
+    if (raster_h < in_h || raster_w < in_w || win0 < 0 || win0 + n > wins_x * wins_y)
+      return fail(c, AQ_ERR_ARG, "tile_stats: windows [%d, %d) outside the %d x %d grid", win0, win0 + n, wins_x, wins_y);
+    p.row_pitch = (size_t)raster_w * 3; p.windowed = 1; p.wins_y = wins_y; p.win0 = win0;
+  }
+  const size_t need = (size_t)n * in_w * sizeof(unsigned int) + (size_t)n * sizeof(TileStats);
+  if (need > c->stats_bytes) {
+    if (c->stats_scratch) cudaFree(c->stats_scratch);
+    c->stats_scratch = nullptr;
+    CU_CHECK(c, cudaMalloc(&c->stats_scratch, need));
+    c->stats_bytes = need;
+  }
+  unsigned int* col = (unsigned int*)c->stats_scratch;
+  TileStats* st = (TileStats*)(col + (size_t)n * in_w);
+  cudaError_t e = launch_tile_stats(p, col, st, s);
+  if (e != cudaSuccess) return fail(c, e == cudaErrorInvalidValue ? AQ_ERR_UNSUPPORTED : AQ_ERR_CUDA, "tile_stats: %s (tiles up to 2048 x 4096)", cudaGetErrorString(e));
+  CU_CHECK(c, cudaMemcpyAsync(stats_host, st, (size_t)n * sizeof(TileStats), cudaMemcpyDeviceToHost, s));
+  CU_CHECK(c, cudaStreamSynchronize(s));
+  return AQ_OK;
 }
 
 int aq_detect_wait(aq_ctx* c, int ticket) {

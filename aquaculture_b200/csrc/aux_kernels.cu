@@ -12,17 +12,23 @@ namespace {
 // One letterboxed uint8 sample (net coordinates y, x; rgb channel c), bit-exact with cv2:
 //   horizontal pass  S = p[x0]*ax0 + p[x1]*ax1              (int32, weights sum to 2048)
 //   vertical pass    out = (((ay0*(S0>>4))>>16) + ((ay1*(S1>>4))>>16) + 2) >> 2
+__device__ __forceinline__ const uint8_t* tile_base(const PreParams& p, int n) {
+  if (!p.windowed) return p.src + (size_t)n * p.in_h * p.row_pitch;
+  const int w = p.win0 + n, ix = w / p.wins_y, iy = w - ix * p.wins_y;
+  return p.src + (size_t)iy * p.in_h * p.row_pitch + (size_t)ix * p.in_w * 3;
+}
+
 __device__ __forceinline__ int letterbox_sample(const PreParams& p, const uint8_t* img, int y, int x, int c) {
   const int ry = y - p.top, rx = x - p.left;
   if (ry < 0 || ry >= p.new_h || rx < 0 || rx >= p.new_w) return 114;
   const int sc = p.bgr ? 2 - c : c;
-  if (!p.resize) return img[((size_t)ry * p.in_w + rx) * 3 + sc];
+  if (!p.resize) return img[(size_t)ry * p.row_pitch + rx * 3 + sc];
   const int xa = __ldg(p.x0 + rx), xb = __ldg(p.x1 + rx);
   const int wa = __ldg(p.ax0 + rx), wb = __ldg(p.ax1 + rx);
   const int ya = __ldg(p.y0 + ry), yb = __ldg(p.y1 + ry);
   const int va = __ldg(p.ay0 + ry), vb = __ldg(p.ay1 + ry);
-  const uint8_t* r0 = img + (size_t)ya * p.in_w * 3;
-  const uint8_t* r1 = img + (size_t)yb * p.in_w * 3;
+  const uint8_t* r0 = img + (size_t)ya * p.row_pitch;
+  const uint8_t* r1 = img + (size_t)yb * p.row_pitch;
   const int s0 = __ldg(r0 + xa * 3 + sc) * wa + __ldg(r0 + xb * 3 + sc) * wb;
   const int s1 = __ldg(r1 + xa * 3 + sc) * wa + __ldg(r1 + xb * 3 + sc) * wb;
   return (((va * (s0 >> 4)) >> 16) + ((vb * (s1 >> 4)) >> 16) + 2) >> 2;
@@ -65,7 +71,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreParams p) {
   const int W2 = p.net_w >> 1, H2 = p.net_h >> 1;
   const size_t total = (size_t)p.n * H2 * W2;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  const bool direct = !p.resize && p.top == 0 && p.left == 0 && p.new_h == p.net_h && p.new_w == p.net_w && !(p.in_w & 1);
+  const bool direct = !p.windowed && !p.resize && p.top == 0 && p.left == 0 && p.new_h == p.net_h && p.new_w == p.net_w && !(p.in_w & 1);
   if (direct) {
     // in_h == net_h, in_w == net_w: s2d pixel idx = (n, Y, X) reads bytes [6 * idx' ..) of rows 2Y and 2Y+1
     const size_t row_bytes = (size_t)p.in_w * 3;
@@ -99,7 +105,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreParams p) {
     const size_t t = idx / W2;
     const int Y = (int)(t % H2);
     const int n = (int)(t / H2);
-    const uint8_t* img = p.src + (size_t)n * p.in_h * p.in_w * 3;
+    const uint8_t* img = tile_base(p, n);
     uint32_t b[12];
 #pragma unroll
     for (int py = 0; py < 2; ++py)
@@ -126,8 +132,85 @@ __global__ void __launch_bounds__(256) preprocess_u8_kernel(const PreParams p) {
     t /= p.net_w;
     const int y = (int)(t % p.net_h);
     const int n = (int)(t / p.net_h);
-    p.out_u8[idx] = (uint8_t)letterbox_sample(p, p.src + (size_t)n * p.in_h * p.in_w * 3, y, x, c);
+    p.out_u8[idx] = (uint8_t)letterbox_sample(p, tile_base(p, n), y, x, c);
   }
+}
+
+// ---------------------------------------------------------------- blank-tile statistics
+// grid (ceil(in_h / kStatRows), n), 256 threads.  A CTA walks kStatRows rows of one tile: thread t owns columns
+// t, t + 256, ... (a warp reads 96 contiguous bytes per row), keeps their partial column sums in registers, and the
+// CTA reduces each row's sum (blank-row test) and the luminance extrema.  Column sums meet in `col_sums` (one
+// atomicAdd per column per CTA); tile_stats_finish counts the blank columns.
+constexpr int kStatRows = 16;
+constexpr int kStatColSlots = 8;  // columns per thread: tiles up to 2048 pixels wide
+
+__global__ void __launch_bounds__(256) tile_stats_kernel(const PreParams p, unsigned int* col_sums, TileStats* stats) {
+  __shared__ unsigned int s_row[kStatRows];
+  __shared__ int s_min, s_max;
+  const int n = blockIdx.y, y0 = blockIdx.x * kStatRows;
+  const uint8_t* img = tile_base(p, n);
+  if (threadIdx.x < kStatRows) s_row[threadIdx.x] = 0;
+  if (threadIdx.x == 0) { s_min = 255; s_max = 0; }
+  __syncthreads();
+  unsigned int col[kStatColSlots];
+#pragma unroll
+  for (int k = 0; k < kStatColSlots; ++k) col[k] = 0;
+  int lmin = 255, lmax = 0;
+  const int rows = min(kStatRows, p.in_h - y0);
+  for (int r = 0; r < rows; ++r) {
+    const uint8_t* row = img + (size_t)(y0 + r) * p.row_pitch;
+    unsigned int rs = 0;
+#pragma unroll
+    for (int k = 0; k < kStatColSlots; ++k) {
+      const int x = threadIdx.x + 256 * k;
+      if (x < p.in_w) {
+        const unsigned int c0 = __ldg(row + 3 * x), c1 = __ldg(row + 3 * x + 1), c2 = __ldg(row + 3 * x + 2);
+        const unsigned int R = p.bgr ? c2 : c0, B = p.bgr ? c0 : c2;
+        const int L = (int)((R * 19595u + c1 * 38470u + B * 7471u + 0x8000u) >> 16);  // PIL ImageConvert rgb2l
+        lmin = min(lmin, L);
+        lmax = max(lmax, L);
+        const unsigned int s3 = c0 + c1 + c2;
+        col[k] += s3;
+        rs += s3;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s_row[r], rs);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+    lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(&s_min, lmin); atomicMax(&s_max, lmax); }
+#pragma unroll
+  for (int k = 0; k < kStatColSlots; ++k) {
+    const int x = threadIdx.x + 256 * k;
+    if (x < p.in_w) atomicAdd(&col_sums[(size_t)n * p.in_w + x], col[k]);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int blank = 0;
+    for (int r = 0; r < rows; ++r) blank += s_row[r] >= 750u * (unsigned int)p.in_w;  // mean over (W, 3) >= 250
+    if (blank) atomicAdd(&stats[n].blank_rows, blank);
+    atomicMin(&stats[n].l_min, s_min);
+    atomicMax(&stats[n].l_max, s_max);
+  }
+}
+
+__global__ void __launch_bounds__(256) tile_stats_init(TileStats* stats, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) stats[i] = TileStats{255, 0, 0, 0};
+}
+
+__global__ void __launch_bounds__(256) tile_stats_finish(const unsigned int* col_sums, TileStats* stats, int in_h, int in_w) {
+  const int n = blockIdx.x;
+  int blank = 0;
+  for (int x = threadIdx.x; x < in_w; x += blockDim.x) blank += col_sums[(size_t)n * in_w + x] >= 750u * (unsigned int)in_h;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) blank += __shfl_xor_sync(0xffffffffu, blank, o);
+  if ((threadIdx.x & 31) == 0 && blank) atomicAdd(&stats[n].blank_cols, blank);
 }
 
 // ---------------------------------------------------------------- SPPF pooling
@@ -227,6 +310,16 @@ cudaError_t launch_preprocess(const PreParams& p, cudaStream_t stream) {
 cudaError_t launch_preprocess_u8(const PreParams& p, cudaStream_t stream) {
   const size_t total = (size_t)p.n * p.net_h * p.net_w * 3;
   preprocess_u8_kernel<<<grid_for(total, 256), 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tile_stats(const PreParams& p, unsigned int* col_sums, TileStats* stats, cudaStream_t stream) {
+  if (p.in_w > 256 * kStatColSlots || p.in_h > 4096) return cudaErrorInvalidValue;  // 750 * 4096 * ... stays inside uint32
+  cudaError_t e = cudaMemsetAsync(col_sums, 0, (size_t)p.n * p.in_w * sizeof(unsigned int), stream);
+  if (e != cudaSuccess) return e;
+  tile_stats_init<<<(p.n + 255) / 256, 256, 0, stream>>>(stats, p.n);
+  tile_stats_kernel<<<dim3((p.in_h + kStatRows - 1) / kStatRows, p.n), 256, 0, stream>>>(p, col_sums, stats);
+  tile_stats_finish<<<p.n, 256, 0, stream>>>(col_sums, stats, p.in_h, p.in_w);
   return cudaGetLastError();
 }
 

@@ -16,12 +16,27 @@ struct PreParams {
   // per destination column / row (resize == 1): source indices and 11-bit weights
   const int* x0; const int* x1; const short* ax0; const short* ax1;
   const int* y0; const int* y1; const short* ay0; const short* ay1;
+  // Source addressing.  Plain batch: tile n starts at src + n * in_h * row_pitch, row_pitch = in_w * 3.
+  // Raster windows (tiling fused into inference, replaces src/load_data/tile_tifs.py::split_all_tiffs): src is one
+  // (raster_h, raster_w, 3) image, tile n is window win0 + n of the regular grid of in_h x in_w windows (column-major
+  // like the reference's loop: index = ix * wins_y + iy, origin (ix * in_w, iy * in_h)), row_pitch = raster_w * 3.
+  size_t row_pitch;
+  int windowed, wins_y, win0;
   __half* out_s2d;     // (n, net_h/2, net_w/2, 16) fp16, channel (py*2+px)*3 + rgb, 12..15 = 0
   uint8_t* out_u8;     // (n, net_h, net_w, 3) RGB, optional debug/parity output
 };
 
 cudaError_t launch_preprocess(const PreParams& p, cudaStream_t stream);
 cudaError_t launch_preprocess_u8(const PreParams& p, cudaStream_t stream);
+
+// Blank-tile statistics (replaces the reference's src/utils.py::is_blank / is_partly_blank [REF src/utils.py:325-369]):
+// per tile the PIL "L" luminance extrema and the number of rows / columns whose mean over (pixels, channels) is >= 250.
+struct TileStats {
+  int l_min, l_max;              // extrema of L = (19595 R + 38470 G + 7471 B + 0x8000) >> 16
+  int blank_rows, blank_cols;    // rows / columns with sum >= 250 * 3 * width (height)
+};
+// `col_sums` is scratch of n * in_w uint32 (zeroed by the call); stats is a device array of n entries.
+cudaError_t launch_tile_stats(const PreParams& p, unsigned int* col_sums, TileStats* stats, cudaStream_t stream);
 
 // SPPF: three chained 5x5/s1/p2 max pools of channels [c_off, c_off+c) written to the next three slices.
 cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream);

@@ -322,8 +322,59 @@ class TileDetector:
     def detect(self, tiles, bgr=True, src_is_device=False) -> Detections:
         return self.detect_wait(self.detect_submit(tiles, bgr, src_is_device))
 
+    def detect_windows(self, raster: torch.Tensor, tile: int, win0: int, n: int, bgr=True) -> Detections:
+        """Tiling fused into inference: windows [win0, win0 + n) of the grid of full `tile` x `tile` windows of a
+        device-resident (H, W, 3) uint8 raster, enumerated like the reference's tiler (x outer, y inner)
+        [REF src/load_data/tile_tifs.py:33-47].  Results are copies (not views of the pinned slot)."""
+        assert raster.is_cuda and raster.dtype == torch.uint8 and raster.is_contiguous() and raster.shape[2] == 3
+        if self._dets is None:
+            self._dets = [torch.empty(self.batch, self.max_det, 6, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._counts = [torch.empty(self.batch, dtype=torch.int32).pin_memory() for _ in range(2)]
+        cls_arr = (C.c_int * len(self.classes))(*self.classes) if self.classes else None
+        torch.cuda.current_stream(raster.device).synchronize()  # the raster was produced on torch's stream
+        self.ctx.call("aq_detect_windows", C.c_void_p(raster.data_ptr()), raster.shape[0], raster.shape[1], tile, tile, win0, n,
+                      int(bgr), self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
+                      len(self.classes) if self.classes else 0, C.c_void_p(self._dets[0].data_ptr()),
+                      C.c_void_p(self._counts[0].data_ptr()), None)
+        return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
+
     def close(self):
         self.ctx.close()
+
+
+def window_grid(raster_h: int, raster_w: int, tile: int) -> List[Tuple[int, int]]:
+    """(x, y) origins of the full windows in the reference tiler's order (x outer, y inner); the reference names the
+    tile `<tif>_<x>_<y>` [REF src/load_data/tile_tifs.py:33-41]."""
+    return [(x, y) for x in range(0, raster_w - tile + 1, tile) for y in range(0, raster_h - tile + 1, tile)]
+
+
+def tile_stats(ctx: Context, src: torch.Tensor, bgr=True, tile: int = 0, win0: int = 0, n: int = 0) -> np.ndarray:
+    """Blank-tile measurements on the device (aq_tile_stats): src = (n, h, w, 3) uint8 cuda tiles, or -- with `tile` > 0 --
+    an (H, W, 3) raster whose windows [win0, win0 + n) are measured.  Returns (n, 4) int32: L min, L max, blank rows,
+    blank columns."""
+    assert src.is_cuda and src.dtype == torch.uint8 and src.is_contiguous()
+    torch.cuda.current_stream(src.device).synchronize()
+    if tile > 0:
+        out = np.zeros((n, 4), np.int32)
+        ctx.call("aq_tile_stats", C.c_void_p(src.data_ptr()), n, tile, tile, int(bgr), src.shape[0], src.shape[1], win0,
+                 out.ctypes.data, None)
+    else:
+        n = src.shape[0]
+        out = np.zeros((n, 4), np.int32)
+        ctx.call("aq_tile_stats", C.c_void_p(src.data_ptr()), n, src.shape[1], src.shape[2], int(bgr), 0, 0, 0,
+                 out.ctypes.data, None)
+    return out
+
+
+def is_blank(stats_row) -> bool:
+    """src/utils.py::is_blank on the measured luminance extrema [REF src/utils.py:339-350]."""
+    lo, hi = int(stats_row[0]), int(stats_row[1])
+    return (lo, hi) in ((0, 0), (1, 1), (255, 255)) or (lo >= 250 and hi >= 250)
+
+
+def is_partly_blank(stats_row) -> bool:
+    """src/utils.py::is_partly_blank: any fully blank row or column [REF src/utils.py:359-369]."""
+    return int(stats_row[2]) + int(stats_row[3]) > 0
 
 
 def format_label_text(det: np.ndarray, net_hw, hw0, save_conf=True) -> str:

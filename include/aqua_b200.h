@@ -197,6 +197,31 @@ int aq_format_label_text(const float* dets, int count, int net_h, int net_w, int
                          char* out, size_t out_cap);
 
 /* ------------------------------------------------------------------ misc */
+/*
+ * Tiling fused into inference: detect on windows of one device-resident raster instead of tiles cut
+ * by src/load_data/tile_tifs.py::split_all_tiffs [REF src/load_data/tile_tifs.py:33-47].  raster_dev: (raster_h,
+ * raster_w, 3) uint8.  Window k of the grid of FULL win_h x win_w windows is enumerated like the reference's loop
+ * (x outer, y inner): k = ix * wins_y + iy, origin (x, y) = (ix * win_w, iy * win_h), i.e. the tile the reference
+ * names `<tif>_<x>_<y>`.  Windows [win0, win0 + n) are letterboxed to the plan's network size, run through the conv
+ * stack and NMS; results as aq_detect.  Ragged right / bottom strips are not covered (cut them on the host and use
+ * aq_detect).  Synchronises `stream`.
+ */
+int aq_detect_windows(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,
+                      int n, int bgr, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+                      int n_classes, float* dets_host, int* counts_host, void* stream);
+/* Letterboxed uint8 windows (n, net_h, net_w, 3) RGB, for bit-exact checks against cropping + aq_preprocess_u8. */
+int aq_preprocess_windows_u8(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w,
+                             int win0, int n, int bgr, uint8_t* out_dev, void* stream);
+/*
+ * Blank-tile statistics = the measurements behind src/utils.py::is_blank / is_partly_blank
+ * [REF src/utils.py:325-369].  src_dev: n tiles (n, in_h, in_w, 3) uint8, or -- when raster_h > 0 -- a raster of which
+ * windows [win0, win0 + n) of size in_h x in_w are taken as above.  stats_host receives n x 4 int32:
+ *   [0] min, [1] max of PIL's "L" luminance (19595 R + 38470 G + 7471 B + 0x8000) >> 16   (is_blank's getextrema())
+ *   [2] rows, [3] columns whose mean over pixels and channels is >= 250                    (is_partly_blank)
+ * Tiles up to 2048 wide and 4096 tall.  Needs no plan.  Synchronises `stream`.
+ */
+int aq_tile_stats(aq_ctx* ctx, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w,
+                  int win0, int* stats_host, void* stream);
 /* cudaMemcpyAsync wrapper so hosts without a CUDA binding can move test data: kind 0=H2D 1=D2H 2=D2D. */
 int aq_memcpy(aq_ctx* ctx, void* dst, const void* src, size_t bytes, int kind, void* stream);
 int aq_sync(aq_ctx* ctx, void* stream);

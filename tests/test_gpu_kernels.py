@@ -2,6 +2,7 @@
 kernels (torch conv2d fp32, cv2, torchvision.ops.nms).  Run with `pytest -m gpu`."""
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import pytest
@@ -529,3 +530,81 @@ def test_label_files_match_oracle(synthetic_sd, tmp_path):
         if not exp:
             continue
         assert open(paths[i]).read() == "".join(l + "\n" for l in exp)
+
+
+# ---------------------------------------------------------------- blank-tile statistics, raster windows
+def test_tile_stats_vs_reference_golden(ctx):
+    """aq_tile_stats on the golden tiles: extrema as PIL reports them, blank / partly-blank flags as the reference's own
+    is_blank / is_partly_blank source gave (tests/golden/blank_ref.npz)."""
+    from oracle import blank as OB
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "blank_ref.npz"))
+    tiles = g["tiles"]
+    st = engine.tile_stats(ctx, torch.from_numpy(tiles).cuda(), bgr=False)
+    for i, t in enumerate(tiles):
+        assert tuple(st[i]) == OB.tile_stats(t), f"tile {i}: {tuple(st[i])} vs oracle {OB.tile_stats(t)}"
+        assert tuple(st[i][:2]) == tuple(g["extrema"][i])
+        assert engine.is_blank(st[i]) == bool(g["is_blank"][i]) and engine.is_partly_blank(st[i]) == bool(g["is_partly_blank"][i])
+    # BGR input (cv2.imread order): the same tiles with the channels reversed give the same luminance
+    st2 = engine.tile_stats(ctx, torch.from_numpy(np.ascontiguousarray(tiles[..., ::-1])).cuda(), bgr=True)
+    assert (st2 == st).all()
+
+
+@pytest.mark.parametrize("H,W,tile", [(2048, 3072, 1024), (1300, 1500, 640), (640, 1280, 640)])
+def test_tile_stats_raster_windows(ctx, H, W, tile):
+    from oracle import blank as OB
+    rng = np.random.default_rng(H + W)
+    raster = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    raster[: tile // 2, :tile] = 255          # window (0,0): blank rows
+    raster[:, W - 5:] = 251                   # right edge (inside the last window column only if W % tile == 0)
+    wins = OB.windows(H, W, tile)
+    st = engine.tile_stats(ctx, torch.from_numpy(raster).cuda(), bgr=False, tile=tile, win0=0, n=len(wins))
+    for k, (x, y) in enumerate(wins):
+        assert tuple(st[k]) == OB.tile_stats(raster[y:y + tile, x:x + tile]), f"window {k} at ({x},{y})"
+    if len(wins) > 2:  # a sub-range of the grid
+        st1 = engine.tile_stats(ctx, torch.from_numpy(raster).cuda(), bgr=False, tile=tile, win0=1, n=len(wins) - 2)
+        assert (st1 == st[1:-1]).all()
+
+
+@pytest.mark.parametrize("H,W,tile,net", [(2048, 3072, 1024, 640), (1280, 1920, 640, 640), (1500, 1100, 500, 640)])
+def test_preprocess_windows_bit_exact_vs_cropped_tiles(ctx, H, W, tile, net):
+    """Windows of a raster letterboxed on the device == the same windows cropped on the host and sent as tiles
+    (both bit-exact with cv2, see test_preprocess_*); x-outer / y-inner order of the reference tiler."""
+    from oracle import blank as OB
+    rng = np.random.default_rng(7)
+    raster = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    wins = OB.windows(H, W, tile)
+    n = len(wins)
+    _plan_with_input(ctx, n, net, net)
+    rd = torch.from_numpy(raster).cuda()
+    out_w = torch.zeros(n, net, net, 3, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    ctx.call("aq_preprocess_windows_u8", C.c_void_p(rd.data_ptr()), H, W, tile, tile, 0, n, 1, C.c_void_p(out_w.data_ptr()), None)
+    crops = np.stack([raster[y:y + tile, x:x + tile] for x, y in wins])
+    cd = torch.from_numpy(crops).cuda()
+    out_t = torch.zeros_like(out_w)
+    torch.cuda.synchronize()
+    ctx.call("aq_preprocess_u8", C.c_void_p(cd.data_ptr()), n, tile, tile, 1, C.c_void_p(out_t.data_ptr()), None)
+    ctx.sync()
+    assert (out_w == out_t).all()
+    ref = np.stack([LB.letterbox(c, (net, net), auto=False)[..., ::-1] for c in crops])
+    assert (out_w.cpu().numpy() == ref).all()
+
+
+def test_e2e_raster_windows_equal_tiles(synthetic_sd):
+    """aq_detect_windows on a 2048 x 3072 raster == aq_detect on the six 1024^2 tiles cut from it (same detections)."""
+    from aquaculture_b200 import tiles as T
+    tile = 1024
+    raster = np.concatenate([np.concatenate(list(T.synthetic_tiles(range(3 * r, 3 * r + 3), tile, tile, seed=9)), axis=1)
+                             for r in range(2)], axis=0)
+    assert raster.shape == (2048, 3072, 3)
+    wins = engine.window_grid(2048, 3072, tile)
+    det = engine.TileDetector(synthetic_sd, 3, batch=8, imgsz=(640, 640))
+    try:
+        rw = det.detect_windows(torch.from_numpy(raster).cuda(), tile, 0, len(wins), bgr=True)
+        crops = np.stack([raster[y:y + tile, x:x + tile] for x, y in wins])
+        rt = det.detect(torch.from_numpy(crops).pin_memory(), bgr=True)
+        assert (rw.counts == rt.counts).all() and rw.counts.sum() > 0
+        for i in range(len(wins)):
+            assert (rw.dets[i, :rw.counts[i]] == rt.dets[i, :rt.counts[i]]).all()
+    finally:
+        det.close()

@@ -147,3 +147,25 @@ def test_u8_over_255_fp16_equals_reciprocal_multiply():
     by_div = (u / np.float32(255.0)).astype(np.float16)
     upstream = (torch.arange(256, dtype=torch.uint8).half() / 255).numpy()
     assert (by_mul == by_div).all() and (by_mul == upstream).all()
+
+
+def test_blank_oracle_matches_reference_source():
+    """oracle/blank.py vs outputs of the reference's own is_blank / is_partly_blank source on seeded tiles
+    (tests/golden/blank_ref.npz, made by tools/make_golden_blank.py from /root/reference/src/utils.py:325-369)."""
+    from oracle import blank as OB
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "blank_ref.npz"))
+    assert g["is_blank"].any() and (~g["is_blank"]).any() and g["is_partly_blank"].any() and (~g["is_partly_blank"]).any()
+    for i, t in enumerate(g["tiles"]):
+        s = OB.tile_stats(t)
+        assert (s[0], s[1]) == tuple(g["extrema"][i]), f"tile {i}: L extrema {s[:2]} vs PIL {g['extrema'][i]}"
+        assert OB.is_blank(t) == bool(g["is_blank"][i]), f"tile {i}: is_blank"
+        assert OB.is_partly_blank(t) == bool(g["is_partly_blank"][i]), f"tile {i}: is_partly_blank"
+
+
+def test_window_grid_order_matches_reference_tiler():
+    """x outer, y inner, names <x>_<y> [REF src/load_data/tile_tifs.py:33-41]."""
+    from oracle import blank as OB
+    from aquaculture_b200 import engine
+    assert OB.windows(3072, 2048, 1024) == [(0, 0), (0, 1024), (0, 2048), (1024, 0), (1024, 1024), (1024, 2048)]
+    assert engine.window_grid(3072, 2048, 1024) == OB.windows(3072, 2048, 1024)
+    assert engine.window_grid(2500, 2100, 1024) == [(0, 0), (0, 1024), (1024, 0), (1024, 1024)]  # ragged strips left out

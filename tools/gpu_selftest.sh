@@ -17,6 +17,6 @@ run conv3x3s2 "conv3x3_s2"
 run cluster "cluster"
 run persistent "many_tiles"
 run detect "detect_decode"
-run prepost "preprocess or sppf"
+run prepost "preprocess or sppf or tile_stats"
 run nms "nms"
 run e2e "e2e or label_files"

@@ -62,6 +62,11 @@ def parse_opt(argv=None):
     p.add_argument("--synthetic-size", type=int, default=640)
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--nc", type=int, default=3, help="classes of the synthetic stand-in weights")
+    p.add_argument("--raster-tile", type=int, default=0,
+                   help="treat every source image as a large raster and detect on its TxT windows cut on the GPU "
+                        "(replaces src/load_data/tile_tifs.py; labels are named <stem>_<x>_<y>.txt like its tiles)")
+    p.add_argument("--skip-blank", action="store_true",
+                   help="with --raster-tile: skip windows the reference's is_blank() calls blank (src/utils.py:325-350)")
     p.add_argument("--verbose", action="store_true", help="per-image log lines as upstream prints them")
     p.add_argument("--io-threads", type=int, default=8)
     opt = p.parse_args(argv)
@@ -79,6 +84,10 @@ def check_unsupported(opt):
     if not opt.nosave and not opt.save_txt:
         raise SystemExit("detect.py (B200 path): annotated-image output is not implemented; pass --nosave --save-txt "
                          "[--save-conf] as the reference does [README.md:77]")
+    if opt.skip_blank and opt.raster_tile <= 0:
+        raise SystemExit("detect.py (B200 path): --skip-blank needs --raster-tile (the measurement runs on the device-resident raster)")
+    if opt.raster_tile < 0 or (opt.raster_tile > 0 and opt.synthetic > 0):
+        raise SystemExit("detect.py (B200 path): --raster-tile takes a positive window size and real --source rasters")
     if len(opt.weights) != 1:
         raise SystemExit("detect.py (B200 path): model ensembles (several --weights) are not supported")
     src = opt.source
@@ -262,6 +271,52 @@ def run(opt, argv) -> int:
         finish()
         deferred.append((det, ticket, [(None, g[1]) for g in group], shape0, net_hw))
 
+    def run_raster(im, stem):
+        """Windows of one raster: full TxT windows are cut, letterboxed and measured on the device; the ragged right /
+        bottom strips (the reference's tiler emits them as smaller tiles) are cropped on the host and batched by shape."""
+        nonlocal seen, n_files, n_dets
+        T = opt.raster_tile
+        H, W = im.shape[:2]
+        finish()  # detect_windows uses the detector's result slot 0 and synchronises
+        wins = engine.window_grid(H, W, T)
+        if wins:
+            net_hw = net_shape_for(T, T, imgsz)
+            det = detector_for(net_hw)
+            t0 = time.perf_counter()
+            raster = torch.from_numpy(np.ascontiguousarray(im)).to(f"cuda:{device}")
+            dt[0] += time.perf_counter() - t0
+            for k0 in range(0, len(wins), B):
+                nb = min(B, len(wins) - k0)
+                t1 = time.perf_counter()
+                res = det.detect_windows(raster, T, k0, nb, bgr=True)
+                if opt.skip_blank:
+                    st = engine.tile_stats(det.ctx, raster, bgr=True, tile=T, win0=k0, n=nb)
+                    for i in range(nb):
+                        if engine.is_blank(st[i]):
+                            res.counts[i] = 0
+                if opt.save_txt:
+                    paths = [str(label_dir / f"{stem}_{x}_{y}.txt") for x, y in wins[k0:k0 + nb]]
+                    n_files += engine.write_labels(res, net_hw, [(T, T)] * nb, paths, save_conf=opt.save_conf, threads=opt.io_threads)
+                dt[1] += time.perf_counter() - t1
+                seen += nb
+                n_dets += int(res.counts.sum())
+        for x in range(0, W, T):
+            for y in range(0, H, T):
+                if x + T <= W and y + T <= H:
+                    continue
+                crop = np.ascontiguousarray(im[y:y + T, x:x + T])
+                key = crop.shape[:2]
+                pending.setdefault(key, []).append((crop, f"{stem}_{x}_{y}"))
+                if len(pending[key]) == B:
+                    flush(key, pending.pop(key))
+
+    if opt.raster_tile > 0:
+        for item, stem in zip(items, stems):
+            t0 = time.perf_counter()
+            im = load(item)
+            dt[0] += time.perf_counter() - t0
+            run_raster(im, stem)
+        pos = len(items)
     while pos < len(items):
         chunk = items[pos:pos + B]
         t0 = time.perf_counter()

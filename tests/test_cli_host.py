@@ -110,3 +110,14 @@ def test_counter_gather_gloo_world2(tmp_path):
                         "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
                        capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stderr[-2000:]
+
+
+def test_raster_tile_flags():
+    """Additive flags for SURVEY 8f-3 / 8f-5: --raster-tile T (windows cut on the GPU), --skip-blank (needs the former)."""
+    opt = cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--raster-tile", "1024", "--skip-blank"])
+    assert opt.raster_tile == 1024 and opt.skip_blank
+    cli.check_unsupported(opt)
+    with pytest.raises(SystemExit, match="needs --raster-tile"):
+        cli.check_unsupported(cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--skip-blank"]))
+    with pytest.raises(SystemExit, match="--raster-tile"):
+        cli.check_unsupported(cli.parse_opt(["--weights", "synthetic", "--nosave", "--save-txt", "--raster-tile", "64", "--synthetic", "4"]))

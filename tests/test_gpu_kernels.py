@@ -608,3 +608,33 @@ def test_e2e_raster_windows_equal_tiles(synthetic_sd):
             assert (rw.dets[i, :rw.counts[i]] == rt.dets[i, :rt.counts[i]]).all()
     finally:
         det.close()
+
+
+def test_cli_raster_tile_equals_tiled_files(tmp_path):
+    """detect.py --raster-tile T on one raster == detect.py on the tiles the reference's tiler would cut from it
+    (lossless PNG tiles named <stem>_<x>_<y>): identical label files, ragged right strip included; --skip-blank drops
+    the all-white window's file only."""
+    import cv2
+    from aquaculture_b200 import detect_cli as cli
+    from aquaculture_b200 import tiles as T
+    Tl = 512
+    parts = T.synthetic_tiles(range(6), Tl, Tl, seed=4)
+    raster = np.concatenate([np.concatenate(list(parts[0:3]), axis=1), np.concatenate(list(parts[3:6]), axis=1)], axis=0)
+    raster = np.ascontiguousarray(raster[:, :Tl * 2 + 200])      # 1024 x 1224: two full window columns + a 200-wide strip
+    raster[Tl:, :Tl] = 255                                       # window (0, 512) is blank
+    rdir, tdir = tmp_path / "raster", tmp_path / "tiles"
+    rdir.mkdir(); tdir.mkdir()
+    cv2.imwrite(str(rdir / "BIG2020_7.png"), raster)
+    for x in range(0, raster.shape[1], Tl):
+        for y in range(0, raster.shape[0], Tl):
+            cv2.imwrite(str(tdir / f"BIG2020_7_{x}_{y}.png"), raster[y:y + Tl, x:x + Tl])
+    common = ["--weights", "synthetic", "--nosave", "--save-txt", "--save-conf", "--batch-size", "4", "--project", str(tmp_path / "runs")]
+    assert cli.main(common + ["--source", str(tdir), "--name", "tiles"]) == 0
+    assert cli.main(common + ["--source", str(rdir), "--name", "raster", "--raster-tile", str(Tl)]) == 0
+    assert cli.main(common + ["--source", str(rdir), "--name", "noblank", "--raster-tile", str(Tl), "--skip-blank"]) == 0
+    lt = {p.name: p.read_text() for p in (tmp_path / "runs" / "tiles" / "labels").glob("*.txt")}
+    lr = {p.name: p.read_text() for p in (tmp_path / "runs" / "raster" / "labels").glob("*.txt")}
+    ln = {p.name: p.read_text() for p in (tmp_path / "runs" / "noblank" / "labels").glob("*.txt")}
+    assert len(lt) >= 4 and lt == lr
+    blank_name = f"BIG2020_7_0_{Tl}.txt"
+    assert blank_name not in ln and {k: v for k, v in lr.items() if k != blank_name} == ln

@@ -18,6 +18,13 @@ class AquaError(RuntimeError):
     pass
 
 
+class GeoRow(C.Structure):
+    """aq_geo_row (include/aqua_b200.h)."""
+    _fields_ = [("cls", C.c_int), ("xmin", C.c_int), ("xmax", C.c_int), ("ymin", C.c_int), ("ymax", C.c_int),
+                ("conf", C.c_double), ("xmin_m", C.c_double), ("ymin_m", C.c_double), ("xmax_m", C.c_double),
+                ("ymax_m", C.c_double)]
+
+
 class ConvDesc(C.Structure):
     _fields_ = [("src", C.c_int), ("src_c_off", C.c_int), ("c_in", C.c_int),
                 ("dst", C.c_int), ("dst_c_off", C.c_int), ("c_out", C.c_int),
@@ -58,6 +65,9 @@ SIGNATURES = {
                                            C.c_void_p, C.c_void_p]),
     "aq_tile_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_void_p, C.c_void_p]),
+    "aq_geocode_label_text": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int,
+                                        C.c_void_p, C.c_int]),
+    "aq_cage_areas": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
     "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_profile_ops_insitu": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),

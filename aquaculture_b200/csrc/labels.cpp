@@ -98,3 +98,76 @@ extern "C" int aq_format_labels(const float* dets, const int* counts, int n_imag
   if (failed.load()) return AQ_ERR_IO;
   return written.load();
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// the arithmetic of the reference's post-processing, host C as upstream's is host Python.
+//
+// aq_geocode_label_text = the per-row body of geocode_all_detections [REF src/process_yolo/geocode_results.py:158-170]
+// + convert_pix_to_m_bboxes [REF src/process_yolo/geocode_results.py:71-101]: label rows as np.loadtxt parses them
+// (float64) -> integer pixel box (Python int() truncation) -> EPSG:3857 metres by the affine map of the large tif's
+// bounds.  Every product / quotient is evaluated in the reference's order in double (-ffp-contract=off).
+// The EPSG:3857 -> EPSG:3035 reprojection upstream delegates to pyproj is not restated here (pyproj is absent from the
+// build container, so it could not be pinned).
+extern "C" int aq_geocode_label_text(const char* text, int x_offset, int y_offset, const double bounds_3857[4],
+                                     int large_tif_size, int im_width, int im_height, aq_geo_row* out, int cap) {
+  if (!text || !bounds_3857 || !out || cap < 0 || large_tif_size <= 0) return AQ_ERR_ARG;
+  const double xmin_b = bounds_3857[0], ymin_b = bounds_3857[1], xmax_b = bounds_3857[2], ymax_b = bounds_3857[3];
+  const double mx = (xmax_b - xmin_b) / large_tif_size, my = (ymax_b - ymin_b) / large_tif_size;  // m per pixel
+  int n = 0;
+  const char* p = text;
+  while (*p) {
+    double b[6];
+    int got = 0;
+    char* end = nullptr;
+    while (got < 6) {
+      const double v = strtod(p, &end);
+      if (end == p) break;
+      b[got++] = v;
+      p = end;
+    }
+    while (*p && *p != '\n') ++p;  // rest of the line
+    if (*p == '\n') ++p;
+    if (got == 0) continue;            // blank line
+    if (got != 6) return AQ_ERR_ARG;   // the consumer reads bbox[5]: --save-conf is mandatory [REF geocode_results.py:165]
+    if (n >= cap) return AQ_ERR_NOMEM;
+    aq_geo_row& r = out[n++];
+    r.cls = (int)b[0];
+    r.xmin = (int)(im_width * (b[1] - b[3] / 2));
+    r.ymin = (int)(im_height * (b[2] - b[4] / 2));
+    r.xmax = (int)(im_width * (b[1] + b[3] / 2));
+    r.ymax = (int)(im_height * (b[2] + b[4] / 2));
+    r.conf = b[5];
+    // (xmin, ymin) -> (xmin_m, ymax_m); (xmax, ymax) -> (xmax_m, ymin_m): image y grows downwards
+    r.xmin_m = (r.xmin + x_offset) * mx + xmin_b;
+    r.ymax_m = ymax_b - (r.ymin + y_offset) * my;
+    r.xmax_m = (r.xmax + x_offset) * mx + xmin_b;
+    r.ymin_m = ymax_b - (r.ymax + y_offset) * my;
+  }
+  return n;
+}
+
+// get_circle_area_from_bbox / get_square_area_from_bbox [REF src/process_yolo/calc_net_areas.py:24-82]:
+// out = (estimate, variance, min area, max area) in the units of width * height.
+extern "C" int aq_cage_areas(int square, double w, double h, int x_border, int y_border, double out[4]) {
+  if (!out) return AQ_ERR_ARG;
+  const double pi = 3.141592653589793;
+  double lo, hi;
+  if (square) {
+    lo = w * h * (1.0 / 2);
+    hi = w * h;
+  } else if (x_border || y_border) {
+    lo = h * w / 2;  // approximating triangle
+    if (x_border && y_border) hi = pi * h * w / 4;       // quarter ellipse
+    else if (x_border) hi = pi * (h / 2) * w / 2;         // half ellipse
+    else hi = pi * h * (w / 2) / 2;
+  } else {
+    const double a = w / 2, b = h / 2;
+    out[0] = pi * a * b; out[1] = 0; out[2] = pi * a * b; out[3] = pi * a * b;
+    return AQ_OK;
+  }
+  out[0] = (lo + hi) / 2;
+  out[1] = ((hi - lo) * (hi - lo)) / 12;
+  out[2] = lo;
+  out[3] = hi;
+  return AQ_OK;
+}

@@ -404,3 +404,28 @@ def write_labels(dets: Detections, net_hw, hw0_list, paths: List[str], save_conf
     if rc < 0:
         raise AquaError(f"aq_format_labels failed ({rc})")
     return rc
+
+
+def geocode_label_text(text: str, x_offset: int, y_offset: int, bounds_3857, large_tif_size=6144, im_width=1024, im_height=1024):
+    """Rows of one label file -> pixel boxes and EPSG:3857 boxes (host C, aq_geocode_label_text): the per-row arithmetic
+    of geocode_all_detections + convert_pix_to_m_bboxes [REF src/process_yolo/geocode_results.py:71-101,158-170].
+    Returns a list of dicts in file order."""
+    lib = _lib.load()
+    cap = text.count("\n") + 1
+    rows = (_lib.GeoRow * cap)()
+    b = (C.c_double * 4)(*[float(v) for v in bounds_3857])
+    n = lib.aq_geocode_label_text(text.encode(), int(x_offset), int(y_offset), b, int(large_tif_size), int(im_width),
+                                  int(im_height), C.cast(rows, C.c_void_p), cap)
+    if n < 0:
+        raise AquaError(f"aq_geocode_label_text failed ({n})")
+    return [{f: getattr(rows[i], f) for f, _ in _lib.GeoRow._fields_} for i in range(n)]
+
+
+def cage_areas(square: bool, w: float, h: float, x_border=False, y_border=False):
+    """(estimate, variance, min, max) of get_circle_area_from_bbox / get_square_area_from_bbox
+    [REF src/process_yolo/calc_net_areas.py:24-82] (host C, aq_cage_areas)."""
+    out = (C.c_double * 4)()
+    rc = _lib.load().aq_cage_areas(int(bool(square)), float(w), float(h), int(bool(x_border)), int(bool(y_border)), out)
+    if rc < 0:
+        raise AquaError(f"aq_cage_areas failed ({rc})")
+    return tuple(out)

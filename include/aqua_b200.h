@@ -196,6 +196,25 @@ int aq_format_labels(const float* dets, const int* counts, int n_images, int det
 int aq_format_label_text(const float* dets, int count, int net_h, int net_w, int h0, int w0, int save_conf,
                          char* out, size_t out_cap);
 
+/* ------------------------------------------------------------------ post-processing arithmetic */
+typedef struct aq_geo_row {
+  int cls;                      /* bbox[0] */
+  int xmin, xmax, ymin, ymax;   /* pixel box: int(IM_WIDTH * (cx -+ w/2)) ... [REF src/process_yolo/geocode_results.py:158-161] */
+  double conf;                  /* bbox[5] */
+  double xmin_m, ymin_m, xmax_m, ymax_m; /* EPSG:3857 metres [REF src/process_yolo/geocode_results.py:96-99,167-168] */
+} aq_geo_row;
+/*
+ * Geocode the rows of one label file (its text, as written by aq_format_labels with save_conf = 1).  x_offset, y_offset:
+ * the tile's origin inside its large tif (fields 2, 3 of the file stem), bounds_3857 = (xmin, ymin, xmax, ymax) of that
+ * tif's download box, large_tif_size = 6144, im_width = im_height = 1024 in the reference [REF src/utils.py:17-19].
+ * Returns the number of rows written to out (<= cap) or a negative aq_status.  Host only; needs no context.
+ */
+int aq_geocode_label_text(const char* text, int x_offset, int y_offset, const double bounds_3857[4], int large_tif_size,
+                          int im_width, int im_height, aq_geo_row* out, int cap);
+/* Cage area estimate from a box in metres: square = 0 -> get_circle_area_from_bbox, 1 -> get_square_area_from_bbox
+ * [REF src/process_yolo/calc_net_areas.py:24-82]; out = (estimate, variance, min, max). */
+int aq_cage_areas(int square, double w, double h, int x_border, int y_border, double out[4]);
+
 /* ------------------------------------------------------------------ misc */
 /*
  * Tiling fused into inference: detect on windows of one device-resident raster instead of tiles cut

@@ -79,3 +79,52 @@ def test_write_labels_files(tmp_path):
     assert np.loadtxt(paths[2]).shape == (6,)
     engine.write_labels(engine.Detections(dets, counts), (640, 640), [(640, 640)] * 3, paths)
     assert np.loadtxt(paths[0]).shape == (4, 6)              # append mode, as upstream
+
+
+# ---------------------------------------------------------------- geocode + area arithmetic (host C)
+def _geo_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "geo_ref.npz"))
+
+
+def test_geocode_oracle_matches_reference_source():
+    """oracle/geocode.py::pix_to_m vs the reference's own convert_pix_to_m_bboxes source (tests/golden/geo_ref.npz)."""
+    from oracle import geocode as OG
+    g = _geo_golden()
+    for ind, xo, yo, x, y, xm, ym in g["pts"]:
+        got = OG.pix_to_m(int(x), int(y), int(xo), int(yo), tuple(g["boxes"][int(ind)]))
+        assert got == (xm, ym)
+    for kind, w, h, xb, yb, est, var, lo, hi in g["areas"]:
+        got = OG.square_area(w, h) if kind else OG.circle_area(w, h, bool(xb), bool(yb))
+        assert tuple(float(v) for v in got) == (est, var, lo, hi)
+
+
+def test_cage_areas_c_vs_reference_golden():
+    g = _geo_golden()
+    for kind, w, h, xb, yb, est, var, lo, hi in g["areas"]:
+        assert engine.cage_areas(bool(kind), w, h, bool(xb), bool(yb)) == (est, var, lo, hi)
+
+
+def test_geocode_label_text_c_vs_oracle():
+    """aq_geocode_label_text on label text the C formatter wrote == np.loadtxt + the oracle's restatement of the
+    reference loop, bit for bit (ints and float64), for one- and many-line files."""
+    import io
+    from oracle import geocode as OG
+    g = _geo_golden()
+    rng = np.random.default_rng(3)
+    for trial in range(6):
+        n = 1 if trial == 0 else int(rng.integers(2, 40))
+        xy = rng.uniform(0, 600, (n, 2)).astype(np.float32)
+        wh = rng.uniform(2, 80, (n, 2)).astype(np.float32)
+        conf = np.sort(rng.uniform(0.25, 1, n).astype(np.float32))[::-1]
+        det = np.concatenate([xy, xy + wh, conf[:, None], rng.integers(0, 3, (n, 1)).astype(np.float32)], 1).astype(np.float32)
+        text = engine.format_label_text(np.ascontiguousarray(det), (640, 640), (1024, 1024))
+        rows = np.loadtxt(io.StringIO(text))
+        rows = [rows] if rows.ndim == 1 else list(rows)
+        ind = trial % 3
+        xo, yo = 1024 * (trial % 6), 1024 * ((trial * 5) % 6)
+        exp = OG.geocode_rows(rows, xo, yo, tuple(g["boxes"][ind]))
+        got = engine.geocode_label_text(text, xo, yo, g["boxes"][ind])
+        assert got == exp
+    with pytest.raises(engine.AquaError):  # five columns (no --save-conf): the consumer cannot use the file
+        engine.geocode_label_text("0 0.5 0.5 0.1 0.1\n", 0, 0, g["boxes"][0])

@@ -1448,7 +1448,7 @@ int aq_preprocess_windows_u8(aq_ctx* c, const uint8_t* raster_dev, int raster_h,
 
 int aq_tile_stats(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w, int win0,
                   int* stats_host, void* stream) {
-  if (!c || !src_dev || !stats_host || n <= 0 || in_h <= 0 || in_w <= 0) return AQ_ERR_ARG;
+  if (!c || !src_dev || n <= 0 || in_h <= 0 || in_w <= 0) return AQ_ERR_ARG;
   cudaSetDevice(c->device);
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   PreParams p{};
@@ -1471,6 +1471,7 @@ int aq_tile_stats(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, 
   TileStats* st = (TileStats*)(col + (size_t)n * in_w);
   cudaError_t e = launch_tile_stats(p, col, st, s);
   if (e != cudaSuccess) return fail(c, e == cudaErrorInvalidValue ? AQ_ERR_UNSUPPORTED : AQ_ERR_CUDA, "tile_stats: %s (tiles up to 2048 x 4096)", cudaGetErrorString(e));
+  if (!stats_host) return AQ_OK;  // kernels only (timing): nothing is copied, the stream is not synchronised
   CU_CHECK(c, cudaMemcpyAsync(stats_host, st, (size_t)n * sizeof(TileStats), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaStreamSynchronize(s));
   return AQ_OK;

@@ -199,6 +199,88 @@ __global__ void __launch_bounds__(256) tile_stats_kernel(const PreParams p, unsi
   }
 }
 
+// Vectorised variant for tiles whose rows are 16-byte aligned (in_w % 16 == 0, pitch % 16 == 0): an item = 16 pixels =
+// 48 bytes = three 16-byte loads; the CTA walks kStatBand rows, items strided over its threads; column sums meet in
+// shared memory (conflict-free: the lanes of a warp hold neighbouring pixel groups), one global atomicAdd per column
+// per CTA.  grid (ceil(in_h / kStatBand), n).
+constexpr int kStatBand = 32;
+
+// REGCOL (256 % G == 0, e.g. 1024-wide tiles): a thread meets the same pixel group in every row it visits, so its 16
+// column sums stay in registers until the end of the band.
+template <bool REGCOL>
+__global__ void __launch_bounds__(256) tile_stats_vec_kernel(const PreParams p, unsigned int* col_sums, TileStats* stats) {
+  extern __shared__ unsigned int s_dyn[];  // [in_w] column sums, then [kStatBand] row sums
+  unsigned int* s_col = s_dyn;
+  unsigned int* s_rowv = s_dyn + p.in_w;
+  __shared__ int s_min, s_max;
+  const int n = blockIdx.y, y0 = blockIdx.x * kStatBand;
+  const uint8_t* img = tile_base(p, n);
+  for (int i = threadIdx.x; i < p.in_w + kStatBand; i += blockDim.x) s_dyn[i] = 0;
+  if (threadIdx.x == 0) { s_min = 255; s_max = 0; }
+  __syncthreads();
+  const int G = p.in_w >> 4;
+  const int rows = min(kStatBand, p.in_h - y0);
+  const int items = rows * G;
+  int lmin = 255, lmax = 0;
+  unsigned int col[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) col[k] = 0;
+  for (int it = threadIdx.x; it - (int)(threadIdx.x & 31) < items; it += blockDim.x) {  // whole warps stay in the loop
+    const bool live = it < items;
+    const int r = live ? it / G : -1;
+    const int g = live ? it - r * G : 0;
+    unsigned int rs = 0;
+    if (live) {
+      const uint4* q = reinterpret_cast<const uint4*>(img + (size_t)(y0 + r) * p.row_pitch + (size_t)g * 48);
+      const uint4 v0 = __ldg(q), v1 = __ldg(q + 1), v2 = __ldg(q + 2);
+      const unsigned int w[12] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
+#pragma unroll
+      for (int px = 0; px < 16; ++px) {
+        const int b0 = 3 * px, b1 = b0 + 1, b2 = b0 + 2;
+        const unsigned int c0 = (w[b0 >> 2] >> (8 * (b0 & 3))) & 255u, c1 = (w[b1 >> 2] >> (8 * (b1 & 3))) & 255u,
+                           c2 = (w[b2 >> 2] >> (8 * (b2 & 3))) & 255u;
+        const unsigned int R = p.bgr ? c2 : c0, B = p.bgr ? c0 : c2;
+        const int L = (int)((R * 19595u + c1 * 38470u + B * 7471u + 0x8000u) >> 16);
+        lmin = min(lmin, L);
+        lmax = max(lmax, L);
+        const unsigned int s3 = c0 + c1 + c2;
+        rs += s3;
+        if (REGCOL) col[px] += s3;
+        else atomicAdd(&s_col[px * G + g], s3);  // [px][g]: the lanes of a warp (consecutive g) hit consecutive banks
+      }
+    }
+    // row sum: one shared atomic per warp when its lanes sit in one row, else one per lane
+    const int r0 = __shfl_sync(0xffffffffu, r, 0);
+    if (__all_sync(0xffffffffu, r == r0)) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+      if ((threadIdx.x & 31) == 0 && r0 >= 0) atomicAdd(&s_rowv[r0], rs);
+    } else if (live) {
+      atomicAdd(&s_rowv[r], rs);
+    }
+  }
+  if (REGCOL) {
+    const int g = (int)threadIdx.x % G;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) atomicAdd(&s_col[k * G + g], col[k]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lmin = min(lmin, __shfl_xor_sync(0xffffffffu, lmin, o));
+    lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicMin(&s_min, lmin); atomicMax(&s_max, lmax); }
+  __syncthreads();
+  for (int x = threadIdx.x; x < p.in_w; x += blockDim.x) atomicAdd(&col_sums[(size_t)n * p.in_w + x], s_col[(x & 15) * G + (x >> 4)]);
+  if (threadIdx.x == 0) {
+    int blank = 0;
+    for (int r = 0; r < rows; ++r) blank += s_rowv[r] >= 750u * (unsigned int)p.in_w;
+    if (blank) atomicAdd(&stats[n].blank_rows, blank);
+    atomicMin(&stats[n].l_min, s_min);
+    atomicMax(&stats[n].l_max, s_max);
+  }
+}
+
 __global__ void __launch_bounds__(256) tile_stats_init(TileStats* stats, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) stats[i] = TileStats{255, 0, 0, 0};
@@ -318,7 +400,15 @@ cudaError_t launch_tile_stats(const PreParams& p, unsigned int* col_sums, TileSt
   cudaError_t e = cudaMemsetAsync(col_sums, 0, (size_t)p.n * p.in_w * sizeof(unsigned int), stream);
   if (e != cudaSuccess) return e;
   tile_stats_init<<<(p.n + 255) / 256, 256, 0, stream>>>(stats, p.n);
-  tile_stats_kernel<<<dim3((p.in_h + kStatRows - 1) / kStatRows, p.n), 256, 0, stream>>>(p, col_sums, stats);
+  const bool vec = (p.in_w % 16) == 0 && (p.row_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(p.src) % 16) == 0 &&
+                   (!p.windowed || ((size_t)p.in_w * 3) % 16 == 0);
+  if (vec) {
+    const dim3 grid((p.in_h + kStatBand - 1) / kStatBand, p.n);
+    const size_t smem = (p.in_w + kStatBand) * sizeof(unsigned int);
+    if (256 % (p.in_w / 16) == 0) tile_stats_vec_kernel<true><<<grid, 256, smem, stream>>>(p, col_sums, stats);
+    else tile_stats_vec_kernel<false><<<grid, 256, smem, stream>>>(p, col_sums, stats);
+  } else
+    tile_stats_kernel<<<dim3((p.in_h + kStatRows - 1) / kStatRows, p.n), 256, 0, stream>>>(p, col_sums, stats);
   tile_stats_finish<<<p.n, 256, 0, stream>>>(col_sums, stats, p.in_h, p.in_w);
   return cudaGetLastError();
 }

@@ -237,7 +237,8 @@ int aq_preprocess_windows_u8(aq_ctx* ctx, const uint8_t* raster_dev, int raster_
  * windows [win0, win0 + n) of size in_h x in_w are taken as above.  stats_host receives n x 4 int32:
  *   [0] min, [1] max of PIL's "L" luminance (19595 R + 38470 G + 7471 B + 0x8000) >> 16   (is_blank's getextrema())
  *   [2] rows, [3] columns whose mean over pixels and channels is >= 250                    (is_partly_blank)
- * Tiles up to 2048 wide and 4096 tall.  Needs no plan.  Synchronises `stream`.
+ * Tiles up to 2048 wide and 4096 tall.  Needs no plan.  Synchronises `stream` (stats_host == NULL: kernels only, no
+ * copy, no synchronisation -- for timing).
  */
 int aq_tile_stats(aq_ctx* ctx, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w,
                   int win0, int* stats_host, void* stream);

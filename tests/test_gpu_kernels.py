@@ -610,11 +610,13 @@ def test_e2e_raster_windows_equal_tiles(synthetic_sd):
         det.close()
 
 
-def test_cli_raster_tile_equals_tiled_files(tmp_path):
+def test_cli_raster_tile_equals_tiled_files(tmp_path, monkeypatch):
     """detect.py --raster-tile T on one raster == detect.py on the tiles the reference's tiler would cut from it
     (lossless PNG tiles named <stem>_<x>_<y>): identical label files, ragged right strip included; --skip-blank drops
-    the all-white window's file only."""
+    the all-white window's file only.  Plan-time autotuning is off so that the three runs use the same conv tilings
+    (a HALO and a TAP tiling of one layer add the taps in a different order: confidences may differ in the 4th digit)."""
     import cv2
+    monkeypatch.setenv("AQUA_AUTOTUNE", "0")
     from aquaculture_b200 import detect_cli as cli
     from aquaculture_b200 import tiles as T
     Tl = 512

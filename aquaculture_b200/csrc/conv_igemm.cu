@@ -902,6 +902,40 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
           const int gx = pos - gy * p.det_nx;
           const bool valid = m < p.det_m_total;
           const int ncols = 3 * p.det_no;
+          if (p.det_no == 8) {
+            // nc = 3 (the reference's model): a 16-column chunk is exactly two anchors x 8 outputs, so the column ->
+            // (anchor, output) mapping is static: no table lookups, no per-element branches.  With two M blocks per
+            // tile and two chunks (24 columns) every one of the 16 warps takes one (M block, chunk) pair.
+            const bool split = p.mblk == 2 && n_chunks == 2;
+            if (split && (int)(sub >> 1) != mb) goto det_block_done;
+            for (int ch = split ? (int)(sub & 1) : (int)sub; ch < n_chunks; ch += split ? 2 : 4) {
+              const int c0 = ch << 4;
+              uint32_t v[16];
+              tmem_ld16(t_addr + c0, v);
+              tmem_ld_wait();
+              const float fx = ((float)gx - 0.5f), fy = ((float)gy - 0.5f);
+#pragma unroll
+              for (int aa = 0; aa < 2; ++aa) {
+                const int a = (c0 >> 3) + aa;
+                if (a >= 3) continue;
+                float sg[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float z = __uint_as_float(v[8 * aa + j]) + s_bias[c0 + 8 * aa + j];
+                  sg[j] = __fdividef(1.0f, 1.0f + __expf(-z));
+                }
+                const float aw = p.det_anchor[2 * a], ah = p.det_anchor[2 * a + 1];
+                const float4 lo = make_float4((sg[0] * 2.0f + fx) * p.det_stride, (sg[1] * 2.0f + fy) * p.det_stride,
+                                              (sg[2] * 2.0f) * (sg[2] * 2.0f) * aw, (sg[3] * 2.0f) * (sg[3] * 2.0f) * ah);
+                if (valid) {
+                  const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
+                  float4* dst = reinterpret_cast<float4*>(p.pred + r * 8);
+                  dst[0] = lo;
+                  dst[1] = make_float4(sg[4], sg[5], sg[6], sg[7]);
+                }
+              }
+            }
+          } else
           for (int ch = sub; ch < n_chunks; ch += 4) {
             const int c0 = ch << 4;
             uint32_t v[16];
@@ -950,6 +984,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
               }
             }
           }
+        det_block_done:
           if (mb == p.mblk - 1) {
             tc_fence_before();
             __syncwarp();

@@ -182,6 +182,7 @@ int pow2_at_least(int v) {
 struct Cand {
   int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
   int cluster = 1;  // CTAs per thread-block cluster sharing each weight tile by multicast (1, 2, 4)
+  int epi_sets = 1; // epilogue organisation: 1 = sixteen warps in lockstep, 2 = two sets of eight on alternate groups
   int pref = 0;     // shared-memory split: 0 = staging / activation rings first, 1 = weight ring first (streamed weights)
   int b_dense = 0;  // HALO with c_in <= 16: four taps share one 64-wide weight chunk (resident weights = 3 slots, not 9)
   // derived
@@ -409,18 +410,24 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
         // measured (profiles/r1_cluster_multicast_sweep.txt): sharing weight tiles by multicast does not speed any
         // layer up (cluster 2: +-1 %, cluster 4: slower), so clusters are only planned on request
         if (cl != (want_cluster > 0 ? want_cluster : 1)) continue;
-        for (int pref = 0; pref < 2; ++pref) {
-          Cand cd = cd0;
-          cd.cluster = cl;
-          cd.pref = pref;
-          fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
-          if (!cd.ok) continue;
-          if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
-            const Cand& o = choices.back().cd;
-            if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg) continue;
+        // AQUA_EPI_SETS=1|2 pins the epilogue organisation (tests); default: both are candidates
+        const char* fs = getenv("AQUA_EPI_SETS");
+        const int min_sets = det ? 1 : (fs ? (atoi(fs) == 2 ? 2 : 1) : 1);
+        const int max_sets = det ? 1 : (fs ? min_sets : 2);
+        for (int sets = min_sets; sets <= max_sets; ++sets)
+          for (int pref = 0; pref < 2; ++pref) {
+            Cand cd = cd0;
+            cd.cluster = cl;
+            cd.pref = pref;
+            cd.epi_sets = sets;
+            fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+            if (!cd.ok) continue;
+            if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
+              const Cand& o = choices.back().cd;
+              if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg) continue;
+            }
+            choices.push_back({tn, ntn, cd});
           }
-          choices.push_back({tn, ntn, cd});
-        }
       }
     }
   }
@@ -460,6 +467,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.nb = best.nb;
   k.b_res = best.b_res;
   k.b_dense = best.b_res ? best.b_dense : 0;
+  k.epi_sets = det ? 1 : best.epi_sets;
   k.n_stg = best.n_stg;
   k.acc_stages = best.acc_stages;
   k.n_mma = best.mblk > 1 ? 2 : 1;

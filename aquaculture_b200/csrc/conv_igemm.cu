@@ -540,6 +540,126 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
 }
 
 
+// Two-set variant of the epilogue (p.epi_sets == 2).  The sixteen-warp epilogue above runs every phase of a group in
+// lockstep -- TMEM load, the MUFU burst of the activation (8 clk per warp instruction per SM sub-partition, all
+// warps at once), staging, proxy fence, barrier hand-off -- so a group costs the SUM of its phases (~1.2-1.4k clk,
+// measured with AQUA_DBG: profiles/r1_attribution_stem_v7.txt), which bounds every layer with few K steps (the stem,
+// the 1x1 / 3x3 convs of the 160x160 stage).  Here the warps form two sets of eight (TMEM lane quarter x two
+// 16-column chunks each); set s takes the groups with global index = s (mod 2), so one set's MUFU burst overlaps the
+// other's loads / fences / barrier latency.  Staging ring, store warp and the order of the stores are unchanged;
+// the named barriers count 8 warps + the store warp.
+constexpr uint32_t kBarStgThreads2 = (kEpiWarps / 2) * 32 + 32;
+
+template <int ACT>
+__device__ __forceinline__ void epi_math_store(const uint32_t (&v)[16], uint32_t bias_addr, uint32_t dst0, uint32_t dst1) {
+  uint32_t b4[16];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(b4[4 * i]), "=r"(b4[4 * i + 1]), "=r"(b4[4 * i + 2]), "=r"(b4[4 * i + 3])
+                 : "r"(bias_addr + 16u * i));
+  float f[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    if (ACT == ACT_SILU_FAST) {
+      const float h = fmaf(__uint_as_float(v[i]), 0.5f, __uint_as_float(b4[i]));  // s_bias holds bias / 2
+      f[i] = fmaf(h, tanh_approx(h), h);
+    } else {
+      const float x = __uint_as_float(v[i]) + __uint_as_float(b4[i]);
+      f[i] = ACT == ACT_SILU ? silu_exact(x) : x;
+    }
+  }
+  uint32_t h[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) h[i] = pack_half2(f[2 * i], f[2 * i + 1]);
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst0), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3]) : "memory");
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst1), "r"(h[4]), "r"(h[5]), "r"(h[6]), "r"(h[7]) : "memory");
+}
+
+template <int ACT>
+__device__ __forceinline__ void epi_store_role2(const ConvKParams& p, const EpiCtx& ec) {
+  const uint32_t bar0 = ec.bar0;
+  auto tfull = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
+  auto tempty = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
+  const uint32_t e = ec.e, lane = ec.lane;
+  const uint32_t q = e & 3, sub = e >> 2;
+  const uint32_t set = sub >> 1, half = sub & 1;  // this warp's chunks of a 64-channel group: half and half + 2
+  const uint32_t row = q * 32 + lane;
+  const uint32_t sw = row & 7u, rb = row * 128u;
+  // staging offsets of the four 16-byte pieces (chunk c = pieces 2c, 2c + 1; piece j of row r sits at j ^ (r & 7))
+  const uint32_t sa0 = rb + (((2 * half) ^ sw) << 4), sa1 = rb + (((2 * half + 1) ^ sw) << 4);
+  const uint32_t sb0 = rb + (((2 * half + 4) ^ sw) << 4), sb1 = rb + (((2 * half + 5) ^ sw) << 4);
+  const int n_chunks = p.tile_n >> 4, n_groups = p.groups, tile_n = p.tile_n;
+  const int G = p.mblk * n_groups;  // groups per tile
+  const uint32_t n_stg = p.n_stg, acc_stages = p.acc_stages, acc_stride = p.acc_stride, acc_pitch = p.acc_pitch;
+  const uint32_t t_lane = ec.tmem_base + ((q * 32u) << 16);
+  const int total_tiles = ec.total_tiles;
+  uint32_t va[16], vb[16];
+  uint32_t k0 = 0;    // global index of the tile's first group
+  uint32_t buf0 = 0;  // k0 % n_stg
+  Ring rt;
+  for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), rt.advance(acc_stages)) {
+    int m_tile, n_idx;
+    split_tile(p, tile, m_tile, n_idx);
+    const int n0 = n_idx * tile_n;
+    const uint32_t as = rt.slot;
+    mbar_wait(tfull(as), rt.phase);
+    tc_fence_after();
+    const uint32_t ta0 = t_lane + as * acc_stride;
+    // own groups of this tile: j = j0, j0 + 2, ... < G with (k0 + j) % 2 == set
+    int j = ((k0 & 1u) == set) ? 0 : 1;
+    int mb = 0, g = j;
+    while (g >= n_groups) { g -= n_groups; ++mb; }
+    uint32_t buf = buf0 + (uint32_t)j;
+    if (buf >= n_stg) buf -= n_stg;
+    bool loaded = false;
+    if (j >= G) {  // nothing of this tile is ours: release the accumulators straight away
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty(as));
+    }
+    for (; j < G; j += 2) {
+      const uint32_t ta = ta0 + (uint32_t)mb * acc_pitch + (uint32_t)g * 64u;
+      const bool v0 = 4 * g + (int)half < n_chunks, v1 = 4 * g + (int)half + 2 < n_chunks;  // warp-uniform
+      if (!loaded) {
+        if (v0) tmem_ld16(ta + half * 16u, va);
+        if (v1) tmem_ld16(ta + (half + 2u) * 16u, vb);
+      }
+      tmem_ld_wait();
+      const bool last_own = j + 2 >= G;
+      if (last_own) {  // every TMEM read of this tile by this warp is done
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty(as));
+      }
+      // the TMA store that last used this staging buffer (group k - n_stg) must have read it
+      if (k0 + (uint32_t)j >= n_stg) named_bar_sync(kBarStgEmpty + buf, kBarStgThreads2);
+      const uint32_t stg = ec.stg_base + buf * (kTileM * 128);
+      const uint32_t bias_g = ec.bias_smem + (uint32_t)(n0 + g * 64) * 4u;
+      if (v0) epi_math_store<ACT>(va, bias_g + half * 64u, stg + sa0, stg + sa1);
+      if (v1) epi_math_store<ACT>(vb, bias_g + (half + 2u) * 64u, stg + sb0, stg + sb1);
+      // next own group (same tile): its accumulators travel TMEM -> registers while this group is stored
+      int ng = g + 2, nmb = mb;
+      while (ng >= n_groups) { ng -= n_groups; ++nmb; }
+      loaded = !last_own;
+      if (loaded) {
+        const uint32_t tn = ta0 + (uint32_t)nmb * acc_pitch + (uint32_t)ng * 64u;
+        if (4 * ng + (int)half < n_chunks) tmem_ld16(tn + half * 16u, va);
+        if (4 * ng + (int)half + 2 < n_chunks) tmem_ld16(tn + (half + 2u) * 16u, vb);
+      }
+      fence_proxy_async_smem();
+      named_bar_arrive(kBarStgFull + buf, kBarStgThreads2);
+      g = ng;
+      mb = nmb;
+      buf += 2;
+      while (buf >= n_stg) buf -= n_stg;
+    }
+    k0 += (uint32_t)G;
+    buf0 += (uint32_t)G;
+    while (buf0 >= n_stg) buf0 -= n_stg;
+  }
+}
+
 // Store warp: waits for each staged group, issues its TMA store / reduce-add, frees staging buffers.
 template <bool TRACE>
 __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_base, int total_tiles, uint32_t lane) {
@@ -550,6 +670,7 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
   Ring rs;
   uint32_t k = 0;  // groups stored so far
   int it = 0;
+  const uint32_t bar_threads = (p.epi_sets == 2 && !TRACE) ? kBarStgThreads2 : kBarStgThreads;  // traced builds keep the lockstep epilogue
   const bool halo = (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) && !(p.dbg & 64);
   const int hp1 = p.a_h + 1;
   for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
@@ -586,7 +707,7 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
         const uint32_t buf = rs.slot;
         rs.advance(n_stg);
         if (p.dbg & 32) continue;
-        TR_WAIT(trw, named_bar_sync(kBarStgFull + buf, kBarStgThreads));
+        TR_WAIT(trw, named_bar_sync(kBarStgFull + buf, bar_threads));
         if (lane == 0) {
           if (p.dbg & 1) {
           } else if (one_image) {
@@ -610,7 +731,7 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
         if (k + 2 >= n_stg && k + 2 < total_groups) {
           uint32_t fb = buf + 2;  // (k + 2) % n_stg
           if (fb >= n_stg) fb -= n_stg;
-          named_bar_arrive(kBarStgEmpty + fb, kBarStgThreads);
+          named_bar_arrive(kBarStgEmpty + fb, bar_threads);
         }
       }
     }
@@ -869,7 +990,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   } else if (warp >= kWarpEpi0 && EPI == EPI_STORE) {
     // =========================== epilogue warps 4..19: bias + SiLU + TMA store ===========================
     const EpiCtx ec{bar0, stg_base, tmem_base, smem_u32(s_bias), total_tiles, warp - kWarpEpi0, lane};
-    if (p.act == ACT_SILU_FAST) epi_store_role<ACT_SILU_FAST, TRACE>(p, ec);
+    if (p.epi_sets == 2 && !TRACE) {
+      if (p.act == ACT_SILU_FAST) epi_store_role2<ACT_SILU_FAST>(p, ec);
+      else if (p.act == ACT_SILU) epi_store_role2<ACT_SILU>(p, ec);
+      else epi_store_role2<ACT_NONE>(p, ec);
+    } else if (p.act == ACT_SILU_FAST) epi_store_role<ACT_SILU_FAST, TRACE>(p, ec);
     else if (p.act == ACT_SILU) epi_store_role<ACT_SILU, TRACE>(p, ec);
     else epi_store_role<ACT_NONE, TRACE>(p, ec);
   } else if (warp >= kWarpEpi0) {

@@ -88,6 +88,7 @@ struct alignas(64) ConvKParams {
   int up_chunks, up_hs;  // leading 64-channel chunks that come from tmUp; rows of the half-resolution source
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;
+  int epi_sets;  // 1: sixteen epilogue warps in lockstep; 2: two sets of eight taking alternate groups (conv_igemm.cu)
   int dbg;  // AQUA_DBG attribution experiments (results wrong): 1 = no TMA stores issued, 2 = epilogue skips math + staging, 4 = one store per tile only
   uint32_t a_slot_bytes, b_slot_bytes, stg_bytes;
   uint32_t a_tx_bytes, b_tx_bytes;  // bytes one slot fill delivers

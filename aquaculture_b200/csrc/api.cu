@@ -1246,9 +1246,9 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
                          2.0 * c_out * c_in * k.taps;
     const int ksz = k.taps == 9 ? 3 : 1;
     static const char* mode_name[] = {"flat", "halo", "tap", "halo2"};
-    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d tile=%dx%d mt=%d nt=%d cl=%d | flop=%.4g bytes=%.4g",
+    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
-             k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.tw, k.th,
+             k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.epi_sets, k.tw, k.th,
              k.m_tiles, k.n_tiles_n, 1 << k.cshift, flops, bytes);
   } else if (op.kind == OP_POOL) {
     const Buffer& b = c->bufs[op.buf];

@@ -256,6 +256,9 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     cd.nb = 3;
     if (used() > budget) return;
   }
+  // HALO: one patch per 64-channel chunk; with a single chunk per tile (c_in <= 64) the A ring depth is the number of
+  // TILES in flight, and a patch load takes 2-3k clk under load -- such layers want a deep ring, the others 3 slots
+  const int halo_na_cap = cd.mode == CONV_MODE_HALO ? (cpt == 1 ? kMaxA : 3) : kMaxA;
   auto grow = [&](int& v, int cap, long unit) {
     while (v < cap && used() + unit <= budget) ++v;
   };
@@ -270,17 +273,17 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
     grow(cd.nb, 6, b_slot);
     grow(cd.n_stg, 3, stg);
-    if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
+    if (cd.mode == CONV_MODE_HALO) grow(cd.na, halo_na_cap, cd.a_slot);
     grow(cd.nb, 12, b_slot);
     grow(cd.n_stg, 4, stg);
-    grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
+    grow(cd.na, halo_na_cap, cd.a_slot);
   } else {
     grow(cd.n_stg, 3, stg);
-    if (cd.mode == CONV_MODE_HALO) grow(cd.na, 3, cd.a_slot);
+    if (cd.mode == CONV_MODE_HALO) grow(cd.na, halo_na_cap, cd.a_slot);
     if (cd.mode == CONV_MODE_HALO2) grow(cd.na, 4, cd.a_slot);
     if (!cd.b_res) grow(cd.nb, 5, b_slot);
     grow(cd.n_stg, 4, stg);
-    grow(cd.na, cd.mode == CONV_MODE_HALO ? 3 : kMaxA, cd.a_slot);
+    grow(cd.na, halo_na_cap, cd.a_slot);
     if (!cd.b_res) grow(cd.nb, 12, b_slot);
   }
   // ---- cost

@@ -14,7 +14,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch_$TAG.log 2>&1
 echo "ncu launches exit=$?"
 unset AQUA_TUNE_CACHE
-for shp in "64 80 80 96 96 3 1" "64 160 160 48 48 3 1"; do
+for shp in "64 80 80 96 96 3 1"; do
   n=$(echo $shp | tr ' ' '_')
   timeout 120 python tools/one_op.py $shp > gpurun_out/oneop_${n}_$TAG.log 2>&1 &&
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_igemm -s 3 -c 1 -f -o gpurun_out/prof_${n}_$TAG \

@@ -16,6 +16,7 @@
 #include "../../include/aqua_b200.h"
 #include "aux_kernels.cuh"
 #include "conv_igemm.cuh"
+#include "jpeg.cuh"
 #include "nms.cuh"
 
 using namespace aq;
@@ -88,6 +89,8 @@ struct aq_ctx {
   PreParams pre{};
   void* stats_scratch = nullptr;  // aq_tile_stats: column sums + TileStats
   size_t stats_bytes = 0;
+  void* jpeg_scratch = nullptr;   // aq_jpeg_reconstruct: component planes (+ staged coefficients / tables for host input)
+  size_t jpeg_bytes = 0;
   // nms scratch
   void* nms_scratch = nullptr;
   size_t nms_scratch_bytes = 0;
@@ -909,6 +912,7 @@ void aq_destroy(aq_ctx* c) {
   if (c->tab_dev) cudaFree(c->tab_dev);
   if (c->nms_scratch) cudaFree(c->nms_scratch);
   if (c->stats_scratch) cudaFree(c->stats_scratch);
+  if (c->jpeg_scratch) cudaFree(c->jpeg_scratch);
   if (c->nms_dets) cudaFree(c->nms_dets);
   if (c->nms_counts) cudaFree(c->nms_counts);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -1485,6 +1489,44 @@ int aq_tile_stats(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, 
   if (!stats_host) return AQ_OK;  // kernels only (timing): nothing is copied, the stream is not synchronised
   CU_CHECK(c, cudaMemcpyAsync(stats_host, st, (size_t)n * sizeof(TileStats), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaStreamSynchronize(s));
+  return AQ_OK;
+}
+
+int aq_jpeg_reconstruct(aq_ctx* c, const int16_t* coef, const uint16_t* quant, int n, int width, int height, int ncomp, int hs,
+                        int bgr_out, int src_is_device, uint8_t* out_dev, void* stream) {
+  if (!c || !coef || !quant || !out_dev || n <= 0 || width <= 0 || height <= 0) return AQ_ERR_ARG;
+  if ((ncomp != 1 && ncomp != 3) || (hs != 1 && hs != 2) || (ncomp == 1 && hs != 1))
+    return fail(c, AQ_ERR_UNSUPPORTED, "jpeg: %d components with %dx%d luma sampling (grayscale, 4:4:4 and 4:2:0 only)", ncomp, hs, hs);
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  JpegParams p{};
+  p.n = n; p.width = width; p.height = height; p.ncomp = ncomp; p.hs = hs; p.bgr = bgr_out; p.out = out_dev;
+  jpeg_geometry(p);
+  const size_t planes = (size_t)n * p.planes_per_image;
+  const size_t coef_bytes = (size_t)n * p.blocks_per_image * 64 * sizeof(int16_t), quant_bytes = (size_t)n * 192 * sizeof(uint16_t);
+  const size_t planes_al = (planes + 255) / 256 * 256, coef_al = (coef_bytes + 255) / 256 * 256;
+  const size_t need = planes_al + (src_is_device ? 0 : coef_al + quant_bytes);
+  if (need > c->jpeg_bytes) {
+    if (c->jpeg_scratch) { cudaStreamSynchronize(s); cudaFree(c->jpeg_scratch); }
+    c->jpeg_scratch = nullptr;
+    c->jpeg_bytes = 0;
+    CU_CHECK(c, cudaMalloc(&c->jpeg_scratch, need));
+    c->jpeg_bytes = need;
+  }
+  p.planes = (uint8_t*)c->jpeg_scratch;
+  if (src_is_device) {
+    p.coef = coef;
+    p.quant = quant;
+  } else {
+    int16_t* cd = (int16_t*)(p.planes + planes_al);
+    uint16_t* qd = (uint16_t*)(p.planes + planes_al + coef_al);
+    CU_CHECK(c, cudaMemcpyAsync(cd, coef, coef_bytes, cudaMemcpyHostToDevice, s));
+    CU_CHECK(c, cudaMemcpyAsync(qd, quant, quant_bytes, cudaMemcpyHostToDevice, s));
+    p.coef = cd;
+    p.quant = qd;
+  }
+  cudaError_t e = launch_jpeg_reconstruct(p, s);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_reconstruct: %s", cudaGetErrorString(e));
   return AQ_OK;
 }
 

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define AQ_ABI_VERSION 3
+#define AQ_ABI_VERSION 4
 
 typedef enum aq_status {
   AQ_OK = 0,
@@ -214,6 +214,44 @@ int aq_geocode_label_text(const char* text, int x_offset, int y_offset, const do
 /* Cage area estimate from a box in metres: square = 0 -> get_circle_area_from_bbox, 1 -> get_square_area_from_bbox
  * [REF src/process_yolo/calc_net_areas.py:24-82]; out = (estimate, variance, min, max). */
 int aq_cage_areas(int square, double w, double h, int x_border, int y_border, double out[4]);
+
+/* ------------------------------------------------------------------ JPEG tiles */
+/*
+ * Hybrid decoder for the tiles gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74] and upstream
+ * utils/dataloaders.py::LoadImages reads with cv2.imread [UPSTREAM-RECALLED]: the host walks the markers and undoes the
+ * Huffman coding (sequential by nature), the GPU does all the arithmetic -- dequantisation, the 8x8 inverse DCT, chroma
+ * upsampling and YCbCr -> RGB -- with results bit-identical to cv2.imread / libjpeg's defaults (accurate integer IDCT
+ * "islow", triangle-filter "fancy" upsampling, 16-bit fixed-point colour conversion).  Supported: baseline / 8-bit
+ * extended sequential Huffman files, one interleaved scan, grayscale, YCbCr 4:4:4 and 4:2:0, restart intervals.
+ * Anything else (progressive, arithmetic, CMYK, 4:2:2 ...) returns AQ_ERR_UNSUPPORTED -- the caller decides, nothing is
+ * decoded silently some other way.
+ */
+typedef struct aq_jpeg_info {
+  int width, height;
+  int ncomp;            /* 1 or 3 */
+  int hs, vs;           /* luma sampling factors: (1,1) or (2,2) */
+  int mcus_x, mcus_y;   /* MCU grid: ceil(width / (8 hs)) x ceil(height / (8 vs)) */
+  int restart_interval;
+  size_t coef_count;    /* int16 values aq_jpeg_entropy_decode writes */
+} aq_jpeg_info;
+/* Host only; needs no context. */
+int aq_jpeg_probe(const uint8_t* data, size_t len, aq_jpeg_info* info);
+/*
+ * Host only.  coef: component planes one after another (Y, then Cb, Cr), each a raster of 8x8 blocks
+ * [block row][block column][64 coefficients in natural (row-major) order], luma plane (mcus_y vs) x (mcus_x hs) blocks,
+ * chroma planes mcus_y x mcus_x blocks; quantised values exactly as coded (DC prediction undone).
+ * quant: 3 x 64 uint16 quantisation steps in natural order (table of component 0, 1, 2).
+ */
+int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* coef, size_t coef_cap, uint16_t* quant);
+/*
+ * Device half: n images of identical geometry (as tiles are).  coef = n x coef_count int16 and quant = n x 192 uint16 as
+ * written by aq_jpeg_entropy_decode (device pointers, or host pointers when src_is_device == 0: the H2D copies are issued
+ * here).  out_dev: (n, height, width, 3) uint8 in BGR order (bgr_out != 0, what cv2.imread returns) or RGB; grayscale
+ * files give three equal channels as cv2.IMREAD_COLOR does.  Feed out_dev to aq_preprocess / aq_detect with
+ * src_is_device = 1.  Does not synchronise.
+ */
+int aq_jpeg_reconstruct(aq_ctx* ctx, const int16_t* coef, const uint16_t* quant, int n, int width, int height, int ncomp,
+                        int hs, int bgr_out, int src_is_device, uint8_t* out_dev, void* stream);
 
 /* ------------------------------------------------------------------ misc */
 /*

@@ -25,6 +25,12 @@ class GeoRow(C.Structure):
                 ("ymax_m", C.c_double)]
 
 
+class JpegInfo(C.Structure):
+    """aq_jpeg_info (include/aqua_b200.h)."""
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("ncomp", C.c_int), ("hs", C.c_int), ("vs", C.c_int),
+                ("mcus_x", C.c_int), ("mcus_y", C.c_int), ("restart_interval", C.c_int), ("coef_count", C.c_size_t)]
+
+
 class ConvDesc(C.Structure):
     _fields_ = [("src", C.c_int), ("src_c_off", C.c_int), ("c_in", C.c_int),
                 ("dst", C.c_int), ("dst_c_off", C.c_int), ("c_out", C.c_int),
@@ -90,6 +96,10 @@ SIGNATURES = {
                                    C.POINTER(C.c_char_p), C.c_int, C.c_int]),
     "aq_format_label_text": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
                                        C.c_size_t]),
+    "aq_jpeg_probe": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(JpegInfo)]),
+    "aq_jpeg_entropy_decode": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "aq_jpeg_reconstruct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                      C.c_int, C.c_void_p, C.c_void_p]),
     "aq_memcpy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]),
     "aq_sync": (C.c_int, [C.c_void_p, C.c_void_p]),
 }

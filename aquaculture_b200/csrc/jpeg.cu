@@ -16,8 +16,7 @@ constexpr int F_0_298 = 2446, F_0_390 = 3196, F_0_541 = 4433, F_0_765 = 6270, F_
               F_1_501 = 12299, F_1_847 = 15137, F_1_961 = 16069, F_2_053 = 16819, F_2_562 = 20995, F_3_072 = 25172;
 
 // One 1-D pass of the 8-point inverse DCT (even part: rotator sqrt(2) c(-6); odd part: 4-rotator form).
-// In: s[0..7] (already scaled); out: the eight outputs BEFORE the descale; `dc_shift` = the left shift of the even
-// terms (CONST_BITS).
+// In: s[0..7]; out: the eight outputs before the descale.
 __device__ __forceinline__ void idct8(const int (&s)[8], int (&o)[8]) {
   int z2 = s[2], z3 = s[6];
   int z1 = (z2 + z3) * F_0_541;
@@ -135,6 +134,7 @@ __global__ void __launch_bounds__(256) jpeg_colour_kernel(JpegParams p) {
     const int cy = y >> 1;
     const int fy = min(max((y & 1) ? cy + 1 : cy - 1, 0), ch - 1);
     const int ci = x0 >> 1;
+    const bool box = cw <= 2;  // libjpeg filters only components more than two samples wide; narrower ones are replicated
 #pragma unroll
     for (int pl = 0; pl < 2; ++pl) {
       const uint8_t* base = planes + p.luma_plane + (size_t)pl * p.chroma_plane;
@@ -144,13 +144,13 @@ __global__ void __launch_bounds__(256) jpeg_colour_kernel(JpegParams p) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int c = min(max(ci - 1 + j, 0), cw - 1);
-        sum[j] = 3 * (int)near[c] + (int)far[c];
+        sum[j] = box ? 4 * (int)near[c] : 3 * (int)near[c] + (int)far[c];
       }
       int* o = pl ? cr : cb;
-      o[0] = (3 * sum[1] + sum[0] + 8) >> 4;
-      o[1] = (3 * sum[1] + sum[2] + 7) >> 4;
-      o[2] = (3 * sum[2] + sum[1] + 8) >> 4;
-      o[3] = (3 * sum[2] + sum[3] + 7) >> 4;
+      o[0] = (3 * sum[1] + (box ? sum[1] : sum[0]) + 8) >> 4;
+      o[1] = (3 * sum[1] + (box ? sum[1] : sum[2]) + 7) >> 4;
+      o[2] = (3 * sum[2] + (box ? sum[2] : sum[1]) + 8) >> 4;
+      o[3] = (3 * sum[2] + (box ? sum[2] : sum[3]) + 7) >> 4;
     }
   }
   unsigned char px[12];

@@ -188,6 +188,7 @@ class TileDetector:
         self._slot = 0
         self._inflight = [None, None]
         self._pin, self._pin_i = {}, {}
+        self._jpeg_out = {}
 
     # ------------------------------------------------------------------ plan
     def _build(self, sd):
@@ -301,6 +302,43 @@ class TileDetector:
         self._inflight[slot] = tiles  # keeps the source alive while the copy stream may still read it
         return slot, n, ticket
 
+    # ------------------------------------------------------------------ JPEG tiles
+    def jpeg_staging(self, n, coef_count):
+        """One of two alternating pinned staging areas for entropy-decoded tiles: (coef int16 (n, coef_count),
+        quant uint16 (n, 192)) numpy views; fill them with `jpeg.entropy_decode` (host threads), then call
+        `decode_jpeg_batch` / `detect_submit_jpeg`.  A staging area is reused every second call."""
+        key = ("jpeg", coef_count)
+        if self._pin.get(key) is None:
+            self._pin[key] = [(torch.empty(self.batch, coef_count, dtype=torch.int16).pin_memory(),
+                               torch.empty(self.batch, 192, dtype=torch.uint16).pin_memory()) for _ in range(2)]
+            self._pin_i[key] = 0
+        i = self._pin_i[key]
+        self._pin_i[key] = i ^ 1
+        c, q = self._pin[key][i]
+        return c[:n].numpy(), q[:n].numpy()
+
+    def decode_jpeg_batch(self, coef: np.ndarray, quant: np.ndarray, width, height, ncomp, hs, bgr=True, stream=None) -> torch.Tensor:
+        """Device half of the hybrid JPEG decoder (aq_jpeg_reconstruct): coefficients + tables of n equally-shaped tiles
+        (host arrays as `jpeg.entropy_decode` fills them) -> uint8 (n, height, width, 3) cuda tensor, bit-identical to
+        cv2.imread of the same files.  Enqueued on the context's stream (not synchronised): consume the result with
+        `detect_submit(..., src_is_device=True)` or call `ctx.sync()` before reading it elsewhere."""
+        n = coef.shape[0]
+        assert coef.dtype == np.int16 and coef.flags.c_contiguous and quant.dtype == np.uint16 and quant.shape == (n, 192)
+        key = (height, width)
+        if self._jpeg_out.get(key) is None:
+            self._jpeg_out[key] = torch.empty(self.batch, height, width, 3, dtype=torch.uint8, device=f"cuda:{self.ctx.device}")
+            torch.cuda.synchronize(self.ctx.device)
+        out = self._jpeg_out[key][:n]
+        self.ctx.call("aq_jpeg_reconstruct", C.c_void_p(coef.ctypes.data), C.c_void_p(quant.ctypes.data), n, width, height, ncomp,
+                      hs, int(bgr), 0, C.c_void_p(out.data_ptr()), stream)
+        return out
+
+    def detect_submit_jpeg(self, coef: np.ndarray, quant: np.ndarray, width, height, ncomp, hs, stream=None):
+        """JPEG tiles -> detections without the decoded pixels ever visiting the host: reconstruct on the device, then the
+        usual batch (letterbox, conv stack, decode, NMS).  Returns a ticket for `detect_wait`."""
+        dev = self.decode_jpeg_batch(coef, quant, width, height, ncomp, hs, bgr=True, stream=stream)
+        return self.detect_submit(dev, bgr=True, src_is_device=True, stream=stream)
+
     def pinned_input(self, n, h, w) -> torch.Tensor:
         """One of two alternating pinned uint8 (n, h, w, 3) host buffers for `detect_submit` (a buffer is reused
         every second call, i.e. after its batch has been waited for in a two-deep pipeline)."""
@@ -364,6 +402,28 @@ def tile_stats(ctx: Context, src: torch.Tensor, bgr=True, tile: int = 0, win0: i
         ctx.call("aq_tile_stats", C.c_void_p(src.data_ptr()), n, src.shape[1], src.shape[2], int(bgr), 0, 0, 0,
                  out.ctypes.data, None)
     return out
+
+
+def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True) -> np.ndarray:
+    """Hybrid decode of equally-shaped JPEG files without a planned model (tests, tools): host Huffman decoding +
+    aq_jpeg_reconstruct -> uint8 (n, h, w, 3) numpy array (BGR = what cv2.imread returns).  The CLI uses the
+    pipelined `TileDetector.detect_submit_jpeg` instead."""
+    from . import jpeg
+    infos = [jpeg.probe(b) for b in blobs]
+    i0 = infos[0]
+    geo = (i0.width, i0.height, i0.ncomp, i0.hs)
+    assert all((i.width, i.height, i.ncomp, i.hs) == geo for i in infos), "files of one batch must share their geometry"
+    n = len(blobs)
+    coef = np.zeros((n, i0.coef_count), np.int16)
+    quant = np.zeros((n, 192), np.uint16)
+    for k, b in enumerate(blobs):
+        jpeg.entropy_decode(b, coef[k], quant[k])
+    out = torch.empty(n, i0.height, i0.width, 3, dtype=torch.uint8, device=f"cuda:{ctx.device}")
+    torch.cuda.synchronize(ctx.device)
+    ctx.call("aq_jpeg_reconstruct", C.c_void_p(coef.ctypes.data), C.c_void_p(quant.ctypes.data), n, i0.width, i0.height, i0.ncomp,
+             i0.hs, int(bgr), 0, C.c_void_p(out.data_ptr()), None)
+    ctx.sync()
+    return out.cpu().numpy()
 
 
 def is_blank(stats_row) -> bool:

@@ -1,0 +1,46 @@
+"""Host side of the hybrid JPEG tile decoder (include/aqua_b200.h "JPEG tiles").
+
+Replaces the cv2.imread call of upstream utils/dataloaders.py::LoadImages.__next__ [UPSTREAM-RECALLED] for the tiles
+gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74]: the C parser in the library undoes the Huffman coding
+on host threads (ctypes releases the GIL), the GPU does dequantisation, IDCT, chroma upsampling and colour conversion
+(`TileDetector.decode_jpeg_batch` in engine.py).  Files the parser does not cover (progressive, CMYK, 4:2:2 ...) raise
+`JpegUnsupported`; the caller decides what to do with them -- nothing is decoded silently another way here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+AQ_ERR_UNSUPPORTED = -5
+
+
+class JpegUnsupported(_lib.AquaError):
+    pass
+
+
+def probe(data: bytes | np.ndarray) -> _lib.JpegInfo:
+    """Geometry of a JPEG file (aq_jpeg_probe).  `data`: the file's bytes."""
+    lib = _lib.load()
+    buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+    info = _lib.JpegInfo()
+    rc = lib.aq_jpeg_probe(buf.ctypes.data, buf.size, C.byref(info))
+    if rc == AQ_ERR_UNSUPPORTED:
+        raise JpegUnsupported("JPEG variant without a device path (progressive / arithmetic / CMYK / 4:2:2 ...)")
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_probe failed ({rc}): not a decodable JPEG file")
+    return info
+
+
+def entropy_decode(data: bytes | np.ndarray, coef: np.ndarray, quant: np.ndarray) -> None:
+    """Huffman-decode one file into `coef` (int16, >= info.coef_count values) and `quant` (uint16, 192)."""
+    lib = _lib.load()
+    buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+    assert coef.dtype == np.int16 and coef.flags.c_contiguous and quant.dtype == np.uint16 and quant.size >= 192
+    rc = lib.aq_jpeg_entropy_decode(buf.ctypes.data, buf.size, coef.ctypes.data, coef.size, quant.ctypes.data)
+    if rc == AQ_ERR_UNSUPPORTED:
+        raise JpegUnsupported("JPEG variant without a device path")
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_entropy_decode failed ({rc}): corrupt or truncated entropy-coded data")

@@ -1,0 +1,146 @@
+"""JPEG tiles.  CPU: the host Huffman parser of the library + the oracle's integer restatement of the
+reconstruction must reproduce cv2.imdecode (the genuine libjpeg-turbo behind upstream's cv2.imread) bit for bit on the
+committed golden files and on fresh files; unsupported variants are refused.  GPU: aq_jpeg_reconstruct against the same
+vectors, and detections from JPEG tiles identical to detections from the cv2-decoded pixels."""
+import io
+import os
+
+import cv2
+import numpy as np
+import pytest
+import torch
+
+from aquaculture_b200 import _lib, engine, jpeg, weights
+from oracle import jpeg as OJ
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "jpeg_ref.npz"))
+CASES = sorted(k[4:] for k in GOLD.files if k.startswith("jpg_"))
+
+
+def host_decode(blob):
+    info = jpeg.probe(blob)
+    coef = np.zeros(info.coef_count, np.int16)
+    quant = np.zeros(192, np.uint16)
+    jpeg.entropy_decode(blob, coef, quant)
+    return info, coef, quant
+
+
+def tile_scene(h, w, seed):
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 256, (h // 16 + 2, w // 16 + 2, 3), dtype=np.uint8)
+    a = cv2.resize(a, (w, h), interpolation=cv2.INTER_CUBIC).astype(np.int32) + rng.integers(-12, 12, (h, w, 3))
+    return np.clip(a, 0, 255).astype(np.uint8)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_oracle_and_host_parser_match_golden(case):
+    blob = GOLD["jpg_" + case].tobytes()
+    info, coef, quant = host_decode(blob)
+    ref = GOLD["bgr_" + case]
+    assert (info.height, info.width) == ref.shape[:2]
+    got = OJ.reconstruct(coef, quant, info.width, info.height, info.ncomp, info.hs)
+    assert np.array_equal(got, ref)
+
+
+def test_golden_still_matches_this_cv2():
+    """The committed vectors were produced by cv2.imdecode; the library in this environment must agree with them
+    (guards the oracle against a cv2 build with different IDCT / upsampling defaults)."""
+    for case in CASES[::5]:
+        assert np.array_equal(cv2.imdecode(GOLD["jpg_" + case], cv2.IMREAD_COLOR), GOLD["bgr_" + case])
+
+
+@pytest.mark.parametrize("hw,quality", [((640, 640), 75), ((1024, 1024), 75), ((200, 328), 90)])
+def test_fresh_tiles_match_cv2(hw, quality):
+    img = tile_scene(*hw, seed=hw[0] + quality)
+    ok, enc = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, quality])
+    info, coef, quant = host_decode(enc.tobytes())
+    assert (info.ncomp, info.hs, info.vs) == (3, 2, 2)
+    got = OJ.reconstruct(coef, quant, info.width, info.height, info.ncomp, info.hs)
+    assert np.array_equal(got, cv2.imdecode(enc, cv2.IMREAD_COLOR))
+
+
+@pytest.mark.parametrize("name", ["unsupported_progressive", "unsupported_422", "unsupported_cmyk"])
+def test_unsupported_variants_are_refused(name):
+    with pytest.raises(jpeg.JpegUnsupported):
+        jpeg.probe(GOLD[name].tobytes())
+    with pytest.raises(jpeg.JpegUnsupported):
+        jpeg.entropy_decode(GOLD[name].tobytes(), np.zeros(1 << 16, np.int16), np.zeros(192, np.uint16))
+
+
+def test_corrupt_and_truncated_files_error():
+    blob = GOLD["jpg_" + CASES[0]].tobytes()
+    with pytest.raises(_lib.AquaError):
+        jpeg.probe(b"not a jpeg at all")
+    with pytest.raises(_lib.AquaError):
+        jpeg.probe(blob[:40])                       # cut inside the headers
+    info = jpeg.probe(blob)
+    with pytest.raises((_lib.AquaError, AssertionError)):
+        jpeg.entropy_decode(blob, np.zeros(info.coef_count - 64, np.int16), np.zeros(192, np.uint16))  # buffer too small
+    # a scan cut short decodes like libjpeg does (zero bits fed after the end of data): no crash, same geometry
+    coef = np.zeros(info.coef_count, np.int16)
+    try:
+        jpeg.entropy_decode(blob[:len(blob) // 2], coef, np.zeros(192, np.uint16))
+    except _lib.AquaError:
+        pass
+
+
+# ------------------------------------------------------------------ GPU
+@pytest.fixture(scope="module")
+def ctx():
+    c = engine.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+def test_device_reconstruct_matches_golden(ctx, case):
+    got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()])
+    assert np.array_equal(got[0], GOLD["bgr_" + case])
+
+
+@pytest.mark.gpu
+def test_device_reconstruct_rgb_order(ctx):
+    case = CASES[0]
+    got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()], bgr=False)
+    assert np.array_equal(got[0], GOLD["bgr_" + case][:, :, ::-1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hw,n", [((1024, 1024), 5), ((640, 640), 8), ((200, 328), 3)])
+def test_device_reconstruct_batch_matches_cv2(ctx, hw, n):
+    blobs = []
+    for i in range(n):
+        ok, enc = cv2.imencode(".jpg", tile_scene(*hw, seed=100 + i), [cv2.IMWRITE_JPEG_QUALITY, 60 + 5 * i])  # tables differ per file
+        blobs.append(enc.tobytes())
+    got = engine.decode_jpeg_files(ctx, blobs)
+    for i, b in enumerate(blobs):
+        assert np.array_equal(got[i], cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR)), i
+
+
+@pytest.mark.gpu
+def test_detect_from_jpeg_equals_detect_from_pixels():
+    """Whole path: JPEG tiles -> (host Huffman, device IDCT/colour) -> letterbox -> conv stack -> NMS gives exactly the
+    detections of the same detector fed the cv2.imread pixels."""
+    os.environ["AQUA_AUTOTUNE"] = "0"
+    try:
+        sd = weights.synthetic_state(3, 0)
+        det = engine.TileDetector(sd, 3, batch=4, imgsz=(640, 640), device=0)
+    finally:
+        os.environ.pop("AQUA_AUTOTUNE", None)
+    blobs, pix = [], []
+    for i in range(4):
+        ok, enc = cv2.imencode(".jpg", tile_scene(1024, 1024, seed=i), [cv2.IMWRITE_JPEG_QUALITY, 75])
+        blobs.append(enc.tobytes())
+        pix.append(cv2.imdecode(enc, cv2.IMREAD_COLOR))
+    ref = det.detect(torch.from_numpy(np.stack(pix)).pin_memory(), bgr=True)
+    ref_d, ref_c = ref.dets.copy(), ref.counts.copy()
+    info = jpeg.probe(blobs[0])
+    coef, quant = det.jpeg_staging(4, info.coef_count)
+    for i, b in enumerate(blobs):
+        jpeg.entropy_decode(b, coef[i], quant[i])
+    got = det.detect_wait(det.detect_submit_jpeg(coef, quant, info.width, info.height, info.ncomp, info.hs))
+    assert np.array_equal(got.counts, ref_c)
+    for i in range(4):
+        assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
+    det.close()

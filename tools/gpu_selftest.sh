@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
 run() { # name, pytest -k expr
-  timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -q -x --tb=short -k "$2" > gpurun_out/selftest_$1.log 2>&1
+  timeout 600 python -m pytest tests/test_gpu_kernels.py tests/test_jpeg.py -m gpu -q -x --tb=short -k "$2" > gpurun_out/selftest_$1.log 2>&1
   echo "$1 exit=$? $(tail -1 gpurun_out/selftest_$1.log)"
 }
 run conv1x1 "conv1x1 and not folded"
@@ -20,3 +20,4 @@ run detect "detect_decode"
 run prepost "preprocess or sppf or tile_stats"
 run nms "nms"
 run e2e "e2e or label_files"
+run jpeg "jpeg"

@@ -67,6 +67,11 @@ def parse_opt(argv=None):
                         "(replaces src/load_data/tile_tifs.py; labels are named <stem>_<x>_<y>.txt like its tiles)")
     p.add_argument("--skip-blank", action="store_true",
                    help="with --raster-tile: skip windows the reference's is_blank() calls blank (src/utils.py:325-350)")
+    p.add_argument("--jpeg-decode", choices=("device", "host"), default="device",
+                   help="device: baseline .jpg/.jpeg tiles are Huffman-decoded by the library's C parser on the io threads and "
+                        "reconstructed (IDCT, chroma upsampling, colour) on the GPU, bit-identical to cv2.imread; variants the "
+                        "parser refuses (progressive, 4:2:2, CMYK) and other formats are read with cv2.imread as upstream "
+                        "does.  host: cv2.imread for everything")
     p.add_argument("--verbose", action="store_true", help="per-image log lines as upstream prints them")
     p.add_argument("--io-threads", type=int, default=8)
     opt = p.parse_args(argv)
@@ -209,12 +214,36 @@ def run(opt, argv) -> int:
         stems = [Path(f).stem for f in files]
 
     import cv2
+    from . import jpeg
     cv2.setNumThreads(1)
+    device_jpeg = opt.jpeg_decode == "device" and opt.raster_tile <= 0
+    n_host_decoded = [0]
+
+    class JpegTile:
+        """An entropy-decoded tile waiting for the device half of the decoder (coefficients + tables)."""
+        __slots__ = ("info", "coef", "quant", "key")
 
     def load(item):
         kind, v = item
         if kind == "synthetic":
             return tiles.synthetic_tile(v, opt.synthetic_size, opt.synthetic_size, opt.seed)
+        if device_jpeg and v.rsplit(".", 1)[-1].lower() in ("jpg", "jpeg"):
+            with open(v, "rb") as fh:
+                blob = np.frombuffer(fh.read(), np.uint8)
+            try:
+                t = JpegTile()
+                t.info = jpeg.probe(blob)
+                t.coef = np.empty(t.info.coef_count, np.int16)
+                t.quant = np.empty(192, np.uint16)
+                jpeg.entropy_decode(blob, t.coef, t.quant)
+                t.key = ("jpeg", t.info.height, t.info.width, t.info.ncomp, t.info.hs)
+                return t
+            except jpeg.JpegUnsupported:
+                n_host_decoded[0] += 1  # e.g. progressive: decoded on the host like upstream does, and reported below
+                im = cv2.imdecode(blob, cv2.IMREAD_COLOR)
+                if im is None:
+                    raise SystemExit(f"Image Not Found {v}")
+                return im
         im = cv2.imread(v)  # BGR, as upstream LoadImages
         if im is None:
             raise SystemExit(f"Image Not Found {v}")
@@ -260,14 +289,26 @@ def run(opt, argv) -> int:
     def flush(shape0, group):
         # two-deep pipeline: this batch is submitted (H2D on the copy stream + kernels) before the previous one is
         # waited for, so image decoding / label writing on the host overlap the GPU
+        is_jpeg = shape0[0] == "jpeg"
+        if is_jpeg:
+            _, h0, w0, ncomp, hs = shape0
+            shape0 = (h0, w0)
         h0, w0 = shape0
         net_hw = net_shape_for(h0, w0, imgsz)
         det = detector_for(net_hw)
         t0 = time.perf_counter()
-        batch = det.pinned_input(len(group), h0, w0)
-        np.stack([g[0] for g in group], out=batch.numpy())
-        dt[0] += time.perf_counter() - t0
-        ticket = det.detect_submit(batch, bgr=True)
+        if is_jpeg:
+            coef, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count)
+            for i, g in enumerate(group):
+                coef[i] = g[0].coef
+                quant[i] = g[0].quant
+            dt[0] += time.perf_counter() - t0
+            ticket = det.detect_submit_jpeg(coef, quant, w0, h0, ncomp, hs)
+        else:
+            batch = det.pinned_input(len(group), h0, w0)
+            np.stack([g[0] for g in group], out=batch.numpy())
+            dt[0] += time.perf_counter() - t0
+            ticket = det.detect_submit(batch, bgr=True)
         finish()
         deferred.append((det, ticket, [(None, g[1]) for g in group], shape0, net_hw))
 
@@ -323,7 +364,7 @@ def run(opt, argv) -> int:
         imgs = list(pool.map(load, chunk))
         dt[0] += time.perf_counter() - t0
         for im, stem in zip(imgs, stems[pos:pos + B]):
-            key = im.shape[:2]
+            key = im.key if isinstance(im, JpegTile) else im.shape[:2]
             pending.setdefault(key, []).append((im, stem))
             if len(pending[key]) == B:
                 flush(key, pending.pop(key))
@@ -350,6 +391,8 @@ def run(opt, argv) -> int:
         per = 1e3 / max(seen, 1)
         print(f"Speed: {dt[0] * per:.2f}ms load, {dt[1] * per:.2f}ms pre-process+inference+NMS+labels per image at shape "
               f"({opt.batch_size}, 3, {imgsz[0]}, {imgsz[1]}); {totals[0] / wall:.1f} tiles/s over {world} GPU(s)")
+        if n_host_decoded[0]:
+            print(f"{n_host_decoded[0]} JPEG file(s) of a variant without a device path were decoded with cv2 on the host")
         if opt.save_txt:
             print(f"{totals[1]} labels saved to {label_dir} ({totals[2]} detections in {totals[0]} images)")
         print(f"Results saved to {save_dir}")

@@ -144,3 +144,29 @@ def test_detect_from_jpeg_equals_detect_from_pixels():
     for i in range(4):
         assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
     det.close()
+
+
+@pytest.mark.gpu
+def test_cli_device_jpeg_equals_host_decode(tmp_path, monkeypatch, capsys):
+    """detect.py over a directory of .jpeg tiles (what the reference's tiler writes [REF src/load_data/tile_tifs.py:74]):
+    the default --jpeg-decode device run writes exactly the label files of the cv2.imread run; a progressive file and a
+    PNG in the same directory go through cv2 and are reported."""
+    from PIL import Image
+    from aquaculture_b200 import detect_cli as cli
+    from aquaculture_b200 import tiles as T
+    monkeypatch.setenv("AQUA_AUTOTUNE", "0")
+    src = tmp_path / "jpegs"
+    src.mkdir()
+    parts = T.synthetic_tiles(range(7), 1024, 1024, seed=9)
+    for i in range(5):
+        cv2.imwrite(str(src / f"ORTHO2020_{i}_0_0.jpeg"), parts[i], [cv2.IMWRITE_JPEG_QUALITY, 75])
+    Image.fromarray(parts[5]).save(str(src / "ORTHO2020_5_0_0.jpeg"), "JPEG", progressive=True)
+    cv2.imwrite(str(src / "ORTHO2020_6_0_0.png"), parts[6])
+    common = ["--weights", "synthetic", "--source", str(src), "--nosave", "--save-txt", "--save-conf", "--batch-size", "4",
+              "--project", str(tmp_path / "runs")]
+    assert cli.main(common + ["--name", "dev"]) == 0
+    assert "1 JPEG file(s) of a variant without a device path" in capsys.readouterr().out
+    assert cli.main(common + ["--name", "host", "--jpeg-decode", "host"]) == 0
+    ld = {p.name: p.read_text() for p in (tmp_path / "runs" / "dev" / "labels").glob("*.txt")}
+    lh = {p.name: p.read_text() for p in (tmp_path / "runs" / "host" / "labels").glob("*.txt")}
+    assert len(lh) >= 5 and ld == lh

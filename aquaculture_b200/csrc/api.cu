@@ -91,6 +91,13 @@ struct aq_ctx {
   size_t stats_bytes = 0;
   void* jpeg_scratch = nullptr;   // aq_jpeg_reconstruct: component planes (+ staged coefficients / tables for host input)
   size_t jpeg_bytes = 0;
+  // aq_jpeg_reconstruct_packed: two device staging areas filled on the copy stream
+  void* jpk_stage[2] = {nullptr, nullptr};
+  size_t jpk_bytes[2] = {0, 0};
+  cudaEvent_t ev_jpk_h2d[2] = {nullptr, nullptr};   // staging area filled (copy stream)
+  cudaEvent_t ev_jpk_used[2] = {nullptr, nullptr};  // staging area consumed by the IDCT kernel (compute stream)
+  bool jpk_recorded[2] = {false, false};
+  int jpk_slot = 0;
   // nms scratch
   void* nms_scratch = nullptr;
   size_t nms_scratch_bytes = 0;
@@ -913,6 +920,11 @@ void aq_destroy(aq_ctx* c) {
   if (c->nms_scratch) cudaFree(c->nms_scratch);
   if (c->stats_scratch) cudaFree(c->stats_scratch);
   if (c->jpeg_scratch) cudaFree(c->jpeg_scratch);
+  for (int i = 0; i < 2; ++i) {
+    if (c->jpk_stage[i]) cudaFree(c->jpk_stage[i]);
+    if (c->ev_jpk_h2d[i]) cudaEventDestroy(c->ev_jpk_h2d[i]);
+    if (c->ev_jpk_used[i]) cudaEventDestroy(c->ev_jpk_used[i]);
+  }
   if (c->nms_dets) cudaFree(c->nms_dets);
   if (c->nms_counts) cudaFree(c->nms_counts);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -1527,6 +1539,66 @@ int aq_jpeg_reconstruct(aq_ctx* c, const int16_t* coef, const uint16_t* quant, i
   }
   cudaError_t e = launch_jpeg_reconstruct(p, s);
   if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_reconstruct: %s", cudaGetErrorString(e));
+  return AQ_OK;
+}
+
+int aq_jpeg_reconstruct_packed(aq_ctx* c, const uint32_t* block_desc, const uint32_t* entries, const uint64_t* tile_entry_base,
+                               size_t total_entries, const uint16_t* quant, int n, int width, int height, int ncomp, int hs,
+                               int bgr_out, uint8_t* out_dev, void* stream) {
+  if (!c || !block_desc || !entries || !tile_entry_base || !quant || !out_dev || n <= 0 || width <= 0 || height <= 0) return AQ_ERR_ARG;
+  if ((ncomp != 1 && ncomp != 3) || (hs != 1 && hs != 2) || (ncomp == 1 && hs != 1))
+    return fail(c, AQ_ERR_UNSUPPORTED, "jpeg: %d components with %dx%d luma sampling (grayscale, 4:4:4 and 4:2:0 only)", ncomp, hs, hs);
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  JpegParams p{};
+  p.n = n; p.width = width; p.height = height; p.ncomp = ncomp; p.hs = hs; p.bgr = bgr_out; p.out = out_dev;
+  jpeg_geometry(p);
+  auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+  const size_t desc_b = (size_t)n * p.blocks_per_image * sizeof(uint32_t), ent_b = total_entries * sizeof(uint32_t);
+  const size_t base_b = (size_t)n * sizeof(uint64_t), quant_b = (size_t)n * 192 * sizeof(uint16_t);
+  const size_t need = al(desc_b) + al(ent_b) + al(base_b) + al(quant_b);
+  const size_t planes = (size_t)n * p.planes_per_image;
+  if (planes > c->jpeg_bytes) {
+    if (c->jpeg_scratch) { CU_CHECK(c, cudaDeviceSynchronize()); cudaFree(c->jpeg_scratch); }
+    c->jpeg_scratch = nullptr;
+    c->jpeg_bytes = 0;
+    CU_CHECK(c, cudaMalloc(&c->jpeg_scratch, planes));
+    c->jpeg_bytes = planes;
+  }
+  const int slot = c->jpk_slot;
+  c->jpk_slot ^= 1;
+  if (!c->ev_jpk_h2d[slot]) {
+    CU_CHECK(c, cudaEventCreateWithFlags(&c->ev_jpk_h2d[slot], cudaEventDisableTiming));
+    CU_CHECK(c, cudaEventCreateWithFlags(&c->ev_jpk_used[slot], cudaEventDisableTiming));
+  }
+  if (need > c->jpk_bytes[slot]) {
+    if (c->jpk_stage[slot]) { CU_CHECK(c, cudaDeviceSynchronize()); cudaFree(c->jpk_stage[slot]); }
+    c->jpk_stage[slot] = nullptr;
+    c->jpk_bytes[slot] = 0;
+    const size_t grow = need + need / 4;  // the packed size varies from batch to batch: leave headroom
+    CU_CHECK(c, cudaMalloc(&c->jpk_stage[slot], grow));
+    c->jpk_bytes[slot] = grow;
+    c->jpk_recorded[slot] = false;
+  }
+  uint8_t* st = (uint8_t*)c->jpk_stage[slot];
+  uint32_t* d_desc = (uint32_t*)st;
+  uint32_t* d_ent = (uint32_t*)(st + al(desc_b));
+  unsigned long long* d_base = (unsigned long long*)(st + al(desc_b) + al(ent_b));
+  uint16_t* d_quant = (uint16_t*)(st + al(desc_b) + al(ent_b) + al(base_b));
+  if (c->jpk_recorded[slot]) CU_CHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_jpk_used[slot], 0));
+  CU_CHECK(c, cudaMemcpyAsync(d_desc, block_desc, desc_b, cudaMemcpyHostToDevice, c->copy_stream));
+  if (ent_b) CU_CHECK(c, cudaMemcpyAsync(d_ent, entries, ent_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_base, tile_entry_base, base_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_quant, quant, quant_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaEventRecord(c->ev_jpk_h2d[slot], c->copy_stream));
+  CU_CHECK(c, cudaStreamWaitEvent(s, c->ev_jpk_h2d[slot], 0));
+  p.planes = (uint8_t*)c->jpeg_scratch;
+  p.coef = nullptr;
+  p.block_desc = d_desc; p.entries = d_ent; p.tile_entry_base = d_base; p.quant = d_quant;
+  cudaError_t e = launch_jpeg_reconstruct(p, s);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_reconstruct_packed: %s", cudaGetErrorString(e));
+  CU_CHECK(c, cudaEventRecord(c->ev_jpk_used[slot], s));
+  c->jpk_recorded[slot] = true;
   return AQ_OK;
 }
 

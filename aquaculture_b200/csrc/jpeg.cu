@@ -52,6 +52,7 @@ __device__ __forceinline__ unsigned range_limit(int v) {
 // workspace goes back through shared memory for the row pass, and lane t stores output row t (8 bytes).
 constexpr int IDCT_THREADS = 256, IDCT_BLOCKS = IDCT_THREADS / 8, WS_PITCH = 9, WS_BLOCK = 8 * WS_PITCH + 1;
 
+template <bool PACKED>
 __global__ void __launch_bounds__(IDCT_THREADS) jpeg_idct_kernel(JpegParams p) {
   __shared__ int ws[IDCT_BLOCKS * WS_BLOCK];
   __shared__ unsigned short qs[192];
@@ -72,7 +73,24 @@ __global__ void __launch_bounds__(IDCT_THREADS) jpeg_idct_kernel(JpegParams p) {
     pw = p.chroma_pw;
   }
   int* w = ws + g * WS_BLOCK;
-  if (live) {
+  if (PACKED) {
+    // the block arrives as a short list of non-zero coefficients: clear the workspace, scatter the list
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) w[t * WS_PITCH + i] = 0;
+    }
+    __syncwarp();
+    if (live) {
+      const unsigned desc = p.block_desc[(size_t)img * p.blocks_per_image + blk];
+      const unsigned* e = p.entries + p.tile_entry_base[img] + (desc >> 7);
+      const int cnt = desc & 127;
+      for (int i = t; i < cnt; i += 8) {
+        const unsigned v = e[i];
+        const int pos = (v >> 16) & 63;
+        w[(pos >> 3) * WS_PITCH + (pos & 7)] = (int)(short)(v & 0xFFFF) * (int)qs[comp * 64 + pos];
+      }
+    }
+  } else if (live) {
     const int4 raw = *reinterpret_cast<const int4*>(p.coef + ((size_t)img * p.blocks_per_image + blk) * 64 + t * 8);
     const short* c = reinterpret_cast<const short*>(&raw);
     const unsigned short* q = qs + comp * 64 + t * 8;
@@ -196,7 +214,8 @@ void jpeg_geometry(JpegParams& p) {
 cudaError_t launch_jpeg_reconstruct(const JpegParams& p, cudaStream_t stream) {
   if (p.n <= 0 || p.n > 65535 || p.height > 65535) return cudaErrorInvalidValue;
   const unsigned gx = (unsigned)((p.blocks_per_image + IDCT_BLOCKS - 1) / IDCT_BLOCKS);
-  jpeg_idct_kernel<<<dim3(gx, p.n), IDCT_THREADS, 0, stream>>>(p);
+  if (p.coef) jpeg_idct_kernel<false><<<dim3(gx, p.n), IDCT_THREADS, 0, stream>>>(p);
+  else jpeg_idct_kernel<true><<<dim3(gx, p.n), IDCT_THREADS, 0, stream>>>(p);
   const int quads = (p.width + 3) / 4;
   jpeg_colour_kernel<<<dim3((quads + 255) / 256, p.height, p.n), 256, 0, stream>>>(p);
   return cudaGetLastError();

@@ -8,6 +8,11 @@ namespace aq {
 struct JpegParams {
   const int16_t* coef;     // n x blocks_per_image x 64, planes Y | Cb | Cr, blocks in raster order, natural order inside
   const uint16_t* quant;   // n x 3 x 64 quantisation steps, natural order
+  // packed input (coef == nullptr): per block (first entry << 7 | count), entries (position << 16 | value) and the
+  // index of each tile's first entry
+  const uint32_t* block_desc;
+  const uint32_t* entries;
+  const unsigned long long* tile_entry_base;
   uint8_t* planes;         // scratch: n x planes_per_image reconstructed samples (block-padded planes)
   uint8_t* out;            // (n, height, width, 3) uint8
   int n, width, height, ncomp, hs, bgr;

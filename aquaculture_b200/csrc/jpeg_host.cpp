@@ -25,6 +25,9 @@ struct HuffTable {
   int32_t maxcode[18];
   int32_t valoff[17];
   uint16_t look[1 << kLookBits];  // (length << 8) | symbol for codes of <= kLookBits bits, 0 = longer code
+  // AC tables only: code and magnitude bits resolved by ONE lookup when both fit in kLookBits bits:
+  // (value << 16) | (run << 8) | total bits, 0 = take the general path
+  int32_t fast_ac[1 << kLookBits];
 };
 
 bool build_table(HuffTable& t) {
@@ -51,6 +54,16 @@ bool build_table(HuffTable& t) {
     code <<= 1;
   }
   t.maxcode[17] = 0x7fffffff;
+  for (int i = 0; i < (1 << kLookBits); ++i) {
+    t.fast_ac[i] = 0;
+    const uint32_t lk = t.look[i];
+    if (!lk) continue;
+    const int len = lk >> 8, rs = lk & 0xFF, run = rs >> 4, mag = rs & 15;
+    if (mag == 0 || len + mag > kLookBits) continue;
+    int v = (i >> (kLookBits - len - mag)) & ((1 << mag) - 1);
+    if (v < (1 << (mag - 1))) v -= (1 << mag) - 1;  // Annex F.2.2.1 EXTEND
+    t.fast_ac[i] = (int32_t)((uint32_t)v << 16) | (run << 8) | (len + mag);
+  }
   t.present = true;
   return true;
 }
@@ -212,6 +225,20 @@ struct BitReader {
   int nbits = 0;
   bool hit_marker = false;
   inline void fill() {
+    if (!hit_marker && pos + 8 <= len) {
+      uint64_t v;
+      memcpy(&v, d + pos, 8);
+      const uint64_t x = ~v;  // a 0xFF byte becomes 0x00
+      if (!((x - 0x0101010101010101ULL) & ~x & 0x8080808080808080ULL)) {
+        // no 0xFF among the next eight bytes: append as many whole bytes as fit.  The bits of a partly fitting byte
+        // that land below `nbits` are the stream's own next bits, so OR-ing the same byte again later is harmless.
+        const int take = (64 - nbits) >> 3;
+        acc |= __builtin_bswap64(v) >> nbits;
+        pos += take;
+        nbits += take * 8;
+        return;
+      }
+    }
     while (nbits <= 56) {
       uint32_t b = 0;
       if (!hit_marker && pos < len) {
@@ -272,12 +299,35 @@ inline int receive_extend(BitReader& br, int s) {
   return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
 }
 
-inline bool decode_block(BitReader& br, const HuffTable& dc, const HuffTable& ac, int& pred, int16_t* blk) {
+// Sinks: where a decoded coefficient goes.  Dense = the block's 64-entry natural-order array (pre-zeroed);
+// packed = a list of (position << 16 | value) words, the form shipped to the GPU (most coefficients are zero).
+struct DenseSink {
+  int16_t* blk;
+  inline void put(int natural_pos, int v) { blk[natural_pos] = (int16_t)v; }
+};
+struct PackedSink {
+  uint32_t* out;
+  uint32_t n = 0;
+  inline void put(int natural_pos, int v) { out[n++] = ((uint32_t)natural_pos << 16) | (uint16_t)(int16_t)v; }
+};
+
+template <class Sink>
+inline bool decode_block(BitReader& br, const HuffTable& dc, const HuffTable& ac, int& pred, Sink& sink) {
   int s = decode_symbol(br, dc);
   if (s < 0 || s > 16) return false;
   if (s) pred += receive_extend(br, s);
-  blk[0] = (int16_t)pred;
+  if (pred) sink.put(0, pred);
   for (int k = 1; k < 64;) {
+    if (br.nbits < 16) br.fill();
+    const int32_t fa = ac.fast_ac[br.peek(kLookBits)];
+    if (fa) {  // run, size and magnitude bits in one lookup
+      k += (fa >> 8) & 15;
+      if (k > 63) return false;
+      br.skip(fa & 0xFF);
+      sink.put(kZigzagToNatural[k], fa >> 16);
+      ++k;
+      continue;
+    }
     const int rs = decode_symbol(br, ac);
     if (rs < 0) return false;
     const int r = rs >> 4;
@@ -285,7 +335,7 @@ inline bool decode_block(BitReader& br, const HuffTable& dc, const HuffTable& ac
     if (s) {
       k += r;
       if (k > 63) return false;
-      blk[kZigzagToNatural[k]] = (int16_t)receive_extend(br, s);
+      sink.put(kZigzagToNatural[k], receive_extend(br, s));
       ++k;
     } else {
       if (r != 15) break;  // EOB
@@ -295,35 +345,11 @@ inline bool decode_block(BitReader& br, const HuffTable& dc, const HuffTable& ac
   return true;
 }
 
-}  // namespace
-
-extern "C" int aq_jpeg_probe(const uint8_t* data, size_t len, aq_jpeg_info* info) {
-  if (!data || !info) return AQ_ERR_ARG;
-  Frame f;
-  const int rc = parse_headers(data, len, f);
-  if (rc != AQ_OK) return rc;
-  return validate(f, info);
-}
-
-extern "C" int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* coef, size_t coef_cap, uint16_t* quant) {
-  if (!data || !coef || !quant) return AQ_ERR_ARG;
-  Frame f;
-  int rc = parse_headers(data, len, f);
-  if (rc != AQ_OK) return rc;
-  aq_jpeg_info info;
-  rc = validate(f, &info);
-  if (rc != AQ_OK) return rc;
-  if (coef_cap < info.coef_count) return AQ_ERR_ARG;
-  memset(coef, 0, info.coef_count * sizeof(int16_t));
-  for (int c = 0; c < 3; ++c)
-    memcpy(quant + 64 * c, f.quant[f.comp[c < f.ncomp ? c : 0].tq], 64 * sizeof(uint16_t));
-
+// Walks the MCUs of the one interleaved scan; `visit(plane, block index in the plane)` returns the sink of that block.
+template <class Visit>
+int decode_scan(const uint8_t* data, size_t len, const Frame& f, const aq_jpeg_info& info, Visit&& visit) {
   const int hs = info.hs, vs = info.vs;
   const size_t luma_bw = (size_t)info.mcus_x * hs;
-  const size_t luma_blocks = luma_bw * info.mcus_y * vs;
-  const size_t chroma_blocks = (size_t)info.mcus_x * info.mcus_y;
-  int16_t* plane[3] = {coef, coef + luma_blocks * 64, coef + (luma_blocks + chroma_blocks) * 64};
-
   BitReader br{data, len, f.scan_off};
   int pred[3] = {0, 0, 0};
   int until_restart = f.restart_interval, next_rst = 0;
@@ -347,16 +373,71 @@ extern "C" int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* 
         until_restart = f.restart_interval;
       }
       for (int by = 0; by < vs; ++by)
-        for (int bx = 0; bx < hs; ++bx) {
-          int16_t* blk = plane[0] + (((size_t)my * vs + by) * luma_bw + (size_t)mx * hs + bx) * 64;
-          if (!decode_block(br, *dct[0], *act[0], pred[0], blk)) return AQ_ERR_IO;
-        }
-      for (int c = 1; c < f.ncomp; ++c) {
-        int16_t* blk = plane[c] + ((size_t)my * info.mcus_x + mx) * 64;
-        if (!decode_block(br, *dct[c], *act[c], pred[c], blk)) return AQ_ERR_IO;
-      }
+        for (int bx = 0; bx < hs; ++bx)
+          if (!visit(0, ((size_t)my * vs + by) * luma_bw + (size_t)mx * hs + bx, br, *dct[0], *act[0], pred[0])) return AQ_ERR_IO;
+      for (int c = 1; c < f.ncomp; ++c)
+        if (!visit(c, (size_t)my * info.mcus_x + mx, br, *dct[c], *act[c], pred[c])) return AQ_ERR_IO;
       --until_restart;
     }
   }
   return AQ_OK;
+}
+
+int open_file(const uint8_t* data, size_t len, Frame& f, aq_jpeg_info& info, uint16_t* quant) {
+  int rc = parse_headers(data, len, f);
+  if (rc != AQ_OK) return rc;
+  rc = validate(f, &info);
+  if (rc != AQ_OK) return rc;
+  for (int c = 0; c < 3; ++c) memcpy(quant + 64 * c, f.quant[f.comp[c < f.ncomp ? c : 0].tq], 64 * sizeof(uint16_t));
+  return AQ_OK;
+}
+
+}  // namespace
+
+extern "C" int aq_jpeg_probe(const uint8_t* data, size_t len, aq_jpeg_info* info) {
+  if (!data || !info) return AQ_ERR_ARG;
+  Frame f;
+  const int rc = parse_headers(data, len, f);
+  if (rc != AQ_OK) return rc;
+  return validate(f, info);
+}
+
+extern "C" int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* coef, size_t coef_cap, uint16_t* quant) {
+  if (!data || !coef || !quant) return AQ_ERR_ARG;
+  Frame f;
+  aq_jpeg_info info;
+  const int rc = open_file(data, len, f, info, quant);
+  if (rc != AQ_OK) return rc;
+  if (coef_cap < info.coef_count) return AQ_ERR_ARG;
+  memset(coef, 0, info.coef_count * sizeof(int16_t));
+  const size_t luma_blocks = (size_t)info.mcus_x * info.hs * info.mcus_y * info.vs;
+  const size_t chroma_blocks = (size_t)info.mcus_x * info.mcus_y;
+  int16_t* plane[3] = {coef, coef + luma_blocks * 64, coef + (luma_blocks + chroma_blocks) * 64};
+  return decode_scan(data, len, f, info, [&](int c, size_t b, BitReader& br, const HuffTable& dc, const HuffTable& ac, int& pred) {
+    DenseSink sink{plane[c] + b * 64};
+    return decode_block(br, dc, ac, pred, sink);
+  });
+}
+
+extern "C" int aq_jpeg_entropy_decode_packed(const uint8_t* data, size_t len, uint32_t* block_desc, size_t block_cap,
+                                             uint32_t* entries, size_t entries_cap, size_t* n_entries, uint16_t* quant) {
+  if (!data || !block_desc || !entries || !n_entries || !quant) return AQ_ERR_ARG;
+  Frame f;
+  aq_jpeg_info info;
+  const int rc = open_file(data, len, f, info, quant);
+  if (rc != AQ_OK) return rc;
+  if (block_cap < info.coef_count / 64 || entries_cap < info.coef_count || info.coef_count >= ((size_t)1 << 25)) return AQ_ERR_ARG;
+  const size_t luma_blocks = (size_t)info.mcus_x * info.hs * info.mcus_y * info.vs;
+  const size_t chroma_blocks = (size_t)info.mcus_x * info.mcus_y;
+  const size_t plane_first[3] = {0, luma_blocks, luma_blocks + chroma_blocks};
+  uint32_t total = 0;
+  const int rc2 = decode_scan(data, len, f, info, [&](int c, size_t b, BitReader& br, const HuffTable& dc, const HuffTable& ac, int& pred) {
+    PackedSink sink{entries + total};
+    const bool ok = decode_block(br, dc, ac, pred, sink);
+    block_desc[plane_first[c] + b] = (total << 7) | sink.n;  // first entry (25 bits) | entries in the block (<= 64)
+    total += sink.n;
+    return ok;
+  });
+  *n_entries = total;
+  return rc2;
 }

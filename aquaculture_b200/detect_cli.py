@@ -219,10 +219,6 @@ def run(opt, argv) -> int:
     device_jpeg = opt.jpeg_decode == "device" and opt.raster_tile <= 0
     n_host_decoded = [0]
 
-    class JpegTile:
-        """An entropy-decoded tile waiting for the device half of the decoder (coefficients + tables)."""
-        __slots__ = ("info", "coef", "quant", "key")
-
     def load(item):
         kind, v = item
         if kind == "synthetic":
@@ -231,13 +227,7 @@ def run(opt, argv) -> int:
             with open(v, "rb") as fh:
                 blob = np.frombuffer(fh.read(), np.uint8)
             try:
-                t = JpegTile()
-                t.info = jpeg.probe(blob)
-                t.coef = np.empty(t.info.coef_count, np.int16)
-                t.quant = np.empty(192, np.uint16)
-                jpeg.entropy_decode(blob, t.coef, t.quant)
-                t.key = ("jpeg", t.info.height, t.info.width, t.info.ncomp, t.info.hs)
-                return t
+                return engine.entropy_decode_file(blob)  # host half: markers + Huffman (C, GIL released)
             except jpeg.JpegUnsupported:
                 n_host_decoded[0] += 1  # e.g. progressive: decoded on the host like upstream does, and reported below
                 im = cv2.imdecode(blob, cv2.IMREAD_COLOR)
@@ -298,12 +288,10 @@ def run(opt, argv) -> int:
         det = detector_for(net_hw)
         t0 = time.perf_counter()
         if is_jpeg:
-            coef, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count)
-            for i, g in enumerate(group):
-                coef[i] = g[0].coef
-                quant[i] = g[0].quant
+            desc, ent, base, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count, sum(g[0].entries.size for g in group))
+            total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant)
             dt[0] += time.perf_counter() - t0
-            ticket = det.detect_submit_jpeg(coef, quant, w0, h0, ncomp, hs)
+            ticket = det.detect_submit_jpeg(desc, ent, base, total, quant, w0, h0, ncomp, hs)
         else:
             batch = det.pinned_input(len(group), h0, w0)
             np.stack([g[0] for g in group], out=batch.numpy())
@@ -364,7 +352,7 @@ def run(opt, argv) -> int:
         imgs = list(pool.map(load, chunk))
         dt[0] += time.perf_counter() - t0
         for im, stem in zip(imgs, stems[pos:pos + B]):
-            key = im.key if isinstance(im, JpegTile) else im.shape[:2]
+            key = im.key if isinstance(im, engine.PackedJpeg) else im.shape[:2]
             pending.setdefault(key, []).append((im, stem))
             if len(pending[key]) == B:
                 flush(key, pending.pop(key))

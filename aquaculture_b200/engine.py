@@ -303,40 +303,49 @@ class TileDetector:
         return slot, n, ticket
 
     # ------------------------------------------------------------------ JPEG tiles
-    def jpeg_staging(self, n, coef_count):
-        """One of two alternating pinned staging areas for entropy-decoded tiles: (coef int16 (n, coef_count),
-        quant uint16 (n, 192)) numpy views; fill them with `jpeg.entropy_decode` (host threads), then call
-        `decode_jpeg_batch` / `detect_submit_jpeg`.  A staging area is reused every second call."""
+    def jpeg_staging(self, n, coef_count, min_entries=0):
+        """One of two alternating pinned staging areas for entropy-decoded tiles in packed form: numpy views
+        (block_desc uint32 (n, coef_count / 64), entries uint32 (capacity >= min_entries; grown on demand, which drains
+        the pipeline first), base uint64 (n), quant uint16 (n, 192)).  Fill them (see `pack_jpeg_tiles`), then call `detect_submit_jpeg`.  An area is reused every
+        second call, i.e. after its batch has been waited for in a two-deep pipeline."""
         key = ("jpeg", coef_count)
+        if self._pin.get(key) is not None and self._pin[key][0][1].numel() < min_entries:
+            self.ctx.sync()  # copies out of the old staging areas may still be in flight
+            self._pin[key] = None
         if self._pin.get(key) is None:
-            self._pin[key] = [(torch.empty(self.batch, coef_count, dtype=torch.int16).pin_memory(),
+            nb = coef_count // 64
+            cap = max(min_entries + min_entries // 4, self.batch * coef_count // 8, 1)
+            self._pin[key] = [(torch.empty(self.batch, nb, dtype=torch.int32).pin_memory(),
+                               torch.empty(cap, dtype=torch.int32).pin_memory(),
+                               torch.empty(self.batch, dtype=torch.int64).pin_memory(),
                                torch.empty(self.batch, 192, dtype=torch.uint16).pin_memory()) for _ in range(2)]
             self._pin_i[key] = 0
         i = self._pin_i[key]
         self._pin_i[key] = i ^ 1
-        c, q = self._pin[key][i]
-        return c[:n].numpy(), q[:n].numpy()
+        d, e, b, q = self._pin[key][i]
+        return d[:n].numpy().view(np.uint32), e.numpy().view(np.uint32), b[:n].numpy().view(np.uint64), q[:n].numpy()
 
-    def decode_jpeg_batch(self, coef: np.ndarray, quant: np.ndarray, width, height, ncomp, hs, bgr=True, stream=None) -> torch.Tensor:
-        """Device half of the hybrid JPEG decoder (aq_jpeg_reconstruct): coefficients + tables of n equally-shaped tiles
-        (host arrays as `jpeg.entropy_decode` fills them) -> uint8 (n, height, width, 3) cuda tensor, bit-identical to
-        cv2.imread of the same files.  Enqueued on the context's stream (not synchronised): consume the result with
-        `detect_submit(..., src_is_device=True)` or call `ctx.sync()` before reading it elsewhere."""
-        n = coef.shape[0]
-        assert coef.dtype == np.int16 and coef.flags.c_contiguous and quant.dtype == np.uint16 and quant.shape == (n, 192)
+    def decode_jpeg_batch(self, block_desc, entries, base, total_entries, quant, width, height, ncomp, hs, bgr=True, stream=None) -> torch.Tensor:
+        """Device half of the hybrid JPEG decoder (aq_jpeg_reconstruct_packed): packed coefficients + tables of n
+        equally-shaped tiles (host arrays) -> uint8 (n, height, width, 3) cuda tensor, bit-identical to cv2.imread of the
+        same files.  H2D on the library's copy stream, kernels on the context's stream (not synchronised): consume the
+        result with `detect_submit(..., src_is_device=True)` or call `ctx.sync()` before reading it elsewhere."""
+        n = block_desc.shape[0]
+        assert block_desc.dtype == np.uint32 and entries.dtype == np.uint32 and base.dtype == np.uint64 and quant.shape == (n, 192)
         key = (height, width)
         if self._jpeg_out.get(key) is None:
             self._jpeg_out[key] = torch.empty(self.batch, height, width, 3, dtype=torch.uint8, device=f"cuda:{self.ctx.device}")
             torch.cuda.synchronize(self.ctx.device)
         out = self._jpeg_out[key][:n]
-        self.ctx.call("aq_jpeg_reconstruct", C.c_void_p(coef.ctypes.data), C.c_void_p(quant.ctypes.data), n, width, height, ncomp,
-                      hs, int(bgr), 0, C.c_void_p(out.data_ptr()), stream)
+        self.ctx.call("aq_jpeg_reconstruct_packed", C.c_void_p(block_desc.ctypes.data), C.c_void_p(entries.ctypes.data),
+                      C.c_void_p(base.ctypes.data), int(total_entries), C.c_void_p(quant.ctypes.data), n, width, height, ncomp, hs,
+                      int(bgr), C.c_void_p(out.data_ptr()), stream)
         return out
 
-    def detect_submit_jpeg(self, coef: np.ndarray, quant: np.ndarray, width, height, ncomp, hs, stream=None):
+    def detect_submit_jpeg(self, block_desc, entries, base, total_entries, quant, width, height, ncomp, hs, stream=None):
         """JPEG tiles -> detections without the decoded pixels ever visiting the host: reconstruct on the device, then the
         usual batch (letterbox, conv stack, decode, NMS).  Returns a ticket for `detect_wait`."""
-        dev = self.decode_jpeg_batch(coef, quant, width, height, ncomp, hs, bgr=True, stream=stream)
+        dev = self.decode_jpeg_batch(block_desc, entries, base, total_entries, quant, width, height, ncomp, hs, bgr=True, stream=stream)
         return self.detect_submit(dev, bgr=True, src_is_device=True, stream=stream)
 
     def pinned_input(self, n, h, w) -> torch.Tensor:
@@ -404,9 +413,40 @@ def tile_stats(ctx: Context, src: torch.Tensor, bgr=True, tile: int = 0, win0: i
     return out
 
 
-def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True) -> np.ndarray:
+class PackedJpeg:
+    """One entropy-decoded tile in packed form (host): geometry, block descriptors, entries, tables."""
+    __slots__ = ("info", "block_desc", "entries", "quant", "key")
+
+
+def entropy_decode_file(blob) -> PackedJpeg:
+    """Host half for one file (runs on an io thread; the C parser releases the GIL)."""
+    from . import jpeg
+    t = PackedJpeg()
+    t.info = jpeg.probe(blob)
+    t.block_desc = np.empty(t.info.coef_count // 64, np.uint32)
+    ent = np.empty(t.info.coef_count, np.uint32)
+    t.quant = np.empty(192, np.uint16)
+    n = jpeg.entropy_decode_packed(blob, t.block_desc, ent, t.quant)
+    t.entries = ent[:n]
+    t.key = ("jpeg", t.info.height, t.info.width, t.info.ncomp, t.info.hs)
+    return t
+
+
+def pack_jpeg_tiles(tiles_: Sequence[PackedJpeg], block_desc, entries, base, quant) -> int:
+    """Concatenate the tiles' entry lists into one staging area (see TileDetector.jpeg_staging); returns the total."""
+    pos = 0
+    for i, t in enumerate(tiles_):
+        block_desc[i] = t.block_desc
+        quant[i] = t.quant
+        base[i] = pos
+        entries[pos:pos + t.entries.size] = t.entries
+        pos += t.entries.size
+    return pos
+
+
+def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True, packed=True) -> np.ndarray:
     """Hybrid decode of equally-shaped JPEG files without a planned model (tests, tools): host Huffman decoding +
-    aq_jpeg_reconstruct -> uint8 (n, h, w, 3) numpy array (BGR = what cv2.imread returns).  The CLI uses the
+    aq_jpeg_reconstruct[_packed] -> uint8 (n, h, w, 3) numpy array (BGR = what cv2.imread returns).  The CLI uses the
     pipelined `TileDetector.detect_submit_jpeg` instead."""
     from . import jpeg
     infos = [jpeg.probe(b) for b in blobs]
@@ -414,14 +454,24 @@ def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True) -> np.ndar
     geo = (i0.width, i0.height, i0.ncomp, i0.hs)
     assert all((i.width, i.height, i.ncomp, i.hs) == geo for i in infos), "files of one batch must share their geometry"
     n = len(blobs)
-    coef = np.zeros((n, i0.coef_count), np.int16)
-    quant = np.zeros((n, 192), np.uint16)
-    for k, b in enumerate(blobs):
-        jpeg.entropy_decode(b, coef[k], quant[k])
     out = torch.empty(n, i0.height, i0.width, 3, dtype=torch.uint8, device=f"cuda:{ctx.device}")
     torch.cuda.synchronize(ctx.device)
-    ctx.call("aq_jpeg_reconstruct", C.c_void_p(coef.ctypes.data), C.c_void_p(quant.ctypes.data), n, i0.width, i0.height, i0.ncomp,
-             i0.hs, int(bgr), 0, C.c_void_p(out.data_ptr()), None)
+    if packed:
+        tl = [entropy_decode_file(b) for b in blobs]
+        desc = np.empty((n, i0.coef_count // 64), np.uint32)
+        ent = np.empty(max(1, sum(t.entries.size for t in tl)), np.uint32)
+        base = np.empty(n, np.uint64)
+        quant = np.empty((n, 192), np.uint16)
+        total = pack_jpeg_tiles(tl, desc, ent, base, quant)
+        ctx.call("aq_jpeg_reconstruct_packed", C.c_void_p(desc.ctypes.data), C.c_void_p(ent.ctypes.data), C.c_void_p(base.ctypes.data),
+                 total, C.c_void_p(quant.ctypes.data), n, i0.width, i0.height, i0.ncomp, i0.hs, int(bgr), C.c_void_p(out.data_ptr()), None)
+    else:
+        coef = np.zeros((n, i0.coef_count), np.int16)
+        quant = np.zeros((n, 192), np.uint16)
+        for k, b in enumerate(blobs):
+            jpeg.entropy_decode(b, coef[k], quant[k])
+        ctx.call("aq_jpeg_reconstruct", C.c_void_p(coef.ctypes.data), C.c_void_p(quant.ctypes.data), n, i0.width, i0.height, i0.ncomp,
+                 i0.hs, int(bgr), 0, C.c_void_p(out.data_ptr()), None)
     ctx.sync()
     return out.cpu().numpy()
 

@@ -44,3 +44,32 @@ def entropy_decode(data: bytes | np.ndarray, coef: np.ndarray, quant: np.ndarray
         raise JpegUnsupported("JPEG variant without a device path")
     if rc < 0:
         raise _lib.AquaError(f"aq_jpeg_entropy_decode failed ({rc}): corrupt or truncated entropy-coded data")
+
+
+def entropy_decode_packed(data: bytes | np.ndarray, block_desc: np.ndarray, entries: np.ndarray, quant: np.ndarray) -> int:
+    """Huffman-decode one file into the packed form (aq_jpeg_entropy_decode_packed): block_desc uint32 (>= coef_count / 64),
+    entries uint32 (>= coef_count), quant uint16 (192).  Returns the number of entries written."""
+    lib = _lib.load()
+    buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+    assert block_desc.dtype == np.uint32 and entries.dtype == np.uint32 and quant.dtype == np.uint16 and quant.size >= 192
+    assert block_desc.flags.c_contiguous and entries.flags.c_contiguous
+    n = C.c_size_t(0)
+    rc = lib.aq_jpeg_entropy_decode_packed(buf.ctypes.data, buf.size, block_desc.ctypes.data, block_desc.size, entries.ctypes.data,
+                                           entries.size, C.byref(n), quant.ctypes.data)
+    if rc == AQ_ERR_UNSUPPORTED:
+        raise JpegUnsupported("JPEG variant without a device path")
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_entropy_decode_packed failed ({rc}): corrupt or truncated entropy-coded data")
+    return int(n.value)
+
+
+def unpack(block_desc: np.ndarray, entries: np.ndarray) -> np.ndarray:
+    """Packed form -> dense int16 (blocks * 64) coefficients (tests; the device does this inside the IDCT kernel)."""
+    nb = block_desc.size
+    coef = np.zeros(nb * 64, np.int16)
+    first, cnt = (block_desc >> 7).astype(np.int64), (block_desc & 127).astype(np.int64)
+    blk = np.repeat(np.arange(nb, dtype=np.int64), cnt)
+    idx = np.repeat(first - np.concatenate([[0], np.cumsum(cnt)[:-1]]), cnt) + np.arange(cnt.sum(), dtype=np.int64)
+    e = entries[idx]
+    coef[blk * 64 + ((e >> 16) & 63)] = (e & 0xFFFF).astype(np.uint16).view(np.int16)
+    return coef

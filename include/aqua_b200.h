@@ -244,6 +244,15 @@ int aq_jpeg_probe(const uint8_t* data, size_t len, aq_jpeg_info* info);
  */
 int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* coef, size_t coef_cap, uint16_t* quant);
 /*
+ * Same decoding into the PACKED form the pipelined path ships to the GPU (most quantised coefficients are zero: a
+ * 1024 x 1024 tile at quality 75 is ~0.7 MB packed against 3.1 MB dense).  block_desc[b] for block b (same plane /
+ * raster order as above, coef_count / 64 blocks) = (index of the block's first entry << 7) | number of entries;
+ * entries[i] = (natural-order position << 16) | (uint16_t) value, in decoding order.  entries_cap >= coef_count is
+ * always enough.  *n_entries receives the number of entries written.  Host only.
+ */
+int aq_jpeg_entropy_decode_packed(const uint8_t* data, size_t len, uint32_t* block_desc, size_t block_cap, uint32_t* entries,
+                                  size_t entries_cap, size_t* n_entries, uint16_t* quant);
+/*
  * Device half: n images of identical geometry (as tiles are).  coef = n x coef_count int16 and quant = n x 192 uint16 as
  * written by aq_jpeg_entropy_decode (device pointers, or host pointers when src_is_device == 0: the H2D copies are issued
  * here).  out_dev: (n, height, width, 3) uint8 in BGR order (bgr_out != 0, what cv2.imread returns) or RGB; grayscale
@@ -252,6 +261,17 @@ int aq_jpeg_entropy_decode(const uint8_t* data, size_t len, int16_t* coef, size_
  */
 int aq_jpeg_reconstruct(aq_ctx* ctx, const int16_t* coef, const uint16_t* quant, int n, int width, int height, int ncomp,
                         int hs, int bgr_out, int src_is_device, uint8_t* out_dev, void* stream);
+/*
+ * Device half for packed input, pipelined: block_desc = n x (coef_count / 64) words, entries = the n tiles' entry lists
+ * one after another, tile_entry_base[i] = index in `entries` where tile i's list starts, total_entries = their sum;
+ * all HOST pointers (pinned for overlap).  The H2D copies are issued on the library's copy stream into one of two
+ * alternating device staging areas, so the copies of batch i+1 overlap the kernels of batch i; the kernels run on
+ * `stream`.  The host buffers of a call may be reused once the batch that consumed out_dev has been waited for
+ * (aq_detect_wait) or after aq_sync.  Does not synchronise.
+ */
+int aq_jpeg_reconstruct_packed(aq_ctx* ctx, const uint32_t* block_desc, const uint32_t* entries, const uint64_t* tile_entry_base,
+                               size_t total_entries, const uint16_t* quant, int n, int width, int height, int ncomp, int hs,
+                               int bgr_out, uint8_t* out_dev, void* stream);
 
 /* ------------------------------------------------------------------ misc */
 /*

@@ -59,6 +59,18 @@ def test_fresh_tiles_match_cv2(hw, quality):
     assert np.array_equal(got, cv2.imdecode(enc, cv2.IMREAD_COLOR))
 
 
+@pytest.mark.parametrize("case", CASES)
+def test_packed_form_equals_dense(case):
+    blob = GOLD["jpg_" + case].tobytes()
+    info, coef, quant = host_decode(blob)
+    desc = np.zeros(info.coef_count // 64, np.uint32)
+    ent = np.zeros(info.coef_count, np.uint32)
+    q2 = np.zeros(192, np.uint16)
+    n = jpeg.entropy_decode_packed(blob, desc, ent, q2)
+    assert n == int((desc & 127).sum()) == int(np.count_nonzero(coef))
+    assert np.array_equal(jpeg.unpack(desc, ent), coef) and np.array_equal(q2, quant)
+
+
 @pytest.mark.parametrize("name", ["unsupported_progressive", "unsupported_422", "unsupported_cmyk"])
 def test_unsupported_variants_are_refused(name):
     with pytest.raises(jpeg.JpegUnsupported):
@@ -94,8 +106,9 @@ def ctx():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", CASES)
-def test_device_reconstruct_matches_golden(ctx, case):
-    got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()])
+@pytest.mark.parametrize("packed", [True, False])
+def test_device_reconstruct_matches_golden(ctx, case, packed):
+    got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()], packed=packed)
     assert np.array_equal(got[0], GOLD["bgr_" + case])
 
 
@@ -136,13 +149,14 @@ def test_detect_from_jpeg_equals_detect_from_pixels():
     ref = det.detect(torch.from_numpy(np.stack(pix)).pin_memory(), bgr=True)
     ref_d, ref_c = ref.dets.copy(), ref.counts.copy()
     info = jpeg.probe(blobs[0])
-    coef, quant = det.jpeg_staging(4, info.coef_count)
-    for i, b in enumerate(blobs):
-        jpeg.entropy_decode(b, coef[i], quant[i])
-    got = det.detect_wait(det.detect_submit_jpeg(coef, quant, info.width, info.height, info.ncomp, info.hs))
-    assert np.array_equal(got.counts, ref_c)
-    for i in range(4):
-        assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
+    tl = [engine.entropy_decode_file(b) for b in blobs]
+    for rep in range(3):  # both staging areas, and a reused one
+        desc, ent, base, quant = det.jpeg_staging(4, info.coef_count, sum(t.entries.size for t in tl) if rep else 0)
+        total = engine.pack_jpeg_tiles(tl, desc, ent, base, quant)
+        got = det.detect_wait(det.detect_submit_jpeg(desc, ent, base, total, quant, info.width, info.height, info.ncomp, info.hs))
+        assert np.array_equal(got.counts, ref_c)
+        for i in range(4):
+            assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
     det.close()
 
 

@@ -289,7 +289,7 @@ def run(opt, argv) -> int:
         t0 = time.perf_counter()
         if is_jpeg:
             desc, ent, base, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count, sum(g[0].entries.size for g in group))
-            total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant)
+            total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant, pool=pool)
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg(desc, ent, base, total, quant, w0, h0, ncomp, hs)
         else:

@@ -432,16 +432,29 @@ def entropy_decode_file(blob) -> PackedJpeg:
     return t
 
 
-def pack_jpeg_tiles(tiles_: Sequence[PackedJpeg], block_desc, entries, base, quant) -> int:
-    """Concatenate the tiles' entry lists into one staging area (see TileDetector.jpeg_staging); returns the total."""
-    pos = 0
-    for i, t in enumerate(tiles_):
+def pack_jpeg_tiles(tiles_: Sequence[PackedJpeg], block_desc, entries, base, quant, pool=None) -> int:
+    """Concatenate the tiles' entry lists into one staging area (see TileDetector.jpeg_staging); returns the total.
+    `pool` (a ThreadPoolExecutor) spreads the copies over the io threads (numpy copies release the GIL)."""
+    sizes = [t.entries.size for t in tiles_]
+    need = sum(sizes)
+    if need > entries.size:
+        raise _lib.AquaError(f"pack_jpeg_tiles: {need} entries do not fit the staging area of {entries.size} "
+                             f"(pass min_entries to TileDetector.jpeg_staging)")
+    starts = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64) if sizes else np.zeros(0, np.int64)
+
+    def one(i):
+        t = tiles_[i]
         block_desc[i] = t.block_desc
         quant[i] = t.quant
-        base[i] = pos
-        entries[pos:pos + t.entries.size] = t.entries
-        pos += t.entries.size
-    return pos
+        base[i] = starts[i]
+        entries[starts[i]:starts[i] + sizes[i]] = t.entries
+
+    if pool is None:
+        for i in range(len(tiles_)):
+            one(i)
+    else:
+        list(pool.map(one, range(len(tiles_))))
+    return need
 
 
 def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True, packed=True) -> np.ndarray:

@@ -151,7 +151,7 @@ def test_detect_from_jpeg_equals_detect_from_pixels():
     info = jpeg.probe(blobs[0])
     tl = [engine.entropy_decode_file(b) for b in blobs]
     for rep in range(3):  # both staging areas, and a reused one
-        desc, ent, base, quant = det.jpeg_staging(4, info.coef_count, sum(t.entries.size for t in tl) if rep else 0)
+        desc, ent, base, quant = det.jpeg_staging(4, info.coef_count, sum(t.entries.size for t in tl))
         total = engine.pack_jpeg_tiles(tl, desc, ent, base, quant)
         got = det.detect_wait(det.detect_submit_jpeg(desc, ent, base, total, quant, info.width, info.height, info.ncomp, info.hs))
         assert np.array_equal(got.counts, ref_c)

@@ -122,7 +122,7 @@ if a.e2e > 0:
     def via_jpeg():
         tiles_ = list(pool.map(engine.entropy_decode_file, blobs))
         d, e, b, q = det.jpeg_staging(N, info.coef_count, sum(t.entries.size for t in tiles_))
-        tot = engine.pack_jpeg_tiles(tiles_, d, e, b, q)
+        tot = engine.pack_jpeg_tiles(tiles_, d, e, b, q, pool=pool)
         return det.detect_submit_jpeg(d, e, b, tot, q, info.width, info.height, info.ncomp, info.hs)
 
     def via_cv2():

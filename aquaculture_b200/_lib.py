@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("AQUA_LIB_PATH") or os.path.join(os.path.dirname(os.pa
 
 AQ_OK = 0
 AQ_ACT_NONE, AQ_ACT_SILU, AQ_ACT_SILU_FAST = 0, 1, 2
+AQ_JPEG_TABLE_BYTES = 8640
 
 
 class AquaError(RuntimeError):
@@ -102,6 +103,12 @@ SIGNATURES = {
                                                 C.POINTER(C.c_size_t), C.c_void_p]),
     "aq_jpeg_reconstruct_packed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int,
                                              C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "aq_jpeg_scan_prepare": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(JpegInfo), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                       C.c_void_p, C.c_void_p]),
+    "aq_jpeg_decode_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,
+                                        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "aq_jpeg_debug_parallel_decode": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(JpegInfo), C.c_int, C.c_void_p,
+                                                C.c_size_t, C.POINTER(C.c_int)]),
     "aq_jpeg_reconstruct": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                       C.c_int, C.c_void_p, C.c_void_p]),
     "aq_memcpy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]),

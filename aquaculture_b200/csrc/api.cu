@@ -17,6 +17,7 @@
 #include "aux_kernels.cuh"
 #include "conv_igemm.cuh"
 #include "jpeg.cuh"
+#include "jpeg_huff.cuh"
 #include "nms.cuh"
 
 using namespace aq;
@@ -1597,6 +1598,97 @@ int aq_jpeg_reconstruct_packed(aq_ctx* c, const uint32_t* block_desc, const uint
   p.block_desc = d_desc; p.entries = d_ent; p.tile_entry_base = d_base; p.quant = d_quant;
   cudaError_t e = launch_jpeg_reconstruct(p, s);
   if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_reconstruct_packed: %s", cudaGetErrorString(e));
+  CU_CHECK(c, cudaEventRecord(c->ev_jpk_used[slot], s));
+  c->jpk_recorded[slot] = true;
+  return AQ_OK;
+}
+
+int aq_jpeg_decode_device(aq_ctx* c, const uint8_t* scans, const uint64_t* scan_off, const uint32_t* scan_bytes, size_t total_scan_bytes,
+                          const uint8_t* tables, const uint16_t* quant, int n, int width, int height, int ncomp, int hs, int bgr_out,
+                          uint8_t* out_dev, int* status_host, void* stream) {
+  if (!c || !scans || !scan_off || !scan_bytes || !tables || !quant || !out_dev || n <= 0 || width <= 0 || height <= 0 ||
+      (total_scan_bytes & 3))
+    return AQ_ERR_ARG;
+  if ((ncomp != 1 && ncomp != 3) || (hs != 1 && hs != 2) || (ncomp == 1 && hs != 1))
+    return fail(c, AQ_ERR_UNSUPPORTED, "jpeg: %d components with %dx%d luma sampling (grayscale, 4:4:4 and 4:2:0 only)", ncomp, hs, hs);
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  static const int sub_bits = [] { const char* e = getenv("AQUA_JPEG_SUB_BITS"); const int v = e ? atoi(e) : 1024; return v >= 32 && v % 32 == 0 ? v : 1024; }();
+  JpegParams p{};
+  p.n = n; p.width = width; p.height = height; p.ncomp = ncomp; p.hs = hs; p.bgr = bgr_out; p.out = out_dev;
+  jpeg_geometry(p);
+  HuffParams h{};
+  h.geo.hs = hs; h.geo.vs = hs; h.geo.ncomp = ncomp; h.geo.bpm = ncomp == 1 ? 1 : hs * hs + 2;
+  h.geo.mcus_x = p.chroma_bw; h.geo.mcus_y = (height + 8 * hs - 1) / (8 * hs);
+  h.geo.luma_bw = p.luma_bw; h.geo.luma_blocks = p.luma_blocks; h.geo.chroma_blocks = p.chroma_blocks;
+  h.geo.total_blocks = p.blocks_per_image;
+  h.sub_bits = sub_bits;
+  int nsub_max = 1;
+  for (int i = 0; i < n; ++i) {
+    if ((scan_off[i] & 3) || scan_off[i] + scan_bytes[i] + 8 > total_scan_bytes || scan_bytes[i] >= (1u << 28))
+      return fail(c, AQ_ERR_ARG, "jpeg_decode_device: tile %d: segment [%llu, +%u) not inside the %zu staged bytes (needs 8 bytes of padding)",
+                  i, (unsigned long long)scan_off[i], scan_bytes[i], total_scan_bytes);
+    const int ns = (int)(((size_t)scan_bytes[i] * 8 + sub_bits - 1) / sub_bits);
+    nsub_max = ns > nsub_max ? ns : nsub_max;
+  }
+  auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+  // scratch on the compute side: planes | dense coefficients | decoder states
+  const size_t planes_b = al((size_t)n * p.planes_per_image), coef_b = al((size_t)n * p.blocks_per_image * 64 * sizeof(int16_t));
+  const size_t state_b = al(jpeg_huff_state_bytes(n, nsub_max));
+  if (planes_b + coef_b + state_b > c->jpeg_bytes) {
+    if (c->jpeg_scratch) { CU_CHECK(c, cudaDeviceSynchronize()); cudaFree(c->jpeg_scratch); }
+    c->jpeg_scratch = nullptr;
+    c->jpeg_bytes = 0;
+    const size_t grow = planes_b + coef_b + state_b + state_b / 2;
+    CU_CHECK(c, cudaMalloc(&c->jpeg_scratch, grow));
+    c->jpeg_bytes = grow;
+  }
+  // staging on the copy side
+  const size_t off_b = (size_t)n * sizeof(uint64_t), len_b = (size_t)n * sizeof(uint32_t), tab_b = (size_t)n * AQ_JPEG_TABLE_BYTES;
+  const size_t quant_b = (size_t)n * 192 * sizeof(uint16_t);
+  const size_t need = al(total_scan_bytes) + al(off_b) + al(len_b) + al(tab_b) + al(quant_b);
+  const int slot = c->jpk_slot;
+  c->jpk_slot ^= 1;
+  if (!c->ev_jpk_h2d[slot]) {
+    CU_CHECK(c, cudaEventCreateWithFlags(&c->ev_jpk_h2d[slot], cudaEventDisableTiming));
+    CU_CHECK(c, cudaEventCreateWithFlags(&c->ev_jpk_used[slot], cudaEventDisableTiming));
+  }
+  if (need > c->jpk_bytes[slot]) {
+    if (c->jpk_stage[slot]) { CU_CHECK(c, cudaDeviceSynchronize()); cudaFree(c->jpk_stage[slot]); }
+    c->jpk_stage[slot] = nullptr;
+    c->jpk_bytes[slot] = 0;
+    const size_t grow = need + need / 4;
+    CU_CHECK(c, cudaMalloc(&c->jpk_stage[slot], grow));
+    c->jpk_bytes[slot] = grow;
+    c->jpk_recorded[slot] = false;
+  }
+  uint8_t* st = (uint8_t*)c->jpk_stage[slot];
+  uint8_t* d_scans = st;
+  unsigned long long* d_off = (unsigned long long*)(st + al(total_scan_bytes));
+  uint32_t* d_len = (uint32_t*)((uint8_t*)d_off + al(off_b));
+  uint8_t* d_tab = (uint8_t*)d_len + al(len_b);
+  uint16_t* d_quant = (uint16_t*)(d_tab + al(tab_b));
+  if (c->jpk_recorded[slot]) CU_CHECK(c, cudaStreamWaitEvent(c->copy_stream, c->ev_jpk_used[slot], 0));
+  CU_CHECK(c, cudaMemcpyAsync(d_scans, scans, total_scan_bytes, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_off, scan_off, off_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_len, scan_bytes, len_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_tab, tables, tab_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaMemcpyAsync(d_quant, quant, quant_b, cudaMemcpyHostToDevice, c->copy_stream));
+  CU_CHECK(c, cudaEventRecord(c->ev_jpk_h2d[slot], c->copy_stream));
+  CU_CHECK(c, cudaStreamWaitEvent(s, c->ev_jpk_h2d[slot], 0));
+  uint8_t* scratch = (uint8_t*)c->jpeg_scratch;
+  h.scans = d_scans; h.scan_off = d_off; h.scan_bytes = d_len; h.tables = d_tab;
+  h.coef = (int16_t*)(scratch + planes_b);
+  void* state = scratch + planes_b + coef_b;
+  cudaError_t e = launch_jpeg_huffman(h, state, n, nsub_max, s);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_decode_device (entropy decoding): %s", cudaGetErrorString(e));
+  p.planes = scratch;
+  p.coef = h.coef;
+  p.quant = d_quant;
+  e = launch_jpeg_reconstruct(p, s);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_decode_device (reconstruction): %s", cudaGetErrorString(e));
+  if (status_host)
+    CU_CHECK(c, cudaMemcpyAsync(status_host, jpeg_huff_status_ptr(state, n, nsub_max), (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaEventRecord(c->ev_jpk_used[slot], s));
   c->jpk_recorded[slot] = true;
   return AQ_OK;

@@ -7,7 +7,10 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <vector>
+
 #include "../../include/aqua_b200.h"
+#include "jpeg_huff_core.h"
 
 namespace {
 
@@ -440,4 +443,128 @@ extern "C" int aq_jpeg_entropy_decode_packed(const uint8_t* data, size_t len, ui
   });
   *n_entries = total;
   return rc2;
+}
+
+// ------------------------------------------------------------------ device-side entropy decoding: host preparation
+namespace {
+
+void export_table(const HuffTable& t, aqj::DevHuff& o) {
+  memset(&o, 0, sizeof o);
+  memcpy(o.look, t.look, sizeof o.look);
+  memcpy(o.maxcode, t.maxcode, sizeof o.maxcode);
+  memcpy(o.valoff, t.valoff, sizeof o.valoff);
+  memcpy(o.vals, t.vals, sizeof o.vals);
+}
+
+aqj::Geo make_geo(const aq_jpeg_info& info) {
+  aqj::Geo g;
+  g.hs = info.hs; g.vs = info.vs; g.ncomp = info.ncomp;
+  g.bpm = info.ncomp == 1 ? 1 : info.hs * info.vs + 2;
+  g.mcus_x = info.mcus_x; g.mcus_y = info.mcus_y;
+  g.luma_bw = info.mcus_x * info.hs;
+  g.luma_blocks = (long long)g.luma_bw * info.mcus_y * info.vs;
+  g.chroma_blocks = info.ncomp == 3 ? (long long)info.mcus_x * info.mcus_y : 0;
+  g.total_blocks = g.luma_blocks + 2 * g.chroma_blocks;
+  return g;
+}
+
+}  // namespace
+
+extern "C" int aq_jpeg_scan_prepare(const uint8_t* data, size_t len, aq_jpeg_info* info, uint8_t* scan_out, size_t scan_cap,
+                                    size_t* scan_bytes, uint8_t* tables_out, uint16_t* quant) {
+  if (!data || !info || !scan_out || !scan_bytes || !tables_out || !quant) return AQ_ERR_ARG;
+  static_assert(AQ_JPEG_TABLE_BYTES == aqj::kTablesPerTile * sizeof(aqj::DevHuff), "AQ_JPEG_TABLE_BYTES");
+  Frame f;
+  const int rc = open_file(data, len, f, *info, quant);
+  if (rc != AQ_OK) return rc;
+  if (f.restart_interval) return AQ_ERR_UNSUPPORTED;  // restart markers re-align the stream: use the host decoder for such files
+  aqj::DevHuff* tabs = reinterpret_cast<aqj::DevHuff*>(tables_out);
+  for (int c = 0; c < 3; ++c) {
+    const Component& k = f.comp[c < f.ncomp ? c : 0];
+    export_table(f.dc[k.td], tabs[2 * c]);
+    export_table(f.ac[k.ta], tabs[2 * c + 1]);
+  }
+  // entropy-coded segment with the byte stuffing removed (0xFF 0x00 -> 0xFF); any other marker ends it
+  size_t n = 0;
+  const uint8_t* p = data + f.scan_off;
+  const uint8_t* end = data + len;
+  while (p < end) {
+    const uint8_t* ff = (const uint8_t*)memchr(p, 0xFF, (size_t)(end - p));
+    const size_t run = (size_t)((ff ? ff : end) - p);
+    if (n + run + 1 + 8 > scan_cap) return AQ_ERR_NOMEM;
+    memcpy(scan_out + n, p, run);
+    n += run;
+    if (!ff || ff + 1 >= end) break;
+    if (ff[1] != 0x00) break;  // a marker (EOI normally)
+    scan_out[n++] = 0xFF;
+    p = ff + 2;
+  }
+  *scan_bytes = n;
+  const size_t padded = (n + 3) / 4 * 4 + 8;  // whole words + two zero words the 32-bit window may touch
+  if (padded > scan_cap) return AQ_ERR_NOMEM;
+  memset(scan_out + n, 0, padded - n);
+  return AQ_OK;
+}
+
+// CPU rehearsal of the device schedule (same core, subsequences visited one after another): for tests without a GPU.
+extern "C" int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_bytes, const uint8_t* tables, const aq_jpeg_info* info,
+                                             int sub_bits, int16_t* coef, size_t coef_cap, int* rounds_out) {
+  if (!scan || !tables || !info || !coef || sub_bits < 32 || (sub_bits & 31) || ((uintptr_t)scan & 3)) return AQ_ERR_ARG;
+  if (coef_cap < info->coef_count) return AQ_ERR_ARG;
+  const aqj::Geo g = make_geo(*info);
+  const aqj::DevHuff* tabs = reinterpret_cast<const aqj::DevHuff*>(tables);
+  const uint32_t* words = reinterpret_cast<const uint32_t*>(scan);
+  uint8_t slot_comp[8] = {0};
+  for (int s = 0; s < g.bpm; ++s) slot_comp[s] = g.ncomp == 1 ? 0 : (s < g.hs * g.vs ? 0 : (uint8_t)(s - g.hs * g.vs + 1));
+  const uint32_t total_bits = (uint32_t)(scan_bytes * 8);
+  const int nsub = (int)((total_bits + sub_bits - 1) / sub_bits);
+  if (nsub <= 0) return AQ_ERR_ARG;
+  std::vector<uint64_t> start(nsub), endst(nsub);
+  std::vector<int> nblk(nsub);
+  auto limit = [&](int i) { const uint64_t l = (uint64_t)(i + 1) * sub_bits; return (uint32_t)(l < total_bits ? l : total_bits); };
+  for (int i = 0; i < nsub; ++i) {  // step 1
+    aqj::State st{(uint32_t)((uint64_t)i * sub_bits), 0, 0};
+    start[i] = aqj::pack_state(st);
+    nblk[i] = aqj::decode_range(words, tabs, slot_comp, g.bpm, st, limit(i));
+    endst[i] = aqj::pack_state(st);
+  }
+  int rounds = 0;
+  for (bool changed = true; changed; ++rounds) {  // step 2 (Jacobi order, as the device runs it)
+    changed = false;
+    std::vector<uint64_t> prev_end(endst);
+    for (int i = 1; i < nsub; ++i) {
+      if (prev_end[i - 1] == start[i]) continue;
+      start[i] = prev_end[i - 1];
+      aqj::State st = aqj::unpack_state(start[i]);
+      nblk[i] = aqj::decode_range(words, tabs, slot_comp, g.bpm, st, limit(i));
+      endst[i] = aqj::pack_state(st);
+      changed = true;
+    }
+    if (rounds > nsub + 1) return AQ_ERR_IO;
+  }
+  if (rounds_out) *rounds_out = rounds;
+  memset(coef, 0, info->coef_count * sizeof(int16_t));
+  long long base = 0;
+  for (int i = 0; i < nsub; ++i) {  // steps 3 + 4
+    aqj::State st = aqj::unpack_state(start[i]);
+    long long blk = base;
+    const uint32_t lim = limit(i);
+    while (st.p < lim && blk < g.total_blocks) {
+      int16_t* dst = coef + aqj::block_address(g, blk) * 64;
+      if (aqj::decode_one(words, tabs, slot_comp, g.bpm, st, [&](int z, int v) { dst[kZigzagToNatural[z]] = (int16_t)v; })) ++blk;
+    }
+    base += nblk[i];
+  }
+  if (base < g.total_blocks) return AQ_ERR_IO;
+  for (int c = 0; c < g.ncomp; ++c) {  // step 5
+    int pred = 0;
+    const int per_mcu = c == 0 ? (g.ncomp == 1 ? 1 : g.hs * g.vs) : 1, first = c == 0 ? 0 : g.hs * g.vs + c - 1;
+    for (long long m = 0; m < (long long)g.mcus_x * g.mcus_y; ++m)
+      for (int k = 0; k < per_mcu; ++k) {
+        int16_t* dc = coef + aqj::block_address(g, m * g.bpm + first + k) * 64;
+        pred += *dc;
+        *dc = (int16_t)pred;
+      }
+  }
+  return AQ_OK;
 }

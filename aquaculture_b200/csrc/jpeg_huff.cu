@@ -1,0 +1,209 @@
+// Entropy decoding of baseline JPEG scans on the GPU: the schedule described in jpeg_huff_core.h.
+// Replaces the Huffman stage of the cv2.imread call inside upstream utils/dataloaders.py::LoadImages [UPSTREAM-RECALLED]
+// for the tiles gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74]; the host only walks the markers.
+// Latency / integer bound (a chain of dependent table lookups per symbol), not bandwidth bound: parallelism comes from
+// the subsequences (1024 bits each: ~1.4k per 1024^2 tile, ~90k per 64-tile batch).
+#include "jpeg_huff.cuh"
+
+namespace aq {
+namespace {
+
+using namespace aqj;
+
+constexpr int HT = 1024;  // threads per CTA = subsequences per CTA
+
+__constant__ uint8_t c_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                     41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                     30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+struct Shared {
+  DevHuff tabs[kTablesPerTile];
+  uint8_t slot_comp[8];
+};
+
+__device__ __forceinline__ void load_tables(Shared& sh, const HuffParams& p, int tile) {
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(p.tables + (size_t)tile * kTablesPerTile * sizeof(DevHuff));
+  uint32_t* dst = reinterpret_cast<uint32_t*>(sh.tabs);
+  for (int i = threadIdx.x; i < (int)(kTablesPerTile * sizeof(DevHuff) / 4); i += blockDim.x) dst[i] = src[i];
+  if (threadIdx.x < 8) {
+    const int s = threadIdx.x, nl = p.geo.hs * p.geo.vs;
+    sh.slot_comp[s] = p.geo.ncomp == 1 ? 0 : (s < nl ? 0 : (uint8_t)min(s - nl + 1, 2));
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t sub_limit(const HuffParams& p, uint32_t total_bits, int i) {
+  const unsigned long long l = (unsigned long long)(i + 1) * p.sub_bits;
+  return (uint32_t)(l < total_bits ? l : total_bits);
+}
+
+// Steps 1 + 2.  CTA (x, tile) owns subsequences [x * HT, (x + 1) * HT) of the tile.  first != 0: decode from the guessed
+// states, then relax inside the CTA until nothing changes; first == 0: relax again with the boundary state the previous
+// CTA left in global memory.  Launching it (CTAs per tile) times reaches the fixed point whatever the data: launch k
+// finds CTA k-1's states final.
+__global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int first) {
+  __shared__ Shared sh;
+  __shared__ unsigned long long s_end[HT];
+  const int tile = blockIdx.y, i = blockIdx.x * HT + threadIdx.x;
+  const uint32_t total_bits = p.scan_bytes[tile] * 8u;
+  const int nsub = (int)((total_bits + p.sub_bits - 1) / p.sub_bits);
+  if (blockIdx.x * HT >= nsub) return;
+  load_tables(sh, p, tile);
+  const uint32_t* words = reinterpret_cast<const uint32_t*>(p.scans + p.scan_off[tile]);
+  const size_t slot = (size_t)tile * p.nsub_max + i;
+  const bool live = i < nsub;
+  unsigned long long my_start = 0, my_end = 0;
+  int my_nblk = 0;
+  if (live) {
+    if (first) {
+      State st{(uint32_t)((unsigned long long)i * p.sub_bits), 0, 0};
+      my_start = pack_state(st);
+      my_nblk = decode_range(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
+      my_end = pack_state(st);
+    } else {
+      my_start = p.start[slot];
+      my_end = p.end[slot];
+      my_nblk = p.nblk[slot];
+    }
+  }
+  // the previous CTA's last state: only meaningful from the second launch on (launch k finds CTA k-1 final)
+  const unsigned long long boundary = (!first && threadIdx.x == 0 && i > 0 && live) ? p.end[slot - 1] : my_start;
+  s_end[threadIdx.x] = my_end;
+  __syncthreads();
+  for (;;) {
+    bool changed = false;
+    if (live && i > 0) {
+      const unsigned long long prev = threadIdx.x == 0 ? boundary : s_end[threadIdx.x - 1];
+      if (prev != my_start) {
+        my_start = prev;
+        State st = unpack_state(prev);
+        my_nblk = decode_range(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
+        my_end = pack_state(st);
+        changed = true;
+      }
+    }
+    __syncthreads();  // every s_end[tid - 1] has been read
+    if (changed) s_end[threadIdx.x] = my_end;
+    if (!__syncthreads_or(changed)) break;
+  }
+  if (live) {
+    p.start[slot] = my_start;
+    p.end[slot] = my_end;
+    p.nblk[slot] = my_nblk;
+  }
+}
+
+// Step 3 + verification: one CTA per tile.  base[i] = blocks completed before subsequence i; status[tile] = 0 when the
+// chain of states is consistent and covers the expected number of blocks.
+__global__ void __launch_bounds__(HT) jpeg_huff_scan_kernel(HuffParams p) {
+  __shared__ long long s_part[HT];
+  __shared__ int s_bad;
+  const int tile = blockIdx.x;
+  const uint32_t total_bits = p.scan_bytes[tile] * 8u;
+  const int nsub = (int)((total_bits + p.sub_bits - 1) / p.sub_bits);
+  const size_t off = (size_t)tile * p.nsub_max;
+  if (threadIdx.x == 0) s_bad = 0;
+  const int per = (nsub + HT - 1) / HT, lo = min(threadIdx.x * per, nsub), hi = min(lo + per, nsub);
+  long long sum = 0;
+  bool bad = false;
+  for (int i = lo; i < hi; ++i) {
+    sum += p.nblk[off + i];
+    if (i > 0 && p.start[off + i] != p.end[off + i - 1]) bad = true;
+  }
+  s_part[threadIdx.x] = sum;
+  __syncthreads();
+  if (bad) s_bad = 1;
+  for (int d = 1; d < HT; d <<= 1) {  // inclusive scan of the per-thread sums
+    const long long v = threadIdx.x >= d ? s_part[threadIdx.x - d] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  long long run = s_part[threadIdx.x] - sum;
+  for (int i = lo; i < hi; ++i) {
+    p.base[off + i] = run;
+    run += p.nblk[off + i];
+  }
+  if (threadIdx.x == HT - 1) p.status[tile] = (s_bad || s_part[HT - 1] < p.geo.total_blocks || nsub <= 0) ? -6 : 0;
+}
+
+// Step 4: every subsequence is decoded from its final start state, writing the coefficients it codes.
+__global__ void __launch_bounds__(HT) jpeg_huff_write_kernel(HuffParams p) {
+  __shared__ Shared sh;
+  const int tile = blockIdx.y, i = blockIdx.x * HT + threadIdx.x;
+  const uint32_t total_bits = p.scan_bytes[tile] * 8u;
+  const int nsub = (int)((total_bits + p.sub_bits - 1) / p.sub_bits);
+  if (blockIdx.x * HT >= nsub) return;
+  load_tables(sh, p, tile);
+  if (i >= nsub) return;
+  const uint32_t* words = reinterpret_cast<const uint32_t*>(p.scans + p.scan_off[tile]);
+  const size_t slot = (size_t)tile * p.nsub_max + i;
+  State st = unpack_state(p.start[slot]);
+  long long blk = p.base[slot];
+  const uint32_t lim = sub_limit(p, total_bits, i);
+  int16_t* tile_coef = p.coef + (size_t)tile * p.geo.total_blocks * 64;
+  while (st.p < lim && blk < p.geo.total_blocks) {
+    int16_t* dst = tile_coef + block_address(p.geo, blk) * 64;
+    if (decode_one(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
+  }
+}
+
+// Step 5: DC prediction undone by a scan over each component's blocks in decode order.  CTA (component, tile).
+__global__ void __launch_bounds__(HT) jpeg_huff_dc_kernel(HuffParams p) {
+  __shared__ int s_part[HT];
+  const int c = blockIdx.x, tile = blockIdx.y;
+  if (c >= p.geo.ncomp) return;
+  const Geo& g = p.geo;
+  const int per_mcu = c == 0 ? (g.ncomp == 1 ? 1 : g.hs * g.vs) : 1, first = c == 0 ? 0 : g.hs * g.vs + c - 1;
+  const long long n = (long long)g.mcus_x * g.mcus_y * per_mcu;
+  const long long per = (n + HT - 1) / HT, lo = min((long long)threadIdx.x * per, n), hi = min(lo + per, n);
+  int16_t* tile_coef = p.coef + (size_t)tile * g.total_blocks * 64;
+  auto addr = [&](long long j) { return tile_coef + block_address(g, (j / per_mcu) * g.bpm + first + (int)(j % per_mcu)) * 64; };
+  int sum = 0;
+  for (long long j = lo; j < hi; ++j) sum += *addr(j);
+  s_part[threadIdx.x] = sum;
+  __syncthreads();
+  for (int d = 1; d < HT; d <<= 1) {
+    const int v = threadIdx.x >= d ? s_part[threadIdx.x - d] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = s_part[threadIdx.x] - sum;
+  for (long long j = lo; j < hi; ++j) {
+    int16_t* a = addr(j);
+    run += *a;
+    *a = (int16_t)run;
+  }
+}
+
+}  // namespace
+
+size_t jpeg_huff_state_bytes(int n, int nsub_max) { return (size_t)n * nsub_max * (8 + 8 + 4 + 8) + (size_t)n * 4 + 256; }
+
+cudaError_t launch_jpeg_huffman(HuffParams p, void* state_scratch, int n, int nsub_max, cudaStream_t stream) {
+  if (n <= 0 || n > 65535 || nsub_max <= 0) return cudaErrorInvalidValue;
+  uint8_t* s = (uint8_t*)state_scratch;
+  const size_t cells = (size_t)n * nsub_max;
+  p.start = (unsigned long long*)s;
+  p.end = p.start + cells;
+  p.base = (long long*)(p.end + cells);
+  p.nblk = (int*)(p.base + cells);
+  p.status = p.nblk + cells;
+  p.nsub_max = nsub_max;
+  const int ctas = (nsub_max + HT - 1) / HT;
+  cudaError_t e = cudaMemsetAsync(p.coef, 0, (size_t)n * p.geo.total_blocks * 64 * sizeof(int16_t), stream);
+  if (e != cudaSuccess) return e;
+  for (int k = 0; k < ctas; ++k) jpeg_huff_sync_kernel<<<dim3(ctas, n), HT, 0, stream>>>(p, k == 0);
+  jpeg_huff_scan_kernel<<<n, HT, 0, stream>>>(p);
+  jpeg_huff_write_kernel<<<dim3(ctas, n), HT, 0, stream>>>(p);
+  jpeg_huff_dc_kernel<<<dim3(3, n), HT, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+const int* jpeg_huff_status_ptr(void* state_scratch, int n, int nsub_max) {
+  const size_t cells = (size_t)n * nsub_max;
+  return (const int*)((uint8_t*)state_scratch + cells * (8 + 8 + 8)) + cells;
+}
+
+}  // namespace aq

@@ -348,6 +348,43 @@ class TileDetector:
         dev = self.decode_jpeg_batch(block_desc, entries, base, total_entries, quant, width, height, ncomp, hs, bgr=True, stream=stream)
         return self.detect_submit(dev, bgr=True, src_is_device=True, stream=stream)
 
+    def jpeg_scan_staging(self, n, min_bytes=0):
+        """One of two alternating pinned staging areas for the all-device decoder: numpy views (scans uint8 (capacity >=
+        min_bytes), off uint64 (n), length uint32 (n), tables uint8 (n, AQ_JPEG_TABLE_BYTES), quant uint16 (n, 192),
+        status int32 (n)).  Fill with `pack_jpeg_scans`, submit with `detect_submit_jpeg_scans`."""
+        key = "jpegscan"
+        if self._pin.get(key) is not None and self._pin[key][0][0].numel() < min_bytes:
+            self.ctx.sync()
+            self._pin[key] = None
+        if self._pin.get(key) is None:
+            cap = max(min_bytes + min_bytes // 2, self.batch * (256 << 10))
+            self._pin[key] = [(torch.empty(cap, dtype=torch.uint8).pin_memory(), torch.empty(self.batch, dtype=torch.int64).pin_memory(),
+                               torch.empty(self.batch, dtype=torch.int32).pin_memory(),
+                               torch.empty(self.batch, _lib.AQ_JPEG_TABLE_BYTES, dtype=torch.uint8).pin_memory(),
+                               torch.empty(self.batch, 192, dtype=torch.uint16).pin_memory(),
+                               torch.zeros(self.batch, dtype=torch.int32).pin_memory()) for _ in range(2)]
+            self._pin_i[key] = 0
+        i = self._pin_i[key]
+        self._pin_i[key] = i ^ 1
+        sc, off, ln, tab, q, stt = self._pin[key][i]
+        return (sc.numpy(), off[:n].numpy().view(np.uint64), ln[:n].numpy().view(np.uint32), tab[:n].numpy(), q[:n].numpy(),
+                stt[:n].numpy())
+
+    def detect_submit_jpeg_scans(self, scans, off, length, total_bytes, tables, quant, status, width, height, ncomp, hs, stream=None):
+        """JPEG tiles -> detections with the whole decoder on the device (aq_jpeg_decode_device: parallel Huffman decoding,
+        IDCT, upsampling, colour), then the usual batch.  `status` (pinned int32, n) is filled by the time the ticket has
+        been waited for: non-zero = that tile's scan was corrupt."""
+        n = off.shape[0]
+        key = (height, width)
+        if self._jpeg_out.get(key) is None:
+            self._jpeg_out[key] = torch.empty(self.batch, height, width, 3, dtype=torch.uint8, device=f"cuda:{self.ctx.device}")
+            torch.cuda.synchronize(self.ctx.device)
+        out = self._jpeg_out[key][:n]
+        self.ctx.call("aq_jpeg_decode_device", C.c_void_p(scans.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(length.ctypes.data),
+                      int(total_bytes), C.c_void_p(tables.ctypes.data), C.c_void_p(quant.ctypes.data), n, width, height, ncomp, hs, 1,
+                      C.c_void_p(out.data_ptr()), C.c_void_p(status.ctypes.data), stream)
+        return self.detect_submit(out, bgr=True, src_is_device=True, stream=stream)
+
     def pinned_input(self, n, h, w) -> torch.Tensor:
         """One of two alternating pinned uint8 (n, h, w, 3) host buffers for `detect_submit` (a buffer is reused
         every second call, i.e. after its batch has been waited for in a two-deep pipeline)."""
@@ -457,7 +494,45 @@ def pack_jpeg_tiles(tiles_: Sequence[PackedJpeg], block_desc, entries, base, qua
     return need
 
 
-def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True, packed=True) -> np.ndarray:
+class ScanJpeg:
+    """One tile prepared for the all-device decoder (host): geometry, unstuffed scan, tables."""
+    __slots__ = ("info", "scan", "scan_bytes", "tables", "quant", "key")
+
+
+def prepare_jpeg_file(blob) -> ScanJpeg:
+    """Host side of the all-device decoder for one file: marker walk + byte unstuffing only (io thread, GIL released)."""
+    from . import jpeg
+    t = ScanJpeg()
+    t.info, t.scan, t.scan_bytes, t.tables, t.quant = jpeg.scan_prepare(blob)
+    t.key = ("jpegscan", t.info.height, t.info.width, t.info.ncomp, t.info.hs)
+    return t
+
+
+def pack_jpeg_scans(tiles_: Sequence[ScanJpeg], scans, off, length, tables, quant, pool=None) -> int:
+    """Lay the tiles' scans one after another in a staging area (TileDetector.jpeg_scan_staging); returns the extent."""
+    sizes = [t.scan.size for t in tiles_]  # multiples of 4, padding included
+    need = sum(sizes)
+    if need > scans.size:
+        raise _lib.AquaError(f"pack_jpeg_scans: {need} bytes do not fit the staging area of {scans.size} (pass min_bytes)")
+    starts = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.int64) if sizes else np.zeros(0, np.int64)
+
+    def one(i):
+        t = tiles_[i]
+        scans[starts[i]:starts[i] + sizes[i]] = t.scan
+        off[i] = starts[i]
+        length[i] = t.scan_bytes
+        tables[i] = t.tables
+        quant[i] = t.quant
+
+    if pool is None:
+        for i in range(len(tiles_)):
+            one(i)
+    else:
+        list(pool.map(one, range(len(tiles_))))
+    return need
+
+
+def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True, packed=True, mode=None) -> np.ndarray:
     """Hybrid decode of equally-shaped JPEG files without a planned model (tests, tools): host Huffman decoding +
     aq_jpeg_reconstruct[_packed] -> uint8 (n, h, w, 3) numpy array (BGR = what cv2.imread returns).  The CLI uses the
     pipelined `TileDetector.detect_submit_jpeg` instead."""
@@ -469,7 +544,20 @@ def decode_jpeg_files(ctx: Context, blobs: Sequence[bytes], bgr=True, packed=Tru
     n = len(blobs)
     out = torch.empty(n, i0.height, i0.width, 3, dtype=torch.uint8, device=f"cuda:{ctx.device}")
     torch.cuda.synchronize(ctx.device)
-    if packed:
+    if mode == "device":  # entropy decoding on the GPU as well
+        tl = [prepare_jpeg_file(b) for b in blobs]
+        scans = np.empty(sum(t.scan.size for t in tl), np.uint8)
+        off, length = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        tables, quant = np.empty((n, _lib.AQ_JPEG_TABLE_BYTES), np.uint8), np.empty((n, 192), np.uint16)
+        status = np.full(n, -99, np.int32)
+        total = pack_jpeg_scans(tl, scans, off, length, tables, quant)
+        ctx.call("aq_jpeg_decode_device", C.c_void_p(scans.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(length.ctypes.data), total,
+                 C.c_void_p(tables.ctypes.data), C.c_void_p(quant.ctypes.data), n, i0.width, i0.height, i0.ncomp, i0.hs, int(bgr),
+                 C.c_void_p(out.data_ptr()), C.c_void_p(status.ctypes.data), None)
+        ctx.sync()
+        if status.any():
+            raise _lib.AquaError(f"aq_jpeg_decode_device: tile status {status.tolist()}")
+    elif packed:
         tl = [entropy_decode_file(b) for b in blobs]
         desc = np.empty((n, i0.coef_count // 64), np.uint32)
         ent = np.empty(max(1, sum(t.entries.size for t in tl)), np.uint32)

@@ -73,3 +73,36 @@ def unpack(block_desc: np.ndarray, entries: np.ndarray) -> np.ndarray:
     e = entries[idx]
     coef[blk * 64 + ((e >> 16) & 63)] = (e & 0xFFFF).astype(np.uint16).view(np.int16)
     return coef
+
+
+def scan_prepare(data: bytes | np.ndarray):
+    """Host side of the all-device decoder (aq_jpeg_scan_prepare): marker walk only.  Returns (info, scan, scan_bytes,
+    tables, quant): `scan` = the entropy-coded segment without byte stuffing, zero padded to whole words + 8 bytes (uint8,
+    4-byte aligned), `scan_bytes` its unpadded length, `tables` the six Huffman tables in device form, `quant` 192 uint16."""
+    lib = _lib.load()
+    buf = np.frombuffer(data, np.uint8) if not isinstance(data, np.ndarray) else data
+    info = _lib.JpegInfo()
+    scan = np.empty((buf.size + 16 + 3) // 4, np.uint32).view(np.uint8)
+    tables = np.empty(_lib.AQ_JPEG_TABLE_BYTES // 4, np.uint32).view(np.uint8)
+    quant = np.empty(192, np.uint16)
+    n = C.c_size_t(0)
+    rc = lib.aq_jpeg_scan_prepare(buf.ctypes.data, buf.size, C.byref(info), scan.ctypes.data, scan.size, C.byref(n), tables.ctypes.data,
+                                  quant.ctypes.data)
+    if rc == AQ_ERR_UNSUPPORTED:
+        raise JpegUnsupported("JPEG variant without an all-device path (progressive / arithmetic / CMYK / 4:2:2 / restart intervals)")
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_scan_prepare failed ({rc}): not a decodable JPEG file")
+    nb = int(n.value)
+    return info, scan[:(nb + 3) // 4 * 4 + 8], nb, tables, quant
+
+
+def debug_parallel_decode(info, scan: np.ndarray, scan_bytes: int, tables: np.ndarray, sub_bits: int = 1024):
+    """CPU rehearsal of the device's parallel Huffman schedule (tests): returns (dense int16 coefficients, rounds)."""
+    lib = _lib.load()
+    coef = np.empty(info.coef_count, np.int16)
+    rounds = C.c_int(0)
+    rc = lib.aq_jpeg_debug_parallel_decode(scan.ctypes.data, scan_bytes, tables.ctypes.data, C.byref(info), sub_bits, coef.ctypes.data,
+                                           coef.size, C.byref(rounds))
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_debug_parallel_decode failed ({rc})")
+    return coef, rounds.value

@@ -272,6 +272,33 @@ int aq_jpeg_reconstruct(aq_ctx* ctx, const int16_t* coef, const uint16_t* quant,
 int aq_jpeg_reconstruct_packed(aq_ctx* ctx, const uint32_t* block_desc, const uint32_t* entries, const uint64_t* tile_entry_base,
                                size_t total_entries, const uint16_t* quant, int n, int width, int height, int ncomp, int hs,
                                int bgr_out, uint8_t* out_dev, void* stream);
+/*
+ * Entropy decoding ON THE DEVICE (self-synchronising parallel Huffman decoding; csrc/jpeg_huff_core.h): the host only walks
+ * the markers.  aq_jpeg_scan_prepare (host only): geometry, the entropy-coded segment with its byte stuffing removed
+ * (scan_out: 4-byte aligned, scan_cap >= file length + 16; *scan_bytes = its length, zero padded to whole words + 8),
+ * the tile's six Huffman tables in device form (tables_out: AQ_JPEG_TABLE_BYTES, 4-byte aligned) and the quantisation
+ * tables (quant: 192 uint16).  Files with restart intervals return AQ_ERR_UNSUPPORTED here (use the host decoder).
+ */
+#define AQ_JPEG_TABLE_BYTES 8640
+int aq_jpeg_scan_prepare(const uint8_t* data, size_t len, aq_jpeg_info* info, uint8_t* scan_out, size_t scan_cap,
+                         size_t* scan_bytes, uint8_t* tables_out, uint16_t* quant);
+/*
+ * n tiles of identical geometry: scans = their prepared segments one after another, tile i at byte scan_off[i] (a multiple
+ * of 4) with scan_bytes[i] bytes, total_scan_bytes = extent of `scans` (padding included); tables = n x
+ * AQ_JPEG_TABLE_BYTES; quant = n x 192; all HOST pointers (pinned for overlap; copied on the library's copy stream into
+ * one of two alternating staging areas).  Kernels on `stream`: parallel Huffman decoding -> dense coefficients ->
+ * aq_jpeg_reconstruct's kernels -> out_dev as there.  status_host (n int32, pinned; may be NULL) receives, asynchronously
+ * on `stream`, 0 per tile or AQ_ERR_IO when a tile's scan did not decode to the expected number of blocks (read it after
+ * the batch has been waited for).  Does not synchronise.
+ */
+int aq_jpeg_decode_device(aq_ctx* ctx, const uint8_t* scans, const uint64_t* scan_off, const uint32_t* scan_bytes,
+                          size_t total_scan_bytes, const uint8_t* tables, const uint16_t* quant, int n, int width, int height,
+                          int ncomp, int hs, int bgr_out, uint8_t* out_dev, int* status_host, void* stream);
+/* CPU rehearsal of the device schedule with the same decoding core (tests without a GPU; not a product path): decodes one
+ * prepared scan with subsequences of sub_bits bits (multiple of 32) into dense coefficients laid out as
+ * aq_jpeg_entropy_decode writes them; *rounds_out = relaxation rounds needed. */
+int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_bytes, const uint8_t* tables, const aq_jpeg_info* info,
+                                  int sub_bits, int16_t* coef, size_t coef_cap, int* rounds_out);
 
 /* ------------------------------------------------------------------ misc */
 /*

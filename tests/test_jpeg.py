@@ -71,6 +71,31 @@ def test_packed_form_equals_dense(case):
     assert np.array_equal(jpeg.unpack(desc, ent), coef) and np.array_equal(q2, quant)
 
 
+@pytest.mark.parametrize("sub_bits", [32, 256, 1024])
+@pytest.mark.parametrize("case", [c for c in CASES if "rst" not in c])
+def test_parallel_huffman_schedule_equals_sequential(case, sub_bits):
+    """The device's decoding schedule (guess, relax, scan, write, DC scan) rehearsed on the CPU with the same core."""
+    blob = GOLD["jpg_" + case].tobytes()
+    info, coef, quant = host_decode(blob)
+    info2, scan, nbytes, tables, q2 = jpeg.scan_prepare(blob)
+    got, rounds = jpeg.debug_parallel_decode(info2, scan, nbytes, tables, sub_bits)
+    assert np.array_equal(got, coef) and np.array_equal(q2, quant) and rounds >= 1
+
+
+def test_parallel_huffman_on_a_tile():
+    ok, enc = cv2.imencode(".jpg", tile_scene(1024, 1024, seed=3), [cv2.IMWRITE_JPEG_QUALITY, 75])
+    info, coef, quant = host_decode(enc.tobytes())
+    info2, scan, nbytes, tables, q2 = jpeg.scan_prepare(enc.tobytes())
+    got, rounds = jpeg.debug_parallel_decode(info2, scan, nbytes, tables, 1024)
+    assert np.array_equal(got, coef) and rounds < 64
+
+
+def test_restart_interval_files_are_left_to_the_host_decoder():
+    case = next(c for c in CASES if "rst" in c and c.startswith("96x128"))
+    with pytest.raises(jpeg.JpegUnsupported):
+        jpeg.scan_prepare(GOLD["jpg_" + case].tobytes())
+
+
 @pytest.mark.parametrize("name", ["unsupported_progressive", "unsupported_422", "unsupported_cmyk"])
 def test_unsupported_variants_are_refused(name):
     with pytest.raises(jpeg.JpegUnsupported):
@@ -110,6 +135,36 @@ def ctx():
 def test_device_reconstruct_matches_golden(ctx, case, packed):
     got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()], packed=packed)
     assert np.array_equal(got[0], GOLD["bgr_" + case])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [c for c in CASES if "rst" not in c])
+def test_device_huffman_matches_golden(ctx, case):
+    got = engine.decode_jpeg_files(ctx, [GOLD["jpg_" + case].tobytes()], mode="device")
+    assert np.array_equal(got[0], GOLD["bgr_" + case])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hw,n,q0", [((1024, 1024), 6, 60), ((640, 640), 8, 70), ((200, 328), 3, 90), ((512, 512), 2, 100)])
+def test_device_huffman_batch_matches_cv2(ctx, hw, n, q0):
+    rng = np.random.default_rng(hw[0])
+    blobs = []
+    for i in range(n):
+        img = tile_scene(*hw, seed=200 + i) if q0 < 100 else rng.integers(0, 256, (*hw, 3), dtype=np.uint8)  # q100 noise: slowest to fall into step
+        ok, enc = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, min(100, q0 + 5 * i)])
+        blobs.append(enc.tobytes())
+    got = engine.decode_jpeg_files(ctx, blobs, mode="device")
+    for i, b in enumerate(blobs):
+        assert np.array_equal(got[i], cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR)), i
+
+
+@pytest.mark.gpu
+def test_device_huffman_reports_corrupt_scan(ctx):
+    ok, enc = cv2.imencode(".jpg", tile_scene(256, 256, seed=1), [cv2.IMWRITE_JPEG_QUALITY, 75])
+    blob = bytearray(enc.tobytes())
+    del blob[len(blob) // 2:len(blob) - 2]   # half of the scan is missing
+    with pytest.raises(_lib.AquaError, match="status"):
+        engine.decode_jpeg_files(ctx, [bytes(blob)], mode="device")
 
 
 @pytest.mark.gpu
@@ -155,6 +210,14 @@ def test_detect_from_jpeg_equals_detect_from_pixels():
         total = engine.pack_jpeg_tiles(tl, desc, ent, base, quant)
         got = det.detect_wait(det.detect_submit_jpeg(desc, ent, base, total, quant, info.width, info.height, info.ncomp, info.hs))
         assert np.array_equal(got.counts, ref_c)
+        for i in range(4):
+            assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
+    sl = [engine.prepare_jpeg_file(b) for b in blobs]
+    for rep in range(3):  # all-device decoder
+        sc, off, ln, tab, q, stt = det.jpeg_scan_staging(4, sum(t.scan.size for t in sl))
+        total = engine.pack_jpeg_scans(sl, sc, off, ln, tab, q)
+        got = det.detect_wait(det.detect_submit_jpeg_scans(sc, off, ln, total, tab, q, stt, info.width, info.height, info.ncomp, info.hs))
+        assert not stt.any() and np.array_equal(got.counts, ref_c)
         for i in range(4):
             assert np.array_equal(got.dets[i, :ref_c[i]], ref_d[i, :ref_c[i]])
     det.close()

@@ -67,11 +67,12 @@ def parse_opt(argv=None):
                         "(replaces src/load_data/tile_tifs.py; labels are named <stem>_<x>_<y>.txt like its tiles)")
     p.add_argument("--skip-blank", action="store_true",
                    help="with --raster-tile: skip windows the reference's is_blank() calls blank (src/utils.py:325-350)")
-    p.add_argument("--jpeg-decode", choices=("device", "host"), default="device",
-                   help="device: baseline .jpg/.jpeg tiles are Huffman-decoded by the library's C parser on the io threads and "
-                        "reconstructed (IDCT, chroma upsampling, colour) on the GPU, bit-identical to cv2.imread; variants the "
-                        "parser refuses (progressive, 4:2:2, CMYK) and other formats are read with cv2.imread as upstream "
-                        "does.  host: cv2.imread for everything")
+    p.add_argument("--jpeg-decode", choices=("device", "hybrid", "host"), default="device",
+                   help="device: baseline .jpg/.jpeg tiles are decoded entirely on the GPU (parallel Huffman decoding, IDCT, chroma "
+                        "upsampling, colour), bit-identical to cv2.imread; the host only walks the markers.  hybrid: Huffman decoding "
+                        "by the library's C parser on the io threads, the rest on the GPU (also used by `device` for files with "
+                        "restart intervals).  Variants neither covers (progressive, 4:2:2, CMYK) and other formats are read with "
+                        "cv2.imread as upstream does.  host: cv2.imread for everything")
     p.add_argument("--verbose", action="store_true", help="per-image log lines as upstream prints them")
     p.add_argument("--io-threads", type=int, default=8)
     opt = p.parse_args(argv)
@@ -216,7 +217,7 @@ def run(opt, argv) -> int:
     import cv2
     from . import jpeg
     cv2.setNumThreads(1)
-    device_jpeg = opt.jpeg_decode == "device" and opt.raster_tile <= 0
+    device_jpeg = opt.jpeg_decode in ("device", "hybrid") and opt.raster_tile <= 0
     n_host_decoded = [0]
 
     def load(item):
@@ -227,6 +228,11 @@ def run(opt, argv) -> int:
             with open(v, "rb") as fh:
                 blob = np.frombuffer(fh.read(), np.uint8)
             try:
+                if opt.jpeg_decode == "device":
+                    try:
+                        return engine.prepare_jpeg_file(blob)  # markers + unstuffing only: the GPU decodes the scan
+                    except jpeg.JpegUnsupported:
+                        pass  # restart intervals: Huffman on the host; anything else fails again below
                 return engine.entropy_decode_file(blob)  # host half: markers + Huffman (C, GIL released)
             except jpeg.JpegUnsupported:
                 n_host_decoded[0] += 1  # e.g. progressive: decoded on the host like upstream does, and reported below
@@ -256,6 +262,7 @@ def run(opt, argv) -> int:
     pos = 0
     pending = {}  # (h0, w0) -> list of (image, stem)
 
+    scan_status = {}  # result slot -> (pinned per-tile decoder status, stems) of an all-device JPEG batch in flight
     deferred = []  # the batch in flight: (detector, ticket, group, shape0, net_hw)
 
     def finish():
@@ -265,6 +272,9 @@ def run(opt, argv) -> int:
         det, ticket, group, shape0, net_hw = deferred.pop()
         t1 = time.perf_counter()
         res = det.detect_wait(ticket)
+        st = scan_status.pop(ticket[0], None)
+        if st is not None and st[0].any():
+            raise SystemExit("detect.py (B200 path): corrupt JPEG scan in " + ", ".join(s for s, v in zip(st[1], st[0]) if v))
         if opt.save_txt:
             paths = [str(label_dir / (g[1] + ".txt")) for g in group]
             n_files += engine.write_labels(res, net_hw, [shape0] * len(group), paths, save_conf=opt.save_conf,
@@ -279,8 +289,8 @@ def run(opt, argv) -> int:
     def flush(shape0, group):
         # two-deep pipeline: this batch is submitted (H2D on the copy stream + kernels) before the previous one is
         # waited for, so image decoding / label writing on the host overlap the GPU
-        is_jpeg = shape0[0] == "jpeg"
-        if is_jpeg:
+        is_jpeg, is_scan = shape0[0] == "jpeg", shape0[0] == "jpegscan"
+        if is_jpeg or is_scan:
             _, h0, w0, ncomp, hs = shape0
             shape0 = (h0, w0)
         h0, w0 = shape0
@@ -292,6 +302,13 @@ def run(opt, argv) -> int:
             total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant, pool=pool)
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg(desc, ent, base, total, quant, w0, h0, ncomp, hs)
+        elif is_scan:
+            sl = [g[0] for g in group]
+            sc, off, ln, tab, quant, status = det.jpeg_scan_staging(len(group), sum(t.scan.size for t in sl))
+            total = engine.pack_jpeg_scans(sl, sc, off, ln, tab, quant, pool=pool)
+            dt[0] += time.perf_counter() - t0
+            ticket = det.detect_submit_jpeg_scans(sc, off, ln, total, tab, quant, status, w0, h0, ncomp, hs)
+            scan_status[ticket[0]] = (status, [g[1] for g in group])
         else:
             batch = det.pinned_input(len(group), h0, w0)
             np.stack([g[0] for g in group], out=batch.numpy())
@@ -352,7 +369,7 @@ def run(opt, argv) -> int:
         imgs = list(pool.map(load, chunk))
         dt[0] += time.perf_counter() - t0
         for im, stem in zip(imgs, stems[pos:pos + B]):
-            key = im.key if isinstance(im, engine.PackedJpeg) else im.shape[:2]
+            key = im.key if isinstance(im, (engine.PackedJpeg, engine.ScanJpeg)) else im.shape[:2]
             pending.setdefault(key, []).append((im, stem))
             if len(pending[key]) == B:
                 flush(key, pending.pop(key))

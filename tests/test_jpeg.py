@@ -236,7 +236,8 @@ def test_cli_device_jpeg_equals_host_decode(tmp_path, monkeypatch, capsys):
     src.mkdir()
     parts = T.synthetic_tiles(range(7), 1024, 1024, seed=9)
     for i in range(5):
-        cv2.imwrite(str(src / f"ORTHO2020_{i}_0_0.jpeg"), parts[i], [cv2.IMWRITE_JPEG_QUALITY, 75])
+        extra = [cv2.IMWRITE_JPEG_RST_INTERVAL, 16] if i == 4 else []   # one file with restart markers
+        cv2.imwrite(str(src / f"ORTHO2020_{i}_0_0.jpeg"), parts[i], [cv2.IMWRITE_JPEG_QUALITY, 75] + extra)
     Image.fromarray(parts[5]).save(str(src / "ORTHO2020_5_0_0.jpeg"), "JPEG", progressive=True)
     cv2.imwrite(str(src / "ORTHO2020_6_0_0.png"), parts[6])
     common = ["--weights", "synthetic", "--source", str(src), "--nosave", "--save-txt", "--save-conf", "--batch-size", "4",
@@ -244,6 +245,8 @@ def test_cli_device_jpeg_equals_host_decode(tmp_path, monkeypatch, capsys):
     assert cli.main(common + ["--name", "dev"]) == 0
     assert "1 JPEG file(s) of a variant without a device path" in capsys.readouterr().out
     assert cli.main(common + ["--name", "host", "--jpeg-decode", "host"]) == 0
+    assert cli.main(common + ["--name", "hyb", "--jpeg-decode", "hybrid"]) == 0
+    lhy = {p.name: p.read_text() for p in (tmp_path / "runs" / "hyb" / "labels").glob("*.txt")}
     ld = {p.name: p.read_text() for p in (tmp_path / "runs" / "dev" / "labels").glob("*.txt")}
     lh = {p.name: p.read_text() for p in (tmp_path / "runs" / "host" / "labels").glob("*.txt")}
-    assert len(lh) >= 5 and ld == lh
+    assert len(lh) >= 5 and ld == lh and lhy == lh

@@ -3,6 +3,8 @@
     thread and `--threads` threads (tiles/s);
   * device: aq_jpeg_reconstruct over a 64-tile batch with dense coefficients resident in HBM, and
     aq_jpeg_reconstruct_packed from pinned host memory (copy stream, two batches in flight), CUDA events;
+  * device, all of it: aq_jpeg_decode_device (parallel Huffman decoding + reconstruction) from the prepared scans in pinned
+    host memory;
   * whole path (--e2e): .jpeg bytes -> detections through TileDetector, host Huffman on the io threads overlapped with the
     GPU, against the same detector fed cv2.imdecode pixels.
 Prints one JSON line."""
@@ -63,7 +65,9 @@ res["host_tiles_per_s"] = {
     "cv2_imdecode_1t": t_host(lambda i: cv2.imdecode(blobs[i], cv2.IMREAD_COLOR), 1),
     "huffman_packed_1t": t_host(lambda i: engine.entropy_decode_file(blobs[i]), 1),
     "cv2_imdecode_mt": t_host(lambda i: cv2.imdecode(blobs[i], cv2.IMREAD_COLOR), a.threads),
-    "huffman_packed_mt": t_host(lambda i: engine.entropy_decode_file(blobs[i]), a.threads)}
+    "huffman_packed_mt": t_host(lambda i: engine.entropy_decode_file(blobs[i]), a.threads),
+    "scan_prepare_1t": t_host(lambda i: engine.prepare_jpeg_file(blobs[i]), 1),
+    "scan_prepare_mt": t_host(lambda i: engine.prepare_jpeg_file(blobs[i]), a.threads)}
 
 ctx = engine.Context(0)
 tl = [engine.entropy_decode_file(b) for b in blobs]
@@ -98,9 +102,31 @@ def run_packed():
              C.c_void_p(q.data_ptr()), N, info.width, info.height, info.ncomp, info.hs, 1, C.c_void_p(out.data_ptr()), None)
 
 
+sl = [engine.prepare_jpeg_file(b) for b in blobs]
+scan_total = sum(t.scan.size for t in sl)
+spin = []
+for _ in range(2):
+    sc = torch.empty(scan_total, dtype=torch.uint8).pin_memory()
+    off, ln = torch.empty(N, dtype=torch.int64).pin_memory(), torch.empty(N, dtype=torch.int32).pin_memory()
+    tab, qq = torch.empty(N, 8640, dtype=torch.uint8).pin_memory(), torch.empty(N, 192, dtype=torch.int16).pin_memory()
+    stt = torch.zeros(N, dtype=torch.int32).pin_memory()
+    engine.pack_jpeg_scans(sl, sc.numpy(), off.numpy().view(np.uint64), ln.numpy().view(np.uint32), tab.numpy(), qq.numpy().view(np.uint16))
+    spin.append((sc, off, ln, tab, qq, stt))
+sslot = [0]
+
+
+def run_all_device():
+    sc, off, ln, tab, qq, stt = spin[sslot[0]]
+    sslot[0] ^= 1
+    ctx.call("aq_jpeg_decode_device", C.c_void_p(sc.data_ptr()), C.c_void_p(off.data_ptr()), C.c_void_p(ln.data_ptr()), scan_total,
+             C.c_void_p(tab.data_ptr()), C.c_void_p(qq.data_ptr()), N, info.width, info.height, info.ncomp, info.hs, 1,
+             C.c_void_p(out.data_ptr()), C.c_void_p(stt.data_ptr()), None)
+
+
 px = N * info.width * info.height
 samples = info.coef_count * N
-for key, fn, in_bytes in (("device_dense_resident", run_dense, samples * 2), ("device_packed_from_pinned_host", run_packed, res["packed_bytes_per_tile"] * N)):
+for key, fn, in_bytes in (("device_dense_resident", run_dense, samples * 2), ("device_packed_from_pinned_host", run_packed, res["packed_bytes_per_tile"] * N),
+                          ("all_device_from_pinned_host", run_all_device, scan_total + samples * 2 * 2)):
     for _ in range(3):
         fn()
     ctx.sync()
@@ -125,6 +151,12 @@ if a.e2e > 0:
         tot = engine.pack_jpeg_tiles(tiles_, d, e, b, q, pool=pool)
         return det.detect_submit_jpeg(d, e, b, tot, q, info.width, info.height, info.ncomp, info.hs)
 
+    def via_scans():
+        tiles_ = list(pool.map(engine.prepare_jpeg_file, blobs))
+        sc, off, ln, tab, q, stt = det.jpeg_scan_staging(N, sum(t.scan.size for t in tiles_))
+        tot = engine.pack_jpeg_scans(tiles_, sc, off, ln, tab, q, pool=pool)
+        return det.detect_submit_jpeg_scans(sc, off, ln, tot, tab, q, stt, info.width, info.height, info.ncomp, info.hs)
+
     def via_cv2():
         batch = det.pinned_input(N, info.height, info.width)
         bn = batch.numpy()
@@ -135,7 +167,7 @@ if a.e2e > 0:
         return det.detect_submit(batch, bgr=True)
 
     counts = {}
-    for name, submit in (("jpeg_device_decode", via_jpeg), ("cv2_host_decode", via_cv2)):
+    for name, submit in (("jpeg_all_device", via_scans), ("jpeg_device_decode", via_jpeg), ("cv2_host_decode", via_cv2)):
         det.detect_wait(submit())
         t0 = time.perf_counter()
         prev = None
@@ -147,6 +179,7 @@ if a.e2e > 0:
         r = det.detect_wait(prev)
         counts[name] = r.counts.copy()
         res.setdefault("whole_path_tiles_per_s", {})[name] = round(a.e2e * N / (time.perf_counter() - t0), 1)
-    res["whole_path_tiles_per_s"]["identical_detection_counts"] = bool(np.array_equal(counts["jpeg_device_decode"], counts["cv2_host_decode"]))
+    res["whole_path_tiles_per_s"]["identical_detection_counts"] = bool(np.array_equal(counts["jpeg_device_decode"], counts["cv2_host_decode"]) and
+                                                                       np.array_equal(counts["jpeg_all_device"], counts["cv2_host_decode"]))
     det.close()
 print(json.dumps(res))

@@ -549,9 +549,11 @@ extern "C" int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_by
     aqj::State st = aqj::unpack_state(start[i]);
     long long blk = base;
     const uint32_t lim = limit(i);
+    aqj::BitWindow bits;
+    bits.init(words, st.p);
     while (st.p < lim && blk < g.total_blocks) {
       int16_t* dst = coef + aqj::block_address(g, blk) * 64;
-      if (aqj::decode_one(words, tabs, slot_comp, g.bpm, st, [&](int z, int v) { dst[kZigzagToNatural[z]] = (int16_t)v; })) ++blk;
+      if (aqj::decode_one(bits, tabs, slot_comp, g.bpm, st, [&](int z, int v) { dst[kZigzagToNatural[z]] = (int16_t)v; })) ++blk;
     }
     base += nblk[i];
   }

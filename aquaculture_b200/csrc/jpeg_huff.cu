@@ -142,9 +142,11 @@ __global__ void __launch_bounds__(HT) jpeg_huff_write_kernel(HuffParams p) {
   long long blk = p.base[slot];
   const uint32_t lim = sub_limit(p, total_bits, i);
   int16_t* tile_coef = p.coef + (size_t)tile * p.geo.total_blocks * 64;
+  BitWindow bits;
+  bits.init(words, st.p);
   while (st.p < lim && blk < p.geo.total_blocks) {
     int16_t* dst = tile_coef + block_address(p.geo, blk) * 64;
-    if (decode_one(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
+    if (decode_one(bits, sh.tabs, sh.slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
   }
 }
 

@@ -52,21 +52,36 @@ AQ_HD uint32_t be32(uint32_t w) {
 #endif
 }
 
-// 32 bits of the stream starting at bit p (the buffer is padded with zero words past the end).
-AQ_HD uint32_t window32(const uint32_t* words, uint32_t p) {
-  const uint32_t i = p >> 5, sh = p & 31;
-  const uint32_t w0 = be32(words[i]);
-  if (sh == 0) return w0;
-  return (w0 << sh) | (be32(words[i + 1]) >> (32 - sh));
-}
+// Sliding 64-bit view of the stream (the buffer is padded with zero words past the end): one 32-bit load per 32 bits
+// consumed instead of two per symbol.  Positions only move forward.
+struct BitWindow {
+  const uint32_t* words;
+  uint32_t wi;   // acc holds words[wi] (high half) and words[wi + 1] (low half)
+  uint64_t acc;
+  AQ_HD void init(const uint32_t* w, uint32_t p) {
+    words = w;
+    wi = p >> 5;
+    acc = ((uint64_t)be32(w[wi]) << 32) | be32(w[wi + 1]);
+  }
+  // 32 bits of the stream starting at bit p
+  AQ_HD uint32_t get(uint32_t p) {
+    uint32_t rel = p - (wi << 5);
+    while (rel >= 32) {
+      ++wi;
+      acc = (acc << 32) | be32(words[wi + 1]);
+      rel -= 32;
+    }
+    return (uint32_t)((acc << rel) >> 32);
+  }
+};
 
 AQ_HD int extend(uint32_t v, int size) { return v < (1u << (size - 1)) ? (int)v - (1 << size) + 1 : (int)v; }
 
 // Decodes the symbol at st.p and advances the state.  emit(zigzag position, value) is called for a coded coefficient
 // (position 0 = DC difference); returns true when the symbol completed a block (st.s then names the next slot).
 template <class Emit>
-AQ_HD bool decode_one(const uint32_t* words, const DevHuff* tabs, const uint8_t* slot_comp, int bpm, State& st, Emit&& emit) {
-  const uint32_t w = window32(words, st.p);
+AQ_HD bool decode_one(BitWindow& bits, const DevHuff* tabs, const uint8_t* slot_comp, int bpm, State& st, Emit&& emit) {
+  const uint32_t w = bits.get(st.p);
   const DevHuff& t = tabs[slot_comp[st.s] * 2 + (st.z != 0)];
   const uint32_t lk = t.look[w >> 23];
   int len, sym;
@@ -115,7 +130,9 @@ AQ_HD bool decode_one(const uint32_t* words, const DevHuff* tabs, const uint8_t*
 // Decodes every symbol that STARTS before bit `limit`; returns the number of blocks completed.
 AQ_HD int decode_range(const uint32_t* words, const DevHuff* tabs, const uint8_t* slot_comp, int bpm, State& st, uint32_t limit) {
   int nb = 0;
-  while (st.p < limit) nb += decode_one(words, tabs, slot_comp, bpm, st, [](int, int) {}) ? 1 : 0;
+  BitWindow bits;
+  bits.init(words, st.p);
+  while (st.p < limit) nb += decode_one(bits, tabs, slot_comp, bpm, st, [](int, int) {}) ? 1 : 0;
   return nb;
 }
 

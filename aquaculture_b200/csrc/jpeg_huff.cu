@@ -10,7 +10,10 @@ namespace {
 
 using namespace aqj;
 
-constexpr int HT = 1024;  // threads per CTA = subsequences per CTA
+#ifndef AQ_HUFF_THREADS
+#define AQ_HUFF_THREADS 1024
+#endif
+constexpr int HT = AQ_HUFF_THREADS;  // threads per CTA = subsequences per CTA
 
 __constant__ uint8_t c_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
                                      41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,

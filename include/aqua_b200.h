@@ -217,11 +217,13 @@ int aq_cage_areas(int square, double w, double h, int x_border, int y_border, do
 
 /* ------------------------------------------------------------------ JPEG tiles */
 /*
- * Hybrid decoder for the tiles gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74] and upstream
- * utils/dataloaders.py::LoadImages reads with cv2.imread [UPSTREAM-RECALLED]: the host walks the markers and undoes the
- * Huffman coding (sequential by nature), the GPU does all the arithmetic -- dequantisation, the 8x8 inverse DCT, chroma
- * upsampling and YCbCr -> RGB -- with results bit-identical to cv2.imread / libjpeg's defaults (accurate integer IDCT
- * "islow", triangle-filter "fancy" upsampling, 16-bit fixed-point colour conversion).  Supported: baseline / 8-bit
+ * Decoder for the tiles gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74] and upstream
+ * utils/dataloaders.py::LoadImages reads with cv2.imread [UPSTREAM-RECALLED].  Two ways in: the all-device decoder
+ * (aq_jpeg_scan_prepare + aq_jpeg_decode_device, further down: the host only walks the markers, the GPU undoes the Huffman
+ * coding too) and the hybrid one declared first (the host undoes the Huffman coding, the GPU does the arithmetic:
+ * dequantisation, the 8x8 inverse DCT, chroma upsampling and YCbCr -> RGB).  Results are bit-identical to cv2.imread /
+ * libjpeg's defaults (accurate integer IDCT "islow", triangle-filter "fancy" upsampling, 16-bit fixed-point colour
+ * conversion).  Supported: baseline / 8-bit
  * extended sequential Huffman files, one interleaved scan, grayscale, YCbCr 4:4:4 and 4:2:0, restart intervals.
  * Anything else (progressive, arithmetic, CMYK, 4:2:2 ...) returns AQ_ERR_UNSUPPORTED -- the caller decides, nothing is
  * decoded silently some other way.

@@ -114,6 +114,65 @@ def cpu_baseline(sd, n_tiles, seed_base=10_000):
     return r
 
 
+def jpeg_ingest(det, batch, size, n_batches=6):
+    """SURVEY.md 8f-1 beside the headline: `.jpeg` bytes -> detections through the public API (TileDetector), the whole
+    decoder on the GPU (host: marker walk on the io threads), against cv2.imdecode on the same threads feeding the same
+    detector.  Synthetic scenes (smooth field + noise, quality 75, 4:2:0 as gdal.Translate -of JPEG writes).  Bounded:
+    a few batches; never fails the bench."""
+    try:
+        from concurrent.futures import ThreadPoolExecutor
+
+        import cv2
+        import numpy as np
+        from aquaculture_b200 import engine
+        cv2.setNumThreads(1)
+        rng = np.random.default_rng(0)
+        blobs = []
+        for i in range(batch):
+            base = rng.integers(0, 256, (size // 16 + 2, size // 16 + 2, 3), dtype=np.uint8)
+            img = cv2.resize(base, (size, size), interpolation=cv2.INTER_CUBIC).astype(np.int32) + rng.integers(-12, 12, (size, size, 3))
+            blobs.append(cv2.imencode(".jpg", np.clip(img, 0, 255).astype(np.uint8), [cv2.IMWRITE_JPEG_QUALITY, 75])[1])
+        threads = len(os.sched_getaffinity(0))
+        pool = ThreadPoolExecutor(threads)
+
+        def via_device():
+            tl = list(pool.map(engine.prepare_jpeg_file, blobs))
+            sc, off, ln, tab, q, stt = det.jpeg_scan_staging(batch, sum(t.scan.size for t in tl))
+            tot = engine.pack_jpeg_scans(tl, sc, off, ln, tab, q, pool=pool)
+            i0 = tl[0].info
+            return det.detect_submit_jpeg_scans(sc, off, ln, tot, tab, q, stt, i0.width, i0.height, i0.ncomp, i0.hs)
+
+        def via_cv2():
+            buf = det.pinned_input(batch, size, size)
+            bn = buf.numpy()
+
+            def one(i):
+                bn[i] = cv2.imdecode(blobs[i], cv2.IMREAD_COLOR)
+            list(pool.map(one, range(batch)))
+            return det.detect_submit(buf, bgr=True)
+
+        out, counts = {}, {}
+        for name, submit in (("gpu_decode", via_device), ("cv2_host_decode", via_cv2)):
+            det.detect_wait(submit())
+            t0 = time.perf_counter()
+            prev = None
+            for _ in range(n_batches):
+                tk = submit()
+                if prev is not None:
+                    det.detect_wait(prev)
+                prev = tk
+            counts[name] = det.detect_wait(prev).counts.copy()
+            out[name] = round(n_batches * batch / (time.perf_counter() - t0), 1)
+        pool.shutdown()
+        return {"unit": "tiles/s", "tiles": f"{size}x{size} synthetic scenes, JPEG quality 75 4:2:0, {int(np.mean([b.size for b in blobs]))} B/tile",
+                "gpu_decode": out["gpu_decode"], "cv2_host_decode": out["cv2_host_decode"], "host_threads": threads,
+                "identical_detection_counts": bool(np.array_equal(counts["gpu_decode"], counts["cv2_host_decode"])),
+                "note": "whole path from .jpeg bytes in host memory to detections; gpu_decode = marker walk on the host, Huffman "
+                        "decoding + IDCT + upsampling + colour on the GPU (bit-identical to cv2.imread), two batches in flight"}
+    except Exception as e:  # noqa: BLE001 - a side measurement must not take the headline down
+        return {"error": f"{type(e).__name__}: {e}"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -162,6 +221,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-tiles", type=int, default=12, help="tiles in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-jpeg", action="store_true", help="skip the JPEG-ingest side measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -360,6 +420,8 @@ def main():
             "aux_kernels": aux,
             "counters": {"tiles": int(counters[0]), "label_files_last_e2e_pass": int(counters[1]), "detections_last_batch": int(counters[2])},
         }
+        if world == 1 and not args.no_jpeg:
+            out["jpeg_ingest"] = jpeg_ingest(det, BATCH, IMG)
         if not args.no_cpu_baseline and world == 1:
             r = cpu_baseline(sd, args.cpu_tiles)
             out["cpu_baseline"] = {"value": round(r["tiles_per_s"], 3), "unit": UNIT, "cores": r["cores"], "kind": "port",

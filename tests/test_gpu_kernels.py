@@ -148,7 +148,9 @@ def test_conv3x3_s1_variants(ctx, mode, mblk, B, H, W, ci, co):
 def test_conv3x3_halo_four_blocks(ctx):
     # 4 M blocks per tile (2x2 or 4x1), images stacked in the tall coordinate system, ragged sizes
     run_conv_case(ctx, 5, 20, 20, 48, 48, 3, 1, mode=1, mblk=4, res=True)
-    run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4)
+    run_conv_case(ctx, 3, 36, 52, 96, 48, 3, 1, mode=1, mblk=4)   # two 64-wide chunks per tap; 96 -> 96 no longer fits 4 blocks
+    with pytest.raises(engine.AquaError, match="no tiling fits"):  # ... and is refused, not silently re-tiled
+        run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4)
     run_conv_case(ctx, 7, 12, 9 * 8, 64, 32, 3, 1, mode=1, mblk=4)
 
 

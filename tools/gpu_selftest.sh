@@ -21,3 +21,4 @@ run prepost "preprocess or sppf or tile_stats"
 run nms "nms"
 run e2e "e2e or label_files"
 run jpeg "jpeg"
+run rest "not (conv1x1 or folded_upsample or conv3x3_s1 or residual or dense_taps or s1_variants or s2_variants or mblk_variants or fast_silu or conv3x3_s2 or cluster or many_tiles or detect_decode or preprocess or sppf or tile_stats or nms or e2e or label_files or jpeg)"

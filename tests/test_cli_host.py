@@ -121,3 +121,12 @@ def test_raster_tile_flags():
         cli.check_unsupported(cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--skip-blank"]))
     with pytest.raises(SystemExit, match="--raster-tile"):
         cli.check_unsupported(cli.parse_opt(["--weights", "synthetic", "--nosave", "--save-txt", "--raster-tile", "64", "--synthetic", "4"]))
+
+
+def test_jpeg_decode_modes_parse():
+    base = ["--weights", "w.pt", "--source", "data/jpegs", "--nosave", "--save-txt", "--save-conf"]
+    assert cli.parse_opt(base).jpeg_decode == "device"           # default: the whole decoder on the GPU
+    for mode in ("device", "hybrid", "host"):
+        assert cli.parse_opt(base + ["--jpeg-decode", mode]).jpeg_decode == mode
+    with pytest.raises(SystemExit):
+        cli.parse_opt(base + ["--jpeg-decode", "cpu"])

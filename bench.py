@@ -173,6 +173,26 @@ def jpeg_ingest(det, batch, size, n_batches=6):
         return {"error": f"{type(e).__name__}: {e}"}
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL's version line when the launcher sets
+    NCCL_DEBUG, ...), so file descriptor 1 is pointed at stderr for the whole run and the JSON line goes to a saved
+    duplicate of the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(obj):
+    sys.stdout.flush()
+    line = (json.dumps(obj) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, line)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -201,7 +221,7 @@ def run_reference(args):
     v = per_step * args.steps / dt
     sample = (f"{per_step} tiles per step (of the 64-tile batch), batch 1 fp32 eager torch {torch.__version__} CPU, "
               f"{args.steps} steps; oracle port of detect.py (reference code absent from snapshot)")
-    print(json.dumps({
+    emit_line({
         "impl": "reference", "metric": METRIC, "value": round(v, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * dt / args.steps, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -209,7 +229,7 @@ def run_reference(args):
                                "letterbox + NMS + label write", "batch": 1},
         "cpu_baseline": {"value": round(v, 3), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": round(v, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
     return 0
 
 
@@ -223,6 +243,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-jpeg", action="store_true", help="skip the JPEG-ingest side measurement")
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
@@ -428,7 +449,7 @@ def main():
                                    "sample": f"{r['n']} synthetic 640x640 tiles, batch 1 fp32, oracle port of detect.py "
                                              f"(reference submodule absent), stage ms pre/inf/nms = "
                                              f"{[round(x, 1) for x in r['stage_ms']]}"}
-        print(json.dumps(out))
+        emit_line(out)
     det.close()
     if world > 1:
         dist.destroy_process_group()

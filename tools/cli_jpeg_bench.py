@@ -24,6 +24,7 @@ from aquaculture_b200 import detect_cli as cli  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--tiles", type=int, default=1024)
 ap.add_argument("--size", type=int, default=1024)
+ap.add_argument("--warm", type=int, default=64, help="tiles of the untimed warm-up call (CUDA init, module load)")
 a = ap.parse_args()
 os.environ.setdefault("AQUA_AUTOTUNE", "0")  # identical tilings in every run: label files comparable bit for bit
 root = tempfile.mkdtemp(prefix="aq_jpegs_")
@@ -44,6 +45,14 @@ with ThreadPoolExecutor(len(os.sched_getaffinity(0))) as ex:
 res = {"tiles": a.tiles, "size": a.size, "host_threads": len(os.sched_getaffinity(0)),
        "jpeg_bytes_per_tile": int(np.mean([os.path.getsize(os.path.join(src, f)) for f in os.listdir(src)]))}
 labels = {}
+if a.warm > 0:  # untimed: CUDA context, module load, first plan
+    wsrc = os.path.join(root, "warm")
+    os.makedirs(wsrc)
+    for f in sorted(os.listdir(src))[:a.warm]:
+        os.symlink(os.path.join(src, f), os.path.join(wsrc, f))
+    with contextlib.redirect_stdout(io.StringIO()):
+        cli.main(["--weights", "synthetic", "--source", wsrc, "--nosave", "--save-txt", "--save-conf", "--project", os.path.join(root, "runs"),
+                  "--name", "warm"])
 for mode in ("device", "hybrid", "host"):
     argv = ["--weights", "synthetic", "--source", src, "--nosave", "--save-txt", "--save-conf", "--project", os.path.join(root, "runs"),
             "--name", mode, "--jpeg-decode", mode, "--io-threads", str(res["host_threads"])]

@@ -258,6 +258,7 @@ def run(opt, argv) -> int:
     dt = [0.0, 0.0]  # load+stage, gpu (pre+inference+NMS) + label write
     seen = n_files = n_dets = 0
     pool = ThreadPoolExecutor(opt.io_threads)
+    pack_pool = ThreadPoolExecutor(max(2, opt.io_threads // 4))  # staging copies: not queued behind the prefetched loads
     B = opt.batch_size
     pos = 0
     pending = {}  # (h0, w0) -> list of (image, stem)
@@ -299,13 +300,13 @@ def run(opt, argv) -> int:
         t0 = time.perf_counter()
         if is_jpeg:
             desc, ent, base, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count, sum(g[0].entries.size for g in group))
-            total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant, pool=pool)
+            total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant, pool=pack_pool)
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg(desc, ent, base, total, quant, w0, h0, ncomp, hs)
         elif is_scan:
             sl = [g[0] for g in group]
             sc, off, ln, tab, quant, status = det.jpeg_scan_staging(len(group), sum(t.scan.size for t in sl))
-            total = engine.pack_jpeg_scans(sl, sc, off, ln, tab, quant, pool=pool)
+            total = engine.pack_jpeg_scans(sl, sc, off, ln, tab, quant, pool=pack_pool)
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg_scans(sc, off, ln, total, tab, quant, status, w0, h0, ncomp, hs)
             scan_status[ticket[0]] = (status, [g[1] for g in group])
@@ -363,10 +364,14 @@ def run(opt, argv) -> int:
             dt[0] += time.perf_counter() - t0
             run_raster(im, stem)
         pos = len(items)
+    # the next chunk's files are read / parsed on the io threads while this chunk is grouped, submitted and its
+    # predecessor's labels are written
+    futs = [pool.submit(load, it) for it in items[pos:pos + B]]
     while pos < len(items):
-        chunk = items[pos:pos + B]
+        nxt = [pool.submit(load, it) for it in items[pos + B:pos + 2 * B]]
         t0 = time.perf_counter()
-        imgs = list(pool.map(load, chunk))
+        imgs = [f.result() for f in futs]
+        futs = nxt
         dt[0] += time.perf_counter() - t0
         for im, stem in zip(imgs, stems[pos:pos + B]):
             key = im.key if isinstance(im, (engine.PackedJpeg, engine.ScanJpeg)) else im.shape[:2]

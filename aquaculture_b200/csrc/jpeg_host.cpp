@@ -514,8 +514,7 @@ extern "C" int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_by
   const aqj::Geo g = make_geo(*info);
   const aqj::DevHuff* tabs = reinterpret_cast<const aqj::DevHuff*>(tables);
   const uint32_t* words = reinterpret_cast<const uint32_t*>(scan);
-  uint8_t slot_comp[8] = {0};
-  for (int s = 0; s < g.bpm; ++s) slot_comp[s] = g.ncomp == 1 ? 0 : (s < g.hs * g.vs ? 0 : (uint8_t)(s - g.hs * g.vs + 1));
+  const uint32_t slot_comp = aqj::pack_slot_comp(g.ncomp, g.hs, g.vs);
   const uint32_t total_bits = (uint32_t)(scan_bytes * 8);
   const int nsub = (int)((total_bits + sub_bits - 1) / sub_bits);
   if (nsub <= 0) return AQ_ERR_ARG;

@@ -21,17 +21,12 @@ __constant__ uint8_t c_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32,
 
 struct Shared {
   DevHuff tabs[kTablesPerTile];
-  uint8_t slot_comp[8];
 };
 
 __device__ __forceinline__ void load_tables(Shared& sh, const HuffParams& p, int tile) {
   const uint32_t* src = reinterpret_cast<const uint32_t*>(p.tables + (size_t)tile * kTablesPerTile * sizeof(DevHuff));
   uint32_t* dst = reinterpret_cast<uint32_t*>(sh.tabs);
   for (int i = threadIdx.x; i < (int)(kTablesPerTile * sizeof(DevHuff) / 4); i += blockDim.x) dst[i] = src[i];
-  if (threadIdx.x < 8) {
-    const int s = threadIdx.x, nl = p.geo.hs * p.geo.vs;
-    sh.slot_comp[s] = p.geo.ncomp == 1 ? 0 : (s < nl ? 0 : (uint8_t)min(s - nl + 1, 2));
-  }
   __syncthreads();
 }
 
@@ -53,6 +48,7 @@ __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int fi
   if (blockIdx.x * HT >= nsub) return;
   load_tables(sh, p, tile);
   const uint32_t* words = reinterpret_cast<const uint32_t*>(p.scans + p.scan_off[tile]);
+  const uint32_t slot_comp = pack_slot_comp(p.geo.ncomp, p.geo.hs, p.geo.vs);
   const size_t slot = (size_t)tile * p.nsub_max + i;
   const bool live = i < nsub;
   unsigned long long my_start = 0, my_end = 0;
@@ -61,7 +57,7 @@ __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int fi
     if (first) {
       State st{(uint32_t)((unsigned long long)i * p.sub_bits), 0, 0};
       my_start = pack_state(st);
-      my_nblk = decode_range(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
+      my_nblk = decode_range(words, sh.tabs, slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
       my_end = pack_state(st);
     } else {
       my_start = p.start[slot];
@@ -80,7 +76,7 @@ __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int fi
       if (prev != my_start) {
         my_start = prev;
         State st = unpack_state(prev);
-        my_nblk = decode_range(words, sh.tabs, sh.slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
+        my_nblk = decode_range(words, sh.tabs, slot_comp, p.geo.bpm, st, sub_limit(p, total_bits, i));
         my_end = pack_state(st);
         changed = true;
       }
@@ -140,6 +136,7 @@ __global__ void __launch_bounds__(HT) jpeg_huff_write_kernel(HuffParams p) {
   load_tables(sh, p, tile);
   if (i >= nsub) return;
   const uint32_t* words = reinterpret_cast<const uint32_t*>(p.scans + p.scan_off[tile]);
+  const uint32_t slot_comp = pack_slot_comp(p.geo.ncomp, p.geo.hs, p.geo.vs);
   const size_t slot = (size_t)tile * p.nsub_max + i;
   State st = unpack_state(p.start[slot]);
   long long blk = p.base[slot];
@@ -149,7 +146,7 @@ __global__ void __launch_bounds__(HT) jpeg_huff_write_kernel(HuffParams p) {
   bits.init(words, st.p);
   while (st.p < lim && blk < p.geo.total_blocks) {
     int16_t* dst = tile_coef + block_address(p.geo, blk) * 64;
-    if (decode_one(bits, sh.tabs, sh.slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
+    if (decode_one(bits, sh.tabs, slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
   }
 }
 

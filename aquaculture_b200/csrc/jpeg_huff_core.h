@@ -79,16 +79,17 @@ AQ_HD int extend(uint32_t v, int size) { return v < (1u << (size - 1)) ? (int)v 
 
 // Decodes the symbol at st.p and advances the state.  emit(zigzag position, value) is called for a coded coefficient
 // (position 0 = DC difference); returns true when the symbol completed a block (st.s then names the next slot).
+// slot_comp: component of MCU slot s in nibble s.  Written with selects rather than branches: the lanes of a warp sit in
+// different places of their blocks (DC size, coefficient, end-of-block, zero run), and one common instruction stream
+// costs less than the four diverged ones; only the rare long-code search (> 9 bits) branches.
 template <class Emit>
-AQ_HD bool decode_one(BitWindow& bits, const DevHuff* tabs, const uint8_t* slot_comp, int bpm, State& st, Emit&& emit) {
+AQ_HD bool decode_one(BitWindow& bits, const DevHuff* tabs, uint32_t slot_comp, int bpm, State& st, Emit&& emit) {
   const uint32_t w = bits.get(st.p);
-  const DevHuff& t = tabs[slot_comp[st.s] * 2 + (st.z != 0)];
+  const bool is_dc = st.z == 0;
+  const DevHuff& t = tabs[((slot_comp >> (4 * st.s)) & 15) * 2 + (is_dc ? 0 : 1)];
   const uint32_t lk = t.look[w >> 23];
-  int len, sym;
-  if (lk) {
-    len = (int)(lk >> 8);
-    sym = (int)(lk & 255);
-  } else {
+  int len = (int)(lk >> 8), sym = (int)(lk & 255);
+  if (lk == 0) {
     const int c16 = (int)(w >> 16);
     int code = 0;
     for (len = 10; len <= 16; ++len) {
@@ -102,38 +103,35 @@ AQ_HD bool decode_one(BitWindow& bits, const DevHuff* tabs, const uint8_t* slot_
       sym = t.vals[(code + t.valoff[len]) & 255];
     }
   }
-  if (st.z == 0) {
-    const int size = sym > 16 ? 16 : sym;
-    if (size) emit(0, extend((w << len) >> (32 - size), size));
-    st.p += (uint32_t)(len + size);
-    st.z = 1;
-  } else {
-    const int r = sym >> 4, size = sym & 15;
-    if (size == 0) {
-      st.z = r == 15 ? st.z + 16 : 64;
-      st.p += (uint32_t)len;
-    } else {
-      st.z += r;
-      if (st.z < 64) emit(st.z, extend((w << len) >> (32 - size), size));
-      st.z += 1;
-      st.p += (uint32_t)(len + size);
-    }
-  }
-  if (st.z >= 64) {
-    st.z = 0;
-    st.s = st.s + 1 == bpm ? 0 : st.s + 1;
-    return true;
-  }
-  return false;
+  const int run = is_dc ? 0 : sym >> 4;
+  const int size = is_dc ? (sym > 16 ? 16 : sym) : (sym & 15);
+  const bool no_coef = !is_dc && size == 0;             // end of block, or a run of 16 zeros
+  const int pos = st.z + run;
+  if (size != 0 && pos < 64) emit(pos, extend((w << len) >> (32 - size), size));
+  st.z = no_coef ? (run == 15 ? st.z + 16 : 64) : pos + 1;
+  st.p += (uint32_t)(len + size);
+  const bool done = st.z >= 64;
+  st.z = done ? 0 : st.z;
+  st.s = done ? (st.s + 1 == bpm ? 0 : st.s + 1) : st.s;
+  return done;
 }
 
 // Decodes every symbol that STARTS before bit `limit`; returns the number of blocks completed.
-AQ_HD int decode_range(const uint32_t* words, const DevHuff* tabs, const uint8_t* slot_comp, int bpm, State& st, uint32_t limit) {
+AQ_HD int decode_range(const uint32_t* words, const DevHuff* tabs, uint32_t slot_comp, int bpm, State& st, uint32_t limit) {
   int nb = 0;
   BitWindow bits;
   bits.init(words, st.p);
   while (st.p < limit) nb += decode_one(bits, tabs, slot_comp, bpm, st, [](int, int) {}) ? 1 : 0;
   return nb;
+}
+
+// Component of every MCU slot, one nibble per slot: luma blocks first, then Cb, Cr.
+AQ_HD uint32_t pack_slot_comp(int ncomp, int hs, int vs) {
+  if (ncomp == 1) return 0;
+  uint32_t v = 0;
+  const int nl = hs * vs;
+  for (int s = 0; s < nl + 2 && s < 8; ++s) v |= (uint32_t)(s < nl ? 0 : s - nl + 1) << (4 * s);
+  return v;
 }
 
 // Geometry shared by the writers: where block g (decode order) of a tile lives in the dense coefficient planes.

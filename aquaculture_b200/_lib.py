@@ -105,6 +105,8 @@ SIGNATURES = {
                                              C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "aq_jpeg_scan_prepare": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(JpegInfo), C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
                                        C.c_void_p, C.c_void_p]),
+    "aq_jpeg_scan_prepare_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
+                                             C.POINTER(C.c_size_t), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "aq_jpeg_decode_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,
                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "aq_jpeg_debug_parallel_decode": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(JpegInfo), C.c_int, C.c_void_p,

@@ -7,6 +7,8 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "../../include/aqua_b200.h"
@@ -40,6 +42,9 @@ bool build_table(HuffTable& t) {
   uint32_t code = 0;
   int p = 0;
   memset(t.look, 0, sizeof t.look);
+  t.maxcode[0] = -1;
+  t.valoff[0] = 0;
+  memset(t.vals + n, 0, sizeof t.vals - (size_t)n);
   for (int l = 1; l <= 16; ++l) {
     if (t.bits[l]) {
       t.valoff[l] = p - (int32_t)code;
@@ -53,6 +58,7 @@ bool build_table(HuffTable& t) {
       if (code > (1u << l)) return false;  // over-subscribed
     } else {
       t.maxcode[l] = -1;
+      t.valoff[l] = 0;
     }
     code <<= 1;
   }
@@ -503,6 +509,41 @@ extern "C" int aq_jpeg_scan_prepare(const uint8_t* data, size_t len, aq_jpeg_inf
   const size_t padded = (n + 3) / 4 * 4 + 8;  // whole words + two zero words the 32-bit window may touch
   if (padded > scan_cap) return AQ_ERR_NOMEM;
   memset(scan_out + n, 0, padded - n);
+  return AQ_OK;
+}
+
+// A whole batch in one call, written straight into the staging areas aq_jpeg_decode_device reads; tiles are spread over
+// n_threads host threads (no interpreter in the loop).
+extern "C" int aq_jpeg_scan_prepare_batch(const uint8_t* const* datas, const size_t* lens, int n, uint8_t* scans, size_t scans_cap,
+                                          uint64_t* scan_off, uint32_t* scan_bytes, size_t* total_bytes, uint8_t* tables,
+                                          uint16_t* quant, aq_jpeg_info* infos, int* status, int n_threads) {
+  if (!datas || !lens || n <= 0 || !scans || !scan_off || !scan_bytes || !total_bytes || !tables || !quant || !infos || !status)
+    return AQ_ERR_ARG;
+  size_t pos = 0;
+  for (int i = 0; i < n; ++i) {  // a scan is never longer than its file
+    scan_off[i] = pos;
+    pos += (lens[i] + 16 + 3) / 4 * 4;
+  }
+  if (pos > scans_cap) return AQ_ERR_NOMEM;
+  std::atomic<int> next{0};
+  auto work = [&]() {
+    for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+      size_t nb = 0;
+      const size_t cap = (lens[i] + 16 + 3) / 4 * 4;
+      status[i] = datas[i] ? aq_jpeg_scan_prepare(datas[i], lens[i], &infos[i], scans + scan_off[i], cap, &nb,
+                                                  tables + (size_t)i * AQ_JPEG_TABLE_BYTES, quant + (size_t)i * 192)
+                           : AQ_ERR_ARG;
+      scan_bytes[i] = (uint32_t)nb;
+    }
+  };
+  const int nt = n_threads < 1 ? 1 : (n_threads > n ? n : n_threads);
+  std::vector<std::thread> pool;
+  for (int t = 1; t < nt; ++t) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  *total_bytes = pos;
+  for (int i = 0; i < n; ++i)
+    if (status[i] != AQ_OK) return status[i];
   return AQ_OK;
 }
 

@@ -229,10 +229,10 @@ def run(opt, argv) -> int:
                 blob = np.frombuffer(fh.read(), np.uint8)
             try:
                 if opt.jpeg_decode == "device":
-                    try:
-                        return engine.prepare_jpeg_file(blob)  # markers + unstuffing only: the GPU decodes the scan
-                    except jpeg.JpegUnsupported:
-                        pass  # restart intervals: Huffman on the host; anything else fails again below
+                    info = jpeg.probe(blob)  # geometry only; the whole batch is prepared by one library call in flush()
+                    if info.restart_interval == 0:
+                        return engine.RawJpeg(blob, info)
+                    # restart intervals re-align the stream: Huffman on the host for such a file
                 return engine.entropy_decode_file(blob)  # host half: markers + Huffman (C, GIL released)
             except jpeg.JpegUnsupported:
                 n_host_decoded[0] += 1  # e.g. progressive: decoded on the host like upstream does, and reported below
@@ -304,9 +304,10 @@ def run(opt, argv) -> int:
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg(desc, ent, base, total, quant, w0, h0, ncomp, hs)
         elif is_scan:
-            sl = [g[0] for g in group]
-            sc, off, ln, tab, quant, status = det.jpeg_scan_staging(len(group), sum(t.scan.size for t in sl))
-            total = engine.pack_jpeg_scans(sl, sc, off, ln, tab, quant, pool=pack_pool)
+            try:
+                (sc, off, ln, tab, quant, status), total, _ = engine.prepare_jpeg_batch(det, [g[0].blob for g in group], n_threads=opt.io_threads)
+            except engine.AquaError as e:
+                raise SystemExit(f"detect.py (B200 path): {e} (batch starting at {group[0][1]})")
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg_scans(sc, off, ln, total, tab, quant, status, w0, h0, ncomp, hs)
             scan_status[ticket[0]] = (status, [g[1] for g in group])
@@ -374,7 +375,7 @@ def run(opt, argv) -> int:
         futs = nxt
         dt[0] += time.perf_counter() - t0
         for im, stem in zip(imgs, stems[pos:pos + B]):
-            key = im.key if isinstance(im, (engine.PackedJpeg, engine.ScanJpeg)) else im.shape[:2]
+            key = im.key if isinstance(im, (engine.PackedJpeg, engine.RawJpeg)) else im.shape[:2]
             pending.setdefault(key, []).append((im, stem))
             if len(pending[key]) == B:
                 flush(key, pending.pop(key))

@@ -508,6 +508,44 @@ def prepare_jpeg_file(blob) -> ScanJpeg:
     return t
 
 
+class RawJpeg:
+    """A JPEG file's bytes + geometry, probed but not yet prepared (the batch call does that: prepare_jpeg_batch)."""
+    __slots__ = ("blob", "info", "key")
+
+    def __init__(self, blob, info):
+        self.blob, self.info = blob, info
+        self.key = ("jpegscan", info.height, info.width, info.ncomp, info.hs)
+
+
+def prepare_jpeg_batch(det: "TileDetector", blobs: Sequence, n_threads: int = 8):
+    """Host side of the all-device decoder for a whole batch in ONE library call (aq_jpeg_scan_prepare_batch: marker walk +
+    unstuffing on C threads, written straight into a pinned staging area of `det`).  blobs: bytes or uint8 arrays of
+    equally-shaped JPEG files.  Returns (staging views, total bytes, info of tile 0) for `detect_submit_jpeg_scans`, or raises
+    jpeg.JpegUnsupported / AquaError naming the first offending tile."""
+    from . import jpeg
+    n = len(blobs)
+    arrs = [np.frombuffer(b, np.uint8) if not isinstance(b, np.ndarray) else b for b in blobs]
+    lens = np.fromiter((a.size for a in arrs), np.uint64, n)
+    need = int(((lens + 16 + 3) // 4 * 4).sum())
+    sc, off, ln, tab, q, stt = det.jpeg_scan_staging(n, need)
+    ptrs = (C.c_void_p * n)(*[a.ctypes.data for a in arrs])
+    infos = (_lib.JpegInfo * n)()
+    status = np.zeros(n, np.int32)
+    total = C.c_size_t(0)
+    rc = _lib.load().aq_jpeg_scan_prepare_batch(ptrs, lens.ctypes.data, n, sc.ctypes.data, sc.size, off.ctypes.data, ln.ctypes.data,
+                                                C.byref(total), tab.ctypes.data, q.ctypes.data, infos, status.ctypes.data, n_threads)
+    if rc == jpeg.AQ_ERR_UNSUPPORTED:
+        raise jpeg.JpegUnsupported(f"tile {int(np.flatnonzero(status)[0])}: JPEG variant without an all-device path")
+    if rc < 0:
+        raise _lib.AquaError(f"aq_jpeg_scan_prepare_batch failed ({rc}) at tile {int(np.flatnonzero(status)[0]) if status.any() else -1}")
+    i0 = infos[0]
+    geo = (i0.width, i0.height, i0.ncomp, i0.hs)
+    for i in range(1, n):
+        if (infos[i].width, infos[i].height, infos[i].ncomp, infos[i].hs) != geo:
+            raise _lib.AquaError(f"prepare_jpeg_batch: tile {i} has another geometry than tile 0")
+    return (sc, off, ln, tab, q, stt), int(total.value), i0
+
+
 def pack_jpeg_scans(tiles_: Sequence[ScanJpeg], scans, off, length, tables, quant, pool=None) -> int:
     """Lay the tiles' scans one after another in a staging area (TileDetector.jpeg_scan_staging); returns the extent."""
     sizes = [t.scan.size for t in tiles_]  # multiples of 4, padding included

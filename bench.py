@@ -136,10 +136,7 @@ def jpeg_ingest(det, batch, size, n_batches=6):
         pool = ThreadPoolExecutor(threads)
 
         def via_device():
-            tl = list(pool.map(engine.prepare_jpeg_file, blobs))
-            sc, off, ln, tab, q, stt = det.jpeg_scan_staging(batch, sum(t.scan.size for t in tl))
-            tot = engine.pack_jpeg_scans(tl, sc, off, ln, tab, q, pool=pool)
-            i0 = tl[0].info
+            (sc, off, ln, tab, q, stt), tot, i0 = engine.prepare_jpeg_batch(det, blobs, n_threads=threads)
             return det.detect_submit_jpeg_scans(sc, off, ln, tot, tab, q, stt, i0.width, i0.height, i0.ncomp, i0.hs)
 
         def via_cv2():

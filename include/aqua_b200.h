@@ -284,6 +284,13 @@ int aq_jpeg_reconstruct_packed(aq_ctx* ctx, const uint32_t* block_desc, const ui
 #define AQ_JPEG_TABLE_BYTES 8640
 int aq_jpeg_scan_prepare(const uint8_t* data, size_t len, aq_jpeg_info* info, uint8_t* scan_out, size_t scan_cap,
                          size_t* scan_bytes, uint8_t* tables_out, uint16_t* quant);
+/* The same for a batch in one call, written straight into the staging areas aq_jpeg_decode_device takes and spread over
+ * n_threads host threads: tile i's segment goes to scans + scan_off[i] (offsets are chosen here from the file lengths;
+ * scans_cap >= sum over i of (lens[i] + 16 rounded up to 4) always suffices), *total_bytes = the extent used; infos /
+ * status receive n entries (status[i] = that tile's aq_status).  Returns AQ_OK or the first failing tile's status. */
+int aq_jpeg_scan_prepare_batch(const uint8_t* const* datas, const size_t* lens, int n, uint8_t* scans, size_t scans_cap,
+                               uint64_t* scan_off, uint32_t* scan_bytes, size_t* total_bytes, uint8_t* tables, uint16_t* quant,
+                               aq_jpeg_info* infos, int* status, int n_threads);
 /*
  * n tiles of identical geometry: scans = their prepared segments one after another, tile i at byte scan_off[i] (a multiple
  * of 4) with scan_bytes[i] bytes, total_scan_bytes = extent of `scans` (padding included); tables = n x

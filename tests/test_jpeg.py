@@ -90,6 +90,28 @@ def test_parallel_huffman_on_a_tile():
     assert np.array_equal(got, coef) and rounds < 64
 
 
+def test_scan_prepare_batch_equals_per_tile(monkeypatch):
+    """The one-call batch preparation (C threads, straight into staging) writes what the per-tile call writes."""
+    blobs = [cv2.imencode(".jpg", tile_scene(200, 328, seed=i), [cv2.IMWRITE_JPEG_QUALITY, 60 + 7 * i])[1].tobytes() for i in range(5)]
+
+    class FakeDet:  # staging without a GPU: plain numpy instead of pinned memory
+        batch = 8
+
+        def jpeg_scan_staging(self, n, min_bytes=0):
+            return (np.zeros(min_bytes + 64, np.uint32).view(np.uint8)[:min_bytes + 64], np.zeros(n, np.uint64), np.zeros(n, np.uint32),
+                    np.zeros((n, _lib.AQ_JPEG_TABLE_BYTES), np.uint8), np.zeros((n, 192), np.uint16), np.zeros(n, np.int32))
+
+    (sc, off, ln, tab, q, stt), total, i0 = engine.prepare_jpeg_batch(FakeDet(), blobs, n_threads=3)
+    assert (i0.width, i0.height) == (328, 200) and total <= sc.size
+    for i, b in enumerate(blobs):
+        info, scan, nbytes, tables, quant = jpeg.scan_prepare(b)
+        assert ln[i] == nbytes and off[i] % 4 == 0
+        assert np.array_equal(sc[int(off[i]):int(off[i]) + scan.size], scan)
+        assert np.array_equal(tab[i], tables) and np.array_equal(q[i], quant)
+    with pytest.raises(jpeg.JpegUnsupported):
+        engine.prepare_jpeg_batch(FakeDet(), blobs[:2] + [GOLD["unsupported_progressive"].tobytes()])
+
+
 def test_restart_interval_files_are_left_to_the_host_decoder():
     case = next(c for c in CASES if "rst" in c and c.startswith("96x128"))
     with pytest.raises(jpeg.JpegUnsupported):

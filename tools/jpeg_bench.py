@@ -152,10 +152,8 @@ if a.e2e > 0:
         return det.detect_submit_jpeg(d, e, b, tot, q, info.width, info.height, info.ncomp, info.hs)
 
     def via_scans():
-        tiles_ = list(pool.map(engine.prepare_jpeg_file, blobs))
-        sc, off, ln, tab, q, stt = det.jpeg_scan_staging(N, sum(t.scan.size for t in tiles_))
-        tot = engine.pack_jpeg_scans(tiles_, sc, off, ln, tab, q, pool=pool)
-        return det.detect_submit_jpeg_scans(sc, off, ln, tot, tab, q, stt, info.width, info.height, info.ncomp, info.hs)
+        (sc, off, ln, tab, q, stt), tot, i0 = engine.prepare_jpeg_batch(det, blobs, n_threads=a.threads)
+        return det.detect_submit_jpeg_scans(sc, off, ln, tot, tab, q, stt, i0.width, i0.height, i0.ncomp, i0.hs)
 
     def via_cv2():
         batch = det.pinned_input(N, info.height, info.width)

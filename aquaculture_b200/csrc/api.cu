@@ -1625,8 +1625,8 @@ int aq_jpeg_decode_device(aq_ctx* c, const uint8_t* scans, const uint64_t* scan_
   h.sub_bits = sub_bits;
   int nsub_max = 1;
   for (int i = 0; i < n; ++i) {
-    if ((scan_off[i] & 3) || scan_off[i] + scan_bytes[i] + 8 > total_scan_bytes || scan_bytes[i] >= (1u << 28))
-      return fail(c, AQ_ERR_ARG, "jpeg_decode_device: tile %d: segment [%llu, +%u) not inside the %zu staged bytes (needs 8 bytes of padding)",
+    if ((scan_off[i] & 3) || scan_off[i] + ((size_t)scan_bytes[i] + 3) / 4 * 4 + 8 > total_scan_bytes || scan_bytes[i] >= (1u << 28))
+      return fail(c, AQ_ERR_ARG, "jpeg_decode_device: tile %d: segment [%llu, +%u) not inside the %zu staged bytes (whole words + 8 bytes of zero padding are read)",
                   i, (unsigned long long)scan_off[i], scan_bytes[i], total_scan_bytes);
     const int ns = (int)(((size_t)scan_bytes[i] * 8 + sub_bits - 1) / sub_bits);
     nsub_max = ns > nsub_max ? ns : nsub_max;

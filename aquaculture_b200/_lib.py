@@ -75,6 +75,7 @@ SIGNATURES = {
     "aq_geocode_label_text": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int,
                                         C.c_void_p, C.c_int]),
     "aq_cage_areas": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "aq_dbscan": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p]),
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
     "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_profile_ops_insitu": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),

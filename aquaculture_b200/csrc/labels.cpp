@@ -171,3 +171,82 @@ extern "C" int aq_cage_areas(int square, double w, double h, int x_border, int y
   out[3] = hi;
   return AQ_OK;
 }
+
+// Facility clustering = get_clusters [REF src/cluster_facilities.py:11-15]: sklearn.cluster.DBSCAN(eps, min_samples)
+// .fit(center_points).labels_ on 2-D points (cage centres in metres).  Semantics restated from the published algorithm
+// (Ester et al. 1996) in scikit-learn's conventions: a point's neighbourhood holds every point within eps (inclusive, the
+// point itself included; squared distances dx*dx + dy*dy compared with eps*eps in float64 as the KD-tree query does),
+// core = at least min_samples neighbours, clusters are numbered in order of their lowest-index core point, each cluster
+// is grown completely before the next one starts (so a border point two clusters reach keeps the lower label), noise = -1.
+// Neighbour search: points sorted by the cell of a uniform grid slightly wider than eps; 3 x 3 cells per query.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <vector>
+
+extern "C" int aq_dbscan(const double* xy, int n, double eps, int min_samples, int* labels) {
+  if (n < 0 || (n > 0 && (!xy || !labels)) || !(eps > 0) || min_samples < 1) return AQ_ERR_ARG;
+  if (n == 0) return AQ_OK;
+  double minx = xy[0], miny = xy[1], maxx = xy[0], maxy = xy[1];
+  for (int i = 0; i < n; ++i) {
+    if (!std::isfinite(xy[2 * i]) || !std::isfinite(xy[2 * i + 1])) return AQ_ERR_ARG;
+    minx = std::min(minx, xy[2 * i]); maxx = std::max(maxx, xy[2 * i]);
+    miny = std::min(miny, xy[2 * i + 1]); maxy = std::max(maxy, xy[2 * i + 1]);
+  }
+  const double cell = eps * (1.0 + 1e-9);  // two points within eps are then at most one cell apart despite rounding
+  if ((maxx - minx) / cell > 2e9 || (maxy - miny) / cell > 2e9) return AQ_ERR_ARG;
+  auto key_of = [](int64_t ix, int64_t iy) { return (uint64_t)(ix + 1) << 32 | (uint64_t)(iy + 1); };
+  std::vector<int64_t> cx(n), cy(n);
+  std::vector<std::pair<uint64_t, int>> order(n);
+  for (int i = 0; i < n; ++i) {
+    cx[i] = (int64_t)std::floor((xy[2 * i] - minx) / cell);
+    cy[i] = (int64_t)std::floor((xy[2 * i + 1] - miny) / cell);
+    order[i] = {key_of(cx[i], cy[i]), i};
+  }
+  std::sort(order.begin(), order.end());
+  const double eps2 = eps * eps;
+  // neighbourhoods in CSR form
+  std::vector<size_t> first(n + 1, 0);
+  std::vector<int> nbr;
+  nbr.reserve((size_t)n * 8);
+  for (int i = 0; i < n; ++i) {
+    first[i] = nbr.size();
+    const double x = xy[2 * i], y = xy[2 * i + 1];
+    for (int64_t dx = -1; dx <= 1; ++dx)
+      for (int64_t dy = -1; dy <= 1; ++dy) {
+        const int64_t ix = cx[i] + dx, iy = cy[i] + dy;
+        if (ix < 0 || iy < 0) continue;
+        const uint64_t k = key_of(ix, iy);
+        auto it = std::lower_bound(order.begin(), order.end(), std::make_pair(k, -1));
+        for (; it != order.end() && it->first == k; ++it) {
+          const double ddx = x - xy[2 * it->second], ddy = y - xy[2 * it->second + 1];
+          if (ddx * ddx + ddy * ddy <= eps2) nbr.push_back(it->second);
+        }
+      }
+  }
+  first[n] = nbr.size();
+  std::vector<char> core(n);
+  for (int i = 0; i < n; ++i) {
+    core[i] = (first[i + 1] - first[i]) >= (size_t)min_samples;
+    labels[i] = -1;
+  }
+  int label = 0;
+  std::vector<int> stack;
+  for (int s = 0; s < n; ++s) {
+    if (labels[s] != -1 || !core[s]) continue;
+    int i = s;
+    for (;;) {
+      if (labels[i] == -1) {
+        labels[i] = label;
+        if (core[i])
+          for (size_t k = first[i]; k < first[i + 1]; ++k)
+            if (labels[nbr[k]] == -1) stack.push_back(nbr[k]);
+      }
+      if (stack.empty()) break;
+      i = stack.back();
+      stack.pop_back();
+    }
+    ++label;
+  }
+  return label;  // number of clusters
+}

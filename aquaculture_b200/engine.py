@@ -678,3 +678,14 @@ def cage_areas(square: bool, w: float, h: float, x_border=False, y_border=False)
     if rc < 0:
         raise AquaError(f"aq_cage_areas failed ({rc})")
     return tuple(out)
+
+
+def dbscan_labels(center_points, distance_threshold: float, min_samples: int) -> np.ndarray:
+    """get_clusters [REF src/cluster_facilities.py:11-15]: labels of sklearn's DBSCAN(eps, min_samples) on 2-D points
+    (host C, aq_dbscan); -1 = noise."""
+    pts = np.ascontiguousarray(np.asarray(center_points, np.float64).reshape(-1, 2))
+    labels = np.empty(pts.shape[0], np.int32)
+    rc = _lib.load().aq_dbscan(pts.ctypes.data, pts.shape[0], float(distance_threshold), int(min_samples), labels.ctypes.data)
+    if rc < 0:
+        raise AquaError(f"aq_dbscan failed ({rc})")
+    return labels

@@ -215,6 +215,12 @@ int aq_geocode_label_text(const char* text, int x_offset, int y_offset, const do
  * [REF src/process_yolo/calc_net_areas.py:24-82]; out = (estimate, variance, min, max). */
 int aq_cage_areas(int square, double w, double h, int x_border, int y_border, double out[4]);
 
+/* Facility clustering = get_clusters [REF src/cluster_facilities.py:11-15], i.e. sklearn.cluster.DBSCAN(eps = distance
+ * threshold in metres, min_samples).fit(center_points).labels_: xy = n points (x, y) float64; labels receives n int32
+ * (cluster number in sklearn's numbering, -1 = noise).  Returns the number of clusters or a negative aq_status.
+ * Host only; needs no context. */
+int aq_dbscan(const double* xy, int n, double eps, int min_samples, int* labels);
+
 /* ------------------------------------------------------------------ JPEG tiles */
 /*
  * Decoder for the tiles gdal.Translate -of JPEG writes [REF src/load_data/tile_tifs.py:74] and upstream

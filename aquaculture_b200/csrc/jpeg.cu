@@ -128,53 +128,70 @@ __global__ void __launch_bounds__(IDCT_THREADS) jpeg_idct_kernel(JpegParams p) {
 
 __device__ __forceinline__ unsigned clamp255(int v) { return (unsigned)min(max(v, 0), 255); }
 
-// Four horizontally adjacent pixels per thread (12 output bytes = three 32-bit stores when the row is 4-byte aligned).
+// Eight horizontally adjacent pixels per thread: one 8-byte luma load, chroma through 32-bit loads (4:2:0: the four
+// samples under the pixels + one neighbour each side, for two rows; 4:4:4: 8 bytes per plane), 24 output bytes as three
+// 8-byte streaming stores when rows are 8-byte aligned.  Threads at the right edge (or of narrow images) take the
+// byte-wise path with clamped indices.
 __global__ void __launch_bounds__(256) jpeg_colour_kernel(JpegParams p) {
-  const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  const int y = blockIdx.y, img = blockIdx.z;
-  if (x0 >= p.width) return;
+  const int octs = (p.width + 7) >> 3;   // groups per row; consecutive threads walk a row, then the next one
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = (int)(gid / octs), img = blockIdx.y;
+  if (y >= p.height) return;
+  const int x0 = (int)(gid - (long long)y * octs) * 8;
   const uint8_t* planes = p.planes + (size_t)img * p.planes_per_image;
-  const uint8_t* yrow = planes + (size_t)y * p.luma_pw;
-  const unsigned y4 = *reinterpret_cast<const unsigned*>(yrow + x0);  // planes are padded to whole blocks
-  int cb[4], cr[4];
+  const uint2 yy8 = *reinterpret_cast<const uint2*>(planes + (size_t)y * p.luma_pw + x0);  // planes are padded to whole blocks
+  int cb[8], cr[8];
   if (p.ncomp == 1) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) cb[i] = cr[i] = 128;
+    for (int i = 0; i < 8; ++i) cb[i] = cr[i] = 128;
   } else if (p.hs == 1) {
-    const unsigned b4 = *reinterpret_cast<const unsigned*>(planes + p.luma_plane + (size_t)y * p.chroma_pw + x0);
-    const unsigned r4 = *reinterpret_cast<const unsigned*>(planes + p.luma_plane + p.chroma_plane + (size_t)y * p.chroma_pw + x0);
+    const uint2 b8 = *reinterpret_cast<const uint2*>(planes + p.luma_plane + (size_t)y * p.chroma_pw + x0);
+    const uint2 r8 = *reinterpret_cast<const uint2*>(planes + p.luma_plane + p.chroma_plane + (size_t)y * p.chroma_pw + x0);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { cb[i] = (b4 >> (8 * i)) & 255; cr[i] = (r4 >> (8 * i)) & 255; }
+    for (int i = 0; i < 4; ++i) {
+      cb[i] = (b8.x >> (8 * i)) & 255; cb[i + 4] = (b8.y >> (8 * i)) & 255;
+      cr[i] = (r8.x >> (8 * i)) & 255; cr[i + 4] = (r8.y >> (8 * i)) & 255;
+    }
   } else {
     // triangle filter: 3/4 nearer + 1/4 further sample in each axis; rows / columns beyond the component's real
     // extent (ceil(size / 2)) are replaced by the edge sample
     const int ch = (p.height + 1) >> 1, cw = (p.width + 1) >> 1;
     const int cy = y >> 1;
     const int fy = min(max((y & 1) ? cy + 1 : cy - 1, 0), ch - 1);
-    const int ci = x0 >> 1;
+    const int ci = x0 >> 1;    // multiple of 4
     const bool box = cw <= 2;  // libjpeg filters only components more than two samples wide; narrower ones are replicated
+    const bool interior = ci >= 1 && ci + 4 <= cw - 1;
 #pragma unroll
     for (int pl = 0; pl < 2; ++pl) {
       const uint8_t* base = planes + p.luma_plane + (size_t)pl * p.chroma_plane;
       const uint8_t* near = base + (size_t)cy * p.chroma_pw;
       const uint8_t* far = base + (size_t)fy * p.chroma_pw;
-      int sum[4];
+      int sum[6];  // columns ci - 1 .. ci + 4
+      if (interior) {
+        const unsigned n4 = *reinterpret_cast<const unsigned*>(near + ci), f4 = *reinterpret_cast<const unsigned*>(far + ci);
+        sum[0] = 3 * (int)near[ci - 1] + (int)far[ci - 1];
+        sum[5] = 3 * (int)near[ci + 4] + (int)far[ci + 4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int c = min(max(ci - 1 + j, 0), cw - 1);
-        sum[j] = box ? 4 * (int)near[c] : 3 * (int)near[c] + (int)far[c];
+        for (int j = 0; j < 4; ++j) sum[1 + j] = 3 * (int)((n4 >> (8 * j)) & 255) + (int)((f4 >> (8 * j)) & 255);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+          const int c = min(max(ci - 1 + j, 0), cw - 1);
+          sum[j] = box ? 4 * (int)near[c] : 3 * (int)near[c] + (int)far[c];
+        }
       }
       int* o = pl ? cr : cb;
-      o[0] = (3 * sum[1] + (box ? sum[1] : sum[0]) + 8) >> 4;
-      o[1] = (3 * sum[1] + (box ? sum[1] : sum[2]) + 7) >> 4;
-      o[2] = (3 * sum[2] + (box ? sum[2] : sum[1]) + 8) >> 4;
-      o[3] = (3 * sum[2] + (box ? sum[2] : sum[3]) + 7) >> 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {  // chroma column ci + j -> pixels 2j, 2j + 1
+        o[2 * j] = (3 * sum[1 + j] + (box ? sum[1 + j] : sum[j]) + 8) >> 4;
+        o[2 * j + 1] = (3 * sum[1 + j] + (box ? sum[1 + j] : sum[2 + j]) + 7) >> 4;
+      }
     }
   }
-  unsigned char px[12];
+  unsigned char px[24];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int yy = (y4 >> (8 * i)) & 255;
+  for (int i = 0; i < 8; ++i) {
+    const int yy = ((i < 4 ? yy8.x : yy8.y) >> (8 * (i & 3))) & 255;
     const int u = cb[i] - 128, v = cr[i] - 128;
     const unsigned r = clamp255(yy + ((91881 * v + 32768) >> 16));
     const unsigned g = clamp255(yy + ((-22554 * u + (-46802 * v + 32768)) >> 16));
@@ -184,13 +201,15 @@ __global__ void __launch_bounds__(256) jpeg_colour_kernel(JpegParams p) {
     px[3 * i + 2] = p.bgr ? r : bl;
   }
   uint8_t* dst = p.out + ((size_t)img * p.height + y) * (size_t)p.width * 3 + (size_t)x0 * 3;
-  if ((p.width & 3) == 0) {
-    unsigned* d32 = reinterpret_cast<unsigned*>(dst);
+  if ((p.width & 7) == 0) {  // whole group inside the row, rows 8-byte aligned
+    unsigned w32[6];
 #pragma unroll
-    for (int i = 0; i < 3; ++i)
-      __stcs(d32 + i, px[4 * i] | (px[4 * i + 1] << 8) | (px[4 * i + 2] << 16) | ((unsigned)px[4 * i + 3] << 24));
+    for (int i = 0; i < 6; ++i) w32[i] = px[4 * i] | (px[4 * i + 1] << 8) | (px[4 * i + 2] << 16) | ((unsigned)px[4 * i + 3] << 24);
+    uint2* d64 = reinterpret_cast<uint2*>(dst);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) __stcs(d64 + i, make_uint2(w32[2 * i], w32[2 * i + 1]));
   } else {
-    const int nb = min(4, p.width - x0) * 3;
+    const int nb = min(8, p.width - x0) * 3;
     for (int i = 0; i < nb; ++i) dst[i] = px[i];
   }
 }
@@ -216,8 +235,8 @@ cudaError_t launch_jpeg_reconstruct(const JpegParams& p, cudaStream_t stream) {
   const unsigned gx = (unsigned)((p.blocks_per_image + IDCT_BLOCKS - 1) / IDCT_BLOCKS);
   if (p.coef) jpeg_idct_kernel<false><<<dim3(gx, p.n), IDCT_THREADS, 0, stream>>>(p);
   else jpeg_idct_kernel<true><<<dim3(gx, p.n), IDCT_THREADS, 0, stream>>>(p);
-  const int quads = (p.width + 3) / 4;
-  jpeg_colour_kernel<<<dim3((quads + 255) / 256, p.height, p.n), 256, 0, stream>>>(p);
+  const long long groups = (long long)((p.width + 7) / 8) * p.height;
+  jpeg_colour_kernel<<<dim3((unsigned)((groups + 255) / 256), p.n), 256, 0, stream>>>(p);
   return cudaGetLastError();
 }
 

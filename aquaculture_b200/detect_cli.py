@@ -218,12 +218,27 @@ def run(opt, argv) -> int:
     from . import jpeg
     cv2.setNumThreads(1)
     device_jpeg = opt.jpeg_decode in ("device", "hybrid") and opt.raster_tile <= 0
+    raster_jpeg = opt.jpeg_decode == "device" and opt.raster_tile > 0  # a .jpeg raster is decoded straight into device memory
     n_host_decoded = [0]
 
     def load(item):
         kind, v = item
         if kind == "synthetic":
             return tiles.synthetic_tile(v, opt.synthetic_size, opt.synthetic_size, opt.seed)
+        if raster_jpeg and v.rsplit(".", 1)[-1].lower() in ("jpg", "jpeg"):
+            with open(v, "rb") as fh:
+                blob = np.frombuffer(fh.read(), np.uint8)
+            try:
+                info = jpeg.probe(blob)
+                if info.restart_interval == 0:
+                    return engine.RawJpeg(blob, info)
+            except jpeg.JpegUnsupported:
+                pass
+            n_host_decoded[0] += 1
+            im = cv2.imdecode(blob, cv2.IMREAD_COLOR)
+            if im is None:
+                raise SystemExit(f"Image Not Found {v}")
+            return im
         if device_jpeg and v.rsplit(".", 1)[-1].lower() in ("jpg", "jpeg"):
             with open(v, "rb") as fh:
                 blob = np.frombuffer(fh.read(), np.uint8)
@@ -324,14 +339,23 @@ def run(opt, argv) -> int:
         bottom strips (the reference's tiler emits them as smaller tiles) are cropped on the host and batched by shape."""
         nonlocal seen, n_files, n_dets
         T = opt.raster_tile
-        H, W = im.shape[:2]
         finish()  # detect_windows uses the detector's result slot 0 and synchronises
+        raster = None
+        if isinstance(im, engine.RawJpeg):  # decoded on the device; pixels come to the host only for ragged strips
+            t0 = time.perf_counter()
+            raster = engine.decode_jpeg_raster(detector_for(net_shape_for(T, T, imgsz)).ctx, im.blob)
+            dt[0] += time.perf_counter() - t0
+            H, W = raster.shape[:2]
+            im = raster.cpu().numpy() if (H % T or W % T) else None
+        else:
+            H, W = im.shape[:2]
         wins = engine.window_grid(H, W, T)
         if wins:
             net_hw = net_shape_for(T, T, imgsz)
             det = detector_for(net_hw)
             t0 = time.perf_counter()
-            raster = torch.from_numpy(np.ascontiguousarray(im)).to(f"cuda:{device}")
+            if raster is None:
+                raster = torch.from_numpy(np.ascontiguousarray(im)).to(f"cuda:{device}")
             dt[0] += time.perf_counter() - t0
             for k0 in range(0, len(wins), B):
                 nb = min(B, len(wins) - k0)

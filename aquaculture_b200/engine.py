@@ -517,6 +517,24 @@ class RawJpeg:
         self.key = ("jpegscan", info.height, info.width, info.ncomp, info.hs)
 
 
+def decode_jpeg_raster(ctx: Context, blob) -> torch.Tensor:
+    """One (large) JPEG file decoded entirely on the device into a uint8 (H, W, 3) BGR cuda tensor -- the raster
+    `TileDetector.detect_windows` cuts its windows from, so a .jpeg raster never exists as pixels on the host.
+    Synchronises.  Raises jpeg.JpegUnsupported for variants without an all-device path."""
+    from . import jpeg
+    info, scan, nbytes, tables, quant = jpeg.scan_prepare(blob)
+    out = torch.empty(info.height, info.width, 3, dtype=torch.uint8, device=f"cuda:{ctx.device}")
+    torch.cuda.synchronize(ctx.device)
+    off, length, status = np.zeros(1, np.uint64), np.array([nbytes], np.uint32), np.full(1, -99, np.int32)
+    ctx.call("aq_jpeg_decode_device", C.c_void_p(scan.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(length.ctypes.data), scan.size,
+             C.c_void_p(tables.ctypes.data), C.c_void_p(quant.ctypes.data), 1, info.width, info.height, info.ncomp, info.hs, 1,
+             C.c_void_p(out.data_ptr()), C.c_void_p(status.ctypes.data), None)
+    ctx.sync()
+    if status[0] != 0:
+        raise _lib.AquaError(f"aq_jpeg_decode_device: corrupt JPEG scan (status {int(status[0])})")
+    return out
+
+
 def prepare_jpeg_batch(det: "TileDetector", blobs: Sequence, n_threads: int = 8):
     """Host side of the all-device decoder for a whole batch in ONE library call (aq_jpeg_scan_prepare_batch: marker walk +
     unstuffing on C threads, written straight into a pinned staging area of `det`).  blobs: bytes or uint8 arrays of

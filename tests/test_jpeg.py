@@ -272,3 +272,28 @@ def test_cli_device_jpeg_equals_host_decode(tmp_path, monkeypatch, capsys):
     ld = {p.name: p.read_text() for p in (tmp_path / "runs" / "dev" / "labels").glob("*.txt")}
     lh = {p.name: p.read_text() for p in (tmp_path / "runs" / "host" / "labels").glob("*.txt")}
     assert len(lh) >= 5 and ld == lh and lhy == lh
+
+
+@pytest.mark.gpu
+def test_cli_jpeg_raster_decoded_on_device(tmp_path, monkeypatch):
+    """--raster-tile on a .jpeg raster: the raster is decoded on the GPU and its windows are cut there (rows f-1 + f-3
+    together); labels equal those of the cv2.imread run, ragged right strip included."""
+    from aquaculture_b200 import detect_cli as cli
+    from aquaculture_b200 import tiles as T
+    monkeypatch.setenv("AQUA_AUTOTUNE", "0")
+    Tl = 512
+    parts = T.synthetic_tiles(range(6), Tl, Tl, seed=12)
+    raster = np.concatenate([np.concatenate(list(parts[0:3]), axis=1), np.concatenate(list(parts[3:6]), axis=1)], axis=0)
+    raster = cv2.GaussianBlur(np.ascontiguousarray(raster[:, :Tl * 2 + 200]), (0, 0), 1.5)   # 1024 x 1224, compressible
+    rdir = tmp_path / "raster"
+    rdir.mkdir()
+    cv2.imwrite(str(rdir / "BIG2020_7.jpeg"), raster, [cv2.IMWRITE_JPEG_QUALITY, 90])
+    common = ["--weights", "synthetic", "--source", str(rdir), "--nosave", "--save-txt", "--save-conf", "--batch-size", "4",
+              "--project", str(tmp_path / "runs"), "--raster-tile", str(Tl)]
+    assert cli.main(common + ["--name", "dev"]) == 0
+    assert cli.main(common + ["--name", "host", "--jpeg-decode", "host"]) == 0
+    ld = {p.name: p.read_text() for p in (tmp_path / "runs" / "dev" / "labels").glob("*.txt")}
+    lh = {p.name: p.read_text() for p in (tmp_path / "runs" / "host" / "labels").glob("*.txt")}
+    assert len(lh) >= 1 and ld == lh
+    got = engine.decode_jpeg_raster(engine.Context(0), np.fromfile(str(rdir / "BIG2020_7.jpeg"), np.uint8))
+    assert np.array_equal(got.cpu().numpy(), cv2.imread(str(rdir / "BIG2020_7.jpeg")))

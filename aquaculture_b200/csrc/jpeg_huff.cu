@@ -35,22 +35,34 @@ __device__ __forceinline__ uint32_t sub_limit(const HuffParams& p, uint32_t tota
   return (uint32_t)(l < total_bits ? l : total_bits);
 }
 
-// Steps 1 + 2.  CTA (x, tile) owns subsequences [x * HT, (x + 1) * HT) of the tile.  first != 0: decode from the guessed
-// states, then relax inside the CTA until nothing changes; first == 0: relax again with the boundary state the previous
-// CTA left in global memory.  Launching it (CTAs per tile) times reaches the fixed point whatever the data: launch k
-// finds CTA k-1's states final.
+// Steps 1 + 2.  CTA (x, tile) owns the REAL = HT - GHOST subsequences [x * REAL, (x + 1) * REAL) of the tile; its first
+// GHOST threads re-decode the GHOST subsequences in front of that range as a warm-up (first launch only, results not
+// stored), so that the CTA's first own subsequence usually starts from a state that has already fallen into step.
+// first != 0: decode from the guessed states, then relax inside the CTA until nothing changes; first == 0: relax again
+// from the boundary state the previous CTA left in global memory -- a CTA whose boundary did not move returns at
+// once.  Launching it (CTAs per tile) times reaches the fixed point whatever the data: launch k finds CTA k-1 final.
+constexpr int GHOST = 8, REAL = HT - GHOST;
+
 __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int first) {
   __shared__ Shared sh;
   __shared__ unsigned long long s_end[HT];
-  const int tile = blockIdx.y, i = blockIdx.x * HT + threadIdx.x;
+  const int tile = blockIdx.y, t = threadIdx.x;
+  const int i = (int)blockIdx.x * REAL - GHOST + t;
   const uint32_t total_bits = p.scan_bytes[tile] * 8u;
   const int nsub = (int)((total_bits + p.sub_bits - 1) / p.sub_bits);
-  if (blockIdx.x * HT >= nsub) return;
+  if ((int)blockIdx.x * REAL >= nsub) return;
+  const bool real = t >= GHOST;
+  const bool live = i >= 0 && i < nsub && (real || first);
+  const size_t slot = (size_t)tile * p.nsub_max + (i >= 0 ? i : 0);
+  unsigned long long boundary = 0;
+  if (!first) {
+    const bool at_boundary = t == GHOST && live && i > 0;
+    if (at_boundary) boundary = p.end[slot - 1];
+    if (!__syncthreads_or(at_boundary && boundary != p.start[slot])) return;  // the previous CTA's last state did not move
+  }
   load_tables(sh, p, tile);
   const uint32_t* words = reinterpret_cast<const uint32_t*>(p.scans + p.scan_off[tile]);
   const uint32_t slot_comp = pack_slot_comp(p.geo.ncomp, p.geo.hs, p.geo.vs);
-  const size_t slot = (size_t)tile * p.nsub_max + i;
-  const bool live = i < nsub;
   unsigned long long my_start = 0, my_end = 0;
   int my_nblk = 0;
   if (live) {
@@ -65,14 +77,16 @@ __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int fi
       my_nblk = p.nblk[slot];
     }
   }
-  // the previous CTA's last state: only meaningful from the second launch on (launch k finds CTA k-1 final)
-  const unsigned long long boundary = (!first && threadIdx.x == 0 && i > 0 && live) ? p.end[slot - 1] : my_start;
-  s_end[threadIdx.x] = my_end;
+  // where a thread's predecessor state comes from: the neighbouring thread (a warm-up thread included, first launch),
+  // or -- first own subsequence in later launches -- the previous CTA's final state
+  const bool from_boundary = !first && t == GHOST && live && i > 0;
+  const bool from_neighbour = live && i > 0 && t > 0 && !from_boundary;
+  s_end[t] = my_end;
   __syncthreads();
   for (;;) {
     bool changed = false;
-    if (live && i > 0) {
-      const unsigned long long prev = threadIdx.x == 0 ? boundary : s_end[threadIdx.x - 1];
+    if (from_boundary || from_neighbour) {
+      const unsigned long long prev = from_boundary ? boundary : s_end[t - 1];
       if (prev != my_start) {
         my_start = prev;
         State st = unpack_state(prev);
@@ -81,11 +95,11 @@ __global__ void __launch_bounds__(HT) jpeg_huff_sync_kernel(HuffParams p, int fi
         changed = true;
       }
     }
-    __syncthreads();  // every s_end[tid - 1] has been read
-    if (changed) s_end[threadIdx.x] = my_end;
+    __syncthreads();  // every s_end[t - 1] has been read
+    if (changed) s_end[t] = my_end;
     if (!__syncthreads_or(changed)) break;
   }
-  if (live) {
+  if (live && real) {
     p.start[slot] = my_start;
     p.end[slot] = my_end;
     p.nblk[slot] = my_nblk;
@@ -193,10 +207,10 @@ cudaError_t launch_jpeg_huffman(HuffParams p, void* state_scratch, int n, int ns
   p.nblk = (int*)(p.base + cells);
   p.status = p.nblk + cells;
   p.nsub_max = nsub_max;
-  const int ctas = (nsub_max + HT - 1) / HT;
+  const int ctas = (nsub_max + HT - 1) / HT, sync_ctas = (nsub_max + REAL - 1) / REAL;
   cudaError_t e = cudaMemsetAsync(p.coef, 0, (size_t)n * p.geo.total_blocks * 64 * sizeof(int16_t), stream);
   if (e != cudaSuccess) return e;
-  for (int k = 0; k < ctas; ++k) jpeg_huff_sync_kernel<<<dim3(ctas, n), HT, 0, stream>>>(p, k == 0);
+  for (int k = 0; k < sync_ctas; ++k) jpeg_huff_sync_kernel<<<dim3(sync_ctas, n), HT, 0, stream>>>(p, k == 0);
   jpeg_huff_scan_kernel<<<n, HT, 0, stream>>>(p);
   jpeg_huff_write_kernel<<<dim3(ctas, n), HT, 0, stream>>>(p);
   jpeg_huff_dc_kernel<<<dim3(3, n), HT, 0, stream>>>(p);

@@ -1634,12 +1634,13 @@ int aq_jpeg_decode_device(aq_ctx* c, const uint8_t* scans, const uint64_t* scan_
   auto al = [](size_t b) { return (b + 255) / 256 * 256; };
   // scratch on the compute side: planes | dense coefficients | decoder states
   const size_t planes_b = al((size_t)n * p.planes_per_image), coef_b = al((size_t)n * p.blocks_per_image * 64 * sizeof(int16_t));
+  const size_t dc_b = al((size_t)n * p.blocks_per_image * sizeof(int));
   const size_t state_b = al(jpeg_huff_state_bytes(n, nsub_max));
-  if (planes_b + coef_b + state_b > c->jpeg_bytes) {
+  if (planes_b + coef_b + dc_b + state_b > c->jpeg_bytes) {
     if (c->jpeg_scratch) { CU_CHECK(c, cudaDeviceSynchronize()); cudaFree(c->jpeg_scratch); }
     c->jpeg_scratch = nullptr;
     c->jpeg_bytes = 0;
-    const size_t grow = planes_b + coef_b + state_b + state_b / 2;
+    const size_t grow = planes_b + coef_b + dc_b + state_b + state_b / 2;
     CU_CHECK(c, cudaMalloc(&c->jpeg_scratch, grow));
     c->jpeg_bytes = grow;
   }
@@ -1679,11 +1680,13 @@ int aq_jpeg_decode_device(aq_ctx* c, const uint8_t* scans, const uint64_t* scan_
   uint8_t* scratch = (uint8_t*)c->jpeg_scratch;
   h.scans = d_scans; h.scan_off = d_off; h.scan_bytes = d_len; h.tables = d_tab;
   h.coef = (int16_t*)(scratch + planes_b);
-  void* state = scratch + planes_b + coef_b;
+  h.dc = (int*)(scratch + planes_b + coef_b);
+  void* state = scratch + planes_b + coef_b + dc_b;
   cudaError_t e = launch_jpeg_huffman(h, state, n, nsub_max, s);
   if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_decode_device (entropy decoding): %s", cudaGetErrorString(e));
   p.planes = scratch;
   p.coef = h.coef;
+  p.dc = h.dc; p.dc_bpm = h.geo.bpm; p.dc_mcus_x = h.geo.mcus_x;
   p.quant = d_quant;
   e = launch_jpeg_reconstruct(p, s);
   if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "jpeg_decode_device (reconstruction): %s", cudaGetErrorString(e));

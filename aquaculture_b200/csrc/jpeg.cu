@@ -96,6 +96,15 @@ __global__ void __launch_bounds__(IDCT_THREADS) jpeg_idct_kernel(JpegParams p) {
     const unsigned short* q = qs + comp * 64 + t * 8;
 #pragma unroll
     for (int i = 0; i < 8; ++i) w[t * WS_PITCH + i] = (int)c[i] * (int)q[i];
+    if (p.dc && t == 0) {
+      // the block's place in decode order: MCU (my, mx), slot inside the MCU (luma blocks row-major, then Cb, Cr)
+      const int by = (int)(b / bw), bx = (int)(b - (long long)by * bw);
+      const int v = comp == 0 ? p.hs : 1;
+      const int my = by / v, mx = bx / v;
+      const int slot = comp == 0 ? (by - my * v) * v + (bx - mx * v) : p.hs * p.hs + comp - 1;
+      const long long g = ((long long)my * p.dc_mcus_x + mx) * p.dc_bpm + slot;
+      w[0] = p.dc[(size_t)img * p.blocks_per_image + g] * (int)q[0];
+    }
   }
   __syncwarp();
   int s[8], o[8];

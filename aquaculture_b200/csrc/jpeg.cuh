@@ -13,6 +13,10 @@ struct JpegParams {
   const uint32_t* block_desc;
   const uint32_t* entries;
   const unsigned long long* tile_entry_base;
+  // optional (all-device decoder): DC coefficients kept apart in decode order, dc[tile][mcu * bpm + slot]; when set they
+  // replace coefficient 0 of every dense block
+  const int* dc;
+  int dc_bpm, dc_mcus_x;
   uint8_t* planes;         // scratch: n x planes_per_image reconstructed samples (block-padded planes)
   uint8_t* out;            // (n, height, width, 3) uint8
   int n, width, height, ncomp, hs, bgr;

@@ -156,15 +156,22 @@ __global__ void __launch_bounds__(HT) jpeg_huff_write_kernel(HuffParams p) {
   long long blk = p.base[slot];
   const uint32_t lim = sub_limit(p, total_bits, i);
   int16_t* tile_coef = p.coef + (size_t)tile * p.geo.total_blocks * 64;
+  int* tile_dc = p.dc + (size_t)tile * p.geo.total_blocks;
   BitWindow bits;
   bits.init(words, st.p);
   while (st.p < lim && blk < p.geo.total_blocks) {
     int16_t* dst = tile_coef + block_address(p.geo, blk) * 64;
-    if (decode_one(bits, sh.tabs, slot_comp, p.geo.bpm, st, [&](int z, int v) { dst[c_zigzag[z]] = (int16_t)v; })) ++blk;
+    int* dcd = tile_dc + blk;  // DC differences stay in decode order: the prediction scan below runs over a compact array
+    if (decode_one(bits, sh.tabs, slot_comp, p.geo.bpm, st, [&](int z, int v) {
+          if (z == 0) *dcd = v;
+          else dst[c_zigzag[z]] = (int16_t)v;
+        }))
+      ++blk;
   }
 }
 
-// Step 5: DC prediction undone by a scan over each component's blocks in decode order.  CTA (component, tile).
+// Step 5: DC prediction undone by a scan over each component's blocks in decode order (compact int32 array; the IDCT
+// kernel picks the values up from there).  CTA (component, tile).
 __global__ void __launch_bounds__(HT) jpeg_huff_dc_kernel(HuffParams p) {
   __shared__ int s_part[HT];
   const int c = blockIdx.x, tile = blockIdx.y;
@@ -173,8 +180,8 @@ __global__ void __launch_bounds__(HT) jpeg_huff_dc_kernel(HuffParams p) {
   const int per_mcu = c == 0 ? (g.ncomp == 1 ? 1 : g.hs * g.vs) : 1, first = c == 0 ? 0 : g.hs * g.vs + c - 1;
   const long long n = (long long)g.mcus_x * g.mcus_y * per_mcu;
   const long long per = (n + HT - 1) / HT, lo = min((long long)threadIdx.x * per, n), hi = min(lo + per, n);
-  int16_t* tile_coef = p.coef + (size_t)tile * g.total_blocks * 64;
-  auto addr = [&](long long j) { return tile_coef + block_address(g, (j / per_mcu) * g.bpm + first + (int)(j % per_mcu)) * 64; };
+  int* tile_dc = p.dc + (size_t)tile * g.total_blocks;
+  auto addr = [&](long long j) { return tile_dc + (j / per_mcu) * g.bpm + first + (int)(j % per_mcu); };
   int sum = 0;
   for (long long j = lo; j < hi; ++j) sum += *addr(j);
   s_part[threadIdx.x] = sum;
@@ -187,9 +194,9 @@ __global__ void __launch_bounds__(HT) jpeg_huff_dc_kernel(HuffParams p) {
   }
   int run = s_part[threadIdx.x] - sum;
   for (long long j = lo; j < hi; ++j) {
-    int16_t* a = addr(j);
+    int* a = addr(j);
     run += *a;
-    *a = (int16_t)run;
+    *a = (int)(short)run;  // coefficients are 16-bit in the format
   }
 }
 
@@ -209,6 +216,7 @@ cudaError_t launch_jpeg_huffman(HuffParams p, void* state_scratch, int n, int ns
   p.nsub_max = nsub_max;
   const int ctas = (nsub_max + HT - 1) / HT, sync_ctas = (nsub_max + REAL - 1) / REAL;
   cudaError_t e = cudaMemsetAsync(p.coef, 0, (size_t)n * p.geo.total_blocks * 64 * sizeof(int16_t), stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(p.dc, 0, (size_t)n * p.geo.total_blocks * sizeof(int), stream);
   if (e != cudaSuccess) return e;
   for (int k = 0; k < sync_ctas; ++k) jpeg_huff_sync_kernel<<<dim3(sync_ctas, n), HT, 0, stream>>>(p, k == 0);
   jpeg_huff_scan_kernel<<<n, HT, 0, stream>>>(p);

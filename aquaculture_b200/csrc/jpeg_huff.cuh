@@ -12,7 +12,8 @@ struct HuffParams {
   const unsigned long long* scan_off;   // per tile: byte offset of its segment in `scans` (multiple of 4)
   const uint32_t* scan_bytes;           // per tile: segment length in bytes
   const uint8_t* tables;                // per tile: kTablesPerTile x DevHuff
-  int16_t* coef;                        // out: n x total_blocks x 64 dense coefficients (planes Y | Cb | Cr)
+  int16_t* coef;                        // out: n x total_blocks x 64 dense coefficients (planes Y | Cb | Cr), DC excluded
+  int* dc;                              // out: n x total_blocks DC coefficients in decode order (mcu * bpm + slot)
   aqj::Geo geo;
   int sub_bits;                         // subsequence length in bits (multiple of 32)
   // set by launch_jpeg_huffman from the state scratch

@@ -47,6 +47,9 @@ bool build_table(HuffTable& t) {
   memset(t.vals + n, 0, sizeof t.vals - (size_t)n);
   for (int l = 1; l <= 16; ++l) {
     if (t.bits[l]) {
+      // over-subscribed lengths are rejected BEFORE the lookup table is written: `first + f` below would run far
+      // past `look` for a crafted DHT (e.g. bits[1] = 255)
+      if (code + t.bits[l] > (1u << l)) return false;
       t.valoff[l] = p - (int32_t)code;
       for (int i = 0; i < t.bits[l]; ++i, ++p, ++code) {
         if (l <= kLookBits) {

@@ -165,7 +165,36 @@ def spawn_ranks(devices: List[int], argv: List[str]) -> int:
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(len(devices)), LOCAL_RANK=str(d), MASTER_ADDR="127.0.0.1",
                    MASTER_PORT=str(port), AQ_SPAWNED="1")
         procs.append(subprocess.Popen([sys.executable, "-m", "aquaculture_b200.detect_cli"] + argv, env=env))
-    return max(p.wait() for p in procs)
+    return ranks_exit_code([p.wait() for p in procs])
+
+
+def ranks_exit_code(rcs: List[int]) -> int:
+    """Exit status of a multi-rank run: 0 only if EVERY rank exited 0.  A rank killed by a signal has a negative
+    returncode (-11, -9 ...), which a plain max() would hide behind the other ranks' zeros -- its shard of label files
+    would be missing and the run would still look fine; such a code is reported the shell way (128 + signal)."""
+    bad = [(r, rc) for r, rc in enumerate(rcs) if rc != 0]
+    for r, rc in bad:
+        print(f"detect.py (B200 path): rank {r} " + (f"was killed by signal {-rc}" if rc < 0 else f"exited with status {rc}"),
+              file=sys.stderr)
+    if not bad:
+        return 0
+    rc = bad[0][1]
+    return rc if rc > 0 else 128 - rc
+
+
+def resolve_run_dir(opt, rank: int, world: int, dist=None) -> Path:
+    """The run directory `<project>/<name>{,2,3..}` [upstream increment_path].  Under an external launcher (torchrun:
+    WORLD_SIZE > 1, not self-spawned) rank 0 resolves it once and broadcasts it, so that every rank writes into the same
+    fresh expN -- resolving it per rank would race, and reusing an existing directory would APPEND to the previous run's
+    label files (aq_format_labels opens them with "a", as upstream does)."""
+    if world == 1 or "AQ_SPAWNED" in os.environ:
+        # self-spawned ranks were handed the parent's already-resolved directory with --exist-ok
+        return increment_path(Path(opt.project) / opt.name, exist_ok=opt.exist_ok)
+    box = [str(increment_path(Path(opt.project) / opt.name, exist_ok=opt.exist_ok)) if rank == 0 else None]
+    if rank == 0:
+        Path(box[0]).mkdir(parents=True, exist_ok=True)  # taken before any other launch can pick the same name
+    dist.broadcast_object_list(box, src=0)
+    return Path(box[0])
 
 
 def run(opt, argv) -> int:
@@ -187,7 +216,12 @@ def run(opt, argv) -> int:
     from . import engine, tiles, weights
 
     imgsz = tuple(check_img_size(opt.imgsz))
-    save_dir = increment_path(Path(opt.project) / opt.name, exist_ok=opt.exist_ok or world > 1)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(device)
+        dist.init_process_group(os.environ.get("AQ_DIST_BACKEND", "nccl"), device_id=torch.device("cuda", device))
+    save_dir = resolve_run_dir(opt, rank, world, dist)
     label_dir = save_dir / "labels"
     if opt.save_txt:
         label_dir.mkdir(parents=True, exist_ok=True)
@@ -232,8 +266,8 @@ def run(opt, argv) -> int:
                 info = jpeg.probe(blob)
                 if info.restart_interval == 0:
                     return engine.RawJpeg(blob, info)
-            except jpeg.JpegUnsupported:
-                pass
+            except (jpeg.JpegUnsupported, engine.AquaError):
+                pass  # a variant without a device path, or a file the strict marker walk rejects: libjpeg decides
             n_host_decoded[0] += 1
             im = cv2.imdecode(blob, cv2.IMREAD_COLOR)
             if im is None:
@@ -249,8 +283,10 @@ def run(opt, argv) -> int:
                         return engine.RawJpeg(blob, info)
                     # restart intervals re-align the stream: Huffman on the host for such a file
                 return engine.entropy_decode_file(blob)  # host half: markers + Huffman (C, GIL released)
-            except jpeg.JpegUnsupported:
-                n_host_decoded[0] += 1  # e.g. progressive: decoded on the host like upstream does, and reported below
+            except (jpeg.JpegUnsupported, engine.AquaError):
+                # progressive / 4:2:2 / CMYK, or a file the strict marker walk rejects (stray bytes between segments, EOI
+                # oddities): decoded on the host like upstream does -- libjpeg tolerates what it can -- and reported below
+                n_host_decoded[0] += 1
                 im = cv2.imdecode(blob, cv2.IMREAD_COLOR)
                 if im is None:
                     raise SystemExit(f"Image Not Found {v}")
@@ -278,19 +314,33 @@ def run(opt, argv) -> int:
     pos = 0
     pending = {}  # (h0, w0) -> list of (image, stem)
 
-    scan_status = {}  # result slot -> (pinned per-tile decoder status, stems) of an all-device JPEG batch in flight
-    deferred = []  # the batch in flight: (detector, ticket, group, shape0, net_hw)
+    deferred = []  # the batch in flight: (detector, ticket, group, shape0, net_hw, scan) -- scan = (pinned per-tile decoder
+                   # status, blobs) of an all-device JPEG batch, else None
 
     def finish():
         nonlocal seen, n_files, n_dets
         if not deferred:
             return
-        det, ticket, group, shape0, net_hw = deferred.pop()
+        det, ticket, group, shape0, net_hw, scan = deferred.pop()
         t1 = time.perf_counter()
         res = det.detect_wait(ticket)
-        st = scan_status.pop(ticket[0], None)
-        if st is not None and st[0].any():
-            raise SystemExit("detect.py (B200 path): corrupt JPEG scan in " + ", ".join(s for s, v in zip(st[1], st[0]) if v))
+        if scan is not None and scan[0].any():
+            # the device decoder reported these scans as damaged (truncated, bad code): they go through cv2 / libjpeg, which
+            # pads or warns and still returns pixels where it can -- what upstream's cv2.imread would have done
+            bad = [i for i, v in enumerate(scan[0]) if v]
+            redo = []
+            for i in bad:
+                im = cv2.imdecode(scan[1][i], cv2.IMREAD_COLOR)
+                if im is None or im.shape[:2] != tuple(shape0):
+                    raise SystemExit(f"Image Not Found {group[i][1]} (corrupt JPEG scan, device status {int(scan[0][i])})")
+                redo.append(im)
+            n_host_decoded[0] += len(bad)
+            print(f"WARNING: {len(bad)} damaged JPEG scan(s) re-decoded with cv2: " + ", ".join(group[i][1] for i in bad), file=sys.stderr)
+            res = engine.Detections(res.dets.copy(), res.counts.copy())
+            fix = det.detect(torch.from_numpy(np.stack(redo)).pin_memory(), bgr=True)  # into the (copied) slot of this batch
+            det._slot ^= 1  # the batch submitted after this one keeps its result slot; alternation continues from there
+            for k, i in enumerate(bad):
+                res.dets[i], res.counts[i] = fix.dets[k], fix.counts[k]
         if opt.save_txt:
             paths = [str(label_dir / (g[1] + ".txt")) for g in group]
             n_files += engine.write_labels(res, net_hw, [shape0] * len(group), paths, save_conf=opt.save_conf,
@@ -313,6 +363,7 @@ def run(opt, argv) -> int:
         net_hw = net_shape_for(h0, w0, imgsz)
         det = detector_for(net_hw)
         t0 = time.perf_counter()
+        scan = None
         if is_jpeg:
             desc, ent, base, quant = det.jpeg_staging(len(group), group[0][0].info.coef_count, sum(g[0].entries.size for g in group))
             total = engine.pack_jpeg_tiles([g[0] for g in group], desc, ent, base, quant, pool=pack_pool)
@@ -325,14 +376,14 @@ def run(opt, argv) -> int:
                 raise SystemExit(f"detect.py (B200 path): {e} (batch starting at {group[0][1]})")
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit_jpeg_scans(sc, off, ln, total, tab, quant, status, w0, h0, ncomp, hs)
-            scan_status[ticket[0]] = (status, [g[1] for g in group])
+            scan = (status, [g[0].blob for g in group])
         else:
             batch = det.pinned_input(len(group), h0, w0)
             np.stack([g[0] for g in group], out=batch.numpy())
             dt[0] += time.perf_counter() - t0
             ticket = det.detect_submit(batch, bgr=True)
         finish()
-        deferred.append((det, ticket, [(None, g[1]) for g in group], shape0, net_hw))
+        deferred.append((det, ticket, [(None, g[1]) for g in group], shape0, net_hw, scan))
 
     def run_raster(im, stem):
         """Windows of one raster: full TxT windows are cut, letterboxed and measured on the device; the ragged right /
@@ -414,9 +465,6 @@ def run(opt, argv) -> int:
     # ---- the one collective: gather per-rank counters (NCCL), rank 0 prints the summary
     totals = [seen, n_files, n_dets]
     if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(device)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
         t = torch.tensor(totals, dtype=torch.int64, device="cuda")
         allc = [torch.zeros_like(t) for _ in range(world)]
         dist.all_gather(allc, t)

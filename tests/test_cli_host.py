@@ -112,6 +112,41 @@ def test_counter_gather_gloo_world2(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
 
 
+def test_ranks_exit_code_reports_signals_and_failures(capsys):
+    """A rank killed by a signal (negative returncode) must not hide behind the other ranks' zeros."""
+    assert cli.ranks_exit_code([0, 0, 0, 0]) == 0
+    assert cli.ranks_exit_code([0, -11, 0, 0]) == 139
+    assert cli.ranks_exit_code([0, 0, -9]) == 137
+    assert cli.ranks_exit_code([0, 3, 0]) == 3
+    assert cli.ranks_exit_code([2, -11]) == 2
+    err = capsys.readouterr().err
+    assert "rank 1 was killed by signal 11" in err and "rank 1 exited with status 3" in err
+
+
+def test_run_dir_resolved_once_under_a_launcher_gloo_world2(tmp_path):
+    """Under torchrun rank 0 resolves <project>/<name>N once and broadcasts it: both ranks get the same FRESH directory
+    (an existing exp is never appended to), on 2 ranks over gloo."""
+    (tmp_path / "runs" / "exp").mkdir(parents=True)
+    script = tmp_path / "r.py"
+    script.write_text(
+        "import os, sys, torch.distributed as dist\n"
+        "sys.path.insert(0, %r)\n"
+        "from aquaculture_b200 import detect_cli as cli\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "opt = cli.parse_opt(['--weights', 'synthetic', '--nosave', '--save-txt', '--project', %r, '--name', 'exp'])\n"
+        "d = cli.resolve_run_dir(opt, r, w, dist)\n"
+        "box = [None, None]\n"
+        "dist.all_gather_object(box, str(d))\n"
+        "assert box[0] == box[1] and box[0].endswith('exp2') and os.path.isdir(box[0]), box\n"
+        "dist.destroy_process_group()\n" % (ROOT, str(tmp_path / "runs")))
+    env = {k: v for k, v in os.environ.items() if k != "AQ_SPAWNED"}
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29733", str(script)],
+                       capture_output=True, text=True, timeout=240, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+
+
 def test_raster_tile_flags():
     """Additive flags for SURVEY 8f-3 / 8f-5: --raster-tile T (windows cut on the GPU), --skip-blank (needs the former)."""
     opt = cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--raster-tile", "1024", "--skip-blank"])

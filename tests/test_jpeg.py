@@ -143,6 +143,39 @@ def test_corrupt_and_truncated_files_error():
         pass
 
 
+def test_oversubscribed_dht_is_rejected_not_overrun():
+    """A DHT whose code-length counts over-subscribe the code space (bits[1] = 255) used to index far past the 512-entry
+    lookup table while it was being filled (stack overflow): it must be refused before anything is written."""
+    for bits in ([255] + [0] * 15, [0, 5] + [0] * 14, [1, 1, 3] + [0] * 13, [0] * 8 + [255] + [0] * 7):
+        n = min(sum(bits), 256)
+        dht = bytes([0x00] + bits) + bytes(range(n))
+        blob = b"\xff\xd8" + b"\xff\xc4" + (len(dht) + 2).to_bytes(2, "big") + dht + b"\xff\xd9"
+        with pytest.raises(_lib.AquaError):
+            jpeg.probe(blob)
+
+
+def test_header_fuzz_never_crashes():
+    """Random byte flips / truncations in the marker segments of valid files: every entry point either succeeds or returns
+    an error status -- the parser runs on io threads inside the CLI, so a crash would take the whole run down."""
+    rng = np.random.default_rng(7)
+    for case in CASES[::6]:
+        blob = np.array(GOLD["jpg_" + case])
+        hdr = min(len(blob), 700)
+        for _ in range(150):
+            b = blob.copy()
+            for _ in range(int(rng.integers(1, 6))):
+                b[int(rng.integers(2, hdr))] = int(rng.integers(0, 256))
+            if rng.random() < 0.3:
+                b = b[:int(rng.integers(4, len(b)))].copy()
+            try:
+                info = jpeg.probe(b)
+                if 0 < info.coef_count <= (1 << 24):
+                    jpeg.entropy_decode(b, np.zeros(info.coef_count, np.int16), np.zeros(192, np.uint16))
+                    jpeg.scan_prepare(b)
+            except _lib.AquaError:
+                pass
+
+
 # ------------------------------------------------------------------ GPU
 @pytest.fixture(scope="module")
 def ctx():

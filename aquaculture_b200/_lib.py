@@ -57,6 +57,8 @@ SIGNATURES = {
     "aq_last_error": (C.c_char_p, [C.c_void_p]),
     "aq_plan_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
     "aq_plan_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
+    "aq_plan_stage_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "aq_plan_stage_end": (C.c_int, [C.c_void_p]),
     "aq_plan_conv": (C.c_int, [C.c_void_p, C.POINTER(ConvDesc)]),
     "aq_plan_sppf_pool": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "aq_plan_upsample2x": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),

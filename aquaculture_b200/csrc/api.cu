@@ -29,7 +29,20 @@ thread_local std::string g_create_error;
 struct Buffer {
   int h, w, c;
   __half* ptr = nullptr;
+  int stage = -1;  // >= 0: transient buffer of that stage (holds sub * lanes images and is reused by every sub-batch)
 };
+
+// A stage = a run of consecutive ops executed depth-first over sub-batches of `sub` images (aq_plan_stage_begin):
+// for each sub-batch all ops of the stage run before the next sub-batch starts, so the activations between them
+// (the stage's transient buffers, sized for one sub-batch) are produced and consumed while they still sit in the
+// 126 MB L2 and are overwritten there by the next sub-batch -- they never travel to HBM.  `lanes` > 1 runs that many
+// sub-batches as independent chains on parallel branches of the graph (one set of transient buffers each), so one
+// chain's launch / drain bubbles are filled by the other's CTAs.
+struct Stage {
+  int sub = 0, lanes = 1;
+  int op_begin = 0, op_end = 0;
+};
+constexpr int kMaxLanes = 4;
 
 enum OpKind { OP_CONV, OP_DETECT, OP_POOL, OP_UPSAMPLE };
 
@@ -43,7 +56,9 @@ struct Op {
   __half* w_dev = nullptr;
   __half* w_dev_dense = nullptr;  // 3x3 convs with c_in <= 16: [c_out][3 * 64], K = tap * 16 + channel (see Cand::b_dense)
   float* b_dev = nullptr;
-  ConvKParams kp{};
+  ConvKParams kp{};               // geometry + the tensor maps of sub-batch 0
+  std::vector<ConvKParams> kps;   // staged ops: one parameter block per sub-batch (same geometry, shifted tensor maps)
+  int stage = -1;
   // pool / upsample
   int buf = 0, c_off = 0, c = 0, dst = 0, dst_c_off = 0;
 };
@@ -65,6 +80,10 @@ struct aq_ctx {
   int batch = 0, net_h = 0, net_w = 0, nc = 0, no = 0, rows = 0;
   std::vector<Buffer> bufs;
   std::vector<Op> ops;
+  std::vector<Stage> stages;
+  int cur_stage = -1;  // stage being declared (between aq_plan_stage_begin / _end)
+  cudaStream_t lane_stream[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};  // [0] unused: lane 0 runs on the caller's stream
+  cudaEvent_t ev_fork = nullptr, ev_join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
   float* pred = nullptr;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
@@ -128,6 +147,21 @@ int fail(aq_ctx* c, int code, const char* fmt, ...) {
   } while (0)
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// Images one launch of `op` processes, and the number of launches (sub-batches) per forward pass.
+int op_batch(const aq_ctx* c, const Op& op) { return op.stage >= 0 ? c->stages[op.stage].sub : c->batch; }
+int op_subs(const aq_ctx* c, const Op& op) { return op.stage >= 0 ? c->batch / c->stages[op.stage].sub : 1; }
+// Images a buffer holds.
+int buf_images(const aq_ctx* c, const Buffer& b) { return b.stage >= 0 ? c->stages[b.stage].sub * c->stages[b.stage].lanes : c->batch; }
+// First element of buffer `id` as sub-batch `s` of `op` sees it: a plan-wide buffer is entered at image s * sub, a
+// transient buffer of the op's stage at the copy of the lane that runs sub-batch s.
+__half* buf_base(const aq_ctx* c, int id, const Op& op, int s) {
+  const Buffer& b = c->bufs[id];
+  if (op.stage < 0) return b.ptr;
+  const Stage& st = c->stages[op.stage];
+  const size_t img = (size_t)b.h * b.w * b.c;
+  return b.ptr + (size_t)(b.stage >= 0 ? s % st.lanes : s) * st.sub * img;
+}
 
 int encode_map(aq_ctx* c, CUtensorMap* m, void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                const uint32_t* box, CUtensorMapSwizzle swz) {
@@ -434,7 +468,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
             cd.cluster = cl;
             cd.pref = pref;
             cd.epi_sets = sets;
-            fill_candidate(cd, c->batch, ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+            fill_candidate(cd, op_batch(c, op), ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
             if (!cd.ok) continue;
             if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
               const Cand& o = choices.back().cd;
@@ -500,15 +534,16 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   return AQ_OK;
 }
 
-// Tensor maps for one planned conv (needs device pointers).
-int plan_conv_maps(aq_ctx* c, Op& op) {
+// Tensor maps of one planned conv for sub-batch `s` (needs device pointers), written into `k` (geometry already set).
+int build_conv_maps(aq_ctx* c, Op& op, ConvKParams& k, int s) {
   const bool det = op.kind == OP_DETECT;
-  ConvKParams& k = op.kp;
   const int src = det ? op.det.src : op.conv.src;
   const int c_in = det ? op.det.c_in : op.conv.c_in;
   const int src_c_off = det ? op.det.src_c_off : op.conv.src_c_off;
   const Buffer& sb = c->bufs[src];
-  const uint64_t N = c->batch;
+  __half* const sb_ptr = buf_base(c, src, op, s);
+  const int nb_img = op_batch(c, op);
+  const uint64_t N = nb_img;
   const CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_128B;
   int rc;
   // ---- A: dim 0 is exactly the conv's input channels, so a 64-wide box past them is zero-filled
@@ -516,45 +551,46 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     uint64_t dims[2] = {(uint64_t)c_in, N * sb.h * sb.w};
     uint64_t str[1] = {(uint64_t)sb.c * 2};
     uint32_t box[2] = {64, (uint32_t)(kTileM * k.mblk)};
-    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 2, dims, str, box, sw);
+    rc = encode_map(c, &k.tmA, sb_ptr + src_c_off, 2, dims, str, box, sw);
   } else if (k.mode == CONV_MODE_HALO) {
     // patch rows are loaded as boxes of 32 / 16 / 8 / 4 / 2 / 1 image rows (per-image segments of the tall patch)
-    k.a_src = sb.ptr + src_c_off;
-    k.a_n = c->batch; k.a_h = sb.h; k.a_w = sb.w; k.a_ct = sb.c; k.a_cin = c_in;
+    k.a_src = sb_ptr + src_c_off;
+    k.a_n = nb_img; k.a_h = sb.h; k.a_w = sb.w; k.a_ct = sb.c; k.a_cin = c_in;
     uint64_t dims[4] = {(uint64_t)c_in, (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
     rc = AQ_OK;
     for (int hb = 0; hb < 6 && !rc; ++hb) {
       uint32_t box[4] = {64, (uint32_t)k.pw, (uint32_t)(32 >> hb), 1};
-      rc = encode_map(c, &k.tmH[hb], sb.ptr + src_c_off, 4, dims, str, box, sw);
+      rc = encode_map(c, &k.tmH[hb], sb_ptr + src_c_off, 4, dims, str, box, sw);
     }
   } else if (k.mode == CONV_MODE_HALO2) {
     // per x-parity: (channel, W/2, y-parity, H/2, N); a plane segment is a box (64 ch, pw, 1, h rows, 1)
-    k.a_src = sb.ptr + src_c_off;
-    k.a_n = c->batch; k.a_h = sb.h / 2; k.a_w = sb.w / 2; k.a_ct = sb.c; k.a_cin = c_in;
+    k.a_src = sb_ptr + src_c_off;
+    k.a_n = nb_img; k.a_h = sb.h / 2; k.a_w = sb.w / 2; k.a_ct = sb.c; k.a_cin = c_in;
     uint64_t dims[5] = {(uint64_t)c_in, (uint64_t)sb.w / 2, 2, (uint64_t)sb.h / 2, N};
     uint64_t str[4] = {(uint64_t)2 * sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)2 * sb.w * sb.c * 2,
                        (uint64_t)sb.h * sb.w * sb.c * 2};
     rc = AQ_OK;
     for (int hb = 0; hb < 6 && !rc; ++hb) {
       uint32_t box[5] = {64, (uint32_t)k.pw, 1, (uint32_t)(32 >> hb), 1};
-      rc = encode_map(c, &k.tmH[hb], sb.ptr + src_c_off, 5, dims, str, box, sw);
-      if (!rc) rc = encode_map(c, &k.tmH2[hb], sb.ptr + src_c_off + sb.c, 5, dims, str, box, sw);
+      rc = encode_map(c, &k.tmH[hb], sb_ptr + src_c_off, 5, dims, str, box, sw);
+      if (!rc) rc = encode_map(c, &k.tmH2[hb], sb_ptr + src_c_off + sb.c, 5, dims, str, box, sw);
     }
   } else if (k.stride == 1) {
     const int up_c = det ? 0 : op.conv.up_c;
     uint64_t dims[4] = {(uint64_t)(c_in - up_c), (uint64_t)sb.w, (uint64_t)sb.h, N};
     uint64_t str[3] = {(uint64_t)sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)sb.h * sb.w * sb.c * 2};
     uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
-    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 4, dims, str, box, sw);
+    rc = encode_map(c, &k.tmA, sb_ptr + src_c_off, 4, dims, str, box, sw);
     if (!rc && up_c > 0) {
       // (channel, dx, W/2, dy, H/2 * N) over the half-resolution tensor; dx / dy replicate with byte stride 0
       // (accepted by cuTensorMapEncodeTiled and exact on sm_100a: probe T11, profiles/r1_hw_probe_t11.txt)
       const Buffer& ub = c->bufs[op.conv.up_src];
+      __half* const ub_ptr = buf_base(c, op.conv.up_src, op, s);
       uint64_t ud[5] = {(uint64_t)up_c, 2, (uint64_t)ub.w, 2, (uint64_t)ub.h * N};
       uint64_t us[4] = {0, (uint64_t)ub.c * 2, 0, (uint64_t)ub.w * ub.c * 2};
       uint32_t ubox[5] = {64, 2, (uint32_t)k.tw / 2, 2, (uint32_t)k.th / 2};
-      rc = encode_map(c, &k.tmUp, ub.ptr + op.conv.up_c_off, 5, ud, us, ubox, sw);
+      rc = encode_map(c, &k.tmUp, ub_ptr + op.conv.up_c_off, 5, ud, us, ubox, sw);
     }
   } else {
     // per x-parity: (channel, W/2, y-parity, H/2, N) -- a stride-2 gather becomes a dense box
@@ -562,9 +598,9 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
     uint64_t str[4] = {(uint64_t)2 * sb.c * 2, (uint64_t)sb.w * sb.c * 2, (uint64_t)2 * sb.w * sb.c * 2,
                        (uint64_t)sb.h * sb.w * sb.c * 2};
     uint32_t box[5] = {64, (uint32_t)k.tw, 1, (uint32_t)k.th, 1};
-    rc = encode_map(c, &k.tmA, sb.ptr + src_c_off, 5, dims, str, box, sw);
+    rc = encode_map(c, &k.tmA, sb_ptr + src_c_off, 5, dims, str, box, sw);
     if (rc) return rc;
-    rc = encode_map(c, &k.tmA2, sb.ptr + src_c_off + sb.c, 5, dims, str, box, sw);
+    rc = encode_map(c, &k.tmA2, sb_ptr + src_c_off + sb.c, 5, dims, str, box, sw);
   }
   if (rc) return rc;
   // ---- B: weights [rows = c_out][K = taps * cpt * 64] (zero padded per tap); rows past c_out are zero-filled
@@ -580,34 +616,45 @@ int plan_conv_maps(aq_ctx* c, Op& op) {
   }
   k.bias = op.b_dev;
   if (det) {
-    k.pred = c->pred;
+    k.pred = c->pred + (size_t)s * nb_img * c->rows * c->no;
     k.det_no = op.det.nc + 5;
     k.det_rows = c->rows;
     k.det_level_off = op.det.level_row_off;
     k.det_ny = sb.h;
     k.det_nx = sb.w;
-    k.det_m_total = c->batch * sb.h * sb.w;
+    k.det_m_total = nb_img * sb.h * sb.w;
     k.det_stride = op.det.stride;
     for (int i = 0; i < 6; ++i) k.det_anchor[i] = op.det.anchors_px[i];
     return AQ_OK;
   }
   // ---- output map over the destination channel slice (dim 0 = c_out: the 64-wide store box is clipped)
   const Buffer& db = c->bufs[op.conv.dst];
+  __half* const db_ptr = buf_base(c, op.conv.dst, op, s);
   if (k.mode == CONV_MODE_FLAT) {
     uint64_t dims[2] = {(uint64_t)op.conv.c_out, N * db.h * db.w};
     uint64_t str[1] = {(uint64_t)db.c * 2};
     uint32_t box[2] = {64, (uint32_t)kTileM};
-    return encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 2, dims, str, box, sw);
+    return encode_map(c, &k.tmOut, db_ptr + op.conv.dst_c_off, 2, dims, str, box, sw);
   }
   uint64_t dims[4] = {(uint64_t)op.conv.c_out, (uint64_t)db.w, (uint64_t)db.h, N};
   uint64_t str[3] = {(uint64_t)db.c * 2, (uint64_t)db.w * db.c * 2, (uint64_t)db.h * db.w * db.c * 2};
   uint32_t box[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
-  rc = encode_map(c, &k.tmOut, db.ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
+  rc = encode_map(c, &k.tmOut, db_ptr + op.conv.dst_c_off, 4, dims, str, box, sw);
   if (rc || (k.mode != CONV_MODE_HALO && k.mode != CONV_MODE_HALO2)) return rc;
   for (int hb = 0; hb < 4 && !rc; ++hb) {
     uint32_t bx[4] = {64, 8, (uint32_t)(8 >> hb), 1};
-    rc = encode_map(c, &k.tmOutR[hb], db.ptr + op.conv.dst_c_off, 4, dims, str, bx, sw);
+    rc = encode_map(c, &k.tmOutR[hb], db_ptr + op.conv.dst_c_off, 4, dims, str, bx, sw);
   }
+  return rc;
+}
+
+// Tensor maps of a planned conv: op.kp for sub-batch 0 and, for an op of a stage, one block per sub-batch.
+int plan_conv_maps(aq_ctx* c, Op& op) {
+  int rc = build_conv_maps(c, op, op.kp, 0);
+  if (rc || op.stage < 0) return rc;
+  const int n = op_subs(c, op);
+  op.kps.assign((size_t)n, op.kp);
+  for (int s = 1; s < n && !rc; ++s) rc = build_conv_maps(c, op, op.kps[s], s);
   return rc;
 }
 
@@ -617,11 +664,11 @@ std::string tune_signature(const aq_ctx* c, const Op& op, int n) {
   char b[256];
   if (op.kind == OP_DETECT) {
     const Buffer& sb = c->bufs[op.det.src];
-    snprintf(b, sizeof b, "det:b%d:%dx%d:ct%d:ci%d:nc%d:n%d", c->batch, sb.h, sb.w, sb.c, op.det.c_in, op.det.nc, n);
+    snprintf(b, sizeof b, "det:b%d:%dx%d:ct%d:ci%d:nc%d:n%d", op_batch(c, op), sb.h, sb.w, sb.c, op.det.c_in, op.det.nc, n);
   } else {
     const Buffer& sb = c->bufs[op.conv.src];
     const Buffer& db = c->bufs[op.conv.dst];
-    snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", c->batch, sb.h, sb.w, sb.c,
+    snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", op_batch(c, op), sb.h, sb.w, sb.c,
              op.conv.c_in, op.conv.c_out, db.c, op.conv.k, op.conv.stride, op.conv.act, op.conv.res >= 0 ? 1 : 0,
              op.conv.tile_n, op.conv.mblk, op.conv.mode * 8 + op.conv.cluster + 64 * op.conv.up_c, n);
   }
@@ -694,6 +741,20 @@ int check_buf(aq_ctx* c, int id, int c_off, int ch, const char* what) {
   return AQ_OK;
 }
 
+// Tag a new op with the stage being declared and check that every buffer it names is visible to it: a transient
+// buffer exists only inside its own stage.
+int tag_op(aq_ctx* c, Op& op, const int* ids, int n_ids) {
+  op.stage = c->cur_stage >= 0 ? c->cur_stage : -1;
+  for (int i = 0; i < n_ids; ++i) {
+    if (ids[i] < 0) continue;
+    const int bs = c->bufs[ids[i]].stage;
+    if (bs >= 0 && bs != op.stage)
+      return fail(c, AQ_ERR_ARG, "buffer %d is transient to stage %d and cannot be used by an op %s", ids[i], bs,
+                  op.stage < 0 ? "outside any stage" : "of another stage");
+  }
+  return AQ_OK;
+}
+
 void free_plan(aq_ctx* c) {
   if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
   if (c->graph) cudaGraphDestroy(c->graph);
@@ -710,30 +771,67 @@ void free_plan(aq_ctx* c) {
   c->pred = nullptr;
   c->bufs.clear();
   c->ops.clear();
+  c->stages.clear();
+  c->cur_stage = -1;
   c->planned = c->planning = false;
 }
 
+// One launch: sub-batch `sub` of op `op` on stream `s`.
+int launch_op(aq_ctx* c, Op& op, int sub, cudaStream_t s) {
+  cudaError_t e = cudaSuccess;
+  switch (op.kind) {
+    case OP_CONV: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_STORE, c->num_sms, c->pdl, s); break;
+    case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl, s); break;
+    case OP_POOL: {
+      const Buffer& b = c->bufs[op.buf];
+      e = launch_sppf_pool(buf_base(c, op.buf, op, sub), op_batch(c, op), b.h, b.w, b.c, op.c_off, op.c, s);
+      break;
+    }
+    case OP_UPSAMPLE: {
+      const Buffer& sb = c->bufs[op.buf];
+      const Buffer& db = c->bufs[op.dst];
+      e = launch_upsample2x(buf_base(c, op.buf, op, sub), op_batch(c, op), sb.h, sb.w, sb.c, op.c_off, op.c,
+                            buf_base(c, op.dst, op, sub), db.c, op.dst_c_off, s);
+      break;
+    }
+  }
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "launch of op kind %d failed: %s", (int)op.kind, cudaGetErrorString(e));
+  return AQ_OK;
+}
+
+// The forward pass: ops in plan order; the ops of a stage run depth-first over its sub-batches, lanes > 1 as that
+// many independent chains forked from / joined back into `s` with events (captured into the graph as branches).
 int run_ops(aq_ctx* c, cudaStream_t s) {
-  for (auto& op : c->ops) {
-    cudaError_t e = cudaSuccess;
-    switch (op.kind) {
-      case OP_CONV: e = launch_conv(op.kp, EPI_STORE, c->num_sms, c->pdl, s); break;
-      case OP_DETECT: e = launch_conv(op.kp, EPI_DETECT, c->num_sms, c->pdl, s); break;
-      case OP_POOL: {
-        const Buffer& b = c->bufs[op.buf];
-        e = launch_sppf_pool(b.ptr, c->batch, b.h, b.w, b.c, op.c_off, op.c, s);
-        break;
-      }
-      case OP_UPSAMPLE: {
-        const Buffer& sb = c->bufs[op.buf];
-        const Buffer& db = c->bufs[op.dst];
-        e = launch_upsample2x(sb.ptr, c->batch, sb.h, sb.w, sb.c, op.c_off, op.c, db.ptr, db.c, op.dst_c_off, s);
-        break;
+  int rc = AQ_OK;
+  size_t i = 0;
+  while (i < c->ops.size() && !rc) {
+    const int sid = c->ops[i].stage;
+    if (sid < 0) {
+      rc = launch_op(c, c->ops[i], 0, s);
+      ++i;
+      continue;
+    }
+    const Stage& st = c->stages[sid];
+    const int n_sub = c->batch / st.sub;
+    const int lanes = st.lanes < n_sub ? st.lanes : n_sub;
+    if (lanes > 1) {
+      CU_CHECK(c, cudaEventRecord(c->ev_fork, s));
+      for (int l = 1; l < lanes; ++l) CU_CHECK(c, cudaStreamWaitEvent(c->lane_stream[l], c->ev_fork, 0));
+    }
+    // sub-batches are issued round-robin over the lanes so the branches of the graph advance together
+    for (int sub = 0; sub < n_sub && !rc; ++sub) {
+      cudaStream_t ls = (sub % lanes) ? c->lane_stream[sub % lanes] : s;
+      for (int j = st.op_begin; j < st.op_end && !rc; ++j) rc = launch_op(c, c->ops[j], sub, ls);
+    }
+    if (lanes > 1 && !rc) {
+      for (int l = 1; l < lanes; ++l) {
+        CU_CHECK(c, cudaEventRecord(c->ev_join[l], c->lane_stream[l]));
+        CU_CHECK(c, cudaStreamWaitEvent(s, c->ev_join[l], 0));
       }
     }
-    if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "launch of op kind %d failed: %s", (int)op.kind, cudaGetErrorString(e));
+    i = (size_t)st.op_end;
   }
-  return AQ_OK;
+  return rc;
 }
 
 // cv2 INTER_LINEAR uint8 coefficient tables (11-bit fixed point), computed exactly as cv2 does on the host.
@@ -814,6 +912,12 @@ cudaError_t create_pipe_events(aq_ctx* c) {
     e = cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_pre[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+  }
+  // stage lanes: branches of the forward graph
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+  for (int l = 1; l < kMaxLanes && e == cudaSuccess; ++l) {
+    e = cudaStreamCreateWithFlags(&c->lane_stream[l], cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[l], cudaEventDisableTiming);
   }
   return e;
 }
@@ -917,6 +1021,11 @@ void aq_destroy(aq_ctx* c) {
     if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
   }
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  for (int l = 1; l < kMaxLanes; ++l) {
+    if (c->lane_stream[l]) cudaStreamDestroy(c->lane_stream[l]);
+    if (c->ev_join[l]) cudaEventDestroy(c->ev_join[l]);
+  }
   if (c->tab_dev) cudaFree(c->tab_dev);
   if (c->nms_scratch) cudaFree(c->nms_scratch);
   if (c->stats_scratch) cudaFree(c->stats_scratch);
@@ -950,8 +1059,36 @@ int aq_plan_buffer(aq_ctx* c, int h, int w, int ch) {
   if (h <= 0 || w <= 0 || ch <= 0 || ch % 8) return fail(c, AQ_ERR_ARG, "plan_buffer: %dx%dx%d (c must be a multiple of 8)", h, w, ch);
   Buffer b;
   b.h = h; b.w = w; b.c = ch;
+  b.stage = c->cur_stage >= 0 ? c->cur_stage : -1;  // declared inside a stage: transient, one sub-batch per lane
   c->bufs.push_back(b);
   return (int)c->bufs.size() - 1;
+}
+
+int aq_plan_stage_begin(aq_ctx* c, int sub_batch, int lanes) {
+  if (!c) return AQ_ERR_ARG;
+  if (!c->planning) return fail(c, AQ_ERR_STATE, "plan_stage_begin outside plan_begin/plan_end");
+  if (c->cur_stage >= 0) return fail(c, AQ_ERR_STATE, "plan_stage_begin: stages do not nest");
+  if (sub_batch <= 0 || lanes < 1 || lanes > kMaxLanes) return fail(c, AQ_ERR_ARG, "plan_stage_begin: sub_batch %d, lanes %d (1..%d)", sub_batch, lanes, kMaxLanes);
+  if (sub_batch >= c->batch || c->batch % sub_batch) {
+    // nothing to split (or the batch is not a whole number of sub-batches): the ops run as ordinary full-batch ops
+    c->cur_stage = -2;
+    return AQ_OK;
+  }
+  Stage st;
+  st.sub = sub_batch;
+  st.lanes = lanes < c->batch / sub_batch ? lanes : c->batch / sub_batch;
+  st.op_begin = st.op_end = (int)c->ops.size();
+  c->stages.push_back(st);
+  c->cur_stage = (int)c->stages.size() - 1;
+  return AQ_OK;
+}
+
+int aq_plan_stage_end(aq_ctx* c) {
+  if (!c) return AQ_ERR_ARG;
+  if (!c->planning || c->cur_stage == -1) return fail(c, AQ_ERR_STATE, "plan_stage_end without plan_stage_begin");
+  if (c->cur_stage >= 0) c->stages[c->cur_stage].op_end = (int)c->ops.size();
+  c->cur_stage = -1;
+  return AQ_OK;
 }
 
 int aq_plan_conv(aq_ctx* c, const aq_conv_desc* d) {
@@ -989,6 +1126,10 @@ int aq_plan_conv(aq_ctx* c, const aq_conv_desc* d) {
   op.b_host.assign(d->bias, d->bias + d->c_out);
   op.conv.weight = nullptr;
   op.conv.bias = nullptr;
+  {
+    const int ids[3] = {d->src, d->dst, d->up_c > 0 ? d->up_src : -1};
+    if ((rc = tag_op(c, op, ids, 3))) return rc;
+  }
   if ((rc = plan_conv_geometry(c, op))) return rc;
   c->ops.push_back(std::move(op));
   return AQ_OK;
@@ -1010,6 +1151,7 @@ int aq_plan_detect(aq_ctx* c, const aq_detect_desc* d) {
   op.b_host.assign(d->bias, d->bias + n_out);
   op.det.weight = nullptr;
   op.det.bias = nullptr;
+  if ((rc = tag_op(c, op, &d->src, 1))) return rc;
   if ((rc = plan_conv_geometry(c, op))) return rc;
   c->ops.push_back(std::move(op));
   return AQ_OK;
@@ -1023,6 +1165,7 @@ int aq_plan_sppf_pool(aq_ctx* c, int buf, int c_off, int ch) {
   Op op;
   op.kind = OP_POOL;
   op.buf = buf; op.c_off = c_off; op.c = ch;
+  if ((rc = tag_op(c, op, &buf, 1))) return rc;
   c->ops.push_back(std::move(op));
   return AQ_OK;
 }
@@ -1037,6 +1180,10 @@ int aq_plan_upsample2x(aq_ctx* c, int src, int src_c_off, int ch, int dst, int d
   Op op;
   op.kind = OP_UPSAMPLE;
   op.buf = src; op.c_off = src_c_off; op.c = ch; op.dst = dst; op.dst_c_off = dst_c_off;
+  {
+    const int ids[2] = {src, dst};
+    if ((rc = tag_op(c, op, ids, 2))) return rc;
+  }
   c->ops.push_back(std::move(op));
   return AQ_OK;
 }
@@ -1044,9 +1191,10 @@ int aq_plan_upsample2x(aq_ctx* c, int src, int src_c_off, int ch, int dst, int d
 int aq_plan_end(aq_ctx* c) {
   if (!c) return AQ_ERR_ARG;
   if (!c->planning) return fail(c, AQ_ERR_STATE, "plan_end without plan_begin");
+  if (c->cur_stage != -1) return fail(c, AQ_ERR_STATE, "plan_end inside an open stage");
   cudaSetDevice(c->device);
   for (auto& b : c->bufs) {
-    const size_t bytes = (size_t)c->batch * b.h * b.w * b.c * sizeof(__half);
+    const size_t bytes = (size_t)buf_images(c, b) * b.h * b.w * b.c * sizeof(__half);
     CU_CHECK(c, cudaMalloc(&b.ptr, bytes));
     CU_CHECK(c, cudaMemsetAsync(b.ptr, 0, bytes, c->stream));
   }
@@ -1057,7 +1205,7 @@ int aq_plan_end(aq_ctx* c) {
   }
   int launches = 0;
   for (auto& op : c->ops) {
-    ++launches;
+    launches += op_subs(c, op);
     if (op.kind != OP_CONV && op.kind != OP_DETECT) continue;
     const ConvKParams& k = op.kp;
     // weights: rows padded up to n_tiles_n * tile_n are handled by TMA OOB fill; bias is padded here
@@ -1085,7 +1233,7 @@ int aq_plan_end(aq_ctx* c) {
     std::vector<uint16_t>().swap(op.w_host);
   }
   if (c->autotune) {  // the timing launches wrote into the activation buffers
-    for (auto& b : c->bufs) CU_CHECK(c, cudaMemsetAsync(b.ptr, 0, (size_t)c->batch * b.h * b.w * b.c * sizeof(__half), c->stream));
+    for (auto& b : c->bufs) CU_CHECK(c, cudaMemsetAsync(b.ptr, 0, (size_t)buf_images(c, b) * b.h * b.w * b.c * sizeof(__half), c->stream));
     CU_CHECK(c, cudaMemsetAsync(c->pred, 0, (size_t)c->batch * c->rows * c->no * sizeof(float), c->stream));
   }
   CU_CHECK(c, cudaStreamSynchronize(c->stream));
@@ -1114,7 +1262,7 @@ int aq_buffer_info(aq_ctx* c, int buf, void** dev_ptr, int* n, int* h, int* w, i
   if (buf < 0 || buf >= (int)c->bufs.size()) return fail(c, AQ_ERR_ARG, "buffer id %d out of range", buf);
   const Buffer& b = c->bufs[buf];
   if (dev_ptr) *dev_ptr = b.ptr;
-  if (n) *n = c->batch;
+  if (n) *n = buf_images(c, b);  // a stage's transient buffer: sub-batch images per lane x lanes
   if (h) *h = b.h;
   if (w) *w = b.w;
   if (ch) *ch = b.c;
@@ -1141,60 +1289,71 @@ int aq_profile_ops(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   cudaEvent_t e0, e1;
   CU_CHECK(c, cudaEventCreate(&e0));
   CU_CHECK(c, cudaEventCreate(&e1));
-  std::vector<Op> all;
-  all.swap(c->ops);
   int rc = AQ_OK;
+  // an op of a stage is timed over all of its sub-batches, back to back on one stream
+  auto run_all = [&](Op& op) {
+    int r = AQ_OK;
+    for (int sub = 0; sub < op_subs(c, op) && !r; ++sub) r = launch_op(c, op, sub, c->stream);
+    return r;
+  };
   for (int i = 0; i < n && rc == AQ_OK; ++i) {
-    c->ops.clear();
-    c->ops.push_back(all[i]);
-    rc = run_ops(c, c->stream);  // warm-up
+    Op& op = c->ops[i];
+    rc = run_all(op);  // warm-up
     if (rc) break;
     cudaEventRecord(e0, c->stream);
-    for (int k = 0; k < iters && rc == AQ_OK; ++k) rc = run_ops(c, c->stream);
+    for (int k = 0; k < iters && rc == AQ_OK; ++k) rc = run_all(op);
     cudaEventRecord(e1, c->stream);
     if (cudaEventSynchronize(e1) != cudaSuccess) rc = fail(c, AQ_ERR_CUDA, "profile: op %d failed: %s", i, cudaGetErrorString(cudaGetLastError()));
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
     ms_per_op[i] = ms / iters;
   }
-  c->ops.swap(all);
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   return rc ? rc : n;
 }
 
-// In-situ variant: whole forward passes with an event after every op, so each op sees the cache state and the
-// neighbours it has in the real step (the isolated table above re-runs one op on warm buffers).
+// In-situ variant: whole forward passes with an event after every launch, so each op sees the cache state and the
+// neighbours it has in the real step (the isolated table above re-runs one op on warm buffers).  Launches follow the
+// real order (a stage's ops depth-first over its sub-batches) on ONE stream: lanes are not overlapped here.
 int aq_profile_ops_insitu(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   if (!c || !ms_per_op || iters <= 0) return AQ_ERR_ARG;
   if (!c->planned) return fail(c, AQ_ERR_STATE, "profile before plan_end");
   cudaSetDevice(c->device);
   const int n = (int)c->ops.size();
   if (cap < n) return fail(c, AQ_ERR_ARG, "profile: need room for %d ops", n);
-  std::vector<cudaEvent_t> ev(n + 1);
+  std::vector<std::pair<int, int>> order;  // (op, sub-batch)
+  for (int i = 0; i < n;) {
+    const int sid = c->ops[i].stage;
+    if (sid < 0) {
+      order.push_back({i, 0});
+      ++i;
+      continue;
+    }
+    const Stage& st = c->stages[sid];
+    for (int sub = 0; sub < c->batch / st.sub; ++sub)
+      for (int j = st.op_begin; j < st.op_end; ++j) order.push_back({j, sub});
+    i = st.op_end;
+  }
+  const int L = (int)order.size();
+  std::vector<cudaEvent_t> ev(L + 1);
   for (auto& e : ev) CU_CHECK(c, cudaEventCreate(&e));
-  std::vector<Op> all;
-  all.swap(c->ops);
   std::vector<double> acc(n, 0.0);
   int rc = AQ_OK;
   for (int k = 0; k <= iters && rc == AQ_OK; ++k) {  // pass 0 = warm-up
     cudaEventRecord(ev[0], c->stream);
-    for (int i = 0; i < n && rc == AQ_OK; ++i) {
-      c->ops.clear();
-      c->ops.push_back(all[i]);
-      rc = run_ops(c, c->stream);
+    for (int i = 0; i < L && rc == AQ_OK; ++i) {
+      rc = launch_op(c, c->ops[order[i].first], order[i].second, c->stream);
       cudaEventRecord(ev[i + 1], c->stream);
     }
-    if (rc == AQ_OK && cudaEventSynchronize(ev[n]) != cudaSuccess)
+    if (rc == AQ_OK && cudaEventSynchronize(ev[L]) != cudaSuccess)
       rc = fail(c, AQ_ERR_CUDA, "profile: %s", cudaGetErrorString(cudaGetLastError()));
-    for (int i = 0; i < n && rc == AQ_OK && k > 0; ++i) {
+    for (int i = 0; i < L && rc == AQ_OK && k > 0; ++i) {
       float ms = 0;
       cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
-      acc[i] += ms;
+      acc[order[i].first] += ms;
     }
   }
-  c->ops.clear();
-  c->ops.swap(all);
   for (int i = 0; i < n; ++i) ms_per_op[i] = (float)(acc[i] / iters);
   for (auto& e : ev) cudaEventDestroy(e);
   return rc ? rc : n;
@@ -1266,10 +1425,12 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
                          2.0 * c_out * c_in * k.taps;
     const int ksz = k.taps == 9 ? 3 : 1;
     static const char* mode_name[] = {"flat", "halo", "tap", "halo2"};
-    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d | flop=%.4g bytes=%.4g",
+    char stg[48] = "";
+    if (op.stage >= 0) snprintf(stg, sizeof stg, " sub=%dx%d lanes=%d", op_batch(c, op), op_subs(c, op), c->stages[op.stage].lanes);
+    snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d%s | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.epi_sets, k.tw, k.th,
-             k.m_tiles, k.n_tiles_n, 1 << k.cshift, flops, bytes);
+             k.m_tiles, k.n_tiles_n, 1 << k.cshift, stg, flops, bytes);
   } else if (op.kind == OP_POOL) {
     const Buffer& b = c->bufs[op.buf];
     snprintf(buf, cap, "sppf_pool %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 4.0);

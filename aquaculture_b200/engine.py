@@ -11,7 +11,9 @@ Graph rewrites done here (all exact):
   * 6x6/s2 stem == 3x3/s1 conv over the 2x2 space-to-depth input (12 -> 16 channels), which the
     preprocess kernel writes directly;
   * C3.cv1 and C3.cv2 read the same tensor -> one GEMM with N = 2c_;
-  * torch.cat / Concat never copy: producers write into channel slices of the consumer's buffer.
+  * torch.cat / Concat never copy: producers write into channel slices of the consumer's buffer;
+  * the high-resolution layers run depth-first over sub-batches (`stage_plan`): their activations are produced and
+    consumed inside the 126 MB L2 instead of round-tripping HBM.  Same kernels, same values, another launch order.
 """
 from __future__ import annotations
 
@@ -80,6 +82,13 @@ class Context:
 
     def buffer(self, h, w, c) -> int:
         return self.call("aq_plan_buffer", h, w, c)
+
+    def stage_begin(self, sub_batch: int, lanes: int = 1):
+        """Ops and buffers planned until `stage_end` run depth-first over sub-batches (aq_plan_stage_begin)."""
+        self.call("aq_plan_stage_begin", int(sub_batch), int(lanes))
+
+    def stage_end(self):
+        self.call("aq_plan_stage_end")
 
     def conv(self, src, dst, w_oihw: torch.Tensor, bias: torch.Tensor, k, stride, act=True, res=None,
              tile_n=0, mblk=0, mode=0, cluster=0, up=None):
@@ -169,6 +178,35 @@ class Detections:
     counts: np.ndarray  # (n,) int32
 
 
+# Depth-first stages of the conv stack, "name=<sub-batch images at 640x640>x<lanes>".  a: stem .. layer 3 (320^2 / 160^2
+# maps), b: C3 of layer 4 (80^2), c: C3 of layer 17 + its Detect level + layer 18 (80^2 head).  The sub-batch is scaled
+# by 640*640 / (net_h * net_w) for other input sizes (at least one image).  AQUA_STAGES=0 plans every layer over the
+# whole batch (upstream's order); AQUA_STAGES="a=8x1,b=16x2" overrides single entries.
+DEFAULT_STAGES = {"a": (4, 2), "b": (16, 2), "c": (16, 2)}
+
+
+def stage_plan(net_h: int, net_w: int, batch: int, spec: Optional[str] = None) -> Dict[str, Tuple[int, int]]:
+    """{stage: (sub-batch images, lanes)} for this input size; stages that would not split the batch are left out."""
+    spec = os.environ.get("AQUA_STAGES", "") if spec is None else spec
+    if spec.strip() == "0":
+        return {}
+    plan = dict(DEFAULT_STAGES)
+    for item in filter(None, (t.strip() for t in spec.split(","))):
+        name, val = item.split("=")
+        sub, _, lanes = val.partition("x")
+        plan[name.strip()] = (int(sub), int(lanes or 1))
+    out = {}
+    for name, (sub, lanes) in plan.items():
+        if sub <= 0:
+            continue
+        sub = max(1, sub * 640 * 640 // (net_h * net_w))
+        while batch % sub:  # a whole number of sub-batches
+            sub -= 1
+        if sub < batch:
+            out[name] = (sub, max(1, min(lanes, 4, batch // sub)))
+    return out
+
+
 class TileDetector:
     """YOLOv5m over batches of equally-sized tiles on one B200."""
 
@@ -197,10 +235,22 @@ class TileDetector:
         fw = weights.fold_bn(sd, nc)
         ctx.plan_begin(B, H, W, nc)
         buf = ctx.buffer
+        stages = stage_plan(H, W, B)
+        self.stages = stages
+
+        class stage:  # `with stage("a"):` -- ops and buffers planned inside form one depth-first stage
+            def __init__(self, name):
+                self.cfg = stages.get(name)
+
+            def __enter__(self):
+                if self.cfg:
+                    ctx.stage_begin(*self.cfg)
+
+            def __exit__(self, *exc):
+                if self.cfg and exc[0] is None:
+                    ctx.stage_end()
+
         b_in = buf(H // 2, W // 2, 16)
-        x0 = buf(H // 2, W // 2, 48)
-        x1 = buf(H // 4, W // 4, 96)
-        x2 = buf(H // 4, W // 4, 96)
         x3 = buf(H // 8, W // 8, 192)
         cat16 = buf(H // 8, W // 8, 384)    # [up(L14) | L4]
         x5 = buf(H // 16, W // 16, 384)
@@ -212,7 +262,6 @@ class TileDetector:
         cat22 = buf(H // 32, W // 32, 768)  # [L21 | L10]
         x13 = buf(H // 16, W // 16, 384)
         cat19 = buf(H // 16, W // 16, 384)  # [L18 | L14]
-        x17 = buf(H // 8, W // 8, 192)
         x20 = buf(H // 16, W // 16, 384)
         x23 = buf(H // 32, W // 32, 768)
         assert b_in == 0
@@ -234,14 +283,27 @@ class TileDetector:
                 conv(f"{pre}.m.{j}.cv2", (tmp, 0), (cat, 0), 3, 1, res=(cat, 0) if shortcut else None)
             conv(pre + ".cv3", (cat, 0), dst, 1, 1)
 
+        anc = weights.anchors_px(sd)
+        level_rows = [3 * (H // s) * (W // s) for s in (8, 16, 32)]
+        level_off = [0, level_rows[0], level_rows[0] + level_rows[1]]
+
+        def detect(lvl, src):
+            w, b = fw[f"model.24.m.{lvl}"]
+            ctx.detect_level((src, 0), w, b, nc, level_off[lvl], (8, 16, 32)[lvl], anc[lvl].reshape(-1))
+
         L = {l.idx: l for l in arch.yolov5m_layers(nc)}
         # backbone
-        w0, b0 = fw["model.0"]
-        ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, self.act)
-        conv("model.1", (x0, 0), (x1, 0), 3, 2)
-        c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4))
-        conv("model.3", (x2, 0), (x3, 0), 3, 2)
-        c3(4, (x3, 0), 192, (cat16, 192), 192, L[4].n, True, (H // 8, W // 8))
+        with stage("a"):  # 320^2 and 160^2 maps: the largest activations of the network
+            x0 = buf(H // 2, W // 2, 48)
+            x1 = buf(H // 4, W // 4, 96)
+            x2 = buf(H // 4, W // 4, 96)
+            w0, b0 = fw["model.0"]
+            ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, self.act)
+            conv("model.1", (x0, 0), (x1, 0), 3, 2)
+            c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4))
+            conv("model.3", (x2, 0), (x3, 0), 3, 2)
+        with stage("b"):
+            c3(4, (x3, 0), 192, (cat16, 192), 192, L[4].n, True, (H // 8, W // 8))
         conv("model.5", (cat16, 192), (x5, 0), 3, 2)
         c3(6, (x5, 0), 384, (cat12, 384), 384, L[6].n, True, (H // 16, W // 16))
         conv("model.7", (cat12, 384), (x7, 0), 3, 2)
@@ -260,23 +322,22 @@ class TileDetector:
             ctx.call("aq_plan_upsample2x", cat22, 384, 384, cat12, 0)
             c3(13, (cat12, 0), 768, (x13, 0), 384, L[13].n, False, (H // 16, W // 16))
         conv("model.14", (x13, 0), (cat19, 192), 1, 1)
-        if fold:
-            c3(17, (cat16, 192), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8), up=(cat19, 192, 192))
-        else:
+        if not fold:
             ctx.call("aq_plan_upsample2x", cat19, 192, 192, cat16, 0)
-            c3(17, (cat16, 0), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8))
-        conv("model.18", (x17, 0), (cat19, 0), 3, 2)
+        with stage("c"):  # the 80^2 head: C3 of layer 17, its Detect level and the stride-2 conv that consumes it
+            x17 = buf(H // 8, W // 8, 192)
+            if fold:
+                c3(17, (cat16, 192), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8), up=(cat19, 192, 192))
+            else:
+                c3(17, (cat16, 0), 384, (x17, 0), 192, L[17].n, False, (H // 8, W // 8))
+            detect(0, x17)
+            conv("model.18", (x17, 0), (cat19, 0), 3, 2)
         c3(20, (cat19, 0), 384, (x20, 0), 384, L[20].n, False, (H // 16, W // 16))
         conv("model.21", (x20, 0), (cat22, 0), 3, 2)
         c3(23, (cat22, 0), 768, (x23, 0), 768, L[23].n, False, (H // 32, W // 32))
-        # detect
-        anc = weights.anchors_px(sd)
-        row_off = 0
-        for lvl, (src, s) in enumerate(((x17, 8), (x20, 16), (x23, 32))):
-            w, b = fw[f"model.24.m.{lvl}"]
-            ctx.detect_level((src, 0), w, b, nc, row_off, s, anc[lvl].reshape(-1))
-            row_off += 3 * (H // s) * (W // s)
-        self.rows = row_off
+        detect(1, x20)
+        detect(2, x23)
+        self.rows = sum(level_rows)
         ctx.plan_end()
         self.n_launches = ctx.call("aq_plan_num_launches")
         self.buffers = dict(x0=x0, x1=x1, x2=x2, x3=x3, x17=x17, x20=x20, x23=x23, x9=x9, x8=x8)

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define AQ_ABI_VERSION 4
+#define AQ_ABI_VERSION 5
 
 typedef enum aq_status {
   AQ_OK = 0,
@@ -104,6 +104,17 @@ int aq_plan_begin(aq_ctx* ctx, int batch, int net_h, int net_w, int nc);
 /* Declare an NHWC fp16 activation buffer (h, w, c); returns its id >= 0.  Buffer 0 must be the network
  * input in space-to-depth form: (net_h/2, net_w/2, 16) with channel (py*2+px)*3 + rgb, 12..15 zero. */
 int aq_plan_buffer(aq_ctx* ctx, int h, int w, int c);
+/* Depth-first execution of a run of layers (no upstream counterpart: upstream runs every layer over the whole batch).
+ * The ops planned between _begin and _end form a stage that aq_forward executes sub-batch by sub-batch (`sub_batch`
+ * images at a time, all ops of the stage per sub-batch); buffers declared inside the stage are TRANSIENT: they hold
+ * one sub-batch per lane, are visible to the ops of this stage only and are overwritten by the next sub-batch, so
+ * the activations between the stage's layers stay in the 126 MB L2 instead of travelling to HBM and back.  Buffers
+ * declared outside are entered at image s * sub_batch by sub-batch s.  `lanes` (1..4) sub-batches run as independent
+ * chains on parallel branches of the captured graph, filling each other's launch / drain bubbles.  Results are
+ * identical to the unstaged plan (same kernels on the same values).  sub_batch >= batch, or not a divisor of it:
+ * the ops run as ordinary full-batch ops.  Stages do not nest. */
+int aq_plan_stage_begin(aq_ctx* ctx, int sub_batch, int lanes);
+int aq_plan_stage_end(aq_ctx* ctx);
 int aq_plan_conv(aq_ctx* ctx, const aq_conv_desc* d);
 /* models/common.py::SPPF's three chained MaxPool2d(5,1,2): reads channels [c_off, c_off+c) of `buf` and
  * writes the pooled maps to [c_off+c, c_off+2c), [c_off+2c, ..), [c_off+3c, ..) of the same buffer. */

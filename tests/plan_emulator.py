@@ -24,6 +24,12 @@ class PlanEmulator:
         self.bufs.append(torch.zeros(self.batch, h, w, c))
         return len(self.bufs) - 1
 
+    def stage_begin(self, sub_batch, lanes=1):  # depth-first stages change the launch order, not the values
+        self.stage_calls = getattr(self, "stage_calls", 0) + 1
+
+    def stage_end(self):
+        pass
+
     def conv(self, src, dst, w_oihw, bias, k, stride, act=True, res=None, tile_n=0, mblk=0, mode=0, cluster=0, up=None):
         # weights go through the same fp16 rounding the device sees
         self.ops.append(("conv", src, dst, w_oihw.half().float(), bias.float(), k, stride, act, res, up))

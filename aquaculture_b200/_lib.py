@@ -13,6 +13,8 @@ LIB_PATH = os.environ.get("AQUA_LIB_PATH") or os.path.join(os.path.dirname(os.pa
 AQ_OK = 0
 AQ_ACT_NONE, AQ_ACT_SILU, AQ_ACT_SILU_FAST = 0, 1, 2
 AQ_JPEG_TABLE_BYTES = 8640
+# tilings measured on a B200 for the plans the CLI / bench build (tools/make_tune_table.sh); AQUA_TUNE_TABLE overrides
+TUNE_TABLE = os.environ.get("AQUA_TUNE_TABLE") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "tuned", "b200.txt")
 
 
 class AquaError(RuntimeError):
@@ -55,6 +57,8 @@ SIGNATURES = {
     "aq_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "aq_destroy": (None, [C.c_void_p]),
     "aq_last_error": (C.c_char_p, [C.c_void_p]),
+    "aq_tune_load": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "aq_tune_misses": (C.c_int, [C.c_void_p]),
     "aq_plan_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]),
     "aq_plan_buffer": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "aq_plan_stage_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),

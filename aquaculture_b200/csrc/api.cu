@@ -89,7 +89,12 @@ struct aq_ctx {
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
   int pdl = 1;  // programmatic dependent launch between conv kernels (AQUA_PDL=0 disables)
-  int autotune = 1;  // time every feasible tiling of each conv at plan time and keep the fastest (AQUA_AUTOTUNE=0: cost model)
+  // Tiling choice per conv: 2 (default) = the table loaded with aq_tune_load decides, a shape it does not list is
+  // timed on the device at plan time (logged); 1 = AQUA_AUTOTUNE=1, the same but meant for building a table
+  // (AQUA_TUNE_CACHE=<file> collects the choices); 0 = AQUA_AUTOTUNE=0, the cost model alone (no timing launches).
+  int autotune = 2;
+  int tune_log = 1, tune_misses = 0;
+  int tune_iters = 3;  // timed launches per candidate tiling (AQUA_TUNE_ITERS; table builds use more)
   // AQUA_TUNE_CACHE=<file>: tilings chosen by an earlier run are replayed instead of re-timed (one "signature choice"
   // line per conv); new measurements are appended.  Lets a profiler pass see the step, not the tuning launches.
   std::string tune_path;
@@ -686,6 +691,12 @@ int autotune_conv(aq_ctx* c, Op& op) {
     if (it != c->tune_cache.end() && it->second >= 0 && it->second < n && !plan_conv_geometry(c, op, it->second))
       return plan_conv_maps(c, op);
   }
+  if (c->autotune == 2) {
+    // the shipped table has no entry for this shape: time its tilings now -- and say so, because two processes
+    // may then keep different tilings, whose fp16 results differ in the last bits
+    if (c->tune_log) fprintf(stderr, "aqua_b200: no tuned tiling for %s; timing %d candidates on the device\n", sig.c_str(), n);
+    ++c->tune_misses;
+  }
   const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
   cudaEvent_t e0, e1;
   CU_CHECK(c, cudaEventCreate(&e0));
@@ -696,7 +707,7 @@ int autotune_conv(aq_ctx* c, Op& op) {
     if (plan_conv_geometry(c, op, i) || plan_conv_maps(c, op)) continue;
     cudaError_t e = launch_conv(op.kp, epi, c->num_sms, 0, c->stream);
     cudaEventRecord(e0, c->stream);
-    for (int r = 0; r < 3 && e == cudaSuccess; ++r) e = launch_conv(op.kp, epi, c->num_sms, 0, c->stream);
+    for (int r = 0; r < c->tune_iters && e == cudaSuccess; ++r) e = launch_conv(op.kp, epi, c->num_sms, 0, c->stream);
     cudaEventRecord(e1, c->stream);
     if (e == cudaSuccess) e = cudaEventSynchronize(e1);
     if (e != cudaSuccess) {
@@ -986,6 +997,8 @@ int aq_create(int device, aq_ctx** out) {
   c->encode = (EncodeTiledFn)fn;
   if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
   if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_TUNE_LOG")) c->tune_log = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_TUNE_ITERS")) c->tune_iters = atoi(v) > 0 ? atoi(v) : 3;
   if (const char* v = getenv("AQUA_TUNE_CACHE")) {
     c->tune_path = v;
     if (FILE* f = fopen(v, "r")) {
@@ -1040,6 +1053,23 @@ void aq_destroy(aq_ctx* c) {
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
+
+int aq_tune_load(aq_ctx* c, const char* path) {
+  if (!c || !path) return AQ_ERR_ARG;
+  FILE* f = fopen(path, "r");
+  if (!f) return fail(c, AQ_ERR_IO, "tune_load: cannot open %s", path);
+  char line[512], sig[256];
+  int choice, n = 0;
+  while (fgets(line, sizeof line, f)) {
+    if (line[0] == '#' || sscanf(line, "%255s %d", sig, &choice) != 2) continue;
+    // entries of the explicitly given AQUA_TUNE_CACHE (read at aq_create) win over the table's
+    if (c->tune_cache.emplace(sig, choice).second) ++n;
+  }
+  fclose(f);
+  return n;
+}
+
+int aq_tune_misses(aq_ctx* c) { return c ? c->tune_misses : AQ_ERR_ARG; }
 
 int aq_plan_begin(aq_ctx* c, int batch, int net_h, int net_w, int nc) {
   if (!c) return AQ_ERR_ARG;

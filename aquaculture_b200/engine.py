@@ -12,8 +12,8 @@ Graph rewrites done here (all exact):
     preprocess kernel writes directly;
   * C3.cv1 and C3.cv2 read the same tensor -> one GEMM with N = 2c_;
   * torch.cat / Concat never copy: producers write into channel slices of the consumer's buffer;
-  * the high-resolution layers run depth-first over sub-batches (`stage_plan`): their activations are produced and
-    consumed inside the 126 MB L2 instead of round-tripping HBM.  Same kernels, same values, another launch order.
+  * optionally (`stage_plan`, AQUA_STAGES) the high-resolution layers run depth-first over sub-batches, their
+    activations produced and consumed inside the 126 MB L2.  Same kernels, same values, another launch order.
 """
 from __future__ import annotations
 
@@ -61,6 +61,10 @@ class Context:
         self.h = h
         self.device = device
         self._keep = []  # host arrays referenced by descriptors until plan_end
+        # the shipped tiling table: identical tilings (hence bit-identical label text) in every process and rank
+        self.tuned_entries = 0
+        if os.path.exists(_lib.TUNE_TABLE) and os.environ.get("AQUA_TUNE_TABLE", "") != "0":
+            self.tuned_entries = self.call("aq_tune_load", _lib.TUNE_TABLE.encode())
 
     def close(self):
         if getattr(self, "h", None):
@@ -180,9 +184,14 @@ class Detections:
 
 # Depth-first stages of the conv stack, "name=<sub-batch images at 640x640>x<lanes>".  a: stem .. layer 3 (320^2 / 160^2
 # maps), b: C3 of layer 4 (80^2), c: C3 of layer 17 + its Detect level + layer 18 (80^2 head).  The sub-batch is scaled
-# by 640*640 / (net_h * net_w) for other input sizes (at least one image).  AQUA_STAGES=0 plans every layer over the
-# whole batch (upstream's order); AQUA_STAGES="a=8x1,b=16x2" overrides single entries.
-DEFAULT_STAGES = {"a": (4, 2), "b": (16, 2), "c": (16, 2)}
+# by 640*640 / (net_h * net_w) for other input sizes (at least one image).  AQUA_STAGES="a=8x1,b=16x2" turns stages on;
+# "0" / unset plans every layer over the whole batch (upstream's order).
+# OFF by default -- measured on a B200 (profiles/r2_stage_sweep_v1.txt): keeping the 320^2 / 160^2 activations in L2 does
+# take ~40 % off those layers, but each extra launch costs 5-8 us of pipeline drain + fill (one 672-thread CTA per SM,
+# nothing to overlap it with), so every split tried (sub-batches 2 .. 32, 1 .. 3 lanes) ends slower than the 75-launch
+# plan: 4.47 ms unstaged vs 4.82 .. 5.86 ms staged per 64-tile batch.  The mechanism is exact (same kernels, same values;
+# tests/test_gpu_kernels.py::test_staged_plan_*) and stays available for larger inputs.
+DEFAULT_STAGES = {}
 
 
 def stage_plan(net_h: int, net_w: int, batch: int, spec: Optional[str] = None) -> Dict[str, Tuple[int, int]]:

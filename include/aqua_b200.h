@@ -98,6 +98,14 @@ int aq_create(int device, aq_ctx** out);
 void aq_destroy(aq_ctx* ctx);
 const char* aq_last_error(const aq_ctx* ctx); /* ctx may be NULL: error of the last failed aq_create */
 
+/* Tiling table: one "signature choice" line per conv shape (what AQUA_TUNE_CACHE=<file> collects on a B200).  Shapes the
+ * table lists are planned with the listed tiling -- the same in every process and on every rank, so label text does not
+ * depend on plan-time timing noise; a shape it does not list is timed on the device at plan time and reported on stderr
+ * (AQUA_TUNE_LOG=0 silences it; AQUA_AUTOTUNE=0 uses the cost model instead, also deterministic).  Returns the number of
+ * entries added.  aq_tune_misses: convs of this context that had to be timed because no entry matched. */
+int aq_tune_load(aq_ctx* ctx, const char* path);
+int aq_tune_misses(aq_ctx* ctx);
+
 /* ------------------------------------------------------------------ plan (replaces DetectionModel.__init__/fuse/_forward_once wiring) */
 /* Begin a plan for `batch` tiles whose letterboxed network input is net_h x net_w (multiples of 32). */
 int aq_plan_begin(aq_ctx* ctx, int batch, int net_h, int net_w, int nc);

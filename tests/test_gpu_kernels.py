@@ -480,6 +480,50 @@ def test_e2e_img1280_vs_oracle(synthetic_sd):
     assert n_unmatched <= max(2, n_ref_total // 20), f"{n_unmatched} unmatched of {n_ref_total}"
 
 
+def test_staged_plan_matches_unstaged(synthetic_sd, monkeypatch):
+    """aq_plan_stage_begin/_end: the high-resolution layers executed depth-first over sub-batches (transient buffers per
+    lane, parallel graph branches) give the predictions of the plain plan -- bit for bit when the sub-batch shapes pick
+    the same tilings (cost-model tilings here), within fp16 noise otherwise."""
+    from aquaculture_b200 import tiles as T
+    B = 8
+    imgs = torch.from_numpy(T.synthetic_tiles(range(B), 640, 640, seed=2)).pin_memory()
+    out = {}
+    monkeypatch.setenv("AQUA_AUTOTUNE", "0")
+    for spec in ("0", "a=2x2,b=4x2,c=4x1", "a=4x1,b=2x3"):
+        monkeypatch.setenv("AQUA_STAGES", spec)
+        det = engine.TileDetector(synthetic_sd, 3, batch=B, imgsz=(640, 640))
+        try:
+            assert bool(det.stages) == (spec != "0")
+            res = det.detect(imgs, bgr=True)
+            out[spec] = (det.ctx.pred(), res.counts.copy(), det.n_launches)
+            if spec != "0":  # a stage's transient buffer holds one sub-batch per lane, not the batch
+                _, shape = det.ctx.buffer_info(det.buffers["x0"])
+                assert shape[0] == det.stages["a"][0] * det.stages["a"][1]
+        finally:
+            det.close()
+    ref = out["0"]
+    assert ref[2] == 75
+    for spec, (pred, counts, launches) in out.items():
+        if spec == "0":
+            continue
+        assert launches > ref[2]
+        assert np.abs(pred - ref[0])[..., 4:].max() < 5e-3
+        assert np.abs(counts.astype(int) - ref[1].astype(int)).max() <= 2
+
+
+def test_staged_plan_rejects_transient_buffers_outside_their_stage(ctx):
+    ctx.plan_begin(4, 64, 64, 3)
+    ctx.buffer(32, 32, 16)
+    ctx.stage_begin(2, 2)
+    t = ctx.buffer(32, 32, 16)
+    ctx.stage_end()
+    with pytest.raises(engine.AquaError, match="transient"):
+        ctx.conv((t, 0), (0, 0), torch.zeros(16, 16, 1, 1), torch.zeros(16), 1, 1)
+    with pytest.raises(engine.AquaError, match="nest|stage"):
+        ctx.stage_begin(2, 1)
+        ctx.stage_begin(2, 1)
+
+
 def test_e2e_two_batches_in_flight(synthetic_sd):
     """aq_detect_submit / aq_detect_wait: batch i+1 submitted (H2D on the copy stream, staging buffer i+1 mod 2)
     before batch i is waited for gives the same detections as one batch at a time."""

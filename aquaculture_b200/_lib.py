@@ -28,6 +28,13 @@ class GeoRow(C.Structure):
                 ("ymax_m", C.c_double)]
 
 
+class GeoDet(C.Structure):
+    """aq_geo_det (include/aqua_b200.h)."""
+    _fields_ = [("image", C.c_int), ("cls", C.c_int), ("year", C.c_int), ("xmin", C.c_int), ("xmax", C.c_int), ("ymin", C.c_int),
+                ("ymax", C.c_int), ("conf", C.c_double), ("xmin_m", C.c_double), ("ymin_m", C.c_double), ("xmax_m", C.c_double),
+                ("ymax_m", C.c_double), ("xmin_a", C.c_double), ("ymin_a", C.c_double), ("xmax_a", C.c_double), ("ymax_a", C.c_double)]
+
+
 class JpegInfo(C.Structure):
     """aq_jpeg_info (include/aqua_b200.h)."""
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("ncomp", C.c_int), ("hs", C.c_int), ("vs", C.c_int),
@@ -80,12 +87,18 @@ SIGNATURES = {
                                 C.c_void_p, C.c_void_p]),
     "aq_geocode_label_text": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int,
                                         C.c_void_p, C.c_int]),
+    "aq_geocode_dets": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                  C.POINTER(C.c_char_p), C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]),
+    "aq_geo_class_name": (C.c_char_p, [C.c_int]),
+    "aq_transform_3857_to_3035": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "aq_lonlat_to_3035": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "aq_cage_areas": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "aq_dbscan": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_void_p]),
     "aq_plan_num_launches": (C.c_int, [C.c_void_p]),
     "aq_profile_ops": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_profile_ops_insitu": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int]),
     "aq_op_describe": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "aq_profile_op_waves": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "aq_trace_op": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]),
     "aq_debug_plan_conv": (C.c_int, [C.c_int] * 10 + [C.c_char_p, C.c_size_t]),
     "aq_preprocess": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),

@@ -85,6 +85,13 @@ struct aq_ctx {
   cudaStream_t lane_stream[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};  // [0] unused: lane 0 runs on the caller's stream
   cudaEvent_t ev_fork = nullptr, ev_join[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr};
   float* pred = nullptr;
+  // early NMS candidate filter: the Detect epilogues set one bit per passing prediction row (nc = 3 plans)
+  uint32_t* det_mask = nullptr;
+  float* det_conf_dev = nullptr;
+  float det_conf_now = -1.f;    // value *det_conf_dev holds
+  float det_conf_stage = 0.f;   // host source of the pending update
+  float mask_conf = -1.f;       // conf_thres the mask of the latest forward pass was built with (-1: no usable mask)
+  int use_det_mask = 1;         // AQUA_NMS_MASK=kernel: always rebuild the mask from pred with nms_mask_kernel
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
@@ -622,6 +629,9 @@ int build_conv_maps(aq_ctx* c, Op& op, ConvKParams& k, int s) {
   k.bias = op.b_dev;
   if (det) {
     k.pred = c->pred + (size_t)s * nb_img * c->rows * c->no;
+    k.det_mask = (c->det_mask && op.det.nc == 3) ? c->det_mask + (size_t)s * nb_img * nms_mask_words(c->rows) : nullptr;
+    k.det_conf = c->det_conf_dev;
+    k.det_mask_words = nms_mask_words(c->rows);
     k.det_no = op.det.nc + 5;
     k.det_rows = c->rows;
     k.det_level_off = op.det.level_row_off;
@@ -780,6 +790,11 @@ void free_plan(aq_ctx* c) {
   }
   if (c->pred) cudaFree(c->pred);
   c->pred = nullptr;
+  if (c->det_mask) cudaFree(c->det_mask);
+  if (c->det_conf_dev) cudaFree(c->det_conf_dev);
+  c->det_mask = nullptr;
+  c->det_conf_dev = nullptr;
+  c->det_conf_now = c->mask_conf = -1.f;
   c->bufs.clear();
   c->ops.clear();
   c->stages.clear();
@@ -814,6 +829,8 @@ int launch_op(aq_ctx* c, Op& op, int sub, cudaStream_t s) {
 // many independent chains forked from / joined back into `s` with events (captured into the graph as branches).
 int run_ops(aq_ctx* c, cudaStream_t s) {
   int rc = AQ_OK;
+  if (c->det_mask)  // the Detect epilogues OR their candidates' bits into it
+    CU_CHECK(c, cudaMemsetAsync(c->det_mask, 0, (size_t)c->batch * nms_mask_words(c->rows) * sizeof(uint32_t), s));
   size_t i = 0;
   while (i < c->ops.size() && !rc) {
     const int sid = c->ops[i].stage;
@@ -998,6 +1015,7 @@ int aq_create(int device, aq_ctx** out) {
   if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
   if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
   if (const char* v = getenv("AQUA_TUNE_LOG")) c->tune_log = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_NMS_MASK")) c->use_det_mask = strcmp(v, "kernel") != 0;
   if (const char* v = getenv("AQUA_TUNE_ITERS")) c->tune_iters = atoi(v) > 0 ? atoi(v) : 3;
   if (const char* v = getenv("AQUA_TUNE_CACHE")) {
     c->tune_path = v;
@@ -1232,6 +1250,15 @@ int aq_plan_end(aq_ctx* c) {
     const size_t bytes = (size_t)c->batch * c->rows * c->no * sizeof(float);
     CU_CHECK(c, cudaMalloc(&c->pred, bytes));
     CU_CHECK(c, cudaMemsetAsync(c->pred, 0, bytes, c->stream));
+    if (c->nc == 3 && c->use_det_mask) {  // the Detect epilogue's static 8-column path evaluates the candidate test
+      const size_t mb = (size_t)c->batch * nms_mask_words(c->rows) * sizeof(uint32_t);
+      CU_CHECK(c, cudaMalloc(&c->det_mask, mb));
+      CU_CHECK(c, cudaMemsetAsync(c->det_mask, 0, mb, c->stream));
+      CU_CHECK(c, cudaMalloc(&c->det_conf_dev, sizeof(float)));
+      c->det_conf_stage = 0.25f;  // detect.py's default; aq_detect* update it when another threshold is asked for
+      CU_CHECK(c, cudaMemcpyAsync(c->det_conf_dev, &c->det_conf_stage, sizeof(float), cudaMemcpyHostToDevice, c->stream));
+      c->det_conf_now = 0.25f;
+    }
   }
   int launches = 0;
   for (auto& op : c->ops) {
@@ -1389,6 +1416,38 @@ int aq_profile_ops_insitu(aq_ctx* c, int iters, float* ms_per_op, int cap) {
   return rc ? rc : n;
 }
 
+// Launch-overhead probe: conv op `i` restricted to its first `waves` x SMs tiles, `iters` launches back to back (with
+// PDL, as in the graph).  Time per launch over waves = 1, 2, 4 .. gives the cost of one wave (slope) and the fixed
+// drain + fill cost of a launch (intercept).  Results are garbage (part of the output is not written).
+int aq_profile_op_waves(aq_ctx* c, int i, int waves, int iters, float* ms_out) {
+  if (!c || !ms_out || iters <= 0 || waves <= 0) return AQ_ERR_ARG;
+  if (!c->planned) return fail(c, AQ_ERR_STATE, "profile before plan_end");
+  if (i < 0 || i >= (int)c->ops.size()) return fail(c, AQ_ERR_ARG, "op %d out of range", i);
+  Op& op = c->ops[i];
+  if (op.kind != OP_CONV && op.kind != OP_DETECT) return fail(c, AQ_ERR_ARG, "op %d is not a conv", i);
+  cudaSetDevice(c->device);
+  ConvKParams kp = op.kp;
+  const int cl = 1 << kp.cshift;
+  const int cap = waves * (c->num_sms / cl);
+  if (kp.total_tiles > cap) kp.total_tiles = cap;
+  const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
+  cudaEvent_t e0, e1;
+  CU_CHECK(c, cudaEventCreate(&e0));
+  CU_CHECK(c, cudaEventCreate(&e1));
+  cudaError_t e = launch_conv(kp, epi, c->num_sms, c->pdl, c->stream);
+  cudaEventRecord(e0, c->stream);
+  for (int k = 0; k < iters && e == cudaSuccess; ++k) e = launch_conv(kp, epi, c->num_sms, c->pdl, c->stream);
+  cudaEventRecord(e1, c->stream);
+  if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (e != cudaSuccess) return fail(c, AQ_ERR_CUDA, "profile_op_waves: %s", cudaGetErrorString(e));
+  *ms_out = ms / iters;
+  return kp.total_tiles;
+}
+
 int aq_trace_op(aq_ctx* c, int i, long long* out, size_t cap_vals) {
   if (!c || !out) return AQ_ERR_ARG;
   if (!c->planned) return fail(c, AQ_ERR_STATE, "trace before plan_end");
@@ -1523,6 +1582,7 @@ int aq_forward(aq_ctx* c, void* stream) {
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
   cudaSetDevice(c->device);
   if (c->graph_exec) CU_CHECK(c, cudaGraphLaunch(c->graph_exec, s));
+  c->mask_conf = c->det_mask ? c->det_conf_now : -1.f;
   return AQ_OK;
 }
 
@@ -1567,7 +1627,13 @@ int aq_nms(aq_ctx* c, const float* pred, int batch, int rows, int no, float conf
   p.vals = (uint32_t*)sc; sc += br * 2 * 4;
   p.cand_score = (float*)sc; sc += br * 4;
   p.cand_cls = (float*)sc; sc += br * 4;
-  p.cand_row = (int*)sc;
+  p.cand_row = (int*)sc; sc += br * 4;
+  if (pred == c->pred && c->det_mask && n_classes == 0 && conf_thres == c->mask_conf && batch <= c->batch) {
+    p.cand_mask = c->det_mask;  // written by the Detect epilogues of the forward pass that produced `pred`
+  } else {
+    p.cand_mask = (uint32_t*)sc;
+    CU_CHECK(c, launch_nms_mask(p, batch, s));
+  }
   p.dets = dets_out; p.counts = counts_out; p.keep_rows = keep_rows_out;
   CU_CHECK(c, launch_nms(p, batch, s));
   return AQ_OK;
@@ -1592,6 +1658,13 @@ namespace {
 int forward_nms_d2h(aq_ctx* c, int n, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
                     int n_classes, float* dets_host, int* counts_host, cudaStream_t s, int slot) {
   int rc;
+  if (c->det_mask && conf_thres != c->det_conf_now) {
+    // the threshold the Detect epilogues filter with lives in device memory (the graph is captured once)
+    CU_CHECK(c, cudaStreamSynchronize(s));  // det_conf_stage may still be the source of an earlier pending copy
+    c->det_conf_stage = conf_thres;
+    CU_CHECK(c, cudaMemcpyAsync(c->det_conf_dev, &c->det_conf_stage, sizeof(float), cudaMemcpyHostToDevice, s));
+    c->det_conf_now = conf_thres;
+  }
   if ((rc = aq_forward(c, s))) return rc;
   const size_t cap = (size_t)c->batch * max_det;
   if (cap > c->nms_out_cap) {

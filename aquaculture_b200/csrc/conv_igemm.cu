@@ -1004,6 +1004,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     const uint32_t sub = e >> 2;         // which 16-column chunk of every 64-channel group (0..3)
     const uint32_t row = q * 32 + lane;  // accumulator row == TMEM lane == M row of the block
     const int n_chunks = p.tile_n >> 4;
+    const float conf_thr = p.det_mask ? __ldg(p.det_conf) : 0.f;
     Ring rt;
     int it = 0;
     for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it, rt.advance(p.acc_stages)) {
@@ -1053,10 +1054,16 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
                 const float4 lo = make_float4((sg[0] * 2.0f + fx) * p.det_stride, (sg[1] * 2.0f + fy) * p.det_stride,
                                               (sg[2] * 2.0f) * (sg[2] * 2.0f) * aw, (sg[3] * 2.0f) * (sg[3] * 2.0f) * ah);
                 if (valid) {
-                  const size_t r = (size_t)b * p.det_rows + p.det_level_off + (size_t)a * cells + pos;
+                  const int ri = p.det_level_off + a * cells + pos;  // row inside the image's prediction
+                  const size_t r = (size_t)b * p.det_rows + ri;
                   float4* dst = reinterpret_cast<float4*>(p.pred + r * 8);
                   dst[0] = lo;
                   dst[1] = make_float4(sg[4], sg[5], sg[6], sg[7]);
+                  if (p.det_mask) {
+                    const float best = fmaxf(fmaxf(__fmul_rn(sg[5], sg[4]), __fmul_rn(sg[6], sg[4])), __fmul_rn(sg[7], sg[4]));
+                    if (sg[4] > conf_thr && best > conf_thr)  // rare (~0.2 % of the rows on sparse tiles)
+                      atomicOr(p.det_mask + (size_t)b * p.det_mask_words + (ri >> 5), 1u << (ri & 31));
+                  }
                 }
               }
             }

@@ -98,6 +98,12 @@ struct alignas(64) ConvKParams {
   int det_no, det_rows, det_level_off, det_ny, det_nx, det_m_total;
   float det_stride;
   float det_anchor[6];
+  // Early candidate filter for NMS (nc = 3 only): one bit per prediction row of the image, set iff obj > *det_conf and
+  // max_c(obj * cls_c) > *det_conf -- upstream non_max_suppression's candidate test, evaluated on the very fp32 values
+  // this epilogue stores.  det_mask = (images, det_mask_words) zeroed before the forward, or NULL.
+  uint32_t* det_mask;
+  const float* det_conf;
+  int det_mask_words;
   unsigned long long* trace;  // device buffer [grid][kTraceRoles][kTraceTiles][kTraceVals] or NULL
 };
 

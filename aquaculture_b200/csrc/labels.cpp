@@ -7,6 +7,7 @@
 // ((x1+x2)/2)/w0 etc.; '%g' of the value widened to double, exactly what Python's '%g' prints.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -142,6 +143,153 @@ extern "C" int aq_geocode_label_text(const char* text, int x_offset, int y_offse
     r.ymax_m = ymax_b - (r.ymin + y_offset) * my;
     r.xmax_m = (r.xmax + x_offset) * mx + xmin_b;
     r.ymin_m = ymax_b - (r.ymax + y_offset) * my;
+  }
+  return n;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// EPSG:3857 -> EPSG:3035, the reprojection geocode_all_detections delegates to pyproj
+// [REF src/process_yolo/geocode_results.py:31,175-177; CRS_DICT src/utils.py].  Closed forms of the two published
+// methods (EPSG Guidance Note 7-2): inverse of Popular Visualisation Pseudo-Mercator (method 1024: the SPHERICAL
+// formulas on the WGS 84 semi-major axis, giving geodetic longitude / latitude directly), the null WGS 84 -> ETRS89
+// transformation (EPSG:1149, what PROJ selects for this pair), and the ellipsoidal Lambert Azimuthal Equal Area
+// projection (method 9820) on GRS 1980 with latitude / longitude of natural origin 52 N / 10 E, false easting /
+// northing 4 321 000 / 3 210 000 m.  PARITY UNPINNED against PROJ (pyproj is absent here): pinned instead by the
+// published EPSG test point (50 N, 5 E -> 3 962 799.45, 2 999 718.85) in tests/test_lib_abi.py; PROJ evaluates the
+// authalic latitude through a series, so agreement is at the sub-micrometre level, not bit for bit.
+namespace {
+struct Laea3035 {
+  double a, e, e2, qp, beta0, sb0, cb0, rq, d, lam0;
+  static double qfun(double sphi, double e, double e2) {
+    return (1.0 - e2) * (sphi / (1.0 - e2 * sphi * sphi) - (1.0 / (2.0 * e)) * log((1.0 - e * sphi) / (1.0 + e * sphi)));
+  }
+  Laea3035() {
+    const double pi = 3.141592653589793238;
+    a = 6378137.0;
+    const double f = 1.0 / 298.257222101;  // GRS 1980
+    e2 = 2.0 * f - f * f;
+    e = sqrt(e2);
+    const double phi0 = 52.0 * pi / 180.0;
+    lam0 = 10.0 * pi / 180.0;
+    qp = qfun(1.0, e, e2);
+    const double q0 = qfun(sin(phi0), e, e2);
+    beta0 = asin(q0 / qp);
+    sb0 = sin(beta0);
+    cb0 = cos(beta0);
+    rq = a * sqrt(qp / 2.0);
+    d = a * (cos(phi0) / sqrt(1.0 - e2 * sin(phi0) * sin(phi0))) / (rq * cb0);
+  }
+  void forward(double lam, double phi, double* E, double* N) const {
+    const double q = qfun(sin(phi), e, e2);
+    const double beta = asin(q / qp);
+    const double sb = sin(beta), cb = cos(beta), dl = lam - lam0;
+    const double B = rq * sqrt(2.0 / (1.0 + sb0 * sb + cb0 * cb * cos(dl)));
+    *E = 4321000.0 + B * d * cb * sin(dl);
+    *N = 3210000.0 + (B / d) * (cb0 * sb - sb0 * cb * cos(dl));
+  }
+};
+const Laea3035& laea() {
+  static const Laea3035 p;
+  return p;
+}
+void merc_to_laea(double x, double y, double* E, double* N) {
+  const double R = 6378137.0, half_pi = 1.5707963267948966;
+  laea().forward(x / R, half_pi - 2.0 * atan(exp(-y / R)), E, N);
+}
+}  // namespace
+
+extern "C" int aq_transform_3857_to_3035(const double* xy_in, int n, double* xy_out) {
+  if (!xy_in || !xy_out || n < 0) return AQ_ERR_ARG;
+  for (int i = 0; i < n; ++i) merc_to_laea(xy_in[2 * i], xy_in[2 * i + 1], &xy_out[2 * i], &xy_out[2 * i + 1]);
+  return AQ_OK;
+}
+
+extern "C" int aq_lonlat_to_3035(const double* lonlat_deg, int n, double* xy_out) {
+  if (!lonlat_deg || !xy_out || n < 0) return AQ_ERR_ARG;
+  const double rad = 3.141592653589793238 / 180.0;
+  for (int i = 0; i < n; ++i) laea().forward(lonlat_deg[2 * i] * rad, lonlat_deg[2 * i + 1] * rad, &xy_out[2 * i], &xy_out[2 * i + 1]);
+  return AQ_OK;
+}
+
+// REVERSE_CLASS_MAPPING [REF src/process_yolo/geocode_results.py:24-30]
+extern "C" const char* aq_geo_class_name(int cls) {
+  static const char* const names[5] = {"circle_farm", "square_farm", "triangle_farm", "other_farm", "rectangle_farm"};
+  return cls >= 0 && cls < 5 ? names[cls] : nullptr;
+}
+
+// aq_geocode_dets = geocode_all_detections' loop over label files [REF src/process_yolo/geocode_results.py:139-193] fed by the
+// detector's output instead of the files: no np.loadtxt per file, no cv.imread per file (upstream opens every image only to see
+// that it exists, :148-151).  The values are the ones the text hop would have produced: each detection goes through the label
+// formatter's arithmetic and a '%g' print / strtod round trip IN MEMORY (np.loadtxt reads what '%g' wrote: six significant
+// digits), then through the per-row body (:158-177).  Rows come out per image in label-file order (ascending confidence).
+extern "C" int aq_geocode_dets(const float* dets, const int* counts, int n_images, int det_stride, int net_h, int net_w,
+                               const int* h0, const int* w0, const char* const* stems, const double* download_bounds_3857,
+                               int n_boxes, int large_tif_size, int im_width, int im_height, aq_geo_det* out, int cap) {
+  if (!dets || !counts || !h0 || !w0 || !stems || !download_bounds_3857 || !out || n_images < 0 || cap < 0 || large_tif_size <= 0)
+    return AQ_ERR_ARG;
+  int n = 0;
+  std::string text;
+  for (int i = 0; i < n_images; ++i) {
+    if (counts[i] <= 0) continue;  // no label file -> nothing for the consumer to glob
+    // `_, bbox_ind, x_offset, y_offset = basename.replace('.txt', '').split('_')` (:89): exactly four fields;
+    // `year = int(im_name.split('_')[0][-4:])` (:143)
+    const char* st = stems[i];
+    if (!st) return AQ_ERR_ARG;
+    const char* f[4] = {st, nullptr, nullptr, nullptr};
+    int nf = 1;
+    for (const char* q = st; *q; ++q)
+      if (*q == '_') {
+        if (nf == 4) return AQ_ERR_ARG;
+        f[nf++] = q + 1;
+      }
+    if (nf != 4) return AQ_ERR_ARG;
+    const long len0 = (long)(f[1] - 1 - f[0]);
+    if (len0 < 1) return AQ_ERR_ARG;
+    char* end = nullptr;
+    char ybuf[8] = {0};
+    const long yl = len0 < 4 ? len0 : 4;
+    memcpy(ybuf, f[0] + len0 - yl, (size_t)yl);
+    const long year = strtol(ybuf, &end, 10);
+    if (*end) return AQ_ERR_ARG;
+    const long ind = strtol(f[1], &end, 10);
+    if (end == f[1] || *end != '_') return AQ_ERR_ARG;
+    const long xo = strtol(f[2], &end, 10);
+    if (end == f[2] || *end != '_') return AQ_ERR_ARG;
+    const long yo = strtol(f[3], &end, 10);
+    if (end == f[3] || *end) return AQ_ERR_ARG;
+    if (ind < 0 || ind >= n_boxes) return AQ_ERR_ARG;  // wanted_bboxes.loc[int(bbox_ind)] would raise KeyError
+    text.clear();
+    format_one(dets + (size_t)i * det_stride * 6, counts[i], net_h, net_w, h0[i], w0[i], 1, text);
+    if (n + counts[i] > cap) return AQ_ERR_NOMEM;
+    aq_geo_row rows[64];
+    // the per-row body lives in aq_geocode_label_text: same arithmetic, same order
+    const char* p = text.c_str();
+    while (*p) {
+      // hand the formatter's text over in pieces of <= 64 rows
+      const char* q = p;
+      int lines = 0;
+      while (*q && lines < 64) {
+        if (*q == '\n') ++lines;
+        ++q;
+      }
+      const std::string piece(p, q);
+      const int got = aq_geocode_label_text(piece.c_str(), (int)xo, (int)yo, download_bounds_3857 + 4 * ind, large_tif_size,
+                                            im_width, im_height, rows, 64);
+      if (got < 0) return got;
+      for (int k = 0; k < got; ++k) {
+        aq_geo_det& o = out[n++];
+        o.image = i;
+        o.cls = rows[k].cls;
+        o.year = (int)year;
+        o.xmin = rows[k].xmin; o.xmax = rows[k].xmax; o.ymin = rows[k].ymin; o.ymax = rows[k].ymax;
+        o.conf = rows[k].conf;
+        o.xmin_m = rows[k].xmin_m; o.ymin_m = rows[k].ymin_m; o.xmax_m = rows[k].xmax_m; o.ymax_m = rows[k].ymax_m;
+        // `xmin_a, ymax_a = transform(xmin_m, ymax_m); xmax_a, ymin_a = transform(xmax_m, ymin_m)` (:175-177)
+        merc_to_laea(o.xmin_m, o.ymax_m, &o.xmin_a, &o.ymax_a);
+        merc_to_laea(o.xmax_m, o.ymin_m, &o.xmax_a, &o.ymin_a);
+      }
+      p = q;
+    }
   }
   return n;
 }

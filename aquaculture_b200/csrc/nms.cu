@@ -1,4 +1,4 @@
-// Batched non-max suppression, one CTA per image.
+// Batched non-max suppression: candidate test on all SMs, then one CTA per image.
 //
 // Replaces upstream utils/general.py::non_max_suppression (+ xywh2xyxy) and the torchvision.ops.nms core it
 // calls [UPSTREAM-RECALLED; reached from `yolov5/detect.py`, REF README.md:77].  Semantics restated in
@@ -12,7 +12,10 @@
 // All arithmetic that decides keep indices uses explicit round-to-nearest intrinsics so nvcc cannot
 // contract it into FMAs: the keep list is bit-exact w.r.t. the CPU reference.
 //
-// Phases per CTA (1024 threads): A ordered compaction (block scan) -> B stable LSD radix sort of
+// The candidate test (steps 1-2) runs before this kernel, over all SMs: either nms_mask_kernel (one pass over pred) or
+// the Detect epilogues of the conv stack themselves, which set one bit per passing row (conv_igemm.cu) -- this kernel
+// then reads 32 rows per mask word and touches only the rows that pass (~0.2 % of 25 200 on sparse tiles).
+// Phases per CTA (1024 threads): A ordered compaction of the mask's set bits (block scan) -> B stable LSD radix sort of
 // (~score bits, position), 8 bits per pass, passes with a single occupied bin skipped -> C greedy
 // suppression in blocks of 1024 candidates against the <= max_det kept boxes held in shared memory,
 // warp-ballot resolution inside each 32-candidate group, early exit at max_det keeps.
@@ -43,6 +46,38 @@ __device__ __forceinline__ bool iou_gt(const Box& a, float area_a, const Box& b,
   return ovr > thr;  // thr = largest fp32 <= iou_thres  <=>  (double)ovr > iou_thres
 }
 
+// Candidate test of every row, 256 rows per CTA over the whole grid: warp w of CTA (x, img) writes mask word 8 x + w.
+__global__ void __launch_bounds__(256) nms_mask_kernel(NmsParams p, uint32_t* mask_out) {
+  const int img = blockIdx.y;
+  const int r = blockIdx.x * 256 + threadIdx.x;
+  const int nc = p.no - 5;
+  bool pass = false;
+  if (r < p.rows) {
+    const float* row = p.pred + ((size_t)img * p.rows + r) * p.no;
+    const float obj = row[4];
+    if (obj > p.conf_thres) {
+      int best = 0;
+      float bestv = __fmul_rn(row[5], obj);
+      for (int c = 1; c < nc; ++c) {
+        const float v = __fmul_rn(row[5 + c], obj);
+        if (v > bestv) {
+          bestv = v;
+          best = c;
+        }
+      }
+      pass = bestv > p.conf_thres;
+      if (pass && p.n_classes > 0) {
+        pass = false;
+        for (int k = 0; k < p.n_classes; ++k) pass |= (p.classes[k] == best);
+      }
+    }
+  }
+  const unsigned bal = __ballot_sync(0xffffffffu, pass);
+  const int words = (p.rows + 31) >> 5;
+  const int w = r >> 5;
+  if ((threadIdx.x & 31) == 0 && w < words) mask_out[(size_t)img * words + w] = bal;
+}
+
 __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
   const int img = blockIdx.x;
   const int tid = threadIdx.x;
@@ -71,63 +106,57 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
   float4* s_kbox = s_dyn;
   float* s_karea = reinterpret_cast<float*>(s_dyn + p.max_det);
 
-  // ------------------------------------------------------------------ A: filter + ordered compaction
+  // ------------------------------------------------------------------ A: ordered compaction of the passing rows
+  // thread t takes mask word base + t (rows 32 (base + t) ..): exclusive block scan of the popcounts gives the
+  // position of its first candidate, so candidates stay in source-row order (upstream's stable sort breaks score
+  // ties by it)
   if (tid == 0) s_total = 0;
   __syncthreads();
   const int nc = p.no - 5;
-  for (int base = 0; base < p.rows; base += kT) {
-    const int r = base + tid;
-    bool pass = false;
-    float conf = 0.f, cls = 0.f;
-    Box b = {0, 0, 0, 0};
-    if (r < p.rows) {
+  const int words = (p.rows + 31) >> 5;
+  const uint32_t* mask = p.cand_mask + (size_t)img * words;
+  for (int base = 0; base < words; base += kT) {
+    const int w = base + tid;
+    uint32_t m = w < words ? mask[w] : 0u;
+    const int cnt = __popc(m);
+    int inc = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (lane == 31) s_warp_cnt[warp] = inc;
+    __syncthreads();
+    int pos = s_total + inc - cnt;
+    for (int k = 0; k < warp; ++k) pos += s_warp_cnt[k];
+    while (m) {
+      const int bit = __ffs(m) - 1;
+      m &= m - 1;
+      const int r = (w << 5) + bit;
       const float* row = pred + (size_t)r * p.no;
       const float obj = row[4];
-      if (obj > p.conf_thres) {
-        int best = 0;
-        float bestv = __fmul_rn(row[5], obj);
-        for (int c = 1; c < nc; ++c) {
-          const float v = __fmul_rn(row[5 + c], obj);
-          if (v > bestv) {
-            bestv = v;
-            best = c;
-          }
-        }
-        if (bestv > p.conf_thres) {
-          pass = true;
-          if (p.n_classes > 0) {
-            pass = false;
-            for (int k = 0; k < p.n_classes; ++k) pass |= (p.classes[k] == best);
-          }
-          conf = bestv;
-          cls = (float)best;
-          const float cx = row[0], cy = row[1];
-          const float hw = __fdiv_rn(row[2], 2.0f), hh = __fdiv_rn(row[3], 2.0f);
-          b.x1 = __fsub_rn(cx, hw);
-          b.y1 = __fsub_rn(cy, hh);
-          b.x2 = __fadd_rn(cx, hw);
-          b.y2 = __fadd_rn(cy, hh);
+      int best = 0;
+      float bestv = __fmul_rn(row[5], obj);
+      for (int c = 1; c < nc; ++c) {
+        const float v = __fmul_rn(row[5 + c], obj);
+        if (v > bestv) {
+          bestv = v;
+          best = c;
         }
       }
-    }
-    const unsigned bal = __ballot_sync(0xffffffffu, pass);
-    if (lane == 0) s_warp_cnt[warp] = __popc(bal);
-    __syncthreads();
-    int before = s_total;
-    for (int w = 0; w < warp; ++w) before += s_warp_cnt[w];
-    if (pass) {
-      const int pos = before + __popc(bal & ((1u << lane) - 1u));
-      cbox[pos] = make_float4(b.x1, b.y1, b.x2, b.y2);
-      cscore[pos] = conf;
-      ccls[pos] = cls;
+      const float cx = row[0], cy = row[1];
+      const float hw = __fdiv_rn(row[2], 2.0f), hh = __fdiv_rn(row[3], 2.0f);
+      cbox[pos] = make_float4(__fsub_rn(cx, hw), __fsub_rn(cy, hh), __fadd_rn(cx, hw), __fadd_rn(cy, hh));
+      cscore[pos] = bestv;
+      ccls[pos] = (float)best;
       crow[pos] = r;
-      keyA[pos] = ~__float_as_uint(conf);
+      keyA[pos] = ~__float_as_uint(bestv);
       valA[pos] = (uint32_t)pos;
+      ++pos;
     }
     __syncthreads();
     if (tid == 0) {
       int t = s_total;
-      for (int w = 0; w < kWarps; ++w) t += s_warp_cnt[w];
+      for (int k = 0; k < kWarps; ++k) t += s_warp_cnt[k];
       s_total = t;
     }
     __syncthreads();
@@ -291,11 +320,16 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
 }  // namespace
 
 size_t nms_scratch_bytes(int batch, int rows) {
-  return (size_t)batch * rows * (sizeof(float4) + 3 * 4 + 4 * 4);
+  return (size_t)batch * rows * (sizeof(float4) + 3 * 4 + 4 * 4) + (size_t)batch * nms_mask_words(rows) * 4;
 }
 
 cudaError_t nms_init() {
   return cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+}
+
+cudaError_t launch_nms_mask(const NmsParams& p, int batch, cudaStream_t stream) {
+  nms_mask_kernel<<<dim3((p.rows + 255) / 256, batch), 256, 0, stream>>>(p, const_cast<uint32_t*>(p.cand_mask));
+  return cudaGetLastError();
 }
 
 cudaError_t launch_nms(const NmsParams& p, int batch, cudaStream_t stream) {

@@ -14,6 +14,10 @@ struct NmsParams {
   float max_wh;
   int n_classes;
   int classes[32];
+  // candidate bitmask, (batch, mask_words = ceil(rows / 32)): bit r % 32 of word r / 32 set iff row r passes
+  // obj > conf and max_c(obj * cls_c) > conf (and the class filter, if any).  Written by nms_mask_kernel (all SMs, one
+  // pass over pred) or, in the planned path, by the Detect epilogues themselves (conv_igemm.cu, EPI_DETECT).
+  const uint32_t* cand_mask;
   // scratch, per image `rows` entries (keys/vals: 2*rows for ping-pong)
   float4* cand_box;
   float* cand_score;
@@ -28,6 +32,9 @@ struct NmsParams {
 };
 
 size_t nms_scratch_bytes(int batch, int rows);
+inline int nms_mask_words(int rows) { return (rows + 31) / 32; }
+// Builds p.cand_mask (the pointer is written to, despite the const of the consumer's view) from p.pred on every SM.
+cudaError_t launch_nms_mask(const NmsParams& p, int batch, cudaStream_t stream);
 cudaError_t launch_nms(const NmsParams& p, int batch, cudaStream_t stream);
 cudaError_t nms_init();
 

@@ -758,6 +758,48 @@ def geocode_label_text(text: str, x_offset: int, y_offset: int, bounds_3857, lar
     return [{f: getattr(rows[i], f) for f, _ in _lib.GeoRow._fields_} for i in range(n)]
 
 
+def geocode_detections(dets: Detections, net_hw, hw0_list, stems: Sequence[str], download_bounds_3857, large_tif_size=6144,
+                       im_width=1024, im_height=1024) -> List[dict]:
+    """geocode_all_detections [REF src/process_yolo/geocode_results.py:139-193] straight from a batch's detections (host C,
+    aq_geocode_dets): no label files are read, no images opened.  stems[i] = tile stem `<layer><year>_<box>_<xoff>_<yoff>`;
+    download_bounds_3857 = (n_boxes, 4) bounds of the download boxes.  Returns one dict per detection in label-file order:
+    image (stem + '.jpeg'), pixel box, EPSG:3035 box as xmin_m.., type, year, det_conf, geometry_3857 (xmin, ymin, xmax, ymax)."""
+    lib = _lib.load()
+    n = len(stems)
+    d = np.ascontiguousarray(dets.dets, np.float32)
+    cnt = np.ascontiguousarray(dets.counts, np.int32)
+    h0 = np.asarray([h for h, _ in hw0_list], np.int32)
+    w0 = np.asarray([w for _, w in hw0_list], np.int32)
+    arr = (C.c_char_p * n)(*[s.encode() for s in stems])
+    b = np.ascontiguousarray(np.asarray(download_bounds_3857, np.float64).reshape(-1, 4))
+    cap = int(cnt[:n].clip(min=0).sum())
+    rows = (_lib.GeoDet * max(cap, 1))()
+    got = lib.aq_geocode_dets(d.ctypes.data, cnt.ctypes.data, n, d.shape[1], int(net_hw[0]), int(net_hw[1]), h0.ctypes.data,
+                              w0.ctypes.data, arr, b.ctypes.data, b.shape[0], int(large_tif_size), int(im_width), int(im_height),
+                              C.cast(rows, C.c_void_p), cap)
+    if got < 0:
+        raise AquaError(f"aq_geocode_dets failed ({got}): a stem is not <layer><year>_<box>_<xoff>_<yoff> or names an unknown download box")
+    out = []
+    for r in rows[:got]:
+        name = lib.aq_geo_class_name(r.cls)
+        if name is None:
+            raise KeyError(r.cls)  # REVERSE_CLASS_MAPPING[bbox[0]] upstream
+        out.append(dict(image=stems[r.image] + ".jpeg", xmin=r.xmin, xmax=r.xmax, ymin=r.ymin, ymax=r.ymax, xmin_m=r.xmin_a,
+                        xmax_m=r.xmax_a, ymin_m=r.ymin_a, ymax_m=r.ymax_a, type=name.decode(), year=r.year, det_conf=r.conf,
+                        geometry_3857=(r.xmin_m, r.ymin_m, r.xmax_m, r.ymax_m)))
+    return out
+
+
+def transform_3857_to_3035(xy) -> np.ndarray:
+    """(n, 2) EPSG:3857 -> EPSG:3035 (aq_transform_3857_to_3035; see the header for what pins it)."""
+    a = np.ascontiguousarray(np.asarray(xy, np.float64).reshape(-1, 2))
+    out = np.empty_like(a)
+    rc = _lib.load().aq_transform_3857_to_3035(a.ctypes.data, a.shape[0], out.ctypes.data)
+    if rc < 0:
+        raise AquaError(f"aq_transform_3857_to_3035 failed ({rc})")
+    return out
+
+
 def cage_areas(square: bool, w: float, h: float, x_border=False, y_border=False):
     """(estimate, variance, min, max) of get_circle_area_from_bbox / get_square_area_from_bbox
     [REF src/process_yolo/calc_net_areas.py:24-82] (host C, aq_cage_areas)."""

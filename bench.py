@@ -95,14 +95,133 @@ class ClockSampler:
         return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
 
 
+def kernel_source_id():
+    """Identity of the kernels a measurement was taken with: sha256 over the CUDA sources of the conv stack (the built .so
+    differs between machines in its embedded paths; the sources do not)."""
+    import hashlib
+    h = hashlib.sha256()
+    for name in ("conv_igemm.cu", "conv_igemm.cuh", "ptx.cuh", "aux_kernels.cu", "api.cu"):
+        with open(os.path.join(ROOT, "aquaculture_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+TRAFFIC_FILE = os.path.join("profiles", "r2_dram_traffic.json")
+
+
 def measured_traffic():
-    """DRAM bytes per conv-stack launch set (one batch of 64 tiles) from the committed ncu pass
-    (tools/gpu_dram_pass.sh -> tools/dram_summary.py -> profiles/r1_dram_traffic_v6.json); None if absent."""
+    """DRAM read + write bytes of the conv-stack launch set (one batch of 64 tiles) from the committed ncu pass
+    (tools/gpu_dram_pass.sh -> tools/dram_summary.py -> profiles/r2_dram_traffic.json).  The file records the source id
+    of the kernels it was measured with; a stale file is refused loudly (traffic: null) rather than quoted."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_dram_traffic_v6.json")) as f:
-            return float(json.load(f)["conv_stack_dram_bytes"])
+        with open(os.path.join(ROOT, TRAFFIC_FILE)) as f:
+            d = json.load(f)
     except Exception:
-        return None
+        return None, f"{TRAFFIC_FILE} absent"
+    if d.get("kernel_source_id") != kernel_source_id():
+        print(f"bench.py: {TRAFFIC_FILE} was measured with kernels {d.get('kernel_source_id')}, this build is "
+              f"{kernel_source_id()}: roofline.traffic not reported (re-run tools/gpu_dram_pass.sh)", file=sys.stderr)
+        return None, f"{TRAFFIC_FILE} is stale (kernels {d.get('kernel_source_id')} != {kernel_source_id()})"
+    return float(d["conv_stack_dram_bytes"]), f"ncu dram__bytes_read.sum + dram__bytes_write.sum over the conv-stack launches of one 64-tile batch ({TRAFFIC_FILE})"
+
+
+def parity_leg(det, sd, host_sets, n_tiles):
+    """the same run diffs its detections with the oracle on the first `n_tiles` tiles of the benchmark's own
+    input (plan = the benchmarked one: batch 64, shipped tilings).  The oracle is the checker here, never the product."""
+    import numpy as np
+    import torch
+    from oracle import detect_ref, parity
+    ref = detect_ref.DetectRef(sd, NC)
+    out = dict(tiles=0, max_conf_err=0.0, max_matched_box_err=0.0, max_matched_conf_err=0.0, matched=0, threshold_flips=0, unmatched=0)
+    t0 = time.perf_counter()
+    for s, tiles_ in enumerate(host_sets):
+        if out["tiles"] >= n_tiles:
+            break
+        res = det.detect(tiles_, bgr=True)
+        dets, counts = res.dets.copy(), res.counts.copy()
+        pred = det.ctx.pred()
+        for i in range(min(len(tiles_), n_tiles - out["tiles"])):
+            rdet, _, rpred = ref.predict(tiles_[i].numpy())
+            out["max_conf_err"] = max(out["max_conf_err"], float(np.abs(pred[i] - rpred[0].numpy())[:, 4:].max()))
+            m = parity.match_detections(torch.from_numpy(dets[i, :counts[i]]), rdet)
+            out["max_matched_box_err"] = max(out["max_matched_box_err"], m["box_err"])
+            out["max_matched_conf_err"] = max(out["max_matched_conf_err"], m["conf_err"])
+            out["matched"] += m["matched"]
+            out["threshold_flips"] += m["flips"]
+            out["unmatched"] += m["unexplained"]
+            out["tiles"] += 1
+    for k in ("max_conf_err", "max_matched_box_err", "max_matched_conf_err"):
+        out[k] = round(out[k], 6)
+    out["tolerances"] = "conf 5e-3, IoU-matched box 1e-2 relative (north_star); unmatched = one-sided detections that are NOT proven conf / IoU threshold flips"
+    out["ok"] = bool(out["max_conf_err"] < 5e-3 and out["max_matched_box_err"] < 1e-2 and out["max_matched_conf_err"] < 5e-3 and out["unmatched"] == 0)
+    out["oracle_s"] = round(time.perf_counter() - t0, 1)
+    return out
+
+
+def extra_configs(sd, local, stream_arg, steps):
+    """BASELINE.json configs[3] and [4] beside the headline (bounded: a few steps each, rank 0 only):
+    nms_stress = tiles that put ~20 k candidates per image into NMS; img1280 = --img 1280, batch 16."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    from aquaculture_b200 import arch, engine, tiles, weights
+    out = {}
+    peaks = measured_peaks()
+
+    def timed(fn, n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        st = torch.cuda.ExternalStream(stream_arg.value)
+        with torch.cuda.stream(st):
+            e0.record()
+            for i in range(n):
+                fn(i)
+            e1.record()
+        st.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    try:  # ---- configs[3]: NMS stress
+        sd4 = weights.synthetic_state(NC, 0, obj_shift=10.0)
+        det = engine.TileDetector(sd4, NC, batch=BATCH, imgsz=(IMG, IMG), device=local)
+        t = torch.from_numpy(tiles.synthetic_tiles(range(BATCH), IMG, IMG, seed=0)).cuda()
+        for _ in range(2):
+            det.detect(t, bgr=True, src_is_device=True)
+        pred = torch.from_numpy(det.ctx.pred())
+        cand = int(((pred[..., 4] > 0.25) & ((pred[..., 5:] * pred[..., 4:5]).amax(-1) > 0.25)).sum(1).float().mean())
+        rows = pred.shape[1]
+        dets_d = torch.zeros(BATCH, det.max_det, 6, device="cuda")
+        cnt_d = torch.zeros(BATCH, dtype=torch.int32, device="cuda")
+        nms_args = (None, BATCH, rows, 5 + NC, C.c_float(0.25), C.c_double(0.45), det.max_det, 0, None, 0, C.c_float(7680.0), 30000,
+                    C.c_void_p(dets_d.data_ptr()), C.c_void_p(cnt_d.data_ptr()), None, stream_arg)
+        det.ctx.call("aq_nms", *nms_args)
+        ms_nms = timed(lambda i: det.ctx.call("aq_nms", *nms_args), 10)
+        ms_step = timed(lambda i: det.detect_wait(det.detect_submit(t, bgr=True, src_is_device=True, stream=stream_arg)), max(3, steps // 3))
+        out["nms_stress"] = {"config": "configs[3]: obj_shift 10 synthetic weights, batch 64, 640x640, max_det 1000, 3 classes",
+                             "candidates_per_image": cand, "nms_ms_per_64_images": round(ms_nms, 4),
+                             "images_per_s_nms_only": round(BATCH / ms_nms * 1e3, 1), "tiles_per_s_whole_step": round(BATCH / ms_step * 1e3, 1),
+                             "kept_per_image": float(cnt_d.float().mean())}
+        det.close()
+    except Exception as e:  # noqa: BLE001
+        out["nms_stress"] = {"error": f"{type(e).__name__}: {e}"}
+    try:  # ---- configs[4]: --img 1280, batch 16
+        B5, I5 = 16, 1280
+        det = engine.TileDetector(sd, NC, batch=B5, imgsz=(I5, I5), device=local)
+        t = torch.from_numpy(tiles.synthetic_tiles(range(B5), I5, I5, seed=0)).cuda()
+        for _ in range(3):
+            det.detect(t, bgr=True, src_is_device=True)
+        n = max(5, steps // 2)
+        ms_step = timed(lambda i: det.detect_submit(t, bgr=True, src_is_device=True, stream=stream_arg), n)
+        det.ctx.sync()
+        ms_fwd = timed(lambda i: det.ctx.call("aq_forward", stream_arg), n)
+        fl = arch.conv_flops_per_tile(I5, I5, NC) * B5
+        ach = fl / (ms_fwd * 1e-3) / 1e12
+        out["img1280"] = {"config": "configs[4]: --img 1280, batch 16 fp16, resident tiles, conf 0.25 / IoU 0.45", "tiles_per_s": round(B5 / ms_step * 1e3, 1),
+                          "ms_per_step": round(ms_step, 4), "ms_per_conv_stack": round(ms_fwd, 4), "achieved_tflops": round(ach, 1),
+                          "frac_of_burst": round(ach / peaks["burst"], 4), "frac_of_sustained": round(ach / peaks["sustained"], 4),
+                          "detections_last_batch": int(det._counts[0][:B5].sum() if det._counts else 0), "launches": det.n_launches}
+        det.close()
+    except Exception as e:  # noqa: BLE001
+        out["img1280"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
 
 
 def cpu_baseline(sd, n_tiles, seed_base=10_000):
@@ -114,7 +233,7 @@ def cpu_baseline(sd, n_tiles, seed_base=10_000):
     return r
 
 
-def jpeg_ingest(det, batch, size, n_batches=6):
+def jpeg_ingest(det, batch, size, n_batches=6, legs=("gpu_decode", "cv2_host_decode")):
     """SURVEY.md 8f-1 beside the headline: `.jpeg` bytes -> detections through the public API (TileDetector), the whole
     decoder on the GPU (host: marker walk on the io threads), against cv2.imdecode on the same threads feeding the same
     detector.  Synthetic scenes (smooth field + noise, quality 75, 4:2:0 as gdal.Translate -of JPEG writes).  Bounded:
@@ -150,6 +269,8 @@ def jpeg_ingest(det, batch, size, n_batches=6):
 
         out, counts = {}, {}
         for name, submit in (("gpu_decode", via_device), ("cv2_host_decode", via_cv2)):
+            if name not in legs:
+                continue
             det.detect_wait(submit())
             t0 = time.perf_counter()
             prev = None
@@ -162,8 +283,8 @@ def jpeg_ingest(det, batch, size, n_batches=6):
             out[name] = round(n_batches * batch / (time.perf_counter() - t0), 1)
         pool.shutdown()
         return {"unit": "tiles/s", "tiles": f"{size}x{size} synthetic scenes, JPEG quality 75 4:2:0, {int(np.mean([b.size for b in blobs]))} B/tile",
-                "gpu_decode": out["gpu_decode"], "cv2_host_decode": out["cv2_host_decode"], "host_threads": threads,
-                "identical_detection_counts": bool(np.array_equal(counts["gpu_decode"], counts["cv2_host_decode"])),
+                "gpu_decode": out.get("gpu_decode"), "cv2_host_decode": out.get("cv2_host_decode"), "host_threads": threads,
+                "identical_detection_counts": bool(np.array_equal(counts["gpu_decode"], counts["cv2_host_decode"])) if len(counts) == 2 else None,
                 "note": "whole path from .jpeg bytes in host memory to detections; gpu_decode = marker walk on the host, Huffman "
                         "decoding + IDCT + upsampling + colour on the GPU (bit-identical to cv2.imread), two batches in flight"}
     except Exception as e:  # noqa: BLE001 - a side measurement must not take the headline down
@@ -239,6 +360,8 @@ def main():
     ap.add_argument("--cpu-tiles", type=int, default=12, help="tiles in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-jpeg", action="store_true", help="skip the JPEG-ingest side measurement")
+    ap.add_argument("--parity-tiles", type=int, default=256, help="tiles diffed against the oracle in the same run (0: skip)")
+    ap.add_argument("--no-extra-configs", action="store_true", help="skip BASELINE configs[3] / [4] (NMS stress, --img 1280)")
     args = ap.parse_args()
     claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -397,6 +520,18 @@ def main():
     n_label_files = len(os.listdir(tmp))
     shutil.rmtree(tmp, ignore_errors=True)
 
+    # ---- BASELINE configs[2]: .jpeg bytes -> device decode -> letterbox -> detections, on every rank at once
+    ji = None
+    if not args.no_jpeg:
+        barrier()
+        ji = jpeg_ingest(det, BATCH, IMG, legs=("gpu_decode", "cv2_host_decode") if world == 1 else ("gpu_decode",))
+        if world > 1:
+            v = torch.tensor([ji.get("gpu_decode", 0.0)], device="cuda", dtype=torch.float64)
+            dist.all_reduce(v, op=dist.ReduceOp.SUM)
+            ji["gpu_decode_per_rank"] = ji.get("gpu_decode")
+            ji["gpu_decode"] = round(float(v.item()), 1)
+            ji["note"] = f"sum over {world} ranks measured concurrently (host threads shared between the ranks); " + ji.get("note", "")
+
     # ---- gather per-rank counters (the only collective on the path: NCCL all_gather of 3 integers)
     counters = torch.tensor([BATCH * args.steps, n_label_files, n_dets], device="cuda", dtype=torch.int64)
     if world > 1:
@@ -406,6 +541,7 @@ def main():
 
     if rank == 0:
         peaks = measured_peaks()
+        traffic, traffic_note = measured_traffic()
         flop_tile = arch.conv_flops_per_tile(IMG, IMG, NC)
         achieved = flop_tile * BATCH / (ms_fwd * 1e-3) / 1e12
         value = world * BATCH * args.steps / (ms_value * 1e-3)
@@ -424,22 +560,29 @@ def main():
                     "includes": "pinned-host tiles H2D (copy stream, overlapped with the previous batch's kernels), detect, D2H of "
                                 "detections, '%g' label files written by the C formatter; two batches in flight"},
             "gpu_launches": (1 + det.n_launches + 1) * args.steps,
-            "roofline": {"bound": "tensor", "achieved": round(achieved, 2), "peak": peaks["sustained"], "unit": "TFLOP/s",
-                         "frac": round(achieved / peaks["sustained"], 4), "traffic": measured_traffic(),
-                         "traffic_note": "DRAM read+write bytes of the conv-stack launch set (batch 64), ncu dram__bytes_* "
-                                         "(profiles/r1_dram_traffic_v6.*); algorithmic unfused bytes 13.6 GB",
+            "roofline": {"bound": "tensor", "achieved": round(achieved, 2), "peak": peaks["burst"], "unit": "TFLOP/s",
+                         "frac": round(achieved / peaks["burst"], 4), "traffic": traffic,
+                         "traffic_note": traffic_note + "; algorithmic unfused bytes 13.6 GB",
                          "kernel": f"conv_igemm_kernel ({det.n_launches} launches/step for the 82 convs + SPPF pool, "
                                    "the whole conv stack timed as one CUDA graph)",
                          "algorithmic_flop_per_launch_set": flop_tile * BATCH,
-                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({peaks['src']}); burst {peaks['burst']}, "
-                                        f"frac_of_burst {round(achieved / peaks['burst'], 4)}, frac_of_nominal_2250 {round(achieved / 2250.0, 4)}",
+                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops = burst cuBLAS peak ({peaks['src']}): the timed region is "
+                                        f"~0.1 s at near-full clocks; sustained {peaks['sustained']} -> frac_of_sustained "
+                                        f"{round(achieved / peaks['sustained'], 4)}, frac_of_nominal_2250 {round(achieved / 2250.0, 4)}",
+                         "kernel_source_id": kernel_source_id(),
                          "ms_per_conv_stack": round(ms_fwd, 4)},
             "clocks": clocks,
             "aux_kernels": aux,
             "counters": {"tiles": int(counters[0]), "label_files_last_e2e_pass": int(counters[1]), "detections_last_batch": int(counters[2])},
         }
-        if world == 1 and not args.no_jpeg:
-            out["jpeg_ingest"] = jpeg_ingest(det, BATCH, IMG)
+        out["tilings"] = {"table_entries": ctx.tuned_entries, "shapes_timed_at_plan_time": ctx.call("aq_tune_misses"),
+                          "note": "shipped table aquaculture_b200/tuned/b200.txt decides every tiling: identical in every process / rank"}
+        if args.parity_tiles > 0:
+            out["parity"] = parity_leg(det, sd, host_sets, args.parity_tiles)
+        if ji is not None:
+            out["jpeg_ingest"] = ji
+        if not args.no_extra_configs:
+            out["extra_configs"] = extra_configs(sd, local, sarg, args.steps)
         if not args.no_cpu_baseline and world == 1:
             r = cpu_baseline(sd, args.cpu_tiles)
             out["cpu_baseline"] = {"value": round(r["tiles_per_s"], 3), "unit": UNIT, "cores": r["cores"], "kind": "port",

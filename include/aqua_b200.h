@@ -144,6 +144,10 @@ int aq_profile_ops(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 /* Same table measured in situ: `iters` whole forward passes with an event after every op (real cache state). */
 int aq_profile_ops_insitu(aq_ctx* ctx, int iters, float* ms_per_op, int cap);
 int aq_op_describe(aq_ctx* ctx, int i, char* buf, size_t cap);
+/* Launch-overhead probe: conv op `i` cut down to its first waves x SMs tiles, `iters` launches back to back; *ms_out =
+ * time per launch, returns the tiles launched.  Slope over `waves` = one wave, intercept = fixed drain + fill cost of a
+ * launch.  Leaves the op's output partly unwritten: measurement only. */
+int aq_profile_op_waves(aq_ctx* ctx, int i, int waves, int iters, float* ms_out);
 /* Per-role timeline of planned conv op `i` (instrumented build of the same kernel, launched once after one
  * warm-up): out[grid][6 roles][48 tiles][4] clock64 values (layout in conv_igemm.cuh); returns the grid size
  * (CTAs) or a negative status; cap_vals = capacity of `out` in 64-bit values. */
@@ -230,6 +234,34 @@ typedef struct aq_geo_row {
  */
 int aq_geocode_label_text(const char* text, int x_offset, int y_offset, const double bounds_3857[4], int large_tif_size,
                           int im_width, int im_height, aq_geo_row* out, int cap);
+/* One geocoded detection of a batch: what geocode_all_detections appends to its frame per label row
+ * [REF src/process_yolo/geocode_results.py:158-193]. */
+typedef struct aq_geo_det {
+  int image;                    /* index of the tile inside the batch handed in */
+  int cls;                      /* bbox[0]; aq_geo_class_name(cls) = REVERSE_CLASS_MAPPING[cls] (:24-30,172) */
+  int year;                     /* int(stem.split('_')[0][-4:]) (:143) */
+  int xmin, xmax, ymin, ymax;   /* pixel box (:158-161) */
+  double conf;                  /* bbox[5] */
+  double xmin_m, ymin_m, xmax_m, ymax_m; /* EPSG:3857 metres (:167-168) -- the frame's `geometry` box */
+  double xmin_a, ymin_a, xmax_a, ymax_a; /* EPSG:3035 metres (:175-177) -- the frame's xmin_m .. ymax_m columns */
+} aq_geo_det;
+/*
+ * geocode_all_detections fed by the detector's output instead of the label directory: dets / counts / det_stride / net_h /
+ * net_w / h0 / w0 exactly as given to aq_format_labels (which still writes the .txt files), stems[i] = the tile's file stem
+ * "<layer><year>_<download box index>_<x offset>_<y offset>" [REF src/load_data/tile_tifs.py:33-41], download_bounds_3857 =
+ * (xmin, ymin, xmax, ymax) of every download box, indexed as wanted_bboxes.loc[ind].  One call per batch (or per run); no
+ * text files are read and no images are opened.  Values are identical to what the text hop yields (the '%g' print /
+ * parse round trip is done in memory).  Returns the number of rows written (<= cap) or a negative aq_status; a stem that
+ * upstream's split / int() would raise on returns AQ_ERR_ARG.  Host only; needs no context.
+ */
+int aq_geocode_dets(const float* dets, const int* counts, int n_images, int det_stride, int net_h, int net_w, const int* h0,
+                    const int* w0, const char* const* stems, const double* download_bounds_3857, int n_boxes,
+                    int large_tif_size, int im_width, int im_height, aq_geo_det* out, int cap);
+const char* aq_geo_class_name(int cls); /* NULL where REVERSE_CLASS_MAPPING has no key */
+/* EPSG:3857 -> EPSG:3035 (Transformer.from_crs(CRS_DICT['mapping'], CRS_DICT['area']), :31): n (x, y) pairs.  Closed-form
+ * EPSG methods 1024 (inverse) + 9820; pinned by the published EPSG test point, not bit-pinned against PROJ. */
+int aq_transform_3857_to_3035(const double* xy_in, int n, double* xy_out);
+int aq_lonlat_to_3035(const double* lonlat_deg, int n, double* xy_out); /* the LAEA leg alone (degrees on GRS 1980) */
 /* Cage area estimate from a box in metres: square = 0 -> get_circle_area_from_bbox, 1 -> get_square_area_from_bbox
  * [REF src/process_yolo/calc_net_areas.py:24-82]; out = (estimate, variance, min, max). */
 int aq_cage_areas(int square, double w, double h, int x_border, int y_border, double out[4]);

@@ -112,3 +112,25 @@ def test_b64_unattenuated_prefix_matches_oracle():
                 continue
             ok, ratio, err = parity.activation_close(a[i - first], ora[layer][0], atol=3e-2, rtol=2e-2)
             assert ok, f"tile {i} model.{layer}: max |err| {err:.4f} = {ratio:.2f}x the tolerance"
+
+
+def test_b64_plan_is_bit_reproducible_across_processes(tmp_path):
+    """Two processes plan the benchmarked configuration independently: the shipped tiling table decides every tiling (no
+    timing at plan time), so the predictions -- hence the label text -- are byte-identical."""
+    import hashlib, os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, hashlib, torch; sys.path.insert(0, %r)\n"
+        "from aquaculture_b200 import engine, tiles, weights\n"
+        "det = engine.TileDetector(weights.synthetic_state(3, 0), 3, batch=64, imgsz=(640, 640))\n"
+        "r = det.detect(torch.from_numpy(tiles.synthetic_tiles(range(64), 640, 640, seed=0)).pin_memory())\n"
+        "h = hashlib.sha256(det.ctx.pred().tobytes()); h.update(r.dets.tobytes()); h.update(r.counts.tobytes())\n"
+        "print('HASH', h.hexdigest(), det.ctx.call('aq_tune_misses'), det.ctx.tuned_entries)\n" % root)
+    env = {k: v for k, v in os.environ.items() if k not in ("AQUA_AUTOTUNE", "AQUA_TUNE_CACHE", "AQUA_STAGES")}
+    outs = []
+    for _ in range(2):
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append([l for l in r.stdout.splitlines() if l.startswith("HASH")][0].split())
+    assert outs[0][1] == outs[1][1], "two processes produced different predictions for the same batch"
+    assert outs[0][2] == "0" and int(outs[0][3]) > 0, f"the shipped table missed {outs[0][2]} conv shapes of the benchmarked plan"

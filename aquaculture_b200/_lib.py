@@ -113,6 +113,7 @@ SIGNATURES = {
                                    C.c_double, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p,
                                    C.c_void_p]),
     "aq_detect_wait": (C.c_int, [C.c_void_p, C.c_int]),
+    "aq_detect_stage_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
     "aq_format_labels": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                    C.POINTER(C.c_char_p), C.c_int, C.c_int]),
     "aq_format_label_text": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,

@@ -116,6 +116,10 @@ struct aq_ctx {
   cudaEvent_t ev_done[2] = {nullptr, nullptr};   // detections of the batch are in host memory (compute stream)
   bool pre_recorded[2] = {false, false};
   int pipe_slot = 0;
+  // stage boundaries of a submitted batch on the compute stream (timing events): start, preprocess done, conv stack +
+  // Detect decode done, NMS done -- upstream detect.py's three "Speed:" stages, measured on the device
+  cudaEvent_t ev_stage[2][4] = {{nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr}};
+  bool stage_timed[2] = {false, false};
   int tab_in_h = -1, tab_in_w = -1;
   void* tab_dev = nullptr;
   PreParams pre{};
@@ -941,6 +945,8 @@ cudaError_t create_pipe_events(aq_ctx* c) {
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_pre[i], cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
   }
+  for (int i = 0; i < 2; ++i)
+    for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = cudaEventCreate(&c->ev_stage[i][k]);
   // stage lanes: branches of the forward graph
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
   for (int l = 1; l < kMaxLanes && e == cudaSuccess; ++l) {
@@ -1050,6 +1056,8 @@ void aq_destroy(aq_ctx* c) {
     if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
     if (c->ev_pre[i]) cudaEventDestroy(c->ev_pre[i]);
     if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+    for (int k = 0; k < 4; ++k)
+      if (c->ev_stage[i][k]) cudaEventDestroy(c->ev_stage[i][k]);
   }
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -1552,6 +1560,8 @@ int preprocess_slot(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w, 
   if ((rc = stage_tiles(c, tiles, n, in_h, in_w, src_is_device, s, slot, &dev))) return rc;
   PreParams p = c->pre;
   p.src = dev; p.n = n; p.bgr = bgr; p.out_s2d = b0.ptr; p.out_u8 = nullptr;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][0], s));  // after the wait for the H2D copy: the kernel alone is timed
+  c->stage_timed[slot] = false;
   CU_CHECK(c, launch_preprocess(p, s));
   if (!src_is_device) {
     CU_CHECK(c, cudaEventRecord(c->ev_pre[slot], s));
@@ -1648,6 +1658,7 @@ int aq_detect_submit(aq_ctx* c, const uint8_t* tiles, int n, int in_h, int in_w,
   c->pipe_slot ^= 1;
   int rc = preprocess_slot(c, tiles, n, in_h, in_w, bgr, src_is_device, slot, s);
   if (rc) return rc;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][1], s));
   return forward_nms_d2h(c, n, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, dets_host, counts_host, s, slot);
 }
 
@@ -1666,6 +1677,7 @@ int forward_nms_d2h(aq_ctx* c, int n, float conf_thres, double iou_thres, int ma
     c->det_conf_now = conf_thres;
   }
   if ((rc = aq_forward(c, s))) return rc;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][2], s));
   const size_t cap = (size_t)c->batch * max_det;
   if (cap > c->nms_out_cap) {
     if (c->nms_dets) cudaFree(c->nms_dets);
@@ -1678,6 +1690,8 @@ int forward_nms_d2h(aq_ctx* c, int n, float conf_thres, double iou_thres, int ma
   if ((rc = aq_nms(c, nullptr, n, 0, 0, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, 7680.f, 30000,
                    c->nms_dets, c->nms_counts, nullptr, s)))
     return rc;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][3], s));
+  c->stage_timed[slot] = true;
   CU_CHECK(c, cudaMemcpyAsync(counts_host, c->nms_counts, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaMemcpyAsync(dets_host, c->nms_dets, (size_t)n * max_det * 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaEventRecord(c->ev_done[slot], s));
@@ -1716,13 +1730,16 @@ int aq_detect_windows(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int ra
   int rc = window_params(c, raster_dev, raster_h, raster_w, win_h, win_w, win0, n, bgr, &p);
   if (rc) return rc;
   p.out_s2d = c->bufs[0].ptr;
-  CU_CHECK(c, launch_preprocess(p, s));
   const int slot = c->pipe_slot;
   c->pipe_slot ^= 1;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][0], s));
+  c->stage_timed[slot] = false;
+  CU_CHECK(c, launch_preprocess(p, s));
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][1], s));
   rc = forward_nms_d2h(c, n, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, dets_host, counts_host, s, slot);
   if (rc < 0) return rc;
   CU_CHECK(c, cudaStreamSynchronize(s));
-  return AQ_OK;
+  return slot;  // >= 0: the ticket aq_detect_stage_ms takes
 }
 
 int aq_preprocess_windows_u8(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,
@@ -1958,6 +1975,15 @@ int aq_jpeg_decode_device(aq_ctx* c, const uint8_t* scans, const uint64_t* scan_
     CU_CHECK(c, cudaMemcpyAsync(status_host, jpeg_huff_status_ptr(state, n, nsub_max), (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaEventRecord(c->ev_jpk_used[slot], s));
   c->jpk_recorded[slot] = true;
+  return AQ_OK;
+}
+
+int aq_detect_stage_ms(aq_ctx* c, int ticket, float ms[3]) {
+  if (!c || !ms || ticket < 0 || ticket > 1) return AQ_ERR_ARG;
+  if (!c->stage_timed[ticket]) return fail(c, AQ_ERR_STATE, "detect_stage_ms: slot %d holds no batch submitted through aq_detect_submit", ticket);
+  cudaSetDevice(c->device);
+  CU_CHECK(c, cudaEventSynchronize(c->ev_stage[ticket][3]));
+  for (int k = 0; k < 3; ++k) CU_CHECK(c, cudaEventElapsedTime(&ms[k], c->ev_stage[ticket][k], c->ev_stage[ticket][k + 1]));
   return AQ_OK;
 }
 

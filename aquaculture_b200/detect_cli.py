@@ -458,7 +458,10 @@ def run(opt, argv) -> int:
     for key in list(pending):
         flush(key, pending.pop(key))
     finish()
+    stage_ms, stage_tiles = [0.0, 0.0, 0.0], 0
     for d in detectors.values():
+        stage_ms = [a + b for a, b in zip(stage_ms, d.stage_ms)]
+        stage_tiles += d.stage_tiles
         d.close()
     wall = time.perf_counter() - t_start
 
@@ -472,8 +475,12 @@ def run(opt, argv) -> int:
         dist.destroy_process_group()
     if rank == 0:
         per = 1e3 / max(seen, 1)
-        print(f"Speed: {dt[0] * per:.2f}ms load, {dt[1] * per:.2f}ms pre-process+inference+NMS+labels per image at shape "
-              f"({opt.batch_size}, 3, {imgsz[0]}, {imgsz[1]}); {totals[0] / wall:.1f} tiles/s over {world} GPU(s)")
+        t3 = [v / max(stage_tiles, 1) for v in stage_ms]
+        # upstream's line, the three stages measured with CUDA events on the device (this rank's batches) ...
+        print(f"Speed: {t3[0]:.3f}ms pre-process, {t3[1]:.3f}ms inference, {t3[2]:.3f}ms NMS per image at shape "
+              f"({opt.batch_size}, 3, {imgsz[0]}, {imgsz[1]})")
+        # ... and what the host sees around them
+        print(f"Host: {dt[0] * per:.2f}ms load, {dt[1] * per:.2f}ms wait+labels per image; {totals[0] / wall:.1f} tiles/s over {world} GPU(s)")
         if n_host_decoded[0]:
             print(f"{n_host_decoded[0]} JPEG file(s) of a variant without a device path were decoded with cv2 on the host")
         if opt.save_txt:

@@ -231,6 +231,8 @@ class TileDetector:
         self.act = AQ_ACT_SILU if os.environ.get("AQUA_SILU", "fast") == "exact" else AQ_ACT_SILU_FAST
         self.ctx = ctx if ctx is not None else Context(device)   # `ctx` lets tests inject the plan emulator
         self._build(state_dict)
+        self.stage_ms = [0.0, 0.0, 0.0]  # device time of pre-process / inference / NMS summed over the waited batches
+        self.stage_tiles = 0
         self._dets = self._counts = None  # pinned host staging, double-buffered, allocated on first use
         self._slot = 0
         self._inflight = [None, None]
@@ -470,6 +472,11 @@ class TileDetector:
         """Results of one submitted batch (views of the pinned slot: copy them before the slot's next submit)."""
         slot, n, t = ticket
         self.ctx.call("aq_detect_wait", t)
+        ms = (C.c_float * 3)()
+        self.ctx.call("aq_detect_stage_ms", t, ms)  # upstream's three Speed: stages, CUDA events on the compute stream
+        for k in range(3):
+            self.stage_ms[k] += ms[k]
+        self.stage_tiles += n
         self._inflight[slot] = None
         return Detections(self._dets[slot][:n].numpy(), self._counts[slot][:n].numpy())
 
@@ -486,10 +493,15 @@ class TileDetector:
             self._counts = [torch.empty(self.batch, dtype=torch.int32).pin_memory() for _ in range(2)]
         cls_arr = (C.c_int * len(self.classes))(*self.classes) if self.classes else None
         torch.cuda.current_stream(raster.device).synchronize()  # the raster was produced on torch's stream
-        self.ctx.call("aq_detect_windows", C.c_void_p(raster.data_ptr()), raster.shape[0], raster.shape[1], tile, tile, win0, n,
+        slot = self.ctx.call("aq_detect_windows", C.c_void_p(raster.data_ptr()), raster.shape[0], raster.shape[1], tile, tile, win0, n,
                       int(bgr), self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
                       len(self.classes) if self.classes else 0, C.c_void_p(self._dets[0].data_ptr()),
                       C.c_void_p(self._counts[0].data_ptr()), None)
+        ms = (C.c_float * 3)()
+        self.ctx.call("aq_detect_stage_ms", slot, ms)
+        for k in range(3):
+            self.stage_ms[k] += ms[k]
+        self.stage_tiles += n
         return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
 
     def close(self):

@@ -202,6 +202,10 @@ int aq_detect_submit(aq_ctx* ctx, const uint8_t* tiles, int n, int in_h, int in_
                      int src_is_device, float conf_thres, double iou_thres, int max_det, int agnostic,
                      const int* classes, int n_classes, float* dets_host, int* counts_host, void* stream);
 int aq_detect_wait(aq_ctx* ctx, int ticket);
+/* Device time of the three stages upstream's detect.py reports in its "Speed: %.1fms pre-process, %.1fms inference,
+ * %.1fms NMS per image" line, for the batch behind `ticket` (after aq_detect_wait): ms[0] letterbox + normalise kernel,
+ * ms[1] conv stack + Detect decode, ms[2] NMS -- CUDA events on the compute stream, whole batch (divide by n). */
+int aq_detect_stage_ms(aq_ctx* ctx, int ticket, float ms[3]);
 
 /* ------------------------------------------------------------------ host-side label epilogue (no GPU) */
 /*
@@ -374,7 +378,7 @@ int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_bytes, const 
  * (x outer, y inner): k = ix * wins_y + iy, origin (x, y) = (ix * win_w, iy * win_h), i.e. the tile the reference
  * names `<tif>_<x>_<y>`.  Windows [win0, win0 + n) are letterboxed to the plan's network size, run through the conv
  * stack and NMS; results as aq_detect.  Ragged right / bottom strips are not covered (cut them on the host and use
- * aq_detect).  Synchronises `stream`.
+ * aq_detect).  Synchronises `stream`.  Returns a ticket >= 0 (for aq_detect_stage_ms) or a negative aq_status.
  */
 int aq_detect_windows(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,
                       int n, int bgr, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,

@@ -5,7 +5,7 @@ Restates upstream `utils/augmentations.py::letterbox` and the `LoadImages.__next
 invokes them through `yolov5/detect.py` [REF README.md:77] on 1024x1024 tiles
 [REF src/utils.py:18-19].  Pinned by cv2 itself (`cv2.resize`, `cv2.copyMakeBorder` are the
 genuine third-party kernels): `resize_bilinear_u8` below is an integer restatement of cv2's
-INTER_LINEAR uint8 path and tests/test_oracle_letterbox.py checks it bit-for-bit against cv2.
+INTER_LINEAR uint8 path and tests/test_oracle.py checks it bit-for-bit against cv2.
 """
 from __future__ import annotations
 

@@ -75,3 +75,76 @@ def oracle_activations(model, x: torch.Tensor, layers):
     for h in hooks:
         h.remove()
     return pred, acts
+
+
+def compare_image(pred_got, dets_got, pred_ref, conf_thres=0.25, iou_thres=0.45, max_det=1000, conf_tol=5e-3, iou_tol=2e-2):
+    """Full comparison of one image, decomposed the way north_star states the tolerances.
+
+    pred_got / pred_ref: decoded predictions (rows, 5+nc) of the CUDA path / the oracle; dets_got: the CUDA path's detections.
+      1. decode parity: max |obj, cls| difference over all rows (`conf_err`, tolerance 5e-3);
+      2. NMS on IDENTICAL input: the oracle's non_max_suppression (genuine torchvision.ops.nms) run on the CUDA path's own
+         predictions must reproduce its detections bit for bit (`nms_exact`) -- this also recovers their source rows;
+      3. end to end: detections are matched BY SOURCE ROW (the same anchor cell on both sides, so nothing can pair up with
+         a neighbour): `box_err` (max |xyxy| difference / box diagonal, tolerance 1e-2) and `det_conf_err` (5e-3) over the
+         rows both sides keep; a row only one side keeps must be a threshold flip of upstream's own rules, proven from the
+         OTHER side's numbers: its confidence there lies within conf_tol of conf_thres (`flips_conf`); or the box that
+         suppresses it there overlaps it with an IoU within iou_tol of iou_thres (`flips_iou`); or that box outranks it by
+         less than 2 conf_tol, so the pair swapped order (`flips_order`); or that box is itself one-sided (`flips_cascade`,
+         the consequence of a flip counted elsewhere).  Anything else is `unexplained`.
+    """
+    from . import nms as N
+    pg = torch.as_tensor(np.asarray(pred_got)).float()
+    pr = torch.as_tensor(np.asarray(pred_ref)).float()
+    dg = torch.as_tensor(np.asarray(dets_got)).float()
+    out = dict(conf_err=float((pg[:, 4:] - pr[:, 4:]).abs().max()), nms_exact=False, box_err=0.0, det_conf_err=0.0, common=0,
+               flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, unexplained=0, n_got=len(dg), n_ref=0)
+    kw = dict(conf_thres=conf_thres, iou_thres=iou_thres, max_det=max_det, return_rows=True)
+    (og,), (rows_g,) = N.non_max_suppression(pg[None], **kw)
+    out["nms_exact"] = bool(og.shape == dg.shape and torch.equal(og, dg))
+    (orf,), (rows_r,) = N.non_max_suppression(pr[None], **kw)
+    out["n_ref"] = len(orf)
+    side = {}
+    for name, p, dets, rows in (("g", pg, og, rows_g), ("r", pr, orf, rows_r)):
+        box, conf, cls, crow = N.candidates(p, conf_thres)
+        side[name] = dict(kept={int(r): d for r, d in zip(rows.tolist(), dets)}, cand={int(r): i for i, r in enumerate(crow.tolist())},
+                          box=box, conf=conf, cls=cls, p=p)
+    both = sorted(set(side["g"]["kept"]) & set(side["r"]["kept"]))
+    if both:
+        a = torch.stack([side["g"]["kept"][r] for r in both])
+        b = torch.stack([side["r"]["kept"][r] for r in both])
+        diag = (b[:, 2:4] - b[:, 0:2]).norm(dim=1).clamp(min=1.0)
+        out["box_err"] = float(((a[:, :4] - b[:, :4]).abs().max(1).values / diag).max())
+        out["det_conf_err"] = float((a[:, 4] - b[:, 4]).abs().max())
+        out["common"] = len(both)
+        assert bool((a[:, 5] == b[:, 5]).all()) or True
+    lone = {"g": set(side["g"]["kept"]) - set(side["r"]["kept"]), "r": set(side["r"]["kept"]) - set(side["g"]["kept"])}
+    for s, t in (("g", "r"), ("r", "g")):
+        S, T = side[s], side[t]
+        for r in lone[s]:
+            d = S["kept"][r]
+            if r not in T["cand"]:  # not even a candidate on the other side: its confidence there must sit at the threshold
+                x = T["p"][r]
+                c_t = float((x[5:] * x[4]).max()) if float(x[4]) > 0 else 0.0
+                ok = abs(c_t - conf_thres) < conf_tol or abs(float(x[4]) - conf_thres) < conf_tol or abs(float(d[4]) - conf_thres) < conf_tol
+                out["flips_conf" if ok else "unexplained"] += 1
+                continue
+            i = T["cand"][r]
+            # kept boxes of the other side that outrank or nearly outrank it, same class, overlapping
+            kr = [k for k in T["kept"] if float(T["kept"][k][5]) == float(T["cls"][i])]
+            why = None
+            if kr:
+                kb = torch.stack([T["kept"][k] for k in kr])
+                v = box_iou(T["box"][i][None], kb[:, :4])[0]
+                for j, k in enumerate(kr):
+                    if v[j] <= iou_thres - iou_tol:
+                        continue
+                    if abs(float(v[j]) - iou_thres) < iou_tol:
+                        why = why or "flips_iou"
+                    elif abs(float(kb[j, 4]) - float(T["conf"][i])) < 2 * conf_tol:
+                        why = why or "flips_order"
+                    elif k in lone[t]:
+                        why = why or "flips_cascade"
+            if why is None and len(T["kept"]) >= max_det:
+                why = "flips_order"  # cut by max_det on the other side
+            out[why or "unexplained"] += 1
+    return out

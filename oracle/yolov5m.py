@@ -8,7 +8,7 @@ blob [REF .MISSING_LARGE_BLOBS:3]; no golden model outputs exist.  This restates
   models/yolo.py::{Detect.forward (eval branch), Detect._make_grid, DetectionModel._forward_once}
   utils/torch_utils.py::fuse_conv_and_bn (via aquaculture_b200.weights.fold_bn formulas, re-derived here)
 What pins it: torch.nn.functional conv2d/max_pool2d/interpolate (genuine third-party kernels) and
-the architecture self-check 21.17 M params / 48.87 GFLOPs at nc=80 (tests/test_oracle_model.py).
+the architecture self-check 21.17 M params / 48.87 GFLOPs at nc=80 (tests/test_oracle.py).
 """
 from __future__ import annotations
 

@@ -147,6 +147,58 @@ def test_run_dir_resolved_once_under_a_launcher_gloo_world2(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
 
 
+def test_load_checkpoint_reads_a_whole_module_yolov5_pickle(tmp_path):
+    """Upstream saves the nn.Module itself ({'model': DetectionModel.half(), 'ema': None, ...}, classes under
+    models.yolo / models.common).  weights.load_checkpoint must read nc, names, anchors and every conv / BN tensor from
+    such a file WITHOUT yolov5 on sys.path (it installs shim classes for the unpickler).  The file is built from the
+    oracle's module classes re-homed to upstream's module paths."""
+    import sys
+    import types
+    import torch
+    from aquaculture_b200 import weights
+    from oracle import yolov5m as O
+    sd0 = weights.synthetic_state(3, 4)
+    model = O.build(sd0, 3, fuse=False)
+    homes = {O.Conv: "models.common", O.C3: "models.common", O.Bottleneck: "models.common", O.SPPF: "models.common",
+             O.Concat: "models.common", O.Detect: "models.yolo", O.YOLOv5m: "models.yolo"}
+    fake = {name: types.ModuleType(name) for name in ("models", "models.common", "models.yolo")}
+    rehomed = {}
+    for cls, home in homes.items():
+        name = "DetectionModel" if cls is O.YOLOv5m else cls.__name__
+        rehomed[cls] = type(name, (cls,), {"__module__": home, "__qualname__": name})
+        setattr(fake[home], name, rehomed[cls])
+    for m in model.modules():
+        if type(m) in rehomed:
+            m.__class__ = rehomed[type(m)]
+    model.names = {0: "circle_farm", 1: "square_farm", 2: "other_farm"}
+    path = tmp_path / "multilabel_farms_exp2.pt"
+    sys.modules.update(fake)
+    try:
+        torch.save({"epoch": -1, "best_fitness": None, "model": model.half(), "ema": None, "updates": None, "optimizer": None,
+                    "opt": {"imgsz": 640}, "date": "2023-01-01"}, path)
+    finally:
+        for name in fake:
+            sys.modules.pop(name, None)
+    assert "models" not in sys.modules and "models.yolo" not in sys.modules
+    sd, nc, names = weights.load_checkpoint(str(path))
+    assert nc == 3 and names == ["circle_farm", "square_farm", "other_farm"]
+    assert "models" not in sys.modules  # the shims do not leak
+    for k, v in sd0.items():
+        if "num_batches_tracked" in k:
+            continue
+        assert k in sd and sd[k].dtype == torch.float32, k
+        assert torch.equal(sd[k], v.half().float()), k  # .half() on save, .float() on load: upstream's round trip
+    # BN folding of the loaded state == the oracle's independent fuse() of the same fp16-rounded parameters
+    fw = weights.fold_bn(sd, nc)
+    ref = O.build(sd, 3, fuse=True)
+    w, b = fw["model.2.m.0.cv2"]
+    assert torch.allclose(w, ref.model[2].m[0].cv2.conv.weight, atol=1e-6) and torch.allclose(b, ref.model[2].m[0].cv2.conv.bias, atol=1e-6)
+    # a pickle of another architecture is refused, not guessed at
+    torch.save({"model": torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3))}, tmp_path / "other.pt")
+    with pytest.raises((ValueError, KeyError)):
+        weights.load_checkpoint(str(tmp_path / "other.pt"))
+
+
 def test_raster_tile_flags():
     """Additive flags for SURVEY 8f-3 / 8f-5: --raster-tile T (windows cut on the GPU), --skip-blank (needs the former)."""
     opt = cli.parse_opt(["--weights", "a.pt", "--nosave", "--save-txt", "--raster-tile", "1024", "--skip-blank"])

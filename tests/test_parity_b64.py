@@ -56,7 +56,7 @@ def b64(request):
 def test_b64_plan_is_the_benchmarked_one(b64):
     _, _, _, pred, acts, stages = b64
     assert pred.shape == (B, 25200, 8)
-    assert stages, "the default plan runs the high-resolution layers in depth-first stages"
+    assert not stages, "the default plan runs every layer over the whole batch (depth-first stages measured slower)"
 
 
 def test_b64_intermediate_activations_match_oracle(b64):
@@ -75,18 +75,23 @@ def test_b64_intermediate_activations_match_oracle(b64):
 
 
 def test_b64_predictions_and_detections_match_oracle(b64):
+    """north_star's tolerances, decomposed (oracle/parity.py::compare_image): decoded confidences within 5e-3; the oracle's
+    NMS (genuine torchvision.ops.nms) on the CUDA path's own predictions reproduces its detections bit for bit; detections
+    matched by source row agree within 1e-2 (box / diagonal) and 5e-3 (conf); EVERY detection only one side keeps is
+    proven to be a threshold flip -- there is no budget of unexplained rows."""
     sd, imgs, res, pred, _, _ = b64
     ora = run_oracle(sd, imgs, CHECK)
     n_ref = flips = 0
     for i in CHECK:
         rpred, _, rdet = ora[i]
-        err = np.abs(pred[i] - rpred)[:, 4:].max()
-        assert err < 5e-3, f"tile {i}: decoded confidences differ from the oracle by {err:.4f}"
-        m = parity.match_detections(torch.from_numpy(res.dets[i, :res.counts[i]]), rdet)
-        assert m["box_err"] < 1e-2 and m["conf_err"] < 5e-3, (i, m)
+        m = parity.compare_image(pred[i], res.dets[i, :res.counts[i]], rpred)
+        assert m["conf_err"] < 5e-3, f"tile {i}: decoded confidences differ from the oracle by {m['conf_err']:.4f}"
+        assert m["nms_exact"], f"tile {i}: NMS of identical predictions is not bit-exact"
+        assert m["n_ref"] == len(rdet)
+        assert m["box_err"] < 1e-2 and m["det_conf_err"] < 5e-3, (i, m)
         assert m["unexplained"] == 0, f"tile {i}: {m['unexplained']} one-sided detections that are not threshold flips ({m})"
-        n_ref += len(rdet)
-        flips += m["flips"]
+        n_ref += m["n_ref"]
+        flips += m["flips_conf"] + m["flips_iou"] + m["flips_order"] + m["flips_cascade"]
     assert n_ref > 0, "no detections: the check would be vacuous"
     assert flips <= max(2, n_ref // 20), (flips, n_ref)  # flips are proven above; this only guards against a systematic bias
 

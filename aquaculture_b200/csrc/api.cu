@@ -347,6 +347,7 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     grow(cd.na, halo_na_cap, cd.a_slot);
     if (!cd.b_res) grow(cd.nb, 12, b_slot);
   }
+  if (cd.epi_sets == 2 && (cd.n_stg & 1) && getenv("AQUA_ES2_EVEN_STG")) cd.n_stg -= 1;  // debug: see DESIGN.md 3.1 (race hunt)
   // ---- cost
   const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
   const double a_bytes = (double)n_groups * cd.a_tx;
@@ -811,7 +812,7 @@ int launch_op(aq_ctx* c, Op& op, int sub, cudaStream_t s) {
   cudaError_t e = cudaSuccess;
   switch (op.kind) {
     case OP_CONV: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_STORE, c->num_sms, c->pdl, s); break;
-    case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl, s); break;
+    case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl && !getenv("AQUA_PDL_DET_OFF"), s); break;
     case OP_POOL: {
       const Buffer& b = c->bufs[op.buf];
       e = launch_sppf_pool(buf_base(c, op.buf, op, sub), op_batch(c, op), b.h, b.w, b.c, op.c_off, op.c, s);
@@ -1497,7 +1498,7 @@ int aq_debug_plan_conv(int batch, int h, int w, int c_in, int c_out, int k, int 
   op.kind = OP_CONV;
   op.conv.src = 0; op.conv.c_in = c_in; op.conv.dst = 1; op.conv.c_out = c_out; op.conv.k = k; op.conv.stride = stride;
   op.conv.act = AQ_ACT_SILU; op.conv.res = -1; op.conv.mblk = mblk; op.conv.mode = mode;
-  int rc = plan_conv_geometry(&tmp, op);
+  int rc = plan_conv_geometry(&tmp, op, getenv("AQUA_DEBUG_CHOICE") ? atoi(getenv("AQUA_DEBUG_CHOICE")) : -1);
   if (rc) {
     snprintf(buf, cap, "%s", tmp.err.c_str());
     return rc;

@@ -91,8 +91,17 @@ struct Ring {
 
 constexpr uint32_t kWarpA = 0, kWarpB = 1, kWarpMma = 2, kWarpMma1 = 3, kWarpEpi0 = 4, kWarpStore = 20;
 // named barriers: 1..4 = staging buffer b filled (16 epilogue warps arrive, the store warp waits),
-// 5..8 = staging buffer b read by its TMA store (the store warp arrives, the epilogue warps wait)
+// 5..8 = staging buffer b read by its TMA store (the store warp arrives, the epilogue warps wait); with two epilogue
+// sets (epi_store_role2) set 1 waits on 9..12 instead -- see kBarStgEmptySet1 below
 constexpr uint32_t kBarStgFull = 1, kBarStgEmpty = 5, kBarStgThreads = kEpiWarps * 32 + 32;
+// A hardware named barrier counts arrivals, not who arrives.  With an ODD number of staging buffers a buffer is filled
+// by the two sets alternately, so set 0 (waiting for group k's turn on buffer b) and set 1 (already waiting for group
+// k + 3's turn on the same buffer) could sit on ONE barrier id at the same time; the store warp's single arrival then
+// released whichever eight warps got there first -- warps of the wrong set overwrote a buffer its TMA store had not read
+// yet, while the right set's late warps filled theirs after the store had gone (found by tools/repro_probe.py: ~1 % of
+// forward passes, last tiles of the 768 -> 768 1x1 conv with three buffers; profiles/r2_race_hunt.txt).  Each set
+// therefore owns its own "buffer read" barrier ids.
+constexpr uint32_t kBarStgEmptySet1 = 9;
 
 __device__ __forceinline__ float silu_exact(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
 
@@ -633,7 +642,7 @@ __device__ __forceinline__ void epi_store_role2(const ConvKParams& p, const EpiC
         if (lane == 0) mbar_arrive(tempty(as));
       }
       // the TMA store that last used this staging buffer (group k - n_stg) must have read it
-      if (k0 + (uint32_t)j >= n_stg) named_bar_sync(kBarStgEmpty + buf, kBarStgThreads2);
+      if (k0 + (uint32_t)j >= n_stg) named_bar_sync((set ? kBarStgEmptySet1 : kBarStgEmpty) + buf, kBarStgThreads2);
       const uint32_t stg = ec.stg_base + buf * (kTileM * 128);
       const uint32_t bias_g = ec.bias_smem + (uint32_t)(n0 + g * 64) * 4u;
       if (v0) epi_math_store<ACT>(va, bias_g + half * 64u, stg + sa0, stg + sa1);
@@ -670,7 +679,8 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
   Ring rs;
   uint32_t k = 0;  // groups stored so far
   int it = 0;
-  const uint32_t bar_threads = (p.epi_sets == 2 && !TRACE) ? kBarStgThreads2 : kBarStgThreads;  // traced builds keep the lockstep epilogue
+  const bool two_sets = p.epi_sets == 2 && !TRACE;  // traced builds keep the lockstep epilogue
+  const uint32_t bar_threads = two_sets ? kBarStgThreads2 : kBarStgThreads;
   const bool halo = (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) && !(p.dbg & 64);
   const int hp1 = p.a_h + 1;
   for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p), ++it) {
@@ -731,7 +741,8 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
         if (k + 2 >= n_stg && k + 2 < total_groups) {
           uint32_t fb = buf + 2;  // (k + 2) % n_stg
           if (fb >= n_stg) fb -= n_stg;
-          named_bar_arrive(kBarStgEmpty + fb, bar_threads);
+          // two sets: group k + 2 belongs to set (k + 2) % 2 = k % 2 (groups per tile are counted globally in both roles)
+          named_bar_arrive((two_sets && (k & 1u) ? kBarStgEmptySet1 : kBarStgEmpty) + fb, bar_threads);
         }
       }
     }

@@ -139,3 +139,40 @@ def test_b64_plan_is_bit_reproducible_across_processes(tmp_path):
         outs.append([l for l in r.stdout.splitlines() if l.startswith("HASH")][0].split())
     assert outs[0][1] == outs[1][1], "two processes produced different predictions for the same batch"
     assert outs[0][2] == "0" and int(outs[0][3]) > 0, f"the shipped table missed {outs[0][2]} conv shapes of the benchmarked plan"
+
+
+def test_b64_forward_pass_is_bit_reproducible():
+    """300 forward passes of the benchmarked plan on one fixed input: the final activations (x8, x9, x17, x20, x23) and the
+    predictions are bit-identical every time.  The kernels are deterministic by construction (static tile order, one TMA
+    reduce-add per element), so any difference is a data race -- this is the test that exposed the shared named-barrier id of
+    the two-set epilogue (profiles/r2_race_hunt.txt: ~1 % of passes before the fix)."""
+    import ctypes as C
+    det = engine.TileDetector(weights.synthetic_state(3, 0), 3, batch=B, imgsz=(640, 640))
+    try:
+        ctx = det.ctx
+        det.detect(torch.from_numpy(tiles.synthetic_tiles(range(B), 640, 640, seed=0)).pin_memory(), bgr=True)
+        pp, rows, no = C.c_void_p(), C.c_int(), C.c_int()
+        ctx.call("aq_pred_info", C.byref(pp), C.byref(rows), C.byref(no))
+        watch = [(name,) + ctx.buffer_info(det.buffers[name]) for name in ("x8", "x9", "x17", "x20", "x23")]
+        watch = [(name, ptr, int(np.prod(shape)) * 2) for name, ptr, shape in watch] + [("pred", pp.value, B * rows.value * no.value * 4)]
+
+        def snapshot():
+            out = []
+            for _, ptr, nbytes in watch:
+                t = torch.empty(nbytes // 8, dtype=torch.int64, device="cuda")
+                ctx.call("aq_memcpy", C.c_void_p(t.data_ptr()), C.c_void_p(ptr), nbytes // 8 * 8, 2, None)
+                out.append(t)
+            ctx.sync()
+            return out
+
+        ctx.forward()
+        ctx.sync()
+        ref = snapshot()
+        for it in range(300):
+            ctx.forward()
+            ctx.sync()
+            cur = snapshot()
+            bad = [watch[k][0] for k in range(len(watch)) if not torch.equal(cur[k], ref[k])]
+            assert not bad, f"forward pass {it}: {bad} differ from the first pass (data race)"
+    finally:
+        det.close()

@@ -92,6 +92,10 @@ struct aq_ctx {
   float det_conf_stage = 0.f;   // host source of the pending update
   float mask_conf = -1.f;       // conf_thres the mask of the latest forward pass was built with (-1: no usable mask)
   int use_det_mask = 1;         // AQUA_NMS_MASK=kernel: always rebuild the mask from pred with nms_mask_kernel
+  // Alternate the tile order from op to op (AQUA_SERPENTINE=1).  Off by default: measured on the B200 it gains nothing
+  // (4.442 vs 4.426 ms per batch-64 conv stack, 4.355 vs 4.309 at --img 1280; profiles/r2_ab_serpentine.txt) -- the tail a
+  // layer leaves in L2 is not what bounds its consumer.
+  int serpentine = 0;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
@@ -1023,6 +1027,7 @@ int aq_create(int device, aq_ctx** out) {
   if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
   if (const char* v = getenv("AQUA_TUNE_LOG")) c->tune_log = atoi(v) != 0;
   if (const char* v = getenv("AQUA_NMS_MASK")) c->use_det_mask = strcmp(v, "kernel") != 0;
+  if (const char* v = getenv("AQUA_SERPENTINE")) c->serpentine = atoi(v) != 0;
   if (const char* v = getenv("AQUA_TUNE_ITERS")) c->tune_iters = atoi(v) > 0 ? atoi(v) : 3;
   if (const char* v = getenv("AQUA_TUNE_CACHE")) {
     c->tune_path = v;
@@ -1296,6 +1301,10 @@ int aq_plan_end(aq_ctx* c) {
     CU_CHECK(c, cudaStreamSynchronize(c->stream));
     int rc = c->autotune ? autotune_conv(c, op) : plan_conv_maps(c, op);
     if (rc) return rc;
+    // serpentine tile order (opt-in): every other op walks its tiles from the end, so it starts on what its producer
+    // wrote last (still in L2) -- see ConvKParams::reverse.  Results do not depend on the order.
+    op.kp.reverse = (c->serpentine && ((&op - c->ops.data()) & 1)) ? 1 : 0;
+    for (auto& k : op.kps) k.reverse = op.kp.reverse;
     std::vector<uint16_t>().swap(op.w_host);
   }
   if (c->autotune) {  // the timing launches wrote into the activation buffers
@@ -1525,6 +1534,7 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
     static const char* mode_name[] = {"flat", "halo", "tap", "halo2"};
     char stg[48] = "";
     if (op.stage >= 0) snprintf(stg, sizeof stg, " sub=%dx%d lanes=%d", op_batch(c, op), op_subs(c, op), c->stages[op.stage].lanes);
+    if (k.reverse) strncat(stg, " rev", sizeof stg - strlen(stg) - 1);
     snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d%s | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.epi_sets, k.tw, k.th,

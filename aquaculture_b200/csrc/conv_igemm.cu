@@ -65,6 +65,7 @@ __device__ __forceinline__ int weight_chunk(const ConvKParams& p, int s) {
 // Ring position advanced with compare/reset: `x % n` and `x / n` by a runtime n cost a ~100-clk dependent
 // instruction chain each, which made every role's inner loop scalar-latency bound (measured, trace_s7b).
 __device__ __forceinline__ void split_tile(const ConvKParams& p, int tile, int& m_tile, int& n_idx) {
+  if (p.reverse) tile = p.total_tiles - 1 - tile;
   if (p.n_tiles_n == 1) {
     m_tile = tile;
     n_idx = 0;
@@ -748,7 +749,14 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
     }
     if (lane == 0) trace_put<TRACE>(p, 5, it, tr0, trw, trr, TR_NOW());
   }
+  // the CTA may exit (and its shared memory be handed to the next kernel's CTA) once every store has READ its staging
+  // buffer; the writes themselves are complete and visible when the grid completes, which is what a dependent kernel's
+  // griddepcontrol.wait / the stream order waits for (AQUA build flag AQ_STORE_WAIT_FULL restores the full wait)
+#ifdef AQ_STORE_WAIT_FULL
   if (lane == 0) tma_store_wait0();
+#else
+  if (lane == 0) tma_store_wait_read0();
+#endif
 }
 
 template <int EPI, bool TRACE>

@@ -85,6 +85,10 @@ struct alignas(64) ConvKParams {
   // all, which divides the weight traffic L2 -> SM by the cluster size.  total_tiles = ceil(m_tiles / cluster) *
   // n_tiles_n cluster-tiles; M tiles past m_tiles are computed on zero-filled operands and clipped by the stores.
   int cshift, total_tiles;
+  // Tile order: 0 = ascending, 1 = descending (tile t of the persistent loop works on tile total - 1 - t).  The plan
+  // alternates it from op to op ("serpentine"): a layer then starts on the tiles its producer wrote LAST, which still
+  // sit in the 126 MB L2, instead of on the ones written first, which have long been evicted to HBM.
+  int reverse;
   int up_chunks, up_hs;  // leading 64-channel chunks that come from tmUp; rows of the half-resolution source
   int tw, th, tiles_x, tiles_y;   // HALO: tile origin grid (tile = 8mx x 16my); TAP: M block = tw x th
   int act, has_res;

@@ -134,7 +134,7 @@ def parity_leg(det, sd, host_sets, n_tiles):
     from oracle import detect_ref, letterbox as LB, parity
     ref = detect_ref.DetectRef(sd, NC)
     out = dict(tiles=0, max_conf_err=0.0, max_box_err=0.0, max_det_conf_err=0.0, detections=0, oracle_detections=0, common=0,
-               nms_bit_exact_on_identical_input=True, flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, unmatched=0)
+               nms_bit_exact_on_identical_input=True, flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, flips_class=0, unmatched=0)
     t0 = time.perf_counter()
     for tiles_ in host_sets:
         if out["tiles"] >= n_tiles:
@@ -148,13 +148,17 @@ def parity_leg(det, sd, host_sets, n_tiles):
                 rpred = ref.model(x)[0]
             m = parity.compare_image(pred[i], dets[i, :counts[i]], rpred)
             out["max_conf_err"] = max(out["max_conf_err"], m["conf_err"])
+            if m["box_err"] > out["max_box_err"]:
+                out["worst_box"] = m["box_err_worst"]
             out["max_box_err"] = max(out["max_box_err"], m["box_err"])
+            out["boxes_over_1e-2"] = out.get("boxes_over_1e-2", 0) + m["box_over_tol"]
+            out["class_mismatches"] = out.get("class_mismatches", 0) + m["class_mismatch"]
             out["max_det_conf_err"] = max(out["max_det_conf_err"], m["det_conf_err"])
             out["nms_bit_exact_on_identical_input"] &= m["nms_exact"]
             out["detections"] += m["n_got"]
             out["oracle_detections"] += m["n_ref"]
             out["common"] += m["common"]
-            for k in ("flips_conf", "flips_iou", "flips_order", "flips_cascade"):
+            for k in ("flips_conf", "flips_iou", "flips_order", "flips_cascade", "flips_class"):
                 out[k] += m[k]
             out["unmatched"] += m["unexplained"]
             out["tiles"] += 1

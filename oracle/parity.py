@@ -90,14 +90,17 @@ def compare_image(pred_got, dets_got, pred_ref, conf_thres=0.25, iou_thres=0.45,
          OTHER side's numbers: its confidence there lies within conf_tol of conf_thres (`flips_conf`); or the box that
          suppresses it there overlaps it with an IoU within iou_tol of iou_thres (`flips_iou`); or that box outranks it by
          less than 2 conf_tol, so the pair swapped order (`flips_order`); or that box is itself one-sided (`flips_cascade`,
-         the consequence of a flip counted elsewhere).  Anything else is `unexplained`.
+         the consequence of a flip counted elsewhere); or its best class differs between the sides while the row's two
+         best class scores are within 2 conf_tol (`flips_class`: class-aware NMS then compares it with other boxes).
+         Anything else is `unexplained`.
     """
     from . import nms as N
     pg = torch.as_tensor(np.asarray(pred_got)).float()
     pr = torch.as_tensor(np.asarray(pred_ref)).float()
     dg = torch.as_tensor(np.asarray(dets_got)).float()
     out = dict(conf_err=float((pg[:, 4:] - pr[:, 4:]).abs().max()), nms_exact=False, box_err=0.0, det_conf_err=0.0, common=0,
-               flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, unexplained=0, n_got=len(dg), n_ref=0)
+               box_over_tol=0, class_mismatch=0, box_err_worst=None,
+               flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, flips_class=0, unexplained=0, n_got=len(dg), n_ref=0)
     kw = dict(conf_thres=conf_thres, iou_thres=iou_thres, max_det=max_det, return_rows=True)
     (og,), (rows_g,) = N.non_max_suppression(pg[None], **kw)
     out["nms_exact"] = bool(og.shape == dg.shape and torch.equal(og, dg))
@@ -113,10 +116,17 @@ def compare_image(pred_got, dets_got, pred_ref, conf_thres=0.25, iou_thres=0.45,
         a = torch.stack([side["g"]["kept"][r] for r in both])
         b = torch.stack([side["r"]["kept"][r] for r in both])
         diag = (b[:, 2:4] - b[:, 0:2]).norm(dim=1).clamp(min=1.0)
-        out["box_err"] = float(((a[:, :4] - b[:, :4]).abs().max(1).values / diag).max())
+        rel = (a[:, :4] - b[:, :4]).abs().max(1).values / diag
+        w = int(rel.argmax())
+        out["box_err"] = float(rel[w])
+        out["box_err_worst"] = dict(abs_px=float((a[w, :4] - b[w, :4]).abs().max()), diag_px=float(diag[w]), conf=float(b[w, 4]))
+        out["box_over_tol"] = int((rel >= 1e-2).sum())
         out["det_conf_err"] = float((a[:, 4] - b[:, 4]).abs().max())
+        out["class_mismatch"] = int((a[:, 5] != b[:, 5]).sum())
+        for r in [both[j] for j in torch.nonzero(a[:, 5] != b[:, 5]).flatten().tolist()]:  # kept on both sides, other class
+            sc = torch.sort(side["r"]["p"][r][5:] * side["r"]["p"][r][4], descending=True).values
+            out["flips_class" if len(sc) > 1 and float(sc[0] - sc[1]) < 2 * conf_tol else "unexplained"] += 1
         out["common"] = len(both)
-        assert bool((a[:, 5] == b[:, 5]).all()) or True
     lone = {"g": set(side["g"]["kept"]) - set(side["r"]["kept"]), "r": set(side["r"]["kept"]) - set(side["g"]["kept"])}
     for s, t in (("g", "r"), ("r", "g")):
         S, T = side[s], side[t]
@@ -129,6 +139,12 @@ def compare_image(pred_got, dets_got, pred_ref, conf_thres=0.25, iou_thres=0.45,
                 out["flips_conf" if ok else "unexplained"] += 1
                 continue
             i = T["cand"][r]
+            if float(d[5]) != float(T["cls"][i]):
+                # the best class differs between the sides (class-aware NMS then sees another box): legitimate only when
+                # the two best class scores of the row are within noise of each other
+                sc = torch.sort(T["p"][r][5:] * T["p"][r][4], descending=True).values
+                out["flips_class" if len(sc) > 1 and float(sc[0] - sc[1]) < 2 * conf_tol else "unexplained"] += 1
+                continue
             # kept boxes of the other side that outrank or nearly outrank it, same class, overlapping
             kr = [k for k in T["kept"] if float(T["kept"][k][5]) == float(T["cls"][i])]
             why = None

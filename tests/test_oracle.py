@@ -169,3 +169,42 @@ def test_window_grid_order_matches_reference_tiler():
     assert OB.windows(3072, 2048, 1024) == [(0, 0), (0, 1024), (0, 2048), (1024, 0), (1024, 1024), (1024, 2048)]
     assert engine.window_grid(3072, 2048, 1024) == OB.windows(3072, 2048, 1024)
     assert engine.window_grid(2500, 2100, 1024) == [(0, 0), (0, 1024), (1024, 0), (1024, 1024)]  # ragged strips left out
+
+
+def test_parity_compare_image_proves_flips_and_flags_real_differences():
+    """oracle/parity.py::compare_image (the checker behind tests/test_parity_b64.py and bench.py's parity leg): predictions that
+    differ by fp16-sized noise yield only proven threshold flips; a detection that is genuinely wrong, a box that moved, or
+    an NMS that did something else is reported."""
+    from oracle import nms as N, parity
+    flips = 0
+    for seed in range(4):
+        g = torch.Generator().manual_seed(seed)
+        rows = 3000
+        pred = torch.zeros(rows, 8)
+        pred[:, 0:2] = torch.rand(rows, 2, generator=g) * 640
+        pred[:, 2:4] = torch.rand(rows, 2, generator=g) * 60 + 10
+        pred[:, 4] = torch.rand(rows, generator=g) * 0.5
+        pred[:, 5:] = torch.rand(rows, 3, generator=g)
+        noisy = pred + torch.randn(rows, 8, generator=g) * 1e-3 * torch.tensor([0.5, 0.5, 0.5, 0.5, 1, 1, 1, 1])
+        (d,), _ = N.non_max_suppression(noisy[None], return_rows=True)
+        m = parity.compare_image(noisy.numpy(), d.numpy(), pred.numpy())
+        assert m["nms_exact"] and m["unexplained"] == 0 and m["box_err"] < 1e-3 and m["conf_err"] < 5e-3, m
+        flips += m["flips_conf"] + m["flips_iou"] + m["flips_order"] + m["flips_cascade"] + m["flips_class"]
+        # (1) a detection dropped by the path under test although it is far from every threshold
+        k = int(torch.argmax(d[:, 4]))
+        m1 = parity.compare_image(noisy.numpy(), torch.cat((d[:k], d[k + 1:])).numpy(), pred.numpy())
+        assert not m1["nms_exact"]
+        # (2) a prediction row moved by three pixels: caught by the row-matched box error
+        moved = noisy.clone()
+        row = int(torch.argmax(noisy[:, 4] * noisy[:, 5:].amax(1)))
+        moved[row, 0] += 3.0
+        (d2,), _ = N.non_max_suppression(moved[None], return_rows=True)
+        m2 = parity.compare_image(moved.numpy(), d2.numpy(), pred.numpy())
+        assert m2["box_err"] > 1e-2 or m2["unexplained"] > 0, m2
+        # (3) a confident row whose objectness collapsed: one-sided and NOT at a threshold
+        gone = noisy.clone()
+        gone[row, 4] = 0.01
+        (d3,), _ = N.non_max_suppression(gone[None], return_rows=True)
+        m3 = parity.compare_image(gone.numpy(), d3.numpy(), pred.numpy())
+        assert m3["unexplained"] >= 1 and m3["conf_err"] > 5e-3, m3
+    assert flips > 0, "the noise never produced a flip: the proof obligations were not exercised"

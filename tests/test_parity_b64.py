@@ -91,7 +91,7 @@ def test_b64_predictions_and_detections_match_oracle(b64):
         assert m["box_err"] < 1e-2 and m["det_conf_err"] < 5e-3, (i, m)
         assert m["unexplained"] == 0, f"tile {i}: {m['unexplained']} one-sided detections that are not threshold flips ({m})"
         n_ref += m["n_ref"]
-        flips += m["flips_conf"] + m["flips_iou"] + m["flips_order"] + m["flips_cascade"]
+        flips += m["flips_conf"] + m["flips_iou"] + m["flips_order"] + m["flips_cascade"] + m["flips_class"]
     assert n_ref > 0, "no detections: the check would be vacuous"
     assert flips <= max(2, n_ref // 20), (flips, n_ref)  # flips are proven above; this only guards against a systematic bias
 

@@ -125,14 +125,14 @@ def measured_traffic():
     return float(d["conv_stack_dram_bytes"]), f"ncu dram__bytes_read.sum + dram__bytes_write.sum over the conv-stack launches of one 64-tile batch ({TRAFFIC_FILE})"
 
 
-def parity_leg(det, sd, host_sets, n_tiles):
+def parity_leg(det, sd, host_sets, n_tiles, threads=None):
     """the same run diffs its detections with the oracle on the first `n_tiles` tiles of the benchmark's own
     input (plan = the benchmarked one: batch 64, shipped tilings).  oracle/parity.py::compare_image per tile: decode
     parity, NMS bit-exactness on identical input, detections matched by source row, every one-sided detection proven to be
     a threshold flip.  The oracle is the checker here, never the product."""
     import torch
     from oracle import detect_ref, letterbox as LB, parity
-    ref = detect_ref.DetectRef(sd, NC)
+    ref = detect_ref.DetectRef(sd, NC, threads=threads)  # torchrun exports OMP_NUM_THREADS=1: ask for the cores explicitly
     out = dict(tiles=0, max_conf_err=0.0, max_box_err=0.0, max_det_conf_err=0.0, detections=0, oracle_detections=0, common=0,
                nms_bit_exact_on_identical_input=True, flips_conf=0, flips_iou=0, flips_order=0, flips_cascade=0, flips_class=0, unmatched=0)
     t0 = time.perf_counter()
@@ -166,8 +166,10 @@ def parity_leg(det, sd, host_sets, n_tiles):
         out[k] = round(out[k], 6)
     out["tolerances"] = ("decoded conf 5e-3; detections matched by source row: box 1e-2 of the diagonal, conf 5e-3 (north_star); flips_* = "
                          "one-sided detections proven to be conf / IoU / order threshold flips from the other side's numbers; unmatched = the rest")
-    out["ok"] = bool(out["max_conf_err"] < 5e-3 and out["max_box_err"] < 1e-2 and out["max_det_conf_err"] < 5e-3 and out["unmatched"] == 0
-                     and out["nms_bit_exact_on_identical_input"])
+    out["within_tolerance"] = {"decoded_conf_5e-3": bool(out["max_conf_err"] < 5e-3), "detection_conf_5e-3": bool(out["max_det_conf_err"] < 5e-3),
+                               "box_1e-2_of_diagonal": bool(out["max_box_err"] < 1e-2), "nms_bit_exact": bool(out["nms_bit_exact_on_identical_input"]),
+                               "no_unexplained_detection": bool(out["unmatched"] == 0)}
+    out["ok"] = all(out["within_tolerance"].values())
     out["oracle_s"] = round(time.perf_counter() - t0, 1)
     return out
 
@@ -592,7 +594,9 @@ def main():
         out["tilings"] = {"table_entries": ctx.tuned_entries, "shapes_timed_at_plan_time": ctx.call("aq_tune_misses"),
                           "note": "shipped table aquaculture_b200/tuned/b200.txt decides every tiling: identical in every process / rank"}
         if args.parity_tiles > 0:
-            out["parity"] = parity_leg(det, sd, host_sets, args.parity_tiles)
+            # bounded: the oracle is ~50 ms per tile on 16 cores; a scaling run (N > 1) diffs one batch instead of four
+            out["parity"] = parity_leg(det, sd, host_sets, args.parity_tiles if world == 1 else min(args.parity_tiles, BATCH),
+                                       threads=len(os.sched_getaffinity(0)))
         if ji is not None:
             out["jpeg_ingest"] = ji
         if not args.no_extra_configs:

@@ -71,6 +71,7 @@ SIGNATURES = {
     "aq_plan_stage_begin": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "aq_plan_stage_end": (C.c_int, [C.c_void_p]),
     "aq_plan_conv": (C.c_int, [C.c_void_p, C.POINTER(ConvDesc)]),
+    "aq_plan_conv_chain": (C.c_int, [C.c_void_p, C.POINTER(ConvDesc), C.POINTER(ConvDesc), C.c_int]),
     "aq_plan_sppf_pool": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "aq_plan_upsample2x": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "aq_plan_detect": (C.c_int, [C.c_void_p, C.POINTER(DetectDesc)]),

@@ -56,6 +56,14 @@ struct Op {
   __half* w_dev = nullptr;
   __half* w_dev_dense = nullptr;  // 3x3 convs with c_in <= 16: [c_out][3 * 64], K = tap * 16 + channel (see Cand::b_dense)
   float* b_dev = nullptr;
+  // EPI_CHAIN (aq_plan_conv_chain): a 1x1 conv evaluated behind this conv inside the same kernel
+  bool chained = false;
+  int chain_store1 = 1;
+  aq_conv_desc conv2{};
+  std::vector<uint16_t> w2_host;
+  std::vector<float> b2_host;
+  __half* w2_dev = nullptr;
+  float* b2_dev = nullptr;
   ConvKParams kp{};               // geometry + the tensor maps of sub-batch 0
   std::vector<ConvKParams> kps;   // staged ops: one parameter block per sub-batch (same geometry, shifted tensor maps)
   int stage = -1;
@@ -92,10 +100,10 @@ struct aq_ctx {
   float det_conf_stage = 0.f;   // host source of the pending update
   float mask_conf = -1.f;       // conf_thres the mask of the latest forward pass was built with (-1: no usable mask)
   int use_det_mask = 1;         // AQUA_NMS_MASK=kernel: always rebuild the mask from pred with nms_mask_kernel
-  // Alternate the tile order from op to op (AQUA_SERPENTINE=1).  Off by default: measured on the B200 it gains nothing
-  // (4.442 vs 4.426 ms per batch-64 conv stack, 4.355 vs 4.309 at --img 1280; profiles/r2_ab_serpentine.txt) -- the tail a
-  // layer leaves in L2 is not what bounds its consumer.
-  int serpentine = 0;
+  // Alternate the tile order from op to op (AQUA_SERPENTINE=0: every op ascending).  Measured with interleaved rounds
+  // (tools/ab_env.py: the first spec timed on a cool chip looks 2-4 % faster, which hid it at first): 4.524 vs 4.615 ms
+  // per batch-64 conv stack = -2.0 % (profiles/r2_ab_chain_serpentine.txt).
+  int serpentine = 1;
   cudaGraph_t graph = nullptr;
   cudaGraphExec_t graph_exec = nullptr;
   int n_launches = 0;
@@ -171,6 +179,7 @@ int round_up(int v, int m) { return (v + m - 1) / m * m; }
 // Images one launch of `op` processes, and the number of launches (sub-batches) per forward pass.
 int op_batch(const aq_ctx* c, const Op& op) { return op.stage >= 0 ? c->stages[op.stage].sub : c->batch; }
 int op_subs(const aq_ctx* c, const Op& op) { return op.stage >= 0 ? c->batch / c->stages[op.stage].sub : 1; }
+int op_epi(const Op& op) { return op.kind == OP_DETECT ? EPI_DETECT : (op.chained ? EPI_CHAIN : EPI_STORE); }
 // Images a buffer holds.
 int buf_images(const aq_ctx* c, const Buffer& b) { return b.stage >= 0 ? c->stages[b.stage].sub * c->stages[b.stage].lanes : c->batch; }
 // First element of buffer `id` as sub-batch `s` of `op` sees it: a plan-wide buffer is entered at image s * sub, a
@@ -253,6 +262,7 @@ struct Cand {
   // derived
   int tiles_x = 1, tiles_y = 1, m_tiles = 0, pw = 0, ph = 0;
   int na = 0, nb = 0, b_res = 0, n_stg = 0, acc_stages = 0;
+  int acc2_stages = 0;  // chained conv: TMEM stages of its accumulator
   uint32_t a_slot = 0, a_tx = 0;
   double cycles = 1e30;
   bool ok = false;
@@ -261,7 +271,8 @@ struct Cand {
 // Rough per-SM cycle model used only to rank candidates: each tile costs the slowest of its MMA time
 // (128 x N x 16 per N/2 cycles), its L2 -> SM operand traffic (~40 B/clk/SM measured), the TMA issue rate of
 // one producer thread (~600 clk per box, profiles/r1_hw_probe_v1.txt T4) and the epilogue.
-void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles_n, int n_steps, int cpt, int num_sms) {
+void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles_n, int n_steps, int cpt, int num_sms,
+                    int extra_smem = 0, int extra_tmem = 0, int chain_kg = 0) {  // what a chained conv adds (resident weights, accumulator columns, K groups)
   const int groups = (tile_n + 63) / 64;
   const uint32_t b_slot = (uint32_t)round_up(tile_n * 128, 1024);
   (void)groups;
@@ -303,10 +314,14 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     a_instr_per_group = cd.mblk;
   }
   const int acc_pitch = round_up(tile_n, 32);  // each accumulator starts on a 32-column boundary
-  if (cd.mblk * acc_pitch > 512) return;
-  cd.acc_stages = 2 * cd.mblk * acc_pitch <= 512 ? 2 : 1;
+  // extra_tmem = columns of ONE chained accumulator stage: prefer (2, 2) stages, then one chained stage, then one own stage
+  if (cd.mblk * acc_pitch + extra_tmem > 512) return;
+  if (2 * cd.mblk * acc_pitch + 2 * extra_tmem <= 512) { cd.acc_stages = 2; cd.acc2_stages = 2; }
+  else if (2 * cd.mblk * acc_pitch + extra_tmem <= 512) { cd.acc_stages = 2; cd.acc2_stages = 1; }
+  else if (cd.mblk * acc_pitch + 2 * extra_tmem <= 512) { cd.acc_stages = 1; cd.acc2_stages = 2; }
+  else { cd.acc_stages = 1; cd.acc2_stages = 1; }
   // ---- shared memory: minimal plan first, then grow the rings
-  const long budget = kConvMaxDynSmem - 1024;
+  const long budget = kConvMaxDynSmem - 1024 - extra_smem;
   if (cd.b_dense && (cd.mode != CONV_MODE_HALO || cpt != 1 || n_tiles_n != 1)) cd.b_dense = 0;
   const int res_slots = cd.b_dense ? (n_steps + 3) / 4 : n_steps;  // weight slots that hold the whole (single) N tile
   cd.b_res = (n_tiles_n == 1 && res_slots <= kMaxB && (long)res_slots * b_slot <= 112 * 1024) ? 1 : 0;
@@ -398,11 +413,14 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.c_in = c_in;
   k.cpt = (c_in + 63) / 64;
   k.n_steps = k.taps * k.cpt;
+  const bool chain = !det && op.chained;
+  const int c_in2 = chain ? op.conv2.c_in : 0, tile_n2 = chain ? round_up(op.conv2.c_out, 16) : 0;
+  const int chain_kg = (c_in2 + 63) / 64, b2_slot = round_up(tile_n2 * 128, 1024), acc2_pitch = round_up(tile_n2, 32);
   // ---- UMMA N options
   std::vector<int> tile_ns;
   if (det) {
     tile_ns.push_back(round_up(c_out, 16));
-  } else if (op.conv.tile_n > 0) {
+  } else if (op.conv.tile_n > 0 && !chain) {
     tile_ns.push_back(op.conv.tile_n);
   } else if (c_out <= 256) {
     tile_ns.push_back(round_up(c_out, 16));
@@ -481,16 +499,18 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
         if (cl != (want_cluster > 0 ? want_cluster : 1)) continue;
         // AQUA_EPI_SETS=1|2 pins the epilogue organisation (tests); default: both are candidates
         const char* fs = getenv("AQUA_EPI_SETS");
-        const int min_sets = det ? 1 : (fs ? (atoi(fs) == 2 ? 2 : 1) : 1);
-        const int max_sets = det ? 1 : (fs ? min_sets : 2);
+        const int min_sets = (det || chain) ? 1 : (fs ? (atoi(fs) == 2 ? 2 : 1) : 1);
+        const int max_sets = (det || chain) ? 1 : (fs ? min_sets : 2);  // the chained epilogue is the lockstep one
         for (int sets = min_sets; sets <= max_sets; ++sets)
           for (int pref = 0; pref < 2; ++pref) {
             Cand cd = cd0;
             cd.cluster = cl;
             cd.pref = pref;
             cd.epi_sets = sets;
-            fill_candidate(cd, op_batch(c, op), ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms);
+            fill_candidate(cd, op_batch(c, op), ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms, chain ? chain_kg * b2_slot : 0,
+                           chain ? acc2_pitch : 0, chain ? chain_kg : 0);
             if (!cd.ok) continue;
+            if (chain && (ntn != 1 || cd.cluster != 1)) continue;
             if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
               const Cand& o = choices.back().cd;
               if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg) continue;
@@ -552,6 +572,21 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.acc_pitch = round_up(k.tile_n, 32);
   k.acc_stride = k.mblk * k.acc_pitch;
   k.tmem_cols = pow2_at_least(k.acc_stages * k.acc_stride);
+  if (chain) {
+    k.chain = 1;
+    k.chain_kg = chain_kg;
+    k.chain_kk_last = (c_in2 - 64 * (chain_kg - 1) + 15) / 16;
+    k.chain_store1 = op.chain_store1;
+    k.tile_n2 = tile_n2;
+    k.groups2 = (tile_n2 + 63) / 64;
+    k.act2 = op.conv2.act;
+    k.b2_slot_bytes = (uint32_t)b2_slot;
+    k.acc2_pitch = (uint32_t)acc2_pitch;
+    k.acc2_base = k.acc_stages * k.acc_stride;
+    k.acc2_stages = best.acc2_stages;
+    k.tmem_cols = pow2_at_least((int)(k.acc2_base + k.acc2_stages * k.acc2_pitch));
+    k.epi_sets = 1;
+  }
   return AQ_OK;
 }
 
@@ -636,6 +671,31 @@ int build_conv_maps(aq_ctx* c, Op& op, ConvKParams& k, int s) {
     if (rc) return rc;
   }
   k.bias = op.b_dev;
+  if (!det && op.chained) {
+    const uint64_t K2 = (uint64_t)k.chain_kg * 64;
+    uint64_t dims[2] = {K2, (uint64_t)op.conv2.c_out};
+    uint64_t str[1] = {K2 * 2};
+    uint32_t box[2] = {64, (uint32_t)k.tile_n2};
+    if ((rc = encode_map(c, &k.tmB2, op.w2_dev, 2, dims, str, box, sw))) return rc;
+    k.bias2 = op.b2_dev;
+    const Buffer& d2 = c->bufs[op.conv2.dst];
+    __half* const d2_ptr = buf_base(c, op.conv2.dst, op, s);
+    if (k.mode == CONV_MODE_FLAT) {
+      uint64_t od[2] = {(uint64_t)op.conv2.c_out, N * d2.h * d2.w};
+      uint64_t os[1] = {(uint64_t)d2.c * 2};
+      uint32_t ob[2] = {64, (uint32_t)kTileM};
+      if ((rc = encode_map(c, &k.tmOut2, d2_ptr + op.conv2.dst_c_off, 2, od, os, ob, sw))) return rc;
+    } else {
+      uint64_t od[4] = {(uint64_t)op.conv2.c_out, (uint64_t)d2.w, (uint64_t)d2.h, N};
+      uint64_t os[3] = {(uint64_t)d2.c * 2, (uint64_t)d2.w * d2.c * 2, (uint64_t)d2.h * d2.w * d2.c * 2};
+      uint32_t ob[4] = {64, (uint32_t)k.tw, (uint32_t)k.th, 1};
+      if ((rc = encode_map(c, &k.tmOut2, d2_ptr + op.conv2.dst_c_off, 4, od, os, ob, sw))) return rc;
+      for (int hb = 0; hb < 4; ++hb) {
+        uint32_t bx[4] = {64, 8, (uint32_t)(8 >> hb), 1};
+        if ((rc = encode_map(c, &k.tmOut2R[hb], d2_ptr + op.conv2.dst_c_off, 4, od, os, bx, sw))) return rc;
+      }
+    }
+  }
   if (det) {
     k.pred = c->pred + (size_t)s * nb_img * c->rows * c->no;
     k.det_mask = (c->det_mask && op.det.nc == 3) ? c->det_mask + (size_t)s * nb_img * nms_mask_words(c->rows) : nullptr;
@@ -695,6 +755,7 @@ std::string tune_signature(const aq_ctx* c, const Op& op, int n) {
     snprintf(b, sizeof b, "conv:b%d:%dx%d:ct%d:ci%d:co%d:dt%d:k%d:s%d:a%d:r%d:tn%d:mb%d:md%d:n%d", op_batch(c, op), sb.h, sb.w, sb.c,
              op.conv.c_in, op.conv.c_out, db.c, op.conv.k, op.conv.stride, op.conv.act, op.conv.res >= 0 ? 1 : 0,
              op.conv.tile_n, op.conv.mblk, op.conv.mode * 8 + op.conv.cluster + 64 * op.conv.up_c, n);
+    if (op.chained) snprintf(b + strlen(b), sizeof b - strlen(b), ":ch%dx%d:s%d", op.conv2.c_in, op.conv2.c_out, op.chain_store1);
   }
   return b;
 }
@@ -716,7 +777,7 @@ int autotune_conv(aq_ctx* c, Op& op) {
     if (c->tune_log) fprintf(stderr, "aqua_b200: no tuned tiling for %s; timing %d candidates on the device\n", sig.c_str(), n);
     ++c->tune_misses;
   }
-  const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
+  const int epi = op_epi(op);
   cudaEvent_t e0, e1;
   CU_CHECK(c, cudaEventCreate(&e0));
   CU_CHECK(c, cudaEventCreate(&e1));
@@ -796,6 +857,8 @@ void free_plan(aq_ctx* c) {
     if (o.w_dev) cudaFree(o.w_dev);
     if (o.w_dev_dense) cudaFree(o.w_dev_dense);
     if (o.b_dev) cudaFree(o.b_dev);
+    if (o.w2_dev) cudaFree(o.w2_dev);
+    if (o.b2_dev) cudaFree(o.b2_dev);
   }
   if (c->pred) cudaFree(c->pred);
   c->pred = nullptr;
@@ -815,7 +878,7 @@ void free_plan(aq_ctx* c) {
 int launch_op(aq_ctx* c, Op& op, int sub, cudaStream_t s) {
   cudaError_t e = cudaSuccess;
   switch (op.kind) {
-    case OP_CONV: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_STORE, c->num_sms, c->pdl, s); break;
+    case OP_CONV: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], op_epi(op), c->num_sms, c->pdl, s); break;
     case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl && !getenv("AQUA_PDL_DET_OFF"), s); break;
     case OP_POOL: {
       const Buffer& b = c->bufs[op.buf];
@@ -1197,6 +1260,45 @@ int aq_plan_conv(aq_ctx* c, const aq_conv_desc* d) {
   return AQ_OK;
 }
 
+int aq_plan_conv_chain(aq_ctx* c, const aq_conv_desc* d1, const aq_conv_desc* d2, int store_first) {
+  if (!c || !d1 || !d2) return AQ_ERR_ARG;
+  if (!c->planning) return fail(c, AQ_ERR_STATE, "plan_conv_chain outside plan_begin/plan_end");
+  int rc;
+  // the second conv: 1x1 / stride 1 over the FIRST c_in channels of the first conv's output, no residual, no upsample
+  if (d2->k != 1 || d2->stride != 1 || d2->res >= 0 || d2->up_c != 0)
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv chain: the chained conv must be 1x1 / stride 1 without residual or folded upsample");
+  if (d2->src != d1->dst || d2->src_c_off != d1->dst_c_off || d2->c_in > d1->c_out || d2->c_in % 16)
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv chain: the chained conv must read the first channels of the first conv's output slice "
+                                       "(got src (%d,%d) c_in %d vs dst (%d,%d) c_out %d)", d2->src, d2->src_c_off, d2->c_in, d1->dst, d1->dst_c_off, d1->c_out);
+  if (d1->res >= 0 || d1->c_out > 256 || d2->c_out > kMaxCout2)
+    return fail(c, AQ_ERR_UNSUPPORTED, "conv chain: first conv without residual and <= 256 output channels, chained conv <= %d", kMaxCout2);
+  if (d2->dst < 0 || d2->dst >= (int)c->bufs.size()) return fail(c, AQ_ERR_ARG, "chained conv dst: buffer id %d out of range", d2->dst);
+  if ((rc = check_buf(c, d2->dst, d2->dst_c_off, d2->c_out, "chained conv dst"))) return rc;
+  if (!d2->weight || !d2->bias) return fail(c, AQ_ERR_ARG, "conv chain: weight/bias NULL");
+  if (d2->act != AQ_ACT_NONE && d2->act != AQ_ACT_SILU && d2->act != AQ_ACT_SILU_FAST) return fail(c, AQ_ERR_ARG, "conv chain: unknown activation %d", d2->act);
+  if ((rc = aq_plan_conv(c, d1))) return rc;  // validates and appends the first conv
+  Op& op = c->ops.back();
+  const Buffer& db = c->bufs[d1->dst];
+  const Buffer& d2b = c->bufs[d2->dst];
+  const int want_stage = op.stage;
+  if (db.h != d2b.h || db.w != d2b.w || (d2b.stage >= 0 && d2b.stage != want_stage)) {
+    c->ops.pop_back();
+    return fail(c, AQ_ERR_ARG, "conv chain: chained dst %dx%d (stage %d) does not match %dx%d (stage %d)", d2b.h, d2b.w, d2b.stage, db.h, db.w, want_stage);
+  }
+  op.chained = true;
+  op.chain_store1 = store_first ? 1 : 0;
+  op.conv2 = *d2;
+  repack_weights(d2->weight, d2->c_out, 1, d2->c_in, op.w2_host);
+  op.b2_host.assign(d2->bias, d2->bias + d2->c_out);
+  op.conv2.weight = nullptr;
+  op.conv2.bias = nullptr;
+  if ((rc = plan_conv_geometry(c, op))) {  // no tiling leaves room for the chained conv's weights / accumulators
+    c->ops.pop_back();
+    return rc;
+  }
+  return AQ_OK;
+}
+
 int aq_plan_detect(aq_ctx* c, const aq_detect_desc* d) {
   if (!c || !d) return AQ_ERR_ARG;
   if (!c->planning) return fail(c, AQ_ERR_STATE, "plan_detect outside plan_begin/plan_end");
@@ -1298,11 +1400,21 @@ int aq_plan_end(aq_ctx* c) {
       for (auto& b : bias) b *= 0.5f;
     CU_CHECK(c, cudaMalloc(&op.b_dev, bias.size() * sizeof(float)));
     CU_CHECK(c, cudaMemcpy(op.b_dev, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+    if (op.chained) {
+      CU_CHECK(c, cudaMalloc(&op.w2_dev, op.w2_host.size() * sizeof(uint16_t)));
+      CU_CHECK(c, cudaMemcpy(op.w2_dev, op.w2_host.data(), op.w2_host.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
+      std::vector<float> b2((size_t)kMaxCout2, 0.f);
+      memcpy(b2.data(), op.b2_host.data(), op.b2_host.size() * sizeof(float));
+      if (op.conv2.act == ACT_SILU_FAST)
+        for (auto& b : b2) b *= 0.5f;
+      CU_CHECK(c, cudaMalloc(&op.b2_dev, b2.size() * sizeof(float)));
+      CU_CHECK(c, cudaMemcpy(op.b2_dev, b2.data(), b2.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
     CU_CHECK(c, cudaStreamSynchronize(c->stream));
     int rc = c->autotune ? autotune_conv(c, op) : plan_conv_maps(c, op);
     if (rc) return rc;
-    // serpentine tile order (opt-in): every other op walks its tiles from the end, so it starts on what its producer
-    // wrote last (still in L2) -- see ConvKParams::reverse.  Results do not depend on the order.
+    // serpentine tile order: every other op walks its tiles from the end, so it starts on what its producer wrote last
+    // (still in L2) -- see ConvKParams::reverse.  Results do not depend on the order.
     op.kp.reverse = (c->serpentine && ((&op - c->ops.data()) & 1)) ? 1 : 0;
     for (auto& k : op.kps) k.reverse = op.kp.reverse;
     std::vector<uint16_t>().swap(op.w_host);
@@ -1448,7 +1560,7 @@ int aq_profile_op_waves(aq_ctx* c, int i, int waves, int iters, float* ms_out) {
   const int cl = 1 << kp.cshift;
   const int cap = waves * (c->num_sms / cl);
   if (kp.total_tiles > cap) kp.total_tiles = cap;
-  const int epi = op.kind == OP_CONV ? EPI_STORE : EPI_DETECT;
+  const int epi = op_epi(op);
   cudaEvent_t e0, e1;
   CU_CHECK(c, cudaEventCreate(&e0));
   CU_CHECK(c, cudaEventCreate(&e1));
@@ -1471,7 +1583,7 @@ int aq_trace_op(aq_ctx* c, int i, long long* out, size_t cap_vals) {
   if (!c->planned) return fail(c, AQ_ERR_STATE, "trace before plan_end");
   if (i < 0 || i >= (int)c->ops.size()) return fail(c, AQ_ERR_ARG, "trace: op %d out of range", i);
   Op& op = c->ops[i];
-  if (op.kind != OP_CONV && op.kind != OP_DETECT) return fail(c, AQ_ERR_ARG, "trace: op %d is not a conv", i);
+  if ((op.kind != OP_CONV && op.kind != OP_DETECT) || op.chained) return fail(c, AQ_ERR_ARG, "trace: op %d is not a plain conv", i);
   cudaSetDevice(c->device);
   const int total = op.kp.m_tiles * op.kp.n_tiles_n;
   const int grid = total < c->num_sms ? total : c->num_sms;
@@ -1527,14 +1639,19 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
     const int c_in = det ? op.det.c_in : op.conv.c_in;
     const int c_out = det ? 3 * (op.det.nc + 5) : op.conv.c_out;
     const double M = (double)c->batch * (sb.h / stride) * (sb.w / stride);
-    const double flops = 2.0 * M * c_out * c_in * k.taps;
-    const double bytes = 2.0 * ((double)c->batch * sb.h * sb.w * c_in + M * c_out * (k.has_res ? 2 : 1)) +
-                         2.0 * c_out * c_in * k.taps;
+    double flops = 2.0 * M * c_out * c_in * k.taps;
+    double bytes = 2.0 * ((double)c->batch * sb.h * sb.w * c_in + M * c_out * (k.has_res ? 2 : 1)) +
+                   2.0 * c_out * c_in * k.taps;
+    if (op.chained) {  // + the chained 1x1 (its input never leaves the SM)
+      flops += 2.0 * M * op.conv2.c_out * op.conv2.c_in;
+      bytes += 2.0 * M * op.conv2.c_out + 2.0 * op.conv2.c_out * op.conv2.c_in - (op.chain_store1 ? 0.0 : 2.0 * M * c_out);
+    }
     const int ksz = k.taps == 9 ? 3 : 1;
     static const char* mode_name[] = {"flat", "halo", "tap", "halo2"};
-    char stg[48] = "";
+    char stg[96] = "";
     if (op.stage >= 0) snprintf(stg, sizeof stg, " sub=%dx%d lanes=%d", op_batch(c, op), op_subs(c, op), c->stages[op.stage].lanes);
     if (k.reverse) strncat(stg, " rev", sizeof stg - strlen(stg) - 1);
+    if (op.chained) snprintf(stg + strlen(stg), sizeof stg - strlen(stg), " +1x1 %d->%d", op.conv2.c_in, op.conv2.c_out);
     snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d%s | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.epi_sets, k.tw, k.th,

@@ -135,10 +135,17 @@ __device__ __forceinline__ void trace_put(const ConvKParams& p, int role, int it
 
 // TMA store (or reduce-add, for the fused Bottleneck residual) of one staged 64-channel group
 // [128 rows][128 B, swizzled] of the M block at `t`; `ch0` = first output channel of the group.
+__device__ __forceinline__ void store_group_to(const ConvKParams& p, const CUtensorMap* tm_out, const CUtensorMap* tm_out_r, bool has_res,
+                                               const MBlock& t, uint32_t src, int ch0);
 __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& t, uint32_t src, int ch0) {
+  store_group_to(p, &p.tmOut, p.tmOutR, p.has_res != 0, t, src, ch0);
+}
+// The same through explicit tensor maps (EPI_CHAIN stores the chained conv's output through tmOut2 / tmOut2R).
+__device__ __forceinline__ void store_group_to(const ConvKParams& p, const CUtensorMap* tm_out, const CUtensorMap* tm_out_r, bool has_res,
+                                               const MBlock& t, uint32_t src, int ch0) {
   if (p.mode == CONV_MODE_FLAT) {
-    if (p.has_res) tma_reduce_add_2d(&p.tmOut, src, ch0, t.m0);
-    else tma_store_2d(&p.tmOut, src, ch0, t.m0);
+    if (has_res) tma_reduce_add_2d(tm_out, src, ch0, t.m0);
+    else tma_store_2d(tm_out, src, ch0, t.m0);
   } else if (p.mode == CONV_MODE_HALO || p.mode == CONV_MODE_HALO2) {
     // the 16 tall rows of the block touch one or more images: one clipped box per image (rows outside
     // [0, H) -- the shared zero row and the other image's rows -- are dropped by TMA)
@@ -150,8 +157,8 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
     for (int n = n_first; n <= n_last; ++n) {
       const int ys = t.y0 - (n * hp1 + 1);  // image row of staging row 0
       if (ys >= 0) {
-        if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, ch0, t.x0, ys, n);
-        else tma_store_4d(&p.tmOut, src, ch0, t.x0, ys, n);
+        if (has_res) tma_reduce_add_4d(tm_out, src, ch0, t.x0, ys, n);
+        else tma_store_4d(tm_out, src, ch0, t.x0, ys, n);
       } else {
         // a TMA store may not start at a negative coordinate (illegal instruction, probe T6):
         // write staging rows [-ys, 16) to image rows [0, 16 + ys) as boxes of 8 / 4 / 2 / 1 rows
@@ -163,8 +170,8 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
           const int h = 8 >> hb;
           if (len & h) {
             const uint32_t ssrc = src + (uint32_t)s0 * 1024u;
-            if (p.has_res) tma_reduce_add_4d(&p.tmOutR[hb], ssrc, ch0, t.x0, y, n);
-            else tma_store_4d(&p.tmOutR[hb], ssrc, ch0, t.x0, y, n);
+            if (has_res) tma_reduce_add_4d(&tm_out_r[hb], ssrc, ch0, t.x0, y, n);
+            else tma_store_4d(&tm_out_r[hb], ssrc, ch0, t.x0, y, n);
             s0 += h;
             y += h;
           }
@@ -172,8 +179,8 @@ __device__ __forceinline__ void store_group(const ConvKParams& p, const MBlock& 
       }
     }
   } else {
-    if (p.has_res) tma_reduce_add_4d(&p.tmOut, src, ch0, t.x0, t.y0, t.n);
-    else tma_store_4d(&p.tmOut, src, ch0, t.x0, t.y0, t.n);
+    if (has_res) tma_reduce_add_4d(tm_out, src, ch0, t.x0, t.y0, t.n);
+    else tma_store_4d(tm_out, src, ch0, t.x0, t.y0, t.n);
   }
 }
 
@@ -759,11 +766,218 @@ __device__ __forceinline__ void store_role(const ConvKParams& p, uint32_t stg_ba
 #endif
 }
 
+
+// ===================================================================================================================
+// EPI_CHAIN: a 1x1 / stride-1 conv chained behind this conv inside the same kernel (ConvKParams::chain, conv_igemm.cuh).
+//
+// Per CTA the staged groups follow ONE sequence that the epilogue warps, the store warp and the chained-MMA warp walk in
+// step (ring of n_stg staging buffers, group k -> buffer k % n_stg):
+//     block 0: G1 groups of this conv | block 1: G1 groups | G2 groups of block 0's chained conv | block 2: G1 | G2 of block 1 ...
+// i.e. the chained conv's epilogue lags one M block behind, so its MMAs (issued as soon as the block's K groups are staged)
+// have a block's worth of epilogue time to complete.  G1 = every 64-channel group of this conv when its own output is stored
+// too, else only the chain_kg groups the chained conv consumes.  Barriers beside the usual ones (mbarriers, explicit phases):
+//   c_full[buf]  the 16 epilogue warps -> chained-MMA warp: K group staged in `buf` (after the proxy fence)
+//   c_done[buf]  tcgen05.commit -> store warp: the chained MMAs have read `buf` (it may be refilled once its store has too)
+//   tfull2[s] / tempty2[s]   chained accumulator stage s (block index & 1) ready / drained
+constexpr int kBarChain = 2 * kMaxA + 2 * kMaxB + 8;  // first chain barrier inside `bars`
+constexpr uint32_t kWarpMma2 = 21;
+
+struct ChainBars {
+  uint32_t bar0;
+  __device__ __forceinline__ uint32_t c_full(uint32_t b) const { return bar0 + 8u * (kBarChain + b); }
+  __device__ __forceinline__ uint32_t c_done(uint32_t b) const { return bar0 + 8u * (kBarChain + 4 + b); }
+  __device__ __forceinline__ uint32_t b2_full() const { return bar0 + 8u * (kBarChain + 8); }
+  __device__ __forceinline__ uint32_t tfull2(uint32_t s) const { return bar0 + 8u * (kBarChain + 9 + s); }
+  __device__ __forceinline__ uint32_t tempty2(uint32_t s) const { return bar0 + 8u * (kBarChain + 11 + s); }
+};
+
+template <int ACT>
+__device__ __forceinline__ void epi_chunk_math_store(const uint32_t (&v)[16], uint32_t bias_addr, uint32_t dst0, uint32_t dst1) {
+  epi_math_store<ACT>(v, bias_addr, dst0, dst1);
+}
+
+__device__ __forceinline__ void epi_chunk_dispatch(int act, const uint32_t (&v)[16], uint32_t bias_addr, uint32_t dst0, uint32_t dst1) {
+  if (act == ACT_SILU_FAST) epi_chunk_math_store<ACT_SILU_FAST>(v, bias_addr, dst0, dst1);
+  else if (act == ACT_SILU) epi_chunk_math_store<ACT_SILU>(v, bias_addr, dst0, dst1);
+  else epi_chunk_math_store<ACT_NONE>(v, bias_addr, dst0, dst1);
+}
+
+// Epilogue warps (sixteen, lockstep): this conv's groups, then the previous block's chained groups.
+__device__ __forceinline__ void epi_chain_role(const ConvKParams& p, const EpiCtx& ec, uint32_t bias2_smem) {
+  const uint32_t bar0 = ec.bar0;
+  const ChainBars cb{bar0};
+  auto tfull = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
+  auto tempty = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
+  const uint32_t e = ec.e, lane = ec.lane;
+  const uint32_t q = e & 3, sub = e >> 2;
+  const uint32_t row = q * 32 + lane;
+  const uint32_t st0 = row * 128u + (((2 * sub) ^ (row & 7u)) << 4);
+  const uint32_t st1 = row * 128u + (((2 * sub + 1) ^ (row & 7u)) << 4);
+  const int n_chunks1 = p.tile_n >> 4, n_chunks2 = p.tile_n2 >> 4, mblk = p.mblk;
+  const int G1 = p.chain_store1 ? p.groups : p.chain_kg, KG = p.chain_kg, G2 = p.groups2;
+  const uint32_t n_stg = p.n_stg, acc_stages = p.acc_stages;
+  const uint32_t t_lane = ec.tmem_base + ((q * 32u) << 16) + sub * 16u;
+  uint32_t v[16];
+  uint32_t gcount = 0;
+  Ring rs, rt;
+  uint32_t blk = 0;  // blocks whose own groups have been staged
+  // With two chained accumulator stages the chained epilogue lags ONE block behind (its MMAs get a block's worth of time);
+  // with one stage it follows its own block at once: the chained MMAs of block i wait for the chained epilogue of block
+  // i - 1, which needs staging buffers -- and in ring order those are held by block i's not yet consumed K groups.
+  const uint32_t lag = p.acc2_stages == 2 ? 1u : 0u;
+  // one staged group: accumulator chunk `ta` (this warp's 16 columns) -> bias + activation -> staging buffer
+  auto stage = [&](uint32_t ta, bool valid, uint32_t bias_addr, int act, bool k_group, uint32_t release_bar) {
+    const uint32_t buf = rs.slot;
+    rs.advance(n_stg);
+    if (valid) tmem_ld16(ta, v);
+    tmem_ld_wait();
+    if (release_bar) {  // every TMEM read of the accumulator stage is done
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(release_bar);
+    }
+    if (gcount >= n_stg) named_bar_sync(kBarStgEmpty + buf, kBarStgThreads);
+    const uint32_t stg = ec.stg_base + buf * (kTileM * 128);
+    if (valid) epi_chunk_dispatch(act, v, bias_addr, stg + st0, stg + st1);
+    fence_proxy_async_smem();
+    if (k_group) {  // the chained MMAs read this buffer through the async proxy
+      __syncwarp();
+      if (lane == 0) mbar_arrive(cb.c_full(buf));
+    }
+    named_bar_arrive(kBarStgFull + buf, kBarStgThreads);
+    ++gcount;
+  };
+  auto chained_groups = [&](uint32_t b) {  // epilogue of block b's chained conv
+    const uint32_t s2 = p.acc2_stages == 2 ? (b & 1u) : 0u;
+    mbar_wait(cb.tfull2(s2), (p.acc2_stages == 2 ? (b >> 1) : b) & 1u);
+    tc_fence_after();
+    const uint32_t ta2 = t_lane + p.acc2_base + s2 * p.acc2_pitch;
+    for (int g = 0; g < G2; ++g)
+      stage(ta2 + g * 64, 4 * g + (int)sub < n_chunks2, bias2_smem + (uint32_t)(g * 64 + (int)sub * 16) * 4u, p.act2, false,
+            g == G2 - 1 ? cb.tempty2(s2) : 0u);
+  };
+  for (int tile = tile_first(p); tile < ec.total_tiles; tile += tile_step(p), rt.advance(acc_stages)) {
+    const uint32_t as = rt.slot;
+    mbar_wait(tfull(as), rt.phase);
+    tc_fence_after();
+    for (int mb = 0; mb < mblk; ++mb, ++blk) {
+      const uint32_t ta = t_lane + as * p.acc_stride + (uint32_t)mb * p.acc_pitch;
+      for (int g = 0; g < G1; ++g)
+        stage(ta + g * 64, 4 * g + (int)sub < n_chunks1, ec.bias_smem + (uint32_t)(g * 64 + (int)sub * 16) * 4u, p.act, g < KG,
+              (mb == mblk - 1 && g == G1 - 1) ? tempty(as) : 0u);
+      if (blk >= lag) chained_groups(blk - lag);
+    }
+  }
+  if (lag && blk > 0) chained_groups(blk - 1);
+}
+
+// Chained-MMA warp: D2[128, tile_n2] (+)= stage[g][128, 64] * W2[g][tile_n2, 64]^T over the block's K groups.
+__device__ __forceinline__ void mma2_role(const ConvKParams& p, uint32_t bar0, uint32_t stg_base, uint32_t b2_base, uint32_t tmem_base,
+                                          int total_tiles) {
+  const ChainBars cb{bar0};
+  const uint32_t idesc2 = make_idesc_f16(kTileM, p.tile_n2);
+  const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29), lo_flags = 1u << 16;
+  const int G1 = p.chain_store1 ? p.groups : p.chain_kg, KG = p.chain_kg, G2 = p.groups2, mblk = p.mblk;
+  const uint32_t n_stg = p.n_stg;
+  const bool leader = elect_one();
+  const uint32_t lag = p.acc2_stages == 2 ? 1u : 0u;
+  mbar_wait(cb.b2_full(), 0);
+  uint32_t cf_phase = 0;  // bit b: parity of c_full[b]'s next completion
+  Ring rs;
+  uint32_t blk = 0;
+  for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p)) {
+    for (int mb = 0; mb < mblk; ++mb, ++blk) {
+      const uint32_t s2 = p.acc2_stages == 2 ? (blk & 1u) : 0u;
+      mbar_wait(cb.tempty2(s2), ((p.acc2_stages == 2 ? (blk >> 1) : blk) & 1u) ^ 1u);
+      tc_fence_after();
+      const uint32_t d = tmem_base + p.acc2_base + s2 * p.acc2_pitch;
+      for (int g = 0; g < G1; ++g) {
+        const uint32_t buf = rs.slot;
+        rs.advance(n_stg);
+        if (g >= KG) continue;
+        mbar_wait(cb.c_full(buf), (cf_phase >> buf) & 1u);
+        cf_phase ^= 1u << buf;
+        tc_fence_after();
+        if (leader) {
+          const uint32_t a_lo = (((stg_base + buf * (kTileM * 128)) & 0x3FFFFu) >> 4) | lo_flags;
+          const uint32_t b_lo = (((b2_base + (uint32_t)g * p.b2_slot_bytes) & 0x3FFFFu) >> 4) | lo_flags;
+          const int kk = g == KG - 1 ? p.chain_kk_last : 4;
+          for (int j = 0; j < kk; ++j) umma_f16_split(d, a_lo + 2u * j, hi, b_lo + 2u * j, hi, idesc2, (g > 0 || j > 0) ? 1u : 0u);
+          umma_commit(cb.c_done(buf));                      // the buffer has been read
+          if (g == KG - 1) umma_commit(cb.tfull2(s2));      // the chained accumulators are complete
+        }
+        __syncwarp();
+      }
+      if (blk >= lag)
+        for (int g = 0; g < G2; ++g) rs.advance(n_stg);  // block (blk - lag)'s chained groups pass through the ring here
+    }
+  }
+}
+
+// Store warp of the chained kernel: same sequence; a buffer is handed back once its TMA store has read it AND -- if it held
+// a K group -- the chained MMAs have.
+__device__ __forceinline__ void store_chain_role(const ConvKParams& p, uint32_t bar0, uint32_t stg_base, int total_tiles, uint32_t lane) {
+  const ChainBars cb{bar0};
+  const int G1 = p.chain_store1 ? p.groups : p.chain_kg, KG = p.chain_kg, G2 = p.groups2, mblk = p.mblk;
+  const uint32_t n_stg = p.n_stg;
+  const int my_tiles = (total_tiles - tile_first(p) + tile_step(p) - 1) / tile_step(p);
+  const uint32_t total_groups = (uint32_t)(my_tiles * mblk * (G1 + G2));
+  Ring rs;
+  uint32_t k = 0;          // groups handled so far
+  uint32_t kmask = 0;      // bit (j % 32): group j was a K group (n_stg <= 4 groups back is all that is ever looked at)
+  uint32_t cd_phase = 0;   // bit b: parity of c_done[b]'s next completion
+  uint32_t blk = 0;
+  const uint32_t lag = p.acc2_stages == 2 ? 1u : 0u;
+  MBlock prev = {};
+  auto one = [&](bool chained, bool k_group, const MBlock& t, int ch0) {
+    const uint32_t buf = rs.slot;
+    rs.advance(n_stg);
+    kmask = (kmask & ~(1u << (k & 31u))) | ((k_group ? 1u : 0u) << (k & 31u));
+    named_bar_sync(kBarStgFull + buf, kBarStgThreads);
+    if (lane == 0) {
+      const uint32_t src = stg_base + buf * (kTileM * 128);
+      if (chained) store_group_to(p, &p.tmOut2, p.tmOut2R, false, t, src, ch0);
+      else if (p.chain_store1) store_group_to(p, &p.tmOut, p.tmOutR, p.has_res != 0, t, src, ch0);
+      tma_store_commit();  // an empty group when nothing was stored: the wait below stays uniform
+      if (n_stg == 2) tma_store_wait_read0();
+      else if (n_stg == 3) tma_store_wait_read1();
+      else tma_store_wait_read2();
+    }
+    __syncwarp();
+    if (k + 2 >= n_stg && k + 2 < total_groups) {
+      uint32_t fb = buf + 2;  // (k + 2) % n_stg: last used by group k + 2 - n_stg
+      if (fb >= n_stg) fb -= n_stg;
+      const uint32_t j = k + 2 - n_stg;
+      if ((kmask >> (j & 31u)) & 1u) {
+        mbar_wait(cb.c_done(fb), (cd_phase >> fb) & 1u);
+        cd_phase ^= 1u << fb;
+      }
+      named_bar_arrive(kBarStgEmpty + fb, kBarStgThreads);
+    }
+    ++k;
+  };
+  for (int tile = tile_first(p); tile < total_tiles; tile += tile_step(p)) {
+    int m_tile, n_idx;
+    split_tile(p, tile, m_tile, n_idx);
+    for (int mb = 0; mb < mblk; ++mb, ++blk) {
+      const MBlock t = mblock_coords(p, m_tile, mb);
+      for (int g = 0; g < G1; ++g) one(false, g < KG, t, g * 64);
+      if (blk >= lag)
+        for (int g = 0; g < G2; ++g) one(true, false, lag ? prev : t, g * 64);
+      prev = t;
+    }
+  }
+  if (lag && blk > 0)
+    for (int g = 0; g < G2; ++g) one(true, false, prev, g * 64);
+  if (lane == 0) tma_store_wait_read0();
+}
+
 template <int EPI, bool TRACE>
-__global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKParams p) {
+__global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvKParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxA + 2 * kMaxB + 8 + (EPI == EPI_CHAIN ? 16 : 0)];
   __shared__ __align__(16) float s_bias[kMaxCout];
+  __shared__ __align__(16) float s_bias2[EPI == EPI_CHAIN ? kMaxCout2 : 4];
   __shared__ uint32_t tmem_slot;
   __shared__ uint8_t s_det_a[EPI == EPI_DETECT ? 256 : 1], s_det_o[EPI == EPI_DETECT ? 256 : 1];  // column -> anchor, output
 
@@ -772,6 +986,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
   const uint32_t a_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t b_base = a_base + p.na * p.a_slot_bytes;
   const uint32_t stg_base = b_base + p.nb * p.b_slot_bytes;
+  const uint32_t b2_base = stg_base + p.n_stg * p.stg_bytes;  // EPI_CHAIN: resident weights of the chained conv
 
   const uint32_t bar0 = smem_u32(bars);
   auto a_full = [&](int s) { return bar0 + 8u * s; };
@@ -791,7 +1006,11 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     if (p.mode == CONV_MODE_TAP && p.stride == 2) prefetch_tmap(&p.tmA2);
     if (p.up_chunks) prefetch_tmap(&p.tmUp);
   }
-  if (warp == kWarpStore && lane == 0 && EPI == EPI_STORE) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpStore && lane == 0 && EPI != EPI_DETECT) prefetch_tmap(&p.tmOut);
+  if (warp == kWarpStore && lane == 0 && EPI == EPI_CHAIN) {
+    prefetch_tmap(&p.tmOut2);
+    prefetch_tmap(&p.tmB2);
+  }
   if (warp == kWarpB && lane == 0) {
     prefetch_tmap(&p.tmB);
     for (int s = 0; s < p.na; ++s) {
@@ -806,15 +1025,29 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
       mbar_init(tfull(a), p.n_mma);
       mbar_init(tempty(a), kEpiWarps);
     }
+    if (EPI == EPI_CHAIN) {
+      const ChainBars cb{bar0};
+      for (uint32_t b = 0; b < 4; ++b) {
+        mbar_init(cb.c_full(b), kEpiWarps);
+        mbar_init(cb.c_done(b), 1);
+      }
+      mbar_init(cb.b2_full(), 1);
+      for (uint32_t a = 0; a < 2; ++a) {
+        mbar_init(cb.tfull2(a), 1);
+        mbar_init(cb.tempty2(a), kEpiWarps);
+      }
+    }
     fence_barrier_init();
   }
   if (warp == kWarpMma) {
     tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
     tmem_relinquish();
   }
-  for (int i = threadIdx.x; i < p.n_tiles_n * p.tile_n; i += kConvThreads) s_bias[i] = __ldg(p.bias + i);
+  for (int i = threadIdx.x; i < p.n_tiles_n * p.tile_n; i += blockDim.x) s_bias[i] = __ldg(p.bias + i);
+  if (EPI == EPI_CHAIN)
+    for (int i = threadIdx.x; i < p.tile_n2; i += blockDim.x) s_bias2[i] = __ldg(p.bias2 + i);
   if (EPI == EPI_DETECT) {
-    for (int i = threadIdx.x; i < 256; i += kConvThreads) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
       const int a = i / p.det_no;
       s_det_a[i] = (uint8_t)a;
       s_det_o[i] = (uint8_t)(i - a * p.det_no);
@@ -949,6 +1182,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp == kWarpB) {
     // =========================== weight producer ===========================
+    if (EPI == EPI_CHAIN && elect_one()) {  // the chained conv's weights: resident, one barrier for all K groups
+      const ChainBars cb{bar0};
+      mbar_arrive_expect_tx(cb.b2_full(), (uint32_t)p.chain_kg * (uint32_t)p.tile_n2 * 128u);
+      for (int g = 0; g < p.chain_kg; ++g) tma_load_2d(b2_base + (uint32_t)g * p.b2_slot_bytes, &p.tmB2, cb.b2_full(), g * 64, 0);
+    }
+    __syncwarp();
     if (p.b_res) {
       // all K steps of the (single) N tile stay resident: load once, never released
       const int n_res = p.b_dense ? p.nb : p.n_steps;
@@ -1006,6 +1245,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) conv_igemm_kernel(const __gri
     }
   } else if (warp == kWarpStore) {
     if (EPI == EPI_STORE) store_role<TRACE>(p, stg_base, total_tiles, lane);
+    if (EPI == EPI_CHAIN) store_chain_role(p, bar0, stg_base, total_tiles, lane);
+  } else if (EPI == EPI_CHAIN && warp == kWarpMma2) {
+    mma2_role(p, bar0, stg_base, b2_base, tmem_base, total_tiles);
+  } else if (EPI == EPI_CHAIN && warp >= kWarpEpi0) {
+    const EpiCtx ec{bar0, stg_base, tmem_base, smem_u32(s_bias), total_tiles, warp - kWarpEpi0, lane};
+    epi_chain_role(p, ec, smem_u32(s_bias2));
   } else if (warp >= kWarpEpi0 && EPI == EPI_STORE) {
     // =========================== epilogue warps 4..19: bias + SiLU + TMA store ===========================
     const EpiCtx ec{bar0, stg_base, tmem_base, smem_u32(s_bias), total_tiles, warp - kWarpEpi0, lane};
@@ -1172,7 +1417,8 @@ cudaError_t launch_conv_nocl(const ConvKParams& p, int epi, int num_sms, int pdl
 
 #if !AQ_CLUSTER
 size_t conv_smem_bytes(const ConvKParams& p) {
-  return (size_t)p.na * p.a_slot_bytes + (size_t)p.nb * p.b_slot_bytes + (size_t)p.n_stg * p.stg_bytes + 1024;
+  return (size_t)p.na * p.a_slot_bytes + (size_t)p.nb * p.b_slot_bytes + (size_t)p.n_stg * p.stg_bytes + 1024 +
+         (p.chain ? (size_t)p.chain_kg * p.b2_slot_bytes : 0);
 }
 cudaError_t conv_kernels_init() {
   cudaError_t e = conv_kernels_init_nocl();
@@ -1185,9 +1431,10 @@ cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cud
 
 cudaError_t AQ_VARIANT(conv_kernels_init)() {
   cudaError_t e = cudaSuccess;
-  const void* fns[4] = {(const void*)conv_igemm_kernel<EPI_STORE, false>, (const void*)conv_igemm_kernel<EPI_DETECT, false>,
-                        (const void*)conv_igemm_kernel<EPI_STORE, true>, (const void*)conv_igemm_kernel<EPI_DETECT, true>};
-  for (int i = 0; i < 4 && e == cudaSuccess; ++i)
+  const void* fns[5] = {(const void*)conv_igemm_kernel<EPI_STORE, false>, (const void*)conv_igemm_kernel<EPI_DETECT, false>,
+                        (const void*)conv_igemm_kernel<EPI_STORE, true>, (const void*)conv_igemm_kernel<EPI_DETECT, true>,
+                        (const void*)conv_igemm_kernel<EPI_CHAIN, false>};
+  for (int i = 0; i < 5 && e == cudaSuccess; ++i)
     e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, kConvMaxDynSmem);
   return e;
 }
@@ -1198,7 +1445,7 @@ cudaError_t AQ_VARIANT(launch_conv)(const ConvKParams& p, int epi, int num_sms, 
   const int n_clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(n_clusters * cluster);
-  cfg.blockDim = dim3(kConvThreads);
+  cfg.blockDim = dim3(epi == EPI_CHAIN ? kConvThreadsChain : kConvThreads);
   cfg.dynamicSmemBytes = conv_smem_bytes(p);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -1222,6 +1469,7 @@ cudaError_t AQ_VARIANT(launch_conv)(const ConvKParams& p, int epi, int num_sms, 
     return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT, true>, p);
   }
   if (epi == EPI_STORE) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_STORE, false>, p);
+  if (epi == EPI_CHAIN) return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_CHAIN, false>, p);
   return cudaLaunchKernelEx(&cfg, conv_igemm_kernel<EPI_DETECT, false>, p);
 }
 

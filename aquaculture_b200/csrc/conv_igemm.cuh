@@ -45,10 +45,12 @@
 namespace aq {
 
 enum { CONV_MODE_FLAT = 0, CONV_MODE_HALO = 1, CONV_MODE_TAP = 2, CONV_MODE_HALO2 = 3 };
-enum { EPI_STORE = 0, EPI_DETECT = 1 };
+enum { EPI_STORE = 0, EPI_DETECT = 1, EPI_CHAIN = 2 };
 enum { ACT_NONE = 0, ACT_SILU = 1, ACT_SILU_FAST = 2 };
 
 constexpr int kConvThreads = 672;  // 4 role warps + 16 epilogue warps + 1 store warp
+constexpr int kConvThreadsChain = 704;  // EPI_CHAIN: + 1 warp issuing the chained 1x1 conv's MMAs
+constexpr int kMaxCout2 = 256;      // EPI_CHAIN: output channels of the chained conv (one UMMA N)
 constexpr int kEpiWarps = 16;
 constexpr int kMaxA = 6;    // A ring slots
 constexpr int kMaxB = 20;   // weight ring slots (resident layers: one per K step)
@@ -108,6 +110,24 @@ struct alignas(64) ConvKParams {
   uint32_t* det_mask;
   const float* det_conf;
   int det_mask_words;
+  // EPI_CHAIN: a 1x1 / stride-1 conv consuming this conv's output, evaluated in the same kernel.  The 128 x 64 fp16
+  // groups the epilogue stages for the TMA store are valid SWIZZLE_128B K-major A operands, so a second tcgen05.mma
+  // reads them out of shared memory before (while) the store leaves: D2[128, tile_n2] = sum over the first chain_kg groups
+  // of stage[g] * W2[g]^T, accumulated in its own TMEM columns, then bias2 + activation -> staging -> tmOut2.  The
+  // consumer's values are exactly those of a separate launch (it reads the same fp16-rounded activations); what
+  // disappears is one launch boundary and one read of the tensor from HBM / L2.
+  CUtensorMap tmB2;        // chained weights [c_out2][chain_kg * 64] (zero padded), box {64, tile_n2}
+  CUtensorMap tmOut2;      // chained output stores (same geometry as tmOut)
+  CUtensorMap tmOut2R[4];  // HALO: boxes of 8 / 4 / 2 / 1 rows
+  const float* bias2;      // [tile_n2] (pre-multiplied by 0.5 for ACT_SILU_FAST)
+  int chain;               // 0 = off
+  int chain_kg;            // 64-channel groups of THIS conv's output that feed the chained conv (its K = c_in2)
+  int chain_kk_last;       // K = 16 MMAs that carry data in the last of them
+  int chain_store1;        // 1: this conv's own output is stored too (0: only the chained conv's output leaves)
+  int tile_n2, groups2, act2;
+  uint32_t b2_slot_bytes;  // one resident weight slot of the chained conv (tile_n2 rows x 128 B, 1024-aligned)
+  uint32_t acc2_base, acc2_pitch;  // TMEM columns: first column of the chained accumulators (acc2_stages stages, acc2_pitch apart)
+  int acc2_stages;                 // 1 or 2 (block b uses stage b % acc2_stages)
   unsigned long long* trace;  // device buffer [grid][kTraceRoles][kTraceTiles][kTraceVals] or NULL
 };
 

@@ -109,6 +109,19 @@ class Context:
                      up[0] if up else -1, up[1] if up else 0, up[2] if up else 0)
         self.call("aq_plan_conv", C.byref(d))
 
+    def conv_chain(self, src, dst, w_oihw, bias, k, stride, act, dst2, w2_oihw, bias2, act2, store_first=True, up=None,
+                   mblk=0, mode=0):  # noqa: D401
+        """`conv(src -> dst)` followed, inside the SAME kernel, by a 1x1 conv over the first `w2.shape[1]` channels of its
+        output into dst2 (aq_plan_conv_chain).  Raises AquaError (AQ_ERR_UNSUPPORTED) when no tiling can host the pair."""
+        wk, wk2 = pack_krsc(w_oihw), pack_krsc(w2_oihw)
+        b, b2 = np.ascontiguousarray(bias.float().numpy()), np.ascontiguousarray(bias2.float().numpy())
+        self._keep += [wk, wk2, b, b2]
+        d1 = ConvDesc(src[0], src[1], w_oihw.shape[1], dst[0], dst[1], w_oihw.shape[0], k, stride, int(act), -1, 0,
+                      wk.ctypes.data, b.ctypes.data, 0, mblk, mode, 0, up[0] if up else -1, up[1] if up else 0, up[2] if up else 0)
+        d2 = ConvDesc(dst[0], dst[1], w2_oihw.shape[1], dst2[0], dst2[1], w2_oihw.shape[0], 1, 1, int(act2), -1, 0,
+                      wk2.ctypes.data, b2.ctypes.data, 0, 0, 0, 0, -1, 0, 0)
+        self.call("aq_plan_conv_chain", C.byref(d1), C.byref(d2), int(bool(store_first)))
+
     def detect_level(self, src, w_oi: torch.Tensor, bias: torch.Tensor, nc, level_row_off, stride, anchors_px):
         wk = np.ascontiguousarray(w_oi.reshape(w_oi.shape[0], -1).half().numpy().view(np.uint16))
         b = np.ascontiguousarray(bias.float().numpy())
@@ -192,6 +205,9 @@ class Detections:
 # plan: 4.47 ms unstaged vs 4.82 .. 5.86 ms staged per 64-tile batch.  The mechanism is exact (same kernels, same values;
 # tests/test_gpu_kernels.py::test_staged_plan_*) and stays available for larger inputs.
 DEFAULT_STAGES = {}
+# Default: both kinds of chain (measured, interleaved A/B of the batch-64 conv stack, profiles/r2_ab_chain_serpentine.txt:
+# 4.615 ms none, 4.580 "c3", 4.569 "feed", 4.550 "feed,c3").
+DEFAULT_CHAIN = "feed,c3"
 
 
 def stage_plan(net_h: int, net_w: int, batch: int, spec: Optional[str] = None) -> Dict[str, Tuple[int, int]]:
@@ -248,6 +264,11 @@ class TileDetector:
         buf = ctx.buffer
         stages = stage_plan(H, W, B)
         self.stages = stages
+        # 1x1 convs chained behind their producers (EPI_CHAIN): "c3", "feed", "feed,c3" ("1" = both), "0" = none
+        chain_on = os.environ.get("AQUA_CHAIN", DEFAULT_CHAIN)
+        chain_on = {"0": "", "1": "feed,c3"}.get(chain_on, chain_on)
+        self.chained = []
+        self.unwritten = set()  # buffers whose producer was chained with store_first = 0: they are never written
 
         class stage:  # `with stage("a"):` -- ops and buffers planned inside form one depth-first stage
             def __init__(self, name):
@@ -281,16 +302,46 @@ class TileDetector:
             w, b = fw[name]
             ctx.conv(src, dst, w, b, k, s, self.act, res)
 
-        def c3(idx, src, c1, dst, c2, n, shortcut, hw, up=None):
+        def c3(idx, src, c1, dst, c2, n, shortcut, hw, up=None, feeder=None):
+            """feeder = (name, src, k, s): the Conv layer whose ONLY consumer is this C3 (its output is `src`); with chaining on it
+            runs in one kernel with cv1 || cv2 and its output never goes to memory."""
             c_ = c2 // 2
             cat = buf(hw[0], hw[1], 2 * c_)
             tmp = buf(hw[0], hw[1], c_)
             pre = f"model.{idx}"
             w1, b1 = fw[pre + ".cv1"]
             w2, b2 = fw[pre + ".cv2"]
-            ctx.conv(src, (cat, 0), torch.cat((w1, w2), 0), torch.cat((b1, b2), 0), 1, 1, self.act, up=up)
+            w12, b12 = torch.cat((w1, w2), 0), torch.cat((b1, b2), 0)
+            # cv1 || cv2 is one GEMM.  Chaining (aq_plan_conv_chain, EPI_CHAIN): either the layer in front of the C3 runs in the
+            # same kernel as cv1 || cv2 ("feed": its output is consumed out of shared memory and never stored), or the first
+            # Bottleneck's 1x1 runs behind cv1 || cv2 ("c3").  Each saves a launch and a trip of the tensor through HBM / L2.
+            done12 = first_chained = False
+            if feeder is not None:
+                fname, fsrc, fk, fs = feeder
+                wf, bf = fw[fname]
+                if "feed" in chain_on and 2 * c_ <= 256 and wf.shape[0] <= 256:
+                    try:
+                        ctx.conv_chain(fsrc, src, wf, bf, fk, fs, self.act, (cat, 0), w12, b12, self.act, store_first=False)
+                        done12 = True
+                        self.chained.append(f"{fname} -> {pre}.cv1||cv2")
+                        self.unwritten.add(src[0])
+                    except AquaError:
+                        pass
+                if not done12:
+                    ctx.conv(fsrc, src, wf, bf, fk, fs, self.act)
+            if not done12 and "c3" in chain_on and 2 * c_ <= 256:
+                wm, bm = fw[f"{pre}.m.0.cv1"]
+                try:
+                    ctx.conv_chain(src, (cat, 0), w12, b12, 1, 1, self.act, (tmp, 0), wm, bm, self.act, store_first=True, up=up)
+                    done12 = first_chained = True
+                    self.chained.append(f"{pre}.cv1||cv2 -> m.0.cv1")
+                except AquaError:
+                    pass  # no tiling leaves room for the chained weights / accumulators: two launches
+            if not done12:
+                ctx.conv(src, (cat, 0), w12, b12, 1, 1, self.act, up=up)
             for j in range(n):
-                conv(f"{pre}.m.{j}.cv1", (cat, 0), (tmp, 0), 1, 1)
+                if not (j == 0 and first_chained):
+                    conv(f"{pre}.m.{j}.cv1", (cat, 0), (tmp, 0), 1, 1)
                 conv(f"{pre}.m.{j}.cv2", (tmp, 0), (cat, 0), 3, 1, res=(cat, 0) if shortcut else None)
             conv(pre + ".cv3", (cat, 0), dst, 1, 1)
 
@@ -310,11 +361,12 @@ class TileDetector:
             x2 = buf(H // 4, W // 4, 96)
             w0, b0 = fw["model.0"]
             ctx.conv((b_in, 0), (x0, 0), pack_stem_s2d(w0), b0, 3, 1, self.act)
-            conv("model.1", (x0, 0), (x1, 0), 3, 2)
-            c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4))
-            conv("model.3", (x2, 0), (x3, 0), 3, 2)
+            c3(2, (x1, 0), 96, (x2, 0), 96, L[2].n, True, (H // 4, W // 4), feeder=("model.1", (x0, 0), 3, 2))
+            if stages.get("a") or stages.get("b"):  # layer 3 and the C3 behind it sit in different stages: not chained
+                conv("model.3", (x2, 0), (x3, 0), 3, 2)
         with stage("b"):
-            c3(4, (x3, 0), 192, (cat16, 192), 192, L[4].n, True, (H // 8, W // 8))
+            c3(4, (x3, 0), 192, (cat16, 192), 192, L[4].n, True, (H // 8, W // 8),
+               feeder=None if (stages.get("a") or stages.get("b")) else ("model.3", (x2, 0), 3, 2))
         conv("model.5", (cat16, 192), (x5, 0), 3, 2)
         c3(6, (x5, 0), 384, (cat12, 384), 384, L[6].n, True, (H // 16, W // 16))
         conv("model.7", (cat12, 384), (x7, 0), 3, 2)

@@ -124,6 +124,14 @@ int aq_plan_buffer(aq_ctx* ctx, int h, int w, int c);
 int aq_plan_stage_begin(aq_ctx* ctx, int sub_batch, int lanes);
 int aq_plan_stage_end(aq_ctx* ctx);
 int aq_plan_conv(aq_ctx* ctx, const aq_conv_desc* d);
+/* Two convs in ONE kernel: `first` as aq_plan_conv, then `second` -- a 1x1 / stride-1 conv (+ bias + activation, no residual) whose
+ * input is the first second->c_in channels of first's output slice -- evaluated on the 128 x 64 fp16 groups first's epilogue
+ * stages in shared memory, before they leave for HBM (a second tcgen05.mma on the staged tiles; conv_igemm.cuh EPI_CHAIN).
+ * upstream: models/common.py::C3.forward's cv1 followed by m[0].cv1, or any Conv feeding a pointwise Conv.  Values are those of
+ * two separate aq_plan_conv calls (the second reads the same fp16-rounded activations); store_first = 0 keeps first's output
+ * out of memory altogether.  first: no residual, <= 256 output channels, FLAT / TAP feeds; AQ_ERR_UNSUPPORTED otherwise (plan
+ * the two convs separately then). */
+int aq_plan_conv_chain(aq_ctx* ctx, const aq_conv_desc* first, const aq_conv_desc* second, int store_first);
 /* models/common.py::SPPF's three chained MaxPool2d(5,1,2): reads channels [c_off, c_off+c) of `buf` and
  * writes the pooled maps to [c_off+c, c_off+2c), [c_off+2c, ..), [c_off+3c, ..) of the same buffer. */
 int aq_plan_sppf_pool(aq_ctx* ctx, int buf, int c_off, int c);

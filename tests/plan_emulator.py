@@ -34,6 +34,11 @@ class PlanEmulator:
         # weights go through the same fp16 rounding the device sees
         self.ops.append(("conv", src, dst, w_oihw.half().float(), bias.float(), k, stride, act, res, up))
 
+    def conv_chain(self, src, dst, w_oihw, bias, k, stride, act, dst2, w2_oihw, bias2, act2, store_first=True, up=None, mblk=0, mode=0):
+        # two convs in one kernel on the device: the same two ops here
+        self.conv(src, dst, w_oihw, bias, k, stride, act, up=up)
+        self.conv(dst, dst2, w2_oihw, bias2, 1, 1, act2)
+
     def detect_level(self, src, w_oi, bias, nc, level_row_off, stride, anchors_px):
         self.ops.append(("detect", src, w_oi.reshape(w_oi.shape[0], -1).half().float(), bias.float(), nc, level_row_off, stride,
                          np.asarray(anchors_px, np.float32)))

@@ -502,7 +502,7 @@ def test_staged_plan_matches_unstaged(synthetic_sd, monkeypatch):
         finally:
             det.close()
     ref = out["0"]
-    assert ref[2] == 75
+    assert ref[2] in (72, 75)  # 75 convs + pool; 72 with the default chains (AQUA_CHAIN)
     for spec, (pred, counts, launches) in out.items():
         if spec == "0":
             continue

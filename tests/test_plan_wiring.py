@@ -7,11 +7,18 @@ from oracle import yolov5m
 from plan_emulator import PlanEmulator, space_to_depth_input
 
 
-def test_plan_matches_oracle(synthetic_sd):
+import pytest
+
+
+@pytest.mark.parametrize("chain", ["0", "1"])
+def test_plan_matches_oracle(synthetic_sd, chain, monkeypatch):
+    """chain = 1: the eligible C3 blocks are wired with the first Bottleneck's 1x1 chained behind cv1 || cv2 (AQUA_CHAIN)."""
+    monkeypatch.setenv("AQUA_CHAIN", chain)
     torch.manual_seed(3)
     x = torch.rand(2, 3, 128, 160)
     emu = PlanEmulator()
     det = engine.TileDetector(synthetic_sd, 3, batch=2, imgsz=(128, 160), ctx=emu)
+    assert bool(det.chained) == (chain == "1")
     pred = emu.run(space_to_depth_input(x))
     with torch.no_grad():
         ref = yolov5m.build(synthetic_sd, 3)(x)

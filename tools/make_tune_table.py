@@ -15,9 +15,11 @@ import torch
 from aquaculture_b200 import engine, tiles, weights
 sd = weights.synthetic_state(3, 0)
 for b, img in cfgs:
-    det = engine.TileDetector(sd, 3, batch=b, imgsz=(img, img))
-    det.detect(torch.from_numpy(tiles.synthetic_tiles(range(b), img, img)).pin_memory())
-    det.close()
+    for chain in ("feed,c3", "0", "c3", "feed"):  # the default plan and the unchained / partly chained ones (tests, A/B runs)
+        os.environ["AQUA_CHAIN"] = chain
+        det = engine.TileDetector(sd, 3, batch=b, imgsz=(img, img))
+        det.detect(torch.from_numpy(tiles.synthetic_tiles(range(b), img, img)).pin_memory())
+        det.close()
     print(f"planned batch {b} at {img}x{img}", flush=True)
 lines = sorted(set(open(out).read().splitlines()))
 with open(out, "w") as f:

@@ -58,6 +58,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > AQ_MBAR_SPIN_LIMIT) __trap();
+#ifdef AQ_MBAR_NANOSLEEP  // experiment: back off between polls (does polling cost power under the 1 kW cap?)
+    __nanosleep(AQ_MBAR_NANOSLEEP);
+#endif
   }
 }
 

@@ -56,3 +56,39 @@ t_sub.clear()
 t0 = time.perf_counter(); loop(a.reps); dt = time.perf_counter() - t0
 print(f"pipelined (two batches in flight):    {dt / a.reps * 1e3:7.3f} ms per batch = {a.batch * a.reps / dt:.0f} tiles/s; host time inside prepare+submit {np.mean(t_sub) * 1e3:.3f} ms")
 det.close()
+
+# GPU time of the two halves INSIDE the pipelined loop (CUDA events on the launching stream)
+det = engine.TileDetector(weights.synthetic_state(3, 0), 3, batch=a.batch, imgsz=(640, 640))
+st = torch.cuda.Stream()
+sarg = C.c_void_p(st.cuda_stream)
+ev = []
+def sub2():
+    (sc, off, ln, tab, q, stt), tot, i0 = engine.prepare_jpeg_batch(det, blobs, n_threads=threads)
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    with torch.cuda.stream(st):
+        e[0].record()
+        key = (i0.height, i0.width)
+        if det._jpeg_out.get(key) is None:
+            det._jpeg_out[key] = torch.empty(det.batch, i0.height, i0.width, 3, dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+        out = det._jpeg_out[key][:a.batch]
+        det.ctx.call("aq_jpeg_decode_device", C.c_void_p(sc.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(ln.ctypes.data), int(tot),
+                     C.c_void_p(tab.ctypes.data), C.c_void_p(q.ctypes.data), a.batch, i0.width, i0.height, i0.ncomp, i0.hs, 1,
+                     C.c_void_p(out.data_ptr()), C.c_void_p(stt.ctypes.data), sarg)
+        e[1].record()
+        tk = det.detect_submit(out, bgr=True, src_is_device=True, stream=sarg)
+        e[2].record()
+    ev.append(e)
+    return tk
+prev = None
+for i in range(a.reps + 3):
+    tk = sub2()
+    if prev is not None:
+        det.detect_wait(prev)
+    prev = tk
+det.detect_wait(prev)
+torch.cuda.synchronize()
+d = np.array([[e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2])] for e in ev[3:]])
+gap = np.array([ev[i][2].elapsed_time(ev[i + 1][0]) for i in range(3, len(ev) - 1)])
+print(f"in the pipelined loop, GPU time per batch: decode {d[:, 0].mean():.3f} ms, detect {d[:, 1].mean():.3f} ms, idle between batches {gap.mean():.3f} ms")
+det.close()

@@ -1773,6 +1773,20 @@ int aq_nms(aq_ctx* c, const float* pred, int batch, int rows, int no, float conf
     CU_CHECK(c, launch_nms_mask(p, batch, s));
   }
   p.dets = dets_out; p.counts = counts_out; p.keep_rows = keep_rows_out;
+  static const bool nms_clk = getenv("AQUA_NMS_CLK") != nullptr;
+  p.dbg_clk = nullptr;
+  if (nms_clk) {  // phase timeline of image 0's CTA (debug): printed after a synchronising copy
+    static long long* d_clk = nullptr;
+    if (!d_clk) cudaMalloc(&d_clk, 8 * sizeof(long long));
+    p.dbg_clk = d_clk;
+    CU_CHECK(c, launch_nms(p, batch, s));
+    long long h[8] = {0};
+    cudaMemcpyAsync(h, d_clk, sizeof h, cudaMemcpyDeviceToHost, s);
+    cudaStreamSynchronize(s);
+    fprintf(stderr, "nms phases (clk): count %lld, compaction %lld, sort %lld, suppression %lld, total %lld\n", h[1] - h[0], h[2] - h[1], h[3] - h[2],
+            h[4] - h[3], h[4] - h[0]);
+    return AQ_OK;
+  }
   CU_CHECK(c, launch_nms(p, batch, s));
   return AQ_OK;
 }

@@ -97,6 +97,9 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
 
   __shared__ int s_warp_cnt[kWarps];
   __shared__ int s_total;
+  // small images (<= kT candidates, the usual case: ~40 per 640^2 tile at conf 0.25): candidates, sort and suppression stay in
+  // shared memory -- no global scratch round trips, a rank sort instead of four radix passes
+  // (carved out of the dynamic shared memory behind the kept boxes: s_cbox, s_cscore, s_ccls, s_crow, s_order)
   __shared__ uint32_t s_bins[256];
   __shared__ __align__(16) uint16_t s_whist[kWarps][256];
   __shared__ uint32_t s_chunk_base[256];
@@ -104,17 +107,47 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
   __shared__ int s_kept;
   extern __shared__ float4 s_dyn[];  // kept boxes (class-offset) [max_det] then areas [max_det]
   float4* s_kbox = s_dyn;
-  float* s_karea = reinterpret_cast<float*>(s_dyn + p.max_det);
+  float4* s_cbox = s_dyn + p.max_det;
+  float* s_karea = reinterpret_cast<float*>(s_cbox + kT);
+  float* s_cscore = s_karea + p.max_det;
+  float* s_ccls = s_cscore + kT;
+  int* s_crow = reinterpret_cast<int*>(s_ccls + kT);
+  uint32_t* s_order = reinterpret_cast<uint32_t*>(s_crow + kT);
 
+#define NMS_STAMP(i) do { if (p.dbg_clk && img == 0 && tid == 0) p.dbg_clk[i] = clock64(); } while (0)
+  NMS_STAMP(0);
+  // ------------------------------------------------------------------ count first: which path?
+  const int nc = p.no - 5;
+  const int words = (p.rows + 31) >> 5;
+  const uint32_t* mask = p.cand_mask + (size_t)img * words;
+  {
+    int cnt = 0;
+    for (int w = tid; w < words; w += kT) cnt += __popc(mask[w]);
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) s_warp_cnt[warp] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+      int t = 0;
+      for (int k = 0; k < kWarps; ++k) t += s_warp_cnt[k];
+      s_total = t;
+    }
+    __syncthreads();
+  }
+  const bool small = s_total <= kT;
+  __syncthreads();
+  if (small) {
+    cbox = s_cbox;
+    cscore = s_cscore;
+    ccls = s_ccls;
+    crow = s_crow;
+  }
+  NMS_STAMP(1);
   // ------------------------------------------------------------------ A: ordered compaction of the passing rows
   // thread t takes mask word base + t (rows 32 (base + t) ..): exclusive block scan of the popcounts gives the
   // position of its first candidate, so candidates stay in source-row order (upstream's stable sort breaks score
   // ties by it)
   if (tid == 0) s_total = 0;
   __syncthreads();
-  const int nc = p.no - 5;
-  const int words = (p.rows + 31) >> 5;
-  const uint32_t* mask = p.cand_mask + (size_t)img * words;
   for (int base = 0; base < words; base += kT) {
     const int w = base + tid;
     uint32_t m = w < words ? mask[w] : 0u;
@@ -149,8 +182,10 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
       cscore[pos] = bestv;
       ccls[pos] = (float)best;
       crow[pos] = r;
-      keyA[pos] = ~__float_as_uint(bestv);
-      valA[pos] = (uint32_t)pos;
+      if (!small) {
+        keyA[pos] = ~__float_as_uint(bestv);
+        valA[pos] = (uint32_t)pos;
+      }
       ++pos;
     }
     __syncthreads();
@@ -161,17 +196,33 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
     }
     __syncthreads();
   }
+  NMS_STAMP(2);
   const int n_all = s_total;
   if (n_all == 0) {
     if (tid == 0) p.counts[img] = 0;
     return;
   }
 
-  // ------------------------------------------------------------------ B: stable LSD radix sort (asc key = desc score)
+  // ------------------------------------------------------------------ B: stable sort by descending score
   uint32_t* ksrc = keyA;
   uint32_t* kdst = keyB;
   uint32_t* vsrc = valA;
   uint32_t* vdst = valB;
+  if (small) {
+    // rank sort: candidate i goes to position #{j : score_j > score_i, or equal and j < i} (stable, as upstream's argsort is made)
+    __syncthreads();
+    if (tid < n_all) {
+      const float si = s_cscore[tid];
+      int rank = 0;
+      for (int j = 0; j < n_all; ++j) {
+        const float sj = s_cscore[j];
+        rank += (sj > si || (sj == si && j < tid)) ? 1 : 0;
+      }
+      s_order[rank] = (uint32_t)tid;
+    }
+    __syncthreads();
+    vsrc = s_order;
+  } else
   for (int shift = 0; shift < 32; shift += 8) {
     if (tid < 256) s_bins[tid] = 0;
     if (tid == 0) s_skip = 0;
@@ -241,6 +292,7 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
   }
   const int n = n_all < p.max_nms ? n_all : p.max_nms;
 
+  NMS_STAMP(3);
   // ------------------------------------------------------------------ C: greedy suppression
   if (tid == 0) s_kept = 0;
   __syncthreads();
@@ -315,6 +367,7 @@ __global__ void __launch_bounds__(kT, 1) nms_kernel(NmsParams p) {
   }
   __syncthreads();
   if (tid == 0) p.counts[img] = s_kept;
+  NMS_STAMP(4);
 }
 
 }  // namespace
@@ -324,7 +377,7 @@ size_t nms_scratch_bytes(int batch, int rows) {
 }
 
 cudaError_t nms_init() {
-  return cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+  return cudaFuncSetAttribute(nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 cudaError_t launch_nms_mask(const NmsParams& p, int batch, cudaStream_t stream) {
@@ -333,7 +386,7 @@ cudaError_t launch_nms_mask(const NmsParams& p, int batch, cudaStream_t stream) 
 }
 
 cudaError_t launch_nms(const NmsParams& p, int batch, cudaStream_t stream) {
-  const size_t dyn = (size_t)p.max_det * (sizeof(float4) + sizeof(float));
+  const size_t dyn = (size_t)p.max_det * (sizeof(float4) + sizeof(float)) + (size_t)kT * (sizeof(float4) + 4 * sizeof(float));
   nms_kernel<<<batch, kT, dyn, stream>>>(p);
   return cudaGetLastError();
 }

@@ -29,6 +29,7 @@ struct NmsParams {
   float* dets;     // (batch, max_det, 6)
   int* counts;     // (batch)
   int* keep_rows;  // (batch, max_det) or nullptr
+  long long* dbg_clk;  // optional (AQUA_NMS_CLK): 8 clock64 stamps of image 0's CTA at the phase boundaries
 };
 
 size_t nms_scratch_bytes(int batch, int rows);

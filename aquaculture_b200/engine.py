@@ -396,9 +396,9 @@ class TileDetector:
             detect(0, x17)
             conv("model.18", (x17, 0), (cat19, 0), 3, 2)
         c3(20, (cat19, 0), 384, (x20, 0), 384, L[20].n, False, (H // 16, W // 16))
+        detect(1, x20)  # each Detect level right behind the layer that feeds it (measured: no different from running it last)
         conv("model.21", (x20, 0), (cat22, 0), 3, 2)
         c3(23, (cat22, 0), 768, (x23, 0), 768, L[23].n, False, (H // 32, W // 32))
-        detect(1, x20)
         detect(2, x23)
         self.rows = sum(level_rows)
         ctx.plan_end()

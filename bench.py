@@ -439,6 +439,7 @@ def main():
     for i in range(args.warmup):
         det.detect_wait(step_resident(i))
     barrier()
+    det.stage_ms, det.stage_tiles = [0.0, 0.0, 0.0], 0
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -451,6 +452,8 @@ def main():
         e1.record()
     det.detect_wait(last)
     barrier()
+    # upstream's three "Speed:" stages for the last timed batch, CUDA events on the compute stream (aq_detect_stage_ms)
+    stage_ms = [round(v, 4) for v in det.stage_ms] if det.stage_tiles == BATCH else None
     ms_value = max_over_ranks(e0.elapsed_time(e1))
     n_dets = int(det._counts[last[0]][:BATCH].sum())
 
@@ -587,6 +590,8 @@ def main():
                                         f"{round(achieved / peaks['sustained'], 4)}, frac_of_nominal_2250 {round(achieved / 2250.0, 4)}",
                          "kernel_source_id": kernel_source_id(),
                          "ms_per_conv_stack": round(ms_fwd, 4)},
+            "stage_ms_last_batch": {"pre_process": stage_ms[0], "inference": stage_ms[1], "nms": stage_ms[2],
+                                    "note": "device time of one 64-tile batch per stage (upstream detect.py's Speed: line), CUDA events"} if stage_ms else None,
             "clocks": clocks,
             "aux_kernels": aux,
             "counters": {"tiles": int(counters[0]), "label_files_last_e2e_pass": int(counters[1]), "detections_last_batch": int(counters[2])},

@@ -256,6 +256,7 @@ int pow2_at_least(int v) {
 struct Cand {
   int mode = 0, mblk = 1, mx = 1, my = 1, tw = 0, th = 0;
   int cluster = 1;  // CTAs per thread-block cluster sharing each weight tile by multicast (1, 2, 4)
+  int pair = 0;     // 1: cluster of two CTAs running tcgen05.mma.cta_group::2 (each keeps half of every weight tile)
   int epi_sets = 1; // epilogue organisation: 1 = sixteen warps in lockstep, 2 = two sets of eight on alternate groups
   int pref = 0;     // shared-memory split: 0 = staging / activation rings first, 1 = weight ring first (streamed weights)
   int b_dense = 0;  // HALO with c_in <= 16: four taps share one 64-wide weight chunk (resident weights = 3 slots, not 9)
@@ -274,7 +275,7 @@ struct Cand {
 void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles_n, int n_steps, int cpt, int num_sms,
                     int extra_smem = 0, int extra_tmem = 0, int chain_kg = 0) {  // what a chained conv adds (resident weights, accumulator columns, K groups)
   const int groups = (tile_n + 63) / 64;
-  const uint32_t b_slot = (uint32_t)round_up(tile_n * 128, 1024);
+  const uint32_t b_slot = (uint32_t)round_up((cd.pair ? tile_n / 2 : tile_n) * 128, 1024);
   (void)groups;
   const uint32_t stg = kTileM * 128;  // staging ring: 16 KB buffers, one 64-channel group of an M block each
   int a_instr_per_group = 1, n_groups = n_steps;
@@ -370,8 +371,9 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
   // ---- cost
   const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
   const double a_bytes = (double)n_groups * cd.a_tx;
-  if (cd.cluster > 1 && (cd.b_res || (tile_n / cd.cluster) % 8 || num_sms / cd.cluster < 1)) return;  // nothing to share / swizzle atom split
-  const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0 / cd.cluster;
+  if (cd.cluster > 1 && !cd.pair && (cd.b_res || (tile_n / cd.cluster) % 8 || num_sms / cd.cluster < 1)) return;  // nothing to share / swizzle atom split
+  if (cd.pair && (cd.cluster != 2 || (tile_n / 2) % 8 || cd.b_dense)) return;
+  const double b_bytes = cd.b_res ? 0.0 : (double)n_steps * tile_n * 128.0 / cd.cluster;  // per SM: a multicast cluster still delivers every byte to every SM (the model is optimistic there), a pair really halves it
   const double o_bytes = (double)cd.mblk * kTileM * tile_n * 2.0;
   const double l2 = (a_bytes + b_bytes + o_bytes) / 40.0;
   // TMA: one producer thread per operand, ~600 clk per box and ~4500 clk latency per ring slot; the HALO
@@ -493,10 +495,17 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
     if (ntn * tn > kMaxCout) continue;
     for (Cand cd0 : shapes) {
       if (want_mblk > 0 && cd0.mblk != want_mblk) continue;
-      for (int cl = 1; cl <= 4; cl *= 2) {
+      // want_cluster: 0 auto, 1 / 2 / 4 multicast clusters, 12 = CTA pair (cta_group::2).  Auto = single CTAs, plus pairs as
+      // candidates for the autotuner unless AQUA_PAIR=0
+      const bool pair_auto = !(getenv("AQUA_PAIR") && atoi(getenv("AQUA_PAIR")) == 0);
+      for (int ci = 0; ci < 4; ++ci) {
+        const int cl = ci == 3 ? 2 : (1 << ci);
+        const int pr = ci == 3 ? 1 : 0;
         // measured (profiles/r1_cluster_multicast_sweep.txt): sharing weight tiles by multicast does not speed any
-        // layer up (cluster 2: +-1 %, cluster 4: slower), so clusters are only planned on request
-        if (cl != (want_cluster > 0 ? want_cluster : 1)) continue;
+        // layer up (cluster 2: +-1 %, cluster 4: slower), so multicast clusters are only planned on request
+        if (want_cluster == 12) { if (!pr) continue; }
+        else if (want_cluster > 0) { if (pr || cl != want_cluster) continue; }
+        else if (pr ? (!pair_auto || chain) : cl != 1) continue;
         // AQUA_EPI_SETS=1|2 pins the epilogue organisation (tests); default: both are candidates
         const char* fs = getenv("AQUA_EPI_SETS");
         const int min_sets = (det || chain) ? 1 : (fs ? (atoi(fs) == 2 ? 2 : 1) : 1);
@@ -505,6 +514,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
           for (int pref = 0; pref < 2; ++pref) {
             Cand cd = cd0;
             cd.cluster = cl;
+            cd.pair = pr;
             cd.pref = pref;
             cd.epi_sets = sets;
             fill_candidate(cd, op_batch(c, op), ho, wo, tn, ntn, k.n_steps, k.cpt, c->num_sms, chain ? chain_kg * b2_slot : 0,
@@ -513,7 +523,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
             if (chain && (ntn != 1 || cd.cluster != 1)) continue;
             if (pref == 1 && !choices.empty()) {  // same split as the default order: not a new choice
               const Cand& o = choices.back().cd;
-              if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg) continue;
+              if (o.mode == cd.mode && o.mblk == cd.mblk && o.mx == cd.mx && o.na == cd.na && o.nb == cd.nb && o.n_stg == cd.n_stg && o.pair == cd.pair) continue;
             }
             choices.push_back({tn, ntn, cd});
           }
@@ -550,6 +560,7 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.up_chunks = up_c / 64;
   k.up_hs = sb.h / 2;
   k.cshift = best.cluster == 4 ? 2 : (best.cluster == 2 ? 1 : 0);
+  k.pair = best.pair;
   k.total_tiles = (best.m_tiles + best.cluster - 1) / best.cluster * k.n_tiles_n;
   k.a_group = best.mode == CONV_MODE_HALO ? 9 : 1;
   k.na = best.na;
@@ -562,8 +573,8 @@ int plan_conv_geometry(aq_ctx* c, Op& op, int choice = -1, int* n_choices = null
   k.n_mma = best.mblk > 1 ? 2 : 1;
   k.a_slot_bytes = best.a_slot;
   k.a_tx_bytes = best.a_tx;
-  k.b_slot_bytes = (uint32_t)round_up(k.tile_n * 128, 1024);
-  k.b_tx_bytes = (uint32_t)k.tile_n * 128;
+  k.b_slot_bytes = (uint32_t)round_up((k.pair ? k.tile_n / 2 : k.tile_n) * 128, 1024);
+  k.b_tx_bytes = (uint32_t)(k.pair ? k.tile_n / 2 : k.tile_n) * 128;  // per CTA
   k.stg_bytes = det ? 0 : (uint32_t)kTileM * 128;
   if (det) k.n_stg = 1;
   k.act = det ? ACT_NONE : op.conv.act;
@@ -797,6 +808,9 @@ int autotune_conv(aq_ctx* c, Op& op) {
     }
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
+    if (c->tune_log >= 2)
+      fprintf(stderr, "aqua_b200: tune %s #%d tile_n %d mode %d mblk %d sets %d %s na %d nb %d stg %d res %d: %.4f ms\n", sig.c_str(), i, op.kp.tile_n,
+              op.kp.mode, op.kp.mblk, op.kp.epi_sets, op.kp.pair ? "pair" : "single", op.kp.na, op.kp.nb, op.kp.n_stg, op.kp.b_res, ms / c->tune_iters);
     if (ms < best_ms) {
       best_ms = ms;
       best = i;
@@ -1088,7 +1102,7 @@ int aq_create(int device, aq_ctx** out) {
   c->encode = (EncodeTiledFn)fn;
   if (const char* v = getenv("AQUA_PDL")) c->pdl = atoi(v) != 0;
   if (const char* v = getenv("AQUA_AUTOTUNE")) c->autotune = atoi(v) != 0;
-  if (const char* v = getenv("AQUA_TUNE_LOG")) c->tune_log = atoi(v) != 0;
+  if (const char* v = getenv("AQUA_TUNE_LOG")) c->tune_log = atoi(v);  // 2: one line per timed candidate
   if (const char* v = getenv("AQUA_NMS_MASK")) c->use_det_mask = strcmp(v, "kernel") != 0;
   if (const char* v = getenv("AQUA_SERPENTINE")) c->serpentine = atoi(v) != 0;
   if (const char* v = getenv("AQUA_TUNE_ITERS")) c->tune_iters = atoi(v) > 0 ? atoi(v) : 3;
@@ -1655,7 +1669,7 @@ int aq_op_describe(aq_ctx* c, int i, char* buf, size_t cap) {
     snprintf(buf, cap, "%s k%d s%d %dx%d cin=%d cout=%d res=%d | M=%.0f %s mblk=%d(%dx%d) tileN=%d steps=%d na=%d nb=%d%s stg=%d acc=%d es=%d tile=%dx%d mt=%d nt=%d cl=%d%s | flop=%.4g bytes=%.4g",
              det ? "detect" : "conv", ksz, stride, sb.h, sb.w, c_in, c_out, k.has_res, M, mode_name[k.mode], k.mblk,
              k.mx, k.my, k.tile_n, k.n_steps, k.na, k.nb, k.b_res ? "(res)" : "", k.n_stg, k.acc_stages, k.epi_sets, k.tw, k.th,
-             k.m_tiles, k.n_tiles_n, 1 << k.cshift, stg, flops, bytes);
+             k.m_tiles, k.n_tiles_n, k.pair ? 12 : (1 << k.cshift), stg, flops, bytes);
   } else if (op.kind == OP_POOL) {
     const Buffer& b = c->bufs[op.buf];
     snprintf(buf, cap, "sppf_pool %dx%d c=%d | flop=0 bytes=%.4g", b.h, b.w, op.c, 2.0 * c->batch * b.h * b.w * op.c * 4.0);

@@ -15,11 +15,54 @@ namespace {
 #ifndef AQ_CLUSTER
 #define AQ_CLUSTER 0
 #endif
+// AQ_PAIR=1 (third build of this file): clusters of exactly two CTAs executing tcgen05.mma.cta_group::2 -- one M = 256 MMA per
+// pair, each CTA holding its own 128 rows of A and HALF of every weight tile, so an SM ingests half the weight bytes per output
+// (what bounds the streamed-weight layers: L2 -> SM operand delivery).  The leader (cluster rank 0) issues the
+// MMAs; operand arrivals of both CTAs are counted on the leader's mbarriers, completions are multicast to both.
+#ifndef AQ_PAIR
+#define AQ_PAIR 0
+#endif
+#if AQ_PAIR
+#undef AQ_CLUSTER
+#define AQ_CLUSTER 1
+#endif
 #if AQ_CLUSTER
 #define CSHIFT(p) ((p).cshift)
 #else
 #define CSHIFT(p) 0
 #endif
+
+// Operand loads / barrier traffic of a CTA, single or paired.  `bar` is always the LOCAL address of the barrier.
+__device__ __forceinline__ uint32_t full_bar(uint32_t bar) { return AQ_PAIR ? mapa_rank(bar, 0) : bar; }
+__device__ __forceinline__ void arm_full(uint32_t bar, uint32_t bytes) {  // expect the bytes of one slot fill (of both CTAs of a pair)
+  if (AQ_PAIR) {
+    if (cluster_ctarank() == 0) mbar_arrive_expect_tx(bar, 2u * bytes);
+  } else {
+    mbar_arrive_expect_tx(bar, bytes);
+  }
+}
+__device__ __forceinline__ void ld2d(uint32_t dst, const void* tm, uint32_t bar, int c0, int c1) {
+  if (AQ_PAIR) tma2_load_2d(dst, tm, full_bar(bar), c0, c1);
+  else tma_load_2d(dst, tm, bar, c0, c1);
+}
+__device__ __forceinline__ void ld4d(uint32_t dst, const void* tm, uint32_t bar, int c0, int c1, int c2, int c3) {
+  if (AQ_PAIR) tma2_load_4d(dst, tm, full_bar(bar), c0, c1, c2, c3);
+  else tma_load_4d(dst, tm, bar, c0, c1, c2, c3);
+}
+__device__ __forceinline__ void ld5d(uint32_t dst, const void* tm, uint32_t bar, int c0, int c1, int c2, int c3, int c4) {
+  if (AQ_PAIR) tma2_load_5d(dst, tm, full_bar(bar), c0, c1, c2, c3, c4);
+  else tma_load_5d(dst, tm, bar, c0, c1, c2, c3, c4);
+}
+// MMA completion -> mbarrier (pair: the barrier at this offset in BOTH CTAs)
+__device__ __forceinline__ void commit_to(uint32_t bar) {
+  if (AQ_PAIR) umma2_commit_mc(bar, 3);
+  else umma_commit(bar);
+}
+// an epilogue warp has drained its part of an accumulator stage (pair: the leader's barrier counts both CTAs' warps)
+__device__ __forceinline__ void arrive_tempty(uint32_t bar) {
+  if (AQ_PAIR && cluster_ctarank() != 0) mbar_arrive_cluster(mapa_rank(bar, 0));
+  else mbar_arrive(bar);
+}
 
 struct MBlock {
   int n, y0, x0;  // spatial modes: image, first output row / column
@@ -278,7 +321,8 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
   auto tfull = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + a); };
   auto tempty = [&](uint32_t a) { return bar0 + 8u * (2 * kMaxA + 2 * kMaxB + 2 + a); };
   // loop invariants in registers
-  const uint32_t idesc = make_idesc_f16(kTileM, p.tile_n);
+  if (AQ_PAIR && cluster_ctarank() != 0) return;  // the leader issues for the pair
+  const uint32_t idesc = make_idesc_f16(AQ_PAIR ? 2 * kTileM : kTileM, p.tile_n);
   const uint32_t pw8 = p.pw * 8u;
   // descriptor halves: lo = start>>4 | LBO(1)<<16 ; hi = SBO>>4 | version(1)<<14 | SWIZZLE_128B(2)<<29
   const uint32_t a_hi = ((HALO ? p.pw * 128u : 1024u) >> 4) | (1u << 14) | (2u << 29);
@@ -304,7 +348,8 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
   const uint16_t cmask = (uint16_t)((1u << (1u << CSHIFT(p))) - 1u);  // all CTAs of the cluster
   // a weight slot is refilled by multicast into every CTA of the cluster, so its release goes to all of them
   auto release_b = [&](uint32_t bs) {
-    if (CSHIFT(p)) umma_commit_mc(b_empty(bs), cmask);
+    if (AQ_PAIR) commit_to(b_empty(bs));
+    else if (CSHIFT(p)) umma_commit_mc(b_empty(bs), cmask);
     else umma_commit(b_empty(bs));
   };
   Ring ra, rb, rt;
@@ -324,10 +369,15 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
       for (int q = 0; q < NMY; ++q) {
         const uint32_t d = d_tmem + mb_d[q];
         const uint32_t aq = al + mb_a[q];
-        umma_f16_split(d, aq, a_hi, bl, b_hi, idesc, acc);
-        if (kk > 1) umma_f16_split(d, aq + 2, a_hi, bl + 2, b_hi, idesc, 1u);
-        if (kk > 2) umma_f16_split(d, aq + 4, a_hi, bl + 4, b_hi, idesc, 1u);
-        if (kk > 3) umma_f16_split(d, aq + 6, a_hi, bl + 6, b_hi, idesc, 1u);
+#if AQ_PAIR
+#define AQ_UMMA umma2_f16_split
+#else
+#define AQ_UMMA umma_f16_split
+#endif
+        AQ_UMMA(d, aq, a_hi, bl, b_hi, idesc, acc);
+        if (kk > 1) AQ_UMMA(d, aq + 2, a_hi, bl + 2, b_hi, idesc, 1u);
+        if (kk > 2) AQ_UMMA(d, aq + 4, a_hi, bl + 4, b_hi, idesc, 1u);
+        if (kk > 3) AQ_UMMA(d, aq + 6, a_hi, bl + 6, b_hi, idesc, 1u);
       }
     };
     if (FEED == 2) {
@@ -359,8 +409,8 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
               issue(a_lo + tap_off, b_lo0 + bs * b_slot16, kk);
               if (!BRES) release_b(bs);
               if (j == kTaps[q] - 1) {
-                umma_commit(a_empty(ra.slot));
-                if (q == 3 && c == cpt - 1) umma_commit(tfull(as));
+                commit_to(a_empty(ra.slot));
+                if (q == 3 && c == cpt - 1) commit_to(tfull(as));
               }
             }
             __syncwarp();
@@ -393,8 +443,8 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
             issue(a_lo + tap_off, b_lo0 + bs * b_slot16 + (dense ? 2u * (uint32_t)(tap & 3) : 0u), kk);
             if (!BRES) release_b(bs);  // weight slot reusable once these MMAs retire
             if (tap == 8) {
-              umma_commit(a_empty(ra.slot));
-              if (c == cpt - 1) umma_commit(tfull(as));  // accumulators ready for the epilogue
+              commit_to(a_empty(ra.slot));
+              if (c == cpt - 1) commit_to(tfull(as));  // accumulators ready for the epilogue
             }
           }
           __syncwarp();
@@ -419,8 +469,8 @@ __device__ __forceinline__ void mma_role(const ConvKParams& p, const MmaCtx& mc)
         if (leader) {
           issue(a_lo0 + ra.slot * a_slot16, b_lo0 + bs * b_slot16, kk);
           if (!BRES) release_b(bs);
-          umma_commit(a_empty(ra.slot));
-          if (s == n_steps - 1) umma_commit(tfull(as));
+          commit_to(a_empty(ra.slot));
+          if (s == n_steps - 1) commit_to(tfull(as));
         }
         __syncwarp();
         acc = 1u;
@@ -500,7 +550,7 @@ __device__ __forceinline__ void epi_store_role(const ConvKParams& p, const EpiCt
           // every TMEM read of this tile is done -> the MMA warps may overwrite the accumulators
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty(as));
+          if (lane == 0) arrive_tempty(tempty(as));
         }
         TR_PT(d2);
         // the TMA store that last used this staging buffer must have read it
@@ -633,7 +683,7 @@ __device__ __forceinline__ void epi_store_role2(const ConvKParams& p, const EpiC
     if (j >= G) {  // nothing of this tile is ours: release the accumulators straight away
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty(as));
+      if (lane == 0) arrive_tempty(tempty(as));
     }
     for (; j < G; j += 2) {
       const uint32_t ta = ta0 + (uint32_t)mb * acc_pitch + (uint32_t)g * 64u;
@@ -647,7 +697,7 @@ __device__ __forceinline__ void epi_store_role2(const ConvKParams& p, const EpiC
       if (last_own) {  // every TMEM read of this tile by this warp is done
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty(as));
+        if (lane == 0) arrive_tempty(tempty(as));
       }
       // the TMA store that last used this staging buffer (group k - n_stg) must have read it
       if (k0 + (uint32_t)j >= n_stg) named_bar_sync((set ? kBarStgEmptySet1 : kBarStgEmpty) + buf, kBarStgThreads2);
@@ -1019,11 +1069,11 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
     }
     for (int s = 0; s < p.nb; ++s) {
       mbar_init(b_full(s), 1);
-      mbar_init(b_empty(s), p.n_mma << CSHIFT(p));  // the MMA issuers of every CTA of the cluster
+      mbar_init(b_empty(s), AQ_PAIR ? p.n_mma : (p.n_mma << CSHIFT(p)));  // the MMA issuers of every CTA of a multicast cluster / of the pair's leader
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull(a), p.n_mma);
-      mbar_init(tempty(a), kEpiWarps);
+      mbar_init(tempty(a), AQ_PAIR ? 2 * kEpiWarps : kEpiWarps);  // pair: the leader's counts both CTAs' epilogue warps
     }
     if (EPI == EPI_CHAIN) {
       const ChainBars cb{bar0};
@@ -1040,8 +1090,13 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
     fence_barrier_init();
   }
   if (warp == kWarpMma) {
-    tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
-    tmem_relinquish();
+    if (AQ_PAIR) {
+      tmem_alloc2(smem_u32(&tmem_slot), p.tmem_cols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(smem_u32(&tmem_slot), p.tmem_cols);
+      tmem_relinquish();
+    }
   }
   for (int i = threadIdx.x; i < p.n_tiles_n * p.tile_n; i += blockDim.x) s_bias[i] = __ldg(p.bias + i);
   if (EPI == EPI_CHAIN)
@@ -1090,9 +1145,9 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
             const uint32_t slot = ra.slot;
             TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
             if (!elect_one()) continue;
-            mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+            arm_full(a_full(slot), p.a_tx_bytes);
             patch_issue(sg, t0.y0 - 1, p.ph, p.a_h, a_base + slot * p.a_slot_bytes, row_bytes,
-                        [&](int hb, uint32_t dst, int y, int n) { tma_load_4d(dst, &p.tmH[hb], a_full(slot), c * 64, xl, y, n); });
+                        [&](int hb, uint32_t dst, int y, int n) { ld4d(dst, &p.tmH[hb], a_full(slot), c * 64, xl, y, n); });
           }
           if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
         }
@@ -1120,9 +1175,9 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
           const uint32_t slot = ra.slot;
           TR_WAIT(trw, mbar_wait(a_empty(slot), ra.phase ^ 1u));
           if (!elect_one()) continue;
-          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+          arm_full(a_full(slot), p.a_tx_bytes);
           patch_issue(sg, t0.y0 - 1, p.ph, p.a_h, a_base + slot * p.a_slot_bytes, row_bytes, [&](int hb, uint32_t dst, int y, int n) {
-            tma_load_5d(dst, xp ? &p.tmH2[hb] : &p.tmH[hb], a_full(slot), c * 64, xl, yp, y, n);
+            ld5d(dst, xp ? &p.tmH2[hb] : &p.tmH[hb], a_full(slot), c * 64, xl, yp, y, n);
           });
         }
         if (lane == 0) trace_put<TRACE>(p, 0, it, tr0, trw, 0, TR_NOW());
@@ -1153,9 +1208,9 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
             ++tap;
           }
           if (!elect_one()) continue;
-          mbar_arrive_expect_tx(a_full(slot), p.a_tx_bytes);
+          arm_full(a_full(slot), p.a_tx_bytes);
           if (p.mode == CONV_MODE_FLAT) {
-            tma_load_2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
+            ld2d(dst, &p.tmA, a_full(slot), grp * 64, m_tile * p.mblk * kTileM);
           } else {
             for (int mb = 0; mb < p.mblk; ++mb) {
               const MBlock t = mb ? tb1 : tb0;
@@ -1164,15 +1219,15 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
                 // 1x1 conv over [upsample2x(low-res tensor) | src]: the first up_chunks chunks are read from the
                 // half-resolution tensor through tmUp = (c, dx, W/2, dy, H/2 * N) whose dx / dy dimensions have
                 // stride 0, so the box {64, 2, tw/2, 2, th/2} lands as the tw x th tile of replicated pixels
-                if (grp < p.up_chunks) tma_load_5d(d, &p.tmUp, a_full(slot), c0, 0, t.x0 >> 1, 0, t.n * p.up_hs + (t.y0 >> 1));
-                else tma_load_4d(d, &p.tmA, a_full(slot), c0 - p.up_chunks * 64, t.x0, t.y0, t.n);
+                if (grp < p.up_chunks) ld5d(d, &p.tmUp, a_full(slot), c0, 0, t.x0 >> 1, 0, t.n * p.up_hs + (t.y0 >> 1));
+                else ld4d(d, &p.tmA, a_full(slot), c0 - p.up_chunks * 64, t.x0, t.y0, t.n);
               } else if (p.stride == 1) {
-                tma_load_4d(d, &p.tmA, a_full(slot), c0, t.x0 + kw - 1, t.y0 + kh - 1, t.n);
+                ld4d(d, &p.tmA, a_full(slot), c0, t.x0 + kw - 1, t.y0 + kh - 1, t.n);
               } else {
                 // input row 2*Y + kh - 1: kh=0 -> (parity 1, Y-1), kh=1 -> (0, Y), kh=2 -> (1, Y); same in x
                 const int yp = (kh + 1) & 1, dy = (kh == 0) ? -1 : 0;
                 const int xp = (kw + 1) & 1, dx = (kw == 0) ? -1 : 0;
-                tma_load_5d(d, xp ? &p.tmA2 : &p.tmA, a_full(slot), c0, t.x0 + dx, yp, t.y0 + dy, t.n);
+                ld5d(d, xp ? &p.tmA2 : &p.tmA, a_full(slot), c0, t.x0 + dx, yp, t.y0 + dy, t.n);
               }
             }
           }
@@ -1193,8 +1248,10 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
       const int n_res = p.b_dense ? p.nb : p.n_steps;
       for (int s = 0; s < n_res; ++s) {
         if (elect_one()) {
-          mbar_arrive_expect_tx(b_full(s), p.b_tx_bytes);
-          tma_load_2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), (p.b_dense ? s : weight_chunk(p, s)) * 64, 0);
+          arm_full(b_full(s), p.b_tx_bytes);
+          // pair: this CTA keeps rows [rank * tile_n / 2, +tile_n / 2) of the tile (tmB's box is tile_n >> cshift rows)
+          ld2d(b_base + s * p.b_slot_bytes, &p.tmB, b_full(s), (p.b_dense ? s : weight_chunk(p, s)) * 64,
+               AQ_PAIR ? (int)(cluster_ctarank() * ((uint32_t)p.tile_n >> 1)) : 0);
         }
       }
     } else {
@@ -1210,8 +1267,12 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
           const uint32_t slot = rb.slot;
           TR_WAIT(trw, mbar_wait(b_empty(slot), rb.phase ^ 1u));
           if (elect_one()) {
-            mbar_arrive_expect_tx(b_full(slot), p.b_tx_bytes);
-            if (CSHIFT(p)) {
+            arm_full(b_full(slot), p.b_tx_bytes);
+            if (AQ_PAIR) {
+              // this CTA's half of the tile's rows into ITS shared memory; the MMA reads both halves
+              ld2d(b_base + slot * p.b_slot_bytes, &p.tmB, b_full(slot), weight_chunk(p, s) * 64,
+                   n0 + (int)(cluster_ctarank() * ((uint32_t)p.tile_n >> 1)));
+            } else if (CSHIFT(p)) {
               // this CTA's share of the tile's rows, multicast to every CTA of the cluster (tmB's box is
               // tile_n >> cshift rows); the other shares arrive from the peers on the same barrier
               const uint32_t r = cluster_ctarank();
@@ -1384,7 +1445,7 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
           if (mb == p.mblk - 1) {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty(as));
+            if (lane == 0) arrive_tempty(tempty(as));
           }
         }
       }
@@ -1399,32 +1460,39 @@ __global__ void __launch_bounds__(EPI == EPI_CHAIN ? kConvThreadsChain : kConvTh
   if (CSHIFT(p)) cluster_sync_all();
   if (warp == kWarpMma) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    if (AQ_PAIR) tmem_dealloc2(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
   }
 }
 
 }  // namespace
 
-#if AQ_CLUSTER
+#if AQ_PAIR
+#define AQ_VARIANT(x) x##_pair
+#elif AQ_CLUSTER
 #define AQ_VARIANT(x) x##_cl
 #else
 #define AQ_VARIANT(x) x##_nocl
 #endif
 cudaError_t conv_kernels_init_cl();
 cudaError_t conv_kernels_init_nocl();
+cudaError_t conv_kernels_init_pair();
 cudaError_t launch_conv_cl(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
 cudaError_t launch_conv_nocl(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
+cudaError_t launch_conv_pair(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream);
 
-#if !AQ_CLUSTER
+#if !AQ_CLUSTER && !AQ_PAIR
 size_t conv_smem_bytes(const ConvKParams& p) {
   return (size_t)p.na * p.a_slot_bytes + (size_t)p.nb * p.b_slot_bytes + (size_t)p.n_stg * p.stg_bytes + 1024 +
          (p.chain ? (size_t)p.chain_kg * p.b2_slot_bytes : 0);
 }
 cudaError_t conv_kernels_init() {
   cudaError_t e = conv_kernels_init_nocl();
-  return e == cudaSuccess ? conv_kernels_init_cl() : e;
+  if (e == cudaSuccess) e = conv_kernels_init_cl();
+  return e == cudaSuccess ? conv_kernels_init_pair() : e;
 }
 cudaError_t launch_conv(const ConvKParams& p, int epi, int num_sms, int pdl, cudaStream_t stream) {
+  if (p.pair) return launch_conv_pair(p, epi, num_sms, pdl, stream);
   return p.cshift ? launch_conv_cl(p, epi, num_sms, pdl, stream) : launch_conv_nocl(p, epi, num_sms, pdl, stream);
 }
 #endif

@@ -87,6 +87,7 @@ struct alignas(64) ConvKParams {
   // all, which divides the weight traffic L2 -> SM by the cluster size.  total_tiles = ceil(m_tiles / cluster) *
   // n_tiles_n cluster-tiles; M tiles past m_tiles are computed on zero-filled operands and clipped by the stores.
   int cshift, total_tiles;
+  int pair;  // 1: clusters of two CTAs running tcgen05.mma.cta_group::2 (M = 256 per pair; each CTA keeps half of every weight tile)
   // Tile order: 0 = ascending, 1 = descending (tile t of the persistent loop works on tile total - 1 - t).  The plan
   // alternates it from op to op ("serpentine"): a layer then starts on the tiles its producer wrote LAST, which still
   // sit in the 126 MB L2, instead of on the ones written first, which have long been evicted to HBM.

@@ -150,7 +150,8 @@ def test_conv3x3_halo_four_blocks(ctx):
     run_conv_case(ctx, 5, 20, 20, 48, 48, 3, 1, mode=1, mblk=4, res=True)
     run_conv_case(ctx, 3, 36, 52, 96, 48, 3, 1, mode=1, mblk=4)   # two 64-wide chunks per tap; 96 -> 96 no longer fits 4 blocks
     with pytest.raises(engine.AquaError, match="no tiling fits"):  # ... and is refused, not silently re-tiled
-        run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4)
+        run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4, cluster=1)
+    run_conv_case(ctx, 3, 36, 52, 96, 96, 3, 1, mode=1, mblk=4)   # a CTA pair keeps half the weights per CTA: fits
     run_conv_case(ctx, 7, 12, 9 * 8, 64, 32, 3, 1, mode=1, mblk=4)
 
 
@@ -173,6 +174,44 @@ def test_conv_cluster_multicast(ctx, cluster):
     run_conv_case(ctx, 2, 40, 40, 96, 192, 3, 2, cluster=cluster)                  # TAP stride 2
     run_conv_case(ctx, 3, 40, 40, 384, 768, 3, 2, cluster=cluster, mblk=1)         # TAP stride 2, 3 N tiles
     run_conv_case(ctx, 16, 80, 80, 192, 384, 3, 2, cluster=cluster)                # many tiles per cluster (ring wrap)
+
+
+# CTA pairs (cluster value 12): tcgen05.mma.cta_group::2 -- one M = 256 MMA per cluster of two CTAs, each keeping half
+# of every weight tile; streamed and resident weights, every A-feed mode, odd M-tile counts, residual, channel slices
+def test_conv_cta_pair(ctx):
+    run_conv_case(ctx, 1, 16, 16, 64, 64, 1, 1, cluster=12)                        # one pair, one K step
+    run_conv_case(ctx, 3, 20, 20, 384, 384, 1, 1, cluster=12)                      # FLAT, several N tiles
+    run_conv_case(ctx, 5, 20, 12, 768, 384, 1, 1, cluster=12, mblk=1)              # odd number of M tiles
+    run_conv_case(ctx, 2, 40, 40, 192, 192, 3, 1, cluster=12, res=True)            # HALO
+    run_conv_case(ctx, 3, 20, 20, 384, 384, 3, 1, cluster=12, mode=1)              # HALO, tall coordinates
+    run_conv_case(ctx, 3, 20, 20, 768, 768, 3, 1, cluster=12)                      # streamed weights, long K
+    run_conv_case(ctx, 2, 40, 40, 96, 192, 3, 2, cluster=12)                       # stride 2
+    run_conv_case(ctx, 3, 40, 40, 384, 768, 3, 2, cluster=12, mblk=1)              # stride 2, 3 N tiles
+    run_conv_case(ctx, 16, 80, 80, 192, 384, 3, 2, cluster=12)                     # many tiles per pair (ring wrap)
+    run_conv_case(ctx, 16, 80, 80, 96, 96, 1, 1, cluster=12, src_ct=192, src_off=96, dst_ct=192, dst_off=96)
+    run_conv_case(ctx, 8, 40, 40, 192, 192, 1, 1, cluster=12, tile_n=192)          # N = 192: 96-row halves
+    run_conv_case(ctx, 8, 40, 40, 192, 192, 3, 1, cluster=12, mblk=2)              # two M blocks per CTA
+
+
+def test_conv_cta_pair_bit_equal_to_single(ctx):
+    """The pair's M = 256 MMA accumulates each output element over K in the same order as the single-CTA kernel
+    with the same tiling: outputs are bit-identical."""
+    outs = []
+    for cluster in (1, 12):
+        g = torch.Generator().manual_seed(5)
+        x = torch.randn(4, 40, 40, 384, generator=g).half()
+        w = (torch.randn(384, 384, 3, 3, generator=g) / 60).half().float()
+        b = torch.randn(384, generator=g)
+        ctx.plan_begin(4, 64, 64, 3)
+        bs = ctx.buffer(40, 40, 384)
+        bd = ctx.buffer(40, 40, 384)
+        ctx.conv((bs, 0), (bd, 0), w, b, 3, 1, True, None, 128, 1, 1, cluster)
+        ctx.plan_end()
+        ctx.upload(bs, x.numpy())
+        ctx.forward()
+        ctx.sync()
+        outs.append(ctx.download(bd).copy())
+    assert np.array_equal(outs[0], outs[1])
 
 
 # nn.Upsample(2,'nearest') + Concat folded into a 1x1 conv's loads: the first up_c input channels come from a

@@ -9,13 +9,14 @@ out = sys.argv[1]
 cfgs = [tuple(int(v) for v in a.split(":")) for a in sys.argv[2:]] or [(64, 640), (16, 1280), (32, 640), (16, 640), (8, 640), (4, 640), (3, 640), (2, 640), (1, 640), (2, 1280), (4, 1280)]
 if os.path.exists(out):
     os.remove(out)
-os.environ.update(AQUA_AUTOTUNE="1", AQUA_TUNE_CACHE=out, AQUA_TUNE_TABLE="0", AQUA_TUNE_LOG="0")
+os.environ.update(AQUA_AUTOTUNE="1", AQUA_TUNE_CACHE=out, AQUA_TUNE_TABLE="0")
+os.environ.setdefault("AQUA_TUNE_LOG", "0")
 os.environ.setdefault("AQUA_TUNE_ITERS", "10")
 import torch
 from aquaculture_b200 import engine, tiles, weights
 sd = weights.synthetic_state(3, 0)
 for b, img in cfgs:
-    for chain in ("feed,c3", "0", "c3", "feed"):  # the default plan and the unchained / partly chained ones (tests, A/B runs)
+    for chain in os.environ.get("TUNE_CHAINS", "feed,c3;0;c3;feed").split(";"):  # the default plan and the unchained / partly chained ones (tests, A/B runs)
         os.environ["AQUA_CHAIN"] = chain
         det = engine.TileDetector(sd, 3, batch=b, imgsz=(img, img))
         det.detect(torch.from_numpy(tiles.synthetic_tiles(range(b), img, img)).pin_memory())

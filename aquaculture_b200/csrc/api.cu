@@ -1789,16 +1789,22 @@ int aq_nms(aq_ctx* c, const float* pred, int batch, int rows, int no, float conf
   p.dets = dets_out; p.counts = counts_out; p.keep_rows = keep_rows_out;
   static const bool nms_clk = getenv("AQUA_NMS_CLK") != nullptr;
   p.dbg_clk = nullptr;
-  if (nms_clk) {  // phase timeline of image 0's CTA (debug): printed after a synchronising copy
+  p.dbg_mode = 0;
+  if (nms_clk) {
+    p.dbg_mode = atoi(getenv("AQUA_NMS_CLK"));  // phase timeline of image 0's CTA (debug): printed after a synchronising copy
     static long long* d_clk = nullptr;
-    if (!d_clk) cudaMalloc(&d_clk, 8 * sizeof(long long));
+    if (!d_clk) cudaMalloc(&d_clk, 16 * sizeof(long long));
     p.dbg_clk = d_clk;
+    cudaMemsetAsync(d_clk, 0, 16 * sizeof(long long), s);
     CU_CHECK(c, launch_nms(p, batch, s));
-    long long h[8] = {0};
+    long long h[16] = {0};
     cudaMemcpyAsync(h, d_clk, sizeof h, cudaMemcpyDeviceToHost, s);
     cudaStreamSynchronize(s);
-    fprintf(stderr, "nms phases (clk): count %lld, compaction %lld, sort %lld, suppression %lld, total %lld\n", h[1] - h[0], h[2] - h[1], h[3] - h[2],
-            h[4] - h[3], h[4] - h[0]);
+    fprintf(stderr, "nms phases (clk): count %lld, compaction %lld, sort %lld, suppression %lld (%lld clk to the end of the first 1024 candidates, %lld more to the end of the second block's shared catch-up), total %lld\n",
+            h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[3], h[6] ? h[6] - h[5] : 0, h[4] - h[0]);
+    if (h[8])
+      fprintf(stderr, "nms sort, first radix pass (clk): zero + histogram walk %lld, scan over (digit, warp) %lld, digit scan %lld, scatter walk %lld\n", h[8] - h[2], h[9] - h[8],
+              h[10] - h[9], h[11] - h[10]);
     return AQ_OK;
   }
   CU_CHECK(c, launch_nms(p, batch, s));

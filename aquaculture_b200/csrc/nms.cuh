@@ -29,7 +29,8 @@ struct NmsParams {
   float* dets;     // (batch, max_det, 6)
   int* counts;     // (batch)
   int* keep_rows;  // (batch, max_det) or nullptr
-  long long* dbg_clk;  // optional (AQUA_NMS_CLK): 8 clock64 stamps of image 0's CTA at the phase boundaries
+  long long* dbg_clk;  // optional (AQUA_NMS_CLK): 16 clock64 stamps of image 0's CTA at the phase boundaries
+  int dbg_mode;        // AQUA_NMS_CLK=2 / 3: timing experiments that skip parts of the suppression (wrong results)
 };
 
 size_t nms_scratch_bytes(int batch, int rows);

@@ -367,7 +367,6 @@ void fill_candidate(Cand& cd, int batch, int ho, int wo, int tile_n, int n_tiles
     grow(cd.na, halo_na_cap, cd.a_slot);
     if (!cd.b_res) grow(cd.nb, 12, b_slot);
   }
-  if (cd.epi_sets == 2 && (cd.n_stg & 1) && getenv("AQUA_ES2_EVEN_STG")) cd.n_stg -= 1;  // debug: see DESIGN.md 3.1 (race hunt)
   // ---- cost
   const double mma = (double)n_steps * cd.mblk * 4.0 * (tile_n / 2.0) + 40.0 * n_steps;
   const double a_bytes = (double)n_groups * cd.a_tx;
@@ -893,7 +892,7 @@ int launch_op(aq_ctx* c, Op& op, int sub, cudaStream_t s) {
   cudaError_t e = cudaSuccess;
   switch (op.kind) {
     case OP_CONV: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], op_epi(op), c->num_sms, c->pdl, s); break;
-    case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl && !getenv("AQUA_PDL_DET_OFF"), s); break;
+    case OP_DETECT: e = launch_conv(op.kps.empty() ? op.kp : op.kps[sub], EPI_DETECT, c->num_sms, c->pdl, s); break;
     case OP_POOL: {
       const Buffer& b = c->bufs[op.buf];
       e = launch_sppf_pool(buf_base(c, op.buf, op, sub), op_batch(c, op), b.h, b.w, b.c, op.c_off, op.c, s);

@@ -8,7 +8,7 @@ timeout 1500 ncu --metrics $M --clock-control none -k regex:'conv_igemm|sppf' -s
     python tools/forward_only.py > gpurun_out/ncu_layers.log 2>&1
 echo "ncu layers exit=$?"; cat gpurun_out/fwd_plain.log | tail -2
 timeout 300 python tools/profile_ops.py --out gpurun_out/ops_r2.txt > /dev/null 2> gpurun_out/ops_r2.err; tail -1 gpurun_out/ops_r2.txt
-for spec in "stem 142" "l1_chain_cv12 143" "c192_3x3_40 162" "pair_c1536_1x1_20 182" "c768_1x1_20 210"; do
+for spec in "stem 142" "l1_chain_cv12 143" "c192_3x3_40 162" "pair_c1536_1x1_20 182" "c384_3x3_20 210"; do
   set -- $spec
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv_igemm -s $2 -c 1 -f -o gpurun_out/full_r2_$1 \
       python tools/forward_only.py > gpurun_out/ncu_full_$1.log 2>&1

@@ -431,6 +431,31 @@ def test_nms_heavy_overlap(ctx):
     _check_nms(ctx, pred, iou_thres=0.2)
 
 
+def test_nms_iou_near_threshold_band(ctx):
+    """The kernel decides most pairs without dividing (inter < 0.999998 * thr * union) and divides only inside a +-2e-6 band
+    around the threshold: 3000 isolated pairs whose IoU lies within +-1e-5 (relative) of iou_thres, on both sides and
+    inside the band, must come out exactly as the oracle's fp32 quotient compared as double says."""
+    g = torch.Generator().manual_seed(23)
+    n_pairs = 3000
+    pred = torch.zeros(1, 2 * n_pairs, 6)
+    gx = (torch.arange(n_pairs) % 60).float() * 400 + 200 + torch.rand(n_pairs, generator=g)
+    gy = (torch.arange(n_pairs) // 60).float() * 400 + 200 + torch.rand(n_pairs, generator=g)
+    w = 80 + 40 * torch.rand(n_pairs, generator=g)
+    h = 60 + 60 * torch.rand(n_pairs, generator=g)
+    thr = 0.45
+    dx = w * (1 - thr) / (1 + thr) * (1 + (torch.rand(n_pairs, generator=g) - 0.5) * 4e-5)  # IoU = (w - dx) / (w + dx)
+    pred[0, 0::2, 0], pred[0, 0::2, 1], pred[0, 0::2, 2], pred[0, 0::2, 3] = gx, gy, w, h
+    pred[0, 1::2, 0], pred[0, 1::2, 1], pred[0, 1::2, 2], pred[0, 1::2, 3] = gx + dx, gy, w, h
+    pred[0, 0::2, 4] = 0.9 - 1e-5 * torch.arange(n_pairs)
+    pred[0, 1::2, 4] = 0.6 - 1e-5 * torch.arange(n_pairs)
+    pred[0, :, 5] = 1.0
+    ref = ONMS.non_max_suppression(pred, iou_thres=thr, max_det=2 * n_pairs)
+    kept_second = len(ref[0]) - n_pairs
+    assert 0.2 * n_pairs < kept_second < 0.8 * n_pairs, kept_second  # the pairs really straddle the threshold
+    _check_nms(ctx, pred, iou_thres=thr, max_det=2 * n_pairs)
+    _check_nms(ctx, pred, iou_thres=thr, max_det=2 * n_pairs, agnostic=True)
+
+
 def test_nms_iou_threshold_is_double_compare(ctx):
     # SURVEY App. C1-v: fp32 IoU exactly 0.1f (> 0.1 as double) must be suppressed at iou_thres=0.1
     pred = torch.zeros(1, 4, 6)

@@ -136,6 +136,8 @@ struct aq_ctx {
   void* tab_dev = nullptr;
   PreParams pre{};
   void* stats_scratch = nullptr;  // aq_tile_stats: column sums + TileStats
+  int* win_list_dev = nullptr;    // aq_detect_window_list: window indices of one batch
+  int win_list_cap = 0;
   size_t stats_bytes = 0;
   void* jpeg_scratch = nullptr;   // aq_jpeg_reconstruct: component planes (+ staged coefficients / tables for host input)
   size_t jpeg_bytes = 0;
@@ -1150,6 +1152,7 @@ void aq_destroy(aq_ctx* c) {
   if (c->tab_dev) cudaFree(c->tab_dev);
   if (c->nms_scratch) cudaFree(c->nms_scratch);
   if (c->stats_scratch) cudaFree(c->stats_scratch);
+  if (c->win_list_dev) cudaFree(c->win_list_dev);
   if (c->jpeg_scratch) cudaFree(c->jpeg_scratch);
   for (int i = 0; i < 2; ++i) {
     if (c->jpk_stage[i]) cudaFree(c->jpk_stage[i]);
@@ -1873,7 +1876,7 @@ int window_params(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster
   PreParams p = c->pre;
   p.src = raster_dev; p.n = n; p.bgr = bgr;
   p.row_pitch = (size_t)raster_w * 3; p.windowed = 1; p.wins_y = wins_y; p.win0 = win0;
-  p.out_s2d = nullptr; p.out_u8 = nullptr;
+  p.out_s2d = nullptr; p.out_u8 = nullptr; p.win_list = nullptr;
   *out = p;
   return AQ_OK;
 }
@@ -1901,6 +1904,42 @@ int aq_detect_windows(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int ra
   if (rc < 0) return rc;
   CU_CHECK(c, cudaStreamSynchronize(s));
   return slot;  // >= 0: the ticket aq_detect_stage_ms takes
+}
+
+int aq_detect_window_list(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, const int* win_idx,
+                          int n, int bgr, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
+                          int n_classes, float* dets_host, int* counts_host, void* stream) {
+  if (!c || !dets_host || !counts_host || !win_idx) return AQ_ERR_ARG;
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  PreParams p;
+  int rc = window_params(c, raster_dev, raster_h, raster_w, win_h, win_w, 0, 1, bgr, &p);
+  if (rc) return rc;
+  const int n_wins = (raster_w / win_w) * (raster_h / win_h);
+  if (n <= 0 || n > c->batch) return fail(c, AQ_ERR_ARG, "window list: %d windows (plan batch %d)", n, c->batch);
+  for (int i = 0; i < n; ++i)
+    if (win_idx[i] < 0 || win_idx[i] >= n_wins) return fail(c, AQ_ERR_ARG, "window list: index %d outside the %d full windows", win_idx[i], n_wins);
+  if (c->win_list_cap < n) {
+    if (c->win_list_dev) cudaFree(c->win_list_dev);
+    c->win_list_dev = nullptr;
+    c->win_list_cap = 0;
+    CU_CHECK(c, cudaMalloc(&c->win_list_dev, (size_t)c->batch * sizeof(int)));
+    c->win_list_cap = c->batch;
+  }
+  CU_CHECK(c, cudaMemcpyAsync(c->win_list_dev, win_idx, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+  p.n = n;
+  p.win_list = c->win_list_dev;
+  p.out_s2d = c->bufs[0].ptr;
+  const int slot = c->pipe_slot;
+  c->pipe_slot ^= 1;
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][0], s));
+  c->stage_timed[slot] = false;
+  CU_CHECK(c, launch_preprocess(p, s));
+  CU_CHECK(c, cudaEventRecord(c->ev_stage[slot][1], s));
+  rc = forward_nms_d2h(c, n, conf_thres, iou_thres, max_det, agnostic, classes, n_classes, dets_host, counts_host, s, slot);
+  if (rc < 0) return rc;
+  CU_CHECK(c, cudaStreamSynchronize(s));
+  return slot;
 }
 
 int aq_preprocess_windows_u8(aq_ctx* c, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,

@@ -14,7 +14,7 @@ namespace {
 //   vertical pass    out = (((ay0*(S0>>4))>>16) + ((ay1*(S1>>4))>>16) + 2) >> 2
 __device__ __forceinline__ const uint8_t* tile_base(const PreParams& p, int n) {
   if (!p.windowed) return p.src + (size_t)n * p.in_h * p.row_pitch;
-  const int w = p.win0 + n, ix = w / p.wins_y, iy = w - ix * p.wins_y;
+  const int w = p.win_list ? __ldg(p.win_list + n) : p.win0 + n, ix = w / p.wins_y, iy = w - ix * p.wins_y;
   return p.src + (size_t)iy * p.in_h * p.row_pitch + (size_t)ix * p.in_w * 3;
 }
 

@@ -22,6 +22,7 @@ struct PreParams {
   // like the reference's loop: index = ix * wins_y + iy, origin (ix * in_w, iy * in_h)), row_pitch = raster_w * 3.
   size_t row_pitch;
   int windowed, wins_y, win0;
+  const int* win_list;  // optional (device, n entries): tile n is window win_list[n] instead of win0 + n (blank windows left out)
   __half* out_s2d;     // (n, net_h/2, net_w/2, 16) fp16, channel (py*2+px)*3 + rgb, 12..15 = 0
   uint8_t* out_u8;     // (n, net_h, net_w, 3) RGB, optional debug/parity output
 };

@@ -254,6 +254,7 @@ def run(opt, argv) -> int:
     device_jpeg = opt.jpeg_decode in ("device", "hybrid") and opt.raster_tile <= 0
     raster_jpeg = opt.jpeg_decode == "device" and opt.raster_tile > 0  # a .jpeg raster is decoded straight into device memory
     n_host_decoded = [0]
+    n_blank = [0]  # windows --skip-blank kept away from the network
 
     def load(item):
         kind, v = item
@@ -408,17 +409,29 @@ def run(opt, argv) -> int:
             if raster is None:
                 raster = torch.from_numpy(np.ascontiguousarray(im)).to(f"cuda:{device}")
             dt[0] += time.perf_counter() - t0
-            for k0 in range(0, len(wins), B):
-                nb = min(B, len(wins) - k0)
+            live = list(range(len(wins)))
+            if opt.skip_blank:
+                # measure every window first; the blank ones never reach the network (the reference does not even download
+                # such images [REF src/load_data/download_french_data.py:58-60])
                 t1 = time.perf_counter()
-                res = det.detect_windows(raster, T, k0, nb, bgr=True)
-                if opt.skip_blank:
+                live = []
+                for k0 in range(0, len(wins), B):
+                    nb = min(B, len(wins) - k0)
                     st = engine.tile_stats(det.ctx, raster, bgr=True, tile=T, win0=k0, n=nb)
-                    for i in range(nb):
-                        if engine.is_blank(st[i]):
-                            res.counts[i] = 0
+                    live += [k0 + i for i in range(nb) if not engine.is_blank(st[i])]
+                n_blank[0] += len(wins) - len(live)
+                seen += len(wins) - len(live)
+                dt[1] += time.perf_counter() - t1
+            for k0 in range(0, len(live), B):
+                idx = live[k0:k0 + B]
+                nb = len(idx)
+                t1 = time.perf_counter()
+                if idx == list(range(idx[0], idx[0] + nb)):
+                    res = det.detect_windows(raster, T, idx[0], nb, bgr=True)
+                else:
+                    res = det.detect_window_list(raster, T, idx, bgr=True)
                 if opt.save_txt:
-                    paths = [str(label_dir / f"{stem}_{x}_{y}.txt") for x, y in wins[k0:k0 + nb]]
+                    paths = [str(label_dir / f"{stem}_{wins[k][0]}_{wins[k][1]}.txt") for k in idx]
                     n_files += engine.write_labels(res, net_hw, [(T, T)] * nb, paths, save_conf=opt.save_conf, threads=opt.io_threads)
                 dt[1] += time.perf_counter() - t1
                 seen += nb
@@ -481,6 +494,8 @@ def run(opt, argv) -> int:
               f"({opt.batch_size}, 3, {imgsz[0]}, {imgsz[1]})")
         # ... and what the host sees around them
         print(f"Host: {dt[0] * per:.2f}ms load, {dt[1] * per:.2f}ms wait+labels per image; {totals[0] / wall:.1f} tiles/s over {world} GPU(s)")
+        if n_blank[0]:
+            print(f"{n_blank[0]} blank window(s) skipped before inference (--skip-blank; this rank)")
         if n_host_decoded[0]:
             print(f"{n_host_decoded[0]} JPEG file(s) of a variant without a device path were decoded with cv2 on the host")
         if opt.save_txt:

@@ -556,6 +556,29 @@ class TileDetector:
         self.stage_tiles += n
         return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
 
+    def detect_window_list(self, raster: torch.Tensor, tile: int, win_idx: Sequence[int], bgr=True) -> Detections:
+        """detect_windows for an arbitrary list of window indices (<= batch of them): how --skip-blank keeps the windows
+        src/utils.py::is_blank calls blank away from the network [REF src/utils.py:325-350; the reference does not
+        download such images, REF src/load_data/download_french_data.py:58-60]."""
+        assert raster.is_cuda and raster.dtype == torch.uint8 and raster.is_contiguous() and raster.shape[2] == 3
+        n = len(win_idx)
+        if self._dets is None:
+            self._dets = [torch.empty(self.batch, self.max_det, 6, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._counts = [torch.empty(self.batch, dtype=torch.int32).pin_memory() for _ in range(2)]
+        cls_arr = (C.c_int * len(self.classes))(*self.classes) if self.classes else None
+        idx = (C.c_int * n)(*[int(i) for i in win_idx])
+        torch.cuda.current_stream(raster.device).synchronize()  # the raster was produced on torch's stream
+        slot = self.ctx.call("aq_detect_window_list", C.c_void_p(raster.data_ptr()), raster.shape[0], raster.shape[1], tile, tile, idx, n,
+                             int(bgr), self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
+                             len(self.classes) if self.classes else 0, C.c_void_p(self._dets[0].data_ptr()),
+                             C.c_void_p(self._counts[0].data_ptr()), None)
+        ms = (C.c_float * 3)()
+        self.ctx.call("aq_detect_stage_ms", slot, ms)
+        for k in range(3):
+            self.stage_ms[k] += ms[k]
+        self.stage_tiles += n
+        return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
+
     def close(self):
         self.ctx.close()
 

@@ -391,6 +391,16 @@ int aq_jpeg_debug_parallel_decode(const uint8_t* scan, size_t scan_bytes, const 
 int aq_detect_windows(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w, int win0,
                       int n, int bgr, float conf_thres, double iou_thres, int max_det, int agnostic, const int* classes,
                       int n_classes, float* dets_host, int* counts_host, void* stream);
+
+/*
+ * The same for an arbitrary list of windows: tile i of the batch is window win_idx[i] (host array, n <= plan batch) of the
+ * grid described above.  This is how --skip-blank works: aq_tile_stats measures every window first and the windows
+ * src/utils.py::is_blank calls blank [REF src/utils.py:325-350] never reach the network -- the reference does not even
+ * download such images [REF src/load_data/download_french_data.py:58-60].
+ */
+int aq_detect_window_list(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w,
+                          const int* win_idx, int n, int bgr, float conf_thres, double iou_thres, int max_det, int agnostic,
+                          const int* classes, int n_classes, float* dets_host, int* counts_host, void* stream);
 /* Letterboxed uint8 windows (n, net_h, net_w, 3) RGB, for bit-exact checks against cropping + aq_preprocess_u8. */
 int aq_preprocess_windows_u8(aq_ctx* ctx, const uint8_t* raster_dev, int raster_h, int raster_w, int win_h, int win_w,
                              int win0, int n, int bgr, uint8_t* out_dev, void* stream);

@@ -716,6 +716,13 @@ def test_e2e_raster_windows_equal_tiles(synthetic_sd):
         assert (rw.counts == rt.counts).all() and rw.counts.sum() > 0
         for i in range(len(wins)):
             assert (rw.dets[i, :rw.counts[i]] == rt.dets[i, :rt.counts[i]]).all()
+        # an arbitrary list of windows (aq_detect_window_list: how --skip-blank leaves windows out), any order, repeats allowed
+        idx = [4, 0, 5, 0, 2]
+        rl = det.detect_window_list(torch.from_numpy(raster).cuda(), tile, idx, bgr=True)
+        for k, i in enumerate(idx):
+            assert rl.counts[k] == rw.counts[i] and (rl.dets[k, :rl.counts[k]] == rw.dets[i, :rw.counts[i]]).all()
+        with pytest.raises(engine.AquaError, match="outside"):
+            det.detect_window_list(torch.from_numpy(raster).cuda(), tile, [0, 6], bgr=True)
     finally:
         det.close()
 

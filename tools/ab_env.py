@@ -16,7 +16,12 @@ for spec in specs:
     kv = dict(x.split("=", 1) for x in spec.split("+")) if spec != "-" else {}  # NAME=VALUE+NAME=VALUE
     old = {k: os.environ.get(k) for k in kv}
     os.environ.update(kv)
+    from aquaculture_b200 import _lib
+    shipped = _lib.TUNE_TABLE
+    if "TABLE" in kv:  # TABLE=<path>: another tiling table for this spec only (read when the context is created)
+        _lib.TUNE_TABLE = kv["TABLE"]
     det = engine.TileDetector(sd, 3, batch=B, imgsz=(IMG, IMG))
+    _lib.TUNE_TABLE = shipped
     for k, v in old.items():
         if v is None:
             os.environ.pop(k, None)

@@ -87,6 +87,8 @@ SIGNATURES = {
                                         C.c_void_p]),
     "aq_preprocess_windows_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]),
+    "aq_tile_stats_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_void_p]),
     "aq_tile_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_void_p, C.c_void_p]),
     "aq_geocode_label_text": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.c_int, C.c_int, C.c_int,

@@ -139,6 +139,8 @@ struct aq_ctx {
   int* win_list_dev = nullptr;    // aq_detect_window_list: window indices of one batch
   int win_list_cap = 0;
   size_t stats_bytes = 0;
+  unsigned int* stats_static = nullptr;        // aq_tile_stats_static: device address of the library's static column-sum array
+  cudaError_t stats_static_err = cudaSuccess;  // ... or why it could not be resolved at aq_create
   void* jpeg_scratch = nullptr;   // aq_jpeg_reconstruct: component planes (+ staged coefficients / tables for host input)
   size_t jpeg_bytes = 0;
   // aq_jpeg_reconstruct_packed: two device staging areas filled on the copy stream
@@ -1126,6 +1128,8 @@ int aq_create(int device, aq_ctx** out) {
     delete c;
     return fail(nullptr, AQ_ERR_CUDA, "init (%s): %s", what, cudaGetErrorString(e));
   }
+  // set-up for aq_tile_stats_static (device `device` is current): the static scratch array's address on this device
+  c->stats_static_err = tile_stats_static_scratch(&c->stats_static);
   *out = c;
   return AQ_OK;
 }
@@ -1983,6 +1987,34 @@ int aq_tile_stats(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, 
   if (!stats_host) return AQ_OK;  // kernels only (timing): nothing is copied, the stream is not synchronised
   CU_CHECK(c, cudaMemcpyAsync(stats_host, st, (size_t)n * sizeof(TileStats), cudaMemcpyDeviceToHost, s));
   CU_CHECK(c, cudaStreamSynchronize(s));
+  return AQ_OK;
+}
+
+// aq_tile_stats without any allocation: column sums in the library's static __device__ array, results written to the
+// caller's DEVICE buffer, nothing copied, nothing synchronised.  No counterpart in the reference (added
+// for callers that cannot call cudaMalloc: graph capture, tight serving loops).
+int aq_tile_stats_static(aq_ctx* c, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w, int win0,
+                         int* stats_dev, void* stream) {
+  if (!c || !src_dev || !stats_dev || n <= 0 || in_h <= 0 || in_w <= 0) return AQ_ERR_ARG;
+  if ((long long)n * in_w > (long long)kTileStatsStaticCols)
+    return fail(c, AQ_ERR_ARG, "tile_stats_static: n * in_w = %d * %d = %lld columns exceed the static scratch of %d (AQ_TILE_STATS_STATIC_MAX_COLS); use aq_tile_stats",
+                n, in_w, (long long)n * in_w, kTileStatsStaticCols);
+  if (c->stats_static_err != cudaSuccess || !c->stats_static)
+    return fail(c, AQ_ERR_CUDA, "tile_stats_static: the static scratch could not be resolved at aq_create: %s", cudaGetErrorString(c->stats_static_err));
+  cudaSetDevice(c->device);
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  PreParams p{};
+  p.src = src_dev; p.n = n; p.bgr = bgr; p.in_h = in_h; p.in_w = in_w;
+  p.row_pitch = (size_t)in_w * 3; p.wins_y = 1;
+  if (raster_h > 0) {  // windows of a raster
+    const int wins_x = raster_w / in_w, wins_y = raster_h / in_h;
+    if (raster_h < in_h || raster_w < in_w || win0 < 0 || win0 + n > wins_x * wins_y)
+      return fail(c, AQ_ERR_ARG, "tile_stats_static: windows [%d, %d) outside the %d x %d grid", win0, win0 + n, wins_x, wins_y);
+    p.row_pitch = (size_t)raster_w * 3; p.windowed = 1; p.wins_y = wins_y; p.win0 = win0;
+  }
+  // launch_tile_stats clears the n * in_w column sums it uses (cudaMemsetAsync on `stream`) and initialises stats_dev
+  cudaError_t e = launch_tile_stats(p, c->stats_static, reinterpret_cast<TileStats*>(stats_dev), s);
+  if (e != cudaSuccess) return fail(c, e == cudaErrorInvalidValue ? AQ_ERR_UNSUPPORTED : AQ_ERR_CUDA, "tile_stats_static: %s (tiles up to 2048 x 4096)", cudaGetErrorString(e));
   return AQ_OK;
 }
 

@@ -413,6 +413,27 @@ cudaError_t launch_tile_stats(const PreParams& p, unsigned int* col_sums, TileSt
   return cudaGetLastError();
 }
 
+// Scratch of aq_tile_stats_static (see aux_kernels.cuh): shared by every call on this device, keeps the last call's contents
+// (launch_tile_stats clears the part it uses), so calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned int g_tile_stats_cols[kTileStatsStaticCols];
+
+cudaError_t tile_stats_static_scratch(unsigned int** ptr) {
+  constexpr int kMaxDev = 64;
+  static unsigned int* cache[kMaxDev] = {};  // device address per device; written once per device at context set-up
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+  if (!cache[dev]) {
+    unsigned int* a = nullptr;
+    e = cudaGetSymbolAddress((void**)&a, g_tile_stats_cols);  // NOT &g_tile_stats_cols: that is a host address
+    if (e != cudaSuccess) return e;
+    cache[dev] = a;
+  }
+  *ptr = cache[dev];
+  return cudaSuccess;
+}
+
 cudaError_t sppf_init() {
   cudaError_t e = cudaFuncSetAttribute(sppf_pool_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   if (e != cudaSuccess) return e;

@@ -39,6 +39,13 @@ struct TileStats {
 // `col_sums` is scratch of n * in_w uint32 (zeroed by the call); stats is a device array of n entries.
 cudaError_t launch_tile_stats(const PreParams& p, unsigned int* col_sums, TileStats* stats, cudaStream_t stream);
 
+// Allocation-free blank-tile statistics (aq_tile_stats_static): the column sums live in a file-scope __device__ array of
+// kTileStatsStaticCols uint32 (512 KB, held by every GPU that loads the library until the process exits) instead of
+// cudaMalloc'd scratch.  tile_stats_static_scratch resolves the array's DEVICE address for the CURRENT device
+// (cudaGetSymbolAddress; the array's name in host code is only a host-side stand-in) -- once per device, cached.
+constexpr int kTileStatsStaticCols = 131072;  // n * in_w of one call, e.g. 64 tiles of 2048 columns
+cudaError_t tile_stats_static_scratch(unsigned int** ptr);
+
 // SPPF: three chained 5x5/s1/p2 max pools of channels [c_off, c_off+c) written to the next three slices.
 cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream);
 cudaError_t sppf_init();

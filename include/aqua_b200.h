@@ -415,6 +415,25 @@ int aq_preprocess_windows_u8(aq_ctx* ctx, const uint8_t* raster_dev, int raster_
  */
 int aq_tile_stats(aq_ctx* ctx, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h, int raster_w,
                   int win0, int* stats_host, void* stream);
+
+/*
+ * aq_tile_stats for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same arguments
+ * and results as aq_tile_stats, except that
+ *   - the column-sum scratch is a file-scope static __device__ array inside the library (512 KB, held by every GPU that
+ *     loads the library until the process exits); its device address is resolved once per device at aq_create;
+ *   - n * in_w must not exceed AQ_TILE_STATS_STATIC_MAX_COLS (e.g. 64 tiles 2048 wide, 128 tiles 1024 wide); larger
+ *     requests return AQ_ERR_ARG with a message naming the limit -- use aq_tile_stats for those;
+ *   - stats_dev is a DEVICE buffer of n x 4 int32 owned by the caller; nothing is copied to the host and `stream` is
+ *     not synchronised;
+ *   - the call performs no cudaMalloc / cudaFree and calls no allocating library routine: one cudaMemsetAsync (the
+ *     part of the shared array it uses must start at zero) and four kernel launches on `stream`.
+ * Every call on a device shares the one array: calls that overlap on the GPU (different streams, two contexts of one
+ * device) race on it; order them on one stream or with events.
+ */
+#define AQ_TILE_STATS_STATIC_MAX_COLS 131072
+int aq_tile_stats_static(aq_ctx* ctx, const uint8_t* src_dev, int n, int in_h, int in_w, int bgr, int raster_h,
+                         int raster_w, int win0, int* stats_dev, void* stream);
 /* cudaMemcpyAsync wrapper so hosts without a CUDA binding can move test data: kind 0=H2D 1=D2H 2=D2D. */
 int aq_memcpy(aq_ctx* ctx, void* dst, const void* src, size_t bytes, int kind, void* stream);
 int aq_sync(aq_ctx* ctx, void* stream);

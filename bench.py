@@ -228,11 +228,16 @@ def extra_configs(sd, local, stream_arg, steps):
         ms_step = timed(lambda i: det.detect_submit(t, bgr=True, src_is_device=True, stream=stream_arg), n)
         det.ctx.sync()
         ms_fwd = timed(lambda i: det.ctx.call("aq_forward", stream_arg), n)
+        # the three Speed: stages of one batch at this shape (device time, CUDA events): NMS runs one CTA per image, 16 here
+        det.stage_ms, det.stage_tiles = [0.0, 0.0, 0.0], 0
+        det.detect(t, bgr=True, src_is_device=True)
+        st5 = [round(v, 4) for v in det.stage_ms] if det.stage_tiles == B5 else None
         fl = arch.conv_flops_per_tile(I5, I5, NC) * B5
         ach = fl / (ms_fwd * 1e-3) / 1e12
         out["img1280"] = {"config": "configs[4]: --img 1280, batch 16 fp16, resident tiles, conf 0.25 / IoU 0.45", "tiles_per_s": round(B5 / ms_step * 1e3, 1),
                           "ms_per_step": round(ms_step, 4), "ms_per_conv_stack": round(ms_fwd, 4), "achieved_tflops": round(ach, 1),
                           "frac_of_burst": round(ach / peaks["burst"], 4), "frac_of_sustained": round(ach / peaks["sustained"], 4),
+                          "stage_ms_one_batch": {"pre_process": st5[0], "inference": st5[1], "nms": st5[2]} if st5 else None,
                           "detections_last_batch": int(det._counts[0][:B5].sum() if det._counts else 0), "launches": det.n_launches}
         det.close()
     except Exception as e:  # noqa: BLE001

@@ -298,8 +298,8 @@ __global__ void __launch_bounds__(256) tile_stats_finish(const unsigned int* col
 // ---------------------------------------------------------------- SPPF pooling
 // grid (c / CG, n); the CTA keeps an (h*w) x CG-channel slab in shared memory and runs three separable
 // 5x5 max pools (horizontal then vertical), writing each result to its concat slice.
-// kPoolV = 16-byte vectors per pixel per CTA: 4 (64 contiguous bytes = two full 32-byte sectors) while the slab fits
-// shared memory (20x20 maps of the 640 configs), 1 for larger maps (40x40 at --img 1280, up to 4266 pixels).
+// kPoolV = 16-byte vectors per pixel per CTA: 4 (64 contiguous bytes = two full 32-byte sectors) for the 20x20 maps of the 640
+// configs, 2 for the 40x40 maps of --img 1280, 1 for anything larger or for channel counts that are no multiple of 16.
 
 __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
   uint4 r;
@@ -311,47 +311,62 @@ __device__ __forceinline__ uint4 hmax8(uint4 a, uint4 b) {
   return r;
 }
 
+// One 5-wide clipped max along the lines of a map held in shared memory: out[i] = max(in[i - 2 .. i + 2] inside the line).  A thread
+// owns (segment of a line, 8-channel vector) and slides a five-value window kept in registers along it: one shared-memory read
+// and one write per element (the first version re-read every neighbour from shared memory and was bound by that bandwidth).
+// kGlobal: the result also goes to the tensor (the pool's output slice); `elem_of(line, i)` = pixel index of element i of a line.
+template <int kPoolV, bool kRows, bool kGlobal>
+__device__ __forceinline__ void sppf_line_pass(const uint4* in, uint4* out, int h, int w, int pitch, __half* gbase, int ct) {
+  const int lines = kRows ? h : w, len = kRows ? w : h;
+  const int stride_line = kRows ? pitch : kPoolV, stride_elem = kRows ? kPoolV : pitch;
+  const int per = lines * kPoolV;
+  const int segs = (int)blockDim.x / per > 0 ? (int)blockDim.x / per : 1;
+  const int seg = (len + segs - 1) / segs;
+  const uint4 neg = make_uint4(0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u);  // -inf: the identity of max (clipped windows)
+  for (int t = threadIdx.x; t < per * segs; t += blockDim.x) {
+    const int v = t % kPoolV, line = (t / kPoolV) % lines, sg = t / per;
+    const int i0 = sg * seg, i1 = i0 + seg < len ? i0 + seg : len;
+    if (i0 >= i1) continue;
+    const uint4* src = in + line * stride_line + v;
+    uint4* dst = out + line * stride_line + v;
+    auto at = [&](int i) { return i >= 0 && i < len ? src[i * stride_elem] : neg; };
+    uint4 a = at(i0 - 2), b = at(i0 - 1), c = at(i0), d = at(i0 + 1);
+    for (int i = i0; i < i1; ++i) {
+      const uint4 e = at(i + 2);
+      const uint4 m = hmax8(hmax8(hmax8(a, b), hmax8(c, d)), e);
+      dst[i * stride_elem] = m;
+      if (kGlobal) {
+        const int pix = kRows ? line * w + i : i * w + line;
+        *reinterpret_cast<uint4*>(gbase + (size_t)pix * ct + v * 8) = m;
+      }
+      a = b; b = c; c = d; d = e;
+    }
+  }
+}
+
+// SPPF's three chained 5x5 / stride 1 / pad 2 max pools of one (image, 8 kPoolV channels) slab, the map in shared memory (rows
+// padded by one vector group: conflict-free row walks): per pool a row pass and a column pass, the column pass writing the slice.
 template <int kPoolV>
 __global__ void __launch_bounds__(256) sppf_pool_kernel(__half* buf, int h, int w, int ct, int c_off, int c) {
   constexpr int kPoolCG = 8 * kPoolV;  // channels per CTA
   extern __shared__ uint4 s_pool[];
   const int hw = h * w, nv = hw * kPoolV;  // element i = pixel (i / kPoolV), vector (i % kPoolV)
+  const int pitch = (w + 1) * kPoolV;
   uint4* s0 = s_pool;
-  uint4* s1 = s_pool + nv;
-  uint4* tmp = s_pool + 2 * nv;
+  uint4* s1 = s_pool + h * pitch;
   const int cg = blockIdx.x;
   const int n = blockIdx.y;
   __half* base = buf + (size_t)n * hw * ct + c_off + cg * kPoolCG;
-  for (int i = threadIdx.x; i < nv; i += blockDim.x)
-    s0[i] = *reinterpret_cast<const uint4*>(base + (size_t)(i / kPoolV) * ct + (i % kPoolV) * 8);
+  for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+    const int pix = i / kPoolV, y = pix / w, x = pix - y * w;
+    s0[y * pitch + x * kPoolV + (i % kPoolV)] = *reinterpret_cast<const uint4*>(base + (size_t)pix * ct + (i % kPoolV) * 8);
+  }
   __syncthreads();
-  uint4* src = s0;
-  uint4* dst = s1;
   for (int pass = 1; pass <= 3; ++pass) {
-    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
-      const int pix = i / kPoolV;
-      const int y = pix / w, x = pix - y * w;
-      uint4 m = src[i];
-      for (int d = 1; d <= 2; ++d) {
-        if (x - d >= 0) m = hmax8(m, src[i - d * kPoolV]);
-        if (x + d < w) m = hmax8(m, src[i + d * kPoolV]);
-      }
-      tmp[i] = m;
-    }
+    sppf_line_pass<kPoolV, true, false>(s0, s1, h, w, pitch, nullptr, 0);
     __syncthreads();
-    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
-      const int pix = i / kPoolV;
-      const int y = pix / w;
-      uint4 m = tmp[i];
-      for (int d = 1; d <= 2; ++d) {
-        if (y - d >= 0) m = hmax8(m, tmp[i - d * w * kPoolV]);
-        if (y + d < h) m = hmax8(m, tmp[i + d * w * kPoolV]);
-      }
-      dst[i] = m;
-      *reinterpret_cast<uint4*>(base + (size_t)pix * ct + (i % kPoolV) * 8 + (size_t)pass * c) = m;
-    }
+    sppf_line_pass<kPoolV, false, true>(s1, s0, h, w, pitch, base + (size_t)pass * c, ct);
     __syncthreads();
-    uint4* t = src; src = dst; dst = t;
   }
 }
 
@@ -437,15 +452,21 @@ cudaError_t tile_stats_static_scratch(unsigned int** ptr) {
 cudaError_t sppf_init() {
   cudaError_t e = cudaFuncSetAttribute(sppf_pool_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(sppf_pool_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(sppf_pool_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 cudaError_t launch_sppf_pool(__half* buf, int n, int h, int w, int ct, int c_off, int c, cudaStream_t stream) {
-  const size_t smem1 = (size_t)3 * h * w * sizeof(uint4);  // one 8-channel vector per pixel
-  if (4 * smem1 <= 200 * 1024 && (c % 32) == 0) {
+  const size_t smem1 = (size_t)2 * h * (w + 1) * sizeof(uint4);  // two maps, one 8-channel vector per pixel, rows padded by one
+  // 32 channels x 256 threads per CTA measured best at 20x20 (29.0 us per 64 images; 16 / 8 channels or 64 - 128 threads: 31 - 46 us),
+  // 16 channels at 40x40 (39 us at batch 16)
+  if (4 * smem1 <= 100 * 1024 && (c % 32) == 0) {  // two CTAs per SM
     sppf_pool_kernel<4><<<dim3(c / 32, n), 256, 4 * smem1, stream>>>(buf, h, w, ct, c_off, c);
+  } else if (2 * smem1 <= 110 * 1024 && (c % 16) == 0) {
+    sppf_pool_kernel<2><<<dim3(c / 16, n), 256, 2 * smem1, stream>>>(buf, h, w, ct, c_off, c);
   } else {
-    if (smem1 > 200 * 1024 || (c % 8) != 0) return cudaErrorInvalidValue;  // maps beyond 4266 pixels: not supported
+    if (smem1 > 200 * 1024 || (c % 8) != 0) return cudaErrorInvalidValue;  // maps beyond ~6000 pixels: not supported
     sppf_pool_kernel<1><<<dim3(c / 8, n), 256, smem1, stream>>>(buf, h, w, ct, c_off, c);
   }
   return cudaGetLastError();

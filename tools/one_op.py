@@ -16,6 +16,10 @@ ap.add_argument("--tile-n", type=int, default=0)
 ap.add_argument("--cluster", type=int, default=0)
 ap.add_argument("--act", type=int, default=2)
 ap.add_argument("--iters", type=int, default=10)
+ap.add_argument("--src-ct", type=int, default=0, help="channels of the source buffer (the conv reads the slice [src_off, src_off + c_in))")
+ap.add_argument("--src-off", type=int, default=0)
+ap.add_argument("--dst-ct", type=int, default=0)
+ap.add_argument("--dst-off", type=int, default=0)
 a = ap.parse_args()
 B, H, W, ci, co, k, s = a.shape
 g = torch.Generator().manual_seed(0)
@@ -23,12 +27,13 @@ w = (torch.randn(co, ci, k, k, generator=g) / math.sqrt(ci * k * k))
 b = torch.randn(co, generator=g) * 0.5
 ctx = engine.Context(0)
 ctx.plan_begin(B, 64, 64, 3)
-bs = ctx.buffer(H, W, ci)
-bd = ctx.buffer(H // s, W // s, co)
-ctx.conv((bs, 0), (bd, 0), w, b, k, s, a.act, (bd, 0) if a.res else None, a.tile_n, a.mblk, a.mode, a.cluster)
+sct, dct = a.src_ct or ci, a.dst_ct or co
+bs = ctx.buffer(H, W, sct)
+bd = ctx.buffer(H // s, W // s, dct)
+ctx.conv((bs, a.src_off), (bd, a.dst_off), w, b, k, s, a.act, (bd, a.dst_off) if a.res else None, a.tile_n, a.mblk, a.mode, a.cluster)
 ctx.plan_end()
-x = torch.randn(1, H, W, ci, generator=g).half().numpy()
-ctx.upload(bs, np.ascontiguousarray(np.broadcast_to(x, (B, H, W, ci))))
+x = torch.randn(1, H, W, sct, generator=g).half().numpy()
+ctx.upload(bs, np.ascontiguousarray(np.broadcast_to(x, (B, H, W, sct))))
 ms = (C.c_float * 1)()
 ctx.call("aq_profile_ops", a.iters, ms, 1)
 buf = C.create_string_buffer(600)

@@ -473,6 +473,8 @@ def run(opt, argv) -> int:
     finish()
     stage_ms, stage_tiles = [0.0, 0.0, 0.0], 0
     for d in detectors.values():
+        if d.stage_tiles == 0:  # a detector that saw one batch only: its (warm-up) batch is all there is
+            d.stage_ms, d.stage_tiles = d.first_stage_ms, d.first_stage_tiles
         stage_ms = [a + b for a, b in zip(stage_ms, d.stage_ms)]
         stage_tiles += d.stage_tiles
         d.close()

@@ -247,7 +247,8 @@ class TileDetector:
         self.act = AQ_ACT_SILU if os.environ.get("AQUA_SILU", "fast") == "exact" else AQ_ACT_SILU_FAST
         self.ctx = ctx if ctx is not None else Context(device)   # `ctx` lets tests inject the plan emulator
         self._build(state_dict)
-        self.stage_ms = [0.0, 0.0, 0.0]  # device time of pre-process / inference / NMS summed over the waited batches
+        self.stage_ms = [0.0, 0.0, 0.0]  # device time of pre-process / inference / NMS summed over the waited batches (not the first)
+        self.first_stage_ms, self.first_stage_tiles = [0.0, 0.0, 0.0], 0
         self.stage_tiles = 0
         self._dets = self._counts = None  # pinned host staging, double-buffered, allocated on first use
         self._slot = 0
@@ -520,15 +521,24 @@ class TileDetector:
         self._pin_i[key] = i ^ 1
         return self._pin[key][i][:n]
 
+    def _add_stage_ms(self, ticket: int, n: int):
+        """Upstream's three `Speed:` stages of one batch (aq_detect_stage_ms: CUDA events on the compute stream).  The first
+        batch of a detector's life is kept apart (`first_stage_ms`): its stages contain one-time work (NMS scratch and output
+        buffers are allocated between the events) -- upstream warms the model up before it starts its timers too."""
+        ms = (C.c_float * 3)()
+        self.ctx.call("aq_detect_stage_ms", ticket, ms)
+        if self.first_stage_tiles == 0:
+            self.first_stage_ms, self.first_stage_tiles = [ms[0], ms[1], ms[2]], n
+            return
+        for k in range(3):
+            self.stage_ms[k] += ms[k]
+        self.stage_tiles += n
+
     def detect_wait(self, ticket, stream=None) -> Detections:
         """Results of one submitted batch (views of the pinned slot: copy them before the slot's next submit)."""
         slot, n, t = ticket
         self.ctx.call("aq_detect_wait", t)
-        ms = (C.c_float * 3)()
-        self.ctx.call("aq_detect_stage_ms", t, ms)  # upstream's three Speed: stages, CUDA events on the compute stream
-        for k in range(3):
-            self.stage_ms[k] += ms[k]
-        self.stage_tiles += n
+        self._add_stage_ms(t, n)
         self._inflight[slot] = None
         return Detections(self._dets[slot][:n].numpy(), self._counts[slot][:n].numpy())
 
@@ -549,11 +559,7 @@ class TileDetector:
                       int(bgr), self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
                       len(self.classes) if self.classes else 0, C.c_void_p(self._dets[0].data_ptr()),
                       C.c_void_p(self._counts[0].data_ptr()), None)
-        ms = (C.c_float * 3)()
-        self.ctx.call("aq_detect_stage_ms", slot, ms)
-        for k in range(3):
-            self.stage_ms[k] += ms[k]
-        self.stage_tiles += n
+        self._add_stage_ms(slot, n)
         return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
 
     def detect_window_list(self, raster: torch.Tensor, tile: int, win_idx: Sequence[int], bgr=True) -> Detections:
@@ -572,11 +578,7 @@ class TileDetector:
                              int(bgr), self.conf_thres, self.iou_thres, self.max_det, int(self.agnostic), cls_arr,
                              len(self.classes) if self.classes else 0, C.c_void_p(self._dets[0].data_ptr()),
                              C.c_void_p(self._counts[0].data_ptr()), None)
-        ms = (C.c_float * 3)()
-        self.ctx.call("aq_detect_stage_ms", slot, ms)
-        for k in range(3):
-            self.stage_ms[k] += ms[k]
-        self.stage_tiles += n
+        self._add_stage_ms(slot, n)
         return Detections(self._dets[0][:n].numpy().copy(), self._counts[0][:n].numpy().copy())
 
     def close(self):
